@@ -1,0 +1,165 @@
+/* include/b2pt.h -- the drop-in C ABI of the B200-native BDPT path (libb2pt.so).
+ *
+ * Plain C: pointers, sizes and PODs only; no C++/torch types cross this boundary.  Every
+ * entry point returns 0 on success or a negative B2_ERR_* code; b2_last_error() gives the
+ * thread-local message.  There is NO CPU fallback: without a CUDA device every compute call
+ * fails with B2_ERR_NO_DEVICE.
+ *
+ * Reference interfaces replaced (paths relative to the reference repository):
+ *   b2_scene_create / b2_scene_build_bvh  <- move_data_to_cuda_bdpt(groups, lights, spl)   include/bdpt_cu_helper.h:5,
+ *                                            src/bdpt_cu_helper.cpp:13-68 (flatten groups -> POD arrays)
+ *   b2_render_bdpt                        <- run_cuda_bdpt(cam, image, ...)                include/bdpt_cu_helper.h:6
+ *                                            and run_cpu_bdpt(camera, groups, lights, ...) include/cpu_bdpt.h:9-17
+ *                                            (the estimator reproduced is the CPU one, src/cpu_bdpt.cpp:173-488)
+ *   b2_intersect (closest)                <- cpu_find_closest_hit                          src/cpu_bdpt.cpp:30-80
+ *   b2_intersect (any)                    <- cpu_check_visibility                          src/cpu_bdpt.cpp:82-107
+ *   b2_bsdf_evaluate / _pdf / _sample     <- bsdf_evaluate / bsdf_pdf / bsdf_sample        include/geometric.cuh:419-562
+ *   b2_mis_weight                         <- cpu_calculate_mis_weight                      src/cpu_bdpt.cpp:112-167
+ *   b2_parse_scene_file                   <- the scene grammar loop                        src/main_cli.cpp:99-141
+ *   b2_film_to_rgb8 / b2_write_image      <- clamp -> gamma 2.2 -> 8-bit + cv::imwrite     src/main_cli.cpp:221-254
+ */
+#ifndef B2PT_H
+#define B2PT_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2_OK 0
+#define B2_ERR_INVALID   (-1)
+#define B2_ERR_NO_DEVICE (-2)
+#define B2_ERR_CUDA      (-3)
+#define B2_ERR_OOM       (-4)
+#define B2_ERR_IO        (-5)
+#define B2_ERR_STATE     (-6)
+
+typedef struct B2Scene B2Scene;
+
+/* Material, include/object.h:28-33 */
+typedef struct B2Material { float base_color[3]; float roughness, metallic, eta; } B2Material;
+/* Triangle, include/object.h:68-80.  obj_id = the file-order counter shared with spheres (main_cli.cpp:109,118);
+ * group = key of the std::map<int,AABB> group it was added to (main_cli.cpp:110,119,126). */
+typedef struct B2Tri { float v0[3], v1[3], v2[3]; int32_t obj_id, group, material; } B2Tri;
+/* Sphere, include/object.h:54-66 (scale is always (1,1,1) on this path, main_cli.cpp:107) */
+typedef struct B2Sphere { float center[3]; float r; int32_t obj_id, group, material; } B2Sphere;
+/* CudaLight, include/geometric.cuh:73-78 as main_cli.cpp:131-139 fills it; cutoff in RADIANS. */
+typedef struct B2Light { float pos[3], dir[3], illum[3]; float cutoff; int32_t is_parallel; float ball_r; } B2Light;
+/* Camera, include/object.h:104-110 (fov in degrees; run_cpu_bdpt uses camera.fov, cpu_bdpt.cpp:191) */
+typedef struct B2Camera { float eye[3], look_at[3], view_up[3]; float fov; } B2Camera;
+
+typedef struct B2BvhParams {
+    int32_t max_leaf_tris;  /* 1..3 triangles per leaf child (0 = default 3) */
+    float   pad_rel;        /* relative padding of triangle boxes (0 = default 2^-18 of the coordinate magnitude) */
+} B2BvhParams;
+
+typedef struct B2BvhInfo {
+    uint64_t n_tris, n_nodes, node_bytes, tri_bytes;
+    int32_t  depth;
+    float    build_ms;      /* device time of the last build (CUDA events) */
+    float    sah_cost;      /* SAH cost of the wide tree (root area normalised) */
+} B2BvhInfo;
+
+#define B2_FILM_MEAN 0  /* film = sum / spp  (what run_cpu_bdpt writes, cpu_bdpt.cpp:479) */
+#define B2_FILM_SUM  1  /* film = raw sum of this shard's samples (for multi-GPU reduction) */
+#define B2_STRATEGIES_REFERENCE 0 /* exactly the strategy set of cpu_bdpt.cpp (parity mode) */
+#define B2_STRATEGIES_FULL      1 /* + t=1 light-tracing splats (not part of the reference estimator) */
+
+typedef struct B2RenderParams {
+    int32_t  width, height;
+    int32_t  spp;            /* total samples per pixel of the whole job */
+    int32_t  spl;            /* light subpaths per light per render (cpu_bdpt.cpp:202) */
+    int32_t  eye_depth, light_depth;
+    uint64_t seed;           /* Philox key */
+    int32_t  sample_offset;  /* this call renders samples s = sample_offset + k*sample_stride < spp */
+    int32_t  sample_stride;  /* (1-GPU: 0,1; G GPUs: g,G) */
+    int32_t  film_mode;      /* B2_FILM_MEAN / B2_FILM_SUM */
+    int32_t  strategies;     /* B2_STRATEGIES_* */
+    int32_t  max_delta;      /* cap on delta bounces per subpath (0 = default 256) */
+    int32_t  max_batch_paths;/* eye paths in flight per wavefront batch (0 = default 2^22) */
+    int32_t  count_traversal;/* !=0: use the counting traversal variant and fill node/tri visit counters */
+    int32_t  reserved;
+} B2RenderParams;
+
+typedef struct B2Stats {
+    uint64_t eye_samples;     /* (pixel, s) iterations, cpu_bdpt.cpp:349 */
+    uint64_t closest_rays;    /* closest-hit queries (eye + light subpaths) */
+    uint64_t shadow_rays;     /* visibility queries, cpu_bdpt.cpp:424 */
+    uint64_t path_samples;    /* connections reaching the MIS evaluation (:431) + depth-0 emitter hits (:372) */
+    uint64_t delta_cap_hits;
+    uint64_t nodes_visited;   /* only with count_traversal */
+    uint64_t tris_tested;     /* only with count_traversal */
+    uint64_t n_batches, n_waves, n_launches;
+    float    ms_total;        /* device time of the call, CUDA events */
+    float    ms_light_pool, ms_closest, ms_shade, ms_connect, ms_shadow, ms_other; /* per-stage device time (profiling runs only) */
+} B2Stats;
+
+/* ---- library / device ---- */
+const char *b2_last_error(void);
+int b2_device_count(int *count);
+const char *b2_version(void);
+
+/* ---- scene ---- */
+int b2_scene_create(const B2Tri *tris, size_t n_tris, const B2Sphere *spheres, size_t n_spheres,
+                    const B2Material *materials, size_t n_materials, const B2Light *lights, size_t n_lights,
+                    int device, B2Scene **out);
+int b2_scene_build_bvh(B2Scene *scene, const B2BvhParams *params);
+int b2_scene_bvh_info(const B2Scene *scene, B2BvhInfo *info);
+void b2_scene_destroy(B2Scene *scene);
+
+/* ---- ray queries (host buffers; copies are part of the call) ----
+ * mode B2_CLOSEST: org/dir are n*3 floats; prim_id = obj_id, -2-k for light ball k, -1 miss; t = 1e20 on a miss.
+ * mode B2_ANY    : org = p1, dir = p2 (segment end points, cpu_check_visibility's arguments);
+ *                  prim_id = 1 if unoccluded else 0; t is not written (may be NULL).
+ * mode | B2_BRUTE_FORCE uses the exhaustive kernel instead of the BVH (parity cross-check). */
+#define B2_CLOSEST 0
+#define B2_ANY 1
+#define B2_BRUTE_FORCE 16
+#define B2_COUNT_VISITS 32
+int b2_intersect(B2Scene *scene, const float *org, const float *dir, size_t n, int mode, int32_t *prim_id, float *t);
+/* Same on device pointers (float3-packed arrays already resident in HBM), asynchronous on `stream` (cudaStream_t). */
+int b2_intersect_device(B2Scene *scene, const float *d_org, const float *d_dir, size_t n, int mode,
+                        int32_t *d_prim_id, float *d_t, void *stream);
+/* Visit counters accumulated by B2_COUNT_VISITS launches since the last reset: out[0]=rays, [1]=nodes, [2]=tris. */
+int b2_intersect_counters(B2Scene *scene, uint64_t out[3], int reset);
+
+/* ---- render ---- */
+int b2_render_bdpt(B2Scene *scene, const B2Camera *cam, const B2RenderParams *params, float *film_rgb_host,
+                   B2Stats *stats);
+/* Film stays on the device (W*H*3 fp32, caller-owned, e.g. a torch tensor); work is enqueued on `stream`
+ * and the call returns after the stream has drained its own work (stats need the counters). */
+int b2_render_bdpt_device(B2Scene *scene, const B2Camera *cam, const B2RenderParams *params, float *d_film_rgb,
+                          void *stream, B2Stats *stats);
+/* The light-vertex pool the render would use: n_lights*spl*light_depth vertices x 20 floats
+ * (pos3 normal3 thr3 mtl6 is_light_source is_parallel source_cutoff pdf_fwd pdf_rev), cpu_bdpt.cpp:202-325. */
+int b2_light_pool(B2Scene *scene, const B2RenderParams *params, float *pool20_host);
+
+/* ---- BSDF / MIS / RNG tables (device kernels over host arrays; parity tests) ---- */
+int b2_bsdf_evaluate(size_t n, const float *mtl6, const float *wo, const float *wi, const float *N, float *out3);
+int b2_bsdf_pdf(size_t n, const float *mtl6, const float *wo, const float *wi, const float *N, float *out);
+int b2_bsdf_sample(size_t n, const float *mtl6, const float *wo, const float *N, const float *u3, const float *cur_eta,
+                   float *wi_out, float *f_out, float *pdf_out, int32_t *delta_out, float *eta_out);
+int b2_mis_weight(size_t n, const float *eye17, const int32_t *n_eye, const int32_t *s_idx, const float *lit20,
+                  const int32_t *n_lit, const int32_t *t_idx, const float *d_vec, const float *dist2,
+                  const float *cam_pos, int32_t max_verts, float *out);
+int b2_philox(size_t n, const uint32_t *ctr4, const uint32_t *key2, uint32_t *out4, float *unit_out4);
+
+/* ---- host-side surface kept from the reference (no GPU needed) ---- */
+typedef struct B2ParsedScene {
+    size_t n_tris, n_spheres, n_materials, n_lights;
+    B2Tri *tris; B2Sphere *spheres; B2Material *materials; B2Light *lights;
+    B2Camera camera;
+    int32_t width, height;  /* the scene's R line */
+} B2ParsedScene;
+int b2_parse_scene_file(const char *path, B2ParsedScene **out);
+void b2_parsed_scene_free(B2ParsedScene *p);
+/* clamp [0,1] -> pow(1/2.2) -> *255 truncated, RGB order, rows top to bottom (main_cli.cpp:225-243) */
+int b2_film_to_rgb8(const float *film_rgb, int32_t width, int32_t height, uint8_t *rgb8);
+/* format from the extension: .ppm (P6), .png (zlib deflate), .pfm (raw float) */
+int b2_write_image(const char *path, const float *film_rgb, int32_t width, int32_t height);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2PT_H */

@@ -1,0 +1,173 @@
+// b2_bsdf.cuh -- BSDF evaluate / pdf / sample of the reference material model, re-authored for the device.
+// Follows include/geometric.cuh:119-221 (frame, Fresnel, GGX) and :419-562 (bsdf_evaluate / bsdf_pdf /
+// bsdf_sample), including its quirks (SURVEY.md 8a rows M,N,O): F == 1 for eta == 0 non-metals through
+// the TIR branch of FrDielectric, the 1e-7 regularisers, delta lobes returning f without cos/pdf.
+// FMA contraction is allowed here: parity of shading values is to ~1e-6 relative, not bitwise.
+#pragma once
+#include "b2_common.cuh"
+
+struct Mat { float3 base; float roughness, metallic, eta; };   // CudaMaterial, geometric.cuh:21-27
+
+struct Frame { float3 T, B, N; };
+B2_HD Frame make_frame(float3 N) {                              // build_local_frame, :119-123
+    Frame f; f.N = N;
+    if (fabsf(N.z) < 0.999f) f.T = normalize3(cross3(mk3(0, 0, 1), N));
+    else f.T = normalize3(cross3(mk3(0, 1, 0), N));
+    f.B = cross3(N, f.T);
+    return f;
+}
+B2_HD float3 to_local(const Frame &f, float3 v) { return mk3(dot3(v, f.T), dot3(v, f.B), dot3(v, f.N)); }
+B2_HD float3 to_world(const Frame &f, float3 v) {
+    return mk3(f.T.x * v.x + f.B.x * v.y + f.N.x * v.z, f.T.y * v.x + f.B.y * v.y + f.N.y * v.z, f.T.z * v.x + f.B.z * v.y + f.N.z * v.z);
+}
+
+B2_HD float fr_dielectric(float cosI, float etaI, float etaT) {  // :145-160
+    cosI = fmaxf(-1.0f, fminf(1.0f, cosI));
+    if (!(cosI > 0.0f)) { float t = etaI; etaI = etaT; etaT = t; cosI = fabsf(cosI); }
+    float sinI = sqrtf(fmaxf(0.0f, 1.0f - cosI * cosI));
+    float sinT = etaI / etaT * sinI;
+    if (sinT >= 1.0f) return 1.0f;
+    float cosT = sqrtf(fmaxf(0.0f, 1.0f - sinT * sinT));
+    float Rparl = ((etaT * cosI) - (etaI * cosT)) / ((etaT * cosI) + (etaI * cosT));
+    float Rperp = ((etaI * cosI) - (etaT * cosT)) / ((etaI * cosI) + (etaT * cosT));
+    return (Rparl * Rparl + Rperp * Rperp) / 2.0f;
+}
+B2_HD float3 fr_schlick(float cosI, float3 R0) {                 // :163-167
+    float c = fmaxf(0.0f, 1.0f - cosI);
+    float c5 = c * c * c * c * c;
+    return R0 + (mk3(1.0f, 1.0f, 1.0f) - R0) * c5;
+}
+B2_HD float roughness_to_alpha(float r) { float x = fmaxf(r, 1e-3f); return x * x; }   // :173
+B2_HD float tr_D(float3 wh, float alpha) {                       // :178-185
+    float cos2 = wh.z * wh.z;
+    float tan2 = fmaxf(0.0f, 1.0f - cos2) / (cos2 + 1e-7f);
+    if (isinf(tan2)) return 0.0f;
+    float e = (cos2 * cos2) * (alpha * alpha + tan2 * tan2);
+    if (e < 1e-12f) return 0.0f;
+    return (alpha * alpha) / (B2_PI * e);
+}
+B2_HD float tr_lambda(float3 w, float alpha) {                   // :187-192
+    float t = fabsf(sqrtf(fmaxf(0.0f, 1.0f - w.z * w.z)) / (w.z + 1e-7f));
+    if (isinf(t)) return 0.0f;
+    float a2t2 = (alpha * t) * (alpha * t);
+    return (-1.0f + sqrtf(1.0f + a2t2)) / 2.0f;
+}
+B2_HD float tr_G(float3 wo, float3 wi, float alpha) { return 1.0f / (1.0f + tr_lambda(wo, alpha) + tr_lambda(wi, alpha)); }
+B2_HD float3 sample_vndf(float3 wo, float alpha, float u1, float u2) {  // :200-221
+    float3 V = normalize3(mk3(alpha * wo.x, alpha * wo.y, wo.z));
+    float3 T1 = (V.z < 0.9999f) ? normalize3(cross3(mk3(0, 0, 1), V)) : mk3(1, 0, 0);
+    float3 T2 = cross3(V, T1);
+    float r = sqrtf(u1);
+    float phi = 2.0f * B2_PI * u2;
+    float t1 = r * cosf(phi);
+    float t2 = r * sinf(phi);
+    float s = 0.5f * (1.0f + V.z);
+    t2 = (1.0f - s) * sqrtf(fmaxf(0.0f, 1.0f - t1 * t1)) + s * t2;
+    float3 Nh = T1 * t1 + T2 * t2 + V * sqrtf(fmaxf(0.0f, 1.0f - t1 * t1 - t2 * t2));
+    return normalize3(mk3(alpha * Nh.x, alpha * Nh.y, fmaxf(0.0f, Nh.z)));
+}
+
+// local-space cores (callers that evaluate several lobes for one normal reuse the frame)
+B2_HD float3 bsdf_eval_local(const Mat &m, float3 wo, float3 wi) {      // :426-455
+    if (wo.z == 0.0f || wi.z == 0.0f) return mk3(0, 0, 0);
+    if (m.eta > 0.0f && m.roughness < 0.001f) return mk3(0, 0, 0);
+    float alpha = roughness_to_alpha(m.roughness);
+    float3 whv = wo + wi;
+    if (length3(whv) < 1e-6f) return mk3(0, 0, 0);
+    float3 wh = normalize3(whv);
+    if (wh.z < 0.0f) wh = wh * -1.0f;
+    float3 diffuse = m.base / B2_PI * (1.0f - m.metallic);
+    if (wo.z * wi.z < 0.0f) diffuse = mk3(0, 0, 0);
+    float D = tr_D(wh, alpha);
+    float G = tr_G(wo, wi, alpha);
+    float3 F;
+    if (m.metallic > 0.0f) F = fr_schlick(fabsf(wo.z), m.base);
+    else { float fr = fr_dielectric(dot3(wo, wh), 1.0f, m.eta); F = mk3(fr, fr, fr); }
+    float3 spec = (F * D * G) / fmaxf(4.0f * fabsf(wo.z) * fabsf(wi.z), 1e-4f);
+    if (wo.z * wi.z > 0.0f) return diffuse + spec;
+    return diffuse;
+}
+B2_HD float bsdf_pdf_local(const Mat &m, float3 wo, float3 wi) {        // :464-483
+    if (wo.z * wi.z <= 0.0f) return 0.0f;
+    if (m.eta > 0.0f && m.roughness < 0.001f) return 0.0f;
+    float alpha = roughness_to_alpha(m.roughness);
+    float3 whv = wo + wi;
+    if (length3(whv) < 1e-6f) return 0.0f;
+    float3 wh = normalize3(whv);
+    if (wh.z < 0.0f) wh = wh * -1.0f;
+    float pdf_diffuse = fabsf(wi.z) / B2_PI;
+    float G1 = 1.0f / (1.0f + tr_lambda(wo, alpha));
+    float owh = dot3(wo, wh);
+    float pdf_wh = tr_D(wh, alpha) * G1 * fmaxf(0.0f, owh) / fabsf(wo.z);
+    float pdf_spec = pdf_wh / (4.0f * owh + 1e-7f);
+    float sw = m.metallic > 0.0f ? 1.0f : 0.5f;
+    return (1.0f - sw) * pdf_diffuse + sw * pdf_spec;
+}
+B2_HD float3 bsdf_evaluate(const Mat &m, float3 wo_w, float3 wi_w, float3 N) {
+    Frame f = make_frame(N);
+    return bsdf_eval_local(m, to_local(f, wo_w), to_local(f, wi_w));
+}
+B2_HD float bsdf_pdf(const Mat &m, float3 wo_w, float3 wi_w, float3 N) {
+    Frame f = make_frame(N);
+    return bsdf_pdf_local(m, to_local(f, wo_w), to_local(f, wi_w));
+}
+
+struct BsdfSample { float3 wi, f; float pdf, new_eta; bool is_delta; };
+// bsdf_sample, :486-562.  On the early returns (pdf = 0) wi/f keep the caller-provided values,
+// like the by-reference outputs of the reference.
+B2_HD void bsdf_sample(const Mat &m, float3 wo_w, float3 N, float u_rr, float u1, float u2, float cur_eta, BsdfSample &s) {
+    s.is_delta = false;
+    s.new_eta = cur_eta;
+    Frame fr = make_frame(N);
+    float3 wo = to_local(fr, wo_w);
+    float3 wi;
+    if (m.eta > 0.0f && m.roughness < 0.001f && m.metallic < 0.01f) {
+        s.is_delta = true;
+        float F = fr_dielectric(wo.z, cur_eta, m.eta);
+        if (u_rr < F) {
+            wi = mk3(-wo.x, -wo.y, wo.z);
+            s.pdf = F;
+            s.f = mk3(F, F, F) / fabsf(wi.z);
+        } else {
+            float eta = wo.z > 0.0f ? (cur_eta / m.eta) : (m.eta / cur_eta);
+            float sin2I = fmaxf(0.0f, 1.0f - wo.z * wo.z);
+            float sin2T = eta * eta * sin2I;
+            if (sin2T >= 1.0f) { s.pdf = 0.0f; return; }
+            float cosT = sqrtf(1.0f - sin2T);
+            if (wo.z > 0.0f) cosT = -cosT;
+            wi = mk3(-eta * wo.x, -eta * wo.y, cosT);
+            s.new_eta = (wo.z > 0.0f) ? m.eta : 1.0f;
+            s.pdf = 1.0f - F;
+            s.f = m.base * (1.0f - F) / fabsf(wi.z);
+        }
+        s.wi = to_world(fr, wi);
+        return;
+    }
+    if (m.metallic > 0.99f && m.roughness < 0.001f) {
+        s.is_delta = true;
+        wi = mk3(-wo.x, -wo.y, wo.z);
+        s.pdf = 1.0f;
+        s.f = fr_schlick(fabsf(wo.z), m.base) / fabsf(wi.z);
+        s.wi = to_world(fr, wi);
+        return;
+    }
+    float alpha = roughness_to_alpha(m.roughness);
+    float sw = m.metallic > 0.0f ? 1.0f : 0.5f;
+    if (u_rr < sw) {
+        float3 wh = sample_vndf(wo.z > 0 ? wo : wo * -1.0f, alpha, u1, u2);
+        if (wo.z < 0.0f) wh = wh * -1.0f;
+        float3 I = wo * -1.0f;
+        wi = I - wh * 2.0f * dot3(wh, I);              // reflect(), :99
+        if (wo.z * wi.z <= 0.0f) { s.pdf = 0.0f; return; }
+    } else {
+        float r = sqrtf(u1);
+        float phi = 2.0f * B2_PI * u2;
+        wi = mk3(r * cosf(phi), r * sinf(phi), sqrtf(fmaxf(0.0f, 1.0f - u1)));
+        if (wo.z < 0.0f) wi.z *= -1.0f;
+    }
+    s.wi = to_world(fr, wi);
+    // the reference re-derives both from world space (:560-561): keep that (wi_w -> local again)
+    float3 wi_l = to_local(fr, s.wi);
+    s.pdf = bsdf_pdf_local(m, wo, wi_l);
+    s.f = bsdf_eval_local(m, wo, wi_l);
+}

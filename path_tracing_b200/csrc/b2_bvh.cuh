@@ -1,0 +1,147 @@
+// b2_bvh.cuh -- traversal of the 8-wide quantised BVH (layout in b2_scene.cuh).
+//
+// One ray per thread.  The traversal stack holds "node groups": {child_base, hits<<8 | imask}, i.e. the
+// still-unvisited hit children of one wide node, 8 bytes per level.  Children are popped in increasing
+// (slot ^ octant), which is roughly front-to-back thanks to the builder's slot assignment.
+// Leaf triangles run through exactly the same tri_test() as the exhaustive kernels, so the result
+// (min t, ties -> highest reference order) is independent of visiting order and bit-identical to them
+// as long as no box containing an accepted hit is culled: boxes are padded at build time and the slab
+// comparison carries a (1 + 4 ulp) slack.
+#pragma once
+#include "b2_isect.cuh"
+
+#define B2_STACK_CAP 64
+
+struct RayPre { float3 o, d, idir, oid; uint32_t oct; };
+B2_HD float safe_rcp(float d) { return fabsf(d) > 1e-30f ? 1.0f / d : copysignf(1e30f, d); }
+B2_HD RayPre ray_pre(float3 o, float3 d) {
+    RayPre r; r.o = o; r.d = d;
+    r.idir = mk3(safe_rcp(d.x), safe_rcp(d.y), safe_rcp(d.z));
+    r.oct = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
+    return r;
+}
+B2_HD uint32_t byte_of(uint32_t lo_word, uint32_t hi_word, int i) { return ((i < 4 ? lo_word : hi_word) >> (8 * (i & 3))) & 0xffu; }
+
+// Tests the 8 children of `node`; returns hit internal children as bits (slot ^ oct) in hits_p and hit leaf
+// triangles as a 24-bit mask relative to the node's tri_base.
+B2_HD void node_test(const uint4 *__restrict__ nodes, uint32_t node, const RayPre &r, float tmin, float tmax,
+                     uint32_t &hits_p, uint32_t &tribits, uint32_t &child_base, uint32_t &tri_base, uint32_t &imask) {
+    const uint4 *np = nodes + (size_t) node * B2_NODE_UINT4;
+    const uint4 w0 = np[0], w1 = np[1], w2 = np[2], w3 = np[3], w4 = np[4];
+    const float sx = u2f((w0.w & 0xffu) << 23), sy = u2f(((w0.w >> 8) & 0xffu) << 23), sz = u2f(((w0.w >> 16) & 0xffu) << 23);
+    imask = w0.w >> 24;
+    child_base = w1.x; tri_base = w1.y;
+    const float ax = sx * r.idir.x, ay = sy * r.idir.y, az = sz * r.idir.z;
+    const float bx = (u2f(w0.x) - r.o.x) * r.idir.x, by = (u2f(w0.y) - r.o.y) * r.idir.y, bz = (u2f(w0.z) - r.o.z) * r.idir.z;
+    // near/far byte planes per axis, chosen by the ray's direction sign
+    const bool nx = r.oct & 1u, ny = r.oct & 2u, nz = r.oct & 4u;
+    const uint32_t xl0 = nx ? w3.z : w2.x, xl1 = nx ? w3.w : w2.y, xh0 = nx ? w2.x : w3.z, xh1 = nx ? w2.y : w3.w;
+    const uint32_t yl0 = ny ? w4.x : w2.z, yl1 = ny ? w4.y : w2.w, yh0 = ny ? w2.z : w4.x, yh1 = ny ? w2.w : w4.y;
+    const uint32_t zl0 = nz ? w4.z : w3.x, zl1 = nz ? w4.w : w3.y, zh0 = nz ? w3.x : w4.z, zh1 = nz ? w3.y : w4.w;
+    hits_p = 0; tribits = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const uint32_t meta = byte_of(w1.z, w1.w, i);
+        if (meta == 0) continue;
+        const float tlx = (float) byte_of(xl0, xl1, i) * ax + bx, thx = (float) byte_of(xh0, xh1, i) * ax + bx;
+        const float tly = (float) byte_of(yl0, yl1, i) * ay + by, thy = (float) byte_of(yh0, yh1, i) * ay + by;
+        const float tlz = (float) byte_of(zl0, zl1, i) * az + bz, thz = (float) byte_of(zh0, zh1, i) * az + bz;
+        const float tn = fmaxf(fmaxf(tlx, tly), fmaxf(tlz, tmin));
+        const float tf = fminf(fminf(thx, thy), fminf(thz, tmax));
+        if (tn <= tf * 1.0000005f + 1e-30f) {
+            const uint32_t cnt = meta >> 5;
+            if (cnt == B2_META_INTERNAL) hits_p |= 1u << ((meta & 7u) ^ r.oct);
+            else tribits |= ((1u << cnt) - 1u) << (meta & 31u);
+        }
+    }
+}
+
+template <bool COUNT>
+B2_HD HitRec closest_hit_bvh(const DevScene &sc, float3 ro, float3 rd, uint2 *stack, int sstride, TravCounters *cnt) {
+    HitRec best; best.prim = B2_PRIM_MISS; best.t = B2_T_INF;
+    uint32_t best_order = 0;
+    if (sc.n_nodes > 0) {
+        const RayPre r = ray_pre(ro, rd);
+        int sp = 0;
+        uint32_t node = 0;
+        bool have = true;
+        uint2 grp = make_uint2(0u, 0u);
+        for (;;) {
+            if (!have) {
+                if ((grp.y >> 8) == 0u) { if (sp == 0) break; grp = stack[(--sp) * sstride]; }
+                const int p = ffs32(grp.y >> 8) - 1;
+                grp.y &= ~(1u << (8 + p));
+                const uint32_t slot = (uint32_t) p ^ r.oct;
+                node = grp.x + popc32(grp.y & 0xffu & ((1u << slot) - 1u));
+            }
+            have = false;
+            uint32_t hits_p, tribits, child_base, tri_base, imask;
+            node_test(sc.nodes, node, r, 1e-4f, best.t, hits_p, tribits, child_base, tri_base, imask);
+            if (COUNT) cnt->nodes++;
+            while (tribits) {
+                const int bit = ffs32(tribits) - 1;
+                tribits &= tribits - 1u;
+                const int ti = (int) tri_base + bit;
+                const float4 a = sc.tri[3 * ti], b = sc.tri[3 * ti + 1], c = sc.tri[3 * ti + 2];
+                if (COUNT) cnt->tris++;
+                float t;
+                if (tri_test(ro, rd, mk3(a), mk3(b), mk3(c), 1e-4f, best.t, t)) {
+                    const uint32_t order = f2u(a.w);
+                    if ((best.prim == B2_PRIM_MISS || closer(t, order, best.t, best_order)) &&
+                        group_pass(sc, (int) f2u(c.w), ro, rd, 1e-4f, B2_T_INF)) {
+                        best.t = t; best.prim = prim_make(B2_KIND_TRI, ti); best_order = order;
+                    }
+                }
+            }
+            if (hits_p) {
+                if ((grp.y >> 8) != 0u && sp < B2_STACK_CAP) stack[(sp++) * sstride] = grp;
+                grp = make_uint2(child_base, (hits_p << 8) | imask);
+            }
+        }
+    }
+    closest_spheres(sc, ro, rd, best, best_order);
+    closest_lights(sc, ro, rd, best);
+    return best;
+}
+
+// true = blocked by an opaque object within [1e-3, tMax] (cpu_check_visibility, cpu_bdpt.cpp:82-107)
+template <bool COUNT>
+B2_HD bool occluded_bvh(const DevScene &sc, float3 ro, float3 rd, float tMax, uint2 *stack, int sstride, TravCounters *cnt) {
+    const float tMin = 1e-3f;
+    if (sc.n_nodes > 0) {
+        const RayPre r = ray_pre(ro, rd);
+        int sp = 0;
+        uint32_t node = 0;
+        bool have = true;
+        uint2 grp = make_uint2(0u, 0u);
+        for (;;) {
+            if (!have) {
+                if ((grp.y >> 8) == 0u) { if (sp == 0) break; grp = stack[(--sp) * sstride]; }
+                const int p = ffs32(grp.y >> 8) - 1;
+                grp.y &= ~(1u << (8 + p));
+                const uint32_t slot = (uint32_t) p ^ r.oct;
+                node = grp.x + popc32(grp.y & 0xffu & ((1u << slot) - 1u));
+            }
+            have = false;
+            uint32_t hits_p, tribits, child_base, tri_base, imask;
+            node_test(sc.nodes, node, r, tMin, tMax, hits_p, tribits, child_base, tri_base, imask);
+            if (COUNT) cnt->nodes++;
+            while (tribits) {
+                const int bit = ffs32(tribits) - 1;
+                tribits &= tribits - 1u;
+                const int ti = (int) tri_base + bit;
+                const float4 b = sc.tri[3 * ti + 1];
+                if (f2u(b.w) & B2_MAT_TRANSPARENT) continue;
+                const float4 a = sc.tri[3 * ti], c = sc.tri[3 * ti + 2];
+                if (COUNT) cnt->tris++;
+                float t;
+                if (tri_test(ro, rd, mk3(a), mk3(b), mk3(c), tMin, tMax, t) && group_pass(sc, (int) f2u(c.w), ro, rd, tMin, tMax)) return true;
+            }
+            if (hits_p) {
+                if ((grp.y >> 8) != 0u && sp < B2_STACK_CAP) stack[(sp++) * sstride] = grp;
+                grp = make_uint2(child_base, (hits_p << 8) | imask);
+            }
+        }
+    }
+    return occluded_spheres(sc, ro, rd, tMin, tMax);
+}

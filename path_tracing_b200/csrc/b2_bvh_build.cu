@@ -1,0 +1,162 @@
+// b2_bvh_build.cu -- GPU BVH build: kernels wrapping the bodies of b2_bvh_build.cuh plus the level loop.
+// Sorting and the two per-level exclusive scans use CUB (shipped with CUDA; plain library primitives off
+// the hot path).  See the header for the pipeline.
+#include <cub/cub.cuh>
+#include "b2_bvh_build.cuh"
+#include "b2_cuda_util.hpp"
+#include "b2_device_scene.hpp"
+
+namespace {
+
+__device__ __forceinline__ uint32_t f2ord(float f) { uint32_t u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
+__host__ __device__ __forceinline__ float ord2f(uint32_t u) {
+    uint32_t b = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+    float f; memcpy(&f, &b, 4); return f;
+}
+
+// 1. padded triangle boxes + centroid bounds (warp shuffle reduction, then one atomic per warp and axis)
+__global__ void k_tri_bounds(const BuildTri *__restrict__ in, int n, float pad, float *__restrict__ tlo, float *__restrict__ thi, uint32_t *cbounds) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    float c[3] = { 3e38f, 3e38f, 3e38f }, C[3] = { -3e38f, -3e38f, -3e38f };
+    if (i < n) {
+        float lo[3], hi[3];
+        tri_bounds(in[i], pad, lo, hi);
+        for (int a = 0; a < 3; ++a) { tlo[3 * i + a] = lo[a]; thi[3 * i + a] = hi[a]; c[a] = C[a] = 0.5f * (lo[a] + hi[a]); }
+    }
+    for (int a = 0; a < 3; ++a) {
+        for (int o = 16; o > 0; o >>= 1) { c[a] = fminf(c[a], __shfl_xor_sync(0xffffffffu, c[a], o)); C[a] = fmaxf(C[a], __shfl_xor_sync(0xffffffffu, C[a], o)); }
+        if ((threadIdx.x & 31) == 0) { atomicMin(&cbounds[a], f2ord(c[a])); atomicMax(&cbounds[3 + a], f2ord(C[a])); }
+    }
+}
+__global__ void k_morton(int n, const float *__restrict__ tlo, const float *__restrict__ thi, float3 cmin, float3 cinv, uint64_t *keys, int *vals) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { keys[i] = morton63(&tlo[3 * i], &thi[3 * i], cmin, cinv); vals[i] = i; }
+}
+__global__ void k_karras(BinTree bt) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < bt.n - 1) karras_node(bt, i);
+}
+__global__ void k_refit(BinTree bt, const float *__restrict__ tlo, const float *__restrict__ thi) {
+    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < bt.n) refit_from_leaf(bt, tlo, thi, j);
+}
+__global__ void k_single_leaf_box(BinTree bt, const float *tlo, const float *thi) {
+    for (int a = 0; a < 3; ++a) { bt.lo[a] = tlo[a]; bt.hi[a] = thi[a]; }
+}
+__global__ void k_collapse_pick(BinTree bt, const CollapseItem *__restrict__ items, int m, int max_leaf, CollapseOut *outs, int *nint, int *ntri) {
+    int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < m) collapse_pick(bt, items[k].bin_node, max_leaf, outs[k], nint[k], ntri[k]);
+}
+__global__ void k_collapse_emit(BinTree bt, const CollapseItem *__restrict__ items, const CollapseOut *__restrict__ outs, int m, int max_leaf,
+                                const int *__restrict__ ioff, const int *__restrict__ toff, uint32_t level_start, uint32_t next_start, uint32_t tris_done,
+                                uint4 *nodes, CollapseItem *next_items, int *perm) {
+    int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < m)
+        collapse_emit(bt, items[k].bin_node, outs[k], max_leaf, next_start + (uint32_t) ioff[k], tris_done + (uint32_t) toff[k],
+                      nodes + (size_t) (level_start + k) * B2_NODE_UINT4, next_items, ioff[k], perm);
+}
+__global__ void k_pack_tris(const BuildTri *__restrict__ in, const int *__restrict__ sorted, const int *__restrict__ perm, int n, float4 *tri, int32_t *obj) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s < n) pack_tri(in, sorted, perm, s, tri, obj);
+}
+
+}  // namespace
+
+int b2_build_bvh_device(const BuildTri *d_in, int n, float pad, int max_leaf, cudaStream_t st, DeviceBvh &out) {
+    out.release();
+    if (n <= 0) return B2_OK;
+    cudaEvent_t ev0, ev1;
+    B2_CUDA(cudaEventCreate(&ev0)); B2_CUDA(cudaEventCreate(&ev1));
+    B2_CUDA(cudaEventRecord(ev0, st));
+    const unsigned T = 256;
+    DevBuf<float> tlo, thi, lo, hi;
+    DevBuf<uint32_t> cb, visit;
+    DevBuf<uint64_t> keys, skeys;
+    DevBuf<int> vals, sorted, left, right, parent, first, last, leaf_parent, perm, nint, ntri, ioff, toff;
+    DevBuf<unsigned char> tmp;
+    DevBuf<CollapseItem> items_a, items_b;
+    DevBuf<CollapseOut> outs;
+    DevBuf<uint4> nodes_tmp;
+    B2_TRY(tlo.alloc(3 * (size_t) n)); B2_TRY(thi.alloc(3 * (size_t) n));
+    B2_TRY(cb.alloc(6));
+    uint32_t cb_init[6] = { 0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u };
+    B2_CUDA(cudaMemcpyAsync(cb.p, cb_init, sizeof(cb_init), cudaMemcpyHostToDevice, st));
+    k_tri_bounds<<<blocks_for(n, T), T, 0, st>>>(d_in, n, pad, tlo.p, thi.p, cb.p);
+    uint32_t cb_h[6];
+    B2_CUDA(cudaMemcpyAsync(cb_h, cb.p, sizeof(cb_h), cudaMemcpyDeviceToHost, st));
+    B2_CUDA(cudaStreamSynchronize(st));
+    float cmn[3], cmx[3];
+    for (int a = 0; a < 3; ++a) { cmn[a] = ord2f(cb_h[a]); cmx[a] = ord2f(cb_h[3 + a]); }
+    float3 cmin = make_float3(cmn[0], cmn[1], cmn[2]);
+    float3 cinv = make_float3(2097152.0f / fmaxf(cmx[0] - cmn[0], 1e-30f), 2097152.0f / fmaxf(cmx[1] - cmn[1], 1e-30f), 2097152.0f / fmaxf(cmx[2] - cmn[2], 1e-30f));
+    B2_TRY(keys.alloc(n)); B2_TRY(skeys.alloc(n)); B2_TRY(vals.alloc(n)); B2_TRY(sorted.alloc(n));
+    k_morton<<<blocks_for(n, T), T, 0, st>>>(n, tlo.p, thi.p, cmin, cinv, keys.p, vals.p);
+    size_t tmp_bytes = 0;
+    B2_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys.p, skeys.p, vals.p, sorted.p, n, 0, 63, st));
+    B2_TRY(tmp.alloc(tmp_bytes));
+    B2_CUDA(cub::DeviceRadixSort::SortPairs(tmp.p, tmp_bytes, keys.p, skeys.p, vals.p, sorted.p, n, 0, 63, st));
+    keys.release(); vals.release();
+
+    B2_TRY(left.alloc(n)); B2_TRY(right.alloc(n)); B2_TRY(parent.alloc(n)); B2_TRY(first.alloc(n)); B2_TRY(last.alloc(n)); B2_TRY(leaf_parent.alloc(n));
+    B2_TRY(lo.alloc(6 * (size_t) n)); B2_TRY(hi.alloc(6 * (size_t) n)); B2_TRY(visit.alloc(n));
+    B2_CUDA(cudaMemsetAsync(visit.p, 0, sizeof(uint32_t) * n, st));
+    B2_CUDA(cudaMemsetAsync(leaf_parent.p, 0xff, sizeof(int) * n, st));
+    BinTree bt{ n, skeys.p, sorted.p, left.p, right.p, parent.p, first.p, last.p, leaf_parent.p, lo.p, hi.p, visit.p };
+    if (n >= 2) {
+        k_karras<<<blocks_for(n - 1, T), T, 0, st>>>(bt);
+        k_refit<<<blocks_for(n, T), T, 0, st>>>(bt, tlo.p, thi.p);
+    } else {
+        k_single_leaf_box<<<1, 1, 0, st>>>(bt, tlo.p, thi.p);
+    }
+    B2_CUDA(cudaGetLastError());
+
+    // level-synchronous collapse
+    B2_TRY(perm.alloc(n));
+    size_t node_cap = (size_t) n + 1;
+    B2_TRY(nodes_tmp.alloc(node_cap * B2_NODE_UINT4));
+    B2_TRY(items_a.alloc(node_cap)); B2_TRY(items_b.alloc(node_cap)); B2_TRY(outs.alloc(node_cap));
+    B2_TRY(nint.alloc(node_cap)); B2_TRY(ntri.alloc(node_cap)); B2_TRY(ioff.alloc(node_cap)); B2_TRY(toff.alloc(node_cap));
+    size_t scan_bytes = 0;
+    B2_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, nint.p, ioff.p, (int) node_cap, st));
+    B2_TRY(tmp.ensure(scan_bytes));
+    CollapseItem root_item; root_item.bin_node = 0;
+    B2_CUDA(cudaMemcpyAsync(items_a.p, &root_item, sizeof(root_item), cudaMemcpyHostToDevice, st));
+    CollapseItem *cur = items_a.p, *nxt = items_b.p;
+    int m = 1, depth = 0;
+    uint32_t level_start = 0, tris_done = 0;
+    while (m > 0) {
+        if ((size_t) level_start + m > node_cap) { b2_set_error("BVH collapse overflow (internal error)"); return B2_ERR_STATE; }
+        k_collapse_pick<<<blocks_for(m, 128), 128, 0, st>>>(bt, cur, m, max_leaf, outs.p, nint.p, ntri.p);
+        B2_CUDA(cub::DeviceScan::ExclusiveSum(tmp.p, scan_bytes, nint.p, ioff.p, m, st));
+        B2_CUDA(cub::DeviceScan::ExclusiveSum(tmp.p, scan_bytes, ntri.p, toff.p, m, st));
+        int tail[4];
+        B2_CUDA(cudaMemcpyAsync(&tail[0], nint.p + (m - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
+        B2_CUDA(cudaMemcpyAsync(&tail[1], ioff.p + (m - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
+        B2_CUDA(cudaMemcpyAsync(&tail[2], ntri.p + (m - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
+        B2_CUDA(cudaMemcpyAsync(&tail[3], toff.p + (m - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
+        B2_CUDA(cudaStreamSynchronize(st));
+        const int itot = tail[0] + tail[1], ttot = tail[2] + tail[3];
+        const uint32_t next_start = level_start + (uint32_t) m;
+        k_collapse_emit<<<blocks_for(m, 128), 128, 0, st>>>(bt, cur, outs.p, m, max_leaf, ioff.p, toff.p, level_start, next_start, tris_done, nodes_tmp.p, nxt, perm.p);
+        B2_CUDA(cudaGetLastError());
+        level_start = next_start; tris_done += (uint32_t) ttot;
+        CollapseItem *t = cur; cur = nxt; nxt = t;
+        m = itot;
+        depth++;
+    }
+    if (tris_done != (uint32_t) n) { b2_set_error("BVH collapse placed %u of %d triangles (internal error)", tris_done, n); return B2_ERR_STATE; }
+    if (depth + 2 > B2_STACK_CAP) { b2_set_error("BVH depth %d exceeds the traversal stack (%d)", depth, B2_STACK_CAP); return B2_ERR_STATE; }
+    const size_t n_nodes = level_start;
+    B2_TRY(out.nodes.alloc(n_nodes * B2_NODE_UINT4));
+    B2_CUDA(cudaMemcpyAsync(out.nodes.p, nodes_tmp.p, n_nodes * B2_NODE_UINT4 * sizeof(uint4), cudaMemcpyDeviceToDevice, st));
+    B2_TRY(out.tri.alloc(3 * (size_t) n)); B2_TRY(out.tri_obj.alloc(n));
+    k_pack_tris<<<blocks_for(n, T), T, 0, st>>>(d_in, sorted.p, perm.p, n, out.tri.p, out.tri_obj.p);
+    B2_CUDA(cudaGetLastError());
+    B2_CUDA(cudaEventRecord(ev1, st));
+    B2_CUDA(cudaStreamSynchronize(st));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ev0, ev1);
+    cudaEventDestroy(ev0); cudaEventDestroy(ev1);
+    out.n_tris = n; out.n_nodes = (int) n_nodes; out.depth = depth; out.build_ms = ms;
+    return B2_OK;
+}

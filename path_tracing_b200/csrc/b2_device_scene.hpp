@@ -1,0 +1,16 @@
+// b2_device_scene.hpp -- host-side owners of the device-resident scene (B2Scene behind the C ABI).
+#pragma once
+#include "b2_cuda_util.hpp"
+#include "b2_bvh_build.cuh"
+#include "b2_bvh.cuh"
+
+struct DeviceBvh {
+    DevBuf<uint4> nodes;
+    DevBuf<float4> tri;
+    DevBuf<int32_t> tri_obj;
+    int n_tris = 0, n_nodes = 0, depth = 0;
+    float build_ms = 0.f;
+    void release() { nodes.release(); tri.release(); tri_obj.release(); n_tris = n_nodes = depth = 0; build_ms = 0.f; }
+};
+
+int b2_build_bvh_device(const BuildTri *d_in, int n, float pad, int max_leaf, cudaStream_t st, DeviceBvh &out);

@@ -1,0 +1,106 @@
+// b2_host_scene.hpp -- host-side flattening of the reference's scene objects into the upload format.
+// Plays the role of move_data_to_cuda_bdpt (src/bdpt_cu_helper.cpp:13-68) for the new path; shared by
+// libb2pt.so (b2_api.cu) and the test-only host build of the device headers (tests/hostsim).
+#pragma once
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <map>
+#include <vector>
+#include "../../include/b2pt.h"
+#include "b2_bvh_build.cuh"
+
+struct HostScene {
+    std::vector<BuildTri> tris;
+    std::vector<float4> sph, lights, mats, groups;
+    float3 scene_min, scene_max;
+    float max_abs;      // largest |coordinate| / extent of the triangle set (box padding scale)
+    int n_sph = 0, n_lights = 0, n_mats = 0, n_groups = 0;
+};
+
+inline float4 hs_f4(float x, float y, float z, float w) { return make_float4(x, y, z, w); }
+inline float hs_bits(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
+
+inline bool flatten_scene(const B2Tri *tris, size_t n_tris, const B2Sphere *sph, size_t n_sph, const B2Material *mats, size_t n_mats,
+                          const B2Light *lights, size_t n_lights, HostScene &hs, const char **err) {
+    // groups: std::map<int,AABB> in key order; bounds grown as AABB::add_obj does (object.cpp:123-147)
+    struct G { float mn[3] = { 99999.f, 99999.f, 99999.f }, mx[3] = { -99999.f, -99999.f, -99999.f }; };
+    std::map<int, G> gm;
+    for (size_t i = 0; i < n_tris; ++i) {
+        if (tris[i].material < 0 || (size_t) tris[i].material >= n_mats) { *err = "triangle material index out of range"; return false; }
+        G &g = gm[tris[i].group];
+        const float *vs[3] = { tris[i].v0, tris[i].v1, tris[i].v2 };
+        for (int k = 0; k < 3; ++k)
+            for (int a = 0; a < 3; ++a) { g.mn[a] = std::min(g.mn[a], vs[k][a]); g.mx[a] = std::max(g.mx[a], vs[k][a]); }
+    }
+    for (size_t i = 0; i < n_sph; ++i) {
+        if (sph[i].material < 0 || (size_t) sph[i].material >= n_mats) { *err = "sphere material index out of range"; return false; }
+        G &g = gm[sph[i].group];
+        for (int a = 0; a < 3; ++a) {
+            float p = sph[i].center[a] + sph[i].r, m = sph[i].center[a] - sph[i].r;
+            g.mn[a] = std::min({ g.mn[a], p, m }); g.mx[a] = std::max({ g.mx[a], p, m });
+        }
+    }
+    std::map<int, int> gindex;
+    // scene bounds for parallel lights: union of the group boxes as run_cpu_bdpt sees them (cpu_bdpt.cpp:181-187)
+    float smn[3] = { 1e9f, 1e9f, 1e9f }, smx[3] = { -1e9f, -1e9f, -1e9f };
+    hs.groups.clear();
+    for (auto &kv : gm) {
+        gindex[kv.first] = (int) gindex.size();
+        G g = kv.second;
+        for (int a = 0; a < 3; ++a) { smn[a] = std::min(smn[a], g.mn[a]); smx[a] = std::max(smx[a], g.mx[a]); }
+        // AABB::intersectAABB widens degenerate extents in place on every call (object.cpp:108-111); apply to the fixed point
+        for (int a = 0; a < 3; ++a)
+            for (int it = 0; it < 64 && g.mx[a] - g.mn[a] < 1e-6f; ++it) { g.mn[a] -= 0.5f * 1e-6f; g.mx[a] += 0.5f * 1e-6f; }
+        hs.groups.push_back(hs_f4(g.mn[0], g.mn[1], g.mn[2], 0.f));
+        hs.groups.push_back(hs_f4(g.mx[0], g.mx[1], g.mx[2], 0.f));
+    }
+    hs.n_groups = (int) gm.size();
+    hs.scene_min = make_float3(smn[0], smn[1], smn[2]);
+    hs.scene_max = make_float3(smx[0], smx[1], smx[2]);
+    // reference visiting order: group key, then insertion order (= obj_id order)
+    struct Key { int group, obj_id, kind; size_t idx; };
+    std::vector<Key> keys; keys.reserve(n_tris + n_sph);
+    for (size_t i = 0; i < n_tris; ++i) keys.push_back({ tris[i].group, tris[i].obj_id, 1, i });
+    for (size_t i = 0; i < n_sph; ++i) keys.push_back({ sph[i].group, sph[i].obj_id, 0, i });
+    std::stable_sort(keys.begin(), keys.end(), [](const Key &a, const Key &b) { return a.group != b.group ? a.group < b.group : a.obj_id < b.obj_id; });
+    std::vector<uint32_t> tri_order(n_tris), sph_order(n_sph);
+    for (size_t r = 0; r < keys.size(); ++r) (keys[r].kind ? tri_order[keys[r].idx] : sph_order[keys[r].idx]) = (uint32_t) r;
+
+    hs.mats.clear();
+    for (size_t i = 0; i < n_mats; ++i) {
+        hs.mats.push_back(hs_f4(mats[i].base_color[0], mats[i].base_color[1], mats[i].base_color[2], mats[i].roughness));
+        hs.mats.push_back(hs_f4(mats[i].metallic, mats[i].eta, 0.f, 0.f));
+    }
+    hs.n_mats = (int) n_mats;
+    hs.tris.resize(n_tris);
+    float max_abs = 0.f;
+    for (size_t i = 0; i < n_tris; ++i) {
+        BuildTri &t = hs.tris[i];
+        memcpy(t.v, tris[i].v0, 12); memcpy(t.v + 3, tris[i].v1, 12); memcpy(t.v + 6, tris[i].v2, 12);
+        for (int k = 0; k < 9; ++k) max_abs = std::max(max_abs, std::fabs(t.v[k]));
+        t.order = tri_order[i];
+        t.matflag = (uint32_t) tris[i].material | (mats[tris[i].material].eta > 0.0f ? B2_MAT_TRANSPARENT : 0u);
+        t.group = (uint32_t) gindex[tris[i].group];
+        t.obj_id = tris[i].obj_id;
+    }
+    hs.max_abs = max_abs;
+    hs.sph.clear();
+    for (size_t i = 0; i < n_sph; ++i) {
+        uint32_t mf = (uint32_t) sph[i].material | (mats[sph[i].material].eta > 0.0f ? B2_MAT_TRANSPARENT : 0u);
+        hs.sph.push_back(hs_f4(sph[i].center[0], sph[i].center[1], sph[i].center[2], sph[i].r));
+        hs.sph.push_back(hs_f4(hs_bits(sph_order[i]), hs_bits(mf), hs_bits((uint32_t) gindex[sph[i].group]), hs_bits((uint32_t) sph[i].obj_id)));
+    }
+    hs.n_sph = (int) n_sph;
+    hs.lights.clear();
+    for (size_t i = 0; i < n_lights; ++i) {
+        const B2Light &L = lights[i];
+        float len = std::sqrt(L.dir[0] * L.dir[0] + L.dir[1] * L.dir[1] + L.dir[2] * L.dir[2]);   // geometric.cuh:97-98
+        hs.lights.push_back(hs_f4(L.pos[0], L.pos[1], L.pos[2], L.ball_r));
+        hs.lights.push_back(hs_f4(L.dir[0], L.dir[1], L.dir[2], L.cutoff));
+        hs.lights.push_back(hs_f4(L.illum[0], L.illum[1], L.illum[2], L.is_parallel ? 1.0f : 0.0f));
+        hs.lights.push_back(hs_f4(L.dir[0] / len, L.dir[1] / len, L.dir[2] / len, cosf(L.cutoff)));
+    }
+    hs.n_lights = (int) n_lights;
+    return true;
+}

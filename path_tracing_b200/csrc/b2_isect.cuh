@@ -1,0 +1,155 @@
+// b2_isect.cuh -- primitive tests (bit-exact restatement of the CPU intersector's arithmetic on the
+// device) and the two traversal flavours: closest-hit (cpu_find_closest_hit, cpu_bdpt.cpp:30-80) and
+// any-hit (cpu_check_visibility, cpu_bdpt.cpp:82-107), each as exhaustive and wide-BVH variants.
+#pragma once
+#include "b2_scene.cuh"
+
+// Triangle::check_intersect, object.cpp:72-95 (Moeller-Trumbore, no culling, t == tMax accepted).
+B2_HD bool tri_test(float3 ro, float3 rd, float3 v0, float3 e1, float3 e2, float tMin, float tMax, float &t) {
+    float3 pvec = x3_cross(rd, e2);
+    float det = x3_dot(e1, pvec);
+    if (fabsf(det) <= 1e-6f) return false;        // (double)fabs(det) < 1e-6  <=>  |det| <= float(1e-6)
+    float inv = x_div(1.0f, det);
+    float3 tvec = x3_sub(ro, v0);
+    float u = x_mul(x3_dot(tvec, pvec), inv);
+    if (u < 0.0f || u > 1.0f) return false;
+    float3 qvec = x3_cross(tvec, e1);
+    float v = x_mul(x3_dot(rd, qvec), inv);
+    if (v < 0.0f || x_add(u, v) > 1.0f) return false;
+    float tt = x_mul(x3_dot(e2, qvec), inv);
+    if (tt < tMin || tt > tMax) return false;
+    t = tt;
+    return true;
+}
+// Sphere::check_intersect, object.cpp:16-56 with scale (1,1,1): refuses origins on/inside the sphere.
+B2_HD bool sphere_test(float3 ro, float3 rd, float3 c, float r, float tMin, float tMax, float &t) {
+    float3 D = g3_normalize(rd);
+    float3 OC = x3_sub(ro, c);
+    float a = x_add(x_add(x_mul(D.x, D.x), x_mul(D.y, D.y)), x_mul(D.z, D.z));
+    float b = x_mul(2.0f, x_add(x_add(x_mul(D.x, OC.x), x_mul(D.y, OC.y)), x_mul(D.z, OC.z)));
+    float cc = x_sub(x_add(x_add(x_mul(OC.x, OC.x), x_mul(OC.y, OC.y)), x_mul(OC.z, OC.z)), x_mul(r, r));
+    if (cc <= 1e-6f) return false;
+    float disc = x_sub(x_mul(b, b), x_mul(x_mul(4.0f, a), cc));
+    if (disc < 0.0f) return false;
+    float sd = x_sqrt(0.0f < disc ? disc : 0.0f);
+    float two_a = x_mul(2.0f, a);
+    float t0 = x_div(x_sub(-b, sd), two_a);
+    float t1 = x_div(x_add(-b, sd), two_a);
+    if (t0 > t1) { float tmp = t0; t0 = t1; t1 = tmp; }
+    float tc = (t0 >= tMin) ? t0 : t1;
+    if (tc < tMin || tc > tMax) return false;
+    t = tc;
+    return true;
+}
+// intersect_sphere (light balls), geometric.cuh:240-259: strict EPSILON < t < max_dist.
+B2_HD bool light_ball_test(float3 ro, float3 rd, float3 c, float r, float max_dist, float &t) {
+    float3 oc = x3_sub(ro, c);
+    float b = x3_dot(oc, rd);
+    float cc = x_sub(x3_dot(oc, oc), x_mul(r, r));
+    float h = x_sub(x_mul(b, b), cc);
+    if (h < 0.0f) return false;
+    h = x_sqrt(h);
+    float th = x_sub(-b, h);
+    if (th > B2_EPSILON && th < max_dist) { t = th; return true; }
+    th = x_add(-b, h);
+    if (th > B2_EPSILON && th < max_dist) { t = th; return true; }
+    return false;
+}
+// AABB::intersectAABB, object.cpp:104-121 (group pre-cull), with the ray's fixed [tmin,tmax].
+B2_HD bool group_slab(float3 ro, float3 rd, float3 mn, float3 mx, float tmin, float tmax) {
+    const float p[3] = { ro.x, ro.y, ro.z }, d[3] = { rd.x, rd.y, rd.z };
+    const float lo[3] = { mn.x, mn.y, mn.z }, hi[3] = { mx.x, mx.y, mx.z };
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        float invD = x_div(1.0f, d[a]);
+        float t0 = x_mul(x_sub(lo[a], p[a]), invD);
+        float t1 = x_mul(x_sub(hi[a], p[a]), invD);
+        if (invD < 0) { float tmp = t0; t0 = t1; t1 = tmp; }
+        tmin = t0 > tmin ? t0 : tmin;
+        tmax = t1 < tmax ? t1 : tmax;
+        if (tmax <= tmin) return false;
+    }
+    return true;
+}
+B2_HD bool group_pass(const DevScene &sc, int g, float3 ro, float3 rd, float tmin, float tmax) {
+    return group_slab(ro, rd, mk3(sc.groups[2 * g]), mk3(sc.groups[2 * g + 1]), tmin, tmax);
+}
+
+struct HitRec { int prim; float t; };
+struct TravCounters { uint32_t nodes, tris; };
+
+// Candidate acceptance in an order-free traversal: the reference visits objects in `order` and accepts
+// t <= best (object.cpp:92), so the winner is min t, ties -> highest order.
+B2_HD bool closer(float t, uint32_t order, float best_t, uint32_t best_order) {
+    return t < best_t || (t == best_t && order > best_order);
+}
+
+// ---- spheres + light balls (short tables, tested after the triangles) ----
+B2_HD void closest_spheres(const DevScene &sc, float3 ro, float3 rd, HitRec &best, uint32_t &best_order) {
+    for (int i = 0; i < sc.n_sph; ++i) {
+        float4 a = sc.sph[2 * i], b = sc.sph[2 * i + 1];
+        float t;
+        if (sphere_test(ro, rd, mk3(a), a.w, 1e-4f, best.t, t)) {
+            uint32_t order = f2u(b.x);
+            if ((best.prim == B2_PRIM_MISS || closer(t, order, best.t, best_order)) &&
+                group_pass(sc, (int) f2u(b.z), ro, rd, 1e-4f, B2_T_INF)) {
+                best.t = t; best.prim = prim_make(B2_KIND_SPHERE, i); best_order = order;
+            }
+        }
+    }
+}
+B2_HD void closest_lights(const DevScene &sc, float3 ro, float3 rd, HitRec &best) {
+    for (int k = 0; k < sc.n_lights; ++k) {                      // cpu_bdpt.cpp:64-78
+        float4 a = sc.lights[4 * k];
+        float t;
+        if (light_ball_test(ro, rd, mk3(a), a.w, best.t, t)) { best.t = t; best.prim = prim_make(B2_KIND_LIGHT, k); }
+    }
+}
+B2_HD bool occluded_spheres(const DevScene &sc, float3 ro, float3 rd, float tMin, float tMax) {
+    for (int i = 0; i < sc.n_sph; ++i) {
+        float4 a = sc.sph[2 * i], b = sc.sph[2 * i + 1];
+        if (f2u(b.y) & B2_MAT_TRANSPARENT) continue;
+        float t;
+        if (sphere_test(ro, rd, mk3(a), a.w, tMin, tMax, t) && group_pass(sc, (int) f2u(b.z), ro, rd, tMin, tMax)) return true;
+    }
+    return false;
+}
+
+// ---- exhaustive reference kernels' bodies (parity cross-check of the BVH path) ----
+B2_HD HitRec closest_hit_brute(const DevScene &sc, float3 ro, float3 rd) {
+    HitRec best; best.prim = B2_PRIM_MISS; best.t = B2_T_INF;
+    uint32_t best_order = 0;
+    for (int i = 0; i < sc.n_tris; ++i) {
+        float4 a = sc.tri[3 * i], b = sc.tri[3 * i + 1], c = sc.tri[3 * i + 2];
+        float t;
+        if (tri_test(ro, rd, mk3(a), mk3(b), mk3(c), 1e-4f, best.t, t)) {
+            uint32_t order = f2u(a.w);
+            if ((best.prim == B2_PRIM_MISS || closer(t, order, best.t, best_order)) &&
+                group_pass(sc, (int) f2u(c.w), ro, rd, 1e-4f, B2_T_INF)) {
+                best.t = t; best.prim = prim_make(B2_KIND_TRI, i); best_order = order;
+            }
+        }
+    }
+    closest_spheres(sc, ro, rd, best, best_order);
+    closest_lights(sc, ro, rd, best);
+    return best;
+}
+// Segment p1 -> p2 exactly as cpu_check_visibility sets it up (cpu_bdpt.cpp:83-91).
+struct ShadowRay { float3 o, d; float tmax; };
+B2_HD ShadowRay make_shadow_ray(float3 p1, float3 p2) {
+    ShadowRay r;
+    float3 diff = x3_sub(p2, p1);
+    float dist = x3_length(diff);
+    r.o = p1; r.d = x3_divs(diff, dist); r.tmax = x_sub(dist, 1e-3f);
+    return r;
+}
+B2_HD bool occluded_brute(const DevScene &sc, float3 ro, float3 rd, float tMax) {
+    const float tMin = 1e-3f;
+    for (int i = 0; i < sc.n_tris; ++i) {
+        float4 a = sc.tri[3 * i], b = sc.tri[3 * i + 1], c = sc.tri[3 * i + 2];
+        if (f2u(b.w) & B2_MAT_TRANSPARENT) continue;
+        float t;
+        if (tri_test(ro, rd, mk3(a), mk3(b), mk3(c), tMin, tMax, t) && group_pass(sc, (int) f2u(c.w), ro, rd, tMin, tMax)) return true;
+    }
+    return occluded_spheres(sc, ro, rd, tMin, tMax);
+}
