@@ -1,0 +1,181 @@
+"""Python host side of the C ABI (include/b2pt.h).  Mirrors the reference's call surface for the BDPT path:
+
+    move_data_to_cuda_bdpt(groups, lights, spl)   -> Scene(scene_data)             (include/bdpt_cu_helper.h:5)
+    run_cuda_bdpt / run_cpu_bdpt(camera, ..., image, eye_depth, light_depth, W, H, spp, spl)
+                                                  -> Scene.render_bdpt(...)        (include/cpu_bdpt.h:9-17)
+    cpu_find_closest_hit / cpu_check_visibility   -> Scene.closest_hit / Scene.visibility   (src/cpu_bdpt.cpp:30,82)
+
+Everything computes in libb2pt.so (hand-written CUDA for sm_100a); there is no CPU fallback here.
+"""
+import ctypes as C
+import numpy as np
+from . import _abi as A
+from .scene import SceneData
+
+CLOSEST, ANY, BRUTE_FORCE, COUNT_VISITS = 0, 1, 16, 32
+FILM_MEAN, FILM_SUM = 0, 1
+
+
+def device_count():
+    n = C.c_int(0)
+    A.check(A.lib().b2_device_count(C.byref(n)))
+    return n.value
+
+
+def _f32(a, shape=None):
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    return a if shape is None else a.reshape(shape)
+
+
+class Scene:
+    """Device-resident scene + wide BVH (opaque B2Scene handle)."""
+
+    def __init__(self, data: SceneData, device=0, max_leaf_tris=0, pad_rel=0.0, build=True):
+        self.data = data
+        self._h = C.c_void_p()
+        L = A.lib()
+        A.check(L.b2_scene_create(A.ptr(data.tris), len(data.tris), A.ptr(data.spheres), len(data.spheres),
+                                  A.ptr(data.materials), len(data.materials), A.ptr(data.lights), len(data.lights),
+                                  int(device), C.byref(self._h)))
+        if build:
+            self.build_bvh(max_leaf_tris, pad_rel)
+
+    def build_bvh(self, max_leaf_tris=0, pad_rel=0.0):
+        p = A.BvhParams(int(max_leaf_tris), float(pad_rel))
+        A.check(A.lib().b2_scene_build_bvh(self._h, C.byref(p)))
+
+    def bvh_info(self):
+        info = A.BvhInfo()
+        A.check(A.lib().b2_scene_bvh_info(self._h, C.byref(info)))
+        return {n: getattr(info, n) for n, _ in info._fields_}
+
+    def close(self):
+        if self._h:
+            A.lib().b2_scene_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- ray queries ----
+    def closest_hit(self, org, dirs, brute_force=False, count=False):
+        org, dirs = _f32(org, (-1, 3)), _f32(dirs, (-1, 3))
+        n = len(org)
+        ids = np.full(n, -1, np.int32)
+        t = np.full(n, 1e20, np.float32)
+        mode = CLOSEST | (BRUTE_FORCE if brute_force else 0) | (COUNT_VISITS if count else 0)
+        A.check(A.lib().b2_intersect(self._h, A.ptr(org), A.ptr(dirs), n, mode, A.ptr(ids), A.ptr(t)))
+        return ids, t
+
+    def visibility(self, p1, p2, brute_force=False, count=False):
+        p1, p2 = _f32(p1, (-1, 3)), _f32(p2, (-1, 3))
+        n = len(p1)
+        vis = np.zeros(n, np.int32)
+        mode = ANY | (BRUTE_FORCE if brute_force else 0) | (COUNT_VISITS if count else 0)
+        A.check(A.lib().b2_intersect(self._h, A.ptr(p1), A.ptr(p2), n, mode, A.ptr(vis), None))
+        return vis
+
+    def intersect_device(self, d_org, d_dir, n, mode, d_prim_id, d_t=0, stream=0):
+        """Raw device pointers (ints), asynchronous on `stream`."""
+        A.check(A.lib().b2_intersect_device(self._h, C.c_void_p(d_org), C.c_void_p(d_dir), n, mode, C.c_void_p(d_prim_id),
+                                            C.c_void_p(d_t) if d_t else None, C.c_void_p(stream) if stream else None))
+
+    def intersect_counters(self, reset=True):
+        out = (C.c_uint64 * 3)()
+        A.check(A.lib().b2_intersect_counters(self._h, C.byref(out), 1 if reset else 0))
+        return dict(rays=out[0], nodes=out[1], tris=out[2])
+
+    # ---- render ----
+    def _params(self, width, height, spp, spl, eye_depth, light_depth, seed, sample_offset, sample_stride, film_mode,
+                max_delta, max_batch_paths, count_traversal):
+        return A.RenderParams(int(width), int(height), int(spp), int(spl), int(eye_depth), int(light_depth), int(seed),
+                              int(sample_offset), int(sample_stride), int(film_mode), 0, int(max_delta), int(max_batch_paths),
+                              1 if count_traversal else 0, 0)
+
+    def render_bdpt(self, camera=None, width=None, height=None, spp=8, spl=8, eye_depth=4, light_depth=4, seed=1,
+                    sample_offset=0, sample_stride=1, film_mode=FILM_MEAN, max_delta=0, max_batch_paths=0,
+                    count_traversal=False, out=None, device_ptr=None, stream=0):
+        """Returns (film[H,W,3] float32, stats dict).  With device_ptr (int) the film stays on the device and None is returned for it."""
+        cam = np.ascontiguousarray(self.data.camera if camera is None else camera, dtype=A.Camera).reshape(())
+        W = int(width if width else self.data.width)
+        H = int(height if height else self.data.height)
+        p = self._params(W, H, spp, spl, eye_depth, light_depth, seed, sample_offset, sample_stride, film_mode, max_delta,
+                         max_batch_paths, count_traversal)
+        st = A.Stats()
+        if device_ptr is not None:
+            A.check(A.lib().b2_render_bdpt_device(self._h, cam.ctypes.data_as(C.c_void_p), C.byref(p), C.c_void_p(int(device_ptr)),
+                                                  C.c_void_p(stream) if stream else None, C.byref(st)))
+            return None, st.as_dict()
+        film = out if out is not None else np.zeros((H, W, 3), np.float32)
+        assert film.dtype == np.float32 and film.size == 3 * W * H and film.flags["C_CONTIGUOUS"]
+        A.check(A.lib().b2_render_bdpt(self._h, cam.ctypes.data_as(C.c_void_p), C.byref(p), A.ptr(film), C.byref(st)))
+        return film, st.as_dict()
+
+    def light_pool(self, spl=8, light_depth=4, seed=1, max_delta=0):
+        n = len(self.data.lights) * spl * light_depth
+        out = np.zeros((n, 20), np.float32)
+        p = self._params(1, 1, 1, spl, 1, light_depth, seed, 0, 1, 0, max_delta, 0, False)
+        A.check(A.lib().b2_light_pool(self._h, C.byref(p), A.ptr(out)))
+        return out
+
+
+# ---- BSDF / MIS / RNG tables (device kernels over host arrays) ----
+def bsdf_evaluate(mtl, wo, wi, N):
+    mtl, wo, wi, N = _f32(mtl, (-1, 6)), _f32(wo, (-1, 3)), _f32(wi, (-1, 3)), _f32(N, (-1, 3))
+    out = np.zeros((len(mtl), 3), np.float32)
+    A.check(A.lib().b2_bsdf_evaluate(len(mtl), A.ptr(mtl), A.ptr(wo), A.ptr(wi), A.ptr(N), A.ptr(out)))
+    return out
+
+
+def bsdf_pdf(mtl, wo, wi, N):
+    mtl, wo, wi, N = _f32(mtl, (-1, 6)), _f32(wo, (-1, 3)), _f32(wi, (-1, 3)), _f32(N, (-1, 3))
+    out = np.zeros(len(mtl), np.float32)
+    A.check(A.lib().b2_bsdf_pdf(len(mtl), A.ptr(mtl), A.ptr(wo), A.ptr(wi), A.ptr(N), A.ptr(out)))
+    return out
+
+
+def bsdf_sample(mtl, wo, N, u, cur_eta):
+    mtl, wo, N, u, cur_eta = _f32(mtl, (-1, 6)), _f32(wo, (-1, 3)), _f32(N, (-1, 3)), _f32(u, (-1, 3)), _f32(cur_eta)
+    n = len(mtl)
+    wi = np.zeros((n, 3), np.float32); f = np.zeros((n, 3), np.float32)
+    pdf = np.zeros(n, np.float32); dl = np.zeros(n, np.int32); ne = np.zeros(n, np.float32)
+    A.check(A.lib().b2_bsdf_sample(n, A.ptr(mtl), A.ptr(wo), A.ptr(N), A.ptr(u), A.ptr(cur_eta), A.ptr(wi), A.ptr(f), A.ptr(pdf), A.ptr(dl), A.ptr(ne)))
+    return dict(wi=wi, f=f, pdf=pdf, is_delta=dl, new_eta=ne)
+
+
+def mis_weight(eye17, n_eye, s_idx, lit20, n_lit, t_idx, d_vec, dist2, cam_pos, max_verts):
+    """eye17: [n, max_verts, 17], lit20: [n, max_verts, 20]."""
+    eye17, lit20 = _f32(eye17, (-1, max_verts, 17)), _f32(lit20, (-1, max_verts, 20))
+    n = len(eye17)
+    i32 = lambda a: np.ascontiguousarray(a, dtype=np.int32)
+    n_eye, s_idx, n_lit, t_idx = i32(n_eye), i32(s_idx), i32(n_lit), i32(t_idx)
+    d_vec, dist2, cam_pos = _f32(d_vec, (-1, 3)), _f32(dist2), _f32(cam_pos, (-1, 3))
+    out = np.zeros(n, np.float32)
+    A.check(A.lib().b2_mis_weight(n, A.ptr(eye17), A.ptr(n_eye), A.ptr(s_idx), A.ptr(lit20), A.ptr(n_lit), A.ptr(t_idx),
+                                  A.ptr(d_vec), A.ptr(dist2), A.ptr(cam_pos), int(max_verts), A.ptr(out)))
+    return out
+
+
+def philox(ctr4, key2):
+    ctr4 = np.ascontiguousarray(ctr4, dtype=np.uint32).reshape(-1, 4)
+    key2 = np.ascontiguousarray(key2, dtype=np.uint32).reshape(-1, 2)
+    out = np.zeros_like(ctr4); unit = np.zeros(ctr4.shape, np.float32)
+    A.check(A.lib().b2_philox(len(ctr4), A.ptr(ctr4), A.ptr(key2), A.ptr(out), A.ptr(unit)))
+    return out, unit
+
+
+# ---- film output (main_cli.cpp:221-254) ----
+def film_to_rgb8(film):
+    film = _f32(film)
+    H, W = film.shape[0], film.shape[1]
+    out = np.zeros((H, W, 3), np.uint8)
+    A.check(A.lib().b2_film_to_rgb8(A.ptr(film), W, H, A.ptr(out)))
+    return out
+
+
+def write_image(path, film):
+    film = _f32(film)
+    A.check(A.lib().b2_write_image(str(path).encode(), A.ptr(film), film.shape[1], film.shape[0]))

@@ -1,0 +1,227 @@
+// b2_api.cu -- the extern "C" entry points of include/b2pt.h that touch the device: scene upload + BVH build,
+// ray queries, the BDPT render, the light pool and the table kernels.  Host-only entry points (scene grammar
+// parser, film writers) live in b2_host.cpp.  There is no CPU execution path in this library: every compute
+// call needs a CUDA device and fails with B2_ERR_NO_DEVICE otherwise.
+#include <cstdarg>
+#include <cstring>
+#include <mutex>
+#include "b2_device_scene.hpp"
+#include "b2_host_scene.hpp"
+#include "b2_queries.hpp"
+#include "b2_render.hpp"
+
+static thread_local char g_err[512] = "";
+void b2_set_error(const char *fmt, ...) {
+    va_list ap; va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+struct B2Scene {
+    int device = 0;
+    HostScene hs;
+    DevBuf<BuildTri> d_in;
+    DevBuf<float4> sph, lights, mats, groups;
+    DeviceBvh bvh;
+    bool built = false;
+    int max_leaf = 3;
+    cudaStream_t stream = nullptr;
+    DevBuf<unsigned long long> isect_counters;
+    RenderWorkspace ws;
+    std::mutex mtx;                       // one call in flight per handle
+    DevScene view() const {
+        DevScene v; memset(&v, 0, sizeof(v));
+        v.tri = bvh.tri.p; v.tri_obj = bvh.tri_obj.p; v.nodes = bvh.nodes.p;
+        v.sph = sph.p; v.lights = lights.p; v.mats = mats.p; v.groups = groups.p;
+        v.n_tris = bvh.n_tris; v.n_nodes = bvh.n_nodes; v.n_sph = hs.n_sph; v.n_lights = hs.n_lights; v.n_mats = hs.n_mats; v.n_groups = hs.n_groups;
+        v.scene_min = hs.scene_min; v.scene_max = hs.scene_max;
+        return v;
+    }
+};
+
+static int need_device(int device) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n <= 0) { cudaGetLastError(); b2_set_error("no CUDA device available (%s); libb2pt has no CPU fallback", e != cudaSuccess ? cudaGetErrorString(e) : "device count 0"); return B2_ERR_NO_DEVICE; }
+    if (device < 0 || device >= n) { b2_set_error("device %d out of range (0..%d)", device, n - 1); return B2_ERR_INVALID; }
+    B2_CUDA(cudaSetDevice(device));
+    return B2_OK;
+}
+template <class T> static int upload(DevBuf<T> &d, const std::vector<T> &h, cudaStream_t st) {
+    B2_TRY(d.alloc(h.size()));
+    if (!h.empty()) B2_CUDA(cudaMemcpyAsync(d.p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, st));
+    return B2_OK;
+}
+
+extern "C" {
+
+const char *b2_last_error(void) { return g_err; }
+const char *b2_version(void) { return "b2pt 0.1 (sm_100a)"; }
+int b2_device_count(int *count) {
+    if (!count) { b2_set_error("count is NULL"); return B2_ERR_INVALID; }
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) { cudaGetLastError(); n = 0; }
+    *count = n;
+    return B2_OK;
+}
+
+int b2_scene_create(const B2Tri *tris, size_t n_tris, const B2Sphere *spheres, size_t n_spheres, const B2Material *materials, size_t n_materials,
+                    const B2Light *lights, size_t n_lights, int device, B2Scene **out) {
+    if (!out) { b2_set_error("out is NULL"); return B2_ERR_INVALID; }
+    *out = nullptr;
+    if ((n_tris && !tris) || (n_spheres && !spheres) || (n_materials && !materials) || (n_lights && !lights)) { b2_set_error("NULL array with non-zero count"); return B2_ERR_INVALID; }
+    if (n_tris >= (1u << 28) || n_spheres >= (1u << 28) || n_lights >= (1u << 20)) { b2_set_error("scene too large"); return B2_ERR_INVALID; }
+    B2_TRY(need_device(device));
+    B2Scene *s = new B2Scene;
+    s->device = device;
+    const char *err = nullptr;
+    if (!flatten_scene(tris, n_tris, spheres, n_spheres, materials, n_materials, lights, n_lights, s->hs, &err)) { b2_set_error("%s", err ? err : "bad scene"); delete s; return B2_ERR_INVALID; }
+    int rc = B2_OK;
+    do {
+        if (cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking) != cudaSuccess) { b2_set_error("cudaStreamCreate failed"); rc = B2_ERR_CUDA; break; }
+        if ((rc = upload(s->d_in, s->hs.tris, s->stream)) != B2_OK) break;
+        if ((rc = upload(s->sph, s->hs.sph, s->stream)) != B2_OK) break;
+        if ((rc = upload(s->lights, s->hs.lights, s->stream)) != B2_OK) break;
+        if ((rc = upload(s->mats, s->hs.mats, s->stream)) != B2_OK) break;
+        if ((rc = upload(s->groups, s->hs.groups, s->stream)) != B2_OK) break;
+        if ((rc = s->isect_counters.alloc(3)) != B2_OK) break;
+        if (cudaMemsetAsync(s->isect_counters.p, 0, 3 * sizeof(unsigned long long), s->stream) != cudaSuccess || cudaStreamSynchronize(s->stream) != cudaSuccess) {
+            b2_set_error("scene upload failed: %s", cudaGetErrorString(cudaGetLastError())); rc = B2_ERR_CUDA; break;
+        }
+    } while (0);
+    if (rc != B2_OK) { b2_scene_destroy(s); return rc; }
+    *out = s;
+    return B2_OK;
+}
+
+void b2_scene_destroy(B2Scene *s) {
+    if (!s) return;
+    cudaSetDevice(s->device);
+    if (s->stream) { cudaStreamSynchronize(s->stream); cudaStreamDestroy(s->stream); }
+    delete s;
+}
+
+int b2_scene_build_bvh(B2Scene *s, const B2BvhParams *params) {
+    if (!s) { b2_set_error("scene is NULL"); return B2_ERR_INVALID; }
+    std::lock_guard<std::mutex> lk(s->mtx);
+    B2_CUDA(cudaSetDevice(s->device));
+    int max_leaf = (params && params->max_leaf_tris > 0) ? params->max_leaf_tris : 3;
+    if (max_leaf > 3) { b2_set_error("max_leaf_tris must be 1..3"); return B2_ERR_INVALID; }
+    const float pad_rel = (params && params->pad_rel > 0.0f) ? params->pad_rel : 3.8146973e-6f;   // 2^-18
+    const HostScene &hs = s->hs;
+    const float ext = std::max({ hs.scene_max.x - hs.scene_min.x, hs.scene_max.y - hs.scene_min.y, hs.scene_max.z - hs.scene_min.z });
+    const float pad = pad_rel * std::max(hs.max_abs, ext) + 1e-30f;
+    B2_TRY(b2_build_bvh_device(s->d_in.p, (int) hs.tris.size(), pad, max_leaf, s->stream, s->bvh));
+    s->built = true; s->max_leaf = max_leaf;
+    return B2_OK;
+}
+
+int b2_scene_bvh_info(const B2Scene *s, B2BvhInfo *info) {
+    if (!s || !info) { b2_set_error("NULL argument"); return B2_ERR_INVALID; }
+    if (!s->built) { b2_set_error("BVH not built: call b2_scene_build_bvh first"); return B2_ERR_STATE; }
+    memset(info, 0, sizeof(*info));
+    info->n_tris = (uint64_t) s->bvh.n_tris; info->n_nodes = (uint64_t) s->bvh.n_nodes;
+    info->node_bytes = (uint64_t) s->bvh.n_nodes * sizeof(uint4) * B2_NODE_UINT4; info->tri_bytes = (uint64_t) s->bvh.n_tris * 48u;
+    info->depth = s->bvh.depth; info->build_ms = s->bvh.build_ms; info->sah_cost = 0.0f;
+    return B2_OK;
+}
+
+static int check_built(B2Scene *s) {
+    if (!s) { b2_set_error("scene is NULL"); return B2_ERR_INVALID; }
+    if (!s->built) { b2_set_error("BVH not built: call b2_scene_build_bvh first"); return B2_ERR_STATE; }
+    return B2_OK;
+}
+
+int b2_intersect_device(B2Scene *s, const float *d_org, const float *d_dir, size_t n, int mode, int32_t *d_prim_id, float *d_t, void *stream) {
+    B2_TRY(check_built(s));
+    if (n && (!d_org || !d_dir || !d_prim_id)) { b2_set_error("NULL ray / result buffer"); return B2_ERR_INVALID; }
+    B2_CUDA(cudaSetDevice(s->device));
+    return b2_intersect_launch(s->view(), s->bvh.depth, d_org, d_dir, n, mode, d_prim_id, d_t, s->isect_counters.p, (cudaStream_t) stream);
+}
+
+int b2_intersect(B2Scene *s, const float *org, const float *dir, size_t n, int mode, int32_t *prim_id, float *t) {
+    B2_TRY(check_built(s));
+    if (n == 0) return B2_OK;
+    if (!org || !dir || !prim_id) { b2_set_error("NULL ray / result buffer"); return B2_ERR_INVALID; }
+    std::lock_guard<std::mutex> lk(s->mtx);
+    B2_CUDA(cudaSetDevice(s->device));
+    DevBuf<float> d_o, d_d, d_t; DevBuf<int32_t> d_id;
+    B2_TRY(d_o.alloc(3 * n)); B2_TRY(d_d.alloc(3 * n)); B2_TRY(d_id.alloc(n));
+    const bool want_t = t && !(mode & B2_ANY);
+    if (want_t) B2_TRY(d_t.alloc(n));
+    B2_CUDA(cudaMemcpyAsync(d_o.p, org, 3 * n * sizeof(float), cudaMemcpyHostToDevice, s->stream));
+    B2_CUDA(cudaMemcpyAsync(d_d.p, dir, 3 * n * sizeof(float), cudaMemcpyHostToDevice, s->stream));
+    B2_TRY(b2_intersect_launch(s->view(), s->bvh.depth, d_o.p, d_d.p, n, mode, d_id.p, want_t ? d_t.p : nullptr, s->isect_counters.p, s->stream));
+    B2_CUDA(cudaMemcpyAsync(prim_id, d_id.p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, s->stream));
+    if (want_t) B2_CUDA(cudaMemcpyAsync(t, d_t.p, n * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
+    B2_CUDA(cudaStreamSynchronize(s->stream));
+    return B2_OK;
+}
+
+int b2_intersect_counters(B2Scene *s, uint64_t out[3], int reset) {
+    if (!s || !out) { b2_set_error("NULL argument"); return B2_ERR_INVALID; }
+    B2_CUDA(cudaSetDevice(s->device));
+    B2_CUDA(cudaDeviceSynchronize());
+    unsigned long long h[3];
+    B2_CUDA(cudaMemcpy(h, s->isect_counters.p, sizeof(h), cudaMemcpyDeviceToHost));
+    out[0] = h[0]; out[1] = h[1]; out[2] = h[2];
+    if (reset) B2_CUDA(cudaMemset(s->isect_counters.p, 0, sizeof(h)));
+    return B2_OK;
+}
+
+int b2_render_bdpt_device(B2Scene *s, const B2Camera *cam, const B2RenderParams *params, float *d_film_rgb, void *stream, B2Stats *stats) {
+    B2_TRY(check_built(s));
+    if (!cam || !params || !d_film_rgb) { b2_set_error("NULL argument"); return B2_ERR_INVALID; }
+    std::lock_guard<std::mutex> lk(s->mtx);
+    B2_CUDA(cudaSetDevice(s->device));
+    return b2_render_device_impl(s->view(), s->bvh.depth, s->ws, *cam, *params, d_film_rgb, stream ? (cudaStream_t) stream : s->stream, stats);
+}
+
+int b2_render_bdpt(B2Scene *s, const B2Camera *cam, const B2RenderParams *params, float *film_rgb_host, B2Stats *stats) {
+    B2_TRY(check_built(s));
+    if (!cam || !params || !film_rgb_host) { b2_set_error("NULL argument"); return B2_ERR_INVALID; }
+    if (params->width <= 0 || params->height <= 0) { b2_set_error("invalid film size"); return B2_ERR_INVALID; }
+    std::lock_guard<std::mutex> lk(s->mtx);
+    B2_CUDA(cudaSetDevice(s->device));
+    const size_t nf = (size_t) 3 * params->width * params->height;
+    DevBuf<float> d_film;
+    B2_TRY(d_film.alloc(nf));
+    B2_TRY(b2_render_device_impl(s->view(), s->bvh.depth, s->ws, *cam, *params, d_film.p, s->stream, stats));
+    B2_CUDA(cudaMemcpyAsync(film_rgb_host, d_film.p, nf * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
+    B2_CUDA(cudaStreamSynchronize(s->stream));
+    return B2_OK;
+}
+
+int b2_light_pool(B2Scene *s, const B2RenderParams *params, float *pool20_host) {
+    B2_TRY(check_built(s));
+    if (!params || !pool20_host) { b2_set_error("NULL argument"); return B2_ERR_INVALID; }
+    std::lock_guard<std::mutex> lk(s->mtx);
+    B2_CUDA(cudaSetDevice(s->device));
+    return b2_light_pool_impl(s->view(), s->bvh.depth, s->ws, *params, pool20_host, s->stream);
+}
+
+int b2_bsdf_evaluate(size_t n, const float *mtl6, const float *wo, const float *wi, const float *N, float *out3) {
+    B2_TRY(need_device(0));
+    return b2_tables_bsdf_evaluate(n, mtl6, wo, wi, N, out3);
+}
+int b2_bsdf_pdf(size_t n, const float *mtl6, const float *wo, const float *wi, const float *N, float *out) {
+    B2_TRY(need_device(0));
+    return b2_tables_bsdf_pdf(n, mtl6, wo, wi, N, out);
+}
+int b2_bsdf_sample(size_t n, const float *mtl6, const float *wo, const float *N, const float *u3, const float *cur_eta,
+                   float *wi_out, float *f_out, float *pdf_out, int32_t *delta_out, float *eta_out) {
+    B2_TRY(need_device(0));
+    return b2_tables_bsdf_sample(n, mtl6, wo, N, u3, cur_eta, wi_out, f_out, pdf_out, delta_out, eta_out);
+}
+int b2_mis_weight(size_t n, const float *eye17, const int32_t *n_eye, const int32_t *s_idx, const float *lit20, const int32_t *n_lit,
+                  const int32_t *t_idx, const float *d_vec, const float *dist2, const float *cam_pos, int32_t max_verts, float *out) {
+    B2_TRY(need_device(0));
+    return b2_tables_mis_weight(n, eye17, n_eye, s_idx, lit20, n_lit, t_idx, d_vec, dist2, cam_pos, max_verts, out);
+}
+int b2_philox(size_t n, const uint32_t *ctr4, const uint32_t *key2, uint32_t *out4, float *unit_out4) {
+    B2_TRY(need_device(0));
+    return b2_tables_philox(n, ctr4, key2, out4, unit_out4);
+}
+
+}  // extern "C"

@@ -7,10 +7,12 @@
 //
 // Stages of one wave (all paths of a batch advance one bounce):
 //   closest  : ray -> (prim, t)                              [closest_hit_bvh]
-//   shade    : hit -> eye vertex record (CV) + BSDF sample + next ray / termination
-//   connect  : CV x pool vertex -> weighted contribution + shadow segment, appended to the shadow queue
-//   shadow   : any-hit test of each queued segment; visible ones are splatted into the film (atomicAdd)
-//   compact  : surviving path ids -> next wave's queue
+//   shade    : hit -> eye vertex record (CV) + BSDF sample + next ray / termination; survivors are
+//              compacted into the next wave's queue (warp ballot + prefix)
+//   connect  : CV x pool vertex: cheap pre-tests (connect_pretest) for every pair; surviving pairs are
+//              compacted in shared memory and finished at full lane occupancy (connect_finish: BSDFs,
+//              shadow segment any-hit, MIS weight) into the path's radiance accumulator
+//   flush    : at the end of a batch every path adds its accumulator to the film (atomicAdd)
 #pragma once
 #include "b2_bvh.cuh"
 #include "b2_rng.cuh"
@@ -57,10 +59,7 @@ B2_HD void store_cv(float4 *cv, int q, const EyeVtx &v) {
 }
 #define B2_CV_NONE 0xffffffffu     // depth field of a queue slot that produced no eye vertex this wave
 
-// ---- shadow-queue entry: 3 x float4 (48 B) = {origin, tmax} {dir, pixel} {contribution, 0} ----
-#define B2_SQ_F4 3
-
-enum { B2_CNT_EYE_SAMPLES = 0, B2_CNT_CLOSEST, B2_CNT_SHADOW, B2_CNT_PATH_SAMPLES, B2_CNT_DELTA_CAP, B2_CNT_NODES, B2_CNT_TRIS, B2_CNT_SQ_OVERFLOW, B2_CNT_N };
+enum { B2_CNT_EYE_SAMPLES = 0, B2_CNT_CLOSEST, B2_CNT_SHADOW, B2_CNT_PATH_SAMPLES, B2_CNT_DELTA_CAP, B2_CNT_NODES, B2_CNT_TRIS, B2_CNT_PAIRS, B2_CNT_N };
 
 struct RenderCtx {
     DevScene sc;
@@ -86,7 +85,7 @@ struct RenderCtx {
     int *live;          // queue of live path ids for this wave
     int *live_next; int *n_live_next;
     float4 *cv;         // eye-vertex records, indexed by queue slot
-    float4 *sq; uint32_t *n_sq; uint32_t sq_cap;
+    float4 *acc;        // {radiance accumulated by this path over all its vertices, -}
     float *film;        // W*H*3 running sums
     unsigned long long *counters;
 };
@@ -241,6 +240,7 @@ B2_HD void eye_gen_body(const RenderCtx &c, int i, long long w0) {
     c.last_pos[i] = mk4(c.cam_eye, 0.0f);
     c.last_n[i] = mk4(d, 0.0f);
     c.pix[i] = pixel; c.sidx[i] = s; c.pstate[i] = 0u;
+    c.acc[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     c.live[i] = i;
 }
 
@@ -258,11 +258,8 @@ B2_HD bool shade_body(const RenderCtx &c, int q, uint32_t &n_emit_hits, uint32_t
     const Surface s = surface_at(sc, ro, rd, h);
     const uint32_t ps = c.pstate[path];
     int depth = (int) (ps & 0xffu), n_delta = (int) (ps >> 8);
-    const uint32_t pixel = c.pix[path];
     if (s.is_light && depth == 0) {                                        // :372-375
-        if (valid_color(s.mtl.base)) {
-            atomic_add_f32(&c.film[3 * pixel], s.mtl.base.x); atomic_add_f32(&c.film[3 * pixel + 1], s.mtl.base.y); atomic_add_f32(&c.film[3 * pixel + 2], s.mtl.base.z);
-        }
+        if (valid_color(s.mtl.base)) c.acc[path] = mk4(s.mtl.base, 0.0f);   // depth 0: nothing accumulated before
         n_emit_hits++;
         return false;
     }
@@ -276,7 +273,7 @@ B2_HD bool shade_body(const RenderCtx &c, int q, uint32_t &n_emit_hits, uint32_t
     EyeVtx ev; ev.pos = s.pos; ev.n = s.n; ev.wo = wo; ev.thr = thr; ev.mtl = s.mtl; ev.depth = depth; ev.path = path;
     store_cv(c.cv, q, ev);
     float u_rr, u1, u2;
-    rng_draw3(c.key, B2_RNG_EYE, pixel, c.sidx[path], (uint32_t) (depth + n_delta), u_rr, u1, u2);
+    rng_draw3(c.key, B2_RNG_EYE, c.pix[path], c.sidx[path], (uint32_t) (depth + n_delta), u_rr, u1, u2);
     BsdfSample bs; bs.wi = mk3(0, 0, 0); bs.f = mk3(0, 0, 0); bs.pdf = 0.0f;
     bsdf_sample(s.mtl, wo, s.n, u_rr, u1, u2, o4.w, bs);
     if (bs.pdf <= 0.0f && !bs.is_delta) return false;
@@ -307,105 +304,125 @@ B2_HD bool shade_body(const RenderCtx &c, int q, uint32_t &n_emit_hits, uint32_t
 }
 
 // =====================================================================================================
-// MIS weight (cpu_calculate_mis_weight, cpu_bdpt.cpp:112-167) for eye vertex `ev` (s_idx = ev.depth) and pool
-// vertex lv_index (t_idx = lv_index % light_depth).  d_vec is passed UNNORMALISED, as the reference does (:431).
-// At connection time the current eye vertex still carries the placeholders pdf_fwd = 0, pdf_rev = 1 (:385).
+// MIS weight (cpu_calculate_mis_weight, cpu_bdpt.cpp:112-167), written once over vertex accessors so the
+// render (per-path history arrays + pool records) and the table kernel behind b2_mis_weight (flat arrays)
+// share it.  d_vec is passed UNNORMALISED, as the reference does (:431).
+//   EA: pos(i) eta(i) pdf_fwd(i) pdf_rev(i) of eye vertex i; cur_n / cur_mtl of vertex s_idx
+//   LA: pos(i) eta(i) pdf_fwd(i) pdf_rev(i) is_src(i) of light vertex i of the SAME light subpath; cur_n / cur_mtl of t_idx
 // =====================================================================================================
-B2_HD float mis_weight_body(const RenderCtx &c, const EyeVtx &ev, const LightVtx &lv, int lv_index, int t_idx, float3 d_vec, float dist2) {
-    const int s_idx = ev.depth;
-    const float3 ns = normalize3(ev.n), nt = normalize3(lv.n);
+template <class EA, class LA>
+B2_HD float mis_weight_core(const EA &E, int s_idx, const LA &L, int t_idx, float3 d_vec, float dist2, float3 cam_pos) {
+    if (s_idx < 0 || t_idx < 0) return 0.0f;
+    const float3 ns = normalize3(E.cur_n()), nt = normalize3(L.cur_n());
     const float3 md = d_vec * -1.0f;
     const float cos_s = fmaxf(0.0f, dot3(ns, d_vec));
     const float cos_t = fmaxf(0.0f, dot3(nt, md));
     if (cos_s <= 0.0f || cos_t <= 0.0f || dist2 < 1e-6f) return 0.0f;
-    const float3 prev_e = (s_idx == 0) ? c.cam_eye : mk3(c.hist_pe[(size_t) (s_idx - 1) * c.max_paths + ev.path]);
-    const float3 wo_s = normalize3(prev_e - ev.pos);
-    const float3 wo_t = (t_idx == 0) ? normalize3(lv.n) : normalize3(mk3(c.pool[B2_LV_F4 * (lv_index - 1)]) - lv.pos);
-    const float pdf_omega_s = fmaxf(bsdf_pdf(ev.mtl, wo_s, d_vec, ns), 1e-6f);
-    const float pdf_omega_t = fmaxf(bsdf_pdf(lv.mtl, wo_t, md, nt), 1e-6f);
+    const float3 ev_pos = E.pos(s_idx), lv_pos = L.pos(t_idx);
+    const float3 wo_s = normalize3(((s_idx == 0) ? cam_pos : E.pos(s_idx - 1)) - ev_pos);
+    const float3 wo_t = (t_idx == 0) ? normalize3(L.cur_n()) : normalize3(L.pos(t_idx - 1) - lv_pos);
+    const float pdf_omega_s = fmaxf(bsdf_pdf(E.cur_mtl(), wo_s, d_vec, ns), 1e-6f);
+    const float pdf_omega_t = fmaxf(bsdf_pdf(L.cur_mtl(), wo_t, md, nt), 1e-6f);
     const float pdf_s_to_t = pdf_omega_s * cos_t / dist2;
     const float pdf_t_to_s = pdf_omega_t * cos_s / dist2;
     float sum = 1.0f, ratio = 1.0f, prev_rev = pdf_t_to_s;
     for (int i = s_idx; i > 0; --i) {                                      // :143-148
-        float eta_i, fwd_i, rev_i;
-        if (i == s_idx) { eta_i = ev.mtl.eta; fwd_i = 0.0f; rev_i = 1.0f; }
-        else {
-            eta_i = c.hist_pe[(size_t) i * c.max_paths + ev.path].w;
-            const float2 p = c.hist_pdf[(size_t) i * c.max_paths + ev.path];
-            fwd_i = p.x; rev_i = p.y;
-        }
-        if (eta_i > 0.0f) break;
-        ratio *= prev_rev / fmaxf(fwd_i, 1e-8f);
+        if (E.eta(i) > 0.0f) break;
+        ratio *= prev_rev / fmaxf(E.pdf_fwd(i), 1e-8f);
         sum += ratio;
-        prev_rev = rev_i;
+        prev_rev = E.pdf_rev(i);
     }
     ratio = 1.0f; prev_rev = pdf_s_to_t;
-    const int base = lv_index - t_idx;
     for (int i = t_idx; i > 0; --i) {                                      // :153-163
-        const float4 f0 = c.pool[B2_LV_F4 * (base + i)], f2 = c.pool[B2_LV_F4 * (base + i) + 2];
-        if (f2u(f0.w) & B2_LV_SRC) { ratio *= prev_rev / fmaxf(f2.w, 1e-8f); sum += ratio; break; }
-        if (c.pool[B2_LV_F4 * (base + i) + 4].z > 0.0f) break;
-        ratio *= prev_rev / fmaxf(f2.w, 1e-8f);
+        if (L.is_src(i)) { ratio *= prev_rev / fmaxf(L.pdf_fwd(i), 1e-8f); sum += ratio; break; }
+        if (L.eta(i) > 0.0f) break;
+        ratio *= prev_rev / fmaxf(L.pdf_fwd(i), 1e-8f);
         sum += ratio;
-        prev_rev = c.pool[B2_LV_F4 * (base + i) + 3].w;
+        prev_rev = L.pdf_rev(i);
     }
     if (isnan(sum) || isinf(sum) || sum <= 0.0f) return 0.0f;
     return 1.0f / sum;
 }
 
+// Render-side accessors.  At connection time the current eye vertex still carries the placeholders
+// pdf_fwd = 0, pdf_rev = 1 (cpu_bdpt.cpp:385); earlier vertices come from the path's history arrays.
+struct RenderEyeAcc {
+    const RenderCtx &c; const EyeVtx &ev;
+    B2_HD float3 pos(int i) const { return i == ev.depth ? ev.pos : mk3(c.hist_pe[(size_t) i * c.max_paths + ev.path]); }
+    B2_HD float eta(int i) const { return i == ev.depth ? ev.mtl.eta : c.hist_pe[(size_t) i * c.max_paths + ev.path].w; }
+    B2_HD float pdf_fwd(int i) const { return i == ev.depth ? 0.0f : c.hist_pdf[(size_t) i * c.max_paths + ev.path].x; }
+    B2_HD float pdf_rev(int i) const { return i == ev.depth ? 1.0f : c.hist_pdf[(size_t) i * c.max_paths + ev.path].y; }
+    B2_HD float3 cur_n() const { return ev.n; }
+    B2_HD const Mat &cur_mtl() const { return ev.mtl; }
+};
+struct RenderLightAcc {
+    const RenderCtx &c; const LightVtx &lv; int base;        // base = pool index of the subpath's vertex 0
+    B2_HD float3 pos(int i) const { return mk3(c.pool[B2_LV_F4 * (base + i)]); }
+    B2_HD float eta(int i) const { return c.pool[B2_LV_F4 * (base + i) + 4].z; }
+    B2_HD float pdf_fwd(int i) const { return c.pool[B2_LV_F4 * (base + i) + 2].w; }
+    B2_HD float pdf_rev(int i) const { return c.pool[B2_LV_F4 * (base + i) + 3].w; }
+    B2_HD bool is_src(int i) const { return (f2u(c.pool[B2_LV_F4 * (base + i)].w) & B2_LV_SRC) != 0u; }
+    B2_HD float3 cur_n() const { return lv.n; }
+    B2_HD const Mat &cur_mtl() const { return lv.mtl; }
+};
+
 // =====================================================================================================
-// Connection of one eye vertex with one pool vertex (cpu_bdpt.cpp:389-439 up to the visibility query).
-// Returns true when a shadow segment has to be traced; `e` then holds the queue entry (contribution already
-// MIS-weighted and clamped; the shadow stage multiplies it by the 0/1 transmittance).
+// Connection of one eye vertex with one pool vertex (cpu_bdpt.cpp:389-439), split in two:
+//   connect_pretest : the geometric rejects up to and including the spot-cone gate (:391-409); needs only
+//                     pos/normal of both ends, so it is what runs for EVERY (eye vertex, pool vertex) pair
+//   connect_finish  : BSDFs, black skip, visibility, G, MIS, clamp (:411-438) for the surviving pairs
+// Pool vertices with |throughput| < 1e-6 (:391) never reach either: they are not in the active list.
 // =====================================================================================================
-struct ShadowEntry { float3 o; float tmax; float3 d; uint32_t pixel; float3 contrib; };
-B2_HD bool connect_pair(const RenderCtx &c, const EyeVtx &ev, uint32_t pixel, int lv_index, ShadowEntry &e) {
-    const LightVtx lv = load_lv(c.pool, lv_index);
-    const float3 d_vec = lv.pos - ev.pos;
+B2_HD bool connect_pretest(const RenderCtx &c, float3 ev_pos, float3 ev_n, int lv_index) {
+    const float4 f0 = c.pool[B2_LV_F4 * lv_index], f1 = c.pool[B2_LV_F4 * lv_index + 1];
+    const float3 d_vec = mk3(f0) - ev_pos;
     const float dist2 = dot3(d_vec, d_vec);
     if (dist2 < 1e-6f) return false;
     const float dist = sqrtf(dist2);
     const float3 wi = d_vec / dist;
     const float3 mwi = wi * -1.0f;
+    const float cosE = fmaxf(0.0f, dot3(ev_n, wi));
+    const float cosL = fmaxf(0.0f, dot3(mk3(f1), mwi));
+    if (cosE <= 0.0f || cosL <= 0.0f) return false;
+    const uint32_t flags = f2u(f0.w);
+    if ((flags & B2_LV_SRC) && f1.w > 0.0f && !(flags & B2_LV_PARALLEL)) {  // spot-cone gate, :405-409
+        const int li = (lv_index / c.light_depth) % c.sc.n_lights;
+        const float4 l3 = c.sc.lights[4 * li + 3];              // {normalize(light.dir), cosf(light.cutoff)}
+        if (dot3(mk3(l3), mwi) < l3.w) return false;
+    }
+    return true;
+}
+// Returns the (validated, clamped) contribution, zero if the pair contributes nothing.  n_shadow / n_path count
+// visibility queries (:424) and connections that reach the MIS evaluation (:431).
+template <bool COUNT>
+B2_HD float3 connect_finish(const RenderCtx &c, const EyeVtx &ev, int lv_index, uint2 *stack, int sstride, TravCounters *tc,
+                            uint32_t &n_shadow, uint32_t &n_path) {
+    const float3 zero = mk3(0.0f, 0.0f, 0.0f);
+    const LightVtx lv = load_lv(c.pool, lv_index);
+    const float3 d_vec = lv.pos - ev.pos;
+    const float dist2 = dot3(d_vec, d_vec);
+    const float dist = sqrtf(dist2);
+    const float3 wi = d_vec / dist;
+    const float3 mwi = wi * -1.0f;
     const float cosE = fmaxf(0.0f, dot3(ev.n, wi));
     const float cosL = fmaxf(0.0f, dot3(lv.n, mwi));
-    if (cosE <= 0.0f || cosL <= 0.0f) return false;
     const int t_idx = lv_index % c.light_depth;
-    const bool is_src = lv.flags & B2_LV_SRC;
-    if (is_src && lv.cutoff > 0.0f && !(lv.flags & B2_LV_PARALLEL)) {      // spot-cone gate, :405-409
-        const int li = (lv_index / c.light_depth) % c.sc.n_lights;
-        const float4 l3 = c.sc.lights[4 * li + 3];
-        if (dot3(mk3(l3), mwi) < l3.w) return false;            // l3.w = cosf(light.cutoff) == cosf(lv.source_cutoff)
-    }
-    const float3 fE = bsdf_evaluate(ev.mtl, ev.wo, wi, ev.n);
+    const bool is_src = (lv.flags & B2_LV_SRC) != 0u;
+    const float3 fE = bsdf_evaluate(ev.mtl, ev.wo, wi, ev.n);                 // :411-412
     float3 fL = mk3(1.0f, 1.0f, 1.0f);
-    if (!is_src && t_idx > 0) {
+    if (!is_src && t_idx > 0) {                                               // :413-419 (previous STORED vertex)
         const float3 wo_l = normalize3(mk3(c.pool[B2_LV_F4 * (lv_index - 1)]) - lv.pos);
         fL = bsdf_evaluate(lv.mtl, wo_l, mwi, lv.n);
     }
-    if ((fE.x <= 0.0f && fE.y <= 0.0f && fE.z <= 0.0f) || (fL.x <= 0.0f && fL.y <= 0.0f && fL.z <= 0.0f)) return false;
-    const float G = (cosE * cosL) / fmaxf(dist2, 1e-4f);
-    const float w = mis_weight_body(c, ev, lv, lv_index, t_idx, d_vec, dist2);
-    float3 contrib = ev.thr * fE * G * fL * lv.thr * w;
-    contrib = valid_color(contrib) ? clamp_radiance(contrib, 15.0f) : mk3(0.0f, 0.0f, 0.0f);
+    if ((fE.x <= 0.0f && fE.y <= 0.0f && fE.z <= 0.0f) || (fL.x <= 0.0f && fL.y <= 0.0f && fL.z <= 0.0f)) return zero;
     const ShadowRay sr = make_shadow_ray(x3_add(ev.pos, x3_muls(ev.n, B2_EPSILON)), x3_add(lv.pos, x3_muls(lv.n, B2_EPSILON)));   // :424
-    e.o = sr.o; e.tmax = sr.tmax; e.d = sr.d; e.pixel = pixel; e.contrib = contrib;
-    return true;
-}
-B2_HD void store_sq(float4 *sq, size_t slot, const ShadowEntry &e) {
-    sq[B2_SQ_F4 * slot] = mk4(e.o, e.tmax);
-    sq[B2_SQ_F4 * slot + 1] = mk4(e.d, u2f(e.pixel));
-    sq[B2_SQ_F4 * slot + 2] = mk4(e.contrib, 0.0f);
-}
-// Shadow stage for queue slot k: returns true if the segment is unoccluded (and splats its contribution).
-template <bool COUNT>
-B2_HD bool shadow_body(const RenderCtx &c, size_t k, uint2 *stack, int sstride, TravCounters *tc) {
-    const float4 a = c.sq[B2_SQ_F4 * k], b = c.sq[B2_SQ_F4 * k + 1];
-    if (occluded_bvh<COUNT>(c.sc, mk3(a), mk3(b), a.w, stack, sstride, tc)) return false;
-    const float4 cc = c.sq[B2_SQ_F4 * k + 2];
-    const uint32_t pixel = f2u(b.w);
-    if (cc.x != 0.0f) atomic_add_f32(&c.film[3 * pixel], cc.x);
-    if (cc.y != 0.0f) atomic_add_f32(&c.film[3 * pixel + 1], cc.y);
-    if (cc.z != 0.0f) atomic_add_f32(&c.film[3 * pixel + 2], cc.z);
-    return true;
+    n_shadow++;
+    if (occluded_bvh<COUNT>(c.sc, sr.o, sr.d, sr.tmax, stack, sstride, tc)) return zero;
+    const float G = (cosE * cosL) / fmaxf(dist2, 1e-4f);                      // :427
+    const RenderEyeAcc EA{ c, ev };
+    const RenderLightAcc LA{ c, lv, lv_index - t_idx };
+    const float w = mis_weight_core(EA, ev.depth, LA, t_idx, d_vec, dist2, c.cam_eye);   // :431
+    n_path++;
+    const float3 contrib = ev.thr * fE * G * fL * lv.thr * w;                 // :433 (transmittance == 1 here)
+    return valid_color(contrib) ? clamp_radiance(contrib, 15.0f) : zero;      // :435-437
 }

@@ -1,0 +1,199 @@
+// b2_queries.cu -- batch kernels behind b2_intersect* (ray queries) and the BSDF / MIS / Philox table entry
+// points of include/b2pt.h.  One item per thread; the closest-hit / any-hit kernels are the same traversal
+// code the renderer uses (b2_bvh.cuh), with shared-memory stacks.
+#include "b2_queries.hpp"
+#include "b2_bdpt.cuh"
+
+namespace {
+
+constexpr int Q_THREADS = 128;
+
+__device__ __forceinline__ int public_id(const DevScene &sc, int prim) {
+    if (prim == B2_PRIM_MISS) return -1;
+    const int k = prim_kind(prim), i = prim_index(prim);
+    if (k == B2_KIND_TRI) return sc.tri_obj[i];
+    if (k == B2_KIND_SPHERE) return (int) __float_as_uint(sc.sph[2 * i + 1].w);
+    return -2 - i;
+}
+__device__ __forceinline__ void warp_add64(unsigned long long *p, uint32_t v) {
+    v = __reduce_add_sync(0xffffffffu, v);
+    if ((threadIdx.x & 31) == 0 && v) atomicAdd(p, (unsigned long long) v);
+}
+__device__ __forceinline__ float3 ld3(const float *p, size_t i) { return make_float3(p[3 * i], p[3 * i + 1], p[3 * i + 2]); }
+__device__ __forceinline__ void st3(float *p, size_t i, float3 v) { p[3 * i] = v.x; p[3 * i + 1] = v.y; p[3 * i + 2] = v.z; }
+
+// MODE bit 0: any-hit; BRUTE: exhaustive kernels; COUNT: visit counters
+template <bool ANY, bool BRUTE, bool COUNT>
+__global__ void __launch_bounds__(Q_THREADS) k_intersect(DevScene sc, const float *__restrict__ org, const float *__restrict__ dir, size_t n,
+                                                         int32_t *__restrict__ prim_id, float *__restrict__ t_out, unsigned long long *counters) {
+    extern __shared__ uint2 s_stack[];
+    TravCounters tc{ 0u, 0u };
+    uint32_t rays = 0;
+    for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
+        const float3 a = ld3(org, i), b = ld3(dir, i);
+        rays++;
+        if (!ANY) {
+            const HitRec h = BRUTE ? closest_hit_brute(sc, a, b) : closest_hit_bvh<COUNT>(sc, a, b, s_stack + threadIdx.x, blockDim.x, &tc);
+            prim_id[i] = public_id(sc, h.prim);
+            if (t_out) t_out[i] = h.t;
+        } else {
+            const ShadowRay sr = make_shadow_ray(a, b);
+            const bool occ = BRUTE ? occluded_brute(sc, sr.o, sr.d, sr.tmax) : occluded_bvh<COUNT>(sc, sr.o, sr.d, sr.tmax, s_stack + threadIdx.x, blockDim.x, &tc);
+            prim_id[i] = occ ? 0 : 1;
+        }
+    }
+    if (COUNT) {
+        // every thread of a warp reaches here (the loop above has no early return)
+        warp_add64(&counters[0], rays); warp_add64(&counters[1], tc.nodes); warp_add64(&counters[2], tc.tris);
+    }
+}
+
+__device__ __forceinline__ Mat ld_mat(const float *m, size_t i) {
+    Mat r; r.base = make_float3(m[6 * i], m[6 * i + 1], m[6 * i + 2]); r.roughness = m[6 * i + 3]; r.metallic = m[6 * i + 4]; r.eta = m[6 * i + 5];
+    return r;
+}
+__global__ void k_bsdf_evaluate(size_t n, const float *mtl, const float *wo, const float *wi, const float *N, float *out) {
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) st3(out, i, bsdf_evaluate(ld_mat(mtl, i), ld3(wo, i), ld3(wi, i), ld3(N, i)));
+}
+__global__ void k_bsdf_pdf(size_t n, const float *mtl, const float *wo, const float *wi, const float *N, float *out) {
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = bsdf_pdf(ld_mat(mtl, i), ld3(wo, i), ld3(wi, i), ld3(N, i));
+}
+__global__ void k_bsdf_sample(size_t n, const float *mtl, const float *wo, const float *N, const float *u, const float *cur_eta,
+                              float *wi_out, float *f_out, float *pdf_out, int32_t *delta_out, float *eta_out) {
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    BsdfSample s; s.wi = make_float3(0, 0, 0); s.f = make_float3(0, 0, 0); s.pdf = 0.0f; s.new_eta = 0.0f; s.is_delta = false;
+    bsdf_sample(ld_mat(mtl, i), ld3(wo, i), ld3(N, i), u[3 * i], u[3 * i + 1], u[3 * i + 2], cur_eta[i], s);
+    st3(wi_out, i, s.wi); st3(f_out, i, s.f); pdf_out[i] = s.pdf; delta_out[i] = s.is_delta ? 1 : 0; eta_out[i] = s.new_eta;
+}
+
+// flat vertex accessors: eye (17) pos3 normal3 thr3 mtl6 pdf_fwd pdf_rev; light (20) ... is_src is_parallel cutoff pdf_fwd pdf_rev
+struct FlatEyeAcc {
+    const float *v; int s;
+    __device__ float3 pos(int i) const { return make_float3(v[17 * i], v[17 * i + 1], v[17 * i + 2]); }
+    __device__ float eta(int i) const { return v[17 * i + 14]; }
+    __device__ float pdf_fwd(int i) const { return v[17 * i + 15]; }
+    __device__ float pdf_rev(int i) const { return v[17 * i + 16]; }
+    __device__ float3 cur_n() const { return make_float3(v[17 * s + 3], v[17 * s + 4], v[17 * s + 5]); }
+    __device__ Mat cur_mtl() const { return ld_mat(v + 17 * (size_t) s + 9, 0); }
+};
+struct FlatLightAcc {
+    const float *v; int t;
+    __device__ float3 pos(int i) const { return make_float3(v[20 * i], v[20 * i + 1], v[20 * i + 2]); }
+    __device__ float eta(int i) const { return v[20 * i + 14]; }
+    __device__ bool is_src(int i) const { return v[20 * i + 15] != 0.0f; }
+    __device__ float pdf_fwd(int i) const { return v[20 * i + 18]; }
+    __device__ float pdf_rev(int i) const { return v[20 * i + 19]; }
+    __device__ float3 cur_n() const { return make_float3(v[20 * t + 3], v[20 * t + 4], v[20 * t + 5]); }
+    __device__ Mat cur_mtl() const { return ld_mat(v + 20 * (size_t) t + 9, 0); }
+};
+__global__ void k_mis_weight(size_t n, const float *eye17, const int32_t *n_eye, const int32_t *s_idx, const float *lit20, const int32_t *n_lit,
+                             const int32_t *t_idx, const float *d_vec, const float *dist2, const float *cam_pos, int max_verts, float *out) {
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int s = s_idx[i], t = t_idx[i];
+    if (s < 0 || t < 0 || s >= n_eye[i] || t >= n_lit[i] || s >= max_verts || t >= max_verts) { out[i] = 0.0f; return; }
+    const FlatEyeAcc E{ eye17 + (size_t) 17 * max_verts * i, s };
+    const FlatLightAcc L{ lit20 + (size_t) 20 * max_verts * i, t };
+    out[i] = mis_weight_core(E, s, L, t, ld3(d_vec, i), dist2[i], ld3(cam_pos, i));
+}
+__global__ void k_philox(size_t n, const uint32_t *ctr4, const uint32_t *key2, uint32_t *out4, float *unit4) {
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint4 o = philox4x32_10(make_uint4(ctr4[4 * i], ctr4[4 * i + 1], ctr4[4 * i + 2], ctr4[4 * i + 3]), make_uint2(key2[2 * i], key2[2 * i + 1]));
+    out4[4 * i] = o.x; out4[4 * i + 1] = o.y; out4[4 * i + 2] = o.z; out4[4 * i + 3] = o.w;
+    if (unit4) { unit4[4 * i] = u32_to_unit(o.x); unit4[4 * i + 1] = u32_to_unit(o.y); unit4[4 * i + 2] = u32_to_unit(o.z); unit4[4 * i + 3] = u32_to_unit(o.w); }
+}
+
+template <bool ANY, bool BRUTE, bool COUNT>
+int launch_isect(const DevScene &sc, int bvh_depth, const float *o, const float *d, size_t n, int32_t *id, float *t, unsigned long long *cnt, cudaStream_t st) {
+    const size_t sb = (size_t) Q_THREADS * (size_t) (bvh_depth + 2) * sizeof(uint2);
+    static size_t configured = 0;
+    if (sb > 48 * 1024 && sb > configured) {
+        B2_CUDA(cudaFuncSetAttribute(k_intersect<ANY, BRUTE, COUNT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb));
+    }
+    // grid: enough blocks to fill 148 SMs x resident CTAs, grid-stride beyond that
+    const size_t want = (n + Q_THREADS - 1) / Q_THREADS;
+    const unsigned grid = (unsigned) std::min<size_t>(want, (size_t) 148 * 64);
+    k_intersect<ANY, BRUTE, COUNT><<<grid, Q_THREADS, sb, st>>>(sc, o, d, n, id, t, cnt);
+    B2_CUDA(cudaGetLastError());
+    return B2_OK;
+}
+
+}  // namespace
+
+int b2_intersect_launch(const DevScene &sc, int bvh_depth, const float *d_org, const float *d_dir, size_t n, int mode,
+                        int32_t *d_prim_id, float *d_t, unsigned long long *d_counters, cudaStream_t st) {
+    if (n == 0) return B2_OK;
+    const bool any = mode & B2_ANY, brute = mode & B2_BRUTE_FORCE, count = (mode & B2_COUNT_VISITS) && !brute;
+    if (!any) {
+        if (brute) return launch_isect<false, true, false>(sc, bvh_depth, d_org, d_dir, n, d_prim_id, d_t, d_counters, st);
+        if (count) return launch_isect<false, false, true>(sc, bvh_depth, d_org, d_dir, n, d_prim_id, d_t, d_counters, st);
+        return launch_isect<false, false, false>(sc, bvh_depth, d_org, d_dir, n, d_prim_id, d_t, d_counters, st);
+    }
+    if (brute) return launch_isect<true, true, false>(sc, bvh_depth, d_org, d_dir, n, d_prim_id, d_t, d_counters, st);
+    if (count) return launch_isect<true, false, true>(sc, bvh_depth, d_org, d_dir, n, d_prim_id, d_t, d_counters, st);
+    return launch_isect<true, false, false>(sc, bvh_depth, d_org, d_dir, n, d_prim_id, d_t, d_counters, st);
+}
+
+// ---- table entry points: host arrays in, host arrays out (device kernels in between) ----
+namespace {
+struct Up {          // upload helper
+    DevBuf<unsigned char> b;
+    template <class T> int put(const T *h, size_t count, T **d) {
+        B2_TRY(b.alloc(std::max<size_t>(count, 1) * sizeof(T)));
+        if (count) B2_CUDA(cudaMemcpy(b.p, h, count * sizeof(T), cudaMemcpyHostToDevice));
+        *d = (T *) b.p;
+        return B2_OK;
+    }
+    template <class T> int make(size_t count, T **d) { B2_TRY(b.alloc(std::max<size_t>(count, 1) * sizeof(T))); *d = (T *) b.p; return B2_OK; }
+};
+template <class T> int down(T *h, const T *d, size_t count) { if (count) B2_CUDA(cudaMemcpy(h, d, count * sizeof(T), cudaMemcpyDeviceToHost)); return B2_OK; }
+}  // namespace
+
+int b2_tables_bsdf_evaluate(size_t n, const float *mtl6, const float *wo, const float *wi, const float *N, float *out3) {
+    Up a, b, c, d, o; float *dm, *dwo, *dwi, *dn, *dout;
+    B2_TRY(a.put(mtl6, 6 * n, &dm)); B2_TRY(b.put(wo, 3 * n, &dwo)); B2_TRY(c.put(wi, 3 * n, &dwi)); B2_TRY(d.put(N, 3 * n, &dn)); B2_TRY(o.make(3 * n, &dout));
+    if (n) k_bsdf_evaluate<<<blocks_for(n, 128), 128>>>(n, dm, dwo, dwi, dn, dout);
+    B2_CUDA(cudaGetLastError()); B2_CUDA(cudaDeviceSynchronize());
+    return down(out3, dout, 3 * n);
+}
+int b2_tables_bsdf_pdf(size_t n, const float *mtl6, const float *wo, const float *wi, const float *N, float *out) {
+    Up a, b, c, d, o; float *dm, *dwo, *dwi, *dn, *dout;
+    B2_TRY(a.put(mtl6, 6 * n, &dm)); B2_TRY(b.put(wo, 3 * n, &dwo)); B2_TRY(c.put(wi, 3 * n, &dwi)); B2_TRY(d.put(N, 3 * n, &dn)); B2_TRY(o.make(n, &dout));
+    if (n) k_bsdf_pdf<<<blocks_for(n, 128), 128>>>(n, dm, dwo, dwi, dn, dout);
+    B2_CUDA(cudaGetLastError()); B2_CUDA(cudaDeviceSynchronize());
+    return down(out, dout, n);
+}
+int b2_tables_bsdf_sample(size_t n, const float *mtl6, const float *wo, const float *N, const float *u3, const float *cur_eta,
+                          float *wi_out, float *f_out, float *pdf_out, int32_t *delta_out, float *eta_out) {
+    Up a, b, c, d, e, o1, o2, o3, o4, o5; float *dm, *dwo, *dn, *du, *de, *dwi, *df, *dp, *dne; int32_t *dd;
+    B2_TRY(a.put(mtl6, 6 * n, &dm)); B2_TRY(b.put(wo, 3 * n, &dwo)); B2_TRY(c.put(N, 3 * n, &dn)); B2_TRY(d.put(u3, 3 * n, &du)); B2_TRY(e.put(cur_eta, n, &de));
+    B2_TRY(o1.make(3 * n, &dwi)); B2_TRY(o2.make(3 * n, &df)); B2_TRY(o3.make(n, &dp)); B2_TRY(o4.make(n, &dd)); B2_TRY(o5.make(n, &dne));
+    if (n) k_bsdf_sample<<<blocks_for(n, 128), 128>>>(n, dm, dwo, dn, du, de, dwi, df, dp, dd, dne);
+    B2_CUDA(cudaGetLastError()); B2_CUDA(cudaDeviceSynchronize());
+    B2_TRY(down(wi_out, dwi, 3 * n)); B2_TRY(down(f_out, df, 3 * n)); B2_TRY(down(pdf_out, dp, n)); B2_TRY(down(delta_out, dd, n));
+    return down(eta_out, dne, n);
+}
+int b2_tables_mis_weight(size_t n, const float *eye17, const int32_t *n_eye, const int32_t *s_idx, const float *lit20, const int32_t *n_lit,
+                         const int32_t *t_idx, const float *d_vec, const float *dist2, const float *cam_pos, int32_t max_verts, float *out) {
+    if (max_verts <= 0) { b2_set_error("max_verts must be > 0"); return B2_ERR_INVALID; }
+    Up a, b, c, d, e, f, g, h, i, o; float *de, *dl, *dd, *d2, *dc, *dout; int32_t *dne, *ds, *dnl, *dt;
+    B2_TRY(a.put(eye17, (size_t) 17 * max_verts * n, &de)); B2_TRY(b.put(n_eye, n, &dne)); B2_TRY(c.put(s_idx, n, &ds));
+    B2_TRY(d.put(lit20, (size_t) 20 * max_verts * n, &dl)); B2_TRY(e.put(n_lit, n, &dnl)); B2_TRY(f.put(t_idx, n, &dt));
+    B2_TRY(g.put(d_vec, 3 * n, &dd)); B2_TRY(h.put(dist2, n, &d2)); B2_TRY(i.put(cam_pos, 3 * n, &dc)); B2_TRY(o.make(n, &dout));
+    if (n) k_mis_weight<<<blocks_for(n, 128), 128>>>(n, de, dne, ds, dl, dnl, dt, dd, d2, dc, max_verts, dout);
+    B2_CUDA(cudaGetLastError()); B2_CUDA(cudaDeviceSynchronize());
+    return down(out, dout, n);
+}
+int b2_tables_philox(size_t n, const uint32_t *ctr4, const uint32_t *key2, uint32_t *out4, float *unit_out4) {
+    Up a, b, o, u; uint32_t *dc, *dk, *dout; float *du;
+    B2_TRY(a.put(ctr4, 4 * n, &dc)); B2_TRY(b.put(key2, 2 * n, &dk)); B2_TRY(o.make(4 * n, &dout)); B2_TRY(u.make(4 * n, &du));
+    if (n) k_philox<<<blocks_for(n, 128), 128>>>(n, dc, dk, dout, du);
+    B2_CUDA(cudaGetLastError()); B2_CUDA(cudaDeviceSynchronize());
+    B2_TRY(down(out4, dout, 4 * n));
+    if (unit_out4) B2_TRY(down(unit_out4, du, 4 * n));
+    return B2_OK;
+}

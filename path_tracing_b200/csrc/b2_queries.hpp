@@ -1,0 +1,18 @@
+// b2_queries.hpp -- host-side declarations of the batch query / table kernels (b2_queries.cu).
+#pragma once
+#include <algorithm>
+#include "b2_cuda_util.hpp"
+#include "b2_scene.cuh"
+
+// mode: B2_CLOSEST / B2_ANY, optionally | B2_BRUTE_FORCE, | B2_COUNT_VISITS (d_counters: rays, nodes, tris).
+// All pointers are device pointers; asynchronous on `st`.
+int b2_intersect_launch(const DevScene &sc, int bvh_depth, const float *d_org, const float *d_dir, size_t n, int mode,
+                        int32_t *d_prim_id, float *d_t, unsigned long long *d_counters, cudaStream_t st);
+
+int b2_tables_bsdf_evaluate(size_t n, const float *mtl6, const float *wo, const float *wi, const float *N, float *out3);
+int b2_tables_bsdf_pdf(size_t n, const float *mtl6, const float *wo, const float *wi, const float *N, float *out);
+int b2_tables_bsdf_sample(size_t n, const float *mtl6, const float *wo, const float *N, const float *u3, const float *cur_eta,
+                          float *wi_out, float *f_out, float *pdf_out, int32_t *delta_out, float *eta_out);
+int b2_tables_mis_weight(size_t n, const float *eye17, const int32_t *n_eye, const int32_t *s_idx, const float *lit20, const int32_t *n_lit,
+                         const int32_t *t_idx, const float *d_vec, const float *dist2, const float *cam_pos, int32_t max_verts, float *out);
+int b2_tables_philox(size_t n, const uint32_t *ctr4, const uint32_t *key2, uint32_t *out4, float *unit_out4);

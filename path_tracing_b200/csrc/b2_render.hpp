@@ -1,0 +1,26 @@
+// b2_render.hpp -- host-side declarations of the wavefront renderer (b2_render.cu) used by the C ABI (b2_api.cu).
+#pragma once
+#include "b2_cuda_util.hpp"
+#include "b2_bdpt.cuh"
+
+// Device buffers of the wavefront state; owned by a B2Scene and kept across calls (grown on demand).
+struct RenderWorkspace {
+    DevBuf<float4> ray_o, ray_d, thr, last_pos, last_n, acc, hist_pe, cv, pool;
+    DevBuf<float2> hist_pdf;
+    DevBuf<uint32_t> pix, sidx, pstate;
+    DevBuf<int2> hit;
+    DevBuf<int> live_a, live_b, pool_active, ints;   // ints[0] = n_pool_active, ints[1] = n_live_next
+    DevBuf<float> film;
+    DevBuf<unsigned long long> counters;
+    int *h_ints = nullptr;                           // pinned read-back slot
+    int cap_paths = 0, cap_depth = 0, cap_pool = 0;
+    unsigned long long closest_rays_host = 0;
+    int ensure(int max_paths, int eye_depth, int n_pool, size_t film_floats);
+    void release();
+    ~RenderWorkspace() { release(); }
+};
+
+// d_film_out: W*H*3 floats on the device.  Blocks until `st` has drained the render (the counters are read back).
+int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws, const B2Camera &cam, const B2RenderParams &p,
+                          float *d_film_out, cudaStream_t st, B2Stats *stats);
+int b2_light_pool_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws, const B2RenderParams &p, float *pool20_host, cudaStream_t st);

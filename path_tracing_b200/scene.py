@@ -91,3 +91,58 @@ class SceneData:
         c = self.camera
         cam = np.concatenate([c["eye"], c["look_at"], c["view_up"], [c["fov"]]]).astype(np.float32)
         return dict(kind=kind, group=group, geom=geom, mtl=mtl, lights=lights, cam=cam, W=self.width, H=self.height)
+
+    # -- text form of the reference grammar (main_cli.cpp:99-141), canonical layout: one directive per line --
+    def write_text(self, path):
+        f = self.to_flat()
+        g9 = lambda v: " ".join(np.format_float_positional(np.float32(x), unique=True, trim="-") if abs(x) < 1e15 and (abs(x) >= 1e-4 or x == 0)
+                               else repr(float(np.float32(x))) for x in v)
+        lines = []
+        c = f["cam"]
+        lines += [f"E {g9(c[0:3])}", f"V {g9(c[3:9])}", f"F {g9(c[9:10])}", f"R {self.width} {self.height}"]
+        for L in f["lights"]:
+            lines.append(f"L {g9(L[0:3])} {g9(L[3:6])} {g9(L[6:9])} {g9([_degrees_for(L[9])])} {int(L[10])} {g9(L[11:12])}")
+        cur_g, cur_m = 0, None
+        for i in range(len(f["kind"])):
+            if f["group"][i] != cur_g:
+                cur_g = int(f["group"][i]); lines.append(f"G {cur_g}")
+            m = f["mtl"][i].tobytes()
+            if m != cur_m:
+                cur_m = m; lines.append(f"M {g9(f['mtl'][i])}")
+            lines.append(f"S {g9(f['geom'][i, 0:4])}" if f["kind"][i] == 0 else f"T {g9(f['geom'][i])}")
+        with open(path, "w") as fh:
+            fh.write("\n".join(lines) + "\n")
+
+
+def _degrees_for(rad):
+    """A float32 number of degrees whose glm::radians() is exactly `rad` (the parser multiplies by pi/180 in fp32)."""
+    k = np.float32(0.01745329251994329576923690768489)
+    rad = np.float32(rad)
+    d0 = np.float32(np.float64(rad) / np.float64(k))
+    cands = [np.float32(round(float(d0)))] + [np.nextafter(d0, np.float32(s * np.inf), dtype=np.float32) for s in (1, -1)] + [d0]
+    c = d0
+    for _ in range(8):
+        cands.append(c); c = np.nextafter(c, np.float32(np.inf), dtype=np.float32)
+    c = d0
+    for _ in range(8):
+        cands.append(c); c = np.nextafter(c, np.float32(-np.inf), dtype=np.float32)
+    for c in cands:
+        if np.float32(c * k) == rad:
+            return float(c)
+    return float(d0)
+
+
+_DATA = None
+
+
+def reference_scene(name):
+    """The reference's own scene files (input.txt -> "cornell", mis_test.txt -> "mis"), stored parsed in
+    data/reference_scenes.npz by tests/golden/make_golden.py."""
+    global _DATA
+    import os
+    if _DATA is None:
+        _DATA = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "data", "reference_scenes.npz"))
+    d = _DATA
+    W, H = (int(x) for x in d[f"{name}_res"])
+    return SceneData.from_flat(d[f"{name}_kind"], d[f"{name}_group"], d[f"{name}_geom"], d[f"{name}_mtl"], d[f"{name}_lights"],
+                               d[f"{name}_cam"], W, H)

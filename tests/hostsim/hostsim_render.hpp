@@ -42,21 +42,22 @@ inline void hs_render(const DevScene &sc, const B2Camera &cam, const B2RenderPar
         hs_build_pool(c, pool, active, out.counters);
         const int max_paths = p.max_batch_paths > 0 ? p.max_batch_paths : (1 << 16);
         c.max_paths = max_paths;
-        std::vector<float4> ray_o(max_paths), ray_d(max_paths), thr(max_paths), last_pos(max_paths), last_n(max_paths), hist_pe((size_t) p.eye_depth * max_paths), cv((size_t) B2_CV_F4 * max_paths);
+        std::vector<float4> ray_o(max_paths), ray_d(max_paths), thr(max_paths), last_pos(max_paths), last_n(max_paths), acc(max_paths), hist_pe((size_t) p.eye_depth * max_paths), cv((size_t) B2_CV_F4 * max_paths);
         std::vector<float2> hist_pdf((size_t) p.eye_depth * max_paths);
         std::vector<uint32_t> pix(max_paths), sidx(max_paths), pstate(max_paths);
         std::vector<int2> hit(max_paths);
         std::vector<int> live(max_paths), live_next(max_paths);
-        c.ray_o = ray_o.data(); c.ray_d = ray_d.data(); c.thr = thr.data(); c.last_pos = last_pos.data(); c.last_n = last_n.data();
+        c.ray_o = ray_o.data(); c.ray_d = ray_d.data(); c.thr = thr.data(); c.last_pos = last_pos.data(); c.last_n = last_n.data(); c.acc = acc.data();
         c.hist_pe = hist_pe.data(); c.hist_pdf = hist_pdf.data(); c.cv = cv.data(); c.pix = pix.data(); c.sidx = sidx.data(); c.pstate = pstate.data();
         c.hit = hit.data(); c.live = live.data(); c.live_next = live_next.data();
         uint2 stack[B2_STACK_CAP]; TravCounters tc{ 0, 0 };
         const long long total = (long long) npix * n_my;
         for (long long w0 = 0; w0 < total; w0 += max_paths) {
             int n_live = (int) std::min<long long>(max_paths, total - w0);
+            const int n_batch = n_live;
             for (int i = 0; i < n_live; ++i) eye_gen_body(c, i, w0);
             out.counters[B2_CNT_EYE_SAMPLES] += n_live;
-            while (n_live > 0) {
+            while (n_live > 0 && p.eye_depth > 0) {
                 for (int q = 0; q < n_live; ++q) {
                     const int path = c.live[q];
                     HitRec h = closest_hit_bvh<true>(c.sc, mk3(c.ray_o[path]), mk3(c.ray_d[path]), stack, 1, &tc);
@@ -64,28 +65,31 @@ inline void hs_render(const DevScene &sc, const B2Camera &cam, const B2RenderPar
                 }
                 out.counters[B2_CNT_CLOSEST] += n_live;
                 int n_next = 0; uint32_t emit = 0, cap = 0;
-                for (int q = 0; q < n_live; ++q) if (shade_body(c, q, emit, cap)) live_next[n_next++] = c.live[q];
+                for (int q = 0; q < n_live; ++q) if (shade_body(c, q, emit, cap)) c.live_next[n_next++] = c.live[q];
                 out.counters[B2_CNT_PATH_SAMPLES] += emit; out.counters[B2_CNT_DELTA_CAP] += cap;
                 for (int q = 0; q < n_live; ++q) {
                     if (f2u(c.cv[B2_CV_F4 * q].w) == B2_CV_NONE) continue;
                     const EyeVtx ev = load_cv(c.cv, q);
-                    const uint32_t pixel = c.pix[ev.path];
+                    float3 sum = mk3(0, 0, 0);
+                    uint32_t nsh = 0, npa = 0;
                     for (int a : active) {
-                        ShadowEntry e;
-                        if (!connect_pair(c, ev, pixel, a, e)) continue;
-                        float4 sq[B2_SQ_F4]; store_sq(sq, 0, e);
-                        c.sq = sq;
-                        out.counters[B2_CNT_SHADOW]++;
-                        if (shadow_body<true>(c, 0, stack, 1, &tc)) out.counters[B2_CNT_PATH_SAMPLES]++;
+                        out.counters[B2_CNT_PAIRS]++;
+                        if (!connect_pretest(c, ev.pos, ev.n, a)) continue;
+                        sum = sum + connect_finish<true>(c, ev, a, stack, 1, &tc, nsh, npa);
                     }
+                    out.counters[B2_CNT_SHADOW] += nsh; out.counters[B2_CNT_PATH_SAMPLES] += npa;
+                    c.acc[ev.path] = mk4(mk3(c.acc[ev.path]) + sum, 0.0f);
                 }
-                live.swap(live_next); c.live = live.data(); c.live_next = live_next.data();
+                std::swap(c.live, c.live_next);
                 n_live = n_next;
+            }
+            for (int i = 0; i < n_batch; ++i) {
+                const float3 v = mk3(c.acc[i]);
+                if (!valid_color(v)) continue;
+                film[3 * (size_t) c.pix[i]] += v.x; film[3 * (size_t) c.pix[i] + 1] += v.y; film[3 * (size_t) c.pix[i] + 2] += v.z;
             }
         }
         out.counters[B2_CNT_NODES] += tc.nodes; out.counters[B2_CNT_TRIS] += tc.tris;
     }
-    const float inv = p.film_mode == B2_FILM_SUM ? 1.0f : 1.0f / (float) p.spp;
     for (size_t i = 0; i < film.size(); ++i) film_out[i] = p.film_mode == B2_FILM_SUM ? film[i] : film[i] / (float) p.spp;
-    (void) inv;
 }

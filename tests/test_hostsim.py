@@ -1,0 +1,89 @@
+"""Device headers (BVH build, traversal, BSDF, RNG, wavefront BDPT stage bodies) compiled for the HOST by tests/hostsim
+and checked against the reference golden vectors and the oracle.  This is how the kernel logic is validated on the
+CPU-only build box; the same bodies run inside the CUDA kernels (tests/test_gpu_parity.py checks those on the GPU)."""
+import os
+import numpy as np
+import pytest
+from hostsim_py import HostSim
+from oracle import oracle_py as O
+from path_tracing_b200.scene import SceneData, reference_scene
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def desc(sd):
+    f = sd.to_flat()
+    return O.SceneDesc(f["kind"], f["group"], f["geom"], f["mtl"], f["lights"], f["cam"], f["W"], f["H"])
+
+
+@pytest.mark.parametrize("name", ["cornell", "mis"])
+def test_traversal_is_bit_exact_against_reference_golden(name):
+    g = np.load(os.path.join(GOLD, f"hits_{name}.npz"))
+    hs = HostSim(reference_scene(name))
+    for mode in (0, 16):      # wide BVH, exhaustive
+        ids, t, _ = hs.intersect(g["org"], g["dir"], mode)
+        assert np.array_equal(ids, g["id"])
+        assert np.array_equal(t.view(np.uint32), g["t"].view(np.uint32))
+    for mode in (1, 17):
+        vis, _, _ = hs.intersect(g["p1"], g["p2"], mode)
+        assert np.array_equal(vis, g["vis"].astype(np.int32))
+    hs.close()
+
+
+def random_soup(n, seed, lights=2):
+    rng = np.random.default_rng(seed)
+    c = rng.uniform(-1, 1, (n, 1, 3)); e = rng.normal(size=(n, 3, 3)) * rng.uniform(0.01, 0.2, (n, 1, 1))
+    geom = (c + e).reshape(n, 9).astype(np.float32)
+    kind = np.ones(n, np.int32); group = rng.integers(0, 3, n).astype(np.int32)
+    mtl = np.tile(np.array([0.7, 0.7, 0.7, 0.5, 0.0, 0.0], np.float32), (n, 1))
+    mtl[rng.uniform(size=n) < 0.2, 5] = 1.5     # transparent to shadow rays
+    L = np.zeros((lights, 12), np.float32)
+    L[:, 0:3] = rng.uniform(-1, 1, (lights, 3)); L[:, 3:6] = [0, -1, 0]; L[:, 6:9] = 1; L[:, 9] = 1.0; L[:, 11] = 0.05
+    cam = np.array([0, 0, -3, 0, 0, 0, 0, 1, 0, 50], np.float32)
+    return SceneData.from_flat(kind, group, geom, mtl, L, cam, 32, 32)
+
+
+@pytest.mark.parametrize("n,max_leaf", [(1, 3), (2, 1), (3, 3), (500, 3), (4000, 2)])
+def test_bvh_equals_brute_force_and_oracle_on_triangle_soup(n, max_leaf):
+    sd = random_soup(n, 100 + n)
+    hs = HostSim(sd, max_leaf=max_leaf)
+    rng = np.random.default_rng(n)
+    m = 3000
+    org = rng.uniform(-1.2, 1.2, (m, 3)).astype(np.float32)
+    dr = rng.normal(size=(m, 3)).astype(np.float32); dr /= np.linalg.norm(dr, axis=1, keepdims=True)
+    dr[:50, 1:] = 0; dr[:50, 0] = 1                     # axis-aligned directions (zero components)
+    a_id, a_t, cnt = hs.intersect(org, dr, 0)
+    b_id, b_t, _ = hs.intersect(org, dr, 16)
+    assert np.array_equal(a_id, b_id) and np.array_equal(a_t.view(np.uint32), b_t.view(np.uint32))
+    P = O.Port(); h = P.scene(desc(sd))
+    r = P.closest_hit(h, org, dr)
+    assert np.array_equal(a_id, r["id"]) and np.array_equal(a_t.view(np.uint32), r["t"].view(np.uint32))
+    p2 = rng.uniform(-1.2, 1.2, (m, 3)).astype(np.float32)
+    v_bvh, _, _ = hs.intersect(org, p2, 1)
+    v_bf, _, _ = hs.intersect(org, p2, 17)
+    assert np.array_equal(v_bvh, v_bf) and np.array_equal(v_bvh, P.visibility(h, org, p2).astype(np.int32))
+    if n >= 500:
+        assert cnt[1] / m < 0.25 * n                    # the tree actually culls
+    P.destroy(h); hs.close()
+
+
+@pytest.mark.parametrize("name,depth", [("cornell", 6), ("mis", 8)])
+def test_wavefront_bodies_reproduce_the_oracle_render(name, depth):
+    sd = reference_scene(name)
+    hs = HostSim(sd)
+    P = O.Port(); d = desc(sd); h = P.scene(d)
+    opts = P.opts(rng_mode=P.PHILOX, seed=5, max_delta=256)
+    pool_o = P.light_pool(h, d.n_lights, depth, 8, opts)
+    pool_h = hs.light_pool(8, depth, seed=5)
+    assert np.allclose(pool_h, pool_o, rtol=1e-5, atol=1e-7)
+    W = H = 24
+    fo, st = P.render(h, d.cam, depth, depth, W, H, 3, 8, opts, want_stats=True)
+    fh, cnt = hs.render(W, H, 3, 8, depth, depth, seed=5, max_batch_paths=500)    # several batches
+    assert cnt["eye_samples"] == st.eye_samples == W * H * 3
+    assert cnt["closest_rays"] == st.closest_rays and cnt["shadow_rays"] == st.shadow_rays and cnt["path_samples"] == st.path_samples
+    assert np.allclose(fh, fo, rtol=1e-4, atol=1e-6)
+    # sample sharding: two shards (s = 0,2 and s = 1) summed == the whole film
+    a, _ = hs.render(W, H, 3, 8, depth, depth, seed=5, sample_offset=0, sample_stride=2, film_mode=1)
+    b, _ = hs.render(W, H, 3, 8, depth, depth, seed=5, sample_offset=1, sample_stride=2, film_mode=1)
+    assert np.allclose((a + b) / 3.0, fo, rtol=1e-4, atol=1e-6)
+    P.destroy(h); hs.close()
