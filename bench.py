@@ -1,0 +1,279 @@
+#!/usr/bin/env python
+"""bench.py -- BDPT throughput of the B200 path (and, with --impl reference, of the reference's own CPU code).
+
+Workload (BASELINE.json configs[1], "C2"): the reference's mis_test.txt scene, 1024 x 1024, 64 spp per GPU, spl 8,
+eye / light depth 8.  A "step" is one complete render of that configuration.  With N GPUs every rank renders its
+own 64 samples per pixel of a 64*N-spp job (sample indices s = rank (mod N), identical Philox streams as a 1-GPU
+run of the same job) and the raw-sum films are reduced to rank 0 with one NCCL reduce ("weak" scaling).
+
+  value      M eye samples / s, scene + BVH resident in HBM, film left on the device (CUDA events)
+  e2e        the same through the public call with HOST buffers: scene upload + BVH build + render + film read-back
+  roofline   dominant kernel of the step, algorithmic bytes / CUDA-event time vs the measured HBM copy bandwidth
+  cpu_baseline  oracle/_ref (the reference's cpu_bdpt.cpp, unmodified) on the host cores, bounded sample
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+import numpy as np  # noqa: E402
+
+WORKLOAD = dict(scene="mis", width=1024, height=1024, spp=64, spl=8, eye_depth=8, light_depth=8, seed=1)
+CPU_SAMPLE = dict(width=512, height=512, spp=16)      # bounded sample of the same workload for the CPU arm
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d.get("hbm_gbs", 6650.0)), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, gpu):
+        self.gpu, self.rows, self.p = gpu, [], None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True); self.t.start()
+        except OSError:
+            self.p = None
+
+    def _read(self):
+        for line in self.p.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def scene_bytes(sd):
+    return int(sd.tris.nbytes + sd.spheres.nbytes + sd.materials.nbytes + sd.lights.nbytes + sd.camera.nbytes)
+
+
+def cpu_arm(steps, warmup, sample=CPU_SAMPLE):
+    """The reference's own CPU implementation (oracle/_ref = unmodified cpu_bdpt.cpp; else the C port) on all host
+    cores, on a bounded sample of the workload (same scene, spl, depths; smaller film).  Returns the JSON fields."""
+    from oracle import oracle_py as O
+    from path_tracing_b200.scene import reference_scene
+    w = dict(WORKLOAD); w.update(sample)
+    sd = reference_scene(w["scene"]); f = sd.to_flat()
+    d = O.SceneDesc(f["kind"], f["group"], f["geom"], f["mtl"], f["lights"], f["cam"], f["W"], f["H"])
+    cores = os.cpu_count() or 1
+    n_samples = w["width"] * w["height"] * w["spp"]
+    if O.have_ref():
+        kind, lib = "reference", O.Ref()
+        h = lib.scene(d)
+        cores = lib.max_threads()
+        devnull = os.open(os.devnull, os.O_WRONLY); saved = os.dup(1)
+
+        def run():
+            sys.stdout.flush(); os.dup2(devnull, 1)       # the reference prints per-thread timings to stdout
+            try:
+                t0 = time.perf_counter()
+                lib.render(h, d.cam, w["eye_depth"], w["light_depth"], w["width"], w["height"], w["spp"], w["spl"])
+                return time.perf_counter() - t0
+            finally:
+                os.dup2(saved, 1)
+    else:
+        kind, lib = "port", O.Port()
+        h = lib.scene(d)
+
+        def run():
+            t0 = time.perf_counter()
+            lib.render(h, d.cam, w["eye_depth"], w["light_depth"], w["width"], w["height"], w["spp"], w["spl"], lib.opts(rng_mode=lib.MT19937))
+            return time.perf_counter() - t0
+    for _ in range(warmup):
+        run()
+    ts = [run() for _ in range(max(steps, 1))]
+    sec = float(np.mean(ts))
+    val = n_samples / sec / 1e6
+    return {"value": val, "unit": "Msamples/s", "cores": int(cores), "kind": kind, "ms_per_step": sec * 1e3,
+            "sample": f"{w['scene']} scene {w['width']}x{w['height']}, {w['spp']} spp, spl {w['spl']}, depth {w['eye_depth']}/{w['light_depth']} "
+                      f"({n_samples / 1e6:.2f} M eye samples per step; full workload is {WORKLOAD['width']}x{WORKLOAD['height']} x {WORKLOAD['spp']} spp)"}
+
+
+def gpu_arm(args):
+    import torch
+    import torch.distributed as dist
+    from path_tracing_b200 import api
+    from path_tracing_b200.scene import reference_scene
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    torch.cuda.set_stream(torch.cuda.Stream(device=dev))      # a real (non-default) stream: the library launches on it, the events time it
+    w = dict(WORKLOAD)
+    for k in ("width", "height", "spp", "spl", "eye_depth", "light_depth"):
+        if getattr(args, k, None):
+            w[k] = getattr(args, k)
+    if args.scene:
+        w["scene"] = args.scene
+    W, H = w["width"], w["height"]
+    spp_total = w["spp"] * world                       # weak scaling: every GPU renders w["spp"] samples per pixel
+    sd = reference_scene(w["scene"])
+    sc = api.Scene(sd, device=local)
+    film = torch.zeros((H, W, 3), dtype=torch.float32, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+    kw = dict(width=W, height=H, spp=spp_total, spl=w["spl"], eye_depth=w["eye_depth"], light_depth=w["light_depth"], seed=w["seed"],
+              sample_offset=rank, sample_stride=world, film_mode=api.FILM_SUM if world > 1 else api.FILM_MEAN)
+
+    def step(profile=False, count=False):
+        _, st = sc.render_bdpt(device_ptr=film.data_ptr(), stream=stream, profile_stages=profile, count_traversal=count, **kw)
+        if world > 1:
+            dist.reduce(film, dst=0, op=dist.ReduceOp.SUM)           # one NCCL reduce of the raw-sum films over NVLink
+            if rank == 0:
+                film.mul_(1.0 / spp_total)
+        return st
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        st = step()
+    # L2: every step writes > 1 GB of path state (max_batch_paths x ~400 B) between reuses of any line: no explicit flush needed
+    sampler = ClockSampler(local); sampler.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    launches = 0
+    for _ in range(args.steps):
+        st = step()
+        launches += st["n_launches"]
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1) / args.steps
+    clocks = sampler.stop()
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    n_samples = W * H * w["spp"] * world
+    value = n_samples / (ms * 1e-3) / 1e6
+
+    # ---- untimed diagnostics on rank 0: stage shares, traversal visit counts, e2e through host buffers ----
+    out = None
+    if rank == 0:
+        kw1 = dict(kw); kw1.update(spp=w["spp"], sample_offset=0, sample_stride=1, film_mode=api.FILM_MEAN)
+        _, sp = sc.render_bdpt(device_ptr=film.data_ptr(), stream=stream, profile_stages=True, **kw1)
+        _, sn = sc.render_bdpt(device_ptr=film.data_ptr(), stream=stream, count_traversal=True, **kw1)
+        stages = {k: sp[k] for k in ("ms_light_pool", "ms_gen", "ms_closest", "ms_shade", "ms_connect", "ms_flush")}
+        rays = sp["closest_rays"] + sp["shadow_rays"]
+        # dominant kernel and its algorithmic bytes
+        dom = max(("ms_gen", "ms_closest", "ms_shade", "ms_connect"), key=lambda k: stages[k])
+        n_closest = sp["closest_rays"]
+        per_node, per_tri = 80, 48
+        alg = {
+            "ms_gen": sp["eye_samples"] * (16 * 6 + 12 + 4),                                  # 6 float4 + pix/sidx/pstate + live
+            "ms_closest": n_closest * (4 + 32 + 8) + sn["nodes_visited"] * per_node + sn["tris_tested"] * per_tri,   # upper bound: shadow visits included
+            "ms_shade": n_closest * (4 + 8 + 32 + 16 + 32 + 12 + 80 + 4),
+            "ms_connect": n_closest * (32 + 16) + sp["pairs_tested"] * 32 + sp["shadow_rays"] * (80 + 80),
+        }[dom]
+        hbm, hbm_src = peaks()
+        # e2e: public host-buffer call; scene upload + BVH build + render + film read-back inside the timed region
+        host_film = np.zeros((H, W, 3), np.float32)
+        e2e_ms = []
+        for i in range(max(2, min(args.steps, 5)) + 1):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            s2 = api.Scene(sd, device=local)
+            s2.render_bdpt(out=host_film, **kw1)
+            s2.close()
+            dtm = (time.perf_counter() - t0) * 1e3
+            if i > 0:
+                e2e_ms.append(dtm)
+        e2e = float(np.mean(e2e_ms))
+        dom_ms = stages[dom]
+        out = {
+            "metric": "bdpt_eye_msamples_per_s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"C2: reference mis_test.txt scene, {W}x{H}, {w['spp']} spp per GPU ({spp_total} spp job), spl {w['spl']}, "
+                                   f"eye/light depth {w['eye_depth']}/{w['light_depth']}, BDPT, Philox seed {w['seed']}",
+                       "l2": "inputs larger than L2: each step streams > 1 GB of path state", "parallelism": f"spp-sharded x{world}, NCCL film reduce"},
+            "mrays_per_s": rays * world / (ms * 1e-3) / 1e6, "mpath_samples_per_s": sp["path_samples"] * world / (ms * 1e-3) / 1e6,
+            "per_sample": {"closest_rays": sp["closest_rays"] / sp["eye_samples"], "shadow_rays": sp["shadow_rays"] / sp["eye_samples"],
+                           "pairs_tested": sp["pairs_tested"] / sp["eye_samples"], "nodes_per_ray": sn["nodes_visited"] / max(rays, 1),
+                           "tris_per_ray": sn["tris_tested"] / max(rays, 1)},
+            "stages_ms": stages, "stage_total_ms": sp["ms_total"],
+            "roofline": {"bound": "hbm", "kernel": {"ms_gen": "k_eye_gen", "ms_closest": "k_closest", "ms_shade": "k_shade", "ms_connect": "k_connect"}[dom],
+                         "achieved": alg / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else None, "peak": hbm, "unit": "GB/s",
+                         "frac": (alg / (dom_ms * 1e-3) / 1e9) / hbm if dom_ms > 0 else None, "traffic": None, "peak_source": hbm_src,
+                         "algorithmic_bytes_per_step": alg, "kernel_ms_per_step": dom_ms},
+            "e2e": {"value": W * H * w["spp"] / (e2e * 1e-3) / 1e6, "unit": "Msamples/s", "ms_per_step": e2e,
+                    "h2d_bytes_per_step": scene_bytes(sd), "d2h_bytes_per_step": int(host_film.nbytes),
+                    "note": "b2_scene_create + b2_scene_build_bvh + b2_render_bdpt(host film) per step, 1 GPU"},
+            "gpu_launches": int(launches), "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu:
+            out["cpu_baseline"] = cpu_arm(1, 0)
+    sc.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if out is not None:
+        print(json.dumps(out))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--scene", default=None)
+    ap.add_argument("--no-cpu", action="store_true")
+    for k in ("width", "height", "spp", "spl", "eye_depth", "light_depth"):
+        ap.add_argument("--" + k.replace("_", "-"), type=int, default=None, dest=k)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        if int(os.environ.get("RANK", "0")) != 0:
+            return
+        c = cpu_arm(min(args.steps, 5), min(args.warmup, 1))
+        W, H = WORKLOAD["width"], WORKLOAD["height"]
+        line = {"impl": "reference", "metric": "bdpt_eye_msamples_per_s", "value": c["value"], "unit": "Msamples/s", "n_gpus": args.gpus,
+                "steps": min(args.steps, 5), "warmup": min(args.warmup, 1), "ms_per_step": c["ms_per_step"], "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": f"C2: reference mis_test.txt scene, {W}x{H}, {WORKLOAD['spp']} spp, spl {WORKLOAD['spl']}, eye/light depth "
+                                       f"{WORKLOAD['eye_depth']}/{WORKLOAD['light_depth']}, BDPT (timed on the bounded sample in cpu_baseline.sample)"},
+                "cpu_baseline": c, "e2e": {"value": c["value"], "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line))
+        return
+    gpu_arm(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -79,7 +79,7 @@ typedef struct B2RenderParams {
     int32_t  max_delta;      /* cap on delta bounces per subpath (0 = default 256) */
     int32_t  max_batch_paths;/* eye paths in flight per wavefront batch (0 = default 2^22) */
     int32_t  count_traversal;/* !=0: use the counting traversal variant and fill node/tri visit counters */
-    int32_t  reserved;
+    int32_t  profile_stages; /* !=0: bracket every stage launch with CUDA events and fill the ms_* stage times */
 } B2RenderParams;
 
 typedef struct B2Stats {
@@ -91,8 +91,10 @@ typedef struct B2Stats {
     uint64_t nodes_visited;   /* only with count_traversal */
     uint64_t tris_tested;     /* only with count_traversal */
     uint64_t n_batches, n_waves, n_launches;
+    uint64_t pairs_tested;    /* (eye vertex, pool vertex) pairs that went through the connection pre-test */
     float    ms_total;        /* device time of the call, CUDA events */
-    float    ms_light_pool, ms_closest, ms_shade, ms_connect, ms_shadow, ms_other; /* per-stage device time (profiling runs only) */
+    float    ms_light_pool;   /* pool generation (always measured) */
+    float    ms_gen, ms_closest, ms_shade, ms_connect, ms_flush; /* per-stage device time, only with profile_stages */
 } B2Stats;
 
 /* ---- library / device ---- */

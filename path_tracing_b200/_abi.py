@@ -35,15 +35,15 @@ class RenderParams(C.Structure):
                 ("eye_depth", C.c_int32), ("light_depth", C.c_int32), ("seed", C.c_uint64),
                 ("sample_offset", C.c_int32), ("sample_stride", C.c_int32), ("film_mode", C.c_int32),
                 ("strategies", C.c_int32), ("max_delta", C.c_int32), ("max_batch_paths", C.c_int32),
-                ("count_traversal", C.c_int32), ("reserved", C.c_int32)]
+                ("count_traversal", C.c_int32), ("profile_stages", C.c_int32)]
 
 
 class Stats(C.Structure):
     _fields_ = [("eye_samples", C.c_uint64), ("closest_rays", C.c_uint64), ("shadow_rays", C.c_uint64),
                 ("path_samples", C.c_uint64), ("delta_cap_hits", C.c_uint64), ("nodes_visited", C.c_uint64),
-                ("tris_tested", C.c_uint64), ("n_batches", C.c_uint64), ("n_waves", C.c_uint64), ("n_launches", C.c_uint64),
-                ("ms_total", C.c_float), ("ms_light_pool", C.c_float), ("ms_closest", C.c_float), ("ms_shade", C.c_float),
-                ("ms_connect", C.c_float), ("ms_shadow", C.c_float), ("ms_other", C.c_float)]
+                ("tris_tested", C.c_uint64), ("n_batches", C.c_uint64), ("n_waves", C.c_uint64), ("n_launches", C.c_uint64), ("pairs_tested", C.c_uint64),
+                ("ms_total", C.c_float), ("ms_light_pool", C.c_float), ("ms_gen", C.c_float), ("ms_closest", C.c_float),
+                ("ms_shade", C.c_float), ("ms_connect", C.c_float), ("ms_flush", C.c_float)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

@@ -278,6 +278,25 @@ static void setup_ctx(RenderCtx &c, const DevScene &sc, const B2Camera &cam, con
     c.cv = ws.cv.p; c.acc = ws.acc.p; c.film = ws.film.p; c.counters = ws.counters.p;
 }
 
+// Optional per-stage device timing: one CUDA event pair per launch, summed per stage after each wave's sync.
+struct StageTimer {
+    enum { GEN, CLOSEST, SHADE, CONNECT, FLUSH, N };
+    bool on = false;
+    cudaStream_t st = nullptr;
+    std::vector<cudaEvent_t> pool;
+    struct Rec { int stage; cudaEvent_t a, b; };
+    std::vector<Rec> pending;
+    float ms[N] = { 0, 0, 0, 0, 0 };
+    cudaEvent_t get() { if (pool.empty()) { cudaEvent_t e; cudaEventCreate(&e); return e; } cudaEvent_t e = pool.back(); pool.pop_back(); return e; }
+    void begin(int stage) { if (!on) return; Rec r{ stage, get(), get() }; cudaEventRecord(r.a, st); pending.push_back(r); }
+    void end() { if (!on) return; cudaEventRecord(pending.back().b, st); }
+    void collect() {             // call after a stream synchronize
+        for (Rec &r : pending) { float t = 0.f; if (cudaEventElapsedTime(&t, r.a, r.b) == cudaSuccess) ms[r.stage] += t; pool.push_back(r.a); pool.push_back(r.b); }
+        pending.clear();
+    }
+    ~StageTimer() { for (cudaEvent_t e : pool) cudaEventDestroy(e); for (Rec &r : pending) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); } }
+};
+
 static size_t stack_bytes(int threads, int bvh_depth) { return (size_t) threads * (size_t) std::max(bvh_depth + 1, 2) * sizeof(uint2); }
 
 // Light pool generation (shared by render and b2_light_pool).  Leaves *n_pool_active in ws.ints[0].
@@ -329,6 +348,7 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
     RenderCtx c; setup_ctx(c, sc, cam, p, ws, max_paths);
     const bool count = p.count_traversal != 0;
     uint64_t n_launches = 0, n_batches = 0, n_waves = 0;
+    StageTimer tm; tm.on = p.profile_stages != 0; tm.st = st;
     cudaEvent_t ev0, ev1, ev2;
     B2_CUDA(cudaEventCreate(&ev0)); B2_CUDA(cudaEventCreate(&ev1)); B2_CUDA(cudaEventCreate(&ev2));
     B2_CUDA(cudaEventRecord(ev0, st));
@@ -345,25 +365,36 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
             int n_live = (int) std::min<long long>(max_paths, total - w0);
             const int n_batch = n_live;
             c.live = ws.live_a.p; c.live_next = ws.live_b.p;
+            tm.begin(StageTimer::GEN);
             k_eye_gen<<<blocks_for(n_live, 256), 256, 0, st>>>(c, n_live, w0);
+            tm.end();
             n_launches++; n_batches++;
             eye_samples += (unsigned long long) n_live;
             while (n_live > 0 && p.eye_depth > 0) {
                 B2_CUDA(cudaMemsetAsync(c.n_live_next, 0, sizeof(int), st));
+                tm.begin(StageTimer::CLOSEST);
                 if (count) k_closest<true><<<blocks_for(n_live, TRAV_THREADS), TRAV_THREADS, sb_t, st>>>(c, n_live);
                 else k_closest<false><<<blocks_for(n_live, TRAV_THREADS), TRAV_THREADS, sb_t, st>>>(c, n_live);
+                tm.end();
+                tm.begin(StageTimer::SHADE);
                 k_shade<<<blocks_for(n_live, SHADE_THREADS), SHADE_THREADS, 0, st>>>(c, n_live);
+                tm.end();
                 B2_CUDA(cudaMemcpyAsync(ws.h_ints, c.n_live_next, sizeof(int), cudaMemcpyDeviceToHost, st));
+                tm.begin(StageTimer::CONNECT);
                 if (count) k_connect<true><<<blocks_for(n_live, CONN_THREADS), CONN_THREADS, sb_c, st>>>(c, n_live);
                 else k_connect<false><<<blocks_for(n_live, CONN_THREADS), CONN_THREADS, sb_c, st>>>(c, n_live);
+                tm.end();
                 n_launches += 3; n_waves++;
                 B2_CUDA(cudaStreamSynchronize(st));
                 B2_CUDA(cudaGetLastError());
+                tm.collect();
                 ws.closest_rays_host += (unsigned long long) n_live;
                 n_live = ws.h_ints[0];
                 std::swap(c.live, c.live_next);
             }
+            tm.begin(StageTimer::FLUSH);
             k_flush<<<blocks_for(n_batch, 256), 256, 0, st>>>(c, n_batch);
+            tm.end();
             n_launches++;
         }
     } else {
@@ -390,7 +421,10 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
         stats->tris_tested = h_cnt[B2_CNT_TRIS];
         stats->n_batches = n_batches; stats->n_waves = n_waves; stats->n_launches = n_launches;
         stats->ms_total = ms_total; stats->ms_light_pool = ms_pool;
-        stats->ms_other = (float) h_cnt[B2_CNT_PAIRS];    // pre-tested (eye vertex, pool vertex) pairs, as a float (diagnostic)
+        stats->pairs_tested = h_cnt[B2_CNT_PAIRS];
+        tm.collect();
+        stats->ms_gen = tm.ms[StageTimer::GEN]; stats->ms_closest = tm.ms[StageTimer::CLOSEST]; stats->ms_shade = tm.ms[StageTimer::SHADE];
+        stats->ms_connect = tm.ms[StageTimer::CONNECT]; stats->ms_flush = tm.ms[StageTimer::FLUSH];
     }
     ws.closest_rays_host = 0;
     cudaEventDestroy(ev0); cudaEventDestroy(ev1); cudaEventDestroy(ev2);
