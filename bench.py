@@ -190,17 +190,22 @@ def gpu_arm(args):
         kw1 = dict(kw); kw1.update(spp=w["spp"], sample_offset=0, sample_stride=1, film_mode=api.FILM_MEAN)
         _, sp = sc.render_bdpt(device_ptr=film.data_ptr(), stream=stream, profile_stages=True, **kw1)
         _, sn = sc.render_bdpt(device_ptr=film.data_ptr(), stream=stream, count_traversal=True, **kw1)
-        stages = {k: sp[k] for k in ("ms_light_pool", "ms_gen", "ms_closest", "ms_shade", "ms_connect", "ms_flush")}
+        stages = {k: sp[k] for k in ("ms_light_pool", "ms_primary", "ms_extend", "ms_connect")}
         rays = sp["closest_rays"] + sp["shadow_rays"]
-        # dominant kernel and its algorithmic bytes
-        dom = max(("ms_gen", "ms_closest", "ms_shade", "ms_connect"), key=lambda k: stages[k])
-        n_closest = sp["closest_rays"]
+        n_primary = sp["eye_samples"]; n_later = sp["closest_rays"] - n_primary
+        n_cv = sp["pairs_tested"] / max(sn["n_pool_active"], 1) if "n_pool_active" in sn else None
+        # dominant kernel and its algorithmic bytes per step: node / triangle fetches use the measured
+        # visit counts of the counting variant (80 B per wide node, 48 B per triangle); path state and eye-vertex records
+        # are counted once per use; shadow-ray visits are attributed to k_connect, closest-hit visits to k_extend.
+        dom = max(("ms_primary", "ms_extend", "ms_connect"), key=lambda k: stages[k])
         per_node, per_tri = 80, 48
+        trav_bytes = sn["nodes_visited"] * per_node + sn["tris_tested"] * per_tri
+        closest_share = sp["closest_rays"] / max(rays, 1)
+        n_ev = sp["eye_vertices"] if "eye_vertices" in sp else 0
         alg = {
-            "ms_gen": sp["eye_samples"] * (16 * 6 + 12 + 4),                                  # 6 float4 + pix/sidx/pstate + live
-            "ms_closest": n_closest * (4 + 32 + 8) + sn["nodes_visited"] * per_node + sn["tris_tested"] * per_tri,   # upper bound: shadow visits included
-            "ms_shade": n_closest * (4 + 8 + 32 + 16 + 32 + 12 + 80 + 4),
-            "ms_connect": n_closest * (32 + 16) + sp["pairs_tested"] * 32 + sp["shadow_rays"] * (80 + 80),
+            "ms_primary": trav_bytes * closest_share * (n_primary / max(sp["closest_rays"], 1)) + n_ev * (80 + 84),
+            "ms_extend": n_later * (4 + 80) + trav_bytes * closest_share * (n_later / max(sp["closest_rays"], 1)) + n_ev * (80 + 84),
+            "ms_connect": sp["pairs_tested"] * 48 / 32 + sp["shadow_rays"] * (80 + 80) + trav_bytes * (1 - closest_share),
         }[dom]
         hbm, hbm_src = peaks()
         # e2e: public host-buffer call; scene upload + BVH build + render + film read-back inside the timed region
@@ -228,7 +233,7 @@ def gpu_arm(args):
                            "pairs_tested": sp["pairs_tested"] / sp["eye_samples"], "nodes_per_ray": sn["nodes_visited"] / max(rays, 1),
                            "tris_per_ray": sn["tris_tested"] / max(rays, 1)},
             "stages_ms": stages, "stage_total_ms": sp["ms_total"],
-            "roofline": {"bound": "hbm", "kernel": {"ms_gen": "k_eye_gen", "ms_closest": "k_closest", "ms_shade": "k_shade", "ms_connect": "k_connect"}[dom],
+            "roofline": {"bound": "hbm", "kernel": {"ms_primary": "k_extend<PRIMARY>", "ms_extend": "k_extend", "ms_connect": "k_connect"}[dom],
                          "achieved": alg / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else None, "peak": hbm, "unit": "GB/s",
                          "frac": (alg / (dom_ms * 1e-3) / 1e9) / hbm if dom_ms > 0 else None, "traffic": None, "peak_source": hbm_src,
                          "algorithmic_bytes_per_step": alg, "kernel_ms_per_step": dom_ms},

@@ -92,9 +92,11 @@ typedef struct B2Stats {
     uint64_t tris_tested;     /* only with count_traversal */
     uint64_t n_batches, n_waves, n_launches;
     uint64_t pairs_tested;    /* (eye vertex, pool vertex) pairs that went through the connection pre-test */
+    uint64_t eye_vertices;    /* eye vertices created (each is connected to the whole pool), cpu_bdpt.cpp:384 */
     float    ms_total;        /* device time of the call, CUDA events */
     float    ms_light_pool;   /* pool generation (always measured) */
-    float    ms_gen, ms_closest, ms_shade, ms_connect, ms_flush; /* per-stage device time, only with profile_stages */
+    float    ms_primary, ms_extend, ms_connect; /* per-stage device time (first-bounce extend, later extends, connect); only with profile_stages */
+    float    ms_reserved[2];
 } B2Stats;
 
 /* ---- library / device ---- */

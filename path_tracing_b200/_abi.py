@@ -41,12 +41,12 @@ class RenderParams(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("eye_samples", C.c_uint64), ("closest_rays", C.c_uint64), ("shadow_rays", C.c_uint64),
                 ("path_samples", C.c_uint64), ("delta_cap_hits", C.c_uint64), ("nodes_visited", C.c_uint64),
-                ("tris_tested", C.c_uint64), ("n_batches", C.c_uint64), ("n_waves", C.c_uint64), ("n_launches", C.c_uint64), ("pairs_tested", C.c_uint64),
-                ("ms_total", C.c_float), ("ms_light_pool", C.c_float), ("ms_gen", C.c_float), ("ms_closest", C.c_float),
-                ("ms_shade", C.c_float), ("ms_connect", C.c_float), ("ms_flush", C.c_float)]
+                ("tris_tested", C.c_uint64), ("n_batches", C.c_uint64), ("n_waves", C.c_uint64), ("n_launches", C.c_uint64), ("pairs_tested", C.c_uint64), ("eye_vertices", C.c_uint64),
+                ("ms_total", C.c_float), ("ms_light_pool", C.c_float), ("ms_primary", C.c_float), ("ms_extend", C.c_float),
+                ("ms_connect", C.c_float), ("ms_reserved", C.c_float * 2)]
 
     def as_dict(self):
-        return {n: getattr(self, n) for n, _ in self._fields_}
+        return {n: getattr(self, n) for n, _ in self._fields_ if n != "ms_reserved"}
 
 
 class ParsedScene(C.Structure):

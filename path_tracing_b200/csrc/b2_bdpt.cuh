@@ -39,25 +39,30 @@ B2_HD void store_lv(float4 *pool, int i, const LightVtx &v) {
     pool[B2_LV_F4 * i + 4] = make_float4(v.mtl.roughness, v.mtl.metallic, v.mtl.eta, 0.0f);
 }
 
-// ---- eye-vertex record handed from shade to connect: 5 x float4 (80 B) ----
-//   f0 = {pos, depth}  f1 = {normal, path}  f2 = {wo, roughness}  f3 = {throughput, metallic}  f4 = {base_color, eta}
+// ---- eye-vertex record handed from the extend stage to the connect stage: 5 x float4 (80 B) ----
+//   f0 = {pos, depth | pixel << 8}  f1 = {normal, path}  f2 = {wo, roughness}  f3 = {throughput, metallic}  f4 = {base_color, eta}
+// Records are appended compactly (one per eye vertex actually created this wave), so the connect stage has no idle threads.
 #define B2_CV_F4 5
-struct EyeVtx { float3 pos, n, wo, thr; Mat mtl; int depth, path; };
+struct EyeVtx { float3 pos, n, wo, thr; Mat mtl; int depth, path; uint32_t pixel; };
 B2_HD EyeVtx load_cv(const float4 *cv, int q) {
     const float4 a = cv[B2_CV_F4 * q], b = cv[B2_CV_F4 * q + 1], c = cv[B2_CV_F4 * q + 2], d = cv[B2_CV_F4 * q + 3], e = cv[B2_CV_F4 * q + 4];
     EyeVtx v;
-    v.pos = mk3(a); v.depth = (int) f2u(a.w); v.n = mk3(b); v.path = (int) f2u(b.w); v.wo = mk3(c); v.mtl.roughness = c.w;
+    v.pos = mk3(a); v.depth = (int) (f2u(a.w) & 0xffu); v.pixel = f2u(a.w) >> 8; v.n = mk3(b); v.path = (int) f2u(b.w); v.wo = mk3(c); v.mtl.roughness = c.w;
     v.thr = mk3(d); v.mtl.metallic = d.w; v.mtl.base = mk3(e); v.mtl.eta = e.w;
     return v;
 }
 B2_HD void store_cv(float4 *cv, int q, const EyeVtx &v) {
-    cv[B2_CV_F4 * q] = mk4(v.pos, u2f((uint32_t) v.depth));
+    cv[B2_CV_F4 * q] = mk4(v.pos, u2f((uint32_t) v.depth | (v.pixel << 8)));
     cv[B2_CV_F4 * q + 1] = mk4(v.n, u2f((uint32_t) v.path));
     cv[B2_CV_F4 * q + 2] = mk4(v.wo, v.mtl.roughness);
     cv[B2_CV_F4 * q + 3] = mk4(v.thr, v.mtl.metallic);
     cv[B2_CV_F4 * q + 4] = mk4(v.mtl.base, v.mtl.eta);
 }
-#define B2_CV_NONE 0xffffffffu     // depth field of a queue slot that produced no eye vertex this wave
+
+// ---- connection pre-test record of an ACTIVE pool vertex: 3 x float4 (48 B), built once per render ----
+//   r0 = {pos, cos(cutoff) of the spot-cone gate or B2_NO_GATE}  r1 = {normal, pool index}  r2 = {normalize(light.dir), 0}
+#define B2_PRE_F4 3
+#define B2_NO_GATE (-2.0f)
 
 enum { B2_CNT_EYE_SAMPLES = 0, B2_CNT_CLOSEST, B2_CNT_SHADOW, B2_CNT_PATH_SAMPLES, B2_CNT_DELTA_CAP, B2_CNT_NODES, B2_CNT_TRIS, B2_CNT_PAIRS, B2_CNT_N };
 
@@ -69,23 +74,20 @@ struct RenderCtx {
     uint2 key;
     // light-vertex pool
     float4 *pool; int n_pool;
-    int *pool_active; int *n_pool_active;
-    // per-path state, capacity max_paths
+    float4 *pre; int *n_pool_active;        // pre-test records of the active pool vertices, ascending pool index
+    // per-path state, capacity max_paths; a slot is allocated when a path creates its first eye vertex
     int max_paths;
     float4 *ray_o;      // {origin, current eta}
     float4 *ray_d;      // {direction, last_pdf_omega}
-    float4 *thr;        // {throughput, -}
-    float4 *last_pos;   // {last_pos, -}
-    float4 *last_n;     // {last_normal, -}
-    uint32_t *pix, *sidx;
-    uint32_t *pstate;   // depth | n_delta << 8
-    int2 *hit;          // {prim, float bits of t}, indexed by queue slot
+    float4 *thr;        // {throughput, depth | n_delta << 8}
+    float4 *last_pos;   // {last_pos, pixel}
+    float4 *last_n;     // {last_normal, sample index}
     float4 *hist_pe;    // [eye_depth][max_paths] {pos, eta} of stored (non-delta) eye vertices
     float2 *hist_pdf;   // [eye_depth][max_paths] {pdf_fwd, pdf_rev}
-    int *live;          // queue of live path ids for this wave
+    int *live;          // queue of live path slots for this wave
     int *live_next; int *n_live_next;
-    float4 *cv;         // eye-vertex records, indexed by queue slot
-    float4 *acc;        // {radiance accumulated by this path over all its vertices, -}
+    int *n_paths;       // slots handed out in this batch
+    float4 *cv; int *n_cv;   // eye-vertex records created this wave
     float *film;        // W*H*3 running sums
     unsigned long long *counters;
 };
@@ -223,84 +225,90 @@ B2_HD bool pool_vertex_active(const float4 *pool, int i) { return !(length3(mk3(
 // =====================================================================================================
 // Eye subpaths
 // =====================================================================================================
-// Path i of a batch covers work item w = w0 + i: pixel = w % npix, local sample = w / npix (cpu_bdpt.cpp:344-361)
-B2_HD void eye_gen_body(const RenderCtx &c, int i, long long w0) {
-    const long long w = w0 + i;
+// Register-resident state of one eye subpath between two bounces.
+struct PathState {
+    float3 ro, rd; float eta, last_pdf;     // next ray, current medium eta, solid-angle pdf of the last sampled direction
+    float3 thr, last_pos, last_n;
+    uint32_t pixel, sidx; int depth, n_delta;
+};
+B2_HD PathState load_path(const RenderCtx &c, int p) {
+    const float4 o = c.ray_o[p], d = c.ray_d[p], t = c.thr[p], lp = c.last_pos[p], ln = c.last_n[p];
+    PathState s;
+    s.ro = mk3(o); s.eta = o.w; s.rd = mk3(d); s.last_pdf = d.w; s.thr = mk3(t); s.depth = (int) (f2u(t.w) & 0xffu); s.n_delta = (int) (f2u(t.w) >> 8);
+    s.last_pos = mk3(lp); s.pixel = f2u(lp.w); s.last_n = mk3(ln); s.sidx = f2u(ln.w);
+    return s;
+}
+B2_HD void store_path(const RenderCtx &c, int p, const PathState &s) {
+    c.ray_o[p] = mk4(s.ro, s.eta); c.ray_d[p] = mk4(s.rd, s.last_pdf);
+    c.thr[p] = mk4(s.thr, u2f((uint32_t) s.depth | ((uint32_t) s.n_delta << 8)));
+    c.last_pos[p] = mk4(s.last_pos, u2f(s.pixel)); c.last_n[p] = mk4(s.last_n, u2f(s.sidx));
+}
+// Work item w of a render: pixel = w % npix, local sample = w / npix (cpu_bdpt.cpp:344-361): jittered primary ray.
+B2_HD PathState primary_path(const RenderCtx &c, long long w) {
     const int npix = c.W * c.H;
-    const uint32_t pixel = (uint32_t) (w % npix);
-    const uint32_t s = (uint32_t) (c.sample_offset + (int) (w / npix) * c.sample_stride);
+    PathState s;
+    s.pixel = (uint32_t) (w % npix);
+    s.sidx = (uint32_t) (c.sample_offset + (int) (w / npix) * c.sample_stride);
     float jx, jy;
-    rng_draw2(c.key, B2_RNG_EYE, pixel, s, jx, jy);
-    const float px = x_add((float) (pixel % (uint32_t) c.W), jx), py = x_add((float) (pixel / (uint32_t) c.W), jy);
+    rng_draw2(c.key, B2_RNG_EYE, s.pixel, s.sidx, jx, jy);
+    const float px = x_add((float) (s.pixel % (uint32_t) c.W), jx), py = x_add((float) (s.pixel / (uint32_t) c.W), jy);
     const float3 pp = x3_add(x3_add(c.cUL, x3_muls(c.cdx, px)), x3_muls(c.cdy, py));
-    const float3 d = f3_normalize(x3_sub(pp, c.cam_eye));
-    c.ray_o[i] = mk4(c.cam_eye, 1.0f);
-    c.ray_d[i] = mk4(d, 1.0f);
-    c.thr[i] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
-    c.last_pos[i] = mk4(c.cam_eye, 0.0f);
-    c.last_n[i] = mk4(d, 0.0f);
-    c.pix[i] = pixel; c.sidx[i] = s; c.pstate[i] = 0u;
-    c.acc[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    c.live[i] = i;
+    s.rd = f3_normalize(x3_sub(pp, c.cam_eye));
+    s.ro = c.cam_eye; s.eta = 1.0f; s.last_pdf = 1.0f;
+    s.thr = mk3(1.0f, 1.0f, 1.0f); s.last_pos = c.cam_eye; s.last_n = s.rd;
+    s.depth = 0; s.n_delta = 0;
+    return s;
 }
 
-// One bounce of queue slot q (cpu_bdpt.cpp:365-472 minus the connection loop, which runs from the CV record).
-// Returns true if the path stays alive.
-B2_HD bool shade_body(const RenderCtx &c, int q, uint32_t &n_emit_hits, uint32_t &n_cap) {
-    const DevScene &sc = c.sc;
-    const int path = c.live[q];
-    const int2 hr = c.hit[q];
-    c.cv[B2_CV_F4 * q].w = u2f(B2_CV_NONE);
-    if (hr.x == B2_PRIM_MISS) return false;
-    const float4 o4 = c.ray_o[path], d4 = c.ray_d[path];
-    const float3 ro = mk3(o4), rd = mk3(d4);
-    HitRec h; h.prim = hr.x; h.t = u2f((uint32_t) hr.y);
-    const Surface s = surface_at(sc, ro, rd, h);
-    const uint32_t ps = c.pstate[path];
-    int depth = (int) (ps & 0xffu), n_delta = (int) (ps >> 8);
-    if (s.is_light && depth == 0) {                                        // :372-375
-        if (valid_color(s.mtl.base)) c.acc[path] = mk4(s.mtl.base, 0.0f);   // depth 0: nothing accumulated before
-        n_emit_hits++;
-        return false;
+// One bounce (cpu_bdpt.cpp:365-472 minus the connection loop, which runs later from the eye-vertex record).
+struct ShadeOut {
+    bool has_cv;        // an eye vertex was created: `ev` is valid (its .path is filled in by the caller)
+    bool alive;         // the path continues: `ps` holds the next ray
+    bool store_hist;    // non-delta vertex of a continuing path: hist[ev.depth] = {pos, eta}, {pdf_fwd, pdf_rev}
+    bool emitter_hit;   // depth-0 light hit: `emitted` goes to the film (:372-375)
+    bool delta_cap;
+    EyeVtx ev; float pdf_fwd, pdf_rev; float3 emitted;
+};
+B2_HD void shade_step(const RenderCtx &c, PathState &ps, HitRec h, ShadeOut &o) {
+    o.has_cv = o.alive = o.store_hist = o.emitter_hit = o.delta_cap = false;
+    if (h.prim == B2_PRIM_MISS) return;
+    const Surface s = surface_at(c.sc, ps.ro, ps.rd, h);
+    if (s.is_light && ps.depth == 0) {                                     // :372-375
+        o.emitter_hit = true; o.emitted = s.mtl.base;
+        return;
     }
-    const float3 last_pos = mk3(c.last_pos[path]), last_n = mk3(c.last_n[path]);
-    const float3 wo = rd * -1.0f;
+    const float3 wo = ps.rd * -1.0f;
     float pdf_fwd = 1.0f;
-    const float3 dp = s.pos - last_pos;
+    const float3 dp = s.pos - ps.last_pos;
     const float dist2 = dot3(dp, dp);
-    if (depth > 0) pdf_fwd = d4.w * fabsf(dot3(s.n, wo)) / fmaxf(dist2, 1e-6f);   // :378-382
-    float3 thr = mk3(c.thr[path]);
-    EyeVtx ev; ev.pos = s.pos; ev.n = s.n; ev.wo = wo; ev.thr = thr; ev.mtl = s.mtl; ev.depth = depth; ev.path = path;
-    store_cv(c.cv, q, ev);
+    if (ps.depth > 0) pdf_fwd = ps.last_pdf * fabsf(dot3(s.n, wo)) / fmaxf(dist2, 1e-6f);   // :378-382
+    o.has_cv = true;
+    o.ev.pos = s.pos; o.ev.n = s.n; o.ev.wo = wo; o.ev.thr = ps.thr; o.ev.mtl = s.mtl; o.ev.depth = ps.depth; o.ev.pixel = ps.pixel; o.ev.path = -1;
     float u_rr, u1, u2;
-    rng_draw3(c.key, B2_RNG_EYE, c.pix[path], c.sidx[path], (uint32_t) (depth + n_delta), u_rr, u1, u2);
+    rng_draw3(c.key, B2_RNG_EYE, ps.pixel, ps.sidx, (uint32_t) (ps.depth + ps.n_delta), u_rr, u1, u2);
     BsdfSample bs; bs.wi = mk3(0, 0, 0); bs.f = mk3(0, 0, 0); bs.pdf = 0.0f;
-    bsdf_sample(s.mtl, wo, s.n, u_rr, u1, u2, o4.w, bs);
-    if (bs.pdf <= 0.0f && !bs.is_delta) return false;
+    bsdf_sample(s.mtl, wo, s.n, u_rr, u1, u2, ps.eta, bs);
+    if (bs.pdf <= 0.0f && !bs.is_delta) return;
     if (bs.is_delta) {                                                     // :453-459
-        thr = thr * bs.f;
-        c.thr[path] = mk4(thr, 0.0f);
-        c.ray_d[path] = mk4(bs.wi, 1.0f);
-        c.ray_o[path] = mk4(s.pos + s.n * (dot3(bs.wi, s.n) < 0.0f ? -B2_EPSILON : B2_EPSILON), bs.new_eta);
-        c.last_pos[path] = mk4(s.pos, 0.0f); c.last_n[path] = mk4(s.n, 0.0f);
-        n_delta++;
-        c.pstate[path] = (uint32_t) depth | ((uint32_t) n_delta << 8);
-        if (n_delta >= c.max_delta) { n_cap++; return false; }
-        return true;
+        ps.thr = ps.thr * bs.f;
+        ps.rd = bs.wi; ps.last_pdf = 1.0f;
+        ps.ro = s.pos + s.n * (dot3(bs.wi, s.n) < 0.0f ? -B2_EPSILON : B2_EPSILON); ps.eta = bs.new_eta;
+        ps.last_pos = s.pos; ps.last_n = s.n;
+        ps.n_delta++;
+        if (ps.n_delta >= c.max_delta) { o.delta_cap = true; return; }
+        o.alive = true;
+        return;
     }
-    const float pdf_rev = bsdf_pdf(s.mtl, bs.wi, wo, s.n) * fabsf(dot3(last_n, rd)) / fmaxf(dist2, 1e-6f);   // :461-465
-    c.hist_pe[(size_t) depth * c.max_paths + path] = mk4(s.pos, s.mtl.eta);
-    c.hist_pdf[(size_t) depth * c.max_paths + path] = make_float2(pdf_fwd, pdf_rev);
-    thr = thr * bs.f * fabsf(dot3(s.n, bs.wi)) / bs.pdf;
-    if (!valid_color(thr)) return false;
-    depth++;
-    if (depth >= c.eye_depth) return false;
-    c.thr[path] = mk4(thr, 0.0f);
-    c.ray_d[path] = mk4(bs.wi, bs.pdf);
-    c.ray_o[path] = mk4(s.pos + s.n * B2_EPSILON, o4.w);
-    c.last_pos[path] = mk4(s.pos, 0.0f); c.last_n[path] = mk4(s.n, 0.0f);
-    c.pstate[path] = (uint32_t) depth | ((uint32_t) n_delta << 8);
-    return true;
+    o.pdf_fwd = pdf_fwd;
+    o.pdf_rev = bsdf_pdf(s.mtl, bs.wi, wo, s.n) * fabsf(dot3(ps.last_n, ps.rd)) / fmaxf(dist2, 1e-6f);   // :461-465
+    ps.thr = ps.thr * bs.f * fabsf(dot3(s.n, bs.wi)) / bs.pdf;
+    if (!valid_color(ps.thr)) return;
+    ps.depth++;
+    if (ps.depth >= c.eye_depth) return;
+    ps.rd = bs.wi; ps.last_pdf = bs.pdf;
+    ps.ro = s.pos + s.n * B2_EPSILON;
+    ps.last_pos = s.pos; ps.last_n = s.n;
+    o.alive = true; o.store_hist = true;
 }
 
 // =====================================================================================================
@@ -391,6 +399,26 @@ B2_HD bool connect_pretest(const RenderCtx &c, float3 ev_pos, float3 ev_n, int l
         if (dot3(mk3(l3), mwi) < l3.w) return false;
     }
     return true;
+}
+// The same tests from a pre-test record, division-free: cos > 0 <=> dot(n, d) > 0, and the cone gate
+// dot(l, -d/|d|) < cos(cutoff) <=> -dot(l, d) < cos(cutoff) * |d|.  (Sign-equivalent up to fp32 rounding exactly at the
+// boundary; the cosines are recomputed as the reference does in connect_finish.)
+B2_HD void make_pretest_rec(const RenderCtx &c, int lv_index, float4 *rec) {
+    const float4 f0 = c.pool[B2_LV_F4 * lv_index], f1 = c.pool[B2_LV_F4 * lv_index + 1];
+    const uint32_t flags = f2u(f0.w);
+    float gate = B2_NO_GATE; float3 ldir = mk3(0, 0, 0);
+    if ((flags & B2_LV_SRC) && f1.w > 0.0f && !(flags & B2_LV_PARALLEL)) {
+        const float4 l3 = c.sc.lights[4 * ((lv_index / c.light_depth) % c.sc.n_lights) + 3];
+        gate = l3.w; ldir = mk3(l3);
+    }
+    rec[0] = mk4(mk3(f0), gate); rec[1] = mk4(mk3(f1), u2f((uint32_t) lv_index)); rec[2] = mk4(ldir, 0.0f);
+}
+B2_HD bool pretest_rec(float3 ev_pos, float3 ev_n, float4 r0, float4 r1, float4 r2) {
+    const float3 d = mk3(r0) - ev_pos;
+    const float dist2 = dot3(d, d);
+    bool pass = !(dist2 < 1e-6f) && dot3(ev_n, d) > 0.0f && dot3(mk3(r1), d) < 0.0f;
+    if (r0.w > -1.5f) pass = pass && !(-dot3(mk3(r2), d) < r0.w * sqrtf(dist2));
+    return pass;
 }
 // Returns the (validated, clamped) contribution, zero if the pair contributes nothing.  n_shadow / n_path count
 // visibility queries (:424) and connections that reach the MIS evaluation (:431).

@@ -1,33 +1,32 @@
 // b2_render.cu -- wavefront BDPT on the device: __global__ wrappers around the stage bodies of b2_bdpt.cuh and
 // the host wave loop behind b2_render_bdpt / b2_render_bdpt_device / b2_light_pool (include/b2pt.h).
 //
-// Replaces run_cpu_bdpt (src/cpu_bdpt.cpp:173-488) / run_cuda_bdpt (include/bdpt_cu_helper.h:6).  Layout of one
-// render (everything stays in HBM between stages; the scene tables and the light pool are L2-resident):
+// Replaces run_cpu_bdpt (src/cpu_bdpt.cpp:173-488) / run_cuda_bdpt (include/bdpt_cu_helper.h:6).  One render:
 //
-//   k_light_paths  one thread per light subpath -> pool (5 x float4 per vertex)         cpu_bdpt.cpp:218-325
-//   k_pool_active  ordered compaction of the pool vertices that can contribute           :391
-//   per batch of <= max_paths eye samples:
-//     k_eye_gen    primary rays + path state                                             :349-361
-//     per wave (one bounce of every live path):
-//       k_closest  closest-hit traversal of the 8-wide BVH, shared-memory stacks         :369
-//       k_shade    eye vertex record, BSDF sample, next ray; live-path compaction with
-//                  warp ballot + prefix and one atomic per warp                          :372-385, :442-472
-//       k_connect  eye vertex x pool: pre-tests for all pairs, survivors compacted in a
-//                  shared-memory ring and finished at full occupancy (BSDFs, shadow
-//                  any-hit, MIS), summed per eye vertex in shared memory                 :389-439
-//     k_flush      per-path radiance -> film (atomicAdd)                                 :475-476
-//   k_resolve      film / spp                                                            :479
+//   k_light_paths  one thread per light subpath -> pool (5 x float4 per vertex)              cpu_bdpt.cpp:218-325
+//   k_pool_active  ordered compaction of the pool vertices that can contribute (:391) into 48-byte pre-test records
+//   per batch of <= max_paths eye samples, per wave (one bounce of every live path):
+//     k_extend     wave 0: primary ray generated in registers (:349-361); later waves: path state from HBM.
+//                  Closest-hit traversal of the 8-wide BVH with shared-memory stacks (:369), then the bounce
+//                  (:372-385, :442-472): eye-vertex record appended to a COMPACT list, BSDF sample, next ray.
+//                  Path slots, eye-vertex slots and the next wave's queue are handed out with warp ballot +
+//                  prefix popcount and one atomic per warp.  A sample whose primary ray escapes never touches HBM.
+//     k_connect    eye vertex x pool (:389-439), one warp per 32 eye vertices, warp-autonomous: every lane
+//                  pre-tests its vertex against the pool records (uniform broadcast loads); surviving pairs are
+//                  compacted into the warp's shared-memory ring and finished 32 at a time at full occupancy
+//                  (BSDFs, shadow any-hit, MIS); per-vertex sums go to the film with one atomicAdd per channel.
+//   k_resolve      film / spp                                                                 :479
 #include "b2_render.hpp"
 #include <algorithm>
 #include <vector>
 
 namespace {
 
-constexpr int TRAV_THREADS = 128;     // closest-hit kernel block
-constexpr int SHADE_THREADS = 256;
-constexpr int CONN_THREADS = 256;     // connect kernel block: one eye vertex per thread in the pre-test phase
-constexpr int CONN_CHUNK = 8;         // pool vertices pre-tested between two block barriers
-constexpr int CONN_QCAP = CONN_THREADS * (CONN_CHUNK + 1);   // ring capacity: a full chunk on top of < one drain
+constexpr int EXT_THREADS = 128;      // extend kernel block
+constexpr int CONN_THREADS = 128;     // connect kernel block: 4 independent warps
+constexpr int CONN_WARPS = CONN_THREADS / 32;
+constexpr int CONN_GROUP = 4;         // pool vertices pre-tested between two drain checks
+constexpr int CONN_RING = 256;        // per-warp ring capacity (power of two) >= 31 pending + CONN_GROUP * 32 new entries
 
 __device__ __forceinline__ uint32_t lanemask_lt() { uint32_t m; asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m)); return m; }
 
@@ -36,9 +35,18 @@ __device__ __forceinline__ void warp_count_add(unsigned long long *counter, uint
     v = __reduce_add_sync(0xffffffffu, v);
     if ((threadIdx.x & 31) == 0 && v) atomicAdd(counter, (unsigned long long) v);
 }
+// warp-aggregated slot allocation: lanes with `want` get consecutive indices from *counter (one atomic per warp)
+__device__ __forceinline__ int warp_alloc(int *counter, bool want) {
+    const uint32_t m = __ballot_sync(0xffffffffu, want);
+    if (m == 0u) return -1;
+    int base = 0;
+    if ((threadIdx.x & 31) == (__ffs((int) m) - 1)) base = atomicAdd(counter, __popc(m));
+    base = __shfl_sync(0xffffffffu, base, __ffs((int) m) - 1);
+    return want ? base + __popc(m & lanemask_lt()) : -1;
+}
 
 template <bool COUNT>
-__global__ void __launch_bounds__(TRAV_THREADS) k_light_paths(RenderCtx c, int n_paths) {
+__global__ void __launch_bounds__(EXT_THREADS) k_light_paths(RenderCtx c, int n_paths) {
     extern __shared__ uint2 s_stack[];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     TravCounters tc{ 0u, 0u };
@@ -49,7 +57,7 @@ __global__ void __launch_bounds__(TRAV_THREADS) k_light_paths(RenderCtx c, int n
     if (COUNT) { warp_count_add(&c.counters[B2_CNT_NODES], tc.nodes); warp_count_add(&c.counters[B2_CNT_TRIS], tc.tris); }
 }
 
-// Single block: ascending list of pool vertices with |throughput| >= 1e-6 (deterministic order).
+// Single block: pre-test records of the pool vertices with |throughput| >= 1e-6, in ascending pool order (deterministic).
 __global__ void __launch_bounds__(1024) k_pool_active(RenderCtx c) {
     __shared__ int s_warp[32];
     __shared__ int s_base;
@@ -64,7 +72,7 @@ __global__ void __launch_bounds__(1024) k_pool_active(RenderCtx c) {
         __syncthreads();
         int off = 0, tot = 0;
         for (int w = 0; w < nwarps; ++w) { const int v = s_warp[w]; if (w < warp) off += v; tot += v; }
-        if (act) c.pool_active[s_base + off + __popc(m & lanemask_lt())] = i;
+        if (act) make_pretest_rec(c, i, c.pre + (size_t) B2_PRE_F4 * (s_base + off + __popc(m & lanemask_lt())));
         __syncthreads();
         if (threadIdx.x == 0) s_base += tot;
         __syncthreads();
@@ -72,134 +80,110 @@ __global__ void __launch_bounds__(1024) k_pool_active(RenderCtx c) {
     if (threadIdx.x == 0) *c.n_pool_active = s_base;
 }
 
-__global__ void __launch_bounds__(256) k_eye_gen(RenderCtx c, int n, long long w0) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) eye_gen_body(c, i, w0);
-}
-
-template <bool COUNT>
-__global__ void __launch_bounds__(TRAV_THREADS) k_closest(RenderCtx c, int n_live) {
+// One bounce of every live path.  PRIMARY: item = sample w0 + i of the batch (no state in HBM yet).
+template <bool PRIMARY, bool COUNT>
+__global__ void __launch_bounds__(EXT_THREADS) k_extend(RenderCtx c, int n_items, long long w0) {
     extern __shared__ uint2 s_stack[];
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool active = q < n_items;
     TravCounters tc{ 0u, 0u };
-    if (q < n_live) {
-        const int path = c.live[q];
-        const HitRec h = closest_hit_bvh<COUNT>(c.sc, mk3(c.ray_o[path]), mk3(c.ray_d[path]), s_stack + threadIdx.x, blockDim.x, &tc);
-        c.hit[q] = make_int2(h.prim, (int) __float_as_uint(h.t));
+    PathState ps;
+    ShadeOut so; so.has_cv = so.alive = so.store_hist = so.emitter_hit = so.delta_cap = false;
+    int path = -1;
+    if (active) {
+        if (PRIMARY) ps = primary_path(c, w0 + q);
+        else { path = c.live[q]; ps = load_path(c, path); }
+        const HitRec h = closest_hit_bvh<COUNT>(c.sc, ps.ro, ps.rd, s_stack + threadIdx.x, blockDim.x, &tc);
+        shade_step(c, ps, h, so);
     }
+    if (PRIMARY) path = warp_alloc(c.n_paths, so.has_cv);          // a path gets its slot with its first eye vertex
+    const int cvi = warp_alloc(c.n_cv, so.has_cv);
+    if (so.has_cv) {
+        so.ev.path = path;
+        store_cv(c.cv, cvi, so.ev);
+        if (so.store_hist) {
+            c.hist_pe[(size_t) so.ev.depth * c.max_paths + path] = mk4(so.ev.pos, so.ev.mtl.eta);
+            c.hist_pdf[(size_t) so.ev.depth * c.max_paths + path] = make_float2(so.pdf_fwd, so.pdf_rev);
+        }
+        if (so.alive) store_path(c, path, ps);
+    }
+    const int li = warp_alloc(c.n_live_next, so.alive);
+    if (so.alive) c.live_next[li] = path;
+    if (so.emitter_hit && valid_color(so.emitted)) {                // depth-0 emitter hit, cpu_bdpt.cpp:372-375
+        atomicAdd(&c.film[3 * ps.pixel], so.emitted.x); atomicAdd(&c.film[3 * ps.pixel + 1], so.emitted.y); atomicAdd(&c.film[3 * ps.pixel + 2], so.emitted.z);
+    }
+    warp_count_add(&c.counters[B2_CNT_PATH_SAMPLES], so.emitter_hit ? 1u : 0u);
+    warp_count_add(&c.counters[B2_CNT_DELTA_CAP], so.delta_cap ? 1u : 0u);
     if (COUNT) { warp_count_add(&c.counters[B2_CNT_NODES], tc.nodes); warp_count_add(&c.counters[B2_CNT_TRIS], tc.tris); }
 }
 
-__global__ void __launch_bounds__(SHADE_THREADS) k_shade(RenderCtx c, int n_live) {
-    const int q = blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t emit = 0, cap = 0;
-    bool alive = false;
-    int path = 0;
-    if (q < n_live) { path = c.live[q]; alive = shade_body(c, q, emit, cap); }
-    // live-path compaction: rank within the warp from the ballot, one atomic per warp for the base
-    const uint32_t m = __ballot_sync(0xffffffffu, alive);
-    if (m) {
-        int base = 0;
-        if ((threadIdx.x & 31) == 0) base = atomicAdd(c.n_live_next, __popc(m));
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (alive) c.live_next[base + __popc(m & lanemask_lt())] = path;
-    }
-    warp_count_add(&c.counters[B2_CNT_PATH_SAMPLES], emit);
-    warp_count_add(&c.counters[B2_CNT_DELTA_CAP], cap);
-}
-
-// Connection stage.  Phase A (every thread owns the eye vertex of queue slot q and walks the active pool list;
-// the pool record loads are warp-uniform broadcasts): pairs that pass connect_pretest are pushed into a
-// shared-memory ring as (owner thread << 24 | pool index).  Phase B: whenever the ring holds a full block of
-// entries they are finished with every lane busy (connect_finish traces the shadow segment), and the result is
-// added to the owner's accumulator in shared memory.  One global read-modify-write per eye vertex at the end.
+// Connection stage: one warp per 32 eye-vertex records, no block-level synchronisation.
 template <bool COUNT>
-__global__ void __launch_bounds__(CONN_THREADS) k_connect(RenderCtx c, int n_live) {
+__global__ void __launch_bounds__(CONN_THREADS) k_connect(RenderCtx c) {
     extern __shared__ uint2 s_stack[];                    // CONN_THREADS x stack depth
-    __shared__ uint32_t s_ring[CONN_QCAP];
-    __shared__ float s_acc[3 * CONN_THREADS];
-    __shared__ uint32_t s_tail;
-    const int tid = threadIdx.x;
-    const int q = blockIdx.x * CONN_THREADS + tid;
-    const int qbase = blockIdx.x * CONN_THREADS;
-    bool valid = false;
+    __shared__ uint32_t s_ring[CONN_WARPS][CONN_RING];
+    __shared__ float s_acc[CONN_WARPS][3][32];
+    const int n_cv = *c.n_cv;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int q0 = (blockIdx.x * CONN_WARPS + warp) * 32;
+    if (q0 >= n_cv) return;                               // whole warp out of range (grid is sized for the upper bound)
+    const int q = q0 + lane;
+    const bool valid = q < n_cv;
     float3 my_pos = mk3(0, 0, 0), my_n = mk3(0, 0, 0);
-    if (q < n_live) {
-        const float4 a = c.cv[B2_CV_F4 * q];
-        if (__float_as_uint(a.w) != B2_CV_NONE) { valid = true; my_pos = mk3(a); my_n = mk3(c.cv[B2_CV_F4 * q + 1]); }
-    }
-    s_acc[tid] = 0.0f; s_acc[tid + CONN_THREADS] = 0.0f; s_acc[tid + 2 * CONN_THREADS] = 0.0f;
-    if (tid == 0) s_tail = 0u;
-    __syncthreads();
-    if (__syncthreads_or(valid) == 0) return;            // no eye vertex in this block
+    if (valid) { my_pos = mk3(c.cv[B2_CV_F4 * q]); my_n = mk3(c.cv[B2_CV_F4 * q + 1]); }
+    uint32_t *ring = s_ring[warp];
+    float *acc_x = s_acc[warp][0], *acc_y = s_acc[warp][1], *acc_z = s_acc[warp][2];
+    acc_x[lane] = 0.0f; acc_y[lane] = 0.0f; acc_z[lane] = 0.0f;
+    __syncwarp();
     const int n_act = *c.n_pool_active;
-    uint32_t head = 0u;                                   // block-uniform
-    uint32_t n_shadow = 0, n_path = 0, n_pairs = 0;
+    uint32_t head = 0u, tail = 0u;                        // warp-uniform ring cursors (registers)
+    uint32_t n_shadow = 0, n_path = 0;
     TravCounters tc{ 0u, 0u };
 
-    auto drain = [&](uint32_t count) {                    // count <= CONN_THREADS entries starting at head
-        if ((uint32_t) tid < count) {
-            const uint32_t e = s_ring[(head + (uint32_t) tid) % CONN_QCAP];
-            const int owner = (int) (e >> 24), lvi = (int) (e & 0xffffffu);
-            const EyeVtx ev = load_cv(c.cv, qbase + owner);
-            const float3 r = connect_finish<COUNT>(c, ev, lvi, s_stack + tid, CONN_THREADS, &tc, n_shadow, n_path);
-            if (r.x != 0.0f) atomicAdd(&s_acc[owner], r.x);
-            if (r.y != 0.0f) atomicAdd(&s_acc[owner + CONN_THREADS], r.y);
-            if (r.z != 0.0f) atomicAdd(&s_acc[owner + 2 * CONN_THREADS], r.z);
+    auto drain = [&](uint32_t count) {                    // finish `count` <= 32 entries starting at head
+        if ((uint32_t) lane < count) {
+            const uint32_t e = ring[(head + (uint32_t) lane) % CONN_RING];
+            const int owner = (int) (e >> 27), lvi = (int) (e & 0x7ffffffu);
+            const EyeVtx ev = load_cv(c.cv, q0 + owner);
+            const float3 r = connect_finish<COUNT>(c, ev, lvi, s_stack + threadIdx.x, CONN_THREADS, &tc, n_shadow, n_path);
+            if (r.x != 0.0f) atomicAdd(&acc_x[owner], r.x);
+            if (r.y != 0.0f) atomicAdd(&acc_y[owner], r.y);
+            if (r.z != 0.0f) atomicAdd(&acc_z[owner], r.z);
         }
         head += count;
+        __syncwarp();
     };
 
-    for (int a0 = 0; a0 < n_act; a0 += CONN_CHUNK) {
-        const int a1 = min(a0 + CONN_CHUNK, n_act);
-        for (int a = a0; a < a1; ++a) {
-            const int lvi = c.pool_active[a];
-            const bool pass = valid && connect_pretest(c, my_pos, my_n, lvi);
-            if (valid) n_pairs++;
-            const uint32_t m = __ballot_sync(0xffffffffu, pass);
-            if (m) {
-                uint32_t base = 0u;
-                if ((tid & 31) == 0) base = atomicAdd(&s_tail, (uint32_t) __popc(m));
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (pass) s_ring[(base + (uint32_t) __popc(m & lanemask_lt())) % CONN_QCAP] = ((uint32_t) tid << 24) | (uint32_t) lvi;
+    const float4 *__restrict__ pre = c.pre;
+    for (int a0 = 0; a0 < n_act; a0 += CONN_GROUP) {
+        // pre-test a group of pool vertices (independent broadcast loads, so they pipeline), compacting survivors
+#pragma unroll
+        for (int k = 0; k < CONN_GROUP; ++k) {
+            const int a = a0 + k;
+            if (a < n_act) {
+                const float4 r0 = __ldg(&pre[B2_PRE_F4 * a]), r1 = __ldg(&pre[B2_PRE_F4 * a + 1]), r2 = __ldg(&pre[B2_PRE_F4 * a + 2]);
+                const bool pass = valid && pretest_rec(my_pos, my_n, r0, r1, r2);
+                const uint32_t m = __ballot_sync(0xffffffffu, pass);
+                if (pass) ring[(tail + (uint32_t) __popc(m & lanemask_lt())) % CONN_RING] = ((uint32_t) lane << 27) | __float_as_uint(r1.w);
+                tail += (uint32_t) __popc(m);
             }
         }
-        __syncthreads();
-        const uint32_t tail = s_tail;
-        while (tail - head >= (uint32_t) CONN_THREADS) drain(CONN_THREADS);
-        __syncthreads();                                  // ring slots of drained entries may be overwritten now
+        __syncwarp();
+        // finish surviving pairs 32 at a time; after the last group also the remainder
+        const uint32_t need = (a0 + CONN_GROUP >= n_act) ? 1u : 32u;
+        while (tail - head >= need) drain(min(32u, tail - head));
     }
-    {
-        const uint32_t tail = s_tail;
-        if (tail != head) drain(tail - head);
-    }
-    __syncthreads();
     if (valid) {
-        const float3 r = mk3(s_acc[tid], s_acc[tid + CONN_THREADS], s_acc[tid + 2 * CONN_THREADS]);
-        if (r.x != 0.0f || r.y != 0.0f || r.z != 0.0f) {
-            const int path = (int) __float_as_uint(c.cv[B2_CV_F4 * q + 1].w);
-            float4 acc = c.acc[path];
-            acc.x += r.x; acc.y += r.y; acc.z += r.z;
-            c.acc[path] = acc;
-        }
+        const float3 r = mk3(acc_x[lane], acc_y[lane], acc_z[lane]);
+        const uint32_t pixel = __float_as_uint(c.cv[B2_CV_F4 * q].w) >> 8;
+        if (r.x != 0.0f) atomicAdd(&c.film[3 * pixel], r.x);
+        if (r.y != 0.0f) atomicAdd(&c.film[3 * pixel + 1], r.y);
+        if (r.z != 0.0f) atomicAdd(&c.film[3 * pixel + 2], r.z);
     }
     warp_count_add(&c.counters[B2_CNT_SHADOW], n_shadow);
     warp_count_add(&c.counters[B2_CNT_PATH_SAMPLES], n_path);
-    warp_count_add(&c.counters[B2_CNT_PAIRS], n_pairs);
+    if (lane == 0) atomicAdd(&c.counters[B2_CNT_PAIRS], (unsigned long long) n_act * (unsigned long long) min(32, n_cv - q0));
     if (COUNT) { warp_count_add(&c.counters[B2_CNT_NODES], tc.nodes); warp_count_add(&c.counters[B2_CNT_TRIS], tc.tris); }
-}
-
-// cpu_bdpt.cpp:475-476: a sample whose radiance is not a valid colour contributes nothing
-__global__ void __launch_bounds__(256) k_flush(RenderCtx c, int n) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const float4 a = c.acc[i];
-    const float3 v = mk3(a);
-    if (!valid_color(v)) return;
-    const uint32_t pixel = c.pix[i];
-    if (v.x != 0.0f) atomicAdd(&c.film[3 * pixel], v.x);
-    if (v.y != 0.0f) atomicAdd(&c.film[3 * pixel + 1], v.y);
-    if (v.z != 0.0f) atomicAdd(&c.film[3 * pixel + 2], v.z);
 }
 
 __global__ void __launch_bounds__(256) k_resolve(const float *__restrict__ sum, float *__restrict__ out, size_t n, float inv) {
@@ -230,12 +214,11 @@ int RenderWorkspace::ensure(int max_paths, int eye_depth, int n_pool, size_t fil
     if (max_paths > cap_paths || eye_depth > cap_depth) {
         const int mp = std::max(max_paths, cap_paths), ed = std::max(eye_depth, cap_depth);
         B2_TRY(ray_o.alloc(mp)); B2_TRY(ray_d.alloc(mp)); B2_TRY(thr.alloc(mp)); B2_TRY(last_pos.alloc(mp)); B2_TRY(last_n.alloc(mp));
-        B2_TRY(acc.alloc(mp)); B2_TRY(pix.alloc(mp)); B2_TRY(sidx.alloc(mp)); B2_TRY(pstate.alloc(mp)); B2_TRY(hit.alloc(mp));
         B2_TRY(hist_pe.alloc((size_t) ed * mp)); B2_TRY(hist_pdf.alloc((size_t) ed * mp));
         B2_TRY(live_a.alloc(mp)); B2_TRY(live_b.alloc(mp)); B2_TRY(cv.alloc((size_t) B2_CV_F4 * mp));
         cap_paths = mp; cap_depth = ed;
     }
-    if (n_pool > cap_pool) { B2_TRY(pool.alloc((size_t) B2_LV_F4 * n_pool)); B2_TRY(pool_active.alloc(n_pool)); cap_pool = n_pool; }
+    if (n_pool > cap_pool) { B2_TRY(pool.alloc((size_t) B2_LV_F4 * n_pool)); B2_TRY(pre.alloc((size_t) B2_PRE_F4 * n_pool)); cap_pool = n_pool; }
     if (film_floats > film.n) B2_TRY(film.alloc(film_floats));
     if (!ints.p) B2_TRY(ints.alloc(8));
     if (!counters.p) B2_TRY(counters.alloc(B2_CNT_N));
@@ -243,9 +226,9 @@ int RenderWorkspace::ensure(int max_paths, int eye_depth, int n_pool, size_t fil
     return B2_OK;
 }
 void RenderWorkspace::release() {
-    ray_o.release(); ray_d.release(); thr.release(); last_pos.release(); last_n.release(); acc.release(); pix.release(); sidx.release();
-    pstate.release(); hit.release(); hist_pe.release(); hist_pdf.release(); live_a.release(); live_b.release(); cv.release();
-    pool.release(); pool_active.release(); film.release(); ints.release(); counters.release();
+    ray_o.release(); ray_d.release(); thr.release(); last_pos.release(); last_n.release();
+    hist_pe.release(); hist_pdf.release(); live_a.release(); live_b.release(); cv.release();
+    pool.release(); pre.release(); film.release(); ints.release(); counters.release();
     if (h_ints) { cudaFreeHost(h_ints); h_ints = nullptr; }
     cap_paths = cap_depth = cap_pool = 0;
 }
@@ -255,8 +238,9 @@ static int validate_params(const B2RenderParams &p) {
         b2_set_error("invalid render parameters (width/height/spp must be > 0, light_depth > 0, spl/eye_depth >= 0)"); return B2_ERR_INVALID;
     }
     if (p.eye_depth > 255) { b2_set_error("eye_depth > 255 is not supported"); return B2_ERR_INVALID; }
-    if ((long long) p.width * p.height > (1ll << 30)) { b2_set_error("film too large"); return B2_ERR_INVALID; }
+    if ((long long) p.width * p.height > (1ll << 24)) { b2_set_error("film larger than 2^24 pixels is not supported"); return B2_ERR_INVALID; }
     if (p.sample_offset < 0 || p.sample_stride < 0) { b2_set_error("invalid sample_offset / sample_stride"); return B2_ERR_INVALID; }
+    if ((long long) p.spl * p.light_depth > (1ll << 26)) { b2_set_error("spl * light_depth too large"); return B2_ERR_INVALID; }
     return B2_OK;
 }
 
@@ -269,24 +253,24 @@ static void setup_ctx(RenderCtx &c, const DevScene &sc, const B2Camera &cam, con
     c.sample_offset = p.sample_offset; c.sample_stride = p.sample_stride > 0 ? p.sample_stride : 1;
     c.key = make_uint2((uint32_t) p.seed, (uint32_t) (p.seed >> 32));
     c.pool = ws.pool.p; c.n_pool = sc.n_lights * p.spl * p.light_depth;
-    c.pool_active = ws.pool_active.p; c.n_pool_active = ws.ints.p + 0;
+    c.pre = ws.pre.p; c.n_pool_active = ws.ints.p + 0;
     c.max_paths = max_paths;
     c.ray_o = ws.ray_o.p; c.ray_d = ws.ray_d.p; c.thr = ws.thr.p; c.last_pos = ws.last_pos.p; c.last_n = ws.last_n.p;
-    c.pix = ws.pix.p; c.sidx = ws.sidx.p; c.pstate = ws.pstate.p; c.hit = ws.hit.p;
     c.hist_pe = ws.hist_pe.p; c.hist_pdf = ws.hist_pdf.p;
     c.live = ws.live_a.p; c.live_next = ws.live_b.p; c.n_live_next = ws.ints.p + 1;
-    c.cv = ws.cv.p; c.acc = ws.acc.p; c.film = ws.film.p; c.counters = ws.counters.p;
+    c.n_cv = ws.ints.p + 2; c.n_paths = ws.ints.p + 3;
+    c.cv = ws.cv.p; c.film = ws.film.p; c.counters = ws.counters.p;
 }
 
 // Optional per-stage device timing: one CUDA event pair per launch, summed per stage after each wave's sync.
 struct StageTimer {
-    enum { GEN, CLOSEST, SHADE, CONNECT, FLUSH, N };
+    enum { PRIMARY, EXTEND, CONNECT, N };
     bool on = false;
     cudaStream_t st = nullptr;
     std::vector<cudaEvent_t> pool;
     struct Rec { int stage; cudaEvent_t a, b; };
     std::vector<Rec> pending;
-    float ms[N] = { 0, 0, 0, 0, 0 };
+    float ms[N] = { 0, 0, 0 };
     cudaEvent_t get() { if (pool.empty()) { cudaEvent_t e; cudaEventCreate(&e); return e; } cudaEvent_t e = pool.back(); pool.pop_back(); return e; }
     void begin(int stage) { if (!on) return; Rec r{ stage, get(), get() }; cudaEventRecord(r.a, st); pending.push_back(r); }
     void end() { if (!on) return; cudaEventRecord(pending.back().b, st); }
@@ -304,9 +288,9 @@ static int build_pool(RenderCtx &c, int bvh_depth, bool count, cudaStream_t st, 
     if (c.n_pool <= 0) { B2_CUDA(cudaMemsetAsync(c.n_pool_active, 0, sizeof(int), st)); return B2_OK; }
     B2_CUDA(cudaMemsetAsync(c.pool, 0, sizeof(float4) * B2_LV_F4 * (size_t) c.n_pool, st));    // value-initialised pool, cpu_bdpt.cpp:203
     const int n_paths = c.sc.n_lights * c.spl;
-    const size_t sb = stack_bytes(TRAV_THREADS, bvh_depth);
-    if (count) k_light_paths<true><<<blocks_for(n_paths, TRAV_THREADS), TRAV_THREADS, sb, st>>>(c, n_paths);
-    else k_light_paths<false><<<blocks_for(n_paths, TRAV_THREADS), TRAV_THREADS, sb, st>>>(c, n_paths);
+    const size_t sb = stack_bytes(EXT_THREADS, bvh_depth);
+    if (count) k_light_paths<true><<<blocks_for(n_paths, EXT_THREADS), EXT_THREADS, sb, st>>>(c, n_paths);
+    else k_light_paths<false><<<blocks_for(n_paths, EXT_THREADS), EXT_THREADS, sb, st>>>(c, n_paths);
     k_pool_active<<<1, 1024, 0, st>>>(c);
     n_launches += 2;
     B2_CUDA(cudaGetLastError());
@@ -316,14 +300,16 @@ static int build_pool(RenderCtx &c, int bvh_depth, bool count, cudaStream_t st, 
 static int set_smem_limits(int bvh_depth) {
     static int configured_depth = -1;
     if (bvh_depth <= configured_depth) return B2_OK;
-    const size_t sb_t = stack_bytes(TRAV_THREADS, bvh_depth), sb_c = stack_bytes(CONN_THREADS, bvh_depth);
-    if (sb_c + sizeof(uint32_t) * CONN_QCAP + sizeof(float) * 3 * CONN_THREADS + 64 > 227 * 1024) {
+    const size_t sb_t = stack_bytes(EXT_THREADS, bvh_depth), sb_c = stack_bytes(CONN_THREADS, bvh_depth);
+    if (sb_c + sizeof(uint32_t) * CONN_WARPS * CONN_RING + sizeof(float) * 3 * CONN_THREADS + 64 > 227 * 1024) {
         b2_set_error("BVH depth %d needs more shared memory for traversal stacks than a CTA has", bvh_depth); return B2_ERR_STATE;
     }
     B2_CUDA(cudaFuncSetAttribute(k_light_paths<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_t));
     B2_CUDA(cudaFuncSetAttribute(k_light_paths<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_t));
-    B2_CUDA(cudaFuncSetAttribute(k_closest<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_t));
-    B2_CUDA(cudaFuncSetAttribute(k_closest<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_t));
+    B2_CUDA(cudaFuncSetAttribute(k_extend<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_t));
+    B2_CUDA(cudaFuncSetAttribute(k_extend<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_t));
+    B2_CUDA(cudaFuncSetAttribute(k_extend<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_t));
+    B2_CUDA(cudaFuncSetAttribute(k_extend<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_t));
     B2_CUDA(cudaFuncSetAttribute(k_connect<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_c));
     B2_CUDA(cudaFuncSetAttribute(k_connect<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_c));
     configured_depth = bvh_depth;
@@ -342,6 +328,7 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
     long long mp = p.max_batch_paths > 0 ? p.max_batch_paths : (1ll << 22);
     mp = std::max<long long>(std::min<long long>(mp, std::max<long long>(total, 1)), 1);
     const int max_paths = (int) mp;
+    if ((long long) sc.n_lights * p.spl * p.light_depth >= (1ll << 27)) { b2_set_error("light pool larger than 2^27 vertices is not supported"); return B2_ERR_INVALID; }
     const int n_pool = sc.n_lights * p.spl * p.light_depth;
     B2_TRY(ws.ensure(max_paths, std::max(p.eye_depth, 1), std::max(n_pool, 1), film_floats));
     B2_TRY(set_smem_limits(bvh_depth));
@@ -355,47 +342,48 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
     B2_CUDA(cudaMemsetAsync(ws.film.p, 0, sizeof(float) * film_floats, st));
     B2_CUDA(cudaMemsetAsync(ws.counters.p, 0, sizeof(unsigned long long) * B2_CNT_N, st));
     B2_CUDA(cudaMemsetAsync(ws.ints.p, 0, sizeof(int) * 8, st));
-    unsigned long long eye_samples = 0;
+    unsigned long long eye_samples = 0, eye_vertices = 0;
     // run_cpu_bdpt returns before touching the film when there are no lights (cpu_bdpt.cpp:178); here the film is zero
     if (sc.n_lights > 0 && total > 0) {
         B2_TRY(build_pool(c, bvh_depth, count, st, n_launches));
         B2_CUDA(cudaEventRecord(ev1, st));
-        const size_t sb_t = stack_bytes(TRAV_THREADS, bvh_depth), sb_c = stack_bytes(CONN_THREADS, bvh_depth);
+        const size_t sb_t = stack_bytes(EXT_THREADS, bvh_depth), sb_c = stack_bytes(CONN_THREADS, bvh_depth);
         for (long long w0 = 0; w0 < total; w0 += max_paths) {
             int n_live = (int) std::min<long long>(max_paths, total - w0);
-            const int n_batch = n_live;
             c.live = ws.live_a.p; c.live_next = ws.live_b.p;
-            tm.begin(StageTimer::GEN);
-            k_eye_gen<<<blocks_for(n_live, 256), 256, 0, st>>>(c, n_live, w0);
-            tm.end();
-            n_launches++; n_batches++;
+            n_batches++;
             eye_samples += (unsigned long long) n_live;
+            B2_CUDA(cudaMemsetAsync(c.n_paths, 0, sizeof(int), st));
+            bool primary = true;
             while (n_live > 0 && p.eye_depth > 0) {
-                B2_CUDA(cudaMemsetAsync(c.n_live_next, 0, sizeof(int), st));
-                tm.begin(StageTimer::CLOSEST);
-                if (count) k_closest<true><<<blocks_for(n_live, TRAV_THREADS), TRAV_THREADS, sb_t, st>>>(c, n_live);
-                else k_closest<false><<<blocks_for(n_live, TRAV_THREADS), TRAV_THREADS, sb_t, st>>>(c, n_live);
+                B2_CUDA(cudaMemsetAsync(c.n_live_next, 0, 2 * sizeof(int), st));      // n_live_next, n_cv
+                const unsigned gb = blocks_for(n_live, EXT_THREADS);
+                tm.begin(primary ? StageTimer::PRIMARY : StageTimer::EXTEND);
+                if (primary) {
+                    if (count) k_extend<true, true><<<gb, EXT_THREADS, sb_t, st>>>(c, n_live, w0);
+                    else k_extend<true, false><<<gb, EXT_THREADS, sb_t, st>>>(c, n_live, w0);
+                } else {
+                    if (count) k_extend<false, true><<<gb, EXT_THREADS, sb_t, st>>>(c, n_live, 0);
+                    else k_extend<false, false><<<gb, EXT_THREADS, sb_t, st>>>(c, n_live, 0);
+                }
                 tm.end();
-                tm.begin(StageTimer::SHADE);
-                k_shade<<<blocks_for(n_live, SHADE_THREADS), SHADE_THREADS, 0, st>>>(c, n_live);
-                tm.end();
-                B2_CUDA(cudaMemcpyAsync(ws.h_ints, c.n_live_next, sizeof(int), cudaMemcpyDeviceToHost, st));
+                B2_CUDA(cudaMemcpyAsync(ws.h_ints, c.n_live_next, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+                // at most one eye vertex per item: the grid covers that bound, warps beyond *n_cv exit at once
+                const unsigned gc = blocks_for(n_live, CONN_THREADS);
                 tm.begin(StageTimer::CONNECT);
-                if (count) k_connect<true><<<blocks_for(n_live, CONN_THREADS), CONN_THREADS, sb_c, st>>>(c, n_live);
-                else k_connect<false><<<blocks_for(n_live, CONN_THREADS), CONN_THREADS, sb_c, st>>>(c, n_live);
+                if (count) k_connect<true><<<gc, CONN_THREADS, sb_c, st>>>(c);
+                else k_connect<false><<<gc, CONN_THREADS, sb_c, st>>>(c);
                 tm.end();
-                n_launches += 3; n_waves++;
+                n_launches += 2; n_waves++;
                 B2_CUDA(cudaStreamSynchronize(st));
                 B2_CUDA(cudaGetLastError());
                 tm.collect();
                 ws.closest_rays_host += (unsigned long long) n_live;
                 n_live = ws.h_ints[0];
+                eye_vertices += (unsigned long long) ws.h_ints[1];
                 std::swap(c.live, c.live_next);
+                primary = false;
             }
-            tm.begin(StageTimer::FLUSH);
-            k_flush<<<blocks_for(n_batch, 256), 256, 0, st>>>(c, n_batch);
-            tm.end();
-            n_launches++;
         }
     } else {
         B2_CUDA(cudaEventRecord(ev1, st));
@@ -421,10 +409,9 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
         stats->tris_tested = h_cnt[B2_CNT_TRIS];
         stats->n_batches = n_batches; stats->n_waves = n_waves; stats->n_launches = n_launches;
         stats->ms_total = ms_total; stats->ms_light_pool = ms_pool;
-        stats->pairs_tested = h_cnt[B2_CNT_PAIRS];
+        stats->pairs_tested = h_cnt[B2_CNT_PAIRS]; stats->eye_vertices = eye_vertices;
         tm.collect();
-        stats->ms_gen = tm.ms[StageTimer::GEN]; stats->ms_closest = tm.ms[StageTimer::CLOSEST]; stats->ms_shade = tm.ms[StageTimer::SHADE];
-        stats->ms_connect = tm.ms[StageTimer::CONNECT]; stats->ms_flush = tm.ms[StageTimer::FLUSH];
+        stats->ms_primary = tm.ms[StageTimer::PRIMARY]; stats->ms_extend = tm.ms[StageTimer::EXTEND]; stats->ms_connect = tm.ms[StageTimer::CONNECT];
     }
     ws.closest_rays_host = 0;
     cudaEventDestroy(ev0); cudaEventDestroy(ev1); cudaEventDestroy(ev2);

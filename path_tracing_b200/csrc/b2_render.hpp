@@ -5,11 +5,9 @@
 
 // Device buffers of the wavefront state; owned by a B2Scene and kept across calls (grown on demand).
 struct RenderWorkspace {
-    DevBuf<float4> ray_o, ray_d, thr, last_pos, last_n, acc, hist_pe, cv, pool;
+    DevBuf<float4> ray_o, ray_d, thr, last_pos, last_n, hist_pe, cv, pool, pre;
     DevBuf<float2> hist_pdf;
-    DevBuf<uint32_t> pix, sidx, pstate;
-    DevBuf<int2> hit;
-    DevBuf<int> live_a, live_b, pool_active, ints;   // ints[0] = n_pool_active, ints[1] = n_live_next
+    DevBuf<int> live_a, live_b, ints;                // ints: n_pool_active, n_live_next, n_cv, n_paths
     DevBuf<float> film;
     DevBuf<unsigned long long> counters;
     int *h_ints = nullptr;                           // pinned read-back slot

@@ -73,7 +73,7 @@ void hs_render_bdpt(void *h, const B2Camera *cam, const B2RenderParams *p, float
     HsScene *s = (HsScene *) h;
     HsRenderOut out;
     hs_render(s->view, *cam, *p, film, out);
-    if (counters) memcpy(counters, out.counters, sizeof(out.counters));
+    if (counters) { memcpy(counters, out.counters, sizeof(out.counters)); counters[B2_CNT_N] = out.pretest_mismatch; }
 }
 // pool20 layout as b2_light_pool / or_light_pool
 void hs_light_pool(void *h, const B2RenderParams *p, float *pool20) {
@@ -81,8 +81,8 @@ void hs_light_pool(void *h, const B2RenderParams *p, float *pool20) {
     B2Camera cam; memset(&cam, 0, sizeof(cam)); cam.look_at[2] = 1; cam.view_up[1] = 1; cam.fov = 50;
     B2RenderParams pp = *p; if (pp.width <= 0) pp.width = pp.height = 1;
     RenderCtx c; hs_setup_ctx(c, s->view, cam, pp);
-    std::vector<float4> pool; std::vector<int> active; unsigned long long cnt[B2_CNT_N] = { 0 };
-    hs_build_pool(c, pool, active, cnt);
+    std::vector<float4> pool, pre; unsigned long long cnt[B2_CNT_N] = { 0 };
+    hs_build_pool(c, pool, pre, cnt);
     for (int i = 0; i < c.n_pool; ++i) {
         LightVtx v = load_lv(c.pool, i);
         float *o = pool20 + 20 * i;

@@ -60,7 +60,7 @@ class HostSim:
         p = A.RenderParams(W, H, spp, spl, eye_depth, light_depth, seed, sample_offset, sample_stride, film_mode, 0, 0, max_batch_paths, 1, 0)
         film = np.zeros((H, W, 3), np.float32); cnt = np.zeros(16, np.uint64)
         self.L.hs_render_bdpt(self.h, cam.ctypes.data_as(C.c_void_p), C.byref(p), A.ptr(film), A.ptr(cnt))
-        names = ["eye_samples", "closest_rays", "shadow_rays", "path_samples", "delta_cap_hits", "nodes", "tris", "pairs"]
+        names = ["eye_samples", "closest_rays", "shadow_rays", "path_samples", "delta_cap_hits", "nodes", "tris", "pairs", "pretest_mismatch"]
         return film, {k: int(cnt[i]) for i, k in enumerate(names)}
 
     def light_pool(self, spl, light_depth, seed=1):

@@ -81,6 +81,7 @@ def test_wavefront_bodies_reproduce_the_oracle_render(name, depth):
     fh, cnt = hs.render(W, H, 3, 8, depth, depth, seed=5, max_batch_paths=500)    # several batches
     assert cnt["eye_samples"] == st.eye_samples == W * H * 3
     assert cnt["closest_rays"] == st.closest_rays and cnt["shadow_rays"] == st.shadow_rays and cnt["path_samples"] == st.path_samples
+    assert cnt["pretest_mismatch"] <= 1e-5 * cnt["pairs"]     # division-free record pre-test == the reference-order pre-test
     assert np.allclose(fh, fo, rtol=1e-4, atol=1e-6)
     # sample sharding: two shards (s = 0,2 and s = 1) summed == the whole film
     a, _ = hs.render(W, H, 3, 8, depth, depth, seed=5, sample_offset=0, sample_stride=2, film_mode=1)
