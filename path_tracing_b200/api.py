@@ -109,8 +109,8 @@ class Scene:
             A.check(A.lib().b2_render_bdpt_device(self._h, cam.ctypes.data_as(C.c_void_p), C.byref(p), C.c_void_p(int(device_ptr)),
                                                   C.c_void_p(stream) if stream else None, C.byref(st)))
             return None, st.as_dict()
-        film = out if out is not None else np.zeros((H, W, 3), np.float32)
-        assert film.dtype == np.float32 and film.size == 3 * W * H and film.flags["C_CONTIGUOUS"]
+        film = out if out is not None else np.zeros((max(H, 0), max(W, 0), 3), np.float32)
+        assert film.dtype == np.float32 and film.size == 3 * max(W, 0) * max(H, 0) and film.flags["C_CONTIGUOUS"]
         A.check(A.lib().b2_render_bdpt(self._h, cam.ctypes.data_as(C.c_void_p), C.byref(p), A.ptr(film), C.byref(st)))
         return film, st.as_dict()
 

@@ -103,11 +103,13 @@ B2_HD float bsdf_pdf_local(const Mat &m, float3 wo, float3 wi) {        // :464-
     float sw = m.metallic > 0.0f ? 1.0f : 0.5f;
     return (1.0f - sw) * pdf_diffuse + sw * pdf_spec;
 }
-B2_HD float3 bsdf_evaluate(const Mat &m, float3 wo_w, float3 wi_w, float3 N) {
+// The world-space entry points are deliberately NOT inlined on the device: the connect stage calls each of them twice
+// per pair, and inlining every copy made the kernel miss in the instruction cache (ncu: 41 % stall_no_inst).
+B2_NOINLINE float3 bsdf_evaluate(const Mat &m, float3 wo_w, float3 wi_w, float3 N) {
     Frame f = make_frame(N);
     return bsdf_eval_local(m, to_local(f, wo_w), to_local(f, wi_w));
 }
-B2_HD float bsdf_pdf(const Mat &m, float3 wo_w, float3 wi_w, float3 N) {
+B2_NOINLINE float bsdf_pdf(const Mat &m, float3 wo_w, float3 wi_w, float3 N) {
     Frame f = make_frame(N);
     return bsdf_pdf_local(m, to_local(f, wo_w), to_local(f, wi_w));
 }

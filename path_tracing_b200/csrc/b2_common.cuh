@@ -15,9 +15,11 @@
 #if defined(__CUDACC__)
 #define B2_HD __host__ __device__ __forceinline__
 #define B2_D __device__ __forceinline__
+#define B2_NOINLINE static __host__ __device__ __noinline__
 #else
 #define B2_HD inline
 #define B2_D inline
+#define B2_NOINLINE static inline
 #endif
 
 #define B2_EPSILON 1e-4f                 // geometric.cuh:6

@@ -25,6 +25,8 @@ namespace {
 constexpr int EXT_THREADS = 128;      // extend kernel block
 constexpr int CONN_THREADS = 128;     // connect kernel block: 4 independent warps
 constexpr int CONN_WARPS = CONN_THREADS / 32;
+constexpr int CONN_BLOCKS_PER_SM = 4; // persistent grid = 148 SMs x this
+constexpr int CONN_MIN_SLICE = 8;     // smallest pool slice a connect work item may get (late, nearly empty waves)
 constexpr int CONN_GROUP = 4;         // pool vertices pre-tested between two drain checks
 constexpr int CONN_RING = 256;        // per-warp ring capacity (power of two) >= 31 pending + CONN_GROUP * 32 new entries
 
@@ -117,72 +119,84 @@ __global__ void __launch_bounds__(EXT_THREADS) k_extend(RenderCtx c, int n_items
     if (COUNT) { warp_count_add(&c.counters[B2_CNT_NODES], tc.nodes); warp_count_add(&c.counters[B2_CNT_TRIS], tc.tris); }
 }
 
-// Connection stage: one warp per 32 eye-vertex records, no block-level synchronisation.
+// Connection stage.  Work item = (group of 32 eye-vertex records) x (slice of the active pool); persistent warps
+// pull items grid-stride.  The pool is sliced only when there are too few eye vertices to fill the machine (late
+// waves), so that the serial latency of a nearly empty wave stays short.  No block-level synchronisation.
 template <bool COUNT>
 __global__ void __launch_bounds__(CONN_THREADS) k_connect(RenderCtx c) {
     extern __shared__ uint2 s_stack[];                    // CONN_THREADS x stack depth
     __shared__ uint32_t s_ring[CONN_WARPS][CONN_RING];
     __shared__ float s_acc[CONN_WARPS][3][32];
-    const int n_cv = *c.n_cv;
+    const int n_cv = *c.n_cv, n_act = *c.n_pool_active;
+    if (n_cv <= 0 || n_act <= 0) return;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int q0 = (blockIdx.x * CONN_WARPS + warp) * 32;
-    if (q0 >= n_cv) return;                               // whole warp out of range (grid is sized for the upper bound)
-    const int q = q0 + lane;
-    const bool valid = q < n_cv;
-    float3 my_pos = mk3(0, 0, 0), my_n = mk3(0, 0, 0);
-    if (valid) { my_pos = mk3(c.cv[B2_CV_F4 * q]); my_n = mk3(c.cv[B2_CV_F4 * q + 1]); }
+    const int n_groups = (n_cv + 31) >> 5;
+    const int total_warps = gridDim.x * CONN_WARPS;
+    const int n_slices = max(1, min(total_warps / n_groups, (n_act + CONN_MIN_SLICE - 1) / CONN_MIN_SLICE));
+    const long long n_items = (long long) n_groups * n_slices;
     uint32_t *ring = s_ring[warp];
     float *acc_x = s_acc[warp][0], *acc_y = s_acc[warp][1], *acc_z = s_acc[warp][2];
-    acc_x[lane] = 0.0f; acc_y[lane] = 0.0f; acc_z[lane] = 0.0f;
-    __syncwarp();
-    const int n_act = *c.n_pool_active;
-    uint32_t head = 0u, tail = 0u;                        // warp-uniform ring cursors (registers)
+    const float4 *__restrict__ pre = c.pre;
     uint32_t n_shadow = 0, n_path = 0;
+    unsigned long long n_pairs = 0;
     TravCounters tc{ 0u, 0u };
 
-    auto drain = [&](uint32_t count) {                    // finish `count` <= 32 entries starting at head
-        if ((uint32_t) lane < count) {
-            const uint32_t e = ring[(head + (uint32_t) lane) % CONN_RING];
-            const int owner = (int) (e >> 27), lvi = (int) (e & 0x7ffffffu);
-            const EyeVtx ev = load_cv(c.cv, q0 + owner);
-            const float3 r = connect_finish<COUNT>(c, ev, lvi, s_stack + threadIdx.x, CONN_THREADS, &tc, n_shadow, n_path);
-            if (r.x != 0.0f) atomicAdd(&acc_x[owner], r.x);
-            if (r.y != 0.0f) atomicAdd(&acc_y[owner], r.y);
-            if (r.z != 0.0f) atomicAdd(&acc_z[owner], r.z);
-        }
-        head += count;
+    for (long long item = (long long) blockIdx.x * CONN_WARPS + warp; item < n_items; item += total_warps) {
+        const int group = (int) (item / n_slices), slice = (int) (item % n_slices);
+        const int a_begin = (int) ((long long) slice * n_act / n_slices), a_end = (int) ((long long) (slice + 1) * n_act / n_slices);
+        const int q0 = group << 5, q = q0 + lane;
+        const bool valid = q < n_cv;
+        float3 my_pos = mk3(0, 0, 0), my_n = mk3(0, 0, 0);
+        uint32_t my_pixel = 0u;
+        if (valid) { const float4 f0 = c.cv[B2_CV_F4 * q]; my_pos = mk3(f0); my_pixel = __float_as_uint(f0.w) >> 8; my_n = mk3(c.cv[B2_CV_F4 * q + 1]); }
+        acc_x[lane] = 0.0f; acc_y[lane] = 0.0f; acc_z[lane] = 0.0f;
         __syncwarp();
-    };
+        uint32_t head = 0u, tail = 0u;                    // warp-uniform ring cursors (registers)
 
-    const float4 *__restrict__ pre = c.pre;
-    for (int a0 = 0; a0 < n_act; a0 += CONN_GROUP) {
-        // pre-test a group of pool vertices (independent broadcast loads, so they pipeline), compacting survivors
-#pragma unroll
-        for (int k = 0; k < CONN_GROUP; ++k) {
-            const int a = a0 + k;
-            if (a < n_act) {
-                const float4 r0 = __ldg(&pre[B2_PRE_F4 * a]), r1 = __ldg(&pre[B2_PRE_F4 * a + 1]), r2 = __ldg(&pre[B2_PRE_F4 * a + 2]);
-                const bool pass = valid && pretest_rec(my_pos, my_n, r0, r1, r2);
-                const uint32_t m = __ballot_sync(0xffffffffu, pass);
-                if (pass) ring[(tail + (uint32_t) __popc(m & lanemask_lt())) % CONN_RING] = ((uint32_t) lane << 27) | __float_as_uint(r1.w);
-                tail += (uint32_t) __popc(m);
+        auto drain = [&](uint32_t count) {                // finish `count` <= 32 entries starting at head
+            if ((uint32_t) lane < count) {
+                const uint32_t e = ring[(head + (uint32_t) lane) % CONN_RING];
+                const int owner = (int) (e >> 27), lvi = (int) (e & 0x7ffffffu);
+                const EyeVtx ev = load_cv(c.cv, q0 + owner);
+                const float3 r = connect_finish<COUNT>(c, ev, lvi, s_stack + threadIdx.x, CONN_THREADS, &tc, n_shadow, n_path);
+                if (r.x != 0.0f) atomicAdd(&acc_x[owner], r.x);
+                if (r.y != 0.0f) atomicAdd(&acc_y[owner], r.y);
+                if (r.z != 0.0f) atomicAdd(&acc_z[owner], r.z);
             }
+            head += count;
+            __syncwarp();
+        };
+
+        for (int a0 = a_begin; a0 < a_end; a0 += CONN_GROUP) {
+            // pre-test a group of pool vertices (independent broadcast loads, so they pipeline), compacting survivors
+#pragma unroll
+            for (int k = 0; k < CONN_GROUP; ++k) {
+                const int a = a0 + k;
+                if (a < a_end) {
+                    const float4 r0 = __ldg(&pre[B2_PRE_F4 * a]), r1 = __ldg(&pre[B2_PRE_F4 * a + 1]), r2 = __ldg(&pre[B2_PRE_F4 * a + 2]);
+                    const bool pass = valid && pretest_rec(my_pos, my_n, r0, r1, r2);
+                    const uint32_t m = __ballot_sync(0xffffffffu, pass);
+                    if (pass) ring[(tail + (uint32_t) __popc(m & lanemask_lt())) % CONN_RING] = ((uint32_t) lane << 27) | __float_as_uint(r1.w);
+                    tail += (uint32_t) __popc(m);
+                }
+            }
+            __syncwarp();
+            // finish surviving pairs 32 at a time; after the last group also the remainder
+            const uint32_t need = (a0 + CONN_GROUP >= a_end) ? 1u : 32u;
+            while (tail - head >= need) drain(min(32u, tail - head));
         }
+        if (valid) {
+            const float3 r = mk3(acc_x[lane], acc_y[lane], acc_z[lane]);
+            if (r.x != 0.0f) atomicAdd(&c.film[3 * my_pixel], r.x);
+            if (r.y != 0.0f) atomicAdd(&c.film[3 * my_pixel + 1], r.y);
+            if (r.z != 0.0f) atomicAdd(&c.film[3 * my_pixel + 2], r.z);
+        }
+        n_pairs += (unsigned long long) (a_end - a_begin) * (unsigned long long) min(32, n_cv - q0);
         __syncwarp();
-        // finish surviving pairs 32 at a time; after the last group also the remainder
-        const uint32_t need = (a0 + CONN_GROUP >= n_act) ? 1u : 32u;
-        while (tail - head >= need) drain(min(32u, tail - head));
-    }
-    if (valid) {
-        const float3 r = mk3(acc_x[lane], acc_y[lane], acc_z[lane]);
-        const uint32_t pixel = __float_as_uint(c.cv[B2_CV_F4 * q].w) >> 8;
-        if (r.x != 0.0f) atomicAdd(&c.film[3 * pixel], r.x);
-        if (r.y != 0.0f) atomicAdd(&c.film[3 * pixel + 1], r.y);
-        if (r.z != 0.0f) atomicAdd(&c.film[3 * pixel + 2], r.z);
     }
     warp_count_add(&c.counters[B2_CNT_SHADOW], n_shadow);
     warp_count_add(&c.counters[B2_CNT_PATH_SAMPLES], n_path);
-    if (lane == 0) atomicAdd(&c.counters[B2_CNT_PAIRS], (unsigned long long) n_act * (unsigned long long) min(32, n_cv - q0));
+    if (lane == 0 && n_pairs) atomicAdd(&c.counters[B2_CNT_PAIRS], n_pairs);
     if (COUNT) { warp_count_add(&c.counters[B2_CNT_NODES], tc.nodes); warp_count_add(&c.counters[B2_CNT_TRIS], tc.tris); }
 }
 
@@ -325,7 +339,7 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
     int n_my = 0;
     for (long long s = p.sample_offset; s < p.spp; s += stride) n_my++;
     const long long total = (long long) npix * n_my;
-    long long mp = p.max_batch_paths > 0 ? p.max_batch_paths : (1ll << 22);
+    long long mp = p.max_batch_paths > 0 ? p.max_batch_paths : (1ll << 24);   // 2^24 samples in flight: ~6 GB of wavefront state at depth 8
     mp = std::max<long long>(std::min<long long>(mp, std::max<long long>(total, 1)), 1);
     const int max_paths = (int) mp;
     if ((long long) sc.n_lights * p.spl * p.light_depth >= (1ll << 27)) { b2_set_error("light pool larger than 2^27 vertices is not supported"); return B2_ERR_INVALID; }
@@ -368,8 +382,8 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
                 }
                 tm.end();
                 B2_CUDA(cudaMemcpyAsync(ws.h_ints, c.n_live_next, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
-                // at most one eye vertex per item: the grid covers that bound, warps beyond *n_cv exit at once
-                const unsigned gc = blocks_for(n_live, CONN_THREADS);
+                // persistent warps: one CTA wave over the 148 SMs (grid-stride over the work items computed on the device)
+                const unsigned gc = (unsigned) std::min<long long>(148ll * CONN_BLOCKS_PER_SM, std::max<long long>(1, ((long long) n_live * 8 + CONN_THREADS - 1) / CONN_THREADS));
                 tm.begin(StageTimer::CONNECT);
                 if (count) k_connect<true><<<gc, CONN_THREADS, sb_c, st>>>(c);
                 else k_connect<false><<<gc, CONN_THREADS, sb_c, st>>>(c);
