@@ -126,7 +126,7 @@ def cpu_arm(steps, warmup, sample=CPU_SAMPLE):
 def gpu_arm(args):
     import torch
     import torch.distributed as dist
-    from path_tracing_b200 import api
+    from path_tracing_b200 import api, multi
     from path_tracing_b200.scene import reference_scene
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
     if world > 1:
@@ -152,9 +152,7 @@ def gpu_arm(args):
     def step(profile=False, count=False):
         _, st = sc.render_bdpt(device_ptr=film.data_ptr(), stream=stream, profile_stages=profile, count_traversal=count, **kw)
         if world > 1:
-            dist.reduce(film, dst=0, op=dist.ReduceOp.SUM)           # one NCCL reduce of the raw-sum films over NVLink
-            if rank == 0:
-                film.mul_(1.0 / spp_total)
+            multi.reduce_film(film, spp_total, dst=0)                # one NCCL reduce of the raw-sum films over NVLink, mean on rank 0
         return st
 
     def barrier():

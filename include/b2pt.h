@@ -11,6 +11,7 @@
  *   b2_render_bdpt                        <- run_cuda_bdpt(cam, image, ...)                include/bdpt_cu_helper.h:6
  *                                            and run_cpu_bdpt(camera, groups, lights, ...) include/cpu_bdpt.h:9-17
  *                                            (the estimator reproduced is the CPU one, src/cpu_bdpt.cpp:173-488)
+ *   b2_render_bdpt_multi                  <- (none: the reference is single-GPU) spp sharding + NCCL film reduce
  *   b2_intersect (closest)                <- cpu_find_closest_hit                          src/cpu_bdpt.cpp:30-80
  *   b2_intersect (any)                    <- cpu_check_visibility                          src/cpu_bdpt.cpp:82-107
  *   b2_bsdf_evaluate / _pdf / _sample     <- bsdf_evaluate / bsdf_pdf / bsdf_sample        include/geometric.cuh:419-562
@@ -135,6 +136,11 @@ int b2_render_bdpt(B2Scene *scene, const B2Camera *cam, const B2RenderParams *pa
  * and the call returns after the stream has drained its own work (stats need the counters). */
 int b2_render_bdpt_device(B2Scene *scene, const B2Camera *cam, const B2RenderParams *params, float *d_film_rgb,
                           void *stream, B2Stats *stats);
+/* One node, n_gpus devices, ONE process: scenes[g] is the same scene created on device g (b2_scene_create(..., device g)).
+ * GPU g renders sample indices s = g (mod n_gpus); the raw-sum films are summed onto scenes[0]'s device with one NCCL
+ * reduce (NCCL is dlopen'ed on first use) and resolved per params->film_mode.  stats: counters summed, ms_total = max. */
+int b2_render_bdpt_multi(B2Scene **scenes, int n_gpus, const B2Camera *cam, const B2RenderParams *params,
+                         float *film_rgb_host, B2Stats *stats);
 /* The light-vertex pool the render would use: n_lights*spl*light_depth vertices x 20 floats
  * (pos3 normal3 thr3 mtl6 is_light_source is_parallel source_cutoff pdf_fwd pdf_rev), cpu_bdpt.cpp:202-325. */
 int b2_light_pool(B2Scene *scene, const B2RenderParams *params, float *pool20_host);

@@ -122,6 +122,20 @@ class Scene:
         return out
 
 
+def render_bdpt_multi(scenes, camera=None, width=None, height=None, spp=8, spl=8, eye_depth=4, light_depth=4, seed=1,
+                      film_mode=FILM_MEAN, max_batch_paths=0):
+    """One process, len(scenes) GPUs (b2_render_bdpt_multi): scenes[g] is the same SceneData created on device g."""
+    s0 = scenes[0]
+    cam = np.ascontiguousarray(s0.data.camera if camera is None else camera, dtype=A.Camera).reshape(())
+    W = int(width if width else s0.data.width); H = int(height if height else s0.data.height)
+    p = s0._params(W, H, spp, spl, eye_depth, light_depth, seed, 0, 1, film_mode, 0, max_batch_paths, False)
+    st = A.Stats()
+    film = np.zeros((max(H, 0), max(W, 0), 3), np.float32)
+    handles = (C.c_void_p * len(scenes))(*[s._h for s in scenes])
+    A.check(A.lib().b2_render_bdpt_multi(handles, len(scenes), cam.ctypes.data_as(C.c_void_p), C.byref(p), A.ptr(film), C.byref(st)))
+    return film, st.as_dict()
+
+
 # ---- BSDF / MIS / RNG tables (device kernels over host arrays) ----
 def bsdf_evaluate(mtl, wo, wi, N):
     mtl, wo, wi, N = _f32(mtl, (-1, 6)), _f32(wo, (-1, 3)), _f32(wi, (-1, 3)), _f32(N, (-1, 3))

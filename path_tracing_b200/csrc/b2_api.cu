@@ -9,6 +9,7 @@
 #include "b2_host_scene.hpp"
 #include "b2_queries.hpp"
 #include "b2_render.hpp"
+#include "b2_scene_handle.hpp"
 
 static thread_local char g_err[512] = "";
 void b2_set_error(const char *fmt, ...) {
@@ -16,28 +17,6 @@ void b2_set_error(const char *fmt, ...) {
     vsnprintf(g_err, sizeof(g_err), fmt, ap);
     va_end(ap);
 }
-
-struct B2Scene {
-    int device = 0;
-    HostScene hs;
-    DevBuf<BuildTri> d_in;
-    DevBuf<float4> sph, lights, mats, groups;
-    DeviceBvh bvh;
-    bool built = false;
-    int max_leaf = 3;
-    cudaStream_t stream = nullptr;
-    DevBuf<unsigned long long> isect_counters;
-    RenderWorkspace ws;
-    std::mutex mtx;                       // one call in flight per handle
-    DevScene view() const {
-        DevScene v; memset(&v, 0, sizeof(v));
-        v.tri = bvh.tri.p; v.tri_obj = bvh.tri_obj.p; v.nodes = bvh.nodes.p;
-        v.sph = sph.p; v.lights = lights.p; v.mats = mats.p; v.groups = groups.p;
-        v.n_tris = bvh.n_tris; v.n_nodes = bvh.n_nodes; v.n_sph = hs.n_sph; v.n_lights = hs.n_lights; v.n_mats = hs.n_mats; v.n_groups = hs.n_groups;
-        v.scene_min = hs.scene_min; v.scene_max = hs.scene_max;
-        return v;
-    }
-};
 
 static int need_device(int device) {
     int n = 0;
@@ -127,21 +106,21 @@ int b2_scene_bvh_info(const B2Scene *s, B2BvhInfo *info) {
     return B2_OK;
 }
 
-static int check_built(B2Scene *s) {
+int b2_check_built(B2Scene *s) {
     if (!s) { b2_set_error("scene is NULL"); return B2_ERR_INVALID; }
     if (!s->built) { b2_set_error("BVH not built: call b2_scene_build_bvh first"); return B2_ERR_STATE; }
     return B2_OK;
 }
 
 int b2_intersect_device(B2Scene *s, const float *d_org, const float *d_dir, size_t n, int mode, int32_t *d_prim_id, float *d_t, void *stream) {
-    B2_TRY(check_built(s));
+    B2_TRY(b2_check_built(s));
     if (n && (!d_org || !d_dir || !d_prim_id)) { b2_set_error("NULL ray / result buffer"); return B2_ERR_INVALID; }
     B2_CUDA(cudaSetDevice(s->device));
     return b2_intersect_launch(s->view(), s->bvh.depth, d_org, d_dir, n, mode, d_prim_id, d_t, s->isect_counters.p, (cudaStream_t) stream);
 }
 
 int b2_intersect(B2Scene *s, const float *org, const float *dir, size_t n, int mode, int32_t *prim_id, float *t) {
-    B2_TRY(check_built(s));
+    B2_TRY(b2_check_built(s));
     if (n == 0) return B2_OK;
     if (!org || !dir || !prim_id) { b2_set_error("NULL ray / result buffer"); return B2_ERR_INVALID; }
     std::lock_guard<std::mutex> lk(s->mtx);
@@ -171,7 +150,7 @@ int b2_intersect_counters(B2Scene *s, uint64_t out[3], int reset) {
 }
 
 int b2_render_bdpt_device(B2Scene *s, const B2Camera *cam, const B2RenderParams *params, float *d_film_rgb, void *stream, B2Stats *stats) {
-    B2_TRY(check_built(s));
+    B2_TRY(b2_check_built(s));
     if (!cam || !params || !d_film_rgb) { b2_set_error("NULL argument"); return B2_ERR_INVALID; }
     std::lock_guard<std::mutex> lk(s->mtx);
     B2_CUDA(cudaSetDevice(s->device));
@@ -179,7 +158,7 @@ int b2_render_bdpt_device(B2Scene *s, const B2Camera *cam, const B2RenderParams 
 }
 
 int b2_render_bdpt(B2Scene *s, const B2Camera *cam, const B2RenderParams *params, float *film_rgb_host, B2Stats *stats) {
-    B2_TRY(check_built(s));
+    B2_TRY(b2_check_built(s));
     if (!cam || !params || !film_rgb_host) { b2_set_error("NULL argument"); return B2_ERR_INVALID; }
     if (params->width <= 0 || params->height <= 0) { b2_set_error("invalid film size"); return B2_ERR_INVALID; }
     std::lock_guard<std::mutex> lk(s->mtx);
@@ -194,7 +173,7 @@ int b2_render_bdpt(B2Scene *s, const B2Camera *cam, const B2RenderParams *params
 }
 
 int b2_light_pool(B2Scene *s, const B2RenderParams *params, float *pool20_host) {
-    B2_TRY(check_built(s));
+    B2_TRY(b2_check_built(s));
     if (!params || !pool20_host) { b2_set_error("NULL argument"); return B2_ERR_INVALID; }
     std::lock_guard<std::mutex> lk(s->mtx);
     B2_CUDA(cudaSetDevice(s->device));

@@ -1,0 +1,113 @@
+// b2_multi.cu -- b2_render_bdpt_multi: one node, G GPUs, one host thread per GPU inside ONE process (C++ callers such
+// as pt_cli --gpus G).  Scene, BVH and light pool are replicated (one B2Scene per device, same inputs -> identical
+// deterministic builds and identical Philox streams); GPU g renders the sample indices s = g (mod G) of every pixel
+// into a raw-sum film; the films are summed onto GPU 0 with one NCCL reduce over NVLink and resolved there.
+// NCCL is loaded with dlopen at the first multi-GPU call, so single-GPU users of libb2pt.so need no NCCL at all.
+// (Python callers run one process per GPU under torchrun and use torch.distributed instead: path_tracing_b200/multi.py.)
+#include <dlfcn.h>
+#include <thread>
+#include <vector>
+#include "b2_scene_handle.hpp"
+
+namespace {
+
+// minimal NCCL surface (ABI-stable since NCCL 2.x): opaque communicator, enums as ints
+typedef struct ncclComm *ncclComm_t;
+enum { kNcclSuccess = 0, kNcclFloat32 = 7, kNcclSum = 0 };
+struct Nccl {
+    void *h = nullptr;
+    int (*CommInitAll)(ncclComm_t *, int, const int *) = nullptr;
+    int (*CommDestroy)(ncclComm_t) = nullptr;
+    int (*Reduce)(const void *, void *, size_t, int, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    const char *(*GetErrorString)(int) = nullptr;
+    bool load() {
+        if (h) return true;
+        for (const char *n : { "libnccl.so.2", "libnccl.so" }) { h = dlopen(n, RTLD_NOW | RTLD_GLOBAL); if (h) break; }
+        if (!h) return false;
+        CommInitAll = (decltype(CommInitAll)) dlsym(h, "ncclCommInitAll");
+        CommDestroy = (decltype(CommDestroy)) dlsym(h, "ncclCommDestroy");
+        Reduce = (decltype(Reduce)) dlsym(h, "ncclReduce");
+        GroupStart = (decltype(GroupStart)) dlsym(h, "ncclGroupStart");
+        GroupEnd = (decltype(GroupEnd)) dlsym(h, "ncclGroupEnd");
+        GetErrorString = (decltype(GetErrorString)) dlsym(h, "ncclGetErrorString");
+        return CommInitAll && CommDestroy && Reduce && GroupStart && GroupEnd;
+    }
+};
+Nccl g_nccl;
+
+__global__ void k_scale(float *film, size_t n, float inv) {
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) film[i] *= inv;
+}
+
+}  // namespace
+
+extern "C" int b2_render_bdpt_multi(B2Scene **scenes, int n_gpus, const B2Camera *cam, const B2RenderParams *params, float *film_rgb_host, B2Stats *stats) {
+    if (!scenes || n_gpus <= 0 || !cam || !params || !film_rgb_host) { b2_set_error("NULL / invalid argument"); return B2_ERR_INVALID; }
+    for (int g = 0; g < n_gpus; ++g) {
+        B2_TRY(b2_check_built(scenes[g]));
+        for (int k = 0; k < g; ++k) if (scenes[k]->device == scenes[g]->device) { b2_set_error("two scene handles on device %d", scenes[g]->device); return B2_ERR_INVALID; }
+    }
+    if (params->width <= 0 || params->height <= 0 || params->spp <= 0) { b2_set_error("invalid film size / spp"); return B2_ERR_INVALID; }
+    if (n_gpus == 1) return b2_render_bdpt(scenes[0], cam, params, film_rgb_host, stats);
+    if (!g_nccl.load()) { b2_set_error("multi-GPU render needs NCCL (libnccl.so.2 could not be loaded: %s)", dlerror()); return B2_ERR_STATE; }
+    const size_t nf = (size_t) 3 * params->width * params->height;
+    std::vector<int> devs(n_gpus);
+    for (int g = 0; g < n_gpus; ++g) devs[g] = scenes[g]->device;
+    std::vector<ncclComm_t> comms(n_gpus, nullptr);
+    int nrc = g_nccl.CommInitAll(comms.data(), n_gpus, devs.data());
+    if (nrc != kNcclSuccess) { b2_set_error("ncclCommInitAll failed: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(nrc) : "?"); return B2_ERR_CUDA; }
+    std::vector<float *> d_film(n_gpus, nullptr);
+    std::vector<int> rc(n_gpus, B2_OK);
+    std::vector<std::string> err(n_gpus);
+    std::vector<B2Stats> st(n_gpus);
+    // phase 1: every GPU renders its shard (threads: the wave loop blocks on its own stream)
+    std::vector<std::thread> th;
+    for (int g = 0; g < n_gpus; ++g)
+        th.emplace_back([&, g]() {
+            B2Scene *s = scenes[g];
+            std::lock_guard<std::mutex> lk(s->mtx);
+            if (cudaSetDevice(s->device) != cudaSuccess || cudaMalloc((void **) &d_film[g], nf * sizeof(float)) != cudaSuccess) { rc[g] = B2_ERR_OOM; err[g] = "cudaMalloc(film) failed"; return; }
+            B2RenderParams p = *params;
+            const int stride = p.sample_stride > 0 ? p.sample_stride : 1;
+            p.sample_offset = params->sample_offset + g * stride; p.sample_stride = stride * n_gpus; p.film_mode = B2_FILM_SUM;
+            rc[g] = b2_render_device_impl(s->view(), s->bvh.depth, s->ws, *cam, p, d_film[g], s->stream, &st[g]);
+            if (rc[g] != B2_OK) err[g] = b2_last_error();
+        });
+    for (auto &t : th) t.join();
+    int bad = B2_OK;
+    for (int g = 0; g < n_gpus; ++g) if (rc[g] != B2_OK) { bad = rc[g]; b2_set_error("GPU %d: %s", devs[g], err[g].c_str()); break; }
+    // phase 2: one reduce of the raw-sum films onto GPU 0 (NVLink / NVSwitch), resolve, read back
+    if (bad == B2_OK) {
+        g_nccl.GroupStart();
+        for (int g = 0; g < n_gpus; ++g) {
+            cudaSetDevice(devs[g]);
+            nrc = g_nccl.Reduce(d_film[g], d_film[g], nf, kNcclFloat32, kNcclSum, 0, comms[g], scenes[g]->stream);
+            if (nrc != kNcclSuccess) break;
+        }
+        const int nrc2 = g_nccl.GroupEnd();
+        if (nrc != kNcclSuccess || nrc2 != kNcclSuccess) { b2_set_error("ncclReduce failed: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(nrc != kNcclSuccess ? nrc : nrc2) : "?"); bad = B2_ERR_CUDA; }
+    }
+    if (bad == B2_OK) {
+        for (int g = 1; g < n_gpus; ++g) { cudaSetDevice(devs[g]); cudaStreamSynchronize(scenes[g]->stream); }
+        cudaSetDevice(devs[0]);
+        if (params->film_mode != B2_FILM_SUM) k_scale<<<blocks_for(nf, 256), 256, 0, scenes[0]->stream>>>(d_film[0], nf, 1.0f / (float) params->spp);
+        cudaError_t e = cudaMemcpyAsync(film_rgb_host, d_film[0], nf * sizeof(float), cudaMemcpyDeviceToHost, scenes[0]->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(scenes[0]->stream);
+        if (e != cudaSuccess) { b2_set_error("film read-back failed: %s", cudaGetErrorString(e)); bad = B2_ERR_CUDA; }
+    }
+    for (int g = 0; g < n_gpus; ++g) { cudaSetDevice(devs[g]); if (d_film[g]) cudaFree(d_film[g]); if (comms[g]) g_nccl.CommDestroy(comms[g]); }
+    if (stats && bad == B2_OK) {
+        *stats = st[0];
+        for (int g = 1; g < n_gpus; ++g) {
+            stats->eye_samples += st[g].eye_samples; stats->closest_rays += st[g].closest_rays; stats->shadow_rays += st[g].shadow_rays;
+            stats->path_samples += st[g].path_samples; stats->delta_cap_hits += st[g].delta_cap_hits; stats->nodes_visited += st[g].nodes_visited;
+            stats->tris_tested += st[g].tris_tested; stats->n_launches += st[g].n_launches; stats->pairs_tested += st[g].pairs_tested;
+            stats->eye_vertices += st[g].eye_vertices; stats->n_waves += st[g].n_waves; stats->n_batches += st[g].n_batches;
+            if (st[g].ms_total > stats->ms_total) stats->ms_total = st[g].ms_total;       // device time = max over GPUs
+        }
+    }
+    return bad;
+}

@@ -312,8 +312,10 @@ static int build_pool(RenderCtx &c, int bvh_depth, bool count, cudaStream_t st, 
 }
 
 static int set_smem_limits(int bvh_depth) {
-    static int configured_depth = -1;
-    if (bvh_depth <= configured_depth) return B2_OK;
+    static int configured[64];                 // per device: bvh_depth + 1 already configured (0 = never)
+    int dev = 0;
+    B2_CUDA(cudaGetDevice(&dev));
+    if (dev < 64 && bvh_depth + 1 <= configured[dev]) return B2_OK;
     const size_t sb_t = stack_bytes(EXT_THREADS, bvh_depth), sb_c = stack_bytes(CONN_THREADS, bvh_depth);
     if (sb_c + sizeof(uint32_t) * CONN_WARPS * CONN_RING + sizeof(float) * 3 * CONN_THREADS + 64 > 227 * 1024) {
         b2_set_error("BVH depth %d needs more shared memory for traversal stacks than a CTA has", bvh_depth); return B2_ERR_STATE;
@@ -326,7 +328,7 @@ static int set_smem_limits(int bvh_depth) {
     B2_CUDA(cudaFuncSetAttribute(k_extend<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_t));
     B2_CUDA(cudaFuncSetAttribute(k_connect<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_c));
     B2_CUDA(cudaFuncSetAttribute(k_connect<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_c));
-    configured_depth = bvh_depth;
+    if (dev < 64) configured[dev] = bvh_depth + 1;
     return B2_OK;
 }
 

@@ -247,3 +247,48 @@ def test_invalid_arguments_fail_with_messages():
     with pytest.raises(A.B2Error, match="material index"):
         api.Scene(bad)
     sc.close()
+
+
+def test_pt_cli_renders_the_reference_scene(tmp_path):
+    """The main_cli-equivalent driver: reference flags, scene text in, PNG out; image == the library's own tonemapped film."""
+    import subprocess
+    import __graft_entry__ as g
+    sd = reference_scene("cornell")
+    scene_txt = tmp_path / "scene.txt"; out_png = tmp_path / "o.ppm"
+    sd.write_text(scene_txt)
+    r = subprocess.run([g.CLI, "--input", str(scene_txt), "--output", str(out_png), "--mode", "bdpt", "--device", "gpu", "--spp", "4", "--spl", "4",
+                        "--width", "64", "--height", "48"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "[Success] Image saved!" in r.stdout
+    b = open(out_png, "rb").read()
+    hdr = b"P6\n64 48\n255\n"
+    assert b.startswith(hdr)
+    img = np.frombuffer(b[len(hdr):], np.uint8).reshape(48, 64, 3)
+    sc = api.Scene(sd)
+    film, _ = sc.render_bdpt(width=64, height=48, spp=4, spl=4, eye_depth=4, light_depth=4, seed=1)
+    want = api.film_to_rgb8(film)
+    assert (np.abs(img.astype(int) - want.astype(int)) <= 1).mean() > 0.999      # atomics: last-bit film differences only
+    for bad in (["--mode", "pt"], ["--device", "cpu"]):
+        r = subprocess.run([g.CLI, "--input", str(scene_txt)] + bad, capture_output=True, text=True, timeout=60)
+        assert r.returncode == 2 and "not built" in r.stderr or "no CPU path" in r.stderr
+    sc.close()
+
+
+def test_in_process_multi_gpu_entry_point():
+    """b2_render_bdpt_multi: with one device it is the plain render; with >= 2 devices the NCCL-reduced film of the
+    sharded render equals the 1-GPU film up to summation order."""
+    sd = reference_scene("cornell")
+    kw = dict(width=40, height=32, spp=6, spl=4, eye_depth=4, light_depth=4, seed=21)
+    s0 = api.Scene(sd, device=0)
+    whole, st = s0.render_bdpt(**kw)
+    one, st1 = api.render_bdpt_multi([s0], **kw)
+    assert np.allclose(one, whole, rtol=1e-5, atol=1e-6) and st1["eye_samples"] == st["eye_samples"]
+    n = min(api.device_count(), 4)
+    if n >= 2:
+        scenes = [s0] + [api.Scene(sd, device=g) for g in range(1, n)]
+        film, stn = api.render_bdpt_multi(scenes, **kw)
+        assert stn["eye_samples"] == st["eye_samples"] and stn["shadow_rays"] == st["shadow_rays"]
+        assert np.allclose(film, whole, rtol=1e-5, atol=1e-6)
+        for s in scenes[1:]:
+            s.close()
+    s0.close()
