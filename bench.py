@@ -130,6 +130,8 @@ def gpu_arm(args):
     from path_tracing_b200.scene import reference_scene
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
     if world > 1:
+        if not os.environ.get("B2_KEEP_NCCL_DEBUG"):
+            os.environ["NCCL_DEBUG"] = "WARN"        # NCCL's "NCCL version ..." banner goes to stdout and would precede the JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)

@@ -107,51 +107,42 @@ def test_empty_and_degenerate_inputs():
     P.destroy(h)
 
 
-def _sensitivity(fn, g, keys, n_rep=4, eps=2e-7):
-    """Largest relative change of the ORACLE's own output when every input float moves by <= eps relative: entries
-    where this is large are ill-conditioned (GGX lobes of roughness-0 materials: alpha = 1e-6), and CUDA's FMA
-    contraction legitimately lands elsewhere inside that spread."""
-    rng = np.random.default_rng(0)
-    base = np.asarray(fn(*[g[k] for k in keys]), np.float64)
-    worst = np.zeros(base.shape)
-    for _ in range(n_rep):
-        args = [(g[k] * (1 + rng.uniform(-1, 1, g[k].shape) * eps)).astype(np.float32) if k in ("wo", "wi", "N") else g[k] for k in keys]
-        with np.errstate(all="ignore"):
-            r = np.abs(np.asarray(fn(*args), np.float64) - base) / (np.abs(base) + 1e-3)
-        worst = np.maximum(worst, np.nan_to_num(r, nan=0.0, posinf=1e30))
-    return worst
-
-
-def _close(a, b, spread, what):
-    """Well-conditioned entries (oracle sensitivity < 1e-5, > 90 % of the table): 99.9 % within 2e-4 relative.
-    All entries: within 2e-4 + 50x the oracle's own sensitivity to 2e-7 input noise, except <= 0.5 % (the 4-draw
-    sensitivity estimate is a lower bound for the roughness-0 GGX lobes)."""
+def _close(a, b, sharp, what):
+    """Smooth-lobe entries (roughness >= 0.2): 99.9 % within 2e-4 relative, none beyond 1e-2.
+    Sharp-lobe entries (roughness < 1e-3 -> alpha = 1e-6): the GGX term is computed from `1 - cos^2(theta_h)` with
+    theta_h ~ 1e-4, i.e. from the last 2-3 bits of an fp32 -- the REFERENCE's own value jumps by up to 17 % when an
+    input direction moves by 2 ulp (measured with the oracle), so FMA contraction legitimately lands on a neighbouring
+    plateau.  For those only the zero / non-zero pattern and a factor-2 agreement are required."""
     a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    sharp = np.broadcast_to(np.asarray(sharp).reshape((-1,) + (1,) * (a.ndim - 1)), a.shape)
     assert (np.isnan(a) == np.isnan(b)).mean() > 0.999, what
     ok = np.isfinite(a) & np.isfinite(b)
     err = np.abs(a - b) / (np.abs(b) + 1e-3)
-    bad = ok & (err > 2e-4 + 50 * spread)
-    assert bad.mean() < 5e-3, (what, int(bad.sum()), float(err[ok].max()))
-    well = ok & (spread < 1e-5)
-    assert well.mean() > 0.9 and np.quantile(err[well], 0.999) < 2e-4, (what, float(np.quantile(err[well], 0.999)))
+    smooth = ok & ~sharp
+    assert smooth.sum() > 0.5 * a.size
+    assert np.quantile(err[smooth], 0.999) < 2e-4 and err[smooth].max() < 1e-2, (what, float(np.quantile(err[smooth], 0.999)), float(err[smooth].max()))
+    sh = ok & sharp
+    if sh.any():
+        assert ((a[sh] > 1e-6) == (b[sh] > 1e-6)).mean() > 0.98, what
+        assert (err[sh] < 1.0).mean() > 0.98, (what, float(err[sh].max()))
 
 
 def test_bsdf_tables_against_reference_golden():
     g = np.load(os.path.join(GOLD, "bsdf_tables.npz"))
-    P = O.Port()
-    _close(api.bsdf_evaluate(g["mtl"], g["wo"], g["wi"], g["N"]), g["evaluate"],
-           _sensitivity(P.bsdf_evaluate, g, ("mtl", "wo", "wi", "N")), "evaluate")
-    _close(api.bsdf_pdf(g["mtl"], g["wo"], g["wi"], g["N"]), g["pdf"], _sensitivity(P.bsdf_pdf, g, ("mtl", "wo", "wi", "N")), "pdf")
+    sharp = g["mtl"][:, 3] < 1e-3
+    _close(api.bsdf_evaluate(g["mtl"], g["wo"], g["wi"], g["N"]), g["evaluate"], sharp, "evaluate")
+    _close(api.bsdf_pdf(g["mtl"], g["wo"], g["wi"], g["N"]), g["pdf"], sharp, "pdf")
     s = api.bsdf_sample(g["mtl"], g["wo"], g["N"], g["u"], g["cur_eta"])
     assert np.array_equal(s["is_delta"], g["s_delta"])
     live = (g["s_pdf"] > 0) | (g["s_delta"] != 0)
     agree = (s["pdf"] > 0) == (g["s_pdf"] > 0)
     assert agree.mean() > 0.999
     live &= agree
-    sens = {k: _sensitivity(lambda *a, k=k: P.bsdf_sample(*a)[k], g, ("mtl", "wo", "N", "u", "cur_eta")) for k in ("wi", "f", "pdf")}
-    _close(s["wi"][live], g["s_wi"][live], sens["wi"][live], "sample wi")
-    _close(s["pdf"][live], g["s_pdf"][live], sens["pdf"][live], "sample pdf")
-    _close(s["f"][live], g["s_f"][live], sens["f"][live], "sample f")
+    # delta lobes (mirror / glass) are exact closed forms, not GGX: they belong to the smooth class
+    sharp_s = sharp & (g["s_delta"] == 0)
+    _close(s["wi"][live], g["s_wi"][live], np.zeros(int(live.sum()), bool), "sample wi")
+    _close(s["pdf"][live], g["s_pdf"][live], sharp_s[live], "sample pdf")
+    _close(s["f"][live], g["s_f"][live], sharp_s[live], "sample f")
     assert np.array_equal(s["new_eta"][live], g["s_eta"][live])
 
 
