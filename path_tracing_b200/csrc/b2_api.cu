@@ -18,6 +18,25 @@ void b2_set_error(const char *fmt, ...) {
     va_end(ap);
 }
 
+// ---- per-device workspace cache (one spare workspace per device) ----
+static std::mutex g_ws_mtx;
+static RenderWorkspace *g_ws_cache[64];
+RenderWorkspace &B2Scene::ws_ref() {
+    if (!ws_ptr) {
+        std::lock_guard<std::mutex> lk(g_ws_mtx);
+        if (device >= 0 && device < 64 && g_ws_cache[device]) { ws_ptr = g_ws_cache[device]; g_ws_cache[device] = nullptr; }
+        else ws_ptr = new RenderWorkspace;
+    }
+    return *ws_ptr;
+}
+void b2_workspace_release(B2Scene *s) {
+    if (!s->ws_ptr) return;
+    std::lock_guard<std::mutex> lk(g_ws_mtx);
+    if (s->device >= 0 && s->device < 64 && !g_ws_cache[s->device]) g_ws_cache[s->device] = s->ws_ptr;
+    else delete s->ws_ptr;
+    s->ws_ptr = nullptr;
+}
+
 static int need_device(int device) {
     int n = 0;
     cudaError_t e = cudaGetDeviceCount(&n);
@@ -78,6 +97,7 @@ void b2_scene_destroy(B2Scene *s) {
     if (!s) return;
     cudaSetDevice(s->device);
     if (s->stream) { cudaStreamSynchronize(s->stream); cudaStreamDestroy(s->stream); }
+    b2_workspace_release(s);
     delete s;
 }
 
@@ -154,7 +174,7 @@ int b2_render_bdpt_device(B2Scene *s, const B2Camera *cam, const B2RenderParams 
     if (!cam || !params || !d_film_rgb) { b2_set_error("NULL argument"); return B2_ERR_INVALID; }
     std::lock_guard<std::mutex> lk(s->mtx);
     B2_CUDA(cudaSetDevice(s->device));
-    return b2_render_device_impl(s->view(), s->bvh.depth, s->ws, *cam, *params, d_film_rgb, stream ? (cudaStream_t) stream : s->stream, stats);
+    return b2_render_device_impl(s->view(), s->bvh.depth, s->ws_ref(), *cam, *params, d_film_rgb, stream ? (cudaStream_t) stream : s->stream, stats);
 }
 
 int b2_render_bdpt(B2Scene *s, const B2Camera *cam, const B2RenderParams *params, float *film_rgb_host, B2Stats *stats) {
@@ -164,11 +184,13 @@ int b2_render_bdpt(B2Scene *s, const B2Camera *cam, const B2RenderParams *params
     std::lock_guard<std::mutex> lk(s->mtx);
     B2_CUDA(cudaSetDevice(s->device));
     const size_t nf = (size_t) 3 * params->width * params->height;
-    DevBuf<float> d_film;
-    B2_TRY(d_film.alloc(nf));
-    B2_TRY(b2_render_device_impl(s->view(), s->bvh.depth, s->ws, *cam, *params, d_film.p, s->stream, stats));
-    B2_CUDA(cudaMemcpyAsync(film_rgb_host, d_film.p, nf * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
+    RenderWorkspace &ws = s->ws_ref();
+    B2_TRY(ws.ensure_out(nf));
+    B2_TRY(b2_render_device_impl(s->view(), s->bvh.depth, ws, *cam, *params, ws.film_out.p, s->stream, stats));
+    // device -> pinned staging (full PCIe rate) -> the caller's pageable buffer
+    B2_CUDA(cudaMemcpyAsync(ws.h_film, ws.film_out.p, nf * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
     B2_CUDA(cudaStreamSynchronize(s->stream));
+    memcpy(film_rgb_host, ws.h_film, nf * sizeof(float));
     return B2_OK;
 }
 
@@ -177,7 +199,7 @@ int b2_light_pool(B2Scene *s, const B2RenderParams *params, float *pool20_host) 
     if (!params || !pool20_host) { b2_set_error("NULL argument"); return B2_ERR_INVALID; }
     std::lock_guard<std::mutex> lk(s->mtx);
     B2_CUDA(cudaSetDevice(s->device));
-    return b2_light_pool_impl(s->view(), s->bvh.depth, s->ws, *params, pool20_host, s->stream);
+    return b2_light_pool_impl(s->view(), s->bvh.depth, s->ws_ref(), *params, pool20_host, s->stream);
 }
 
 int b2_bsdf_evaluate(size_t n, const float *mtl6, const float *wo, const float *wi, const float *N, float *out3) {

@@ -5,6 +5,7 @@
 // NCCL is loaded with dlopen at the first multi-GPU call, so single-GPU users of libb2pt.so need no NCCL at all.
 // (Python callers run one process per GPU under torchrun and use torch.distributed instead: path_tracing_b200/multi.py.)
 #include <dlfcn.h>
+#include <cstring>
 #include <thread>
 #include <vector>
 #include "b2_scene_handle.hpp"
@@ -69,11 +70,12 @@ extern "C" int b2_render_bdpt_multi(B2Scene **scenes, int n_gpus, const B2Camera
         th.emplace_back([&, g]() {
             B2Scene *s = scenes[g];
             std::lock_guard<std::mutex> lk(s->mtx);
-            if (cudaSetDevice(s->device) != cudaSuccess || cudaMalloc((void **) &d_film[g], nf * sizeof(float)) != cudaSuccess) { rc[g] = B2_ERR_OOM; err[g] = "cudaMalloc(film) failed"; return; }
+            if (cudaSetDevice(s->device) != cudaSuccess || s->ws_ref().ensure_out(nf) != B2_OK) { rc[g] = B2_ERR_OOM; err[g] = "film buffer allocation failed"; return; }
+            d_film[g] = s->ws_ref().film_out.p;
             B2RenderParams p = *params;
             const int stride = p.sample_stride > 0 ? p.sample_stride : 1;
             p.sample_offset = params->sample_offset + g * stride; p.sample_stride = stride * n_gpus; p.film_mode = B2_FILM_SUM;
-            rc[g] = b2_render_device_impl(s->view(), s->bvh.depth, s->ws, *cam, p, d_film[g], s->stream, &st[g]);
+            rc[g] = b2_render_device_impl(s->view(), s->bvh.depth, s->ws_ref(), *cam, p, d_film[g], s->stream, &st[g]);
             if (rc[g] != B2_OK) err[g] = b2_last_error();
         });
     for (auto &t : th) t.join();
@@ -94,11 +96,13 @@ extern "C" int b2_render_bdpt_multi(B2Scene **scenes, int n_gpus, const B2Camera
         for (int g = 1; g < n_gpus; ++g) { cudaSetDevice(devs[g]); cudaStreamSynchronize(scenes[g]->stream); }
         cudaSetDevice(devs[0]);
         if (params->film_mode != B2_FILM_SUM) k_scale<<<blocks_for(nf, 256), 256, 0, scenes[0]->stream>>>(d_film[0], nf, 1.0f / (float) params->spp);
-        cudaError_t e = cudaMemcpyAsync(film_rgb_host, d_film[0], nf * sizeof(float), cudaMemcpyDeviceToHost, scenes[0]->stream);
+        float *stage = scenes[0]->ws_ref().h_film;                                   // pinned
+        cudaError_t e = cudaMemcpyAsync(stage, d_film[0], nf * sizeof(float), cudaMemcpyDeviceToHost, scenes[0]->stream);
         if (e == cudaSuccess) e = cudaStreamSynchronize(scenes[0]->stream);
+        if (e == cudaSuccess) memcpy(film_rgb_host, stage, nf * sizeof(float));
         if (e != cudaSuccess) { b2_set_error("film read-back failed: %s", cudaGetErrorString(e)); bad = B2_ERR_CUDA; }
     }
-    for (int g = 0; g < n_gpus; ++g) { cudaSetDevice(devs[g]); if (d_film[g]) cudaFree(d_film[g]); if (comms[g]) g_nccl.CommDestroy(comms[g]); }
+    for (int g = 0; g < n_gpus; ++g) { cudaSetDevice(devs[g]); if (comms[g]) g_nccl.CommDestroy(comms[g]); }
     if (stats && bad == B2_OK) {
         *stats = st[0];
         for (int g = 1; g < n_gpus; ++g) {

@@ -239,7 +239,19 @@ int RenderWorkspace::ensure(int max_paths, int eye_depth, int n_pool, size_t fil
     if (!h_ints) B2_CUDA(cudaMallocHost((void **) &h_ints, 8 * sizeof(int)));
     return B2_OK;
 }
+int RenderWorkspace::ensure_out(size_t film_floats) {
+    if (film_floats > film_out.n) B2_TRY(film_out.alloc(film_floats));
+    if (film_floats > h_film_n) {
+        if (h_film) cudaFreeHost(h_film);
+        h_film = nullptr; h_film_n = 0;
+        B2_CUDA(cudaMallocHost((void **) &h_film, film_floats * sizeof(float)));
+        h_film_n = film_floats;
+    }
+    return B2_OK;
+}
 void RenderWorkspace::release() {
+    film_out.release();
+    if (h_film) { cudaFreeHost(h_film); h_film = nullptr; h_film_n = 0; }
     ray_o.release(); ray_d.release(); thr.release(); last_pos.release(); last_n.release();
     hist_pe.release(); hist_pdf.release(); live_a.release(); live_b.release(); cv.release();
     pool.release(); pre.release(); film.release(); ints.release(); counters.release();

@@ -8,7 +8,9 @@ struct RenderWorkspace {
     DevBuf<float4> ray_o, ray_d, thr, last_pos, last_n, hist_pe, cv, pool, pre;
     DevBuf<float2> hist_pdf;
     DevBuf<int> live_a, live_b, ints;                // ints: n_pool_active, n_live_next, n_cv, n_paths
-    DevBuf<float> film;
+    DevBuf<float> film, film_out;                    // running sums; resolved film of the host-buffer entry point
+    float *h_film = nullptr; size_t h_film_n = 0;    // pinned staging for the film read-back
+    int ensure_out(size_t film_floats);
     DevBuf<unsigned long long> counters;
     int *h_ints = nullptr;                           // pinned read-back slot
     int cap_paths = 0, cap_depth = 0, cap_pool = 0;

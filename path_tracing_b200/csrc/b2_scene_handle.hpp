@@ -17,7 +17,9 @@ struct B2Scene {
     int max_leaf = 3;
     cudaStream_t stream = nullptr;
     DevBuf<unsigned long long> isect_counters;
-    RenderWorkspace ws;
+    RenderWorkspace *ws_ptr = nullptr;    // taken from the per-device cache at first use, returned to it by b2_scene_destroy
+    RenderWorkspace &ws_ref();            // (allocating and freeing ~6 GB of wavefront state per scene handle is what made
+                                          //  a create -> render -> destroy cycle 5x slower than the render itself)
     std::mutex mtx;                       // one call in flight per handle
     DevScene view() const {
         DevScene v; memset(&v, 0, sizeof(v));
@@ -30,4 +32,5 @@ struct B2Scene {
 };
 
 
+void b2_workspace_release(B2Scene *s);
 extern "C" int b2_check_built(B2Scene *s);   // internal helper (not part of include/b2pt.h)
