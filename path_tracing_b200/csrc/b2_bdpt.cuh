@@ -70,6 +70,7 @@ struct RenderCtx {
     DevScene sc;
     float3 cam_eye, cUL, cdx, cdy;          // cpu_bdpt.cpp:190-200
     int W, H, spl, eye_depth, light_depth, max_delta;
+    uint32_t w_magic, npix_magic;           // udiv_magic_of(W), udiv_magic_of(W * H): see udiv_magic()
     int sample_offset, sample_stride;
     uint2 key;
     // light-vertex pool
@@ -91,6 +92,16 @@ struct RenderCtx {
     float *film;        // W*H*3 running sums
     unsigned long long *counters;
 };
+
+// Unsigned division by a per-render constant d without the ~20-instruction (32-bit) / ~70-instruction (64-bit) division
+// sequences: with m = floor(2^32 / d), q = mulhi(n, m) is floor(n / d) or one less, for every 32-bit n.
+inline uint32_t udiv_magic_of(uint32_t d) { return d <= 1u ? 0xffffffffu : (uint32_t) (0x100000000ull / d); }
+B2_HD uint32_t udiv_magic(uint32_t n, uint32_t d, uint32_t m, uint32_t &rem) {
+    uint32_t q = mulhi32(n, m), r = n - q * d;
+    if (r >= d) { q++; r -= d; }
+    rem = r;
+    return q;
+}
 
 // camera basis exactly as run_cpu_bdpt derives it (glm arithmetic, cpu_bdpt.cpp:190-199); host-side helper
 inline void camera_basis(const float eye[3], const float look_at[3], const float view_up[3], float fov, int W, int H,
@@ -195,7 +206,7 @@ B2_HD void light_path_body(const RenderCtx &c, int idx, uint2 *stack, int sstrid
         const float3 wo = rd * -1.0f;
         const float cos_hit = fabsf(dot3(s.n, wo));
         const float cos_prev = fabsf(dot3(last_n, rd));
-        const float pdf_fwd = last_pdf * cos_hit / dist2;
+        const float pdf_fwd = fast_div(last_pdf * cos_hit, dist2);
         float u_rr, u1, u2;
         rng_draw3(c.key, B2_RNG_LIGHT, (uint32_t) idx, 0u, (uint32_t) (depth - 1 + n_delta), u_rr, u1, u2);
         bsdf_sample(s.mtl, wo, s.n, u_rr, u1, u2, eta, bs);
@@ -210,7 +221,7 @@ B2_HD void light_path_body(const RenderCtx &c, int idx, uint2 *stack, int sstrid
         }
         v.pos = s.pos; v.n = s.n; v.thr = thr; v.mtl = s.mtl; v.flags = 0u; v.cutoff = 0.0f;
         v.pdf_fwd = pdf_fwd;
-        v.pdf_rev = bsdf_pdf(s.mtl, bs.wi, wo, s.n) * cos_prev / dist2;
+        v.pdf_rev = fast_div(bsdf_pdf(s.mtl, bs.wi, wo, s.n) * cos_prev, dist2);
         store_lv(c.pool, base + depth, v);
         thr = thr * bs.f * fabsf(dot3(s.n, bs.wi)) / bs.pdf;
         if (!valid_color(thr)) break;
@@ -244,14 +255,16 @@ B2_HD void store_path(const RenderCtx &c, int p, const PathState &s) {
     c.last_pos[p] = mk4(s.last_pos, u2f(s.pixel)); c.last_n[p] = mk4(s.last_n, u2f(s.sidx));
 }
 // Work item w of a render: pixel = w % npix, local sample = w / npix (cpu_bdpt.cpp:344-361): jittered primary ray.
-B2_HD PathState primary_path(const RenderCtx &c, long long w) {
-    const int npix = c.W * c.H;
+// A batch starts at w0 = s0 * npix + pix0 (split on the host); item q of the batch is w0 + q, pix0 + q < 2^32.
+B2_HD PathState primary_path(const RenderCtx &c, uint32_t pix0, int s0, uint32_t q) {
     PathState s;
-    s.pixel = (uint32_t) (w % npix);
-    s.sidx = (uint32_t) (c.sample_offset + (int) (w / npix) * c.sample_stride);
+    const uint32_t ds = udiv_magic(pix0 + q, (uint32_t) (c.W * c.H), c.npix_magic, s.pixel);
+    s.sidx = (uint32_t) (c.sample_offset + (s0 + (int) ds) * c.sample_stride);
     float jx, jy;
     rng_draw2(c.key, B2_RNG_EYE, s.pixel, s.sidx, jx, jy);
-    const float px = x_add((float) (s.pixel % (uint32_t) c.W), jx), py = x_add((float) (s.pixel / (uint32_t) c.W), jy);
+    uint32_t col;
+    const uint32_t row = udiv_magic(s.pixel, (uint32_t) c.W, c.w_magic, col);
+    const float px = x_add((float) col, jx), py = x_add((float) row, jy);
     const float3 pp = x3_add(x3_add(c.cUL, x3_muls(c.cdx, px)), x3_muls(c.cdy, py));
     s.rd = f3_normalize(x3_sub(pp, c.cam_eye));
     s.ro = c.cam_eye; s.eta = 1.0f; s.last_pdf = 1.0f;
@@ -281,7 +294,7 @@ B2_HD void shade_step(const RenderCtx &c, PathState &ps, HitRec h, ShadeOut &o) 
     float pdf_fwd = 1.0f;
     const float3 dp = s.pos - ps.last_pos;
     const float dist2 = dot3(dp, dp);
-    if (ps.depth > 0) pdf_fwd = ps.last_pdf * fabsf(dot3(s.n, wo)) / fmaxf(dist2, 1e-6f);   // :378-382
+    if (ps.depth > 0) pdf_fwd = fast_div(ps.last_pdf * fabsf(dot3(s.n, wo)), fmaxf(dist2, 1e-6f));   // :378-382
     o.has_cv = true;
     o.ev.pos = s.pos; o.ev.n = s.n; o.ev.wo = wo; o.ev.thr = ps.thr; o.ev.mtl = s.mtl; o.ev.depth = ps.depth; o.ev.pixel = ps.pixel; o.ev.path = -1;
     float u_rr, u1, u2;
@@ -300,7 +313,7 @@ B2_HD void shade_step(const RenderCtx &c, PathState &ps, HitRec h, ShadeOut &o) 
         return;
     }
     o.pdf_fwd = pdf_fwd;
-    o.pdf_rev = bsdf_pdf(s.mtl, bs.wi, wo, s.n) * fabsf(dot3(ps.last_n, ps.rd)) / fmaxf(dist2, 1e-6f);   // :461-465
+    o.pdf_rev = fast_div(bsdf_pdf(s.mtl, bs.wi, wo, s.n) * fabsf(dot3(ps.last_n, ps.rd)), fmaxf(dist2, 1e-6f));   // :461-465
     ps.thr = ps.thr * bs.f * fabsf(dot3(s.n, bs.wi)) / bs.pdf;
     if (!valid_color(ps.thr)) return;
     ps.depth++;
@@ -331,25 +344,26 @@ B2_HD float mis_weight_core(const EA &E, int s_idx, const LA &L, int t_idx, floa
     const float3 wo_t = (t_idx == 0) ? normalize3(L.cur_n()) : normalize3(L.pos(t_idx - 1) - lv_pos);
     const float pdf_omega_s = fmaxf(bsdf_pdf(E.cur_mtl(), wo_s, d_vec, ns), 1e-6f);
     const float pdf_omega_t = fmaxf(bsdf_pdf(L.cur_mtl(), wo_t, md, nt), 1e-6f);
-    const float pdf_s_to_t = pdf_omega_s * cos_t / dist2;
-    const float pdf_t_to_s = pdf_omega_t * cos_s / dist2;
+    const float inv_d2 = fast_rcp(dist2);
+    const float pdf_s_to_t = pdf_omega_s * cos_t * inv_d2;
+    const float pdf_t_to_s = pdf_omega_t * cos_s * inv_d2;
     float sum = 1.0f, ratio = 1.0f, prev_rev = pdf_t_to_s;
     for (int i = s_idx; i > 0; --i) {                                      // :143-148
         if (E.eta(i) > 0.0f) break;
-        ratio *= prev_rev / fmaxf(E.pdf_fwd(i), 1e-8f);
+        ratio *= fast_div(prev_rev, fmaxf(E.pdf_fwd(i), 1e-8f));
         sum += ratio;
         prev_rev = E.pdf_rev(i);
     }
     ratio = 1.0f; prev_rev = pdf_s_to_t;
     for (int i = t_idx; i > 0; --i) {                                      // :153-163
-        if (L.is_src(i)) { ratio *= prev_rev / fmaxf(L.pdf_fwd(i), 1e-8f); sum += ratio; break; }
+        if (L.is_src(i)) { ratio *= fast_div(prev_rev, fmaxf(L.pdf_fwd(i), 1e-8f)); sum += ratio; break; }
         if (L.eta(i) > 0.0f) break;
-        ratio *= prev_rev / fmaxf(L.pdf_fwd(i), 1e-8f);
+        ratio *= fast_div(prev_rev, fmaxf(L.pdf_fwd(i), 1e-8f));
         sum += ratio;
         prev_rev = L.pdf_rev(i);
     }
     if (isnan(sum) || isinf(sum) || sum <= 0.0f) return 0.0f;
-    return 1.0f / sum;
+    return fast_rcp(sum);
 }
 
 // Render-side accessors.  At connection time the current eye vertex still carries the placeholders
@@ -417,7 +431,7 @@ B2_HD bool pretest_rec(float3 ev_pos, float3 ev_n, float4 r0, float4 r1, float4 
     const float3 d = mk3(r0) - ev_pos;
     const float dist2 = dot3(d, d);
     bool pass = !(dist2 < 1e-6f) && dot3(ev_n, d) > 0.0f && dot3(mk3(r1), d) < 0.0f;
-    if (r0.w > -1.5f) pass = pass && !(-dot3(mk3(r2), d) < r0.w * sqrtf(dist2));
+    if (r0.w > -1.5f) pass = pass && !(-dot3(mk3(r2), d) < r0.w * fast_sqrt(dist2));
     return pass;
 }
 // Returns the (validated, clamped) contribution, zero if the pair contributes nothing.  n_shadow / n_path count
@@ -429,8 +443,7 @@ B2_HD float3 connect_finish(const RenderCtx &c, const EyeVtx &ev, int lv_index, 
     const LightVtx lv = load_lv(c.pool, lv_index);
     const float3 d_vec = lv.pos - ev.pos;
     const float dist2 = dot3(d_vec, d_vec);
-    const float dist = sqrtf(dist2);
-    const float3 wi = d_vec / dist;
+    const float3 wi = div_sqrt3(d_vec, dist2);
     const float3 mwi = wi * -1.0f;
     const float cosE = fmaxf(0.0f, dot3(ev.n, wi));
     const float cosL = fmaxf(0.0f, dot3(lv.n, mwi));
@@ -446,7 +459,7 @@ B2_HD float3 connect_finish(const RenderCtx &c, const EyeVtx &ev, int lv_index, 
     const ShadowRay sr = make_shadow_ray(x3_add(ev.pos, x3_muls(ev.n, B2_EPSILON)), x3_add(lv.pos, x3_muls(lv.n, B2_EPSILON)));   // :424
     n_shadow++;
     if (occluded_bvh<COUNT>(c.sc, sr.o, sr.d, sr.tmax, stack, sstride, tc)) return zero;
-    const float G = (cosE * cosL) / fmaxf(dist2, 1e-4f);                      // :427
+    const float G = fast_div(cosE * cosL, fmaxf(dist2, 1e-4f));                      // :427
     const RenderEyeAcc EA{ c, ev };
     const RenderLightAcc LA{ c, lv, lv_index - t_idx };
     const float w = mis_weight_core(EA, ev.depth, LA, t_idx, d_vec, dist2, c.cam_eye);   // :431

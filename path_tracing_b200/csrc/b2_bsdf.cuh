@@ -24,13 +24,13 @@ B2_HD float3 to_world(const Frame &f, float3 v) {
 B2_HD float fr_dielectric(float cosI, float etaI, float etaT) {  // :145-160
     cosI = fmaxf(-1.0f, fminf(1.0f, cosI));
     if (!(cosI > 0.0f)) { float t = etaI; etaI = etaT; etaT = t; cosI = fabsf(cosI); }
-    float sinI = sqrtf(fmaxf(0.0f, 1.0f - cosI * cosI));
-    float sinT = etaI / etaT * sinI;
+    float sinI = fast_sqrt(fmaxf(0.0f, 1.0f - cosI * cosI));
+    float sinT = fast_div(etaI, etaT) * sinI;                    // etaT == 0 (opaque non-metal): inf or nan -> see below
     if (sinT >= 1.0f) return 1.0f;
-    float cosT = sqrtf(fmaxf(0.0f, 1.0f - sinT * sinT));
-    float Rparl = ((etaT * cosI) - (etaI * cosT)) / ((etaT * cosI) + (etaI * cosT));
-    float Rperp = ((etaI * cosI) - (etaT * cosT)) / ((etaI * cosI) + (etaT * cosT));
-    return (Rparl * Rparl + Rperp * Rperp) / 2.0f;
+    float cosT = fast_sqrt(fmaxf(0.0f, 1.0f - sinT * sinT));
+    float Rparl = fast_div((etaT * cosI) - (etaI * cosT), (etaT * cosI) + (etaI * cosT));
+    float Rperp = fast_div((etaI * cosI) - (etaT * cosT), (etaI * cosI) + (etaT * cosT));
+    return (Rparl * Rparl + Rperp * Rperp) * 0.5f;
 }
 B2_HD float3 fr_schlick(float cosI, float3 R0) {                 // :163-167
     float c = fmaxf(0.0f, 1.0f - cosI);
@@ -40,30 +40,31 @@ B2_HD float3 fr_schlick(float cosI, float3 R0) {                 // :163-167
 B2_HD float roughness_to_alpha(float r) { float x = fmaxf(r, 1e-3f); return x * x; }   // :173
 B2_HD float tr_D(float3 wh, float alpha) {                       // :178-185
     float cos2 = wh.z * wh.z;
-    float tan2 = fmaxf(0.0f, 1.0f - cos2) / (cos2 + 1e-7f);
+    float tan2 = fast_div(fmaxf(0.0f, 1.0f - cos2), cos2 + 1e-7f);
     if (isinf(tan2)) return 0.0f;
     float e = (cos2 * cos2) * (alpha * alpha + tan2 * tan2);
     if (e < 1e-12f) return 0.0f;
-    return (alpha * alpha) / (B2_PI * e);
+    return fast_div(alpha * alpha, B2_PI * e);
 }
 B2_HD float tr_lambda(float3 w, float alpha) {                   // :187-192
-    float t = fabsf(sqrtf(fmaxf(0.0f, 1.0f - w.z * w.z)) / (w.z + 1e-7f));
+    float t = fabsf(fast_div(fast_sqrt(fmaxf(0.0f, 1.0f - w.z * w.z)), w.z + 1e-7f));
     if (isinf(t)) return 0.0f;
     float a2t2 = (alpha * t) * (alpha * t);
-    return (-1.0f + sqrtf(1.0f + a2t2)) / 2.0f;
+    return (-1.0f + fast_sqrt(1.0f + a2t2)) * 0.5f;
 }
-B2_HD float tr_G(float3 wo, float3 wi, float alpha) { return 1.0f / (1.0f + tr_lambda(wo, alpha) + tr_lambda(wi, alpha)); }
+B2_HD float tr_G(float3 wo, float3 wi, float alpha) { return fast_rcp(1.0f + tr_lambda(wo, alpha) + tr_lambda(wi, alpha)); }
 B2_HD float3 sample_vndf(float3 wo, float alpha, float u1, float u2) {  // :200-221
     float3 V = normalize3(mk3(alpha * wo.x, alpha * wo.y, wo.z));
     float3 T1 = (V.z < 0.9999f) ? normalize3(cross3(mk3(0, 0, 1), V)) : mk3(1, 0, 0);
     float3 T2 = cross3(V, T1);
-    float r = sqrtf(u1);
-    float phi = 2.0f * B2_PI * u2;
-    float t1 = r * cosf(phi);
-    float t2 = r * sinf(phi);
+    float r = fast_sqrt(u1);
+    float sphi, cphi;
+    sincos_2pi(u2, sphi, cphi);
+    float t1 = r * cphi;
+    float t2 = r * sphi;
     float s = 0.5f * (1.0f + V.z);
-    t2 = (1.0f - s) * sqrtf(fmaxf(0.0f, 1.0f - t1 * t1)) + s * t2;
-    float3 Nh = T1 * t1 + T2 * t2 + V * sqrtf(fmaxf(0.0f, 1.0f - t1 * t1 - t2 * t2));
+    t2 = (1.0f - s) * fast_sqrt(fmaxf(0.0f, 1.0f - t1 * t1)) + s * t2;
+    float3 Nh = T1 * t1 + T2 * t2 + V * fast_sqrt(fmaxf(0.0f, 1.0f - t1 * t1 - t2 * t2));
     return normalize3(mk3(alpha * Nh.x, alpha * Nh.y, fmaxf(0.0f, Nh.z)));
 }
 
@@ -76,14 +77,14 @@ B2_HD float3 bsdf_eval_local(const Mat &m, float3 wo, float3 wi) {      // :426-
     if (length3(whv) < 1e-6f) return mk3(0, 0, 0);
     float3 wh = normalize3(whv);
     if (wh.z < 0.0f) wh = wh * -1.0f;
-    float3 diffuse = m.base / B2_PI * (1.0f - m.metallic);
+    float3 diffuse = m.base * ((1.0f / B2_PI) * (1.0f - m.metallic));
     if (wo.z * wi.z < 0.0f) diffuse = mk3(0, 0, 0);
     float D = tr_D(wh, alpha);
     float G = tr_G(wo, wi, alpha);
     float3 F;
     if (m.metallic > 0.0f) F = fr_schlick(fabsf(wo.z), m.base);
     else { float fr = fr_dielectric(dot3(wo, wh), 1.0f, m.eta); F = mk3(fr, fr, fr); }
-    float3 spec = (F * D * G) / fmaxf(4.0f * fabsf(wo.z) * fabsf(wi.z), 1e-4f);
+    float3 spec = (F * D * G) / fmaxf(4.0f * fabsf(wo.z) * fabsf(wi.z), 1e-4f);   // operator/ = one reciprocal
     if (wo.z * wi.z > 0.0f) return diffuse + spec;
     return diffuse;
 }
@@ -95,11 +96,11 @@ B2_HD float bsdf_pdf_local(const Mat &m, float3 wo, float3 wi) {        // :464-
     if (length3(whv) < 1e-6f) return 0.0f;
     float3 wh = normalize3(whv);
     if (wh.z < 0.0f) wh = wh * -1.0f;
-    float pdf_diffuse = fabsf(wi.z) / B2_PI;
-    float G1 = 1.0f / (1.0f + tr_lambda(wo, alpha));
+    float pdf_diffuse = fabsf(wi.z) * (1.0f / B2_PI);
+    float G1 = fast_rcp(1.0f + tr_lambda(wo, alpha));
     float owh = dot3(wo, wh);
-    float pdf_wh = tr_D(wh, alpha) * G1 * fmaxf(0.0f, owh) / fabsf(wo.z);
-    float pdf_spec = pdf_wh / (4.0f * owh + 1e-7f);
+    float pdf_wh = fast_div(tr_D(wh, alpha) * G1 * fmaxf(0.0f, owh), fabsf(wo.z));
+    float pdf_spec = fast_div(pdf_wh, 4.0f * owh + 1e-7f);
     float sw = m.metallic > 0.0f ? 1.0f : 0.5f;
     return (1.0f - sw) * pdf_diffuse + sw * pdf_spec;
 }
@@ -135,7 +136,7 @@ B2_HD void bsdf_sample(const Mat &m, float3 wo_w, float3 N, float u_rr, float u1
             float sin2I = fmaxf(0.0f, 1.0f - wo.z * wo.z);
             float sin2T = eta * eta * sin2I;
             if (sin2T >= 1.0f) { s.pdf = 0.0f; return; }
-            float cosT = sqrtf(1.0f - sin2T);
+            float cosT = fast_sqrt(1.0f - sin2T);
             if (wo.z > 0.0f) cosT = -cosT;
             wi = mk3(-eta * wo.x, -eta * wo.y, cosT);
             s.new_eta = (wo.z > 0.0f) ? m.eta : 1.0f;
@@ -162,9 +163,10 @@ B2_HD void bsdf_sample(const Mat &m, float3 wo_w, float3 N, float u_rr, float u1
         wi = I - wh * 2.0f * dot3(wh, I);              // reflect(), :99
         if (wo.z * wi.z <= 0.0f) { s.pdf = 0.0f; return; }
     } else {
-        float r = sqrtf(u1);
-        float phi = 2.0f * B2_PI * u2;
-        wi = mk3(r * cosf(phi), r * sinf(phi), sqrtf(fmaxf(0.0f, 1.0f - u1)));
+        float r = fast_sqrt(u1);
+        float sphi, cphi;
+        sincos_2pi(u2, sphi, cphi);
+        wi = mk3(r * cphi, r * sphi, fast_sqrt(fmaxf(0.0f, 1.0f - u1)));
         if (wo.z < 0.0f) wi.z *= -1.0f;
     }
     s.wi = to_world(fr, wi);

@@ -21,6 +21,18 @@ B2_HD RayPre ray_pre(float3 o, float3 d) {
     return r;
 }
 B2_HD uint32_t byte_of(uint32_t lo_word, uint32_t hi_word, int i) { return ((i < 4 ? lo_word : hi_word) >> (8 * (i & 3))) & 0xffu; }
+// (float) byte i of {lo_word, hi_word}.  B2_CVT_PRMT: one PRMT builds the float 2^23 + byte, one FADD removes the 2^23
+// (exact, same bits as the integer conversion) -- ALU + FMA pipes instead of the quarter-rate conversion pipe.
+#ifndef B2_CVT_PRMT
+#define B2_CVT_PRMT 0
+#endif
+B2_HD float byte_f32(uint32_t lo_word, uint32_t hi_word, int i) {
+#if defined(__CUDA_ARCH__) && B2_CVT_PRMT
+    return __uint_as_float(__byte_perm(i < 4 ? lo_word : hi_word, 0x4B000000u, 0x7650u | (uint32_t) (i & 3))) - 8388608.0f;
+#else
+    return (float) byte_of(lo_word, hi_word, i);
+#endif
+}
 
 // Tests the 8 children of `node`; returns hit internal children as bits (slot ^ oct) in hits_p and hit leaf
 // triangles as a 24-bit mask relative to the node's tri_base.
@@ -43,9 +55,9 @@ B2_HD void node_test(const uint4 *__restrict__ nodes, uint32_t node, const RayPr
     for (int i = 0; i < 8; ++i) {
         const uint32_t meta = byte_of(w1.z, w1.w, i);
         if (meta == 0) continue;
-        const float tlx = (float) byte_of(xl0, xl1, i) * ax + bx, thx = (float) byte_of(xh0, xh1, i) * ax + bx;
-        const float tly = (float) byte_of(yl0, yl1, i) * ay + by, thy = (float) byte_of(yh0, yh1, i) * ay + by;
-        const float tlz = (float) byte_of(zl0, zl1, i) * az + bz, thz = (float) byte_of(zh0, zh1, i) * az + bz;
+        const float tlx = byte_f32(xl0, xl1, i) * ax + bx, thx = byte_f32(xh0, xh1, i) * ax + bx;
+        const float tly = byte_f32(yl0, yl1, i) * ay + by, thy = byte_f32(yh0, yh1, i) * ay + by;
+        const float tlz = byte_f32(zl0, zl1, i) * az + bz, thz = byte_f32(zh0, zh1, i) * az + bz;
         const float tn = fmaxf(fmaxf(tlx, tly), fmaxf(tlz, tmin));
         const float tf = fminf(fminf(thx, thy), fminf(thz, tmax));
         if (tn <= tf * 1.0000005f + 1e-30f) {

@@ -61,16 +61,60 @@ B2_HD float3 g3_normalize(float3 v) { return x3_muls(v, x_div(1.0f, x_sqrt(x3_do
 B2_HD float3 f3_normalize(float3 v) { return x3_divs(v, x3_length(v)); }                       // geometric.cuh:98
 B2_HD float3 x3_neg(float3 a) { return mk3(-a.x, -a.y, -a.z); }
 
+// ---- fast scalar ops for the shading maths (parity there is to ~1e-6 relative, not bitwise) ----
+// One MUFU instruction each on the device (~1-2 ulp, denormals flushed: every caller clamps far above 1e-38); the
+// compiler's own x / y and sqrtf(x) carry range fix-ups that cost 4-7 instructions apiece, and the connection stage
+// evaluates ~50 of them per pair.
+#if defined(__CUDA_ARCH__)
+B2_HD float fast_rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+B2_HD float fast_rsqrt(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+B2_HD float fast_sqrt(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+#else
+B2_HD float fast_rcp(float x) { return 1.0f / x; }
+B2_HD float fast_rsqrt(float x) { return 1.0f / sqrtf(x); }
+B2_HD float fast_sqrt(float x) { return sqrtf(x); }
+#endif
+#if defined(__CUDA_ARCH__)
+B2_HD float fast_div(float a, float b) { return a * fast_rcp(b); }
+#else
+B2_HD float fast_div(float a, float b) { return a / b; }
+#endif
+// sin / cos of 2 pi u, u in [0, 1): sincospif has no slow range-reduction path (sinf / cosf of an angle carry one each)
+B2_HD void sincos_2pi(float u, float &s, float &c) {
+#if defined(__CUDA_ARCH__)
+    sincospif(2.0f * u, &s, &c);
+#else
+    const float phi = 2.0f * B2_PI * u; s = sinf(phi); c = cosf(phi);
+#endif
+}
+
 // ---- fast vector ops (FMA contraction allowed): shading maths, where parity is statistical ----
 B2_HD float3 operator+(float3 a, float3 b) { return mk3(a.x + b.x, a.y + b.y, a.z + b.z); }
 B2_HD float3 operator-(float3 a, float3 b) { return mk3(a.x - b.x, a.y - b.y, a.z - b.z); }
 B2_HD float3 operator*(float3 a, float3 b) { return mk3(a.x * b.x, a.y * b.y, a.z * b.z); }
 B2_HD float3 operator*(float3 a, float s) { return mk3(a.x * s, a.y * s, a.z * s); }
+#if defined(__CUDA_ARCH__)
+B2_HD float3 operator/(float3 a, float s) { const float r = fast_rcp(s); return mk3(a.x * r, a.y * r, a.z * r); }
+#else      // the host build (tests/hostsim) keeps the reference's own operation order: it is compared to the oracle at 1e-5
 B2_HD float3 operator/(float3 a, float s) { return mk3(a.x / s, a.y / s, a.z / s); }
+#endif
 B2_HD float dot3(float3 a, float3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 B2_HD float3 cross3(float3 a, float3 b) { return mk3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
-B2_HD float length3(float3 a) { return sqrtf(dot3(a, a)); }
+B2_HD float length3(float3 a) { return fast_sqrt(dot3(a, a)); }
+#if defined(__CUDA_ARCH__)
+B2_HD float3 normalize3(float3 a) { const float r = fast_rsqrt(dot3(a, a)); return mk3(a.x * r, a.y * r, a.z * r); }
+#else
 B2_HD float3 normalize3(float3 a) { return a / length3(a); }
+#endif
+
+// a / sqrt(x): one reciprocal square root on the device
+B2_HD float3 div_sqrt3(float3 a, float x) {
+#if defined(__CUDA_ARCH__)
+    const float r = fast_rsqrt(x); return mk3(a.x * r, a.y * r, a.z * r);
+#else
+    return a / sqrtf(x);
+#endif
+}
 
 // cpu_bdpt.cpp:12-16
 B2_HD bool valid_color(float3 c) {

@@ -26,9 +26,9 @@ constexpr int EXT_THREADS = 128;      // extend kernel block
 constexpr int CONN_THREADS = 128;     // connect kernel block: 4 independent warps
 constexpr int CONN_WARPS = CONN_THREADS / 32;
 constexpr int CONN_BLOCKS_PER_SM = 4; // persistent grid = 148 SMs x this
-constexpr int CONN_MIN_SLICE = 8;     // smallest pool slice a connect work item may get (late, nearly empty waves)
-constexpr int CONN_GROUP = 4;         // pool vertices pre-tested between two drain checks
-constexpr int CONN_RING = 256;        // per-warp ring capacity (power of two) >= 31 pending + CONN_GROUP * 32 new entries
+constexpr int CONN_CHUNK = 8;         // pool vertices pre-tested per compaction round; the pre-test table is padded to a
+                                      // multiple of this with records that never pass, and pool slices are whole chunks
+constexpr int CONN_BUF = 32 * CONN_CHUNK + 32;   // per-warp pending-pair stack: < 32 left over + at most 32 x CONN_CHUNK new
 
 __device__ __forceinline__ uint32_t lanemask_lt() { uint32_t m; asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m)); return m; }
 
@@ -79,12 +79,18 @@ __global__ void __launch_bounds__(1024) k_pool_active(RenderCtx c) {
         if (threadIdx.x == 0) s_base += tot;
         __syncthreads();
     }
-    if (threadIdx.x == 0) *c.n_pool_active = s_base;
+    // pad to a whole chunk with records no eye vertex can pass (zero normal: dot(n, d) < 0 is false)
+    const int n = s_base, n_pad = (n + CONN_CHUNK - 1) / CONN_CHUNK * CONN_CHUNK;
+    if (threadIdx.x < n_pad - n) {
+        float4 *rec = c.pre + (size_t) B2_PRE_F4 * (n + threadIdx.x);
+        rec[0] = make_float4(0.0f, 0.0f, 0.0f, B2_NO_GATE); rec[1] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); rec[2] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    }
+    if (threadIdx.x == 0) *c.n_pool_active = n;
 }
 
 // One bounce of every live path.  PRIMARY: item = sample w0 + i of the batch (no state in HBM yet).
 template <bool PRIMARY, bool COUNT>
-__global__ void __launch_bounds__(EXT_THREADS) k_extend(RenderCtx c, int n_items, long long w0) {
+__global__ void __launch_bounds__(EXT_THREADS) k_extend(RenderCtx c, int n_items, uint32_t pix0, int s0) {
     extern __shared__ uint2 s_stack[];
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
     const bool active = q < n_items;
@@ -93,7 +99,7 @@ __global__ void __launch_bounds__(EXT_THREADS) k_extend(RenderCtx c, int n_items
     ShadeOut so; so.has_cv = so.alive = so.store_hist = so.emitter_hit = so.delta_cap = false;
     int path = -1;
     if (active) {
-        if (PRIMARY) ps = primary_path(c, w0 + q);
+        if (PRIMARY) ps = primary_path(c, pix0, s0, (uint32_t) q);
         else { path = c.live[q]; ps = load_path(c, path); }
         const HitRec h = closest_hit_bvh<COUNT>(c.sc, ps.ro, ps.rd, s_stack + threadIdx.x, blockDim.x, &tc);
         shade_step(c, ps, h, so);
@@ -119,22 +125,29 @@ __global__ void __launch_bounds__(EXT_THREADS) k_extend(RenderCtx c, int n_items
     if (COUNT) { warp_count_add(&c.counters[B2_CNT_NODES], tc.nodes); warp_count_add(&c.counters[B2_CNT_TRIS], tc.tris); }
 }
 
-// Connection stage.  Work item = (group of 32 eye-vertex records) x (slice of the active pool); persistent warps
-// pull items grid-stride.  The pool is sliced only when there are too few eye vertices to fill the machine (late
-// waves), so that the serial latency of a nearly empty wave stays short.  No block-level synchronisation.
+// Connection stage.  Work item = (group of 32 eye-vertex records) x (slice of the active pool, whole chunks);
+// persistent warps pull items grid-stride.  The pool is sliced only when there are too few eye vertices to fill the
+// machine (late waves), so that the serial latency of a nearly empty wave stays short.  No block-level synchronisation.
+//   pre-test : every lane owns one eye vertex and tests it against CONN_CHUNK pool records (warp-uniform addresses, the
+//              loop is fully unrolled: 2 broadcast loads + ~16 FP instructions per pair), collecting a bit per record
+//   compact  : only if any lane has a bit set: warp scan of the pop-counts, (owner lane, pool index) pairs pushed on
+//              the warp's shared-memory stack
+//   finish   : 32 pending pairs at a time at full lane occupancy (connect_finish), per-owner sums in shared memory,
+//              one film atomicAdd per eye vertex and channel at the end of the item
 template <bool COUNT>
 __global__ void __launch_bounds__(CONN_THREADS) k_connect(RenderCtx c) {
     extern __shared__ uint2 s_stack[];                    // CONN_THREADS x stack depth
-    __shared__ uint32_t s_ring[CONN_WARPS][CONN_RING];
+    __shared__ uint32_t s_buf[CONN_WARPS][CONN_BUF];
     __shared__ float s_acc[CONN_WARPS][3][32];
     const int n_cv = *c.n_cv, n_act = *c.n_pool_active;
     if (n_cv <= 0 || n_act <= 0) return;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int n_groups = (n_cv + 31) >> 5;
+    const int n_chunks = (n_act + CONN_CHUNK - 1) / CONN_CHUNK;
     const int total_warps = gridDim.x * CONN_WARPS;
-    const int n_slices = max(1, min(total_warps / n_groups, (n_act + CONN_MIN_SLICE - 1) / CONN_MIN_SLICE));
+    const int n_slices = max(1, min(total_warps / n_groups, n_chunks));
     const long long n_items = (long long) n_groups * n_slices;
-    uint32_t *ring = s_ring[warp];
+    uint32_t *buf = s_buf[warp];
     float *acc_x = s_acc[warp][0], *acc_y = s_acc[warp][1], *acc_z = s_acc[warp][2];
     const float4 *__restrict__ pre = c.pre;
     uint32_t n_shadow = 0, n_path = 0;
@@ -142,20 +155,22 @@ __global__ void __launch_bounds__(CONN_THREADS) k_connect(RenderCtx c) {
     TravCounters tc{ 0u, 0u };
 
     for (long long item = (long long) blockIdx.x * CONN_WARPS + warp; item < n_items; item += total_warps) {
-        const int group = (int) (item / n_slices), slice = (int) (item % n_slices);
-        const int a_begin = (int) ((long long) slice * n_act / n_slices), a_end = (int) ((long long) (slice + 1) * n_act / n_slices);
+        int group, slice;
+        if (n_slices == 1) { group = (int) item; slice = 0; }
+        else { group = (int) (item / n_slices); slice = (int) (item % n_slices); }
+        const int ch_begin = (int) ((long long) slice * n_chunks / n_slices), ch_end = (int) ((long long) (slice + 1) * n_chunks / n_slices);
         const int q0 = group << 5, q = q0 + lane;
         const bool valid = q < n_cv;
-        float3 my_pos = mk3(0, 0, 0), my_n = mk3(0, 0, 0);
+        float3 my_pos = mk3(0, 0, 0), my_n = mk3(0, 0, 0);            // a zero normal never passes: idle lanes need no branch
         uint32_t my_pixel = 0u;
         if (valid) { const float4 f0 = c.cv[B2_CV_F4 * q]; my_pos = mk3(f0); my_pixel = __float_as_uint(f0.w) >> 8; my_n = mk3(c.cv[B2_CV_F4 * q + 1]); }
         acc_x[lane] = 0.0f; acc_y[lane] = 0.0f; acc_z[lane] = 0.0f;
         __syncwarp();
-        uint32_t head = 0u, tail = 0u;                    // warp-uniform ring cursors (registers)
+        int n_buf = 0;                                    // warp-uniform stack height
 
-        auto drain = [&](uint32_t count) {                // finish `count` <= 32 entries starting at head
-            if ((uint32_t) lane < count) {
-                const uint32_t e = ring[(head + (uint32_t) lane) % CONN_RING];
+        auto drain = [&](int count) {                     // finish the top `count` <= 32 entries
+            if (lane < count) {
+                const uint32_t e = buf[n_buf - count + lane];
                 const int owner = (int) (e >> 27), lvi = (int) (e & 0x7ffffffu);
                 const EyeVtx ev = load_cv(c.cv, q0 + owner);
                 const float3 r = connect_finish<COUNT>(c, ev, lvi, s_stack + threadIdx.x, CONN_THREADS, &tc, n_shadow, n_path);
@@ -163,27 +178,42 @@ __global__ void __launch_bounds__(CONN_THREADS) k_connect(RenderCtx c) {
                 if (r.y != 0.0f) atomicAdd(&acc_y[owner], r.y);
                 if (r.z != 0.0f) atomicAdd(&acc_z[owner], r.z);
             }
-            head += count;
+            n_buf -= count;
             __syncwarp();
         };
 
-        for (int a0 = a_begin; a0 < a_end; a0 += CONN_GROUP) {
-            // pre-test a group of pool vertices (independent broadcast loads, so they pipeline), compacting survivors
+        for (int ch = ch_begin;; ++ch) {                  // one extra pass after the last chunk empties the stack
+            const bool last = ch >= ch_end;
+            while (n_buf >= 32 || (last && n_buf > 0)) drain(min(32, n_buf));     // the only call site: connect_finish is big
+            if (last) break;
+            const float4 *__restrict__ rec = pre + (size_t) B2_PRE_F4 * CONN_CHUNK * ch;
+            uint32_t mask = 0u;
 #pragma unroll
-            for (int k = 0; k < CONN_GROUP; ++k) {
-                const int a = a0 + k;
-                if (a < a_end) {
-                    const float4 r0 = __ldg(&pre[B2_PRE_F4 * a]), r1 = __ldg(&pre[B2_PRE_F4 * a + 1]), r2 = __ldg(&pre[B2_PRE_F4 * a + 2]);
-                    const bool pass = valid && pretest_rec(my_pos, my_n, r0, r1, r2);
-                    const uint32_t m = __ballot_sync(0xffffffffu, pass);
-                    if (pass) ring[(tail + (uint32_t) __popc(m & lanemask_lt())) % CONN_RING] = ((uint32_t) lane << 27) | __float_as_uint(r1.w);
-                    tail += (uint32_t) __popc(m);
+            for (int k = 0; k < CONN_CHUNK; ++k) {
+                const float4 r0 = __ldg(&rec[B2_PRE_F4 * k]), r1 = __ldg(&rec[B2_PRE_F4 * k + 1]);
+                const float3 d = mk3(r0) - my_pos;
+                const float dist2 = dot3(d, d);
+                bool pass = !(dist2 < 1e-6f) && dot3(my_n, d) > 0.0f && dot3(mk3(r1), d) < 0.0f;
+                if (r0.w > -1.5f && pass) {                // spot-cone gate (warp-uniform first operand)
+                    const float4 r2 = __ldg(&rec[B2_PRE_F4 * k + 2]);
+                    pass = !(-dot3(mk3(r2), d) < r0.w * fast_sqrt(dist2));
                 }
+                mask |= (pass ? 1u : 0u) << k;
             }
-            __syncwarp();
-            // finish surviving pairs 32 at a time; after the last group also the remainder
-            const uint32_t need = (a0 + CONN_GROUP >= a_end) ? 1u : 32u;
-            while (tail - head >= need) drain(min(32u, tail - head));
+            if (__ballot_sync(0xffffffffu, mask != 0u)) {
+                const int cnt = __popc(mask);
+                int incl = cnt;
+#pragma unroll
+                for (int dlt = 1; dlt < 32; dlt <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, dlt); if (lane >= dlt) incl += t; }
+                int pos = n_buf + incl - cnt;
+                n_buf += __shfl_sync(0xffffffffu, incl, 31);
+                while (mask) {
+                    const int k = __ffs((int) mask) - 1;
+                    mask &= mask - 1u;
+                    buf[pos++] = ((uint32_t) lane << 27) | __float_as_uint(__ldg(&rec[B2_PRE_F4 * k + 1].w));
+                }
+                __syncwarp();
+            }
         }
         if (valid) {
             const float3 r = mk3(acc_x[lane], acc_y[lane], acc_z[lane]);
@@ -191,7 +221,7 @@ __global__ void __launch_bounds__(CONN_THREADS) k_connect(RenderCtx c) {
             if (r.y != 0.0f) atomicAdd(&c.film[3 * my_pixel + 1], r.y);
             if (r.z != 0.0f) atomicAdd(&c.film[3 * my_pixel + 2], r.z);
         }
-        n_pairs += (unsigned long long) (a_end - a_begin) * (unsigned long long) min(32, n_cv - q0);
+        n_pairs += (unsigned long long) (min(ch_end * CONN_CHUNK, n_act) - ch_begin * CONN_CHUNK) * (unsigned long long) min(32, n_cv - q0);
         __syncwarp();
     }
     warp_count_add(&c.counters[B2_CNT_SHADOW], n_shadow);
@@ -232,7 +262,7 @@ int RenderWorkspace::ensure(int max_paths, int eye_depth, int n_pool, size_t fil
         B2_TRY(live_a.alloc(mp)); B2_TRY(live_b.alloc(mp)); B2_TRY(cv.alloc((size_t) B2_CV_F4 * mp));
         cap_paths = mp; cap_depth = ed;
     }
-    if (n_pool > cap_pool) { B2_TRY(pool.alloc((size_t) B2_LV_F4 * n_pool)); B2_TRY(pre.alloc((size_t) B2_PRE_F4 * n_pool)); cap_pool = n_pool; }
+    if (n_pool > cap_pool) { B2_TRY(pool.alloc((size_t) B2_LV_F4 * n_pool)); B2_TRY(pre.alloc((size_t) B2_PRE_F4 * (n_pool + CONN_CHUNK))); cap_pool = n_pool; }
     if (film_floats > film.n) B2_TRY(film.alloc(film_floats));
     if (!ints.p) B2_TRY(ints.alloc(8));
     if (!counters.p) B2_TRY(counters.alloc(B2_CNT_N));
@@ -275,6 +305,7 @@ static void setup_ctx(RenderCtx &c, const DevScene &sc, const B2Camera &cam, con
     c.sc = sc;
     camera_basis(cam.eye, cam.look_at, cam.view_up, cam.fov, p.width, p.height, c.cam_eye, c.cUL, c.cdx, c.cdy);
     c.W = p.width; c.H = p.height; c.spl = p.spl; c.eye_depth = p.eye_depth; c.light_depth = p.light_depth;
+    c.w_magic = udiv_magic_of((uint32_t) p.width); c.npix_magic = udiv_magic_of((uint32_t) p.width * (uint32_t) p.height);
     c.max_delta = p.max_delta > 0 ? p.max_delta : 256;
     c.sample_offset = p.sample_offset; c.sample_stride = p.sample_stride > 0 ? p.sample_stride : 1;
     c.key = make_uint2((uint32_t) p.seed, (uint32_t) (p.seed >> 32));
@@ -329,7 +360,7 @@ static int set_smem_limits(int bvh_depth) {
     B2_CUDA(cudaGetDevice(&dev));
     if (dev < 64 && bvh_depth + 1 <= configured[dev]) return B2_OK;
     const size_t sb_t = stack_bytes(EXT_THREADS, bvh_depth), sb_c = stack_bytes(CONN_THREADS, bvh_depth);
-    if (sb_c + sizeof(uint32_t) * CONN_WARPS * CONN_RING + sizeof(float) * 3 * CONN_THREADS + 64 > 227 * 1024) {
+    if (sb_c + sizeof(uint32_t) * CONN_WARPS * CONN_BUF + sizeof(float) * 3 * CONN_THREADS + 64 > 227 * 1024) {
         b2_set_error("BVH depth %d needs more shared memory for traversal stacks than a CTA has", bvh_depth); return B2_ERR_STATE;
     }
     B2_CUDA(cudaFuncSetAttribute(k_light_paths<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_t));
@@ -388,11 +419,12 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
                 const unsigned gb = blocks_for(n_live, EXT_THREADS);
                 tm.begin(primary ? StageTimer::PRIMARY : StageTimer::EXTEND);
                 if (primary) {
-                    if (count) k_extend<true, true><<<gb, EXT_THREADS, sb_t, st>>>(c, n_live, w0);
-                    else k_extend<true, false><<<gb, EXT_THREADS, sb_t, st>>>(c, n_live, w0);
+                    const uint32_t pix0 = (uint32_t) (w0 % npix); const int s0 = (int) (w0 / npix);
+                    if (count) k_extend<true, true><<<gb, EXT_THREADS, sb_t, st>>>(c, n_live, pix0, s0);
+                    else k_extend<true, false><<<gb, EXT_THREADS, sb_t, st>>>(c, n_live, pix0, s0);
                 } else {
-                    if (count) k_extend<false, true><<<gb, EXT_THREADS, sb_t, st>>>(c, n_live, 0);
-                    else k_extend<false, false><<<gb, EXT_THREADS, sb_t, st>>>(c, n_live, 0);
+                    if (count) k_extend<false, true><<<gb, EXT_THREADS, sb_t, st>>>(c, n_live, 0u, 0);
+                    else k_extend<false, false><<<gb, EXT_THREADS, sb_t, st>>>(c, n_live, 0u, 0);
                 }
                 tm.end();
                 B2_CUDA(cudaMemcpyAsync(ws.h_ints, c.n_live_next, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));

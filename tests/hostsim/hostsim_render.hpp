@@ -11,6 +11,7 @@ inline void hs_setup_ctx(RenderCtx &c, const DevScene &sc, const B2Camera &cam, 
     c.sc = sc;
     camera_basis(cam.eye, cam.look_at, cam.view_up, cam.fov, p.width, p.height, c.cam_eye, c.cUL, c.cdx, c.cdy);
     c.W = p.width; c.H = p.height; c.spl = p.spl; c.eye_depth = p.eye_depth; c.light_depth = p.light_depth;
+    c.w_magic = udiv_magic_of((uint32_t) p.width); c.npix_magic = udiv_magic_of((uint32_t) p.width * (uint32_t) p.height);
     c.max_delta = p.max_delta > 0 ? p.max_delta : 256;
     c.sample_offset = p.sample_offset; c.sample_stride = p.sample_stride > 0 ? p.sample_stride : 1;
     c.key = make_uint2((uint32_t) p.seed, (uint32_t) (p.seed >> 32));
@@ -62,7 +63,7 @@ inline void hs_render(const DevScene &sc, const B2Camera &cam, const B2RenderPar
                 int n_next = 0, n_cv = 0;
                 for (int q = 0; q < n_live; ++q) {
                     PathState ps; int path = -1;
-                    if (primary) ps = primary_path(c, w0 + q); else { path = c.live[q]; ps = load_path(c, path); }
+                    if (primary) ps = primary_path(c, (uint32_t) (w0 % ((long long) c.W * c.H)), (int) (w0 / ((long long) c.W * c.H)), (uint32_t) q); else { path = c.live[q]; ps = load_path(c, path); }
                     const HitRec h = closest_hit_bvh<true>(c.sc, ps.ro, ps.rd, stack, 1, &tc);
                     ShadeOut so; shade_step(c, ps, h, so);
                     if (so.has_cv) {

@@ -2,7 +2,7 @@
 import json, sys, time
 import numpy as np
 sys.path.insert(0, ".")
-import path_tracing_b200 as b2
+from path_tracing_b200 import api as b2
 from path_tracing_b200.scene import reference_scene
 
 data = reference_scene("mis")
