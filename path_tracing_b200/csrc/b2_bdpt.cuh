@@ -89,6 +89,7 @@ struct RenderCtx {
     int *live_next; int *n_live_next;
     int *n_paths;       // slots handed out in this batch
     float4 *cv; int *n_cv;   // eye-vertex records created this wave
+    unsigned int *conn_cursor;   // next unclaimed work item of the connection stage (zeroed with n_live_next / n_cv every wave)
     float *film;        // W*H*3 running sums
     unsigned long long *counters;
 };

@@ -118,7 +118,15 @@ B2_NOINLINE float bsdf_pdf(const Mat &m, float3 wo_w, float3 wi_w, float3 N) {
 struct BsdfSample { float3 wi, f; float pdf, new_eta; bool is_delta; };
 // bsdf_sample, :486-562.  On the early returns (pdf = 0) wi/f keep the caller-provided values,
 // like the by-reference outputs of the reference.
-B2_HD void bsdf_sample(const Mat &m, float3 wo_w, float3 N, float u_rr, float u1, float u2, float cur_eta, BsdfSample &s) {
+#ifndef B2_SAMPLE_NOINLINE
+#define B2_SAMPLE_NOINLINE 0
+#endif
+#if B2_SAMPLE_NOINLINE
+B2_NOINLINE
+#else
+B2_HD
+#endif
+void bsdf_sample(const Mat &m, float3 wo_w, float3 N, float u_rr, float u1, float u2, float cur_eta, BsdfSample &s) {
     s.is_delta = false;
     s.new_eta = cur_eta;
     Frame fr = make_frame(N);

@@ -25,7 +25,10 @@ namespace {
 constexpr int EXT_THREADS = 128;      // extend kernel block
 constexpr int CONN_THREADS = 128;     // connect kernel block: 4 independent warps
 constexpr int CONN_WARPS = CONN_THREADS / 32;
-constexpr int CONN_BLOCKS_PER_SM = 4; // persistent grid = 148 SMs x this
+#ifndef B2_CONN_BLOCKS
+#define B2_CONN_BLOCKS 6
+#endif
+constexpr int CONN_BLOCKS_PER_SM = B2_CONN_BLOCKS; // persistent grid = 148 SMs x this (also the register budget: launch bounds)
 constexpr int CONN_CHUNK = 8;         // pool vertices pre-tested per compaction round; the pre-test table is padded to a
                                       // multiple of this with records that never pass, and pool slices are whole chunks
 constexpr int CONN_BUF = 32 * CONN_CHUNK + 32;   // per-warp pending-pair stack: < 32 left over + at most 32 x CONN_CHUNK new
@@ -135,7 +138,7 @@ __global__ void __launch_bounds__(EXT_THREADS) k_extend(RenderCtx c, int n_items
 //   finish   : 32 pending pairs at a time at full lane occupancy (connect_finish), per-owner sums in shared memory,
 //              one film atomicAdd per eye vertex and channel at the end of the item
 template <bool COUNT>
-__global__ void __launch_bounds__(CONN_THREADS) k_connect(RenderCtx c) {
+__global__ void __launch_bounds__(CONN_THREADS, CONN_BLOCKS_PER_SM) k_connect(RenderCtx c) {
     extern __shared__ uint2 s_stack[];                    // CONN_THREADS x stack depth
     __shared__ uint32_t s_buf[CONN_WARPS][CONN_BUF];
     __shared__ float s_acc[CONN_WARPS][3][32];
@@ -154,7 +157,14 @@ __global__ void __launch_bounds__(CONN_THREADS) k_connect(RenderCtx c) {
     unsigned long long n_pairs = 0;
     TravCounters tc{ 0u, 0u };
 
-    for (long long item = (long long) blockIdx.x * CONN_WARPS + warp; item < n_items; item += total_warps) {
+    // Items are claimed from a global cursor, not grid-strided: the work of an item varies with the number of surviving
+    // pairs, and a fixed stride aliases with the image width (2368 warps = 74 rows of 32 groups at 1024 px: every warp
+    // would only ever see one image column; ncu showed max/avg = 1.33 instructions per scheduler).
+    for (;;) {
+        unsigned int item = 0u;
+        if (lane == 0) item = atomicAdd(c.conn_cursor, 1u);
+        item = __shfl_sync(0xffffffffu, item, 0);
+        if ((long long) item >= n_items) break;
         int group, slice;
         if (n_slices == 1) { group = (int) item; slice = 0; }
         else { group = (int) (item / n_slices); slice = (int) (item % n_slices); }
@@ -315,7 +325,7 @@ static void setup_ctx(RenderCtx &c, const DevScene &sc, const B2Camera &cam, con
     c.ray_o = ws.ray_o.p; c.ray_d = ws.ray_d.p; c.thr = ws.thr.p; c.last_pos = ws.last_pos.p; c.last_n = ws.last_n.p;
     c.hist_pe = ws.hist_pe.p; c.hist_pdf = ws.hist_pdf.p;
     c.live = ws.live_a.p; c.live_next = ws.live_b.p; c.n_live_next = ws.ints.p + 1;
-    c.n_cv = ws.ints.p + 2; c.n_paths = ws.ints.p + 3;
+    c.n_cv = ws.ints.p + 2; c.conn_cursor = (unsigned int *) (ws.ints.p + 3); c.n_paths = ws.ints.p + 4;
     c.cv = ws.cv.p; c.film = ws.film.p; c.counters = ws.counters.p;
 }
 
@@ -415,7 +425,7 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
             B2_CUDA(cudaMemsetAsync(c.n_paths, 0, sizeof(int), st));
             bool primary = true;
             while (n_live > 0 && p.eye_depth > 0) {
-                B2_CUDA(cudaMemsetAsync(c.n_live_next, 0, 2 * sizeof(int), st));      // n_live_next, n_cv
+                B2_CUDA(cudaMemsetAsync(c.n_live_next, 0, 3 * sizeof(int), st));      // n_live_next, n_cv, conn_cursor
                 const unsigned gb = blocks_for(n_live, EXT_THREADS);
                 tm.begin(primary ? StageTimer::PRIMARY : StageTimer::EXTEND);
                 if (primary) {
