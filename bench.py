@@ -123,6 +123,21 @@ def cpu_arm(steps, warmup, sample=CPU_SAMPLE):
                       f"({n_samples / 1e6:.2f} M eye samples per step; full workload is {WORKLOAD['width']}x{WORKLOAD['height']} x {WORKLOAD['spp']} spp)"}
 
 
+def measured_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum of all launches of `kernel` in ONE step of this workload, from the newest
+    committed ncu summary (profiles/*_traffic.json, written by tools/ncu_traffic.py from an ncu launch list of
+    tools/render_once.py 64 = the same render as a bench step).  None when no summary is committed."""
+    import glob
+    files = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "*_traffic.json")))
+    if not files:
+        return None, None
+    try:
+        k = json.load(open(files[-1]))["kernels"].get(kernel)
+        return (k["dram_read_bytes"] + k["dram_write_bytes"], "profiles/" + os.path.basename(files[-1])) if k else (None, None)
+    except Exception:
+        return None, None
+
+
 def gpu_arm(args):
     import torch
     import torch.distributed as dist
@@ -208,6 +223,7 @@ def gpu_arm(args):
             "ms_connect": sp["pairs_tested"] * 48 / 32 + sp["shadow_rays"] * (80 + 80) + trav_bytes * (1 - closest_share),
         }[dom]
         hbm, hbm_src = peaks()
+        traffic, traffic_src = measured_traffic({"ms_primary": "k_extend<1, 0>", "ms_extend": "k_extend<0, 0>", "ms_connect": "k_connect<0>"}[dom])
         # e2e: public host-buffer call; scene upload + BVH build + render + film read-back inside the timed region
         host_film = np.zeros((H, W, 3), np.float32)
         e2e_ms = []
@@ -235,7 +251,7 @@ def gpu_arm(args):
             "stages_ms": stages, "stage_total_ms": sp["ms_total"],
             "roofline": {"bound": "hbm", "kernel": {"ms_primary": "k_extend<PRIMARY>", "ms_extend": "k_extend", "ms_connect": "k_connect"}[dom],
                          "achieved": alg / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else None, "peak": hbm, "unit": "GB/s",
-                         "frac": (alg / (dom_ms * 1e-3) / 1e9) / hbm if dom_ms > 0 else None, "traffic": None, "peak_source": hbm_src,
+                         "frac": (alg / (dom_ms * 1e-3) / 1e9) / hbm if dom_ms > 0 else None, "traffic": traffic, "traffic_source": traffic_src, "peak_source": hbm_src,
                          "algorithmic_bytes_per_step": alg, "kernel_ms_per_step": dom_ms},
             "e2e": {"value": W * H * w["spp"] / (e2e * 1e-3) / 1e6, "unit": "Msamples/s", "ms_per_step": e2e,
                     "h2d_bytes_per_step": scene_bytes(sd), "d2h_bytes_per_step": int(host_film.nbytes),
