@@ -164,6 +164,28 @@ typedef struct B2ParsedScene {
 } B2ParsedScene;
 int b2_parse_scene_file(const char *path, B2ParsedScene **out);
 void b2_parsed_scene_free(B2ParsedScene *p);
+
+/* ---- OBJ / MTL meshes (north_star: tiny_obj_loader surface).  The reference vendors include/tiny_obj_loader.h (v2.0.0)
+ * but has no call site and no OBJ -> Triangle adapter; this is that adapter (semantics in csrc/b2_obj.cpp, SURVEY.md
+ * appendix D): faces -> Triangle objects in file order, Kd * map_Kd texel baked per triangle into Material.base_color,
+ * Pr -> roughness, Pm -> metallic, Ni -> eta for transparent illum models, triangles binned into spatial `G` groups. */
+typedef struct B2ObjOptions {
+    int32_t first_obj_id;     /* obj_id of the first face */
+    int32_t first_group;      /* `G` key of the first spatial group; the mesh uses first_group .. first_group + grid*grid - 1 */
+    int32_t group_grid;       /* g: triangles are binned into g x g groups over the x-z extent; 0 = round(sqrt(sqrt(n) / 4)) */
+    float   default_color[3]; /* faces without a usemtl material */
+    float   default_roughness;
+    int32_t reserved[4];
+} B2ObjOptions;
+void b2_obj_default_options(B2ObjOptions *opt);
+/* Triangles + materials of one OBJ file (camera, lights, spheres of the result are empty). */
+int b2_load_obj(const char *obj_path, const B2ObjOptions *opt, B2ParsedScene **out);
+/* The reference grammar plus one directive, `O <path.obj>` (path relative to the scene file): the mesh is spliced in at
+ * that point (obj ids continue, groups start at the current `G` value).  Only this entry point knows the directive:
+ * the reference's own loop (main_cli.cpp:99-141, mirrored by b2_parse_scene_file) would read the path's letters as
+ * directives. */
+#define B2_PARSE_OBJ_DIRECTIVE 1
+int b2_parse_scene_file_ex(const char *path, int flags, B2ParsedScene **out);
 /* clamp [0,1] -> pow(1/2.2) -> *255 truncated, RGB order, rows top to bottom (main_cli.cpp:225-243) */
 int b2_film_to_rgb8(const float *film_rgb, int32_t width, int32_t height, uint8_t *rgb8);
 /* format from the extension: .ppm (P6), .png (zlib deflate), .pfm (raw float) */

@@ -56,11 +56,19 @@ class ParsedScene(C.Structure):
 
 
 # every symbol include/b2pt.h declares (tests check that the built library exports all of them)
+class ObjOptions(C.Structure):
+    _fields_ = [("first_obj_id", C.c_int32), ("first_group", C.c_int32), ("group_grid", C.c_int32),
+                ("default_color", C.c_float * 3), ("default_roughness", C.c_float), ("reserved", C.c_int32 * 4)]
+
+
+PARSE_OBJ_DIRECTIVE = 1
+
 SYMBOLS = [
     "b2_last_error", "b2_device_count", "b2_version", "b2_scene_create", "b2_scene_build_bvh", "b2_scene_bvh_info",
     "b2_scene_destroy", "b2_intersect", "b2_intersect_device", "b2_intersect_counters", "b2_render_bdpt",
     "b2_render_bdpt_device", "b2_render_bdpt_multi", "b2_light_pool", "b2_bsdf_evaluate", "b2_bsdf_pdf", "b2_bsdf_sample", "b2_mis_weight",
     "b2_philox", "b2_parse_scene_file", "b2_parsed_scene_free", "b2_film_to_rgb8", "b2_write_image",
+    "b2_obj_default_options", "b2_load_obj", "b2_parse_scene_file_ex",
 ]
 
 _lib = None
@@ -100,6 +108,11 @@ def lib():
         L.b2_philox.argtypes = [sz, vp, vp, vp, vp]
         L.b2_parse_scene_file.argtypes = [C.c_char_p, C.POINTER(C.POINTER(ParsedScene))]
         L.b2_parsed_scene_free.argtypes = [C.POINTER(ParsedScene)]
+        L.b2_parsed_scene_free.restype = None
+        L.b2_obj_default_options.argtypes = [C.POINTER(ObjOptions)]
+        L.b2_obj_default_options.restype = None
+        L.b2_load_obj.argtypes = [C.c_char_p, C.POINTER(ObjOptions), C.POINTER(C.POINTER(ParsedScene))]
+        L.b2_parse_scene_file_ex.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.POINTER(ParsedScene))]
         L.b2_film_to_rgb8.argtypes = [vp, C.c_int32, C.c_int32, vp]
         L.b2_write_image.argtypes = [C.c_char_p, vp, C.c_int32, C.c_int32]
         _lib = L

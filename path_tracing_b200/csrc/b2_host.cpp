@@ -22,7 +22,12 @@ std::istream &operator>>(std::istream &is, V3 &v) { is >> v.x >> v.y >> v.z; ret
 void put3(float *d, const V3 &v) { d[0] = v.x; d[1] = v.y; d[2] = v.z; }
 }  // namespace
 
-extern "C" int b2_parse_scene_file(const char *path, B2ParsedScene **out) {
+bool b2_obj_append(const std::string &obj_path, const B2ObjOptions &opt, std::vector<B2Tri> &tris, std::vector<B2Material> &mats,
+                   int &obj_id, int &next_group);
+
+extern "C" int b2_parse_scene_file(const char *path, B2ParsedScene **out) { return b2_parse_scene_file_ex(path, 0, out); }
+
+extern "C" int b2_parse_scene_file_ex(const char *path, int flags, B2ParsedScene **out) {
     if (!path || !out) { b2_set_error("NULL argument"); return B2_ERR_INVALID; }
     *out = nullptr;
     std::ifstream input(path);
@@ -61,6 +66,15 @@ extern "C" int b2_parse_scene_file(const char *path, B2ParsedScene **out) {
             cur_mat = -1;
         }
         else if (t == 'G') { input >> group_id; }
+        else if (t == 'O' && (flags & B2_PARSE_OBJ_DIRECTIVE)) {      // new directive, not part of the reference grammar
+            std::string rel; input >> rel;
+            std::string p(path); const size_t k = p.find_last_of('/');
+            const std::string full = (rel.empty() || rel[0] == '/' || k == std::string::npos) ? rel : p.substr(0, k + 1) + rel;
+            B2ObjOptions o; b2_obj_default_options(&o);
+            o.default_color[0] = mtl.base_color[0]; o.default_color[1] = mtl.base_color[1]; o.default_color[2] = mtl.base_color[2];
+            o.default_roughness = mtl.roughness;
+            if (!b2_obj_append(full, o, tris, mats, obj_id, group_id)) return B2_ERR_IO;
+        }
         else if (t == '/') {
             input >> t;
             if (t == '/') { std::string trash; std::getline(input, trash); continue; }

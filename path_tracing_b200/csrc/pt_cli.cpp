@@ -60,7 +60,7 @@ int main(int argc, char **argv) {
     if (device != "gpu") { fprintf(stderr, "[Error] device '%s': this library has no CPU path (the CPU integrator is the reference's cpu_bdpt.cpp)\n", device.c_str()); return 2; }
 
     B2ParsedScene *ps = nullptr;
-    if (b2_parse_scene_file(input_file.c_str(), &ps) != B2_OK) { fprintf(stderr, "[Error] Cannot open input file: %s\n", input_file.c_str()); return -1; }
+    if (b2_parse_scene_file_ex(input_file.c_str(), B2_PARSE_OBJ_DIRECTIVE, &ps) != B2_OK) { fprintf(stderr, "[Error] Cannot open input file: %s\n", input_file.c_str()); return -1; }
     if (width <= 0) width = ps->width;
     if (height <= 0) height = ps->height;
     printf("Eye Position: %g %g %g\nResolution: %d x %d\nTriangle: %zu\nBall: %zu\nLight: %zu\n", ps->camera.eye[0], ps->camera.eye[1], ps->camera.eye[2],

@@ -137,3 +137,90 @@ def random_rays(n, lo, hi, seed=7):
     d /= np.linalg.norm(d, axis=1, keepdims=True)
     p2 = rng.uniform(lo, hi, (n, 3)).astype(np.float32)
     return org, d, p2
+
+
+# ---- C3: the same kind of scene as an OBJ + MTL + PPM textures + scene header, for the OBJ adapter (b2_load_obj) ----
+def _write_ppm(path, img):
+    img = np.clip(np.asarray(img) * 255.0 + 0.5, 0, 255).astype(np.uint8)
+    with open(path, "wb") as f:
+        f.write(b"P6\n%d %d\n255\n" % (img.shape[1], img.shape[0]))
+        f.write(img.tobytes())
+
+
+def write_obj_scene(outdir, n_tris=1 << 20, seed=1, n_blobs=12, width=1920, height=1080, tex_size=1024):
+    """Writes mesh.obj, mesh.mtl, checker.ppm, noise.ppm and scene.txt (reference grammar + `O mesh.obj`) into outdir.
+    ~n_tris triangles: displaced terrain + n_blobs displaced spheres + 5 walls; Kd from the two procedural textures,
+    Pr in {0.2 .. 1.0}, Pm in {0, 0.9}.  Returns the path of scene.txt."""
+    import os
+    os.makedirs(outdir, exist_ok=True)
+    rng = np.random.default_rng(seed)
+    yy, xx = np.meshgrid(np.linspace(0, 1, tex_size, endpoint=False), np.linspace(0, 1, tex_size, endpoint=False), indexing="ij")
+    chk = (((xx * 16).astype(int) + (yy * 16).astype(int)) % 2).astype(np.float64)
+    checker = np.stack([0.35 + 0.6 * chk, 0.35 + 0.55 * chk, 0.3 + 0.5 * chk], -1)
+    nz = _value_noise(xx, yy, seed + 5, 4)
+    noise = np.stack([0.25 + 0.7 * nz, 0.3 + 0.65 * nz, 0.2 + 0.5 * nz], -1)
+    _write_ppm(os.path.join(outdir, "checker.ppm"), checker)
+    _write_ppm(os.path.join(outdir, "noise.ppm"), noise)
+    mtl = [("terrain", (0.75, 0.9, 0.6), 1.0, 0.0, "noise.ppm"), ("blob_a", (0.95, 0.6, 0.4), 0.4, 0.0, "checker.ppm"),
+           ("blob_b", (0.95, 0.85, 0.55), 0.2, 0.9, None), ("blob_c", (0.5, 0.65, 0.95), 0.6, 0.0, "noise.ppm"), ("wall", (0.7, 0.7, 0.7), 1.0, 0.0, None)]
+    with open(os.path.join(outdir, "mesh.mtl"), "w") as f:
+        for name, kd, pr, pm, tex in mtl:
+            f.write(f"newmtl {name}\nKd {kd[0]} {kd[1]} {kd[2]}\nPr {pr}\nPm {pm}\nNi 1.0\nillum 2\n")
+            if tex:
+                f.write(f"map_Kd {tex}\n")
+            f.write("\n")
+    n_terrain = n_tris // 2
+    n = max(int(np.sqrt(n_terrain / 2)), 2)
+
+    def terrain(u, v):
+        h = 0.35 * _value_noise(u, v, seed + 11, 5) + 0.02 * _value_noise(u * 8, v * 8, seed + 12, 2)
+        return np.stack([(u - 0.5) * 4.0, h - 0.6, (v - 0.5) * 4.0 + 2.0], axis=-1)
+
+    grids = [("terrain", n, n, terrain)]
+    per_blob = max((n_tris - 2 * n * n) // max(n_blobs, 1), 8)
+    m = max(int(np.sqrt(per_blob / 4)), 2)
+    for bi in range(n_blobs):
+        c = np.array([rng.uniform(-1.6, 1.6), rng.uniform(-0.1, 0.7), rng.uniform(0.6, 3.4)])
+        r = rng.uniform(0.12, 0.3)
+
+        def blob(u, v, c=c, r=r, bi=bi):
+            th, ph = u * 2 * np.pi, v * np.pi
+            d = 1.0 + 0.15 * (_value_noise(u, v, seed + 100 + bi, 3) - 0.5)
+            return np.stack([c[0] + r * d * np.sin(ph) * np.cos(th), c[1] + r * d * np.cos(ph), c[2] + r * d * np.sin(ph) * np.sin(th)], axis=-1)
+
+        grids.append((("blob_a", "blob_b", "blob_c")[bi % 3], 2 * m, m, blob))
+    n_faces = 0
+    with open(os.path.join(outdir, "mesh.obj"), "w") as f:
+        f.write("# synthetic C3 scene (path_tracing_b200.gen.write_obj_scene)\nmtllib mesh.mtl\n")
+        base = 1
+        for name, nx, ny, fn in grids:
+            u, v = np.meshgrid(np.linspace(0, 1, nx + 1), np.linspace(0, 1, ny + 1), indexing="ij")
+            P = fn(u, v).astype(np.float32).reshape(-1, 3)
+            np.savetxt(f, P, fmt="v %.9g %.9g %.9g")
+            np.savetxt(f, np.stack([u.reshape(-1), v.reshape(-1)], 1).astype(np.float32), fmt="vt %.9g %.9g")
+            idx = (np.arange((nx + 1) * (ny + 1)).reshape(nx + 1, ny + 1) + base)
+            a, b, c, d = idx[:-1, :-1].reshape(-1), idx[1:, :-1].reshape(-1), idx[1:, 1:].reshape(-1), idx[:-1, 1:].reshape(-1)
+            F = np.concatenate([np.stack([a, b, c], 1), np.stack([a, c, d], 1)])
+            T = P[F - base]
+            keep = np.linalg.norm(np.cross(T[:, 1] - T[:, 0], T[:, 2] - T[:, 0]), axis=1) > 1e-12   # collapsed pole triangles
+            F = F[keep]
+            f.write(f"usemtl {name}\n")
+            np.savetxt(f, np.concatenate([F, F], 1)[:, [0, 3, 1, 4, 2, 5]], fmt="f %d/%d %d/%d %d/%d")
+            base += (nx + 1) * (ny + 1)
+            n_faces += len(F)
+        X0, X1, Y0, Y1, Z0, Z1 = -2.2, 2.2, -0.8, 2.2, -0.2, 4.4
+        quads = [((X0, Y0, Z0), (X1, Y0, Z0), (X1, Y0, Z1), (X0, Y0, Z1)), ((X0, Y0, Z1), (X1, Y0, Z1), (X1, Y1, Z1), (X0, Y1, Z1)),
+                 ((X0, Y0, Z0), (X0, Y0, Z1), (X0, Y1, Z1), (X0, Y1, Z0)), ((X1, Y0, Z0), (X1, Y1, Z0), (X1, Y1, Z1), (X1, Y0, Z1)),
+                 ((X0, Y1, Z0), (X0, Y1, Z1), (X1, Y1, Z1), (X1, Y1, Z0))]
+        f.write("usemtl wall\n")
+        for q in quads:
+            for p in q:
+                f.write("v %.9g %.9g %.9g\n" % p)
+            f.write("f -4 -3 -2\nf -4 -2 -1\n")
+            n_faces += 2
+    scene = os.path.join(outdir, "scene.txt")
+    with open(scene, "w") as f:
+        f.write(f"// synthetic C3 scene, {n_faces} triangles\nE 0 0.9 -0.15\nV 0 -0.2 2.2  0 1 0\nF 55\nR {width} {height}\n")
+        f.write("L 0 2 2  0 -1 0.05  6 6 6  70 0 0.05\nL -1.5 1.8 0.8  0.4 -1 0.3  4 3 2  55 0 0.05\nL 1.5 1.8 3.2  -0.4 -1 -0.3  2 3 4  55 0 0.05\n")
+        f.write("G 0\nO mesh.obj\n")
+    return scene

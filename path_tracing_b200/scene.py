@@ -18,10 +18,29 @@ class SceneData:
 
     # -- the reference's text grammar, parsed by the C++ host code behind the C ABI (no GPU needed) --
     @classmethod
-    def from_file(cls, path):
+    def from_file(cls, path, obj_directive=False):
+        """The reference grammar (main_cli.cpp:99-141).  obj_directive=True also accepts `O mesh.obj` lines (new)."""
         L = A.lib()
         pp = C.POINTER(A.ParsedScene)()
-        A.check(L.b2_parse_scene_file(str(path).encode(), C.byref(pp)))
+        A.check(L.b2_parse_scene_file_ex(str(path).encode(), A.PARSE_OBJ_DIRECTIVE if obj_directive else 0, C.byref(pp)))
+        return cls._from_parsed(pp)
+
+    @classmethod
+    def from_obj(cls, path, group_grid=0, first_obj_id=0, first_group=0, default_color=(0.8, 0.8, 0.8), default_roughness=1.0):
+        """Triangles + materials of a Wavefront OBJ (+ MTL, PPM/PFM map_Kd) through b2_load_obj; no camera / lights."""
+        L = A.lib()
+        o = A.ObjOptions()
+        L.b2_obj_default_options(C.byref(o))
+        o.group_grid, o.first_obj_id, o.first_group = int(group_grid), int(first_obj_id), int(first_group)
+        o.default_color[0], o.default_color[1], o.default_color[2] = [float(x) for x in default_color]
+        o.default_roughness = float(default_roughness)
+        pp = C.POINTER(A.ParsedScene)()
+        A.check(L.b2_load_obj(str(path).encode(), C.byref(o), C.byref(pp)))
+        return cls._from_parsed(pp)
+
+    @classmethod
+    def _from_parsed(cls, pp):
+        L = A.lib()
         p = pp.contents
 
         def grab(addr, n, dt):
