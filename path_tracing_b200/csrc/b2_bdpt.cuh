@@ -435,12 +435,12 @@ B2_HD bool pretest_rec(float3 ev_pos, float3 ev_n, float4 r0, float4 r1, float4 
     if (r0.w > -1.5f) pass = pass && !(-dot3(mk3(r2), d) < r0.w * fast_sqrt(dist2));
     return pass;
 }
-// Returns the (validated, clamped) contribution, zero if the pair contributes nothing.  n_shadow / n_path count
-// visibility queries (:424) and connections that reach the MIS evaluation (:431).
-template <bool COUNT>
-B2_HD float3 connect_finish(const RenderCtx &c, const EyeVtx &ev, int lv_index, uint2 *stack, int sstride, TravCounters *tc,
-                            uint32_t &n_shadow, uint32_t &n_path) {
-    const float3 zero = mk3(0.0f, 0.0f, 0.0f);
+// connect_finish in three steps, so that the connection kernel can run each at full lane occupancy with the shadow
+// rays of a whole warp traced in between (k_connect):
+//   connect_prepare : BSDFs, black skip (:411-422), shadow ray (:424), pc = everything of :433 but the MIS weight
+//   (visibility)    : occluded_bvh / any_step on the shadow ray
+//   connect_weight  : MIS weight (:431), validity + clamp (:435-437)
+B2_HD bool connect_prepare(const RenderCtx &c, const EyeVtx &ev, int lv_index, ShadowRay &sr, float3 &pc) {
     const LightVtx lv = load_lv(c.pool, lv_index);
     const float3 d_vec = lv.pos - ev.pos;
     const float dist2 = dot3(d_vec, d_vec);
@@ -456,15 +456,33 @@ B2_HD float3 connect_finish(const RenderCtx &c, const EyeVtx &ev, int lv_index, 
         const float3 wo_l = normalize3(mk3(c.pool[B2_LV_F4 * (lv_index - 1)]) - lv.pos);
         fL = bsdf_evaluate(lv.mtl, wo_l, mwi, lv.n);
     }
-    if ((fE.x <= 0.0f && fE.y <= 0.0f && fE.z <= 0.0f) || (fL.x <= 0.0f && fL.y <= 0.0f && fL.z <= 0.0f)) return zero;
-    const ShadowRay sr = make_shadow_ray(x3_add(ev.pos, x3_muls(ev.n, B2_EPSILON)), x3_add(lv.pos, x3_muls(lv.n, B2_EPSILON)));   // :424
-    n_shadow++;
-    if (occluded_bvh<COUNT>(c.sc, sr.o, sr.d, sr.tmax, stack, sstride, tc)) return zero;
-    const float G = fast_div(cosE * cosL, fmaxf(dist2, 1e-4f));                      // :427
+    if ((fE.x <= 0.0f && fE.y <= 0.0f && fE.z <= 0.0f) || (fL.x <= 0.0f && fL.y <= 0.0f && fL.z <= 0.0f)) return false;
+    sr = make_shadow_ray(x3_add(ev.pos, x3_muls(ev.n, B2_EPSILON)), x3_add(lv.pos, x3_muls(lv.n, B2_EPSILON)));   // :424
+    const float G = fast_div(cosE * cosL, fmaxf(dist2, 1e-4f));              // :427
+    pc = ev.thr * fE * G * fL * lv.thr;                                       // :433 without w (transmittance == 1 here)
+    return true;
+}
+B2_HD float3 connect_weight(const RenderCtx &c, const EyeVtx &ev, int lv_index, float3 pc) {
+    const LightVtx lv = load_lv(c.pool, lv_index);
+    const float3 d_vec = lv.pos - ev.pos;
+    const float dist2 = dot3(d_vec, d_vec);
+    const int t_idx = lv_index % c.light_depth;
     const RenderEyeAcc EA{ c, ev };
     const RenderLightAcc LA{ c, lv, lv_index - t_idx };
     const float w = mis_weight_core(EA, ev.depth, LA, t_idx, d_vec, dist2, c.cam_eye);   // :431
+    const float3 contrib = pc * w;
+    return valid_color(contrib) ? clamp_radiance(contrib, 15.0f) : mk3(0.0f, 0.0f, 0.0f);   // :435-437
+}
+// Returns the (validated, clamped) contribution, zero if the pair contributes nothing.  n_shadow / n_path count
+// visibility queries (:424) and connections that reach the MIS evaluation (:431).
+template <bool COUNT>
+B2_HD float3 connect_finish(const RenderCtx &c, const EyeVtx &ev, int lv_index, uint2 *stack, int sstride, TravCounters *tc,
+                            uint32_t &n_shadow, uint32_t &n_path) {
+    const float3 zero = mk3(0.0f, 0.0f, 0.0f);
+    ShadowRay sr; float3 pc;
+    if (!connect_prepare(c, ev, lv_index, sr, pc)) return zero;
+    n_shadow++;
+    if (occluded_bvh<COUNT>(c.sc, sr.o, sr.d, sr.tmax, stack, sstride, tc)) return zero;
     n_path++;
-    const float3 contrib = ev.thr * fE * G * fL * lv.thr * w;                 // :433 (transmittance == 1 here)
-    return valid_color(contrib) ? clamp_radiance(contrib, 15.0f) : zero;      // :435-437
+    return connect_weight(c, ev, lv_index, pc);
 }

@@ -31,7 +31,6 @@ constexpr int CONN_WARPS = CONN_THREADS / 32;
 constexpr int CONN_BLOCKS_PER_SM = B2_CONN_BLOCKS; // persistent grid = 148 SMs x this (also the register budget: launch bounds)
 constexpr int CONN_CHUNK = 8;         // pool vertices pre-tested per compaction round; the pre-test table is padded to a
                                       // multiple of this with records that never pass, and pool slices are whole chunks
-constexpr int CONN_BUF = 32 * CONN_CHUNK + 32;   // per-warp pending-pair stack: < 32 left over + at most 32 x CONN_CHUNK new
 
 __device__ __forceinline__ uint32_t lanemask_lt() { uint32_t m; asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m)); return m; }
 
@@ -129,29 +128,45 @@ __global__ void __launch_bounds__(EXT_THREADS) k_extend(RenderCtx c, int n_items
 }
 
 // Connection stage.  Work item = (group of 32 eye-vertex records) x (slice of the active pool, whole chunks);
-// persistent warps pull items grid-stride.  The pool is sliced only when there are too few eye vertices to fill the
-// machine (late waves), so that the serial latency of a nearly empty wave stays short.  No block-level synchronisation.
-//   pre-test : every lane owns one eye vertex and tests it against CONN_CHUNK pool records (warp-uniform addresses, the
-//              loop is fully unrolled: 2 broadcast loads + ~16 FP instructions per pair), collecting a bit per record
-//   compact  : only if any lane has a bit set: warp scan of the pop-counts, (owner lane, pool index) pairs pushed on
-//              the warp's shared-memory stack
-//   finish   : 32 pending pairs at a time at full lane occupancy (connect_finish), per-owner sums in shared memory,
-//              one film atomicAdd per eye vertex and channel at the end of the item
+// persistent warps claim items from a global cursor.  The pool is sliced only when there are too few eye vertices to
+// fill the machine (late waves), so that the serial latency of a nearly empty wave stays short.  No block-level
+// synchronisation.  Per item a warp runs ONE loop that picks, warp-uniformly, the next of four phases:
+//   weight   : >= 32 visible pairs queued: MIS weight, clamp, per-owner sums in shared memory (connect_weight)
+//   pre-test : the pair stack runs low and pool chunks remain: every lane tests ITS eye vertex against CONN_CHUNK pool
+//              records (warp-uniform addresses, fully unrolled: 2 broadcast loads + ~16 FP instructions per pair), one
+//              bit per record; survivors go on the PAIR stack (owner lane, pool index), pool vertex by pool vertex
+//   refill   : >= B2_REFILL_MIN lanes have no shadow ray: they pop pairs and run connect_prepare (BSDFs, black skip,
+//              shadow ray, contribution without the MIS weight); the ray stays in the lane's registers
+//   trace    : one any-hit step (wide node + its leaf triangles) for every lane holding a ray; an occluded ray frees
+//              its lane, a visible one is queued for the weight phase
+// so a lane whose ray is decided gets the next pair while the others keep walking (occluded rays end after a few
+// steps, visible ones walk the whole segment; with prepare -> trace -> weight done per 32 pairs ncu showed 13 of 32
+// lanes active in the node tests of the 1 M-triangle scene).  One film atomicAdd per eye vertex and channel per item.
+constexpr int CONN_LOW = 32;          // pre-test another chunk while fewer pairs than this are stacked
+constexpr int CONN_MQ = 64;           // visible-pair queue: < 32 left + 32 new per trace step
+#ifndef B2_REFILL_MIN
+#define B2_REFILL_MIN 20              // idle lanes that trigger a refill (connect_prepare then runs at >= this occupancy)
+#endif
+struct ConnSmem {
+    uint32_t pair[CONN_LOW + 32 * CONN_CHUNK];
+    float mq_px[CONN_MQ], mq_py[CONN_MQ], mq_pz[CONN_MQ]; uint32_t mq_e[CONN_MQ];
+    float acc[3][32];
+};
 template <bool COUNT>
 __global__ void __launch_bounds__(CONN_THREADS, CONN_BLOCKS_PER_SM) k_connect(RenderCtx c) {
     extern __shared__ uint2 s_stack[];                    // CONN_THREADS x stack depth
-    __shared__ uint32_t s_buf[CONN_WARPS][CONN_BUF];
-    __shared__ float s_acc[CONN_WARPS][3][32];
+    __shared__ ConnSmem s_q[CONN_WARPS];
     const int n_cv = *c.n_cv, n_act = *c.n_pool_active;
     if (n_cv <= 0 || n_act <= 0) return;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t lt = lanemask_lt();
     const int n_groups = (n_cv + 31) >> 5;
     const int n_chunks = (n_act + CONN_CHUNK - 1) / CONN_CHUNK;
     const int total_warps = gridDim.x * CONN_WARPS;
     const int n_slices = max(1, min(total_warps / n_groups, n_chunks));
     const long long n_items = (long long) n_groups * n_slices;
-    uint32_t *buf = s_buf[warp];
-    float *acc_x = s_acc[warp][0], *acc_y = s_acc[warp][1], *acc_z = s_acc[warp][2];
+    ConnSmem &Q = s_q[warp];
+    uint2 *stack = s_stack + threadIdx.x;
     const float4 *__restrict__ pre = c.pre;
     uint32_t n_shadow = 0, n_path = 0;
     unsigned long long n_pairs = 0;
@@ -174,59 +189,98 @@ __global__ void __launch_bounds__(CONN_THREADS, CONN_BLOCKS_PER_SM) k_connect(Re
         float3 my_pos = mk3(0, 0, 0), my_n = mk3(0, 0, 0);            // a zero normal never passes: idle lanes need no branch
         uint32_t my_pixel = 0u;
         if (valid) { const float4 f0 = c.cv[B2_CV_F4 * q]; my_pos = mk3(f0); my_pixel = __float_as_uint(f0.w) >> 8; my_n = mk3(c.cv[B2_CV_F4 * q + 1]); }
-        acc_x[lane] = 0.0f; acc_y[lane] = 0.0f; acc_z[lane] = 0.0f;
+        Q.acc[0][lane] = 0.0f; Q.acc[1][lane] = 0.0f; Q.acc[2][lane] = 0.0f;
         __syncwarp();
-        int n_buf = 0;                                    // warp-uniform stack height
+        int n_buf = 0, n_mq = 0, ch = ch_begin;            // warp-uniform
+        bool busy = false;                                 // this lane holds a shadow ray: tv, pc, e
+        AnyTrav tv; float3 pc = mk3(0, 0, 0); uint32_t e = 0u;
 
-        auto drain = [&](int count) {                     // finish the top `count` <= 32 entries
-            if (lane < count) {
-                const uint32_t e = buf[n_buf - count + lane];
-                const int owner = (int) (e >> 27), lvi = (int) (e & 0x7ffffffu);
-                const EyeVtx ev = load_cv(c.cv, q0 + owner);
-                const float3 r = connect_finish<COUNT>(c, ev, lvi, s_stack + threadIdx.x, CONN_THREADS, &tc, n_shadow, n_path);
-                if (r.x != 0.0f) atomicAdd(&acc_x[owner], r.x);
-                if (r.y != 0.0f) atomicAdd(&acc_y[owner], r.y);
-                if (r.z != 0.0f) atomicAdd(&acc_z[owner], r.z);
-            }
-            n_buf -= count;
-            __syncwarp();
-        };
-
-        for (int ch = ch_begin;; ++ch) {                  // one extra pass after the last chunk empties the stack
-            const bool last = ch >= ch_end;
-            while (n_buf >= 32 || (last && n_buf > 0)) drain(min(32, n_buf));     // the only call site: connect_finish is big
-            if (last) break;
-            const float4 *__restrict__ rec = pre + (size_t) B2_PRE_F4 * CONN_CHUNK * ch;
-            uint32_t mask = 0u;
-#pragma unroll
-            for (int k = 0; k < CONN_CHUNK; ++k) {
-                const float4 r0 = __ldg(&rec[B2_PRE_F4 * k]), r1 = __ldg(&rec[B2_PRE_F4 * k + 1]);
-                const float3 d = mk3(r0) - my_pos;
-                const float dist2 = dot3(d, d);
-                bool pass = !(dist2 < 1e-6f) && dot3(my_n, d) > 0.0f && dot3(mk3(r1), d) < 0.0f;
-                if (r0.w > -1.5f && pass) {                // spot-cone gate (warp-uniform first operand)
-                    const float4 r2 = __ldg(&rec[B2_PRE_F4 * k + 2]);
-                    pass = !(-dot3(mk3(r2), d) < r0.w * fast_sqrt(dist2));
+        for (;;) {
+            const uint32_t busy_m = __ballot_sync(0xffffffffu, busy);
+            const int n_idle = 32 - __popc(busy_m);
+            if (n_mq >= 32 || (n_mq > 0 && busy_m == 0u && n_buf == 0 && ch >= ch_end)) {
+                // ---- weight: top min(32, n_mq) visible pairs ----
+                const int count = min(32, n_mq);
+                if (lane < count) {
+                    const int k = n_mq - count + lane;
+                    const uint32_t ee = Q.mq_e[k];
+                    const int owner = (int) (ee >> 27);
+                    const EyeVtx ev = load_cv(c.cv, q0 + owner);
+                    const float3 r = connect_weight(c, ev, (int) (ee & 0x7ffffffu), mk3(Q.mq_px[k], Q.mq_py[k], Q.mq_pz[k]));
+                    n_path++;
+                    if (r.x != 0.0f) atomicAdd(&Q.acc[0][owner], r.x);
+                    if (r.y != 0.0f) atomicAdd(&Q.acc[1][owner], r.y);
+                    if (r.z != 0.0f) atomicAdd(&Q.acc[2][owner], r.z);
                 }
-                mask |= (pass ? 1u : 0u) << k;
-            }
-            if (__ballot_sync(0xffffffffu, mask != 0u)) {
-                const int cnt = __popc(mask);
-                int incl = cnt;
-#pragma unroll
-                for (int dlt = 1; dlt < 32; dlt <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, dlt); if (lane >= dlt) incl += t; }
-                int pos = n_buf + incl - cnt;
-                n_buf += __shfl_sync(0xffffffffu, incl, 31);
-                while (mask) {
-                    const int k = __ffs((int) mask) - 1;
-                    mask &= mask - 1u;
-                    buf[pos++] = ((uint32_t) lane << 27) | __float_as_uint(__ldg(&rec[B2_PRE_F4 * k + 1].w));
-                }
+                n_mq -= count;
                 __syncwarp();
-            }
+            } else if (n_buf < CONN_LOW && ch < ch_end) {
+                // ---- pre-test one chunk of pool records ----
+                const float4 *__restrict__ rec = pre + (size_t) B2_PRE_F4 * CONN_CHUNK * ch;
+                ++ch;
+                uint32_t mask = 0u;
+#pragma unroll
+                for (int k = 0; k < CONN_CHUNK; ++k) {
+                    const float4 r0 = __ldg(&rec[B2_PRE_F4 * k]), r1 = __ldg(&rec[B2_PRE_F4 * k + 1]);
+                    const float3 d = mk3(r0) - my_pos;
+                    const float dist2 = dot3(d, d);
+                    bool pass = !(dist2 < 1e-6f) && dot3(my_n, d) > 0.0f && dot3(mk3(r1), d) < 0.0f;
+                    if (r0.w > -1.5f && pass) {            // spot-cone gate (warp-uniform first operand)
+                        const float4 r2 = __ldg(&rec[B2_PRE_F4 * k + 2]);
+                        pass = !(-dot3(mk3(r2), d) < r0.w * fast_sqrt(dist2));
+                    }
+                    mask |= (pass ? 1u : 0u) << k;
+                }
+                if (__ballot_sync(0xffffffffu, mask != 0u)) {
+                    // pool vertex by pool vertex, owners in lane order: consecutive entries are shadow rays from
+                    // neighbouring eye vertices to the same pool vertex, which keeps the traversal of a warp coherent
+#pragma unroll
+                    for (int k = 0; k < CONN_CHUNK; ++k) {
+                        const bool mine = (mask >> k) & 1u;
+                        const uint32_t m = __ballot_sync(0xffffffffu, mine);
+                        if (mine) Q.pair[n_buf + __popc(m & lt)] = ((uint32_t) lane << 27) | __float_as_uint(__ldg(&rec[B2_PRE_F4 * k + 1].w));
+                        n_buf += __popc(m);
+                    }
+                    __syncwarp();
+                }
+            } else if (n_buf > 0 && (n_idle >= B2_REFILL_MIN || busy_m == 0u)) {
+                // ---- refill: idle lanes pop pairs and prepare their shadow rays ----
+                const int rank = __popc(~busy_m & lt);
+                if (!busy && rank < n_buf) {
+                    e = Q.pair[n_buf - 1 - rank];
+                    const EyeVtx ev = load_cv(c.cv, q0 + (int) (e >> 27));
+                    ShadowRay sr;
+                    if (connect_prepare(c, ev, (int) (e & 0x7ffffffu), sr, pc)) {
+                        n_shadow++;
+                        any_init(tv, c.sc, sr.o, sr.d, sr.tmax);
+                        busy = true;
+                    }
+                }
+                n_buf -= min(n_idle, n_buf);
+                __syncwarp();
+            } else if (busy_m != 0u) {
+                // ---- trace: one step per lane that holds a ray ----
+                bool visible = false;
+                if (busy) {
+                    int r = any_step<COUNT>(c.sc, tv, stack, CONN_THREADS, &tc);
+                    if (r == B2_TRAV_EXHAUSTED) {
+                        if (occluded_spheres(c.sc, tv.r.o, tv.r.d, 1e-3f, tv.tmax)) r = B2_TRAV_HIT; else visible = true;
+                    }
+                    if (r != B2_TRAV_CONTINUE) busy = false;
+                }
+                const uint32_t vm = __ballot_sync(0xffffffffu, visible);
+                if (vm) {
+                    if (visible) {
+                        const int k = n_mq + __popc(vm & lt);
+                        Q.mq_px[k] = pc.x; Q.mq_py[k] = pc.y; Q.mq_pz[k] = pc.z; Q.mq_e[k] = e;
+                    }
+                    n_mq += __popc(vm);
+                    __syncwarp();
+                }
+            } else break;                                  // nothing stacked, nothing in flight, no chunk left, queue empty
         }
         if (valid) {
-            const float3 r = mk3(acc_x[lane], acc_y[lane], acc_z[lane]);
+            const float3 r = mk3(Q.acc[0][lane], Q.acc[1][lane], Q.acc[2][lane]);
             if (r.x != 0.0f) atomicAdd(&c.film[3 * my_pixel], r.x);
             if (r.y != 0.0f) atomicAdd(&c.film[3 * my_pixel + 1], r.y);
             if (r.z != 0.0f) atomicAdd(&c.film[3 * my_pixel + 2], r.z);
@@ -370,7 +424,7 @@ static int set_smem_limits(int bvh_depth) {
     B2_CUDA(cudaGetDevice(&dev));
     if (dev < 64 && bvh_depth + 1 <= configured[dev]) return B2_OK;
     const size_t sb_t = stack_bytes(EXT_THREADS, bvh_depth), sb_c = stack_bytes(CONN_THREADS, bvh_depth);
-    if (sb_c + sizeof(uint32_t) * CONN_WARPS * CONN_BUF + sizeof(float) * 3 * CONN_THREADS + 64 > 227 * 1024) {
+    if (sb_c + sizeof(ConnSmem) * CONN_WARPS + 64 > 227 * 1024) {
         b2_set_error("BVH depth %d needs more shared memory for traversal stacks than a CTA has", bvh_depth); return B2_ERR_STATE;
     }
     B2_CUDA(cudaFuncSetAttribute(k_light_paths<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_t));
