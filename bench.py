@@ -128,7 +128,9 @@ def measured_traffic(kernel):
     committed ncu summary (profiles/*_traffic.json, written by tools/ncu_traffic.py from an ncu launch list of
     tools/render_once.py 64 = the same render as a bench step).  None when no summary is committed."""
     import glob
-    files = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "*_traffic.json")))
+    import re
+    files = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "*_traffic.json")),
+                   key=lambda f: [int(x) for x in re.findall(r"\d+", os.path.basename(f))])      # r01_v7 < r01_v11
     if not files:
         return None, None
     try:

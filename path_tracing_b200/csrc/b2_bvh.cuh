@@ -156,15 +156,46 @@ B2_HD int any_step(const DevScene &sc, AnyTrav &t, uint2 *stack, int sstride, Tr
     return B2_TRAV_CONTINUE;
 }
 
-// true = blocked by an opaque object within [1e-3, tMax] (cpu_check_visibility, cpu_bdpt.cpp:82-107)
+// true = blocked by an opaque object within [1e-3, tMax] (cpu_check_visibility, cpu_bdpt.cpp:82-107).  The plain loop
+// (state in registers, no resumable struct): b2_intersect's any-hit kernel measured 629 vs 485 Mrays/s against a loop
+// over any_step on the 10 M-triangle soup.
 template <bool COUNT>
 B2_HD bool occluded_bvh(const DevScene &sc, float3 ro, float3 rd, float tMax, uint2 *stack, int sstride, TravCounters *cnt) {
-    AnyTrav t;
-    any_init(t, sc, ro, rd, tMax);
-    for (;;) {
-        const int r = any_step<COUNT>(sc, t, stack, sstride, cnt);
-        if (r == B2_TRAV_HIT) return true;
-        if (r == B2_TRAV_EXHAUSTED) break;
+    const float tMin = 1e-3f;
+    if (sc.n_nodes > 0) {
+        const RayPre r = ray_pre(ro, rd);
+        int sp = 0;
+        uint32_t node = 0;
+        bool have = true;
+        uint2 grp = make_uint2(0u, 0u);
+        for (;;) {
+            if (!have) {
+                if ((grp.y >> 8) == 0u) { if (sp == 0) break; grp = stack[(--sp) * sstride]; }
+                const int p = ffs32(grp.y >> 8) - 1;
+                grp.y &= ~(1u << (8 + p));
+                const uint32_t slot = (uint32_t) p ^ r.oct;
+                node = grp.x + popc32(grp.y & 0xffu & ((1u << slot) - 1u));
+            }
+            have = false;
+            uint32_t hits_p, tribits, child_base, tri_base, imask;
+            node_test(sc.nodes, node, r, tMin, tMax, hits_p, tribits, child_base, tri_base, imask);
+            if (COUNT) cnt->nodes++;
+            while (tribits) {
+                const int bit = ffs32(tribits) - 1;
+                tribits &= tribits - 1u;
+                const int ti = (int) tri_base + bit;
+                const float4 b = sc.tri[3 * ti + 1];
+                if (f2u(b.w) & B2_MAT_TRANSPARENT) continue;
+                const float4 a = sc.tri[3 * ti], c = sc.tri[3 * ti + 2];
+                if (COUNT) cnt->tris++;
+                float t;
+                if (tri_test(ro, rd, mk3(a), mk3(b), mk3(c), tMin, tMax, t) && group_pass(sc, (int) f2u(c.w), ro, rd, tMin, tMax)) return true;
+            }
+            if (hits_p) {
+                if ((grp.y >> 8) != 0u && sp < B2_STACK_CAP) stack[(sp++) * sstride] = grp;
+                grp = make_uint2(child_base, (hits_p << 8) | imask);
+            }
+        }
     }
-    return occluded_spheres(sc, ro, rd, 1e-3f, tMax);
+    return occluded_spheres(sc, ro, rd, tMin, tMax);
 }
