@@ -64,6 +64,7 @@ typedef struct B2BvhInfo {
 
 #define B2_FILM_MEAN 0  /* film = sum / spp  (what run_cpu_bdpt writes, cpu_bdpt.cpp:479) */
 #define B2_FILM_SUM  1  /* film = raw sum of this shard's samples (for multi-GPU reduction) */
+#define B2_FILM_ACCUMULATE 2 /* film += sum / spp: one progressive pass added into a running sum (main.cpp:443-446); device entry only */
 #define B2_STRATEGIES_REFERENCE 0 /* exactly the strategy set of cpu_bdpt.cpp (parity mode) */
 #define B2_STRATEGIES_FULL      1 /* + t=1 light-tracing splats (not part of the reference estimator) */
 
@@ -141,6 +142,17 @@ int b2_render_bdpt_device(B2Scene *scene, const B2Camera *cam, const B2RenderPar
  * reduce (NCCL is dlopen'ed on first use) and resolved per params->film_mode.  stats: counters summed, ms_total = max. */
 int b2_render_bdpt_multi(B2Scene **scenes, int n_gpus, const B2Camera *cam, const B2RenderParams *params,
                          float *film_rgb_host, B2Stats *stats);
+/* Progressive rendering, the one non-graphics behaviour of the reference viewer (src/main.cpp:399-531), headless:
+ * `passes` renders of params->spp samples per pixel, pass k with Philox key params->seed + k (so every pass draws a new
+ * light pool), added into a running sum; film_rgb_host receives sum / passes.  rms (may be NULL, else `passes` floats):
+ * rms[k] = sqrt(sum over pixels and channels of (cur8 - last8)^2) / 255 between the tone-mapped 8-bit frames after pass
+ * k and k-1 (the viewer's convergence curve, main.cpp:502-531; rms[0] = 0).  on_pass (may be NULL) is called after
+ * every pass with the running average (host memory, valid during the call).  stats: counters and device time summed. */
+typedef void (*B2PassCallback)(int32_t pass, const float *film_avg_rgb, int32_t width, int32_t height, void *user);
+int b2_render_bdpt_progressive(B2Scene *scene, const B2Camera *cam, const B2RenderParams *params, int32_t passes,
+                               float *film_rgb_host, float *rms, B2PassCallback on_pass, void *user, B2Stats *stats);
+/* The viewer's frame-to-frame RMS on two 8-bit frames of n bytes each (host only). */
+int b2_frame_rms(const uint8_t *cur_rgb8, const uint8_t *last_rgb8, size_t n, float *out);
 /* The light-vertex pool the render would use: n_lights*spl*light_depth vertices x 20 floats
  * (pos3 normal3 thr3 mtl6 is_light_source is_parallel source_cutoff pdf_fwd pdf_rev), cpu_bdpt.cpp:202-325. */
 int b2_light_pool(B2Scene *scene, const B2RenderParams *params, float *pool20_host);

@@ -68,7 +68,7 @@ SYMBOLS = [
     "b2_scene_destroy", "b2_intersect", "b2_intersect_device", "b2_intersect_counters", "b2_render_bdpt",
     "b2_render_bdpt_device", "b2_render_bdpt_multi", "b2_light_pool", "b2_bsdf_evaluate", "b2_bsdf_pdf", "b2_bsdf_sample", "b2_mis_weight",
     "b2_philox", "b2_parse_scene_file", "b2_parsed_scene_free", "b2_film_to_rgb8", "b2_write_image",
-    "b2_obj_default_options", "b2_load_obj", "b2_parse_scene_file_ex",
+    "b2_obj_default_options", "b2_load_obj", "b2_parse_scene_file_ex", "b2_render_bdpt_progressive", "b2_frame_rms",
 ]
 
 _lib = None
@@ -112,6 +112,8 @@ def lib():
         L.b2_obj_default_options.argtypes = [C.POINTER(ObjOptions)]
         L.b2_obj_default_options.restype = None
         L.b2_load_obj.argtypes = [C.c_char_p, C.POINTER(ObjOptions), C.POINTER(C.POINTER(ParsedScene))]
+        L.b2_render_bdpt_progressive.argtypes = [vp, vp, vp, C.c_int32, vp, vp, vp, vp, vp]
+        L.b2_frame_rms.argtypes = [vp, vp, C.c_size_t, C.POINTER(C.c_float)]
         L.b2_parse_scene_file_ex.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.POINTER(ParsedScene))]
         L.b2_film_to_rgb8.argtypes = [vp, C.c_int32, C.c_int32, vp]
         L.b2_write_image.argtypes = [C.c_char_p, vp, C.c_int32, C.c_int32]

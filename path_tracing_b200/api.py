@@ -114,6 +114,22 @@ class Scene:
         A.check(A.lib().b2_render_bdpt(self._h, cam.ctypes.data_as(C.c_void_p), C.byref(p), A.ptr(film), C.byref(st)))
         return film, st.as_dict()
 
+    def render_progressive(self, passes, camera=None, width=None, height=None, spp=8, spl=8, eye_depth=4, light_depth=4, seed=1,
+                           on_pass=None, want_rms=True):
+        """The viewer's progressive accumulation (src/main.cpp:399-531): `passes` renders of `spp` samples (seed + pass)
+        averaged.  Returns (film, rms[passes] or None, stats).  on_pass(pass, film_avg[H,W,3]) is called after every pass."""
+        cam = np.ascontiguousarray(self.data.camera if camera is None else camera, dtype=A.Camera).reshape(())
+        W = int(width if width else self.data.width); H = int(height if height else self.data.height)
+        p = self._params(W, H, spp, spl, eye_depth, light_depth, seed, 0, 1, FILM_MEAN, 0, 0, False)
+        st = A.Stats()
+        film = np.zeros((max(H, 0), max(W, 0), 3), np.float32)
+        rms = np.zeros(max(int(passes), 0), np.float32) if want_rms else None
+        CB = C.CFUNCTYPE(None, C.c_int32, C.POINTER(C.c_float), C.c_int32, C.c_int32, C.c_void_p)
+        cb = CB(lambda k, ptr, w, h, user: on_pass(int(k), np.ctypeslib.as_array(ptr, shape=(h, w, 3)).copy())) if on_pass else None
+        A.check(A.lib().b2_render_bdpt_progressive(self._h, cam.ctypes.data_as(C.c_void_p), C.byref(p), int(passes), A.ptr(film),
+                                                   A.ptr(rms) if rms is not None else None, C.cast(cb, C.c_void_p) if cb else None, None, C.byref(st)))
+        return film, rms, st.as_dict()
+
     def light_pool(self, spl=8, light_depth=4, seed=1, max_delta=0):
         n = len(self.data.lights) * spl * light_depth
         out = np.zeros((n, 20), np.float32)
@@ -188,6 +204,15 @@ def film_to_rgb8(film):
     out = np.zeros((H, W, 3), np.uint8)
     A.check(A.lib().b2_film_to_rgb8(A.ptr(film), W, H, A.ptr(out)))
     return out
+
+
+def frame_rms(cur_rgb8, last_rgb8):
+    """sqrt(sum (cur - last)^2) / 255 over all bytes: the viewer's convergence curve (main.cpp:502-531)."""
+    a = np.ascontiguousarray(cur_rgb8, np.uint8); b = np.ascontiguousarray(last_rgb8, np.uint8)
+    assert a.size == b.size
+    out = C.c_float(0)
+    A.check(A.lib().b2_frame_rms(A.ptr(a), A.ptr(b), a.size, C.byref(out)))
+    return out.value
 
 
 def write_image(path, film):

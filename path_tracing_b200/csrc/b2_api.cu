@@ -194,6 +194,49 @@ int b2_render_bdpt(B2Scene *s, const B2Camera *cam, const B2RenderParams *params
     return B2_OK;
 }
 
+int b2_render_bdpt_progressive(B2Scene *s, const B2Camera *cam, const B2RenderParams *params, int32_t passes, float *film_rgb_host,
+                               float *rms, B2PassCallback on_pass, void *user, B2Stats *stats) {
+    B2_TRY(b2_check_built(s));
+    if (!cam || !params || !film_rgb_host || passes <= 0) { b2_set_error("NULL / invalid argument"); return B2_ERR_INVALID; }
+    if (params->width <= 0 || params->height <= 0) { b2_set_error("invalid film size"); return B2_ERR_INVALID; }
+    std::lock_guard<std::mutex> lk(s->mtx);
+    B2_CUDA(cudaSetDevice(s->device));
+    const size_t nf = (size_t) 3 * params->width * params->height;
+    RenderWorkspace &ws = s->ws_ref();
+    B2_TRY(ws.ensure_out(nf));
+    const bool per_pass = rms != nullptr || on_pass != nullptr;       // otherwise the film only crosses PCIe once, at the end
+    std::vector<uint8_t> cur8, last8;
+    if (rms) { cur8.resize(nf); last8.resize(nf); }
+    B2Stats tot; memset(&tot, 0, sizeof(tot));
+    for (int32_t k = 0; k < passes; ++k) {
+        B2RenderParams p = *params;
+        p.seed = params->seed + (uint64_t) k;
+        p.film_mode = k == 0 ? B2_FILM_MEAN : B2_FILM_ACCUMULATE;
+        B2Stats st;
+        B2_TRY(b2_render_device_impl(s->view(), s->bvh.depth, ws, *cam, p, ws.film_out.p, s->stream, &st));
+        tot.eye_samples += st.eye_samples; tot.closest_rays += st.closest_rays; tot.shadow_rays += st.shadow_rays; tot.path_samples += st.path_samples;
+        tot.delta_cap_hits += st.delta_cap_hits; tot.nodes_visited += st.nodes_visited; tot.tris_tested += st.tris_tested;
+        tot.n_batches += st.n_batches; tot.n_waves += st.n_waves; tot.n_launches += st.n_launches; tot.pairs_tested += st.pairs_tested;
+        tot.eye_vertices += st.eye_vertices; tot.ms_total += st.ms_total; tot.ms_light_pool += st.ms_light_pool;
+        tot.ms_primary += st.ms_primary; tot.ms_extend += st.ms_extend; tot.ms_connect += st.ms_connect;
+        if (per_pass || k == passes - 1) {
+            B2_CUDA(cudaMemcpyAsync(ws.h_film, ws.film_out.p, nf * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
+            B2_CUDA(cudaStreamSynchronize(s->stream));
+            const float inv = 1.0f / (float) (k + 1);
+            for (size_t i = 0; i < nf; ++i) film_rgb_host[i] = ws.h_film[i] * inv;
+            if (rms) {
+                b2_film_to_rgb8(film_rgb_host, params->width, params->height, cur8.data());
+                rms[k] = 0.0f;
+                if (k > 0) b2_frame_rms(cur8.data(), last8.data(), nf, &rms[k]);
+                cur8.swap(last8);
+            }
+            if (on_pass) on_pass(k, film_rgb_host, params->width, params->height, user);
+        }
+    }
+    if (stats) *stats = tot;
+    return B2_OK;
+}
+
 int b2_light_pool(B2Scene *s, const B2RenderParams *params, float *pool20_host) {
     B2_TRY(b2_check_built(s));
     if (!params || !pool20_host) { b2_set_error("NULL argument"); return B2_ERR_INVALID; }

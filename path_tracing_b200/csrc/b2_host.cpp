@@ -120,6 +120,15 @@ extern "C" int b2_film_to_rgb8(const float *film, int32_t W, int32_t H, uint8_t 
     return B2_OK;
 }
 
+// the viewer's convergence measure between two displayed frames (main.cpp:502-531): sqrt(sum (cur - last)^2) / 255
+extern "C" int b2_frame_rms(const uint8_t *cur, const uint8_t *last, size_t n, float *out) {
+    if (!cur || !last || !out) { b2_set_error("NULL argument"); return B2_ERR_INVALID; }
+    float acc = 0.0f;                                   // float accumulation and powf-free squares of small integers: exact per term
+    for (size_t i = 0; i < n; ++i) { const float d = (float) cur[i] - (float) last[i]; acc += d * d; }
+    *out = std::sqrt(acc) / 255.0f;
+    return B2_OK;
+}
+
 namespace {
 void be32(std::vector<uint8_t> &v, uint32_t x) { v.push_back(x >> 24); v.push_back(x >> 16); v.push_back(x >> 8); v.push_back(x); }
 void png_chunk(std::vector<uint8_t> &out, const char *type, const uint8_t *data, size_t n) {

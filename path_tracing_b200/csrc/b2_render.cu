@@ -298,6 +298,10 @@ __global__ void __launch_bounds__(256) k_resolve(const float *__restrict__ sum, 
     const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = sum[i] * inv;
 }
+__global__ void __launch_bounds__(256) k_resolve_acc(const float *__restrict__ sum, float *__restrict__ out, size_t n, float spp) {
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] += sum[i] / spp;                  // one progressive pass into the running sum (main.cpp:443-446)
+}
 __global__ void __launch_bounds__(256) k_resolve_div(const float *__restrict__ sum, float *__restrict__ out, size_t n, float spp) {
     const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = sum[i] / spp;                   // accum / spp, cpu_bdpt.cpp:479
@@ -513,6 +517,7 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
         B2_CUDA(cudaEventRecord(ev1, st));
     }
     if (p.film_mode == B2_FILM_SUM) k_resolve<<<blocks_for(film_floats, 256), 256, 0, st>>>(ws.film.p, d_film_out, film_floats, 1.0f);
+    else if (p.film_mode == B2_FILM_ACCUMULATE) k_resolve_acc<<<blocks_for(film_floats, 256), 256, 0, st>>>(ws.film.p, d_film_out, film_floats, (float) p.spp);
     else k_resolve_div<<<blocks_for(film_floats, 256), 256, 0, st>>>(ws.film.p, d_film_out, film_floats, (float) p.spp);
     n_launches++;
     B2_CUDA(cudaGetLastError());

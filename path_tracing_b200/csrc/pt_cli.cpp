@@ -3,6 +3,9 @@
 //   reference flags (main_cli.cpp:54-73):  --spp (8)  --spl (8)  --mode pt|bdpt|ppm  --device gpu|cpu  --output  --input
 //   additions (defaults reproduce the reference): --width --height (default: the scene's R line, main_cli.cpp:103)
 //                --eye-depth --light-depth (default 4/4 = EYE_DEPTH / LIGHT_DEPTH, main_cli.cpp:19-20)  --seed  --gpus
+//                --passes N --dump-every K: the viewer's progressive accumulation (src/main.cpp:399-531) headless: N renders
+//                of --spp samples each (seed + pass) averaged; every K passes the running average is written next to
+//                --output as <stem>_passNNNN<ext>, and the viewer's frame-to-frame RMS curve goes to <stem>_rms.txt
 // Only the BDPT path exists in this library: --mode pt / ppm and --device cpu exit with a message (the CPU integrator
 // is the reference's own cpu_bdpt.cpp; this library has no CPU execution path).  Note the reference's own default mode
 // is "pt"; here the default is "bdpt" because it is the only mode built.
@@ -28,10 +31,22 @@ static void usage() {
            "  --width/--height <int>            Film size (default: the scene's R line)\n"
            "  --eye-depth/--light-depth <int>   Subpath depths (default: 4)\n"
            "  --seed <int>         Philox key (default: 1)\n"
-           "  --gpus <int>         GPUs of this node to shard the samples over (default: 1)\n");
+           "  --gpus <int>         GPUs of this node to shard the samples over (default: 1)\n"
+           "  --passes <int>       Progressive passes of --spp samples each, averaged (default: 1)\n"
+           "  --dump-every <int>   Write the running average every K passes (default: 0 = only the final image)\n");
+}
+
+struct DumpCtx { std::string stem, ext; int every; };
+static void dump_pass(int32_t pass, const float *film, int32_t w, int32_t h, void *user) {
+    const DumpCtx *d = (const DumpCtx *) user;
+    if (d->every <= 0 || (pass + 1) % d->every != 0) return;
+    char name[32]; snprintf(name, sizeof(name), "_pass%04d", pass + 1);
+    const std::string path = d->stem + name + d->ext;
+    if (b2_write_image(path.c_str(), film, w, h) == B2_OK) printf("[Save] pass %d -> %s\n", pass + 1, path.c_str());
 }
 
 int main(int argc, char **argv) {
+    int passes = 1, dump_every = 0;
     int spp = 8, spl = 8, width = 0, height = 0, eye_depth = 4, light_depth = 4, gpus = 1;
     unsigned long long seed = 1;
     std::string mode = "bdpt", output_file = "output.png", input_file = "../../input.txt", device = "gpu";
@@ -50,6 +65,8 @@ int main(int argc, char **argv) {
         else if (arg == "--light-depth") { if (const char *v = next()) light_depth = atoi(v); }
         else if (arg == "--seed") { if (const char *v = next()) seed = strtoull(v, nullptr, 10); }
         else if (arg == "--gpus") { if (const char *v = next()) gpus = atoi(v); }
+        else if (arg == "--passes") { if (const char *v = next()) passes = atoi(v); }
+        else if (arg == "--dump-every") { if (const char *v = next()) dump_every = atoi(v); }
         else if (arg == "--help" || arg == "-h") { usage(); return 0; }
     }
     printf("====================================\n");
@@ -88,7 +105,34 @@ int main(int argc, char **argv) {
         B2RenderParams p; memset(&p, 0, sizeof(p));
         p.width = width; p.height = height; p.spp = spp; p.spl = spl; p.eye_depth = eye_depth; p.light_depth = light_depth;
         p.seed = seed; p.sample_offset = 0; p.sample_stride = 1; p.film_mode = B2_FILM_MEAN;
-        rc = b2_render_bdpt_multi(scenes.data(), gpus, &ps->camera, &p, film.data(), &st);
+        if (passes <= 1) rc = b2_render_bdpt_multi(scenes.data(), gpus, &ps->camera, &p, film.data(), &st);
+        else {
+            const size_t dot = output_file.find_last_of('.');
+            DumpCtx dc{ dot == std::string::npos ? output_file : output_file.substr(0, dot), dot == std::string::npos ? std::string(".png") : output_file.substr(dot), dump_every };
+            std::vector<float> rms(passes, 0.0f);
+            if (gpus == 1) rc = b2_render_bdpt_progressive(scenes[0], &ps->camera, &p, passes, film.data(), rms.data(), dump_pass, &dc, &st);
+            else {                                           // several GPUs: one sharded render per pass, accumulated here as the viewer does
+                std::vector<float> sum(film.size(), 0.0f), one(film.size());
+                std::vector<uint8_t> cur8(film.size()), last8(film.size());
+                for (int k = 0; k < passes && rc == B2_OK; ++k) {
+                    B2RenderParams pk = p; pk.seed = seed + (unsigned long long) k;
+                    B2Stats sk;
+                    rc = b2_render_bdpt_multi(scenes.data(), gpus, &ps->camera, &pk, one.data(), &sk);
+                    if (rc != B2_OK) break;
+                    st.eye_samples += sk.eye_samples; st.closest_rays += sk.closest_rays; st.shadow_rays += sk.shadow_rays; st.path_samples += sk.path_samples; st.ms_total += sk.ms_total;
+                    for (size_t i = 0; i < sum.size(); ++i) { sum[i] += one[i]; film[i] = sum[i] / (float) (k + 1); }
+                    b2_film_to_rgb8(film.data(), width, height, cur8.data());
+                    if (k > 0) b2_frame_rms(cur8.data(), last8.data(), cur8.size(), &rms[k]);
+                    cur8.swap(last8);
+                    dump_pass(k, film.data(), width, height, &dc);
+                }
+            }
+            if (rc == B2_OK) {
+                const std::string rp = dc.stem + "_rms.txt";
+                if (FILE *f = fopen(rp.c_str(), "w")) { for (int k = 0; k < passes; ++k) fprintf(f, "%d %.9g\n", k + 1, rms[k]); fclose(f); printf("[Save] RMS history -> %s\n", rp.c_str()); }
+                for (int k = 0; k < passes; ++k) printf("Render Iteration: %d  frame RMS %.6f\n", k + 1, rms[k]);
+            }
+        }
         const auto ms = std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::steady_clock::now() - t0).count();
         if (rc == B2_OK) {
             printf("\n[Render] Finished in %lld ms (device %.2f ms): %.2f M eye samples/s, %.2f Mrays/s (%llu closest + %llu shadow), %llu connections\n",

@@ -265,6 +265,34 @@ def test_pt_cli_renders_the_reference_scene(tmp_path):
     sc.close()
 
 
+def test_progressive_passes_average_independent_renders(tmp_path):
+    """the viewer's accumulation (main.cpp:399-531) headless.  N passes == mean of N renders with
+    seeds seed + k; the RMS curve is the viewer's frame-to-frame measure on the tone-mapped frames."""
+    import subprocess
+    import __graft_entry__ as g
+    sd = reference_scene("cornell")
+    sc = api.Scene(sd)
+    kw = dict(width=64, height=48, spp=4, spl=4, eye_depth=4, light_depth=4)
+    seen = []
+    film, rms, st = sc.render_progressive(3, seed=7, on_pass=lambda k, f: seen.append((k, f)), **kw)
+    singles = [sc.render_bdpt(seed=7 + k, **kw)[0] for k in range(3)]
+    assert np.allclose(film, np.mean(singles, axis=0), rtol=1e-5, atol=1e-6)
+    assert [k for k, _ in seen] == [0, 1, 2] and np.allclose(seen[1][1], (singles[0] + singles[1]) / 2, rtol=1e-5, atol=1e-6)
+    assert rms[0] == 0.0 and rms[1] > 0.0
+    f8 = [api.film_to_rgb8(f) for _, f in seen]
+    assert abs(rms[2] - api.frame_rms(f8[2], f8[1])) < 1e-6
+    assert st["eye_samples"] == 3 * 64 * 48 * 4
+    # the CLI: --passes / --dump-every
+    scene_txt = tmp_path / "scene.txt"; sd.write_text(scene_txt)
+    r = subprocess.run([g.CLI, "--input", str(scene_txt), "--output", str(tmp_path / "p.ppm"), "--spp", "4", "--spl", "4", "--width", "64", "--height", "48",
+                        "--seed", "7", "--passes", "3", "--dump-every", "2"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert (tmp_path / "p_pass0002.ppm").exists() and not (tmp_path / "p_pass0001.ppm").exists() and (tmp_path / "p.ppm").exists()
+    hist = np.loadtxt(tmp_path / "p_rms.txt")
+    assert hist.shape == (3, 2) and np.allclose(hist[:, 1], rms, atol=2e-3)
+    sc.close()
+
+
 def test_in_process_multi_gpu_entry_point():
     """b2_render_bdpt_multi: with one device it is the plain render; with >= 2 devices the NCCL-reduced film of the
     sharded render equals the 1-GPU film up to summation order."""

@@ -157,3 +157,12 @@ def test_no_cpu_fallback_without_a_device():
         api.bsdf_pdf(np.zeros((1, 6)), np.zeros((1, 3)), np.zeros((1, 3)), np.zeros((1, 3)))
     with pytest.raises(A.B2Error, match="no CUDA device"):
         api.philox(np.zeros((1, 4)), np.zeros((1, 2)))
+
+
+def test_frame_rms_is_the_viewers_formula():
+    """main.cpp:502-531: rms = sqrt(sum over pixels and channels of (cur - last)^2) / 255 on the tone-mapped 8-bit frames."""
+    rng = np.random.default_rng(5)
+    a = rng.integers(0, 256, (37, 41, 3)).astype(np.uint8); b = rng.integers(0, 256, (37, 41, 3)).astype(np.uint8)
+    want = np.sqrt(((a.astype(np.float64) - b.astype(np.float64)) ** 2).sum()) / 255.0
+    assert abs(api.frame_rms(a, b) - want) < 1e-4 * want
+    assert api.frame_rms(a, a) == 0.0
