@@ -89,19 +89,23 @@ def cpu_arm(steps, warmup, sample=CPU_SAMPLE):
     w = dict(WORKLOAD); w.update(sample)
     sd = reference_scene(w["scene"]); f = sd.to_flat()
     d = O.SceneDesc(f["kind"], f["group"], f["geom"], f["mtl"], f["lights"], f["cam"], f["W"], f["H"])
-    cores = os.cpu_count() or 1
+    # every host core this process may run on, set explicitly: torchrun exports OMP_NUM_THREADS=1 to its children, which
+    # would otherwise time the reference on ONE thread (measured: 2.6 instead of 37 Msamples/s)
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except AttributeError:
+        cores = os.cpu_count() or 1
     n_samples = w["width"] * w["height"] * w["spp"]
     if O.have_ref():
         kind, lib = "reference", O.Ref()
         h = lib.scene(d)
-        cores = lib.max_threads()
         devnull = os.open(os.devnull, os.O_WRONLY); saved = os.dup(1)
 
         def run():
             sys.stdout.flush(); os.dup2(devnull, 1)       # the reference prints per-thread timings to stdout
             try:
                 t0 = time.perf_counter()
-                lib.render(h, d.cam, w["eye_depth"], w["light_depth"], w["width"], w["height"], w["spp"], w["spl"])
+                lib.render(h, d.cam, w["eye_depth"], w["light_depth"], w["width"], w["height"], w["spp"], w["spl"], nthreads=cores)
                 return time.perf_counter() - t0
             finally:
                 os.dup2(saved, 1)
@@ -111,7 +115,7 @@ def cpu_arm(steps, warmup, sample=CPU_SAMPLE):
 
         def run():
             t0 = time.perf_counter()
-            lib.render(h, d.cam, w["eye_depth"], w["light_depth"], w["width"], w["height"], w["spp"], w["spl"], lib.opts(rng_mode=lib.MT19937))
+            lib.render(h, d.cam, w["eye_depth"], w["light_depth"], w["width"], w["height"], w["spp"], w["spl"], lib.opts(rng_mode=lib.MT19937, nthreads=cores))
             return time.perf_counter() - t0
     for _ in range(warmup):
         run()
