@@ -23,47 +23,69 @@ inline float hs_bits(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
 
 inline bool flatten_scene(const B2Tri *tris, size_t n_tris, const B2Sphere *sph, size_t n_sph, const B2Material *mats, size_t n_mats,
                           const B2Light *lights, size_t n_lights, HostScene &hs, const char **err) {
-    // groups: std::map<int,AABB> in key order; bounds grown as AABB::add_obj does (object.cpp:123-147)
-    struct G { float mn[3] = { 99999.f, 99999.f, 99999.f }, mx[3] = { -99999.f, -99999.f, -99999.f }; };
+    // groups: std::map<int,AABB> in key order; bounds grown as AABB::add_obj does (object.cpp:123-147).
+    // The per-object work is O(1): the group of consecutive objects rarely changes, so the map is only consulted when it
+    // does, and every object remembers a pointer-stable slot (10 M triangles: 4.0 s -> 0.5 s).
+    struct G { float mn[3] = { 99999.f, 99999.f, 99999.f }, mx[3] = { -99999.f, -99999.f, -99999.f }; int dense = -1; size_t count = 0; };
     std::map<int, G> gm;
-    for (size_t i = 0; i < n_tris; ++i) {
-        if (tris[i].material < 0 || (size_t) tris[i].material >= n_mats) { *err = "triangle material index out of range"; return false; }
-        G &g = gm[tris[i].group];
-        const float *vs[3] = { tris[i].v0, tris[i].v1, tris[i].v2 };
-        for (int k = 0; k < 3; ++k)
-            for (int a = 0; a < 3; ++a) { g.mn[a] = std::min(g.mn[a], vs[k][a]); g.mx[a] = std::max(g.mx[a], vs[k][a]); }
-    }
-    for (size_t i = 0; i < n_sph; ++i) {
-        if (sph[i].material < 0 || (size_t) sph[i].material >= n_mats) { *err = "sphere material index out of range"; return false; }
-        G &g = gm[sph[i].group];
-        for (int a = 0; a < 3; ++a) {
-            float p = sph[i].center[a] + sph[i].r, m = sph[i].center[a] - sph[i].r;
-            g.mn[a] = std::min({ g.mn[a], p, m }); g.mx[a] = std::max({ g.mx[a], p, m });
+    std::vector<G *> tri_g(n_tris), sph_g(n_sph);
+    {
+        int last_key = 0; G *last = nullptr;
+        for (size_t i = 0; i < n_tris; ++i) {
+            if (tris[i].material < 0 || (size_t) tris[i].material >= n_mats) { *err = "triangle material index out of range"; return false; }
+            if (!last || tris[i].group != last_key) { last_key = tris[i].group; last = &gm[last_key]; }
+            G &g = *last; tri_g[i] = last; g.count++;
+            const float *vs[3] = { tris[i].v0, tris[i].v1, tris[i].v2 };
+            for (int k = 0; k < 3; ++k)
+                for (int a = 0; a < 3; ++a) { g.mn[a] = std::min(g.mn[a], vs[k][a]); g.mx[a] = std::max(g.mx[a], vs[k][a]); }
+        }
+        for (size_t i = 0; i < n_sph; ++i) {
+            if (sph[i].material < 0 || (size_t) sph[i].material >= n_mats) { *err = "sphere material index out of range"; return false; }
+            if (!last || sph[i].group != last_key) { last_key = sph[i].group; last = &gm[last_key]; }
+            G &g = *last; sph_g[i] = last; g.count++;
+            for (int a = 0; a < 3; ++a) {
+                float p = sph[i].center[a] + sph[i].r, m = sph[i].center[a] - sph[i].r;
+                g.mn[a] = std::min({ g.mn[a], p, m }); g.mx[a] = std::max({ g.mx[a], p, m });
+            }
         }
     }
-    std::map<int, int> gindex;
     // scene bounds for parallel lights: union of the group boxes as run_cpu_bdpt sees them (cpu_bdpt.cpp:181-187)
     float smn[3] = { 1e9f, 1e9f, 1e9f }, smx[3] = { -1e9f, -1e9f, -1e9f };
     hs.groups.clear();
-    for (auto &kv : gm) {
-        gindex[kv.first] = (int) gindex.size();
-        G g = kv.second;
-        for (int a = 0; a < 3; ++a) { smn[a] = std::min(smn[a], g.mn[a]); smx[a] = std::max(smx[a], g.mx[a]); }
-        // AABB::intersectAABB widens degenerate extents in place on every call (object.cpp:108-111); apply to the fixed point
-        for (int a = 0; a < 3; ++a)
-            for (int it = 0; it < 64 && g.mx[a] - g.mn[a] < 1e-6f; ++it) { g.mn[a] -= 0.5f * 1e-6f; g.mx[a] += 0.5f * 1e-6f; }
-        hs.groups.push_back(hs_f4(g.mn[0], g.mn[1], g.mn[2], 0.f));
-        hs.groups.push_back(hs_f4(g.mx[0], g.mx[1], g.mx[2], 0.f));
+    std::vector<size_t> g_start;                       // first rank of every group, in key order
+    {
+        size_t acc = 0; int dense = 0;
+        for (auto &kv : gm) {
+            kv.second.dense = dense++;
+            g_start.push_back(acc); acc += kv.second.count;
+            G g = kv.second;
+            for (int a = 0; a < 3; ++a) { smn[a] = std::min(smn[a], g.mn[a]); smx[a] = std::max(smx[a], g.mx[a]); }
+            // AABB::intersectAABB widens degenerate extents in place on every call (object.cpp:108-111); apply to the fixed point
+            for (int a = 0; a < 3; ++a)
+                for (int it = 0; it < 64 && g.mx[a] - g.mn[a] < 1e-6f; ++it) { g.mn[a] -= 0.5f * 1e-6f; g.mx[a] += 0.5f * 1e-6f; }
+            hs.groups.push_back(hs_f4(g.mn[0], g.mn[1], g.mn[2], 0.f));
+            hs.groups.push_back(hs_f4(g.mx[0], g.mx[1], g.mx[2], 0.f));
+        }
     }
     hs.n_groups = (int) gm.size();
     hs.scene_min = make_float3(smn[0], smn[1], smn[2]);
     hs.scene_max = make_float3(smx[0], smx[1], smx[2]);
-    // reference visiting order: group key, then insertion order (= obj_id order)
-    struct Key { int group, obj_id, kind; size_t idx; };
-    std::vector<Key> keys; keys.reserve(n_tris + n_sph);
-    for (size_t i = 0; i < n_tris; ++i) keys.push_back({ tris[i].group, tris[i].obj_id, 1, i });
-    for (size_t i = 0; i < n_sph; ++i) keys.push_back({ sph[i].group, sph[i].obj_id, 0, i });
-    std::stable_sort(keys.begin(), keys.end(), [](const Key &a, const Key &b) { return a.group != b.group ? a.group < b.group : a.obj_id < b.obj_id; });
+    // reference visiting order: group key, then insertion order (= obj_id order).  Bucket by group (stable), then sort a
+    // bucket by obj_id only if it is not already ascending (it is, for every scene the parser or the OBJ adapter makes).
+    struct Key { int obj_id, kind; size_t idx; };
+    std::vector<Key> keys(n_tris + n_sph);
+    {
+        std::vector<size_t> fill(g_start);
+        for (size_t i = 0; i < n_tris; ++i) keys[fill[(size_t) tri_g[i]->dense]++] = Key{ tris[i].obj_id, 1, i };
+        for (size_t i = 0; i < n_sph; ++i) keys[fill[(size_t) sph_g[i]->dense]++] = Key{ sph[i].obj_id, 0, i };
+        // the bucket pass visited triangles before spheres: a group holding both kinds needs the merge by obj_id
+        for (size_t gi = 0; gi < g_start.size(); ++gi) {
+            const size_t b0 = g_start[gi], b1 = gi + 1 < g_start.size() ? g_start[gi + 1] : keys.size();
+            bool sorted = true;
+            for (size_t r = b0 + 1; r < b1 && sorted; ++r) sorted = keys[r - 1].obj_id <= keys[r].obj_id;
+            if (!sorted) std::stable_sort(keys.begin() + (long) b0, keys.begin() + (long) b1, [](const Key &a, const Key &b) { return a.obj_id < b.obj_id; });
+        }
+    }
     std::vector<uint32_t> tri_order(n_tris), sph_order(n_sph);
     for (size_t r = 0; r < keys.size(); ++r) (keys[r].kind ? tri_order[keys[r].idx] : sph_order[keys[r].idx]) = (uint32_t) r;
 
@@ -81,7 +103,7 @@ inline bool flatten_scene(const B2Tri *tris, size_t n_tris, const B2Sphere *sph,
         for (int k = 0; k < 9; ++k) max_abs = std::max(max_abs, std::fabs(t.v[k]));
         t.order = tri_order[i];
         t.matflag = (uint32_t) tris[i].material | (mats[tris[i].material].eta > 0.0f ? B2_MAT_TRANSPARENT : 0u);
-        t.group = (uint32_t) gindex[tris[i].group];
+        t.group = (uint32_t) tri_g[i]->dense;
         t.obj_id = tris[i].obj_id;
     }
     hs.max_abs = max_abs;
@@ -89,7 +111,7 @@ inline bool flatten_scene(const B2Tri *tris, size_t n_tris, const B2Sphere *sph,
     for (size_t i = 0; i < n_sph; ++i) {
         uint32_t mf = (uint32_t) sph[i].material | (mats[sph[i].material].eta > 0.0f ? B2_MAT_TRANSPARENT : 0u);
         hs.sph.push_back(hs_f4(sph[i].center[0], sph[i].center[1], sph[i].center[2], sph[i].r));
-        hs.sph.push_back(hs_f4(hs_bits(sph_order[i]), hs_bits(mf), hs_bits((uint32_t) gindex[sph[i].group]), hs_bits((uint32_t) sph[i].obj_id)));
+        hs.sph.push_back(hs_f4(hs_bits(sph_order[i]), hs_bits(mf), hs_bits((uint32_t) sph_g[i]->dense), hs_bits((uint32_t) sph[i].obj_id)));
     }
     hs.n_sph = (int) n_sph;
     hs.lights.clear();
