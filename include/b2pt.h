@@ -66,7 +66,10 @@ typedef struct B2BvhInfo {
 #define B2_FILM_SUM  1  /* film = raw sum of this shard's samples (for multi-GPU reduction) */
 #define B2_FILM_ACCUMULATE 2 /* film += sum / spp: one progressive pass added into a running sum (main.cpp:443-446); device entry only */
 #define B2_STRATEGIES_REFERENCE 0 /* exactly the strategy set of cpu_bdpt.cpp (parity mode) */
-#define B2_STRATEGIES_FULL      1 /* + t=1 light-tracing splats (not part of the reference estimator) */
+/* The three below are NOT the reference estimator (csrc/b2_strategies.cuh): physically based spot lights, s = 1 and t = 1 only. */
+#define B2_STRATEGIES_FULL           1 /* 1/2 next-event estimation (s=1) + 1/2 light tracing with t=1 film splats + emitter hits */
+#define B2_STRATEGIES_LIGHT_TRACING  2 /* only the t=1 splats: W*H*spp light subpaths, atomicAdd into the film */
+#define B2_STRATEGIES_NEE            3 /* only the eye subpaths with next-event estimation (the estimator the splats are validated against) */
 
 typedef struct B2RenderParams {
     int32_t  width, height;

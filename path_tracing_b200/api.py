@@ -14,6 +14,7 @@ from .scene import SceneData
 
 CLOSEST, ANY, BRUTE_FORCE, COUNT_VISITS = 0, 1, 16, 32
 FILM_MEAN, FILM_SUM = 0, 1
+STRATEGIES_REFERENCE, STRATEGIES_FULL, STRATEGIES_LIGHT_TRACING, STRATEGIES_NEE = 0, 1, 2, 3
 
 
 def device_count():
@@ -90,20 +91,20 @@ class Scene:
 
     # ---- render ----
     def _params(self, width, height, spp, spl, eye_depth, light_depth, seed, sample_offset, sample_stride, film_mode,
-                max_delta, max_batch_paths, count_traversal, profile_stages=False):
+                max_delta, max_batch_paths, count_traversal, profile_stages=False, strategies=0):
         return A.RenderParams(int(width), int(height), int(spp), int(spl), int(eye_depth), int(light_depth), int(seed),
-                              int(sample_offset), int(sample_stride), int(film_mode), 0, int(max_delta), int(max_batch_paths),
+                              int(sample_offset), int(sample_stride), int(film_mode), int(strategies), int(max_delta), int(max_batch_paths),
                               1 if count_traversal else 0, 1 if profile_stages else 0)
 
     def render_bdpt(self, camera=None, width=None, height=None, spp=8, spl=8, eye_depth=4, light_depth=4, seed=1,
                     sample_offset=0, sample_stride=1, film_mode=FILM_MEAN, max_delta=0, max_batch_paths=0,
-                    count_traversal=False, profile_stages=False, out=None, device_ptr=None, stream=0):
+                    count_traversal=False, profile_stages=False, out=None, device_ptr=None, stream=0, strategies=STRATEGIES_REFERENCE):
         """Returns (film[H,W,3] float32, stats dict).  With device_ptr (int) the film stays on the device and None is returned for it."""
         cam = np.ascontiguousarray(self.data.camera if camera is None else camera, dtype=A.Camera).reshape(())
         W = int(width if width else self.data.width)
         H = int(height if height else self.data.height)
         p = self._params(W, H, spp, spl, eye_depth, light_depth, seed, sample_offset, sample_stride, film_mode, max_delta,
-                         max_batch_paths, count_traversal, profile_stages)
+                         max_batch_paths, count_traversal, profile_stages, strategies)
         st = A.Stats()
         if device_ptr is not None:
             A.check(A.lib().b2_render_bdpt_device(self._h, cam.ctypes.data_as(C.c_void_p), C.byref(p), C.c_void_p(int(device_ptr)),

@@ -142,6 +142,7 @@ B2_HD Surface surface_at(const DevScene &sc, float3 ro, float3 rd, HitRec h) {
         float3 n = f3_normalize(x3_sub(s.pos, mk3(a)));                    // cpu_bdpt.cpp:74-76
         if (x3_dot(n, rd) > 0.0f) n = x3_muls(n, -1.0f);
         s.n = n; s.mtl.base = mk3(il); s.mtl.eta = 0.0f; s.mtl.roughness = 1.0f; s.mtl.metallic = 0.0f; s.is_light = true;
+        if (sc.ggx_fix) mat_mark_fix(s.mtl);
     }
     return s;
 }

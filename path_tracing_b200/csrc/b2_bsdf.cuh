@@ -7,6 +7,15 @@
 #include "b2_common.cuh"
 
 struct Mat { float3 base; float roughness, metallic, eta; };   // CudaMaterial, geometric.cuh:21-27
+// The reference's tr_D (geometric.cuh:178-185) squares tan^2 once too often: e = cos^4 (alpha^2 + tan^4) instead of
+// cos^4 (alpha^2 + tan^2)^2, so D is not the GGX distribution its own sample_vndf draws from and bsdf_pdf is not the density
+// of bsdf_sample.  Parity mode reproduces that bug for bug.  The strategies that are not part of the reference estimator
+// (b2_strategies.cuh) need a sampler and a pdf that agree, or the two estimators they validate against each other carry
+// different biases: they mark their materials by setting the SIGN BIT of roughness (a material travels through the
+// eye-vertex / light-vertex records as six floats, so the flag costs no storage), and D is then the normalised GGX.
+B2_HD void mat_mark_fix(Mat &m) { m.roughness = u2f(f2u(m.roughness) | 0x80000000u); }
+B2_HD bool mat_fix(const Mat &m) { return (f2u(m.roughness) & 0x80000000u) != 0u; }
+B2_HD float mat_rough(const Mat &m) { return fabsf(m.roughness); }
 
 struct Frame { float3 T, B, N; };
 B2_HD Frame make_frame(float3 N) {                              // build_local_frame, :119-123
@@ -38,11 +47,11 @@ B2_HD float3 fr_schlick(float cosI, float3 R0) {                 // :163-167
     return R0 + (mk3(1.0f, 1.0f, 1.0f) - R0) * c5;
 }
 B2_HD float roughness_to_alpha(float r) { float x = fmaxf(r, 1e-3f); return x * x; }   // :173
-B2_HD float tr_D(float3 wh, float alpha) {                       // :178-185
+B2_HD float tr_D(float3 wh, float alpha, bool fix) {             // :178-185
     float cos2 = wh.z * wh.z;
     float tan2 = fast_div(fmaxf(0.0f, 1.0f - cos2), cos2 + 1e-7f);
     if (isinf(tan2)) return 0.0f;
-    float e = (cos2 * cos2) * (alpha * alpha + tan2 * tan2);
+    float e = (cos2 * cos2) * (fix ? (alpha * alpha + tan2) * (alpha * alpha + tan2) : alpha * alpha + tan2 * tan2);
     if (e < 1e-12f) return 0.0f;
     return fast_div(alpha * alpha, B2_PI * e);
 }
@@ -71,15 +80,15 @@ B2_HD float3 sample_vndf(float3 wo, float alpha, float u1, float u2) {  // :200-
 // local-space cores (callers that evaluate several lobes for one normal reuse the frame)
 B2_HD float3 bsdf_eval_local(const Mat &m, float3 wo, float3 wi) {      // :426-455
     if (wo.z == 0.0f || wi.z == 0.0f) return mk3(0, 0, 0);
-    if (m.eta > 0.0f && m.roughness < 0.001f) return mk3(0, 0, 0);
-    float alpha = roughness_to_alpha(m.roughness);
+    if (m.eta > 0.0f && mat_rough(m) < 0.001f) return mk3(0, 0, 0);
+    float alpha = roughness_to_alpha(mat_rough(m));
     float3 whv = wo + wi;
     if (length3(whv) < 1e-6f) return mk3(0, 0, 0);
     float3 wh = normalize3(whv);
     if (wh.z < 0.0f) wh = wh * -1.0f;
     float3 diffuse = m.base * ((1.0f / B2_PI) * (1.0f - m.metallic));
     if (wo.z * wi.z < 0.0f) diffuse = mk3(0, 0, 0);
-    float D = tr_D(wh, alpha);
+    float D = tr_D(wh, alpha, mat_fix(m));
     float G = tr_G(wo, wi, alpha);
     float3 F;
     if (m.metallic > 0.0f) F = fr_schlick(fabsf(wo.z), m.base);
@@ -90,8 +99,8 @@ B2_HD float3 bsdf_eval_local(const Mat &m, float3 wo, float3 wi) {      // :426-
 }
 B2_HD float bsdf_pdf_local(const Mat &m, float3 wo, float3 wi) {        // :464-483
     if (wo.z * wi.z <= 0.0f) return 0.0f;
-    if (m.eta > 0.0f && m.roughness < 0.001f) return 0.0f;
-    float alpha = roughness_to_alpha(m.roughness);
+    if (m.eta > 0.0f && mat_rough(m) < 0.001f) return 0.0f;
+    float alpha = roughness_to_alpha(mat_rough(m));
     float3 whv = wo + wi;
     if (length3(whv) < 1e-6f) return 0.0f;
     float3 wh = normalize3(whv);
@@ -99,7 +108,7 @@ B2_HD float bsdf_pdf_local(const Mat &m, float3 wo, float3 wi) {        // :464-
     float pdf_diffuse = fabsf(wi.z) * (1.0f / B2_PI);
     float G1 = fast_rcp(1.0f + tr_lambda(wo, alpha));
     float owh = dot3(wo, wh);
-    float pdf_wh = fast_div(tr_D(wh, alpha) * G1 * fmaxf(0.0f, owh), fabsf(wo.z));
+    float pdf_wh = fast_div(tr_D(wh, alpha, mat_fix(m)) * G1 * fmaxf(0.0f, owh), fabsf(wo.z));
     float pdf_spec = fast_div(pdf_wh, 4.0f * owh + 1e-7f);
     float sw = m.metallic > 0.0f ? 1.0f : 0.5f;
     return (1.0f - sw) * pdf_diffuse + sw * pdf_spec;
@@ -132,7 +141,7 @@ void bsdf_sample(const Mat &m, float3 wo_w, float3 N, float u_rr, float u1, floa
     Frame fr = make_frame(N);
     float3 wo = to_local(fr, wo_w);
     float3 wi;
-    if (m.eta > 0.0f && m.roughness < 0.001f && m.metallic < 0.01f) {
+    if (m.eta > 0.0f && mat_rough(m) < 0.001f && m.metallic < 0.01f) {
         s.is_delta = true;
         float F = fr_dielectric(wo.z, cur_eta, m.eta);
         if (u_rr < F) {
@@ -154,7 +163,7 @@ void bsdf_sample(const Mat &m, float3 wo_w, float3 N, float u_rr, float u1, floa
         s.wi = to_world(fr, wi);
         return;
     }
-    if (m.metallic > 0.99f && m.roughness < 0.001f) {
+    if (m.metallic > 0.99f && mat_rough(m) < 0.001f) {
         s.is_delta = true;
         wi = mk3(-wo.x, -wo.y, wo.z);
         s.pdf = 1.0f;
@@ -162,7 +171,7 @@ void bsdf_sample(const Mat &m, float3 wo_w, float3 N, float u_rr, float u1, floa
         s.wi = to_world(fr, wi);
         return;
     }
-    float alpha = roughness_to_alpha(m.roughness);
+    float alpha = roughness_to_alpha(mat_rough(m));
     float sw = m.metallic > 0.0f ? 1.0f : 0.5f;
     if (u_rr < sw) {
         float3 wh = sample_vndf(wo.z > 0 ? wo : wo * -1.0f, alpha, u1, u2);

@@ -17,6 +17,7 @@
 //                  (BSDFs, shadow any-hit, MIS); per-vertex sums go to the film with one atomicAdd per channel.
 //   k_resolve      film / spp                                                                 :479
 #include "b2_render.hpp"
+#include "b2_strategies.cuh"
 #include <algorithm>
 #include <vector>
 
@@ -294,6 +295,42 @@ __global__ void __launch_bounds__(CONN_THREADS, CONN_BLOCKS_PER_SM) k_connect(Re
     if (COUNT) { warp_count_add(&c.counters[B2_CNT_NODES], tc.nodes); warp_count_add(&c.counters[B2_CNT_TRIS], tc.tris); }
 }
 
+// ---- strategies beyond the reference set (b2_strategies.cuh): t = 1 light tracing with film splats, s = 1 next-event ----
+template <bool COUNT>
+__global__ void __launch_bounds__(EXT_THREADS) k_light_trace(RenderCtx c, CamFrame cf, int n_items, uint32_t pix0, int s0, float alpha0_scale) {
+    extern __shared__ uint2 s_stack[];
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    TravCounters tc{ 0u, 0u };
+    uint32_t ncl = 0, nsh = 0, nsp = 0;
+    if (q < n_items) {
+        uint32_t slot;                                      // same (sample, slot) split as the eye samples, so shards partition the subpaths
+        const uint32_t ds = udiv_magic(pix0 + (uint32_t) q, (uint32_t) (c.W * c.H), c.npix_magic, slot);
+        const unsigned long long sample = (unsigned long long) (c.sample_offset + (s0 + (int) ds) * c.sample_stride);
+        light_trace_body<COUNT>(c, cf, sample * (unsigned long long) (c.W * c.H) + slot, alpha0_scale, s_stack + threadIdx.x, blockDim.x, &tc, ncl, nsh, nsp);
+    }
+    warp_count_add(&c.counters[B2_CNT_CLOSEST], ncl);
+    warp_count_add(&c.counters[B2_CNT_SHADOW], nsh);
+    warp_count_add(&c.counters[B2_CNT_PATH_SAMPLES], nsp);
+    if (COUNT) { warp_count_add(&c.counters[B2_CNT_NODES], tc.nodes); warp_count_add(&c.counters[B2_CNT_TRIS], tc.tris); }
+}
+template <bool COUNT>
+__global__ void __launch_bounds__(EXT_THREADS) k_nee(RenderCtx c, float w) {
+    extern __shared__ uint2 s_stack[];
+    const int n_cv = *c.n_cv;
+    TravCounters tc{ 0u, 0u };
+    uint32_t nsh = 0, npa = 0;
+    for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < n_cv; q += gridDim.x * blockDim.x) {
+        const EyeVtx ev = load_cv(c.cv, q);
+        const float3 r = nee_body<COUNT>(c, ev, w, s_stack + threadIdx.x, blockDim.x, &tc, nsh, npa);
+        if (r.x != 0.0f) atomicAdd(&c.film[3 * ev.pixel], r.x);
+        if (r.y != 0.0f) atomicAdd(&c.film[3 * ev.pixel + 1], r.y);
+        if (r.z != 0.0f) atomicAdd(&c.film[3 * ev.pixel + 2], r.z);
+    }
+    warp_count_add(&c.counters[B2_CNT_SHADOW], nsh);
+    warp_count_add(&c.counters[B2_CNT_PATH_SAMPLES], npa);
+    if (COUNT) { warp_count_add(&c.counters[B2_CNT_NODES], tc.nodes); warp_count_add(&c.counters[B2_CNT_TRIS], tc.tris); }
+}
+
 __global__ void __launch_bounds__(256) k_resolve(const float *__restrict__ sum, float *__restrict__ out, size_t n, float inv) {
     const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = sum[i] * inv;
@@ -364,6 +401,7 @@ static int validate_params(const B2RenderParams &p) {
     if (p.eye_depth > 255) { b2_set_error("eye_depth > 255 is not supported"); return B2_ERR_INVALID; }
     if ((long long) p.width * p.height > (1ll << 24)) { b2_set_error("film larger than 2^24 pixels is not supported"); return B2_ERR_INVALID; }
     if (p.sample_offset < 0 || p.sample_stride < 0) { b2_set_error("invalid sample_offset / sample_stride"); return B2_ERR_INVALID; }
+    if (p.strategies < B2_STRATEGIES_REFERENCE || p.strategies > B2_STRATEGIES_NEE) { b2_set_error("unknown strategies value %d", p.strategies); return B2_ERR_INVALID; }
     if ((long long) p.spl * p.light_depth > (1ll << 26)) { b2_set_error("spl * light_depth too large"); return B2_ERR_INVALID; }
     return B2_OK;
 }
@@ -371,6 +409,7 @@ static int validate_params(const B2RenderParams &p) {
 static void setup_ctx(RenderCtx &c, const DevScene &sc, const B2Camera &cam, const B2RenderParams &p, RenderWorkspace &ws, int max_paths) {
     memset(&c, 0, sizeof(c));
     c.sc = sc;
+    c.sc.ggx_fix = p.strategies != B2_STRATEGIES_REFERENCE;      // normalised GGX D only outside parity mode (b2_bsdf.cuh)
     camera_basis(cam.eye, cam.look_at, cam.view_up, cam.fov, p.width, p.height, c.cam_eye, c.cUL, c.cdx, c.cdy);
     c.W = p.width; c.H = p.height; c.spl = p.spl; c.eye_depth = p.eye_depth; c.light_depth = p.light_depth;
     c.w_magic = udiv_magic_of((uint32_t) p.width); c.npix_magic = udiv_magic_of((uint32_t) p.width * (uint32_t) p.height);
@@ -439,6 +478,10 @@ static int set_smem_limits(int bvh_depth) {
     B2_CUDA(cudaFuncSetAttribute(k_extend<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_t));
     B2_CUDA(cudaFuncSetAttribute(k_connect<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_c));
     B2_CUDA(cudaFuncSetAttribute(k_connect<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_c));
+    B2_CUDA(cudaFuncSetAttribute(k_light_trace<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_t));
+    B2_CUDA(cudaFuncSetAttribute(k_light_trace<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_t));
+    B2_CUDA(cudaFuncSetAttribute(k_nee<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_t));
+    B2_CUDA(cudaFuncSetAttribute(k_nee<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_t));
     if (dev < 64) configured[dev] = bvh_depth + 1;
     return B2_OK;
 }
@@ -471,11 +514,28 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
     B2_CUDA(cudaMemsetAsync(ws.ints.p, 0, sizeof(int) * 8, st));
     unsigned long long eye_samples = 0, eye_vertices = 0;
     // run_cpu_bdpt returns before touching the film when there are no lights (cpu_bdpt.cpp:178); here the film is zero
+    const bool ref_set = p.strategies == B2_STRATEGIES_REFERENCE;
+    const bool eye_pass = p.strategies != B2_STRATEGIES_LIGHT_TRACING, lt_pass = p.strategies == B2_STRATEGIES_FULL || p.strategies == B2_STRATEGIES_LIGHT_TRACING;
+    const float w_mix = p.strategies == B2_STRATEGIES_FULL ? 0.5f : 1.0f;    // constant-weight combination of s = 1 and t = 1
     if (sc.n_lights > 0 && total > 0) {
-        B2_TRY(build_pool(c, bvh_depth, count, st, n_launches));
+        if (ref_set) B2_TRY(build_pool(c, bvh_depth, count, st, n_launches));
         B2_CUDA(cudaEventRecord(ev1, st));
         const size_t sb_t = stack_bytes(EXT_THREADS, bvh_depth), sb_c = stack_bytes(CONN_THREADS, bvh_depth);
-        for (long long w0 = 0; w0 < total; w0 += max_paths) {
+        if (lt_pass) {                                       // t = 1: W*H*n_my light subpaths, splatted straight into the film sums
+            const CamFrame cf = cam_frame(c.cdx, c.cdy);
+            const float a0 = (float) sc.n_lights / (float) npix * w_mix;
+            for (long long w0 = 0; w0 < total; w0 += (1ll << 24)) {
+                const int n = (int) std::min<long long>(1ll << 24, total - w0);
+                const uint32_t pix0 = (uint32_t) (w0 % npix); const int s0 = (int) (w0 / npix);
+                tm.begin(StageTimer::CONNECT);
+                if (count) k_light_trace<true><<<blocks_for(n, EXT_THREADS), EXT_THREADS, sb_t, st>>>(c, cf, n, pix0, s0, a0);
+                else k_light_trace<false><<<blocks_for(n, EXT_THREADS), EXT_THREADS, sb_t, st>>>(c, cf, n, pix0, s0, a0);
+                tm.end();
+                n_launches++;
+            }
+            B2_CUDA(cudaGetLastError());
+        }
+        for (long long w0 = 0; eye_pass && w0 < total; w0 += max_paths) {
             int n_live = (int) std::min<long long>(max_paths, total - w0);
             c.live = ws.live_a.p; c.live_next = ws.live_b.p;
             n_batches++;
@@ -499,8 +559,14 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
                 // persistent warps: one CTA wave over the 148 SMs (grid-stride over the work items computed on the device)
                 const unsigned gc = (unsigned) std::min<long long>(148ll * CONN_BLOCKS_PER_SM, std::max<long long>(1, ((long long) n_live * 8 + CONN_THREADS - 1) / CONN_THREADS));
                 tm.begin(StageTimer::CONNECT);
-                if (count) k_connect<true><<<gc, CONN_THREADS, sb_c, st>>>(c);
-                else k_connect<false><<<gc, CONN_THREADS, sb_c, st>>>(c);
+                if (ref_set) {
+                    if (count) k_connect<true><<<gc, CONN_THREADS, sb_c, st>>>(c);
+                    else k_connect<false><<<gc, CONN_THREADS, sb_c, st>>>(c);
+                } else {
+                    const unsigned gn = (unsigned) std::min<long long>(148ll * 8, blocks_for(n_live, EXT_THREADS));
+                    if (count) k_nee<true><<<gn, EXT_THREADS, sb_t, st>>>(c, w_mix);
+                    else k_nee<false><<<gn, EXT_THREADS, sb_t, st>>>(c, w_mix);
+                }
                 tm.end();
                 n_launches += 2; n_waves++;
                 B2_CUDA(cudaStreamSynchronize(st));
@@ -529,7 +595,7 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
         memset(stats, 0, sizeof(*stats));
         float ms_pool = 0.f, ms_total = 0.f;
         cudaEventElapsedTime(&ms_pool, ev0, ev1); cudaEventElapsedTime(&ms_total, ev0, ev2);
-        stats->eye_samples = eye_samples;
+        stats->eye_samples = eye_pass ? eye_samples : (unsigned long long) total;
         stats->closest_rays = h_cnt[B2_CNT_CLOSEST] + ws.closest_rays_host;
         stats->shadow_rays = h_cnt[B2_CNT_SHADOW];
         stats->path_samples = h_cnt[B2_CNT_PATH_SAMPLES];

@@ -44,10 +44,12 @@ struct DevScene {
     const float4 *groups;   // 2 per group: {min, 0}, {max, 0}  (degenerate extents pre-widened, object.cpp:108-111)
     int n_tris, n_nodes, n_sph, n_lights, n_mats, n_groups;
     float3 scene_min, scene_max;   // union of the group boxes (cpu_bdpt.cpp:181-187)
+    int ggx_fix;                   // != 0: materials are marked for the normalised GGX D (mat_mark_fix); 0 in parity mode
 };
 
 B2_HD Mat load_mat(const DevScene &sc, int m) {
     float4 a = sc.mats[2 * m], b = sc.mats[2 * m + 1];
     Mat r; r.base = mk3(a); r.roughness = a.w; r.metallic = b.x; r.eta = b.y;
+    if (sc.ggx_fix) mat_mark_fix(r);
     return r;
 }

@@ -32,6 +32,7 @@ static void usage() {
            "  --eye-depth/--light-depth <int>   Subpath depths (default: 4)\n"
            "  --seed <int>         Philox key (default: 1)\n"
            "  --gpus <int>         GPUs of this node to shard the samples over (default: 1)\n"
+           "  --strategies <string> reference (cpu_bdpt.cpp's set, default) | full (next-event + t=1 splats) | light | nee\n"
            "  --passes <int>       Progressive passes of --spp samples each, averaged (default: 1)\n"
            "  --dump-every <int>   Write the running average every K passes (default: 0 = only the final image)\n");
 }
@@ -46,7 +47,7 @@ static void dump_pass(int32_t pass, const float *film, int32_t w, int32_t h, voi
 }
 
 int main(int argc, char **argv) {
-    int passes = 1, dump_every = 0;
+    int passes = 1, dump_every = 0, strategies = B2_STRATEGIES_REFERENCE;
     int spp = 8, spl = 8, width = 0, height = 0, eye_depth = 4, light_depth = 4, gpus = 1;
     unsigned long long seed = 1;
     std::string mode = "bdpt", output_file = "output.png", input_file = "../../input.txt", device = "gpu";
@@ -65,6 +66,14 @@ int main(int argc, char **argv) {
         else if (arg == "--light-depth") { if (const char *v = next()) light_depth = atoi(v); }
         else if (arg == "--seed") { if (const char *v = next()) seed = strtoull(v, nullptr, 10); }
         else if (arg == "--gpus") { if (const char *v = next()) gpus = atoi(v); }
+        else if (arg == "--strategies") {
+            if (const char *v = next()) {
+                const std::string sv = v;
+                if (sv == "reference") strategies = B2_STRATEGIES_REFERENCE; else if (sv == "full") strategies = B2_STRATEGIES_FULL;
+                else if (sv == "light") strategies = B2_STRATEGIES_LIGHT_TRACING; else if (sv == "nee") strategies = B2_STRATEGIES_NEE;
+                else { fprintf(stderr, "[Error] unknown --strategies '%s'\n", v); return 2; }
+            }
+        }
         else if (arg == "--passes") { if (const char *v = next()) passes = atoi(v); }
         else if (arg == "--dump-every") { if (const char *v = next()) dump_every = atoi(v); }
         else if (arg == "--help" || arg == "-h") { usage(); return 0; }
@@ -104,7 +113,7 @@ int main(int argc, char **argv) {
         const auto t0 = std::chrono::steady_clock::now();
         B2RenderParams p; memset(&p, 0, sizeof(p));
         p.width = width; p.height = height; p.spp = spp; p.spl = spl; p.eye_depth = eye_depth; p.light_depth = light_depth;
-        p.seed = seed; p.sample_offset = 0; p.sample_stride = 1; p.film_mode = B2_FILM_MEAN;
+        p.seed = seed; p.sample_offset = 0; p.sample_stride = 1; p.film_mode = B2_FILM_MEAN; p.strategies = strategies;
         if (passes <= 1) rc = b2_render_bdpt_multi(scenes.data(), gpus, &ps->camera, &p, film.data(), &st);
         else {
             const size_t dot = output_file.find_last_of('.');

@@ -18,6 +18,7 @@ static void hs_make_view(HsScene *s) {
     v.n_tris = (int) s->hs.tris.size(); v.n_nodes = (int) (s->bvh.nodes.size() / B2_NODE_UINT4);
     v.n_sph = s->hs.n_sph; v.n_lights = s->hs.n_lights; v.n_mats = s->hs.n_mats; v.n_groups = s->hs.n_groups;
     v.scene_min = s->hs.scene_min; v.scene_max = s->hs.scene_max;
+    v.ggx_fix = 0;                                      // parity mode
 }
 
 extern "C" {
