@@ -6,6 +6,7 @@
 // (Python callers run one process per GPU under torchrun and use torch.distributed instead: path_tracing_b200/multi.py.)
 #include <dlfcn.h>
 #include <cstring>
+#include <mutex>
 #include <thread>
 #include <vector>
 #include "b2_scene_handle.hpp"
@@ -38,6 +39,22 @@ struct Nccl {
 };
 Nccl g_nccl;
 
+// Communicators are kept per device list for the life of the process: ncclCommInitAll costs ~3 s on an 8-GPU node, which
+// a progressive render (one call per pass) or a second frame should not pay again.
+struct CommSet { std::vector<int> devs; std::vector<ncclComm_t> comms; };
+std::mutex g_comm_mtx;
+std::vector<CommSet> g_comm_cache;
+int get_comms(const std::vector<int> &devs, std::vector<ncclComm_t> &out) {
+    std::lock_guard<std::mutex> lk(g_comm_mtx);
+    for (const CommSet &c : g_comm_cache) if (c.devs == devs) { out = c.comms; return kNcclSuccess; }
+    CommSet c; c.devs = devs; c.comms.assign(devs.size(), nullptr);
+    const int rc = g_nccl.CommInitAll(c.comms.data(), (int) devs.size(), devs.data());
+    if (rc != kNcclSuccess) return rc;
+    g_comm_cache.push_back(c);
+    out = c.comms;
+    return kNcclSuccess;
+}
+
 __global__ void k_scale(float *film, size_t n, float inv) {
     const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) film[i] *= inv;
@@ -57,8 +74,8 @@ extern "C" int b2_render_bdpt_multi(B2Scene **scenes, int n_gpus, const B2Camera
     const size_t nf = (size_t) 3 * params->width * params->height;
     std::vector<int> devs(n_gpus);
     for (int g = 0; g < n_gpus; ++g) devs[g] = scenes[g]->device;
-    std::vector<ncclComm_t> comms(n_gpus, nullptr);
-    int nrc = g_nccl.CommInitAll(comms.data(), n_gpus, devs.data());
+    std::vector<ncclComm_t> comms;
+    int nrc = get_comms(devs, comms);
     if (nrc != kNcclSuccess) { b2_set_error("ncclCommInitAll failed: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(nrc) : "?"); return B2_ERR_CUDA; }
     std::vector<float *> d_film(n_gpus, nullptr);
     std::vector<int> rc(n_gpus, B2_OK);
@@ -102,7 +119,7 @@ extern "C" int b2_render_bdpt_multi(B2Scene **scenes, int n_gpus, const B2Camera
         if (e == cudaSuccess) memcpy(film_rgb_host, stage, nf * sizeof(float));
         if (e != cudaSuccess) { b2_set_error("film read-back failed: %s", cudaGetErrorString(e)); bad = B2_ERR_CUDA; }
     }
-    for (int g = 0; g < n_gpus; ++g) { cudaSetDevice(devs[g]); if (comms[g]) g_nccl.CommDestroy(comms[g]); }
+    for (int g = 0; g < n_gpus; ++g) { cudaSetDevice(devs[g]); }
     if (stats && bad == B2_OK) {
         *stats = st[0];
         for (int g = 1; g < n_gpus; ++g) {
