@@ -145,6 +145,9 @@ __global__ void __launch_bounds__(EXT_THREADS) k_extend(RenderCtx c, int n_items
 // lanes active in the node tests of the 1 M-triangle scene).  One film atomicAdd per eye vertex and channel per item.
 constexpr int CONN_LOW = 32;          // pre-test another chunk while fewer pairs than this are stacked
 constexpr int CONN_MQ = 64;           // visible-pair queue: < 32 left + 32 new per trace step
+#ifndef B2_FAST_SHADOW_TRI
+#define B2_FAST_SHADOW_TRI 1          // contracted Moeller-Trumbore for the shadow rays of the connection stage (b2_isect.cuh)
+#endif
 #ifndef B2_REFILL_MIN
 #define B2_REFILL_MIN 20              // idle lanes that trigger a refill (connect_prepare then runs at >= this occupancy)
 #endif
@@ -263,7 +266,7 @@ __global__ void __launch_bounds__(CONN_THREADS, CONN_BLOCKS_PER_SM) k_connect(Re
                 // ---- trace: one step per lane that holds a ray ----
                 bool visible = false;
                 if (busy) {
-                    int r = any_step<COUNT>(c.sc, tv, stack, CONN_THREADS, &tc);
+                    int r = any_step<COUNT, B2_FAST_SHADOW_TRI != 0>(c.sc, tv, stack, CONN_THREADS, &tc);
                     if (r == B2_TRAV_EXHAUSTED) {
                         if (occluded_spheres(c.sc, tv.r.o, tv.r.d, 1e-3f, tv.tmax)) r = B2_TRAV_HIT; else visible = true;
                     }
