@@ -82,7 +82,7 @@ typedef struct B2RenderParams {
     int32_t  film_mode;      /* B2_FILM_MEAN / B2_FILM_SUM */
     int32_t  strategies;     /* B2_STRATEGIES_* */
     int32_t  max_delta;      /* cap on delta bounces per subpath (0 = default 256) */
-    int32_t  max_batch_paths;/* eye samples in flight per wavefront batch (0 = default 2^24) */
+    int32_t  max_batch_paths;/* eye samples in flight per wavefront batch (0 = up to 2^26, as HBM allows) */
     int32_t  count_traversal;/* !=0: use the counting traversal variant and fill node/tri visit counters */
     int32_t  profile_stages; /* !=0: bracket every stage launch with CUDA events and fill the ms_* stage times */
 } B2RenderParams;

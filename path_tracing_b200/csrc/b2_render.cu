@@ -148,6 +148,9 @@ constexpr int CONN_MQ = 64;           // visible-pair queue: < 32 left + 32 new 
 #ifndef B2_FAST_SHADOW_TRI
 #define B2_FAST_SHADOW_TRI 1          // contracted Moeller-Trumbore for the shadow rays of the connection stage (b2_isect.cuh)
 #endif
+#ifndef B2_DEFAULT_BATCH_LOG2
+#define B2_DEFAULT_BATCH_LOG2 26      // most eye samples in flight per batch when the caller leaves max_batch_paths at 0
+#endif
 #ifndef B2_REFILL_MIN
 #define B2_REFILL_MIN 20              // idle lanes that trigger a refill (connect_prepare then runs at >= this occupancy)
 #endif
@@ -498,7 +501,21 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
     int n_my = 0;
     for (long long s = p.sample_offset; s < p.spp; s += stride) n_my++;
     const long long total = (long long) npix * n_my;
-    long long mp = p.max_batch_paths > 0 ? p.max_batch_paths : (1ll << 24);   // 2^24 samples in flight: ~6 GB of wavefront state at depth 8
+    long long mp = p.max_batch_paths;
+    if (mp <= 0) {
+        // default: up to 2^26 samples in flight (C2 in one batch: the per-batch tails of the extend/connect waves cost ~0.35 ms
+        // each, 8.2 -> 10.0 Gsamples/s from 2^24 to 2^26), halved until the wavefront state (104 + 24 B per depth and sample,
+        // 24 GB at depth 8) fits in half of the free HBM
+        const size_t per_path = 5 * sizeof(float4) + (size_t) std::max(p.eye_depth, 1) * (sizeof(float4) + sizeof(float2)) + 2 * sizeof(int) + B2_CV_F4 * sizeof(float4);
+        mp = std::min<long long>(1ll << B2_DEFAULT_BATCH_LOG2, std::max<long long>(total, 1));
+        if (mp > ws.cap_paths || p.eye_depth > ws.cap_depth) {            // only when the workspace has to grow (cudaMemGetInfo costs > 1 ms)
+            size_t free_b = 0, total_b = 0;
+            B2_CUDA(cudaMemGetInfo(&free_b, &total_b));
+            const size_t have = (size_t) std::max(ws.cap_paths, 0) * (5 * sizeof(float4) + (size_t) std::max(ws.cap_depth, 0) * (sizeof(float4) + sizeof(float2)) + 2 * sizeof(int) + B2_CV_F4 * sizeof(float4));
+            while (mp > (1ll << 20) && (size_t) mp * per_path > (free_b + have) / 2) mp >>= 1;
+            if (mp < ws.cap_paths && p.eye_depth <= ws.cap_depth) mp = ws.cap_paths;
+        }
+    }
     mp = std::max<long long>(std::min<long long>(mp, std::max<long long>(total, 1)), 1);
     const int max_paths = (int) mp;
     if ((long long) sc.n_lights * p.spl * p.light_depth >= (1ll << 27)) { b2_set_error("light pool larger than 2^27 vertices is not supported"); return B2_ERR_INVALID; }
