@@ -10,6 +10,7 @@ run of the same job) and the raw-sum films are reduced to rank 0 with one NCCL r
   e2e        the same through the public call with HOST buffers: scene upload + BVH build + render + film read-back
   roofline   dominant kernel of the step, algorithmic bytes / CUDA-event time vs the measured HBM copy bandwidth
   cpu_baseline  oracle/_ref (the reference's cpu_bdpt.cpp, unmodified) on the host cores, bounded sample
+  reference_cuda_baseline  the reference's existing CUDA BDPT (bdpt_cu.cu, unmodified, built for sm_100a) on this GPU, same sample
 """
 import argparse
 import json
@@ -125,6 +126,25 @@ def cpu_arm(steps, warmup, sample=CPU_SAMPLE):
     return {"value": val, "unit": "Msamples/s", "cores": int(cores), "kind": kind, "ms_per_step": sec * 1e3,
             "sample": f"{w['scene']} scene {w['width']}x{w['height']}, {w['spp']} spp, spl {w['spl']}, depth {w['eye_depth']}/{w['light_depth']} "
                       f"({n_samples / 1e6:.2f} M eye samples per step; full workload is {WORKLOAD['width']}x{WORKLOAD['height']} x {WORKLOAD['spp']} spp)"}
+
+
+def ref_cuda_arm(sample=CPU_SAMPLE, timeout=180):
+    """The reference's EXISTING CUDA BDPT (src/bdpt_cu.cu, compiled unmodified for sm_100a into oracle/_ref/libref_cuda.so)
+    on this GPU, on the same bounded sample as the CPU arm: the same-hardware "kernel to beat" of SURVEY.md 2b.  Runs in
+    a child process (tests/ref_cuda_probe.py) so that a failure of that code cannot take the bench line with it.
+    Wall time of run_cuda_bdpt as main_cli.cpp:207-219 reports it.  None when the library is not there."""
+    if not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libref_cuda.so")):
+        return None
+    w = dict(WORKLOAD); w.update(sample)
+    cmd = [sys.executable, os.path.join(ROOT, "tests", "ref_cuda_probe.py"), w["scene"], str(w["width"]), str(w["spp"]), str(w["spl"]),
+           str(w["eye_depth"]), "bdpt", "ref-only"]
+    try:
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout)
+        d = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])
+        return {"value": d["eye_msamples_per_s"], "unit": "Msamples/s", "kind": "reference CUDA kernels (bdpt_cu.cu, unmodified, sm_100a) on this GPU",
+                "ms_per_step": d["ms"], "sample": f"{w['scene']} scene {w['width']}x{w['height']}, {w['spp']} spp, spl {w['spl']}, depth {w['eye_depth']}/{w['light_depth']}"}
+    except Exception as e:          # noqa: BLE001 -- baseline evidence only
+        return {"unavailable": f"{type(e).__name__}: {e}"[:200]}
 
 
 def measured_traffic(kernel):
@@ -266,6 +286,9 @@ def gpu_arm(args):
         }
         if world == 1 and not args.no_cpu:
             out["cpu_baseline"] = cpu_arm(1, 0)
+            rc = ref_cuda_arm()
+            if rc is not None:
+                out["reference_cuda_baseline"] = rc
     sc.close()
     if world > 1:
         dist.barrier()

@@ -3,6 +3,8 @@
 Two libraries with the same flat-array interface:
   * ``Port``  -- oracle/liboracle_bdpt.so, the plain-C restatement (oracle/bdpt_oracle.c)
   * ``Ref``   -- oracle/_ref/libref_bdpt.so, the UNMODIFIED reference sources behind oracle/ref_shim.cpp
+plus ``RefCuda`` -- oracle/_ref/libref_cuda.so, the reference's existing CUDA integrators (bdpt_cu / pt_cu / ppm_cu)
+compiled unmodified for sm_100a behind oracle/ref_cuda_shim.cpp: a same-GPU baseline, not a parity oracle.
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import this.
 """
 import ctypes as C
@@ -13,6 +15,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 PORT_SO = os.path.join(HERE, "liboracle_bdpt.so")
 REF_SO = os.path.join(HERE, "_ref", "libref_bdpt.so")
+REF_CUDA_SO = os.path.join(HERE, "_ref", "libref_cuda.so")
 
 _f = np.ctypeslib.ndpointer(dtype=np.float32, flags="C_CONTIGUOUS")
 _i = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
@@ -230,6 +233,57 @@ class Port(_Lib):
         out = np.zeros(n, np.float32)
         self.lib.or_mt19937_floats(seed, n, out)
         return out
+
+
+class RefCuda:
+    """The reference's own CUDA integrators on this GPU (needs a device; loads libcudart)."""
+    BDPT, PT, PPM = 0, 1, 2
+
+    def __init__(self):
+        if not os.path.exists(REF_CUDA_SO):
+            raise FileNotFoundError(REF_CUDA_SO)
+        self.lib = C.CDLL(REF_CUDA_SO)
+        self.lib.refcuda_scene_create.restype = C.c_void_p
+        self.lib.refcuda_scene_create.argtypes = [C.c_int, _i, _i, _f, _f, C.c_int, _f]
+        self.lib.refcuda_scene_destroy.argtypes = [C.c_void_p]
+        self.lib.refcuda_render.restype = C.c_double
+        self.lib.refcuda_render.argtypes = [C.c_void_p, C.c_int, _f, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _f, C.c_int]
+
+    def scene(self, d: SceneDesc):
+        return self.lib.refcuda_scene_create(d.n_obj, d.kind, d.group, d.geom.reshape(-1), d.mtl.reshape(-1),
+                                             d.n_lights, d.lights.reshape(-1) if d.n_lights else np.zeros(1, np.float32))
+
+    def destroy(self, h):
+        self.lib.refcuda_scene_destroy(h)
+
+    @staticmethod
+    def camera12(cam10, W, H):
+        """eye, UL, dx, dy the way main_cli.cpp:25-40 (init_camera) derives them, in float32."""
+        f = np.float32
+        c = np.asarray(cam10, np.float32)
+        eye, look, up, fov = c[0:3], c[3:6], c[6:9], c[9]
+        half_h = f(np.tan(f(f(fov * f(np.pi)) / f(180.0)) / f(2.0)))
+        half_w = f(f(W) / f(H)) * half_h
+        nrm = lambda v: (v / np.sqrt(np.dot(v, v), dtype=np.float32)).astype(np.float32)
+        w = nrm(eye - look)
+        u = nrm(np.cross(up, w).astype(np.float32))
+        v = np.cross(w, u).astype(np.float32)
+        UL = eye - half_w * u + half_h * v - w
+        dx = (f(2) * half_w * u) / f(W)
+        dy = (f(-2) * half_h * v) / f(H)
+        return np.concatenate([eye, UL, dx, dy]).astype(np.float32)
+
+    def render(self, h, mode, cam10, eye_depth, light_depth, W, H, spp, spl, quiet=True):
+        """-> (film[H,W,3] mean radiance, wall milliseconds of run_cuda_* as main_cli.cpp:207-219 times it)"""
+        img = np.zeros((H, W, 3), np.float32)
+        ms = self.lib.refcuda_render(h, mode, self.camera12(cam10, W, H), W, H, spp, spl, eye_depth, light_depth, img.reshape(-1), 1 if quiet else 0)
+        if ms < 0:
+            raise ValueError("bad mode")
+        return img, float(ms)
+
+
+def have_ref_cuda():
+    return os.path.exists(REF_CUDA_SO)
 
 
 def have_ref():

@@ -155,13 +155,27 @@ _DATA = None
 
 
 def reference_scene(name):
-    """The reference's own scene files (input.txt -> "cornell", mis_test.txt -> "mis"), stored parsed in
+    """The reference's own scene files (input.txt -> "cornell", mis_test.txt -> "mis", its documented variant -> "mis_variant"), stored parsed in
     data/reference_scenes.npz by tests/golden/make_golden.py."""
     global _DATA
     import os
     if _DATA is None:
         _DATA = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "data", "reference_scenes.npz"))
     d = _DATA
+    if name == "mis_variant":
+        # The documented variant of mis_test.txt (SURVEY.md 8d, C2): as parsed today the three surplus numbers on every `M`
+        # line are dropped, so all four plates get roughness 0 / metallic 0.9, and `cutoff 360` (cos = 1) makes the cone
+        # gate reject almost every connection -- the render is black except for the light balls.  The variant is the scene
+        # the file was meant to be: 6-number `M` lines with the roughness the file lists as its 7th number
+        # (0.1 / 0.3 / 0.5 / 0.7, metallic 0.9) and cutoff 180 degrees on every light; geometry, camera, lights unchanged.
+        mtl = np.array(d["mis_mtl"], np.float32)
+        lights = np.array(d["mis_lights"], np.float32)
+        assert len(mtl) == 48 and len(lights) == 5
+        for plate, rough in enumerate((0.1, 0.3, 0.5, 0.7)):
+            mtl[12 * plate:12 * (plate + 1), 3] = rough
+        lights[:, 9] = np.float32(np.pi)
+        W, H = (int(x) for x in d["mis_res"])
+        return SceneData.from_flat(d["mis_kind"], d["mis_group"], d["mis_geom"], mtl, lights, d["mis_cam"], W, H)
     W, H = (int(x) for x in d[f"{name}_res"])
     return SceneData.from_flat(d[f"{name}_kind"], d[f"{name}_group"], d[f"{name}_geom"], d[f"{name}_mtl"], d[f"{name}_lights"],
                                d[f"{name}_cam"], W, H)

@@ -166,7 +166,7 @@ def test_philox_known_answers_on_device():
     assert np.array_equal(unit, np.array([[P.unit_float(int(x)) for x in row] for row in want], np.float32))
 
 
-@pytest.mark.parametrize("name,depth,spl", [("cornell", 4, 8), ("cornell", 8, 8), ("mis", 8, 8)])
+@pytest.mark.parametrize("name,depth,spl", [("cornell", 4, 8), ("cornell", 8, 8), ("mis", 8, 8), ("mis_variant", 8, 8)])
 def test_render_matches_oracle_on_identical_streams(name, depth, spl):
     """Same Philox streams on both sides -> the films agree sample for sample except where CUDA's libm / FMA
     rounding flips a discrete decision.  Tolerances: counters within 0.2 %, film mean within 0.5 %, 99 % of the
