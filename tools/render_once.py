@@ -5,7 +5,11 @@ from path_tracing_b200 import api as b2
 from path_tracing_b200.scene import reference_scene
 
 spp = int(sys.argv[1]) if len(sys.argv) > 1 else 64
-s = b2.Scene(reference_scene("mis"))
+scene = sys.argv[2] if len(sys.argv) > 2 else "mis"          # "mis_variant": the documented variant, "cornell": input.txt
+s = b2.Scene(reference_scene(scene))
 for _ in range(2):
     film, st = s.render_bdpt(width=1024, height=1024, spp=spp, spl=8, eye_depth=8, light_depth=8, seed=1)
-print(json.dumps({k: st[k] for k in ("ms_total", "eye_samples", "n_launches", "n_waves", "n_batches")}), float(film.mean()))
+out = {k: st[k] for k in ("ms_total", "eye_samples", "path_samples", "closest_rays", "shadow_rays", "pairs_tested", "n_launches", "n_waves", "n_batches")}
+out.update(scene=scene, eye_msamples_per_s=st["eye_samples"] / st["ms_total"] / 1e3, mpath_samples_per_s=st["path_samples"] / st["ms_total"] / 1e3,
+           mrays_per_s=(st["closest_rays"] + st["shadow_rays"]) / st["ms_total"] / 1e3, film_mean=float(film.mean()))
+print(json.dumps(out))
