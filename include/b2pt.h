@@ -71,6 +71,17 @@ typedef struct B2BvhInfo {
 #define B2_STRATEGIES_LIGHT_TRACING  2 /* only the t=1 splats: W*H*spp light subpaths, atomicAdd into the film */
 #define B2_STRATEGIES_NEE            3 /* only the eye subpaths with next-event estimation (the estimator the splats are validated against) */
 
+/* The other two integrators of the reference's command line (src/main_cli.cpp:201-213); every
+ * render entry point below takes them through B2RenderParams.integrator:
+ *   PT  <- run_cuda_pt (include/pt_cu_helper.h:6, kernel src/pt_cu.cu:20-252): eye_depth = its max_depth, spl / light_depth unused
+ *   PPM <- run_cuda_ppm (include/ppm_cu_helper.h, kernels src/ppm_cu.cu:64-322): ONE pass of n_lights*spl photons of
+ *          light_depth bounces over one hit point per pixel; spp is ignored as in the reference (the progressive entry point
+ *          averages passes with fresh seeds); photons do not shard over GPUs (the resolve clamps the summed flux).
+ * The reference has no CPU implementation of either; intersection rules follow its GPU helpers (include/geometric.cuh:240-390). */
+#define B2_INTEGRATOR_BDPT 0
+#define B2_INTEGRATOR_PT   1
+#define B2_INTEGRATOR_PPM  2
+
 typedef struct B2RenderParams {
     int32_t  width, height;
     int32_t  spp;            /* total samples per pixel of the whole job */
@@ -85,6 +96,9 @@ typedef struct B2RenderParams {
     int32_t  max_batch_paths;/* eye samples in flight per wavefront batch (0 = up to 2^26, as HBM allows) */
     int32_t  count_traversal;/* !=0: use the counting traversal variant and fill node/tri visit counters */
     int32_t  profile_stages; /* !=0: bracket every stage launch with CUDA events and fill the ms_* stage times */
+    int32_t  integrator;     /* B2_INTEGRATOR_*: main_cli's --mode (0 = bdpt, the path this library is built around) */
+    float    ppm_radius;     /* ppm: gather radius = grid cell size (0 = PPM_RADIUS 0.05, include/ppm_cu.cuh:5) */
+    int32_t  reserved[2];
 } B2RenderParams;
 
 typedef struct B2Stats {

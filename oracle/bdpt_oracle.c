@@ -988,3 +988,422 @@ void or_render(OrScene *s, const float *cam, int eye_depth, int light_depth, int
         stats->path_samples = total.path_samples; stats->delta_cap_hits = total.delta_cap; stats->seconds = t1 - t0;
     }
 }
+
+/* =====================================================================================
+ * The reference's two other integrators, pt and ppm (src/pt_cu.cu, src/ppm_cu.cu), restated on the CPU.
+ *
+ * Parity status of THIS section: UNPINNED on the CPU.  The reference has no CPU implementation of these
+ * integrators and seeds curand from the clock (pt_cu.cu:279, ppm_cu.cu:357), so nothing here can be compared bit for
+ * bit with it.  The restatement follows the kernels line by line on the Philox streams of the GPU path and is pinned
+ * STATISTICALLY against the reference's own kernels run on the GPU box (oracle/_ref/libref_cuda.so,
+ * tests/test_gpu_pt_ppm.py).  Intersection follows the reference's GPU-side helpers, which differ from cpu_bdpt.cpp's:
+ * intersect_triangle / intersect_sphere for every object (geometric.cuh:240-291), first hit wins ties in the order
+ * spheres, light balls, triangles (:327-390), shadow rays are blocked by every object -- check_visibility (:293-325)
+ * reads mtl_old.refract, which the pt / ppm helpers leave uninitialised (pt_cu_helper.cpp:25,41: the assignment is
+ * commented out); it is taken as zero-initialised here, i.e. opaque.
+ * Draw schedule (shared with path_tracing_b200/csrc/b2_pt.cuh):
+ *   eye / pt paths   kind 2: (pixel, sample) block 0 = jitter, block 1+k = u_rr,u1,u2 of the k-th bsdf_sample call
+ *   pt NEE           kind 4: (pixel, sample) block 1+k lanes 0,1,2 = light choice, point on the light ball
+ *   photons          kind 5: (photon, 0) block 0 = emission, block 1+k = k-th bsdf_sample call
+ * ===================================================================================== */
+static void philox_unit4(const uint32_t key[2], uint32_t id0, uint32_t id1, uint32_t block, uint32_t kind, float u[4]) {
+    uint32_t c[4] = { id0, id1, block, kind }, o[4];
+    or_philox4x32_10(c, key, o);
+    for (int i = 0; i < 4; ++i) u[i] = or_u32_to_unit_float(o[i]);
+}
+/* intersect_triangle, geometric.cuh:261-291 */
+static int gpu_intersect_triangle(v3 ro, v3 rd, const Obj *o, float *t, float max_dist) {
+    v3 e1 = f3_sub(o->v1, o->v0), e2 = f3_sub(o->v2, o->v0);
+    v3 h = f3_cross(rd, e2);
+    float a = f3_dot(e1, h);
+    if (a > -1e-6f && a < 1e-6f) return 0;
+    float f = 1.0f / a;
+    v3 s = f3_sub(ro, o->v0);
+    float u = f * f3_dot(s, h);
+    if (u < 0.0f || u > 1.0f) return 0;
+    v3 q = f3_cross(s, e1);
+    float v = f * f3_dot(rd, q);
+    if (v < 0.0f || u + v > 1.0f) return 0;
+    float th = f * f3_dot(e2, q);
+    if (th > OR_EPSILON && th < max_dist) { *t = th; return 1; }
+    return 0;
+}
+/* find_closest_hit, geometric.cuh:327-390; the helpers fill the sphere / triangle arrays in group-map order (pt_cu_helper.cpp:17-55) */
+static Hit gpu_find_closest_hit(OrScene *s, v3 ro, v3 rd) {
+    Hit best; memset(&best, 0, sizeof(best));
+    best.hit = 0; best.t = 1e20f; best.id = -1;
+    float t;
+    for (int gi = 0; gi < s->n_groups; ++gi) for (int k = 0; k < s->groups[gi].n; ++k) {
+        const Obj *o = &s->objs[s->groups[gi].objs[k]];
+        if (o->kind != 0) continue;
+        if (light_ball_intersect(ro, rd, o->v0, o->r, &t, 1e20f) && t < best.t) {
+            best.hit = 1; best.t = t; best.mtl = o->mtl; best.id = o->obj_id; best.is_light = 0;
+            best.pos = f3_add(ro, f3_muls(rd, t));
+            best.normal = f3_normalize(f3_sub(best.pos, o->v0));
+            if (f3_dot(best.normal, rd) > 0.0f) best.normal = f3_muls(best.normal, -1.0f);
+        }
+    }
+    for (int k = 0; k < s->n_lights; ++k) {
+        const Light *L = &s->lights[k];
+        if (light_ball_intersect(ro, rd, L->pos, L->ball_r, &t, 1e20f) && t < best.t) {
+            best.hit = 1; best.t = t; best.id = -2 - k; best.is_light = 1;
+            best.mtl.base_color = L->illum;                                  /* :359; the other fields keep the previous best's */
+            best.pos = f3_add(ro, f3_muls(rd, t));
+            best.normal = f3_normalize(f3_sub(best.pos, L->pos));
+            if (f3_dot(best.normal, rd) > 0.0f) best.normal = f3_muls(best.normal, -1.0f);
+        }
+    }
+    for (int gi = 0; gi < s->n_groups; ++gi) for (int k = 0; k < s->groups[gi].n; ++k) {
+        const Obj *o = &s->objs[s->groups[gi].objs[k]];
+        if (o->kind == 0) continue;
+        if (gpu_intersect_triangle(ro, rd, o, &t, 1e20f) && t < best.t) {
+            best.hit = 1; best.t = t; best.mtl = o->mtl; best.id = o->obj_id; best.is_light = 0;
+            best.pos = f3_add(ro, f3_muls(rd, t));
+            best.normal = f3_normalize(f3_cross(f3_sub(o->v1, o->v0), f3_sub(o->v2, o->v0)));
+            if (f3_dot(best.normal, rd) > 0.0f) best.normal = f3_muls(best.normal, -1.0f);
+        }
+    }
+    return best;
+}
+/* check_visibility, geometric.cuh:293-325, with mtl_old zero-initialised: 1 = unoccluded */
+static int gpu_check_visibility(OrScene *s, v3 p1, v3 p2) {
+    v3 diff = f3_sub(p2, p1);
+    float dist = f3_length(diff);
+    v3 dir = f3_divs(diff, dist);
+    float max_d = dist - 1e-3f, min_d = 1e-3f, t;
+    for (int i = 0; i < s->n_obj; ++i) {
+        const Obj *o = &s->objs[i];
+        int h = (o->kind == 0) ? light_ball_intersect(p1, dir, o->v0, o->r, &t, max_d) : gpu_intersect_triangle(p1, dir, o, &t, max_d);
+        if (h && t > min_d) return 0;
+    }
+    return 1;
+}
+static void camera_frame(const float *cam, int W, int H, v3 *cam_eye, v3 *cUL, v3 *cdx, v3 *cdy) {   /* cpu_bdpt.cpp:190-200, as or_render */
+    v3 eye = ld3(cam), look_at = ld3(cam + 3), view_up = ld3(cam + 6);
+    float aspect = (float) W / (float) H;
+    float theta = cam[9] * OR_PI / 180.0f;
+    float half_height = tanf(theta / 2.0f);
+    float half_width = aspect * half_height;
+    v3 cw = glm_normalize(f3_sub(eye, look_at));
+    v3 cu = glm_normalize(glm_cross(view_up, cw));
+    v3 cv = glm_cross(cw, cu);
+    *cUL = f3_sub(f3_add(f3_sub(eye, f3_muls(cu, half_width)), f3_muls(cv, half_height)), cw);
+    *cdx = f3_divs(f3_muls(cu, 2.0f * half_width), (float) W);
+    *cdy = f3_divs(f3_muls(cv, -2.0f * half_height), (float) H);
+    *cam_eye = eye;
+}
+static int gathers_light(const Mtl *m) { return m->eta <= 0.0f && (m->metallic < 0.99f || m->roughness > 0.01f); }   /* pt_cu.cu:126, ppm_cu.cu:221 */
+
+/* cuda_path_trace_kernel, pt_cu.cu:20-252.  image = mean over spp. */
+void or_render_pt(OrScene *s, const float *cam, int max_depth, int W, int H, int spp, const OrRenderOpts *opts, float *image, OrStats *stats) {
+    if (stats) memset(stats, 0, sizeof(*stats));
+    v3 cam_eye, cUL, cdx, cdy;
+    camera_frame(cam, W, H, &cam_eye, &cUL, &cdx, &cdy);
+    const int num_lights = s->n_lights;
+    const int nthreads = (opts && opts->nthreads > 0) ? opts->nthreads : omp_get_max_threads();
+    const int max_delta = opts ? opts->max_delta : 0;
+    const int sample_begin = opts ? opts->sample_begin : 0;
+    uint32_t key[2] = { 0u, 0u };
+    if (opts) { key[0] = (uint32_t) opts->seed; key[1] = (uint32_t) (opts->seed >> 32); }
+    Counters total; memset(&total, 0, sizeof(total));
+    double t0 = now_s();
+#pragma omp parallel num_threads(nthreads)
+    {
+        Counters c; memset(&c, 0, sizeof(c));
+#pragma omp for schedule(dynamic, 16)
+        for (int idx = 0; idx < W * H; ++idx) {
+            int px = idx % W, py = idx / W;
+            v3 color_sum = mk3(0, 0, 0);
+            for (int sidx = 0; sidx < spp; ++sidx) {
+                c.eye_samples++;
+                const uint32_t sg = (uint32_t) (sample_begin + sidx);
+                float u[4];
+                philox_unit4(key, (uint32_t) idx, sg, 0u, 2u, u);
+                v3 final_color = mk3(0, 0, 0);
+                float pixel_x = (float) px + u[0], pixel_y = (float) py + u[1];
+                v3 eyeray_point = cam_eye;
+                v3 pixel_pos = f3_add(f3_add(cUL, f3_muls(cdx, pixel_x)), f3_muls(cdy, pixel_y));
+                v3 eyeray_dir = f3_normalize(f3_sub(pixel_pos, eyeray_point));
+                float eyeray_refract = 1.0f;
+                v3 throughput = mk3(1.0f, 1.0f, 1.0f);
+                int last_is_delta = 1, n_delta = 0;
+                for (int depth = 0; depth < max_depth; ++depth) {
+                    Hit hit = gpu_find_closest_hit(s, eyeray_point, eyeray_dir);
+                    c.closest++;
+                    if (!hit.hit) break;
+                    v3 wo = f3_muls(eyeray_dir, -1.0f);
+                    const uint32_t bounce = (uint32_t) (depth + n_delta);
+                    if (hit.is_light) {                                       /* :58-122 */
+                        v3 emission = hit.mtl.base_color;
+                        float area = 1.0f, cone_ratio = 1.0f; int valid_light = 0;
+                        for (int i = 0; i < num_lights; ++i) {
+                            const Light *L = &s->lights[i];
+                            v3 center_to_hit = f3_sub(hit.pos, L->pos);
+                            if (fabsf(f3_length(center_to_hit) - L->ball_r) < 1e-2f) {
+                                valid_light = 1;
+                                area = 4.0f * OR_PI * L->ball_r * L->ball_r;
+                                if (L->cutoff > 0.0f && !L->is_parallel) {
+                                    cone_ratio = (1.0f - cosf(L->cutoff)) / 2.0f;
+                                    v3 main_dir = f3_normalize(L->dir);
+                                    if (depth == 0) cone_ratio = 1.f;
+                                    else if (f3_dot(main_dir, f3_normalize(center_to_hit)) < cosf(L->cutoff)) cone_ratio = 0.0f;
+                                }
+                                break;
+                            }
+                        }
+                        if (valid_light && cone_ratio > 0.0f) emission = f3_divs(emission, area * cone_ratio);
+                        else emission = mk3(0, 0, 0);
+                        if ((emission.x > 0.0f || emission.y > 0.0f || emission.z > 0.0f) && last_is_delta) {
+                            v3 contrib = f3_mul(throughput, emission);
+                            if (is_valid_color(contrib)) { final_color = f3_add(final_color, clamp_radiance(contrib, 15.0f)); c.path_samples++; }
+                        }                                                     /* the !last_is_delta branch never adds: pdf_light_dir = 0, :105-119 */
+                        break;
+                    }
+                    if (gathers_light(&hit.mtl) && num_lights > 0) {          /* :125-208 */
+                        float un[4];
+                        philox_unit4(key, (uint32_t) idx, sg, 1u + bounce, 4u, un);
+                        int l_idx = (int) (un[0] * num_lights); if (l_idx > num_lights - 1) l_idx = num_lights - 1;
+                        const Light *light = &s->lights[l_idx];
+                        if (light->is_parallel) {
+                            v3 light_dir = f3_normalize(f3_muls(f3_normalize(light->dir), -1.0f));
+                            float cos_surface = fmaxf(0.0f, f3_dot(hit.normal, light_dir));
+                            if (cos_surface > 0.0f) {
+                                c.shadow++;
+                                if (gpu_check_visibility(s, f3_add(hit.pos, f3_muls(hit.normal, OR_EPSILON)), f3_add(hit.pos, f3_muls(light_dir, 1e4f)))) {
+                                    v3 brdf = bsdf_evaluate(&hit.mtl, wo, light_dir, hit.normal);
+                                    v3 contrib = f3_muls(f3_muls(f3_mul(f3_mul(throughput, brdf), light->illum), cos_surface), (float) num_lights);
+                                    if (is_valid_color(contrib)) { final_color = f3_add(final_color, clamp_radiance(contrib, 15.0f)); c.path_samples++; }
+                                }
+                            }
+                        } else {
+                            /* random_in_unit_sphere_device + normalize (:153-155) = a uniform direction; drawn from two uniforms */
+                            float z = 1.0f - 2.0f * un[1], r = sqrtf(fmaxf(0.0f, 1.0f - z * z)), phi = 2.0f * OR_PI * un[2];
+                            v3 d_vec_local = mk3(r * cosf(phi), r * sinf(phi), z);
+                            v3 light_pos = f3_add(light->pos, f3_muls(d_vec_local, light->ball_r));
+                            v3 wi_light = f3_sub(light_pos, hit.pos);
+                            float dist2 = f3_dot(wi_light, wi_light);
+                            float dist = sqrtf(dist2);
+                            wi_light = f3_divs(wi_light, dist);
+                            float cos_surface = fmaxf(0.0f, f3_dot(hit.normal, wi_light));
+                            float cos_light = fmaxf(0.0f, f3_dot(d_vec_local, f3_muls(wi_light, -1.0f)));
+                            if (cos_surface > 0.0f && cos_light > 0.0f) {
+                                int inside_cone = 1;
+                                if (light->cutoff > 0.0f && !light->is_parallel) {
+                                    v3 main_dir = f3_normalize(light->dir);
+                                    if (f3_dot(main_dir, f3_muls(wi_light, -1.0f)) < cosf(light->cutoff)) inside_cone = 0;
+                                }
+                                if (inside_cone) {
+                                    c.shadow++;
+                                    if (gpu_check_visibility(s, f3_add(hit.pos, f3_muls(hit.normal, OR_EPSILON)), f3_add(light_pos, f3_muls(d_vec_local, OR_EPSILON)))) {
+                                        float area = 4.0f * OR_PI * light->ball_r * light->ball_r;
+                                        float pdf_light_area = 1.0f / (num_lights * area);
+                                        float pdf_light_dir = pdf_light_area * dist2 / fmaxf(cos_light, 1e-6f);
+                                        float pdf_bsdf = bsdf_pdf(&hit.mtl, wo, wi_light, hit.normal);
+                                        float p_l = pdf_light_dir * pdf_light_dir, p_b = pdf_bsdf * pdf_bsdf;
+                                        float mis_w = p_l / fmaxf(p_l + p_b, 1e-8f);
+                                        v3 brdf = bsdf_evaluate(&hit.mtl, wo, wi_light, hit.normal);
+                                        v3 contrib = f3_muls(f3_divs(f3_muls(f3_mul(f3_mul(throughput, brdf), light->illum), cos_surface), pdf_light_dir), mis_w);
+                                        if (is_valid_color(contrib)) { final_color = f3_add(final_color, clamp_radiance(contrib, 15.0f)); c.path_samples++; }
+                                    }
+                                }
+                            }
+                        }
+                    }
+                    v3 wi = mk3(0, 0, 0), bsdf_val = mk3(0, 0, 0);
+                    float pdf_omega = 0.0f, new_eta = 0.0f; int is_delta = 0;
+                    float ub[4];
+                    philox_unit4(key, (uint32_t) idx, sg, 1u + bounce, 2u, ub);
+                    bsdf_sample(&hit.mtl, wo, hit.normal, ub[0], ub[1], ub[2], eyeray_refract, &wi, &bsdf_val, &pdf_omega, &is_delta, &new_eta);
+                    if (pdf_omega <= 0.0f) break;                             /* :222; a delta sample with pdf 0 (TIR) ends the path too (see b2_pt.cuh) */
+                    if (is_delta) {
+                        throughput = f3_mul(throughput, bsdf_val);
+                        eyeray_dir = wi; eyeray_refract = new_eta;
+                        eyeray_point = f3_add(hit.pos, f3_muls(hit.normal, f3_dot(wi, hit.normal) < 0.0f ? -OR_EPSILON : OR_EPSILON));
+                        last_is_delta = 1;
+                        if (!is_valid_color(throughput)) break;
+                        ++n_delta;
+                        if (max_delta > 0 && n_delta >= max_delta) { c.delta_cap++; break; }
+                        depth--; continue;
+                    }
+                    float cos_wi = fabsf(f3_dot(hit.normal, wi));
+                    throughput = f3_divs(f3_muls(f3_mul(throughput, bsdf_val), cos_wi), pdf_omega);
+                    if (!is_valid_color(throughput)) break;
+                    eyeray_dir = wi;
+                    eyeray_point = f3_add(hit.pos, f3_muls(hit.normal, OR_EPSILON));
+                    last_is_delta = 0;
+                }
+                if (!is_valid_color(final_color)) final_color = mk3(0, 0, 0);
+                color_sum = f3_add(color_sum, final_color);
+            }
+            st3(image + 3 * (size_t) idx, f3_divs(color_sum, (float) spp));
+        }
+#pragma omp critical
+        { total.closest += c.closest; total.shadow += c.shadow; total.path_samples += c.path_samples; total.eye_samples += c.eye_samples; total.delta_cap += c.delta_cap; }
+    }
+    if (stats) {
+        stats->eye_samples = total.eye_samples; stats->closest_rays = total.closest; stats->shadow_rays = total.shadow;
+        stats->path_samples = total.path_samples; stats->delta_cap_hits = total.delta_cap; stats->seconds = now_s() - t0;
+    }
+}
+
+/* ppm_render_wrapper, ppm_cu.cu:325-398: eye pass, photon pass, resolve.  radius <= 0: PPM_RADIUS 0.05 (ppm_cu.cuh:5). */
+typedef struct { v3 pos, normal, wo, thr; Mtl mtl; int pixel, gx, gy, gz; uint64_t key; } OrHitPoint;
+static uint64_t cell_key(int gx, int gy, int gz) {
+    return ((uint64_t) ((uint32_t) (gx + (1 << 20)) & 0x1fffffu) << 42) | ((uint64_t) ((uint32_t) (gy + (1 << 20)) & 0x1fffffu) << 21) | (uint64_t) ((uint32_t) (gz + (1 << 20)) & 0x1fffffu);
+}
+static int cmp_hp(const void *a, const void *b) {
+    const OrHitPoint *x = (const OrHitPoint *) a, *y = (const OrHitPoint *) b;
+    if (x->key != y->key) return x->key < y->key ? -1 : 1;
+    return x->pixel - y->pixel;
+}
+void or_render_ppm(OrScene *s, const float *cam, int eye_depth, int light_depth, int W, int H, int spl, float radius,
+                   const OrRenderOpts *opts, float *image, OrStats *stats) {
+    if (stats) memset(stats, 0, sizeof(*stats));
+    if (!(radius > 0.0f)) radius = 0.05f;
+    v3 cam_eye, cUL, cdx, cdy;
+    camera_frame(cam, W, H, &cam_eye, &cUL, &cdx, &cdy);
+    const int num_lights = s->n_lights, npix = W * H;
+    const int nthreads = (opts && opts->nthreads > 0) ? opts->nthreads : omp_get_max_threads();
+    const int max_delta = opts ? opts->max_delta : 0;
+    const uint32_t sg = (uint32_t) (opts ? opts->sample_begin : 0);
+    uint32_t key[2] = { 0u, 0u };
+    if (opts) { key[0] = (uint32_t) opts->seed; key[1] = (uint32_t) (opts->seed >> 32); }
+    v3 min_bound, max_bound;
+    scene_bounds(s, &min_bound, &max_bound);
+    const float inv_cell = 1.0f / radius;
+    OrHitPoint *hp = (OrHitPoint *) calloc(npix > 0 ? npix : 1, sizeof(OrHitPoint));
+    int n_hp = 0;
+    uint64_t n_closest = 0, n_cap = 0, n_gather = 0;
+    double t0 = now_s();
+    memset(image, 0, sizeof(float) * 3 * (size_t) npix);
+    /* 1. ppm_eye_trace, :64-152 */
+    for (int idx = 0; idx < npix && eye_depth > 0; ++idx) {
+        int px = idx % W, py = idx / W;
+        float u[4];
+        philox_unit4(key, (uint32_t) idx, sg, 0u, 2u, u);
+        v3 pixel_pos = f3_add(f3_add(cUL, f3_muls(cdx, (float) px + u[0])), f3_muls(cdy, (float) py + u[1]));
+        v3 ro = cam_eye, rd = f3_normalize(f3_sub(pixel_pos, cam_eye));
+        float eta = 1.0f;
+        v3 thr = mk3(1.0f, 1.0f, 1.0f);
+        for (int n_delta = 0;; ++n_delta) {
+            Hit hit = gpu_find_closest_hit(s, ro, rd);
+            n_closest++;
+            if (!hit.hit) break;
+            v3 wo = f3_muls(rd, -1.0f);
+            if (hit.is_light) {
+                v3 contrib = f3_mul(thr, hit.mtl.base_color);
+                if (is_valid_color(contrib)) st3(image + 3 * (size_t) idx, clamp_radiance(contrib, 15.0f));
+                break;
+            }
+            v3 wi = mk3(0, 0, 0), bsdf_val = mk3(0, 0, 0);
+            float pdf_omega = 0.0f, new_eta = 0.0f; int is_delta = 0;
+            float ub[4];
+            philox_unit4(key, (uint32_t) idx, sg, 1u + (uint32_t) n_delta, 2u, ub);
+            bsdf_sample(&hit.mtl, wo, hit.normal, ub[0], ub[1], ub[2], eta, &wi, &bsdf_val, &pdf_omega, &is_delta, &new_eta);
+            if (!is_delta) {
+                OrHitPoint *h = &hp[n_hp++];
+                h->pos = hit.pos; h->normal = hit.normal; h->wo = wo; h->thr = thr; h->mtl = hit.mtl; h->pixel = idx;
+                h->gx = (int) floorf((hit.pos.x - min_bound.x) * inv_cell); h->gy = (int) floorf((hit.pos.y - min_bound.y) * inv_cell); h->gz = (int) floorf((hit.pos.z - min_bound.z) * inv_cell);
+                h->key = cell_key(h->gx, h->gy, h->gz);
+                break;
+            }
+            if (pdf_omega <= 0.0f) break;
+            thr = f3_mul(thr, bsdf_val);
+            rd = wi; eta = new_eta;
+            ro = f3_add(hit.pos, f3_muls(hit.normal, f3_dot(wi, hit.normal) < 0.0f ? -OR_EPSILON : OR_EPSILON));
+            if (!is_valid_color(thr)) break;
+            if (max_delta > 0 && n_delta + 1 >= max_delta) { n_cap++; break; }
+        }
+    }
+    /* 2. cell order (the reference's hash grid, :27-58, visits the same hit points: every one within `radius` lies in the 27 cells) */
+    qsort(hp, n_hp, sizeof(OrHitPoint), cmp_hp);
+    double *flux = (double *) calloc(3 * (size_t) (n_hp > 0 ? n_hp : 1), sizeof(double));
+    /* 3. ppm_photon_trace, :158-287 */
+    const int total_photons = num_lights * spl;
+#pragma omp parallel for num_threads(nthreads) schedule(dynamic, 64) reduction(+ : n_closest, n_cap, n_gather)
+    for (int idx = 0; idx < total_photons; ++idx) {
+        const Light *light = &s->lights[idx % num_lights];
+        float u[4];
+        philox_unit4(key, (uint32_t) idx, 0u, 0u, 5u, u);
+        v3 w = f3_normalize(light->dir), uu, vv;
+        if (fabsf(w.x) > 0.9f) uu = mk3(0.0f, 1.0f, 0.0f); else uu = mk3(1.0f, 0.0f, 0.0f);
+        vv = f3_normalize(f3_cross(w, uu));
+        uu = f3_normalize(f3_cross(vv, w));
+        v3 ro, rd;
+        if (light->is_parallel) {
+            rd = w;
+            v3 center = f3_muls(f3_add(min_bound, max_bound), 0.5f);
+            float scene_radius = f3_length(f3_sub(max_bound, min_bound)) * 0.5f, plane = scene_radius * 2.0f;
+            ro = f3_add(f3_add(f3_sub(center, f3_muls(rd, scene_radius * 2.0f)), f3_muls(uu, (u[0] - 0.5f) * plane)), f3_muls(vv, (u[1] - 0.5f) * plane));
+        } else {
+            float theta = acosf(1.0f - u[0] * (1.0f - cosf(light->cutoff))), phi = 2.0f * OR_PI * u[1];
+            v3 ld = mk3(sinf(theta) * cosf(phi), sinf(theta) * sinf(phi), cosf(theta));
+            rd = f3_normalize(f3_add(f3_add(f3_muls(uu, ld.x), f3_muls(vv, ld.y)), f3_muls(w, ld.z)));
+            ro = f3_add(light->pos, f3_muls(rd, light->ball_r));
+        }
+        v3 photon_flux = f3_muls(light->illum, (float) num_lights / fmaxf((float) spl, 1.0f));   /* :209 */
+        float eta = 1.0f;
+        int n_delta = 0;
+        for (int depth = 0; depth < light_depth; depth++) {
+            Hit hit = gpu_find_closest_hit(s, ro, rd);
+            n_closest++;
+            if (!hit.hit || hit.is_light) break;
+            v3 wi_light = f3_muls(rd, -1.0f);
+            if (gathers_light(&hit.mtl)) {
+                int gx = (int) floorf((hit.pos.x - min_bound.x) * inv_cell), gy = (int) floorf((hit.pos.y - min_bound.y) * inv_cell), gz = (int) floorf((hit.pos.z - min_bound.z) * inv_cell);
+                for (int z = -1; z <= 1; z++) for (int y = -1; y <= 1; y++) for (int x = -1; x <= 1; x++) {
+                    uint64_t k = cell_key(gx + x, gy + y, gz + z);
+                    int lo = 0, hi = n_hp;
+                    while (lo < hi) { int mid = (lo + hi) / 2; if (hp[mid].key < k) lo = mid + 1; else hi = mid; }
+                    for (int j = lo; j < n_hp && hp[j].key == k; ++j) {
+                        const OrHitPoint *h = &hp[j];
+                        if (!(f3_dot(h->normal, hit.normal) > 0.01f)) continue;
+                        v3 dd = f3_sub(h->pos, hit.pos);
+                        if (!(f3_dot(dd, dd) < radius * radius)) continue;
+                        v3 brdf = bsdf_evaluate(&h->mtl, h->wo, wi_light, h->normal);
+                        if (is_valid_color(brdf)) {
+                            v3 e = f3_mul(f3_mul(photon_flux, brdf), h->thr);
+#pragma omp atomic
+                            flux[3 * j] += e.x;
+#pragma omp atomic
+                            flux[3 * j + 1] += e.y;
+#pragma omp atomic
+                            flux[3 * j + 2] += e.z;
+                            n_gather++;
+                        }
+                    }
+                }
+            }
+            v3 wi = mk3(0, 0, 0), bsdf_val = mk3(0, 0, 0);
+            float pdf_omega = 0.0f, new_eta = 0.0f; int is_delta = 0;
+            float ub[4];
+            philox_unit4(key, (uint32_t) idx, 0u, 1u + (uint32_t) (depth + n_delta), 5u, ub);
+            bsdf_sample(&hit.mtl, wi_light, hit.normal, ub[0], ub[1], ub[2], eta, &wi, &bsdf_val, &pdf_omega, &is_delta, &new_eta);
+            if (pdf_omega <= 0.0f) break;
+            float cos_wi = fabsf(f3_dot(hit.normal, wi));
+            if (is_delta) {
+                photon_flux = f3_mul(photon_flux, bsdf_val);
+                ++n_delta;
+                if (max_delta > 0 && n_delta >= max_delta) { n_cap++; break; }
+                depth--;
+            } else photon_flux = f3_divs(f3_muls(f3_mul(photon_flux, bsdf_val), cos_wi), pdf_omega);
+            if (!is_valid_color(photon_flux)) break;
+            rd = wi; eta = new_eta;
+            ro = f3_add(hit.pos, f3_muls(hit.normal, f3_dot(wi, hit.normal) < 0.0f ? -OR_EPSILON : OR_EPSILON));
+        }
+    }
+    /* 4. ppm_resolve_image, :293-315 */
+    for (int j = 0; j < n_hp; ++j) {
+        float area = OR_PI * radius * radius;
+        v3 radiance = f3_divs(mk3((float) flux[3 * j], (float) flux[3 * j + 1], (float) flux[3 * j + 2]), fmaxf(area, 1e-6f));
+        if (is_valid_color(radiance)) {
+            float *px = image + 3 * (size_t) hp[j].pixel;
+            st3(px, f3_add(ld3(px), clamp_radiance(radiance, 15.0f)));
+        }
+    }
+    free(flux); free(hp);
+    if (stats) {
+        stats->eye_samples = (uint64_t) npix; stats->closest_rays = n_closest; stats->path_samples = n_gather; stats->delta_cap_hits = n_cap;
+        stats->shadow_rays = (uint64_t) n_hp; stats->seconds = now_s() - t0;
+    }
+}

@@ -85,6 +85,14 @@ void or_light_pool(OrScene *s, int light_depth, int spl, const OrRenderOpts *opt
 void or_render(OrScene *s, const float *cam, int eye_depth, int light_depth, int W, int H, int spp, int spl,
                const OrRenderOpts *opts, float *image, OrStats *stats);
 
+/* The reference's other two integrators (src/pt_cu.cu:20-252, src/ppm_cu.cu:64-322), restated on the Philox streams of the
+ * GPU path.  Parity UNPINNED on the CPU (the reference has no CPU implementation of them and seeds curand from the clock);
+ * pinned statistically against the reference's own kernels on the GPU box (tests/test_gpu_pt_ppm.py).
+ * or_render_ppm: stats->shadow_rays carries the number of hit points, path_samples the photon-to-hit-point gathers. */
+void or_render_pt(OrScene *s, const float *cam, int max_depth, int W, int H, int spp, const OrRenderOpts *opts, float *image, OrStats *stats);
+void or_render_ppm(OrScene *s, const float *cam, int eye_depth, int light_depth, int W, int H, int spl, float radius,
+                   const OrRenderOpts *opts, float *image, OrStats *stats);
+
 /* Philox4x32-10 block and the u32 -> [0,1) float map shared with the GPU (known-answer tested). */
 void or_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]);
 float or_u32_to_unit_float(uint32_t x);

@@ -181,6 +181,9 @@ class Port(_Lib):
         L.or_render.argtypes = [C.c_void_p, _f, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                 C.POINTER(OrRenderOpts), _f, C.POINTER(OrStats)]
         L.or_light_pool.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(OrRenderOpts), _f]
+        L.or_render_pt.argtypes = [C.c_void_p, _f, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(OrRenderOpts), _f, C.POINTER(OrStats)]
+        L.or_render_ppm.argtypes = [C.c_void_p, _f, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float,
+                                    C.POINTER(OrRenderOpts), _f, C.POINTER(OrStats)]
         L.or_parse_scene_file.restype = C.POINTER(OrParsed)
         L.or_parse_scene_file.argtypes = [C.c_char_p]
         L.or_parsed_free.argtypes = [C.POINTER(OrParsed)]
@@ -213,6 +216,22 @@ class Port(_Lib):
         st = OrStats()
         o = opts if opts is not None else self.opts()
         self.lib.or_render(h, _fa(cam), eye_depth, light_depth, W, H, spp, spl, C.byref(o), img.reshape(-1), C.byref(st))
+        return (img, st) if want_stats else img
+
+    def render_pt(self, h, cam, max_depth, W, H, spp, opts=None, want_stats=False):
+        """cuda_path_trace_kernel (src/pt_cu.cu:20-252) restated on Philox streams (opts.seed / sample_begin / max_delta)."""
+        img = np.zeros((H, W, 3), np.float32)
+        st = OrStats()
+        o = opts if opts is not None else self.opts(rng_mode=1)
+        self.lib.or_render_pt(h, _fa(cam), max_depth, W, H, spp, C.byref(o), img.reshape(-1), C.byref(st))
+        return (img, st) if want_stats else img
+
+    def render_ppm(self, h, cam, eye_depth, light_depth, W, H, spl, radius=0.0, opts=None, want_stats=False):
+        """ppm_render_wrapper (src/ppm_cu.cu:325-398) restated on Philox streams; one pass, spp ignored as in the reference."""
+        img = np.zeros((H, W, 3), np.float32)
+        st = OrStats()
+        o = opts if opts is not None else self.opts(rng_mode=1)
+        self.lib.or_render_ppm(h, _fa(cam), eye_depth, light_depth, W, H, spl, float(radius), C.byref(o), img.reshape(-1), C.byref(st))
         return (img, st) if want_stats else img
 
     def light_pool(self, h, n_lights, light_depth, spl, opts=None):

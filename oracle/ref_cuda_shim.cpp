@@ -54,6 +54,16 @@ struct QuietStdout {
     }
     ~QuietStdout() { if (saved >= 0) { fflush(stdout); std::cout.flush(); dup2(saved, 1); close(saved); } }
 };
+// move_data_to_cuda_{bdpt,pt,ppm} build every CudaSphere / CudaTriangle in an UNINITIALISED stack local and never assign its
+// mtl_old (bdpt_cu_helper.cpp:26,42, pt_cu_helper.cpp:25,41: the line is commented out), yet check_visibility decides
+// opaque / transparent on mtl_old.refract and tints by mtl_old.Ks (geometric.cuh:309-320): the reference's shadow rays
+// depend on whatever the caller left on the stack (seen here as a blue channel 3.5x too bright in one process and
+// correct in the next).  The shim zeroes the stack region the helper's frame will occupy, so the undefined read resolves
+// to "zero-initialised" = every object opaque -- the reading this repo's pt / ppm integrators and oracle document.
+__attribute__((noinline)) void scrub_stack() {
+    volatile unsigned char buf[1 << 16];
+    for (size_t i = 0; i < sizeof(buf); ++i) buf[i] = 0;
+}
 }  // namespace
 
 extern "C" {
@@ -115,19 +125,25 @@ double refcuda_render(void *h, int mode, const float *cam12, int W, int H, int s
     double ms = -1.0;
     if (mode == 0) {
         reset_ns(bdpt_ns::cuda_spheres, bdpt_ns::cuda_triangles, bdpt_ns::cuda_lights, bdpt_ns::scene_max_bound, bdpt_ns::scene_min_bound, cap);
-        move_data_to_cuda_bdpt(s->groups, s->lights, spl);
+        std::map<int, AABB> groups_copy = s->groups;      // the by-value argument, built before the scrub
+        scrub_stack();
+        move_data_to_cuda_bdpt(std::move(groups_copy), s->lights, spl);
         const auto t0 = std::chrono::steady_clock::now();
         run_cuda_bdpt(cam, img.data(), eye_depth, light_depth, W, H, spp, spl);
         ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     } else if (mode == 1) {
         reset_ns(pt_ns::cuda_spheres, pt_ns::cuda_triangles, pt_ns::cuda_lights, pt_ns::scene_max_bound, pt_ns::scene_min_bound, cap);
-        move_data_to_cuda_pt(s->groups, s->lights, spl);
+        std::map<int, AABB> groups_copy = s->groups;      // the by-value argument, built before the scrub
+        scrub_stack();
+        move_data_to_cuda_pt(std::move(groups_copy), s->lights, spl);
         const auto t0 = std::chrono::steady_clock::now();
         run_cuda_pt(cam, img.data(), eye_depth, light_depth, W, H, spp);
         ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     } else if (mode == 2) {
         reset_ns(ppm_ns::cuda_spheres, ppm_ns::cuda_triangles, ppm_ns::cuda_lights, ppm_ns::scene_max_bound, ppm_ns::scene_min_bound, cap);
-        move_data_to_cuda_ppm(s->groups, s->lights, spl);
+        std::map<int, AABB> groups_copy = s->groups;      // the by-value argument, built before the scrub
+        scrub_stack();
+        move_data_to_cuda_ppm(std::move(groups_copy), s->lights, spl);
         const auto t0 = std::chrono::steady_clock::now();
         run_cuda_ppm(cam, img.data(), eye_depth, light_depth, W, H, spp);
         ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();

@@ -35,7 +35,8 @@ class RenderParams(C.Structure):
                 ("eye_depth", C.c_int32), ("light_depth", C.c_int32), ("seed", C.c_uint64),
                 ("sample_offset", C.c_int32), ("sample_stride", C.c_int32), ("film_mode", C.c_int32),
                 ("strategies", C.c_int32), ("max_delta", C.c_int32), ("max_batch_paths", C.c_int32),
-                ("count_traversal", C.c_int32), ("profile_stages", C.c_int32)]
+                ("count_traversal", C.c_int32), ("profile_stages", C.c_int32),
+                ("integrator", C.c_int32), ("ppm_radius", C.c_float), ("reserved", C.c_int32 * 2)]
 
 
 class Stats(C.Structure):

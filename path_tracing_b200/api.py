@@ -15,6 +15,7 @@ from .scene import SceneData
 CLOSEST, ANY, BRUTE_FORCE, COUNT_VISITS = 0, 1, 16, 32
 FILM_MEAN, FILM_SUM = 0, 1
 STRATEGIES_REFERENCE, STRATEGIES_FULL, STRATEGIES_LIGHT_TRACING, STRATEGIES_NEE = 0, 1, 2, 3
+INTEGRATOR_BDPT, INTEGRATOR_PT, INTEGRATOR_PPM = 0, 1, 2      # main_cli's --mode (src/main_cli.cpp:201-213)
 
 
 def device_count():
@@ -91,20 +92,21 @@ class Scene:
 
     # ---- render ----
     def _params(self, width, height, spp, spl, eye_depth, light_depth, seed, sample_offset, sample_stride, film_mode,
-                max_delta, max_batch_paths, count_traversal, profile_stages=False, strategies=0):
+                max_delta, max_batch_paths, count_traversal, profile_stages=False, strategies=0, integrator=0, ppm_radius=0.0):
         return A.RenderParams(int(width), int(height), int(spp), int(spl), int(eye_depth), int(light_depth), int(seed),
                               int(sample_offset), int(sample_stride), int(film_mode), int(strategies), int(max_delta), int(max_batch_paths),
-                              1 if count_traversal else 0, 1 if profile_stages else 0)
+                              1 if count_traversal else 0, 1 if profile_stages else 0, int(integrator), float(ppm_radius))
 
     def render_bdpt(self, camera=None, width=None, height=None, spp=8, spl=8, eye_depth=4, light_depth=4, seed=1,
                     sample_offset=0, sample_stride=1, film_mode=FILM_MEAN, max_delta=0, max_batch_paths=0,
-                    count_traversal=False, profile_stages=False, out=None, device_ptr=None, stream=0, strategies=STRATEGIES_REFERENCE):
+                    count_traversal=False, profile_stages=False, out=None, device_ptr=None, stream=0, strategies=STRATEGIES_REFERENCE,
+                    integrator=INTEGRATOR_BDPT, ppm_radius=0.0):
         """Returns (film[H,W,3] float32, stats dict).  With device_ptr (int) the film stays on the device and None is returned for it."""
         cam = np.ascontiguousarray(self.data.camera if camera is None else camera, dtype=A.Camera).reshape(())
         W = int(width if width else self.data.width)
         H = int(height if height else self.data.height)
         p = self._params(W, H, spp, spl, eye_depth, light_depth, seed, sample_offset, sample_stride, film_mode, max_delta,
-                         max_batch_paths, count_traversal, profile_stages, strategies)
+                         max_batch_paths, count_traversal, profile_stages, strategies, integrator, ppm_radius)
         st = A.Stats()
         if device_ptr is not None:
             A.check(A.lib().b2_render_bdpt_device(self._h, cam.ctypes.data_as(C.c_void_p), C.byref(p), C.c_void_p(int(device_ptr)),
@@ -115,13 +117,23 @@ class Scene:
         A.check(A.lib().b2_render_bdpt(self._h, cam.ctypes.data_as(C.c_void_p), C.byref(p), A.ptr(film), C.byref(st)))
         return film, st.as_dict()
 
+    def render_pt(self, max_depth=8, **kw):
+        """run_cuda_pt (include/pt_cu_helper.h:6): path tracing with next-event estimation, max_depth non-delta bounces."""
+        kw.pop("integrator", None)
+        return self.render_bdpt(eye_depth=max_depth, integrator=INTEGRATOR_PT, **kw)
+
+    def render_ppm(self, spl=8, eye_depth=8, light_depth=8, ppm_radius=0.0, **kw):
+        """run_cuda_ppm (include/ppm_cu_helper.h): one photon-mapping pass of n_lights * spl photons; spp is ignored."""
+        kw.pop("integrator", None)
+        return self.render_bdpt(spl=spl, eye_depth=eye_depth, light_depth=light_depth, integrator=INTEGRATOR_PPM, ppm_radius=ppm_radius, **kw)
+
     def render_progressive(self, passes, camera=None, width=None, height=None, spp=8, spl=8, eye_depth=4, light_depth=4, seed=1,
-                           on_pass=None, want_rms=True):
+                           on_pass=None, want_rms=True, integrator=INTEGRATOR_BDPT):
         """The viewer's progressive accumulation (src/main.cpp:399-531): `passes` renders of `spp` samples (seed + pass)
         averaged.  Returns (film, rms[passes] or None, stats).  on_pass(pass, film_avg[H,W,3]) is called after every pass."""
         cam = np.ascontiguousarray(self.data.camera if camera is None else camera, dtype=A.Camera).reshape(())
         W = int(width if width else self.data.width); H = int(height if height else self.data.height)
-        p = self._params(W, H, spp, spl, eye_depth, light_depth, seed, 0, 1, FILM_MEAN, 0, 0, False)
+        p = self._params(W, H, spp, spl, eye_depth, light_depth, seed, 0, 1, FILM_MEAN, 0, 0, False, integrator=integrator)
         st = A.Stats()
         film = np.zeros((max(H, 0), max(W, 0), 3), np.float32)
         rms = np.zeros(max(int(passes), 0), np.float32) if want_rms else None
@@ -140,12 +152,12 @@ class Scene:
 
 
 def render_bdpt_multi(scenes, camera=None, width=None, height=None, spp=8, spl=8, eye_depth=4, light_depth=4, seed=1,
-                      film_mode=FILM_MEAN, max_batch_paths=0):
+                      film_mode=FILM_MEAN, max_batch_paths=0, integrator=INTEGRATOR_BDPT):
     """One process, len(scenes) GPUs (b2_render_bdpt_multi): scenes[g] is the same SceneData created on device g."""
     s0 = scenes[0]
     cam = np.ascontiguousarray(s0.data.camera if camera is None else camera, dtype=A.Camera).reshape(())
     W = int(width if width else s0.data.width); H = int(height if height else s0.data.height)
-    p = s0._params(W, H, spp, spl, eye_depth, light_depth, seed, 0, 1, film_mode, 0, max_batch_paths, False)
+    p = s0._params(W, H, spp, spl, eye_depth, light_depth, seed, 0, 1, film_mode, 0, max_batch_paths, False, integrator=integrator)
     st = A.Stats()
     film = np.zeros((max(H, 0), max(W, 0), 3), np.float32)
     handles = (C.c_void_p * len(scenes))(*[s._h for s in scenes])

@@ -160,7 +160,7 @@ B2_HD int any_step(const DevScene &sc, AnyTrav &t, uint2 *stack, int sstride, Tr
 // true = blocked by an opaque object within [1e-3, tMax] (cpu_check_visibility, cpu_bdpt.cpp:82-107).  The plain loop
 // (state in registers, no resumable struct): b2_intersect's any-hit kernel measured 629 vs 485 Mrays/s against a loop
 // over any_step on the 10 M-triangle soup.
-template <bool COUNT>
+template <bool COUNT, bool OPAQUE = false>       // OPAQUE: transparent materials block too (sc.gpu_sem callers, b2_isect.cuh)
 B2_HD bool occluded_bvh(const DevScene &sc, float3 ro, float3 rd, float tMax, uint2 *stack, int sstride, TravCounters *cnt) {
     const float tMin = 1e-3f;
     if (sc.n_nodes > 0) {
@@ -186,11 +186,11 @@ B2_HD bool occluded_bvh(const DevScene &sc, float3 ro, float3 rd, float tMax, ui
                 tribits &= tribits - 1u;
                 const int ti = (int) tri_base + bit;
                 const float4 b = sc.tri[3 * ti + 1];
-                if (f2u(b.w) & B2_MAT_TRANSPARENT) continue;
+                if (!OPAQUE && (f2u(b.w) & B2_MAT_TRANSPARENT)) continue;
                 const float4 a = sc.tri[3 * ti], c = sc.tri[3 * ti + 2];
                 if (COUNT) cnt->tris++;
                 float t;
-                if (tri_test(ro, rd, mk3(a), mk3(b), mk3(c), tMin, tMax, t) && group_pass(sc, (int) f2u(c.w), ro, rd, tMin, tMax)) return true;
+                if (tri_test(ro, rd, mk3(a), mk3(b), mk3(c), tMin, tMax, t) && (OPAQUE || group_pass(sc, (int) f2u(c.w), ro, rd, tMin, tMax))) return true;
             }
             if (hits_p) {
                 if ((grp.y >> 8) != 0u && sp < B2_STACK_CAP) stack[(sp++) * sstride] = grp;

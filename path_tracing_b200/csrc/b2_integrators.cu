@@ -1,0 +1,351 @@
+// b2_integrators.cu -- the pt and ppm modes of the reference's command line on the wavefront / BVH infrastructure of the
+// BDPT path (bodies in b2_pt.cuh).  Entered from b2_render_device_impl, so every render entry
+// point of include/b2pt.h (host film, device film, progressive, multi-GPU) serves them through B2RenderParams.integrator.
+//
+//   pt  (run_cuda_pt, src/pt_cu.cu): the reference runs one thread per PIXEL looping over spp and depth.  Here one wave =
+//       one bounce of every live path of a batch of up to 2^26 eye samples: k_pt_extend fuses the closest-hit traversal,
+//       the next-event shadow ray and the BSDF sample (a path has ONE shadow ray per vertex, so a separate connection
+//       stage would only add 80 B of HBM traffic per vertex), adds the bounce's radiance to the film with atomics and
+//       compacts the survivors into the next wave's queue with warp ballot + prefix.  Samples shard over GPUs as in BDPT.
+//   ppm (run_cuda_ppm, src/ppm_cu.cu): eye pass -> hit points appended compactly; 63-bit cell keys radix-sorted (CUB) so
+//       the hit points of a grid cell are one contiguous run; an open-addressing table maps cell -> run (the reference
+//       threads a linked list per hash bucket through the unsorted hit points); one thread per photon walks the BVH and
+//       adds its flux to the hit points of the 27 neighbouring cells with a 128-bit vector atomic; resolve per hit point.
+#include "b2_render.hpp"
+#include "b2_pt.cuh"
+#include "b2_warp.cuh"
+#include <algorithm>
+#include <cub/cub.cuh>
+
+namespace {
+
+constexpr int PT_THREADS = 128;
+
+template <bool PRIMARY, bool COUNT>
+__global__ void __launch_bounds__(PT_THREADS) k_pt_extend(RenderCtx c, int n_items, uint32_t pix0, int s0) {
+    extern __shared__ uint2 s_stack[];
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    TravCounters tc{ 0u, 0u };
+    uint32_t n_shadow = 0, n_path = 0, n_cap = 0;
+    PtState ps;
+    int path = -1;
+    bool alive = false;
+    if (q < n_items) {
+        if (PRIMARY) ps = pt_primary(c, pix0, s0, (uint32_t) q);
+        else { path = c.live[q]; ps = pt_load(c, path); }
+        const HitRec h = closest_hit_bvh<COUNT>(c.sc, ps.ro, ps.rd, s_stack + threadIdx.x, blockDim.x, &tc);
+        float3 add;
+        alive = pt_bounce<COUNT>(c, ps, h, s_stack + threadIdx.x, blockDim.x, &tc, add, n_shadow, n_path, n_cap);
+        if (add.x != 0.0f) atomicAdd(&c.film[3 * ps.pixel], add.x);
+        if (add.y != 0.0f) atomicAdd(&c.film[3 * ps.pixel + 1], add.y);
+        if (add.z != 0.0f) atomicAdd(&c.film[3 * ps.pixel + 2], add.z);
+    }
+    if (PRIMARY) path = warp_alloc(c.n_paths, alive);                 // a path gets its state slot when it survives its first bounce
+    const int li = warp_alloc(c.n_live_next, alive);
+    if (alive) { pt_store(c, path, ps); c.live_next[li] = path; }
+    warp_count_add(&c.counters[B2_CNT_SHADOW], n_shadow);
+    warp_count_add(&c.counters[B2_CNT_PATH_SAMPLES], n_path);
+    warp_count_add(&c.counters[B2_CNT_DELTA_CAP], n_cap);
+    if (COUNT) { warp_count_add(&c.counters[B2_CNT_NODES], tc.nodes); warp_count_add(&c.counters[B2_CNT_TRIS], tc.tris); }
+}
+
+// ---- ppm ----
+template <bool COUNT>
+__global__ void __launch_bounds__(PT_THREADS) k_ppm_eye(RenderCtx c, PpmCtx pc, uint32_t sidx) {
+    extern __shared__ uint2 s_stack[];
+    const int pixel = blockIdx.x * blockDim.x + threadIdx.x;
+    TravCounters tc{ 0u, 0u };
+    uint32_t n_closest = 0, n_cap = 0;
+    HitPoint hp;
+    bool have = false;
+    if (pixel < c.W * c.H) {
+        float3 direct;
+        have = ppm_eye_body<COUNT>(c, (uint32_t) pixel, sidx, s_stack + threadIdx.x, blockDim.x, &tc, hp, direct, n_closest, n_cap);
+        c.film[3 * pixel] = direct.x; c.film[3 * pixel + 1] = direct.y; c.film[3 * pixel + 2] = direct.z;
+    }
+    const int k = warp_alloc(pc.n_hp, have);
+    if (have) {
+        float4 *o = pc.hp + (size_t) B2_HP_F4 * k;                   // pc.hp = the unsorted list in this kernel
+        o[0] = mk4(hp.pos, 0.0f); o[1] = mk4(hp.n, u2f(hp.pixel)); o[2] = mk4(hp.wo, hp.mtl.roughness);
+        o[3] = mk4(hp.thr, hp.mtl.metallic); o[4] = mk4(hp.mtl.base, hp.mtl.eta);
+        int gx, gy, gz;
+        ppm_cell_of(c.sc, pc.inv_cell, hp.pos, gx, gy, gz);
+        pc.keys[k] = ppm_cell_key(gx, gy, gz);
+        pc.order[k] = (uint32_t) k;
+    }
+    warp_count_add(&c.counters[B2_CNT_CLOSEST], n_closest);
+    warp_count_add(&c.counters[B2_CNT_DELTA_CAP], n_cap);
+    if (COUNT) { warp_count_add(&c.counters[B2_CNT_NODES], tc.nodes); warp_count_add(&c.counters[B2_CNT_TRIS], tc.tris); }
+}
+// Sorted position k <- unsorted record order[k]; the first hit point of every cell claims a table slot {key + 1, start}.
+__global__ void __launch_bounds__(256) k_ppm_reorder(const float4 *__restrict__ hp_in, PpmCtx pc, const unsigned long long *__restrict__ skeys,
+                                                     const uint32_t *__restrict__ sorder, int n) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const float4 *src = hp_in + (size_t) B2_HP_F4 * sorder[k];
+    float4 *dst = pc.hp + (size_t) B2_HP_F4 * k;
+#pragma unroll
+    for (int j = 0; j < B2_HP_F4; ++j) dst[j] = src[j];
+    pc.flux[k] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    const unsigned long long key = skeys[k];
+    if (k == 0 || skeys[k - 1] != key) {
+        unsigned long long *tab = (unsigned long long *) pc.table;
+        uint32_t slot = ppm_hash(key + 1ull) & pc.table_mask;
+        while (atomicCAS(&tab[2 * (size_t) slot], 0ull, key + 1ull) != 0ull) slot = (slot + 1u) & pc.table_mask;   // keys are distinct here
+        tab[2 * (size_t) slot + 1] = (unsigned long long) (uint32_t) k;
+    }
+}
+// The last hit point of every cell completes its entry: {key + 1, start | count << 32}.
+__global__ void __launch_bounds__(256) k_ppm_cell_ends(PpmCtx pc, const unsigned long long *__restrict__ skeys, int n) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const unsigned long long key = skeys[k];
+    if (k + 1 < n && skeys[k + 1] == key) return;
+    unsigned long long *tab = (unsigned long long *) pc.table;
+    uint32_t slot = ppm_hash(key + 1ull) & pc.table_mask;
+    while (tab[2 * (size_t) slot] != key + 1ull) slot = (slot + 1u) & pc.table_mask;
+    const unsigned long long start = tab[2 * (size_t) slot + 1];
+    tab[2 * (size_t) slot + 1] = start | ((unsigned long long) ((uint32_t) k + 1u - (uint32_t) start) << 32);
+}
+struct FluxAtomic {
+    float4 *flux;
+    __device__ __forceinline__ void operator()(uint32_t k, float3 e) const { atomicAdd(&flux[k], make_float4(e.x, e.y, e.z, 1.0f)); }   // red.global.add.v4.f32
+};
+template <bool COUNT>
+__global__ void __launch_bounds__(PT_THREADS) k_ppm_photons(RenderCtx c, PpmCtx pc, int n_mine) {
+    extern __shared__ uint2 s_stack[];
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    TravCounters tc{ 0u, 0u };
+    uint32_t n_closest = 0, n_gather = 0, n_cap = 0;
+    if (q < n_mine) {
+        FluxAtomic fa{ pc.flux };
+        ppm_photon_body<COUNT>(c, pc, c.sample_offset + q * c.sample_stride, s_stack + threadIdx.x, blockDim.x, &tc, fa, n_closest, n_gather, n_cap);
+    }
+    warp_count_add(&c.counters[B2_CNT_CLOSEST], n_closest);
+    warp_count_add(&c.counters[B2_CNT_PATH_SAMPLES], n_gather);
+    warp_count_add(&c.counters[B2_CNT_DELTA_CAP], n_cap);
+    if (COUNT) { warp_count_add(&c.counters[B2_CNT_NODES], tc.nodes); warp_count_add(&c.counters[B2_CNT_TRIS], tc.tris); }
+}
+__global__ void __launch_bounds__(256) k_ppm_resolve(RenderCtx c, PpmCtx pc, int n) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const uint32_t pixel = f2u(pc.hp[(size_t) B2_HP_F4 * k + 1].w);
+    const float4 f = pc.flux[k];
+    const float3 direct = mk3(c.film[3 * pixel], c.film[3 * pixel + 1], c.film[3 * pixel + 2]);
+    const float3 r = ppm_resolve(direct, mk3(f), true, pc.radius);
+    c.film[3 * pixel] = r.x; c.film[3 * pixel + 1] = r.y; c.film[3 * pixel + 2] = r.z;
+}
+
+__global__ void __launch_bounds__(256) k_film_out(const float *__restrict__ sum, float *__restrict__ out, size_t n, float inv, int accumulate) {
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = accumulate ? out[i] + sum[i] * inv : sum[i] * inv;
+}
+
+int set_limits(int bvh_depth) {
+    static int configured[64];
+    int dev = 0;
+    B2_CUDA(cudaGetDevice(&dev));
+    if (dev < 64 && bvh_depth + 1 <= configured[dev]) return B2_OK;
+    const int sb = (int) stack_bytes(PT_THREADS, bvh_depth);
+    if (sb > 200 * 1024) { b2_set_error("BVH depth %d needs more shared memory for traversal stacks than a CTA has", bvh_depth); return B2_ERR_STATE; }
+    B2_CUDA(cudaFuncSetAttribute(k_pt_extend<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
+    B2_CUDA(cudaFuncSetAttribute(k_pt_extend<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
+    B2_CUDA(cudaFuncSetAttribute(k_pt_extend<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
+    B2_CUDA(cudaFuncSetAttribute(k_pt_extend<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
+    B2_CUDA(cudaFuncSetAttribute(k_ppm_eye<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
+    B2_CUDA(cudaFuncSetAttribute(k_ppm_eye<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
+    B2_CUDA(cudaFuncSetAttribute(k_ppm_photons<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
+    B2_CUDA(cudaFuncSetAttribute(k_ppm_photons<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
+    if (dev < 64) configured[dev] = bvh_depth + 1;
+    return B2_OK;
+}
+
+void fill_stats(B2Stats *stats, const unsigned long long *h_cnt, unsigned long long eye_samples, unsigned long long closest_host,
+                uint64_t n_batches, uint64_t n_waves, uint64_t n_launches, float ms_total) {
+    if (!stats) return;
+    memset(stats, 0, sizeof(*stats));
+    stats->eye_samples = eye_samples;
+    stats->closest_rays = h_cnt[B2_CNT_CLOSEST] + closest_host;
+    stats->shadow_rays = h_cnt[B2_CNT_SHADOW];
+    stats->path_samples = h_cnt[B2_CNT_PATH_SAMPLES];
+    stats->delta_cap_hits = h_cnt[B2_CNT_DELTA_CAP];
+    stats->nodes_visited = h_cnt[B2_CNT_NODES]; stats->tris_tested = h_cnt[B2_CNT_TRIS];
+    stats->n_batches = n_batches; stats->n_waves = n_waves; stats->n_launches = n_launches;
+    stats->ms_total = ms_total;
+}
+
+}  // namespace
+
+int RenderWorkspace::ensure_pt(int max_paths, size_t film_floats) {
+    const size_t mp = (size_t) std::max(max_paths, 1);
+    B2_TRY(ray_o.ensure(mp)); B2_TRY(ray_d.ensure(mp)); B2_TRY(thr.ensure(mp)); B2_TRY(last_pos.ensure(mp));
+    B2_TRY(live_a.ensure(mp)); B2_TRY(live_b.ensure(mp));
+    B2_TRY(film.ensure(film_floats));
+    if (!ints.p) B2_TRY(ints.alloc(8));
+    if (!counters.p) B2_TRY(counters.alloc(B2_CNT_N));
+    if (!h_ints) B2_CUDA(cudaMallocHost((void **) &h_ints, 8 * sizeof(int)));
+    return B2_OK;
+}
+int RenderWorkspace::ensure_ppm(int n_pix, size_t film_floats, size_t sort_tmp_bytes) {
+    const size_t n = (size_t) std::max(n_pix, 1);
+    B2_TRY(hp_in.ensure(B2_HP_F4 * n)); B2_TRY(hp.ensure(B2_HP_F4 * n)); B2_TRY(flux.ensure(n));
+    B2_TRY(hp_keys.ensure(n)); B2_TRY(hp_keys_sorted.ensure(n)); B2_TRY(hp_order.ensure(n)); B2_TRY(hp_order_sorted.ensure(n));
+    size_t cap = 1024;
+    while (cap < 2 * n) cap <<= 1;
+    B2_TRY(cell_table.ensure(cap));
+    B2_TRY(sort_tmp.ensure(sort_tmp_bytes));
+    B2_TRY(film.ensure(film_floats));
+    if (!ints.p) B2_TRY(ints.alloc(8));
+    if (!counters.p) B2_TRY(counters.alloc(B2_CNT_N));
+    if (!h_ints) B2_CUDA(cudaMallocHost((void **) &h_ints, 8 * sizeof(int)));
+    return B2_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// pt: run_cuda_pt (src/pt_cu_helper.cpp:62-72 -> pt_render_wrapper, src/pt_cu.cu:257-303)
+// ---------------------------------------------------------------------------------------------------------
+int b2_render_pt_impl(const DevScene &sc_in, int bvh_depth, RenderWorkspace &ws, const B2Camera &cam, const B2RenderParams &p,
+                      float *d_film_out, cudaStream_t st, B2Stats *stats) {
+    const int npix = p.width * p.height;
+    const size_t film_floats = (size_t) 3 * npix;
+    const int stride = p.sample_stride > 0 ? p.sample_stride : 1;
+    int n_my = 0;
+    for (long long s = p.sample_offset; s < p.spp; s += stride) n_my++;
+    const long long total = (long long) npix * n_my;
+    long long mp = p.max_batch_paths > 0 ? p.max_batch_paths : (1ll << 26);     // 72 B of state per path: 4.8 GB at 2^26
+    mp = std::max<long long>(std::min<long long>(mp, std::max<long long>(total, 1)), 1);
+    const int max_paths = (int) mp;
+    B2_TRY(ws.ensure_pt(max_paths, film_floats));
+    B2_TRY(set_limits(bvh_depth));
+    DevScene sc = sc_in;
+    sc.gpu_sem = 1;
+    RenderCtx c; b2_setup_ctx(c, sc, cam, p, ws, max_paths);
+    const bool count = p.count_traversal != 0;
+    uint64_t n_launches = 0, n_batches = 0, n_waves = 0;
+    unsigned long long eye_samples = 0, closest_host = 0;
+    cudaEvent_t ev0, ev1;
+    B2_CUDA(cudaEventCreate(&ev0)); B2_CUDA(cudaEventCreate(&ev1));
+    B2_CUDA(cudaEventRecord(ev0, st));
+    B2_CUDA(cudaMemsetAsync(ws.film.p, 0, sizeof(float) * film_floats, st));
+    B2_CUDA(cudaMemsetAsync(ws.counters.p, 0, sizeof(unsigned long long) * B2_CNT_N, st));
+    B2_CUDA(cudaMemsetAsync(ws.ints.p, 0, sizeof(int) * 8, st));
+    const size_t sb = stack_bytes(PT_THREADS, bvh_depth);
+    for (long long w0 = 0; w0 < total && p.eye_depth > 0; w0 += max_paths) {
+        int n_live = (int) std::min<long long>(max_paths, total - w0);
+        c.live = ws.live_a.p; c.live_next = ws.live_b.p;
+        n_batches++;
+        eye_samples += (unsigned long long) n_live;
+        B2_CUDA(cudaMemsetAsync(c.n_paths, 0, sizeof(int), st));
+        bool primary = true;
+        while (n_live > 0) {
+            B2_CUDA(cudaMemsetAsync(c.n_live_next, 0, sizeof(int), st));
+            const unsigned gb = blocks_for(n_live, PT_THREADS);
+            if (primary) {
+                const uint32_t pix0 = (uint32_t) (w0 % npix); const int s0 = (int) (w0 / npix);
+                if (count) k_pt_extend<true, true><<<gb, PT_THREADS, sb, st>>>(c, n_live, pix0, s0);
+                else k_pt_extend<true, false><<<gb, PT_THREADS, sb, st>>>(c, n_live, pix0, s0);
+            } else {
+                if (count) k_pt_extend<false, true><<<gb, PT_THREADS, sb, st>>>(c, n_live, 0u, 0);
+                else k_pt_extend<false, false><<<gb, PT_THREADS, sb, st>>>(c, n_live, 0u, 0);
+            }
+            B2_CUDA(cudaMemcpyAsync(ws.h_ints, c.n_live_next, sizeof(int), cudaMemcpyDeviceToHost, st));
+            n_launches++; n_waves++;
+            B2_CUDA(cudaStreamSynchronize(st));
+            B2_CUDA(cudaGetLastError());
+            closest_host += (unsigned long long) n_live;
+            n_live = ws.h_ints[0];
+            std::swap(c.live, c.live_next);
+            primary = false;
+        }
+    }
+    const float inv = p.film_mode == B2_FILM_SUM ? 1.0f : 1.0f / (float) p.spp;
+    k_film_out<<<blocks_for(film_floats, 256), 256, 0, st>>>(ws.film.p, d_film_out, film_floats, inv, p.film_mode == B2_FILM_ACCUMULATE);
+    n_launches++;
+    B2_CUDA(cudaGetLastError());
+    B2_CUDA(cudaEventRecord(ev1, st));
+    unsigned long long h_cnt[B2_CNT_N];
+    B2_CUDA(cudaMemcpyAsync(h_cnt, ws.counters.p, sizeof(h_cnt), cudaMemcpyDeviceToHost, st));
+    B2_CUDA(cudaStreamSynchronize(st));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ev0, ev1);
+    fill_stats(stats, h_cnt, eye_samples, closest_host, n_batches, n_waves, n_launches, ms);
+    cudaEventDestroy(ev0); cudaEventDestroy(ev1);
+    return B2_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// ppm: run_cuda_ppm (src/ppm_cu_helper.cpp:62-70 -> ppm_render_wrapper, src/ppm_cu.cu:325-398)
+// ---------------------------------------------------------------------------------------------------------
+int b2_render_ppm_impl(const DevScene &sc_in, int bvh_depth, RenderWorkspace &ws, const B2Camera &cam, const B2RenderParams &p,
+                       float *d_film_out, cudaStream_t st, B2Stats *stats) {
+    if ((p.sample_stride > 1 || p.sample_offset > 0)) {
+        b2_set_error("the ppm integrator does not shard: the photon flux of all photons is resolved with a clamp (ppm_cu.cu:293-315); render it on one GPU");
+        return B2_ERR_INVALID;
+    }
+    if ((long long) sc_in.n_lights * p.spl > (1ll << 30)) { b2_set_error("too many photons (n_lights * spl > 2^30)"); return B2_ERR_INVALID; }
+    const int npix = p.width * p.height;
+    const size_t film_floats = (size_t) 3 * npix;
+    size_t sort_bytes = 0;
+    B2_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, (unsigned long long *) nullptr, (unsigned long long *) nullptr,
+                                            (uint32_t *) nullptr, (uint32_t *) nullptr, npix, 0, 63, st));
+    B2_TRY(ws.ensure_ppm(npix, film_floats, sort_bytes));
+    B2_TRY(set_limits(bvh_depth));
+    DevScene sc = sc_in;
+    sc.gpu_sem = 1;
+    RenderCtx c; b2_setup_ctx(c, sc, cam, p, ws, 1);
+    PpmCtx pc;
+    pc.radius = p.ppm_radius > 0.0f ? p.ppm_radius : B2_PPM_RADIUS;
+    pc.inv_cell = 1.0f / pc.radius;
+    pc.hp = ws.hp_in.p; pc.flux = ws.flux.p; pc.direct = ws.film.p;
+    pc.keys = ws.hp_keys.p; pc.order = ws.hp_order.p;
+    pc.table = ws.cell_table.p; pc.table_mask = (uint32_t) (ws.cell_table.n - 1);
+    pc.n_hp = ws.ints.p + 5;
+    const bool count = p.count_traversal != 0;
+    uint64_t n_launches = 0;
+    cudaEvent_t ev0, ev1;
+    B2_CUDA(cudaEventCreate(&ev0)); B2_CUDA(cudaEventCreate(&ev1));
+    B2_CUDA(cudaEventRecord(ev0, st));
+    B2_CUDA(cudaMemsetAsync(ws.counters.p, 0, sizeof(unsigned long long) * B2_CNT_N, st));
+    B2_CUDA(cudaMemsetAsync(ws.ints.p, 0, sizeof(int) * 8, st));
+    B2_CUDA(cudaMemsetAsync(ws.cell_table.p, 0, sizeof(ulonglong2) * ws.cell_table.n, st));
+    const size_t sb = stack_bytes(PT_THREADS, bvh_depth);
+    // 1. eye pass (ppm_cu.cu:360-365): hit points, appended compactly
+    if (count) k_ppm_eye<true><<<blocks_for(npix, PT_THREADS), PT_THREADS, sb, st>>>(c, pc, (uint32_t) p.sample_offset);
+    else k_ppm_eye<false><<<blocks_for(npix, PT_THREADS), PT_THREADS, sb, st>>>(c, pc, (uint32_t) p.sample_offset);
+    B2_CUDA(cudaMemcpyAsync(ws.h_ints, pc.n_hp, sizeof(int), cudaMemcpyDeviceToHost, st));
+    B2_CUDA(cudaStreamSynchronize(st));
+    B2_CUDA(cudaGetLastError());
+    n_launches++;
+    const int n_hp = ws.h_ints[0];
+    const int n_photons = sc.n_lights * p.spl;                               // ppm_cu.cu:351
+    if (n_hp > 0) {
+        // 2. cell order + cell table (replaces reset_hash_grid / build_hash_grid_kernel, ppm_cu.cu:40-58, 368-378)
+        B2_CUDA(cub::DeviceRadixSort::SortPairs(ws.sort_tmp.p, sort_bytes, ws.hp_keys.p, ws.hp_keys_sorted.p, ws.hp_order.p, ws.hp_order_sorted.p, n_hp, 0, 63, st));
+        pc.hp = ws.hp.p;
+        k_ppm_reorder<<<blocks_for(n_hp, 256), 256, 0, st>>>(ws.hp_in.p, pc, ws.hp_keys_sorted.p, ws.hp_order_sorted.p, n_hp);
+        k_ppm_cell_ends<<<blocks_for(n_hp, 256), 256, 0, st>>>(pc, ws.hp_keys_sorted.p, n_hp);
+        n_launches += 3;
+        // 3. photons (ppm_cu.cu:381-386)
+        if (n_photons > 0 && p.light_depth > 0) {
+            if (count) k_ppm_photons<true><<<blocks_for(n_photons, PT_THREADS), PT_THREADS, sb, st>>>(c, pc, n_photons);
+            else k_ppm_photons<false><<<blocks_for(n_photons, PT_THREADS), PT_THREADS, sb, st>>>(c, pc, n_photons);
+            n_launches++;
+        }
+        // 4. resolve (ppm_cu.cu:389-392)
+        k_ppm_resolve<<<blocks_for(n_hp, 256), 256, 0, st>>>(c, pc, n_hp);
+        n_launches++;
+    }
+    k_film_out<<<blocks_for(film_floats, 256), 256, 0, st>>>(ws.film.p, d_film_out, film_floats, 1.0f, p.film_mode == B2_FILM_ACCUMULATE);
+    n_launches++;
+    B2_CUDA(cudaGetLastError());
+    B2_CUDA(cudaEventRecord(ev1, st));
+    unsigned long long h_cnt[B2_CNT_N];
+    B2_CUDA(cudaMemcpyAsync(h_cnt, ws.counters.p, sizeof(h_cnt), cudaMemcpyDeviceToHost, st));
+    B2_CUDA(cudaStreamSynchronize(st));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ev0, ev1);
+    fill_stats(stats, h_cnt, (unsigned long long) npix, 0ull, 1, 1, n_launches, ms);
+    if (stats) { stats->eye_vertices = (unsigned long long) n_hp; stats->pairs_tested = (unsigned long long) n_photons; }
+    cudaEventDestroy(ev0); cudaEventDestroy(ev1);
+    return B2_OK;
+}

@@ -103,10 +103,16 @@ B2_HD bool closer(float t, uint32_t order, float best_t, uint32_t best_order) {
 }
 
 // ---- spheres + light balls (short tables, tested after the triangles) ----
+// sc.gpu_sem (the pt / ppm integrators): ordinary spheres go through intersect_sphere like the light balls -- both roots,
+// so a ray that starts inside a sphere hits its far side (find_closest_hit, geometric.cuh:337-351) -- and there is no group cull.
 B2_HD void closest_spheres(const DevScene &sc, float3 ro, float3 rd, HitRec &best, uint32_t &best_order) {
     for (int i = 0; i < sc.n_sph; ++i) {
         float4 a = sc.sph[2 * i], b = sc.sph[2 * i + 1];
         float t;
+        if (sc.gpu_sem) {
+            if (light_ball_test(ro, rd, mk3(a), a.w, best.t, t)) { best.t = t; best.prim = prim_make(B2_KIND_SPHERE, i); best_order = f2u(b.x); }
+            continue;
+        }
         if (sphere_test(ro, rd, mk3(a), a.w, 1e-4f, best.t, t)) {
             uint32_t order = f2u(b.x);
             if ((best.prim == B2_PRIM_MISS || closer(t, order, best.t, best_order)) &&
@@ -123,11 +129,17 @@ B2_HD void closest_lights(const DevScene &sc, float3 ro, float3 rd, HitRec &best
         if (light_ball_test(ro, rd, mk3(a), a.w, best.t, t)) { best.t = t; best.prim = prim_make(B2_KIND_LIGHT, k); }
     }
 }
+// sc.gpu_sem: check_visibility of geometric.cuh:293-325 -- intersect_sphere within (EPSILON, tMax) and t > tMin, every
+// object opaque (its transparency test reads mtl_old, which the pt / ppm helpers never fill: taken as zero-initialised).
 B2_HD bool occluded_spheres(const DevScene &sc, float3 ro, float3 rd, float tMin, float tMax) {
     for (int i = 0; i < sc.n_sph; ++i) {
         float4 a = sc.sph[2 * i], b = sc.sph[2 * i + 1];
-        if (f2u(b.y) & B2_MAT_TRANSPARENT) continue;
         float t;
+        if (sc.gpu_sem) {
+            if (light_ball_test(ro, rd, mk3(a), a.w, tMax, t) && t > tMin) return true;
+            continue;
+        }
+        if (f2u(b.y) & B2_MAT_TRANSPARENT) continue;
         if (sphere_test(ro, rd, mk3(a), a.w, tMin, tMax, t) && group_pass(sc, (int) f2u(b.z), ro, rd, tMin, tMax)) return true;
     }
     return false;

@@ -18,6 +18,7 @@
 //   k_resolve      film / spp                                                                 :479
 #include "b2_render.hpp"
 #include "b2_strategies.cuh"
+#include "b2_warp.cuh"
 #include <algorithm>
 #include <vector>
 
@@ -32,23 +33,6 @@ constexpr int CONN_WARPS = CONN_THREADS / 32;
 constexpr int CONN_BLOCKS_PER_SM = B2_CONN_BLOCKS; // persistent grid = 148 SMs x this (also the register budget: launch bounds)
 constexpr int CONN_CHUNK = 8;         // pool vertices pre-tested per compaction round; the pre-test table is padded to a
                                       // multiple of this with records that never pass, and pool slices are whole chunks
-
-__device__ __forceinline__ uint32_t lanemask_lt() { uint32_t m; asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m)); return m; }
-
-// warp-reduce a per-thread count and add it to a global 64-bit counter with one atomic per warp
-__device__ __forceinline__ void warp_count_add(unsigned long long *counter, uint32_t v) {
-    v = __reduce_add_sync(0xffffffffu, v);
-    if ((threadIdx.x & 31) == 0 && v) atomicAdd(counter, (unsigned long long) v);
-}
-// warp-aggregated slot allocation: lanes with `want` get consecutive indices from *counter (one atomic per warp)
-__device__ __forceinline__ int warp_alloc(int *counter, bool want) {
-    const uint32_t m = __ballot_sync(0xffffffffu, want);
-    if (m == 0u) return -1;
-    int base = 0;
-    if ((threadIdx.x & 31) == (__ffs((int) m) - 1)) base = atomicAdd(counter, __popc(m));
-    base = __shfl_sync(0xffffffffu, base, __ffs((int) m) - 1);
-    return want ? base + __popc(m & lanemask_lt()) : -1;
-}
 
 template <bool COUNT>
 __global__ void __launch_bounds__(EXT_THREADS) k_light_paths(RenderCtx c, int n_paths) {
@@ -396,6 +380,8 @@ void RenderWorkspace::release() {
     ray_o.release(); ray_d.release(); thr.release(); last_pos.release(); last_n.release();
     hist_pe.release(); hist_pdf.release(); live_a.release(); live_b.release(); cv.release();
     pool.release(); pre.release(); film.release(); ints.release(); counters.release();
+    hp_in.release(); hp.release(); flux.release(); hp_keys.release(); hp_keys_sorted.release(); hp_order.release(); hp_order_sorted.release();
+    cell_table.release(); sort_tmp.release();
     if (h_ints) { cudaFreeHost(h_ints); h_ints = nullptr; }
     cap_paths = cap_depth = cap_pool = 0;
 }
@@ -408,11 +394,14 @@ static int validate_params(const B2RenderParams &p) {
     if ((long long) p.width * p.height > (1ll << 24)) { b2_set_error("film larger than 2^24 pixels is not supported"); return B2_ERR_INVALID; }
     if (p.sample_offset < 0 || p.sample_stride < 0) { b2_set_error("invalid sample_offset / sample_stride"); return B2_ERR_INVALID; }
     if (p.strategies < B2_STRATEGIES_REFERENCE || p.strategies > B2_STRATEGIES_NEE) { b2_set_error("unknown strategies value %d", p.strategies); return B2_ERR_INVALID; }
+    if (p.integrator < B2_INTEGRATOR_BDPT || p.integrator > B2_INTEGRATOR_PPM) { b2_set_error("unknown integrator value %d", p.integrator); return B2_ERR_INVALID; }
+    if (p.integrator != B2_INTEGRATOR_BDPT && p.strategies != B2_STRATEGIES_REFERENCE) { b2_set_error("strategies apply to the bdpt integrator only"); return B2_ERR_INVALID; }
+    if (!(p.ppm_radius >= 0.0f)) { b2_set_error("invalid ppm_radius"); return B2_ERR_INVALID; }
     if ((long long) p.spl * p.light_depth > (1ll << 26)) { b2_set_error("spl * light_depth too large"); return B2_ERR_INVALID; }
     return B2_OK;
 }
 
-static void setup_ctx(RenderCtx &c, const DevScene &sc, const B2Camera &cam, const B2RenderParams &p, RenderWorkspace &ws, int max_paths) {
+void b2_setup_ctx(RenderCtx &c, const DevScene &sc, const B2Camera &cam, const B2RenderParams &p, RenderWorkspace &ws, int max_paths) {
     memset(&c, 0, sizeof(c));
     c.sc = sc;
     c.sc.ggx_fix = p.strategies != B2_STRATEGIES_REFERENCE;      // normalised GGX D only outside parity mode (b2_bsdf.cuh)
@@ -451,7 +440,6 @@ struct StageTimer {
     ~StageTimer() { for (cudaEvent_t e : pool) cudaEventDestroy(e); for (Rec &r : pending) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); } }
 };
 
-static size_t stack_bytes(int threads, int bvh_depth) { return (size_t) threads * (size_t) std::max(bvh_depth + 1, 2) * sizeof(uint2); }
 
 // Light pool generation (shared by render and b2_light_pool).  Leaves *n_pool_active in ws.ints[0].
 static int build_pool(RenderCtx &c, int bvh_depth, bool count, cudaStream_t st, uint64_t &n_launches) {
@@ -495,6 +483,8 @@ static int set_smem_limits(int bvh_depth) {
 int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws, const B2Camera &cam, const B2RenderParams &p,
                           float *d_film_out, cudaStream_t st, B2Stats *stats) {
     B2_TRY(validate_params(p));
+    if (p.integrator == B2_INTEGRATOR_PT) return b2_render_pt_impl(sc, bvh_depth, ws, cam, p, d_film_out, st, stats);
+    if (p.integrator == B2_INTEGRATOR_PPM) return b2_render_ppm_impl(sc, bvh_depth, ws, cam, p, d_film_out, st, stats);
     const int npix = p.width * p.height;
     const size_t film_floats = (size_t) 3 * npix;
     const int stride = p.sample_stride > 0 ? p.sample_stride : 1;
@@ -522,7 +512,7 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
     const int n_pool = sc.n_lights * p.spl * p.light_depth;
     B2_TRY(ws.ensure(max_paths, std::max(p.eye_depth, 1), std::max(n_pool, 1), film_floats));
     B2_TRY(set_smem_limits(bvh_depth));
-    RenderCtx c; setup_ctx(c, sc, cam, p, ws, max_paths);
+    RenderCtx c; b2_setup_ctx(c, sc, cam, p, ws, max_paths);
     const bool count = p.count_traversal != 0;
     uint64_t n_launches = 0, n_batches = 0, n_waves = 0;
     StageTimer tm; tm.on = p.profile_stages != 0; tm.st = st;
@@ -641,7 +631,7 @@ int b2_light_pool_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws, c
     B2_TRY(set_smem_limits(bvh_depth));
     B2Camera cam; memset(&cam, 0, sizeof(cam)); cam.look_at[2] = 1.f; cam.view_up[1] = 1.f; cam.fov = 50.f;
     B2RenderParams pp = p; pp.width = pp.height = 1;
-    RenderCtx c; setup_ctx(c, sc, cam, pp, ws, 1);
+    RenderCtx c; b2_setup_ctx(c, sc, cam, pp, ws, 1);
     B2_CUDA(cudaMemsetAsync(ws.counters.p, 0, sizeof(unsigned long long) * B2_CNT_N, st));
     uint64_t nl = 0;
     B2_TRY(build_pool(c, bvh_depth, false, st, nl));

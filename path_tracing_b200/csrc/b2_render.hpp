@@ -16,9 +16,24 @@ struct RenderWorkspace {
     int cap_paths = 0, cap_depth = 0, cap_pool = 0;
     unsigned long long closest_rays_host = 0;
     int ensure(int max_paths, int eye_depth, int n_pool, size_t film_floats);
+    // the pt / ppm integrators (b2_integrators.cu): path state without the BDPT history, hit points and their cell table
+    int ensure_pt(int max_paths, size_t film_floats);
+    DevBuf<float4> hp_in, hp, flux;
+    DevBuf<unsigned long long> hp_keys, hp_keys_sorted;
+    DevBuf<uint32_t> hp_order, hp_order_sorted;
+    DevBuf<ulonglong2> cell_table;
+    DevBuf<unsigned char> sort_tmp;
+    int ensure_ppm(int n_pix, size_t film_floats, size_t sort_tmp_bytes);
     void release();
     ~RenderWorkspace() { release(); }
 };
+
+inline size_t stack_bytes(int threads, int bvh_depth) { return (size_t) threads * (size_t) (bvh_depth + 1 > 2 ? bvh_depth + 1 : 2) * sizeof(uint2); }
+void b2_setup_ctx(RenderCtx &c, const DevScene &sc, const B2Camera &cam, const B2RenderParams &p, RenderWorkspace &ws, int max_paths);
+int b2_render_pt_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws, const B2Camera &cam, const B2RenderParams &p,
+                      float *d_film_out, cudaStream_t st, B2Stats *stats);
+int b2_render_ppm_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws, const B2Camera &cam, const B2RenderParams &p,
+                       float *d_film_out, cudaStream_t st, B2Stats *stats);
 
 // d_film_out: W*H*3 floats on the device.  Blocks until `st` has drained the render (the counters are read back).
 int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws, const B2Camera &cam, const B2RenderParams &p,

@@ -6,9 +6,10 @@
 //                --passes N --dump-every K: the viewer's progressive accumulation (src/main.cpp:399-531) headless: N renders
 //                of --spp samples each (seed + pass) averaged; every K passes the running average is written next to
 //                --output as <stem>_passNNNN<ext>, and the viewer's frame-to-frame RMS curve goes to <stem>_rms.txt
-// Only the BDPT path exists in this library: --mode pt / ppm and --device cpu exit with a message (the CPU integrator
-// is the reference's own cpu_bdpt.cpp; this library has no CPU execution path).  Note the reference's own default mode
-// is "pt"; here the default is "bdpt" because it is the only mode built.
+// --mode pt / ppm run the library's versions of run_cuda_pt / run_cuda_ppm (B2RenderParams.integrator; for pt the depth
+// is --eye-depth, for ppm --spp is ignored as in the reference and --gpus must be 1).  --device cpu exits with a message
+// (the CPU integrator is the reference's own cpu_bdpt.cpp; this library has no CPU execution path).  The default mode is
+// "pt", the reference's own default (main_cli.cpp:47).
 // The camera is Camera{eye, look_at, view_up, fov} as run_cpu_bdpt uses it (cpu_bdpt.cpp:190-200), not the CLI's
 // hard-coded F = 50 (main_cli.cpp:158-160).
 #include <chrono>
@@ -24,7 +25,7 @@ static void usage() {
            "Options:\n"
            "  --spp <int>          Samples per pixel (default: 8)\n"
            "  --spl <int>          Samples per light (default: 8)\n"
-           "  --mode <string>      Render mode: bdpt (pt, ppm: not built) (default: bdpt)\n"
+           "  --mode <string>      Render mode: pt, bdpt, ppm (default: pt)\n"
            "  --device <string>    Compute device: gpu (cpu: not built) (default: gpu)\n"
            "  --output <string>    Output image path (.png, .ppm, .pfm)\n"
            "  --input <string>     Input scene file\n"
@@ -50,7 +51,7 @@ int main(int argc, char **argv) {
     int passes = 1, dump_every = 0, strategies = B2_STRATEGIES_REFERENCE;
     int spp = 8, spl = 8, width = 0, height = 0, eye_depth = 4, light_depth = 4, gpus = 1;
     unsigned long long seed = 1;
-    std::string mode = "bdpt", output_file = "output.png", input_file = "../../input.txt", device = "gpu";
+    std::string mode = "pt", output_file = "output.png", input_file = "../../input.txt", device = "gpu";
     for (int i = 1; i < argc; ++i) {
         const std::string arg = argv[i];
         auto next = [&]() -> const char * { return i + 1 < argc ? argv[++i] : nullptr; };
@@ -79,10 +80,12 @@ int main(int argc, char **argv) {
         else if (arg == "--help" || arg == "-h") { usage(); return 0; }
     }
     printf("====================================\n");
-    printf(" Device : %s\n Mode   : %s\n SPP    : %d\n SPL    : %d (used in BDPT)\n Input  : %s\n Output : %s\n", device.c_str(), mode.c_str(), spp, spl,
+    printf(" Device : %s\n Mode   : %s\n SPP    : %d\n SPL    : %d (used in BDPT/PPM)\n Input  : %s\n Output : %s\n", device.c_str(), mode.c_str(), spp, spl,
            input_file.c_str(), output_file.c_str());
     printf("====================================\n");
-    if (mode != "bdpt") { fprintf(stderr, "[Error] mode '%s' is not built in this library (only the BDPT path is)\n", mode.c_str()); return 2; }
+    int integrator = B2_INTEGRATOR_BDPT;
+    if (mode == "pt") integrator = B2_INTEGRATOR_PT; else if (mode == "ppm") integrator = B2_INTEGRATOR_PPM;
+    else if (mode != "bdpt") { fprintf(stderr, "[Error] unknown mode '%s' (pt, bdpt, ppm)\n", mode.c_str()); return 2; }
     if (device != "gpu") { fprintf(stderr, "[Error] device '%s': this library has no CPU path (the CPU integrator is the reference's cpu_bdpt.cpp)\n", device.c_str()); return 2; }
 
     B2ParsedScene *ps = nullptr;
@@ -113,7 +116,7 @@ int main(int argc, char **argv) {
         const auto t0 = std::chrono::steady_clock::now();
         B2RenderParams p; memset(&p, 0, sizeof(p));
         p.width = width; p.height = height; p.spp = spp; p.spl = spl; p.eye_depth = eye_depth; p.light_depth = light_depth;
-        p.seed = seed; p.sample_offset = 0; p.sample_stride = 1; p.film_mode = B2_FILM_MEAN; p.strategies = strategies;
+        p.seed = seed; p.sample_offset = 0; p.sample_stride = 1; p.film_mode = B2_FILM_MEAN; p.strategies = strategies; p.integrator = integrator;
         if (passes <= 1) rc = b2_render_bdpt_multi(scenes.data(), gpus, &ps->camera, &p, film.data(), &st);
         else {
             const size_t dot = output_file.find_last_of('.');

@@ -18,7 +18,7 @@ static void hs_make_view(HsScene *s) {
     v.n_tris = (int) s->hs.tris.size(); v.n_nodes = (int) (s->bvh.nodes.size() / B2_NODE_UINT4);
     v.n_sph = s->hs.n_sph; v.n_lights = s->hs.n_lights; v.n_mats = s->hs.n_mats; v.n_groups = s->hs.n_groups;
     v.scene_min = s->hs.scene_min; v.scene_max = s->hs.scene_max;
-    v.ggx_fix = 0;                                      // parity mode
+    v.ggx_fix = 0; v.gpu_sem = 0;                       // parity mode
 }
 
 extern "C" {
@@ -69,7 +69,15 @@ void hs_intersect(void *h, const float *org, const float *dir, size_t n, int mod
 }  // extern "C"
 
 #include "hostsim_render.hpp"
+#include "hostsim_pt.hpp"
 extern "C" {
+// integrator 1 = pt, 2 = ppm (B2RenderParams.integrator)
+void hs_render_other(void *h, const B2Camera *cam, const B2RenderParams *p, float *film, unsigned long long *counters) {
+    HsScene *s = (HsScene *) h;
+    HsRenderOut out;
+    if (p->integrator == B2_INTEGRATOR_PPM) hs_render_ppm(s->view, *cam, *p, film, out); else hs_render_pt(s->view, *cam, *p, film, out);
+    if (counters) memcpy(counters, out.counters, sizeof(out.counters));
+}
 void hs_render_bdpt(void *h, const B2Camera *cam, const B2RenderParams *p, float *film, unsigned long long *counters) {
     HsScene *s = (HsScene *) h;
     HsRenderOut out;

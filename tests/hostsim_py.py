@@ -34,6 +34,7 @@ class HostSim:
         L.hs_intersect.argtypes = [vp, vp, vp, sz, C.c_int, vp, vp, vp]
         L.hs_render_bdpt.argtypes = [vp, vp, C.POINTER(A.RenderParams), vp, vp]
         L.hs_light_pool.argtypes = [vp, C.POINTER(A.RenderParams), vp]
+        L.hs_render_other.argtypes = [vp, vp, C.POINTER(A.RenderParams), vp, vp]
         self.data = data
         self.h = L.hs_scene_create(A.ptr(data.tris), len(data.tris), A.ptr(data.spheres), len(data.spheres), A.ptr(data.materials),
                                    len(data.materials), A.ptr(data.lights), len(data.lights), max_leaf, pad_rel)
@@ -61,6 +62,15 @@ class HostSim:
         film = np.zeros((H, W, 3), np.float32); cnt = np.zeros(16, np.uint64)
         self.L.hs_render_bdpt(self.h, cam.ctypes.data_as(C.c_void_p), C.byref(p), A.ptr(film), A.ptr(cnt))
         names = ["eye_samples", "closest_rays", "shadow_rays", "path_samples", "delta_cap_hits", "nodes", "tris", "pairs", "pretest_mismatch"]
+        return film, {k: int(cnt[i]) for i, k in enumerate(names)}
+
+    def render_other(self, integrator, W, H, spp=1, spl=8, eye_depth=8, light_depth=8, seed=1, ppm_radius=0.0, camera=None):
+        """integrator 1 = pt (eye_depth = max_depth), 2 = ppm."""
+        cam = np.ascontiguousarray(self.data.camera if camera is None else camera, dtype=A.Camera).reshape(())
+        p = A.RenderParams(W, H, spp, spl, eye_depth, light_depth, seed, 0, 1, 0, 0, 0, 0, 1, 0, integrator, ppm_radius)
+        film = np.zeros((H, W, 3), np.float32); cnt = np.zeros(16, np.uint64)
+        self.L.hs_render_other(self.h, cam.ctypes.data_as(C.c_void_p), C.byref(p), A.ptr(film), A.ptr(cnt))
+        names = ["eye_samples", "closest_rays", "shadow_rays", "path_samples", "delta_cap_hits", "nodes", "tris"]
         return film, {k: int(cnt[i]) for i, k in enumerate(names)}
 
     def light_pool(self, spl, light_depth, seed=1):

@@ -259,9 +259,9 @@ def test_pt_cli_renders_the_reference_scene(tmp_path):
     film, _ = sc.render_bdpt(width=64, height=48, spp=4, spl=4, eye_depth=4, light_depth=4, seed=1)
     want = api.film_to_rgb8(film)
     assert (np.abs(img.astype(int) - want.astype(int)) <= 1).mean() > 0.999      # atomics: last-bit film differences only
-    for bad in (["--mode", "pt"], ["--device", "cpu"]):
+    for bad in (["--mode", "whitted"], ["--device", "cpu"]):
         r = subprocess.run([g.CLI, "--input", str(scene_txt)] + bad, capture_output=True, text=True, timeout=60)
-        assert r.returncode == 2 and "not built" in r.stderr or "no CPU path" in r.stderr
+        assert r.returncode == 2 and ("unknown mode" in r.stderr or "no CPU path" in r.stderr)
     sc.close()
 
 
@@ -284,7 +284,7 @@ def test_progressive_passes_average_independent_renders(tmp_path):
     assert st["eye_samples"] == 3 * 64 * 48 * 4
     # the CLI: --passes / --dump-every
     scene_txt = tmp_path / "scene.txt"; sd.write_text(scene_txt)
-    r = subprocess.run([g.CLI, "--input", str(scene_txt), "--output", str(tmp_path / "p.ppm"), "--spp", "4", "--spl", "4", "--width", "64", "--height", "48",
+    r = subprocess.run([g.CLI, "--mode", "bdpt", "--input", str(scene_txt), "--output", str(tmp_path / "p.ppm"), "--spp", "4", "--spl", "4", "--width", "64", "--height", "48",
                         "--seed", "7", "--passes", "3", "--dump-every", "2"], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout + r.stderr
     assert (tmp_path / "p_pass0002.ppm").exists() and not (tmp_path / "p_pass0001.ppm").exists() and (tmp_path / "p.ppm").exists()

@@ -1,0 +1,154 @@
+"""The pt and ppm integrators on the GPU (csrc/b2_integrators.cu) through the C ABI:
+ (1) against oracle/bdpt_oracle.c's restatement of src/pt_cu.cu / src/ppm_cu.cu on identical Philox streams;
+ (2) against the reference's OWN kernels (pt_cu.cu / ppm_cu.cu compiled unmodified for sm_100a, oracle/_ref/libref_cuda.so)
+     run on the same GPU -- they seed curand from the clock, so that comparison is statistical, with the reference's
+     run-to-run difference as the noise floor;
+ (3) sample sharding, progressive passes and the argument checks of the new B2RenderParams fields."""
+import numpy as np
+import pytest
+
+from oracle import oracle_py as O
+from path_tracing_b200 import _abi as A
+from path_tracing_b200 import api
+from path_tracing_b200.scene import reference_scene
+
+pytestmark = pytest.mark.gpu
+need_ref_cuda = pytest.mark.skipif(not O.have_ref_cuda(), reason="oracle/_ref/libref_cuda.so not built (needs /root/reference at build time)")
+
+
+def desc(sd):
+    f = sd.to_flat()
+    return O.SceneDesc(f["kind"], f["group"], f["geom"], f["mtl"], f["lights"], f["cam"], f["W"], f["H"])
+
+
+def frac_close(a, b, tol=1e-3):
+    scale = max(float(a.mean()), 1e-6)
+    return float((np.abs(a - b).max(axis=2) <= tol * scale).mean())
+
+
+@pytest.mark.parametrize("name", ["cornell", "mis"])
+def test_pt_matches_the_restated_kernel_on_identical_streams(name):
+    sd = reference_scene(name)
+    d = desc(sd)
+    P = O.Port(); h = P.scene(d)
+    W, H, spp, depth = 96, 64, 8, 8
+    ref, st = P.render_pt(h, d.cam, depth, W, H, spp, P.opts(rng_mode=1, seed=7, max_delta=256), want_stats=True)
+    P.destroy(h)
+    sc = api.Scene(sd)
+    img, gs = sc.render_pt(max_depth=depth, width=W, height=H, spp=spp, seed=7)
+    small, _ = sc.render_pt(max_depth=depth, width=W, height=H, spp=spp, seed=7, max_batch_paths=5000)     # batch split: same streams
+    sc.close()
+    assert gs["eye_samples"] == st.eye_samples == W * H * spp
+    for k, v in (("closest_rays", st.closest_rays), ("shadow_rays", st.shadow_rays), ("path_samples", st.path_samples)):
+        assert abs(gs[k] - v) <= 2e-3 * v + 2, (k, gs[k], v)
+    assert np.allclose(img.mean(axis=(0, 1)), ref.mean(axis=(0, 1)), rtol=5e-3, atol=1e-6)
+    assert frac_close(ref, img) >= 0.99
+    assert frac_close(img, small, 1e-4) >= 0.999          # film atomics: summation order only
+
+
+@pytest.mark.parametrize("name", ["cornell", "mis"])
+def test_ppm_matches_the_restated_kernels_on_identical_streams(name):
+    sd = reference_scene(name)
+    d = desc(sd)
+    P = O.Port(); h = P.scene(d)
+    W, H, spl = 96, 64, 4000
+    ref, st = P.render_ppm(h, d.cam, 8, 6, W, H, spl, 0.0, P.opts(rng_mode=1, seed=9, max_delta=256), want_stats=True)
+    P.destroy(h)
+    sc = api.Scene(sd)
+    img, gs = sc.render_ppm(spl=spl, eye_depth=8, light_depth=6, width=W, height=H, seed=9)
+    sc.close()
+    assert gs["eye_vertices"] == st.shadow_rays                  # hit points
+    assert abs(gs["closest_rays"] - st.closest_rays) <= 2e-3 * st.closest_rays + 2
+    assert abs(gs["path_samples"] - st.path_samples) <= 5e-3 * st.path_samples + 2
+    assert np.allclose(img.mean(axis=(0, 1)), ref.mean(axis=(0, 1)), rtol=1e-2, atol=1e-6)
+    assert frac_close(ref, img) >= 0.97
+
+
+def _block_means(x, b):
+    H, W, _ = x.shape
+    return x[:H // b * b, :W // b * b].reshape(H // b, b, W // b, b, 3).mean(axis=(1, 3))
+
+
+def _robust_agreement(img, img2, ref, block, mean_tol, block_tol):
+    """img / img2: two renders of this repo with different seeds (their difference is the noise floor: the reference seeds
+    curand with time(NULL), so two of ITS renders within one second are identical); ref: the reference kernel's film."""
+    m, m2, mr = img.mean(axis=(0, 1)), img2.mean(axis=(0, 1)), ref.mean(axis=(0, 1))
+    floor = np.abs(m - m2) / np.maximum(mr, 1e-9)
+    assert np.all(np.abs(m - mr) <= np.maximum(4.0 * floor, mean_tol) * mr + 1e-7), (m, m2, mr)
+    a, a2, b = _block_means(img, block), _block_means(img2, block), _block_means(ref, block)
+    sel = b > 0.05 * b.mean()
+    if sel.sum() < 24:            # the mis scene as parsed is black except for a few visible light balls: nothing to compare block by block
+        return
+    noise = np.median(np.abs(a - a2)[sel] / b[sel])
+    got = np.median(np.abs(a - b)[sel] / b[sel])
+    assert got <= max(2.0 * noise, block_tol), (got, noise)
+
+
+@need_ref_cuda
+@pytest.mark.parametrize("name", ["cornell", "mis"])
+def test_pt_agrees_with_the_reference_cuda_kernel(name):
+    sd = reference_scene(name)
+    d = desc(sd)
+    rc = O.RefCuda(); h = rc.scene(d)
+    W = H = 128
+    spp, depth = 64, 6
+    ref, ms = rc.render(h, rc.PT, d.cam, depth, depth, W, H, spp, 8)
+    rc.destroy(h)
+    sc = api.Scene(sd)
+    img, st = sc.render_pt(max_depth=depth, width=W, height=H, spp=spp, seed=11)
+    img2, _ = sc.render_pt(max_depth=depth, width=W, height=H, spp=spp, seed=12)
+    sc.close()
+    assert np.isfinite(ref).all() and ms > 0 and st["eye_samples"] == W * H * spp
+    _robust_agreement(img, img2, ref, 16, 0.02, 0.02)
+
+
+@need_ref_cuda
+@pytest.mark.parametrize("name", ["cornell", "mis"])
+def test_ppm_agrees_with_the_reference_cuda_kernels(name):
+    """Photon depth 3: deeper photon paths through the glossy walls have heavy-tailed weights (a single photon lights every hit
+    point within the radius up to the clamp), which makes film means of depth-8 renders differ by several per cent between
+    two seeds of EITHER implementation."""
+    sd = reference_scene(name)
+    d = desc(sd)
+    rc = O.RefCuda(); h = rc.scene(d)
+    W = H = 128
+    spl, e_depth, l_depth = 400000, 8, 3
+    # the shim forwards (eye_depth, light_depth) in main_cli.cpp:211's argument order, which run_cuda_ppm reads as
+    # (light_depth, eye_depth) (ppm_cu_helper.cpp:62): its FIRST depth is the photon depth
+    ref, ms = rc.render(h, rc.PPM, d.cam, l_depth, e_depth, W, H, 1, spl)
+    rc.destroy(h)
+    sc = api.Scene(sd)
+    img, st = sc.render_ppm(spl=spl, eye_depth=e_depth, light_depth=l_depth, width=W, height=H, seed=13)
+    img2, _ = sc.render_ppm(spl=spl, eye_depth=e_depth, light_depth=l_depth, width=W, height=H, seed=14)
+    sc.close()
+    assert np.isfinite(ref).all() and ms > 0
+    _robust_agreement(img, img2, ref, 16, 0.05, 0.05)
+
+
+def test_pt_sample_shards_sum_to_the_whole_film_and_passes_average():
+    sd = reference_scene("cornell")
+    sc = api.Scene(sd)
+    kw = dict(max_depth=5, width=64, height=48, spp=6, seed=3)
+    whole, st = sc.render_pt(film_mode=api.FILM_SUM, **kw)
+    parts = [sc.render_pt(film_mode=api.FILM_SUM, sample_offset=g, sample_stride=3, **kw)[0] for g in range(3)]
+    mean, _ = sc.render_pt(**kw)
+    assert np.allclose(sum(parts), whole, rtol=1e-5, atol=1e-6)
+    assert np.allclose(mean * 6, whole, rtol=1e-5, atol=1e-6)
+    prog, rms, _ = sc.render_progressive(3, width=64, height=48, spp=4, eye_depth=5, seed=20, integrator=api.INTEGRATOR_PT)
+    singles = [sc.render_pt(max_depth=5, width=64, height=48, spp=4, seed=20 + k)[0] for k in range(3)]
+    assert np.allclose(prog, sum(singles) / 3, rtol=1e-5, atol=1e-6) and rms[0] == 0 and rms[1] > 0
+    sc.close()
+
+
+def test_new_render_params_are_validated():
+    sd = reference_scene("mis")
+    sc = api.Scene(sd)
+    with pytest.raises(A.B2Error, match="does not shard"):
+        sc.render_ppm(width=16, height=16, sample_offset=1, sample_stride=2)
+    with pytest.raises(A.B2Error, match="unknown integrator"):
+        sc.render_bdpt(width=16, height=16, integrator=7)
+    with pytest.raises(A.B2Error, match="bdpt integrator only"):
+        sc.render_bdpt(width=16, height=16, integrator=api.INTEGRATOR_PT, strategies=api.STRATEGIES_NEE)
+    img, st = sc.render_ppm(width=16, height=16, spl=0)            # no photons: only the direct term
+    assert st["path_samples"] == 0 and np.isfinite(img).all()
+    sc.close()

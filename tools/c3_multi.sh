@@ -8,7 +8,7 @@ from path_tracing_b200 import gen
 print(gen.write_obj_scene("$D", n_tris=1 << 20))
 PY
 for spl in 1 8; do
-  timeout 900 path_tracing_b200/pt_cli --input $D/scene.txt --output gpurun_out/c3_n${N}_spl${spl}.ppm --gpus $N --spp $SPP --spl $spl --eye-depth 16 --light-depth 16 --width 1920 --height 1080 | grep -E "Finished|Triangle|Error|GPU"
+  timeout 900 path_tracing_b200/pt_cli --mode bdpt --input $D/scene.txt --output gpurun_out/c3_n${N}_spl${spl}.ppm --gpus $N --spp $SPP --spl $spl --eye-depth 16 --light-depth 16 --width 1920 --height 1080 | grep -E "Finished|Triangle|Error|GPU"
 done
 rm -f gpurun_out/c3_n${N}_spl*.ppm
 rm -rf $D
