@@ -1003,7 +1003,7 @@ void or_render(OrScene *s, const float *cam, int eye_depth, int light_depth, int
  * commented out); it is taken as zero-initialised here, i.e. opaque.
  * Draw schedule (shared with path_tracing_b200/csrc/b2_pt.cuh):
  *   eye / pt paths   kind 2: (pixel, sample) block 0 = jitter, block 1+k = u_rr,u1,u2 of the k-th bsdf_sample call
- *   pt NEE           kind 4: (pixel, sample) block 1+k lanes 0,1,2 = light choice, point on the light ball
+ *   pt NEE           kind 4: (pixel, sample) block 1+depth lanes 0,1,2 = light choice, point on the light ball
  *   photons          kind 5: (photon, 0) block 0 = emission, block 1+k = k-th bsdf_sample call
  * ===================================================================================== */
 static void philox_unit4(const uint32_t key[2], uint32_t id0, uint32_t id1, uint32_t block, uint32_t kind, float u[4]) {
@@ -1161,7 +1161,7 @@ void or_render_pt(OrScene *s, const float *cam, int max_depth, int W, int H, int
                     }
                     if (gathers_light(&hit.mtl) && num_lights > 0) {          /* :125-208 */
                         float un[4];
-                        philox_unit4(key, (uint32_t) idx, sg, 1u + bounce, 4u, un);
+                        philox_unit4(key, (uint32_t) idx, sg, 1u + (uint32_t) depth, 4u, un);   /* keyed by the vertex depth: NEE vertices are never delta bounces */
                         int l_idx = (int) (un[0] * num_lights); if (l_idx > num_lights - 1) l_idx = num_lights - 1;
                         const Light *light = &s->lights[l_idx];
                         if (light->is_parallel) {

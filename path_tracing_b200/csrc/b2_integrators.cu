@@ -3,10 +3,10 @@
 // point of include/b2pt.h (host film, device film, progressive, multi-GPU) serves them through B2RenderParams.integrator.
 //
 //   pt  (run_cuda_pt, src/pt_cu.cu): the reference runs one thread per PIXEL looping over spp and depth.  Here one wave =
-//       one bounce of every live path of a batch of up to 2^26 eye samples: k_pt_extend fuses the closest-hit traversal,
-//       the next-event shadow ray and the BSDF sample (a path has ONE shadow ray per vertex, so a separate connection
-//       stage would only add 80 B of HBM traffic per vertex), adds the bounce's radiance to the film with atomics and
-//       compacts the survivors into the next wave's queue with warp ballot + prefix.  Samples shard over GPUs as in BDPT.
+//       one bounce of every live path of a batch of up to 2^26 eye samples: k_pt_extend (closest hit, emission, BSDF
+//       sample; survivors compacted into the next wave's queue with warp ballot + prefix) and k_pt_nee (one shadow ray
+//       per vertex that takes direct light, read from a compact 80-byte record list), both adding to the film with
+//       atomics.  Samples shard over GPUs as in BDPT.
 //   ppm (run_cuda_ppm, src/ppm_cu.cu): eye pass -> hit points appended compactly; 63-bit cell keys radix-sorted (CUB) so
 //       the hit points of a grid cell are one contiguous run; an open-addressing table maps cell -> run (the reference
 //       threads a linked list per hash bucket through the unsorted hit points); one thread per photon walks the BVH and
@@ -21,31 +21,54 @@ namespace {
 
 constexpr int PT_THREADS = 128;
 
+// One bounce of every live path: closest hit, emission, BSDF sample; vertices that take direct light leave an 80-byte
+// record in the compact list k_pt_nee consumes.  (A first version fused the shadow ray into this kernel: 5 400 SASS
+// instructions, ncu: stall_no_instruction 4.6 - 8.2 per issue and 12 of 32 lanes active; profiles/r01_pt_summary.md.)
 template <bool PRIMARY, bool COUNT>
 __global__ void __launch_bounds__(PT_THREADS) k_pt_extend(RenderCtx c, int n_items, uint32_t pix0, int s0) {
     extern __shared__ uint2 s_stack[];
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
     TravCounters tc{ 0u, 0u };
-    uint32_t n_shadow = 0, n_path = 0, n_cap = 0;
+    uint32_t n_path = 0, n_cap = 0;
     PtState ps;
+    EyeVtx ev;
     int path = -1;
-    bool alive = false;
+    bool alive = false, want_nee = false;
     if (q < n_items) {
         if (PRIMARY) ps = pt_primary(c, pix0, s0, (uint32_t) q);
         else { path = c.live[q]; ps = pt_load(c, path); }
         const HitRec h = closest_hit_bvh<COUNT>(c.sc, ps.ro, ps.rd, s_stack + threadIdx.x, blockDim.x, &tc);
         float3 add;
-        alive = pt_bounce<COUNT>(c, ps, h, s_stack + threadIdx.x, blockDim.x, &tc, add, n_shadow, n_path, n_cap);
+        alive = pt_shade(c, ps, h, add, ev, want_nee, n_path, n_cap);
         if (add.x != 0.0f) atomicAdd(&c.film[3 * ps.pixel], add.x);
         if (add.y != 0.0f) atomicAdd(&c.film[3 * ps.pixel + 1], add.y);
         if (add.z != 0.0f) atomicAdd(&c.film[3 * ps.pixel + 2], add.z);
     }
+    const int cvi = warp_alloc(c.n_cv, want_nee);
+    if (want_nee) store_cv(c.cv, cvi, ev);
     if (PRIMARY) path = warp_alloc(c.n_paths, alive);                 // a path gets its state slot when it survives its first bounce
     const int li = warp_alloc(c.n_live_next, alive);
     if (alive) { pt_store(c, path, ps); c.live_next[li] = path; }
-    warp_count_add(&c.counters[B2_CNT_SHADOW], n_shadow);
     warp_count_add(&c.counters[B2_CNT_PATH_SAMPLES], n_path);
     warp_count_add(&c.counters[B2_CNT_DELTA_CAP], n_cap);
+    if (COUNT) { warp_count_add(&c.counters[B2_CNT_NODES], tc.nodes); warp_count_add(&c.counters[B2_CNT_TRIS], tc.tris); }
+}
+// Next-event estimation of the vertices of this wave: one shadow ray each (grid-stride over the device-side count).
+template <bool COUNT>
+__global__ void __launch_bounds__(PT_THREADS) k_pt_nee(RenderCtx c) {
+    extern __shared__ uint2 s_stack[];
+    const int n_cv = *c.n_cv;
+    TravCounters tc{ 0u, 0u };
+    uint32_t n_shadow = 0, n_path = 0;
+    for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < n_cv; q += gridDim.x * blockDim.x) {
+        const EyeVtx ev = load_cv(c.cv, q);
+        const float3 r = pt_nee<COUNT>(c, ev, s_stack + threadIdx.x, blockDim.x, &tc, n_shadow, n_path);
+        if (r.x != 0.0f) atomicAdd(&c.film[3 * ev.pixel], r.x);
+        if (r.y != 0.0f) atomicAdd(&c.film[3 * ev.pixel + 1], r.y);
+        if (r.z != 0.0f) atomicAdd(&c.film[3 * ev.pixel + 2], r.z);
+    }
+    warp_count_add(&c.counters[B2_CNT_SHADOW], n_shadow);
+    warp_count_add(&c.counters[B2_CNT_PATH_SAMPLES], n_path);
     if (COUNT) { warp_count_add(&c.counters[B2_CNT_NODES], tc.nodes); warp_count_add(&c.counters[B2_CNT_TRIS], tc.tris); }
 }
 
@@ -152,6 +175,8 @@ int set_limits(int bvh_depth) {
     B2_CUDA(cudaFuncSetAttribute(k_pt_extend<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
     B2_CUDA(cudaFuncSetAttribute(k_pt_extend<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
     B2_CUDA(cudaFuncSetAttribute(k_pt_extend<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
+    B2_CUDA(cudaFuncSetAttribute(k_pt_nee<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
+    B2_CUDA(cudaFuncSetAttribute(k_pt_nee<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
     B2_CUDA(cudaFuncSetAttribute(k_ppm_eye<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
     B2_CUDA(cudaFuncSetAttribute(k_ppm_eye<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
     B2_CUDA(cudaFuncSetAttribute(k_ppm_photons<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
@@ -179,7 +204,7 @@ void fill_stats(B2Stats *stats, const unsigned long long *h_cnt, unsigned long l
 int RenderWorkspace::ensure_pt(int max_paths, size_t film_floats) {
     const size_t mp = (size_t) std::max(max_paths, 1);
     B2_TRY(ray_o.ensure(mp)); B2_TRY(ray_d.ensure(mp)); B2_TRY(thr.ensure(mp)); B2_TRY(last_pos.ensure(mp));
-    B2_TRY(live_a.ensure(mp)); B2_TRY(live_b.ensure(mp));
+    B2_TRY(live_a.ensure(mp)); B2_TRY(live_b.ensure(mp)); B2_TRY(cv.ensure((size_t) B2_CV_F4 * mp));
     B2_TRY(film.ensure(film_floats));
     if (!ints.p) B2_TRY(ints.alloc(8));
     if (!counters.p) B2_TRY(counters.alloc(B2_CNT_N));
@@ -238,7 +263,7 @@ int b2_render_pt_impl(const DevScene &sc_in, int bvh_depth, RenderWorkspace &ws,
         B2_CUDA(cudaMemsetAsync(c.n_paths, 0, sizeof(int), st));
         bool primary = true;
         while (n_live > 0) {
-            B2_CUDA(cudaMemsetAsync(c.n_live_next, 0, sizeof(int), st));
+            B2_CUDA(cudaMemsetAsync(c.n_live_next, 0, 2 * sizeof(int), st));             // n_live_next, n_cv
             const unsigned gb = blocks_for(n_live, PT_THREADS);
             if (primary) {
                 const uint32_t pix0 = (uint32_t) (w0 % npix); const int s0 = (int) (w0 / npix);
@@ -249,7 +274,10 @@ int b2_render_pt_impl(const DevScene &sc_in, int bvh_depth, RenderWorkspace &ws,
                 else k_pt_extend<false, false><<<gb, PT_THREADS, sb, st>>>(c, n_live, 0u, 0);
             }
             B2_CUDA(cudaMemcpyAsync(ws.h_ints, c.n_live_next, sizeof(int), cudaMemcpyDeviceToHost, st));
-            n_launches++; n_waves++;
+            const unsigned gn = (unsigned) std::min<long long>(148ll * 16, gb);
+            if (count) k_pt_nee<true><<<gn, PT_THREADS, sb, st>>>(c);
+            else k_pt_nee<false><<<gn, PT_THREADS, sb, st>>>(c);
+            n_launches += 2; n_waves++;
             B2_CUDA(cudaStreamSynchronize(st));
             B2_CUDA(cudaGetLastError());
             closest_host += (unsigned long long) n_live;

@@ -18,7 +18,7 @@
 #pragma once
 #include "b2_bdpt.cuh"
 
-#define B2_RNG_PT_NEE 4u      // ctr = (pixel, sample, 1 + bounce, 4): light choice, two uniforms for the point on the ball
+#define B2_RNG_PT_NEE 4u      // ctr = (pixel, sample, 1 + depth of the vertex, 4): light choice, two uniforms for the point on the ball
 #define B2_RNG_PHOTON 5u      // ctr = (photon index, 0, block, 5): block 0 = emission, 1 + k = k-th bsdf_sample call
 #define B2_PPM_RADIUS 0.05f   // PPM_RADIUS, include/ppm_cu.cuh:5
 
@@ -74,13 +74,15 @@ B2_HD float3 pt_emission(const DevScene &sc, float3 pos, float3 illum, int depth
     return mk3(0, 0, 0);
 }
 
-// One bounce of a path (pt_cu.cu:48-249 for one value of `depth`).  Returns true when the path continues (ps = next ray);
-// `add` is what this bounce contributes to the pixel (already validated and clamped per contribution).
-template <bool COUNT>
-B2_HD bool pt_bounce(const RenderCtx &c, PtState &ps, HitRec h, uint2 *stack, int sstride, TravCounters *tc,
-                     float3 &add, uint32_t &n_shadow, uint32_t &n_path, uint32_t &n_cap) {
+// One bounce of a path (pt_cu.cu:48-249 for one value of `depth`) in two parts, so that the wavefront can run each as its
+// own kernel (b2_integrators.cu): pt_shade = light hit / emission, the BSDF sample and the next ray; pt_nee = the
+// next-event estimation of the same vertex from an eye-vertex record (EyeVtx with .path = sample index).
+//   pt_shade returns true when the path continues (ps = next ray); `add` = the emitted radiance this bounce adds to the
+//   pixel; want_nee: `ev` is a vertex that takes direct light (:126).
+B2_HD bool pt_shade(const RenderCtx &c, PtState &ps, HitRec h, float3 &add, EyeVtx &ev, bool &want_nee, uint32_t &n_path, uint32_t &n_cap) {
     const DevScene &sc = c.sc;
     add = mk3(0, 0, 0);
+    want_nee = false;
     if (h.prim == B2_PRIM_MISS) return false;
     const Surface s = surface_at(sc, ps.ro, ps.rd, h);
     const float3 wo = ps.rd * -1.0f;
@@ -91,52 +93,12 @@ B2_HD bool pt_bounce(const RenderCtx &c, PtState &ps, HitRec h, uint2 *stack, in
         }
         return false;
     }
-    const uint32_t bounce = (uint32_t) (ps.depth + ps.n_delta);
-    if (gathers_light(s.mtl) && sc.n_lights > 0) {                       // :125-208 next-event estimation, one light
-        float ul, u1, u2, unused;
-        rng_draw4(c.key, B2_RNG_PT_NEE, ps.pixel, ps.sidx, 1u + bounce, ul, u1, u2, unused);
-        int li = (int) (ul * (float) sc.n_lights);
-        if (li > sc.n_lights - 1) li = sc.n_lights - 1;
-        const float4 l0 = sc.lights[4 * li], l1 = sc.lights[4 * li + 1], l2 = sc.lights[4 * li + 2], l3 = sc.lights[4 * li + 3];
-        const float3 p1 = x3_add(s.pos, x3_muls(s.n, B2_EPSILON));
-        if (l2.w != 0.0f) {                                               // parallel light, :131-151
-            const float3 ldir = mk3(l3) * -1.0f;
-            const float cos_s = fmaxf(0.0f, dot3(s.n, ldir));
-            if (cos_s > 0.0f) {
-                const ShadowRay sr = make_shadow_ray(p1, s.pos + ldir * 1e4f);
-                n_shadow++;
-                if (!occluded_bvh<COUNT, true>(sc, sr.o, sr.d, sr.tmax, stack, sstride, tc)) {
-                    const float3 contrib = ps.thr * bsdf_evaluate(s.mtl, wo, ldir, s.n) * mk3(l2) * (cos_s * (float) sc.n_lights);
-                    if (valid_color(contrib)) { add = clamp_radiance(contrib, 15.0f); n_path++; }
-                }
-            }
-        } else {                                                          // point on the light ball, :152-206
-            const float z = 1.0f - 2.0f * u1, r = fast_sqrt(fmaxf(0.0f, 1.0f - z * z));
-            float sphi, cphi;
-            sincos_2pi(u2, sphi, cphi);
-            const float3 dl = mk3(r * cphi, r * sphi, z);
-            const float3 lpos = mk3(l0) + dl * l0.w;
-            float3 wi = lpos - s.pos;
-            const float dist2 = dot3(wi, wi);
-            wi = div_sqrt3(wi, dist2);
-            const float cos_s = fmaxf(0.0f, dot3(s.n, wi)), cos_l = fmaxf(0.0f, -dot3(dl, wi));
-            if (cos_s > 0.0f && cos_l > 0.0f && !(l1.w > 0.0f && -dot3(mk3(l3), wi) < l3.w)) {
-                const ShadowRay sr = make_shadow_ray(p1, x3_add(lpos, x3_muls(dl, B2_EPSILON)));
-                n_shadow++;
-                if (!occluded_bvh<COUNT, true>(sc, sr.o, sr.d, sr.tmax, stack, sstride, tc)) {
-                    const float area = 4.0f * B2_PI * l0.w * l0.w;
-                    const float pdf_l = fast_div(dist2, (float) sc.n_lights * area * fmaxf(cos_l, 1e-6f));
-                    const float pdf_b = bsdf_pdf(s.mtl, wo, wi, s.n);
-                    const float pl2 = pdf_l * pdf_l, pb2 = pdf_b * pdf_b;
-                    const float w = fast_div(pl2, fmaxf(pl2 + pb2, 1e-8f));      // power heuristic, :192-194
-                    const float3 contrib = ps.thr * bsdf_evaluate(s.mtl, wo, wi, s.n) * mk3(l2) * (fast_div(cos_s, pdf_l) * w);
-                    if (valid_color(contrib)) { add = clamp_radiance(contrib, 15.0f); n_path++; }
-                }
-            }
-        }
+    if (gathers_light(s.mtl) && sc.n_lights > 0) {
+        want_nee = true;
+        ev.pos = s.pos; ev.n = s.n; ev.wo = wo; ev.thr = ps.thr; ev.mtl = s.mtl; ev.depth = ps.depth; ev.pixel = ps.pixel; ev.path = (int) ps.sidx;
     }
     float u_rr, ua, ub;
-    rng_draw3(c.key, B2_RNG_EYE, ps.pixel, ps.sidx, bounce, u_rr, ua, ub);
+    rng_draw3(c.key, B2_RNG_EYE, ps.pixel, ps.sidx, (uint32_t) (ps.depth + ps.n_delta), u_rr, ua, ub);
     BsdfSample bs; bs.wi = mk3(0, 0, 0); bs.f = mk3(0, 0, 0); bs.pdf = 0.0f;
     bsdf_sample(s.mtl, wo, s.n, u_rr, ua, ub, ps.eta, bs);
     if (bs.pdf <= 0.0f) return false;                                     // :222 (and the pdf-0 delta case, see the header)
@@ -154,6 +116,62 @@ B2_HD bool pt_bounce(const RenderCtx &c, PtState &ps, HitRec h, uint2 *stack, in
     ps.rd = bs.wi; ps.ro = s.pos + s.n * B2_EPSILON;
     ps.last_delta = false;
     return ++ps.depth < c.eye_depth;
+}
+// Next-event estimation of one vertex (:125-208): one light chosen uniformly; a parallel light is a direction, any other a
+// point on its ball with the power heuristic against the BSDF density.  The draw is keyed by the vertex's depth: a
+// vertex that takes direct light is never a delta bounce, so (pixel, sample, depth) names it uniquely.
+template <bool COUNT>
+B2_HD float3 pt_nee(const RenderCtx &c, const EyeVtx &ev, uint2 *stack, int sstride, TravCounters *tc, uint32_t &n_shadow, uint32_t &n_path) {
+    const DevScene &sc = c.sc;
+    float ul, u1, u2, unused;
+    rng_draw4(c.key, B2_RNG_PT_NEE, ev.pixel, (uint32_t) ev.path, 1u + (uint32_t) ev.depth, ul, u1, u2, unused);
+    int li = (int) (ul * (float) sc.n_lights);
+    if (li > sc.n_lights - 1) li = sc.n_lights - 1;
+    const float4 l0 = sc.lights[4 * li], l1 = sc.lights[4 * li + 1], l2 = sc.lights[4 * li + 2], l3 = sc.lights[4 * li + 3];
+    const float3 p1 = x3_add(ev.pos, x3_muls(ev.n, B2_EPSILON));
+    if (l2.w != 0.0f) {                                                   // parallel light, :131-151
+        const float3 ldir = mk3(l3) * -1.0f;
+        const float cos_s = fmaxf(0.0f, dot3(ev.n, ldir));
+        if (!(cos_s > 0.0f)) return mk3(0, 0, 0);
+        const ShadowRay sr = make_shadow_ray(p1, ev.pos + ldir * 1e4f);
+        n_shadow++;
+        if (occluded_bvh<COUNT, true>(sc, sr.o, sr.d, sr.tmax, stack, sstride, tc)) return mk3(0, 0, 0);
+        const float3 contrib = ev.thr * bsdf_evaluate(ev.mtl, ev.wo, ldir, ev.n) * mk3(l2) * (cos_s * (float) sc.n_lights);
+        if (!valid_color(contrib)) return mk3(0, 0, 0);
+        n_path++;
+        return clamp_radiance(contrib, 15.0f);
+    }
+    const float z = 1.0f - 2.0f * u1, r = fast_sqrt(fmaxf(0.0f, 1.0f - z * z));      // point on the light ball, :152-206
+    float sphi, cphi;
+    sincos_2pi(u2, sphi, cphi);
+    const float3 dl = mk3(r * cphi, r * sphi, z);
+    const float3 lpos = mk3(l0) + dl * l0.w;
+    float3 wi = lpos - ev.pos;
+    const float dist2 = dot3(wi, wi);
+    wi = div_sqrt3(wi, dist2);
+    const float cos_s = fmaxf(0.0f, dot3(ev.n, wi)), cos_l = fmaxf(0.0f, -dot3(dl, wi));
+    if (!(cos_s > 0.0f && cos_l > 0.0f) || (l1.w > 0.0f && -dot3(mk3(l3), wi) < l3.w)) return mk3(0, 0, 0);
+    const ShadowRay sr = make_shadow_ray(p1, x3_add(lpos, x3_muls(dl, B2_EPSILON)));
+    n_shadow++;
+    if (occluded_bvh<COUNT, true>(sc, sr.o, sr.d, sr.tmax, stack, sstride, tc)) return mk3(0, 0, 0);
+    const float area = 4.0f * B2_PI * l0.w * l0.w;
+    const float pdf_l = fast_div(dist2, (float) sc.n_lights * area * fmaxf(cos_l, 1e-6f));
+    const float pdf_b = bsdf_pdf(ev.mtl, ev.wo, wi, ev.n);
+    const float pl2 = pdf_l * pdf_l, pb2 = pdf_b * pdf_b;
+    const float w = fast_div(pl2, fmaxf(pl2 + pb2, 1e-8f));              // power heuristic, :192-194
+    const float3 contrib = ev.thr * bsdf_evaluate(ev.mtl, ev.wo, wi, ev.n) * mk3(l2) * (fast_div(cos_s, pdf_l) * w);
+    if (!valid_color(contrib)) return mk3(0, 0, 0);
+    n_path++;
+    return clamp_radiance(contrib, 15.0f);
+}
+// Both parts for one path (the sequential host driver of tests/hostsim).
+template <bool COUNT>
+B2_HD bool pt_bounce(const RenderCtx &c, PtState &ps, HitRec h, uint2 *stack, int sstride, TravCounters *tc,
+                     float3 &add, uint32_t &n_shadow, uint32_t &n_path, uint32_t &n_cap) {
+    EyeVtx ev; bool want_nee;
+    const bool alive = pt_shade(c, ps, h, add, ev, want_nee, n_path, n_cap);
+    if (want_nee) add = add + pt_nee<COUNT>(c, ev, stack, sstride, tc, n_shadow, n_path);
+    return alive;
 }
 
 // ---- photon mapping ----
