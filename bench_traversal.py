@@ -43,7 +43,8 @@ def main():
     ids = torch.empty(n, dtype=torch.int32, device=dev); t = torch.empty(n, dtype=torch.float32, device=dev)
     stream = torch.cuda.current_stream().cuda_stream
     out = {"metric": "traversal_mrays_per_s", "unit": "Mrays/s", "config": {"workload": f"C5: {n} incoherent random rays vs {info['n_tris']}-triangle soup BVH"},
-           "bvh": {k: info[k] for k in ("n_tris", "n_nodes", "node_bytes", "tri_bytes", "depth", "build_ms")}, "scene_gen_s": t_gen, "scene_create_plus_build_wall_s": t_build_wall}
+           "bvh": dict({k: info[k] for k in ("n_tris", "n_nodes", "node_bytes", "tri_bytes", "depth", "build_ms", "build_passes")},
+                   builder="lbvh" if os.environ.get("B2_BVH_BUILDER", "0") == "1" else "ploc", ploc_radius=int(os.environ.get("B2_PLOC_RADIUS", "0")) or 2), "scene_gen_s": t_gen, "scene_create_plus_build_wall_s": t_build_wall}
     hbm, src = peaks()
     for name, mode, second in (("closest", api.CLOSEST, d), ("any", api.ANY, p2)):
         sc.intersect_device(org.data_ptr(), second.data_ptr(), n, mode | api.COUNT_VISITS, ids.data_ptr(), t.data_ptr(), stream)

@@ -50,9 +50,13 @@ typedef struct B2Light { float pos[3], dir[3], illum[3]; float cutoff; int32_t i
 /* Camera, include/object.h:104-110 (fov in degrees; run_cpu_bdpt uses camera.fov, cpu_bdpt.cpp:191) */
 typedef struct B2Camera { float eye[3], look_at[3], view_up[3]; float fov; } B2Camera;
 
+#define B2_BUILDER_PLOC 0  /* parallel locally-ordered clustering over the Morton order (default) */
+#define B2_BUILDER_LBVH 1  /* Karras radix tree over the Morton codes (the A/B baseline) */
 typedef struct B2BvhParams {
     int32_t max_leaf_tris;  /* 1..3 triangles per leaf child (0 = default 3) */
     float   pad_rel;        /* relative padding of triangle boxes (0 = default 2^-18 of the coordinate magnitude) */
+    int32_t builder;        /* B2_BUILDER_* */
+    int32_t ploc_radius;    /* PLOC search radius along the Morton order (0 = default 2) */
 } B2BvhParams;
 
 typedef struct B2BvhInfo {
@@ -60,6 +64,8 @@ typedef struct B2BvhInfo {
     int32_t  depth;
     float    build_ms;      /* device time of the last build (CUDA events) */
     float    sah_cost;      /* SAH cost of the wide tree (root area normalised) */
+    int32_t  build_passes;  /* PLOC clustering passes of the last build */
+    int32_t  reserved;
 } B2BvhInfo;
 
 #define B2_FILM_MEAN 0  /* film = sum / spp  (what run_cpu_bdpt writes, cpu_bdpt.cpp:479) */

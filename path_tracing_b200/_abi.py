@@ -22,12 +22,12 @@ assert Material.itemsize == 24 and Tri.itemsize == 48 and Sphere.itemsize == 28 
 
 
 class BvhParams(C.Structure):
-    _fields_ = [("max_leaf_tris", C.c_int32), ("pad_rel", C.c_float)]
+    _fields_ = [("max_leaf_tris", C.c_int32), ("pad_rel", C.c_float), ("builder", C.c_int32), ("ploc_radius", C.c_int32)]
 
 
 class BvhInfo(C.Structure):
     _fields_ = [("n_tris", C.c_uint64), ("n_nodes", C.c_uint64), ("node_bytes", C.c_uint64), ("tri_bytes", C.c_uint64),
-                ("depth", C.c_int32), ("build_ms", C.c_float), ("sah_cost", C.c_float)]
+                ("depth", C.c_int32), ("build_ms", C.c_float), ("sah_cost", C.c_float), ("build_passes", C.c_int32), ("reserved", C.c_int32)]
 
 
 class RenderParams(C.Structure):

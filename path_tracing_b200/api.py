@@ -8,6 +8,7 @@
 Everything computes in libb2pt.so (hand-written CUDA for sm_100a); there is no CPU fallback here.
 """
 import ctypes as C
+import os
 import numpy as np
 from . import _abi as A
 from .scene import SceneData
@@ -32,7 +33,11 @@ def _f32(a, shape=None):
 class Scene:
     """Device-resident scene + wide BVH (opaque B2Scene handle)."""
 
-    def __init__(self, data: SceneData, device=0, max_leaf_tris=0, pad_rel=0.0, build=True):
+    def __init__(self, data: SceneData, device=0, max_leaf_tris=0, pad_rel=0.0, build=True, builder=None, ploc_radius=0):
+        if builder is None:                                    # A/B runs of the tools: B2_BVH_BUILDER=1 selects the radix-tree builder
+            builder = int(os.environ.get("B2_BVH_BUILDER", "0"))
+        if not ploc_radius:
+            ploc_radius = int(os.environ.get("B2_PLOC_RADIUS", "0"))
         self.data = data
         self._h = C.c_void_p()
         L = A.lib()
@@ -40,10 +45,11 @@ class Scene:
                                   A.ptr(data.materials), len(data.materials), A.ptr(data.lights), len(data.lights),
                                   int(device), C.byref(self._h)))
         if build:
-            self.build_bvh(max_leaf_tris, pad_rel)
+            self.build_bvh(max_leaf_tris, pad_rel, builder, ploc_radius)
 
-    def build_bvh(self, max_leaf_tris=0, pad_rel=0.0):
-        p = A.BvhParams(int(max_leaf_tris), float(pad_rel))
+    def build_bvh(self, max_leaf_tris=0, pad_rel=0.0, builder=0, ploc_radius=0):
+        """builder 0 = PLOC (default), 1 = LBVH (B2_BUILDER_*)."""
+        p = A.BvhParams(int(max_leaf_tris), float(pad_rel), int(builder), int(ploc_radius))
         A.check(A.lib().b2_scene_build_bvh(self._h, C.byref(p)))
 
     def bvh_info(self):

@@ -111,7 +111,10 @@ int b2_scene_build_bvh(B2Scene *s, const B2BvhParams *params) {
     const HostScene &hs = s->hs;
     const float ext = std::max({ hs.scene_max.x - hs.scene_min.x, hs.scene_max.y - hs.scene_min.y, hs.scene_max.z - hs.scene_min.z });
     const float pad = pad_rel * std::max(hs.max_abs, ext) + 1e-30f;
-    B2_TRY(b2_build_bvh_device(s->d_in.p, (int) hs.tris.size(), pad, max_leaf, s->stream, s->bvh));
+    const int builder = params ? params->builder : B2_BUILDER_PLOC;
+    if (builder != B2_BUILDER_PLOC && builder != B2_BUILDER_LBVH) { b2_set_error("unknown BVH builder %d", builder); return B2_ERR_INVALID; }
+    const int radius = (params && params->ploc_radius > 0) ? std::min(params->ploc_radius, 64) : 2;   // measured on C3 / C5: radius 2 > 3 > 4 > 8 (profiles/r01_ploc_summary.md)
+    B2_TRY(b2_build_bvh_device(s->d_in.p, (int) hs.tris.size(), pad, max_leaf, builder, radius, s->stream, s->bvh));
     s->built = true; s->max_leaf = max_leaf;
     return B2_OK;
 }
@@ -122,7 +125,7 @@ int b2_scene_bvh_info(const B2Scene *s, B2BvhInfo *info) {
     memset(info, 0, sizeof(*info));
     info->n_tris = (uint64_t) s->bvh.n_tris; info->n_nodes = (uint64_t) s->bvh.n_nodes;
     info->node_bytes = (uint64_t) s->bvh.n_nodes * sizeof(uint4) * B2_NODE_UINT4; info->tri_bytes = (uint64_t) s->bvh.n_tris * 48u;
-    info->depth = s->bvh.depth; info->build_ms = s->bvh.build_ms; info->sah_cost = 0.0f;
+    info->depth = s->bvh.depth; info->build_ms = s->bvh.build_ms; info->sah_cost = 0.0f; info->build_passes = s->bvh.build_passes;
     return B2_OK;
 }
 

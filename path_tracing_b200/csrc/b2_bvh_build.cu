@@ -43,6 +43,33 @@ __global__ void k_refit(BinTree bt, const float *__restrict__ tlo, const float *
 __global__ void k_single_leaf_box(BinTree bt, const float *tlo, const float *thi) {
     for (int a = 0; a < 3; ++a) { bt.lo[a] = tlo[a]; bt.hi[a] = thi[a]; }
 }
+// ---- PLOC passes (bodies in b2_bvh_build.cuh) ----
+__global__ void k_ploc_leaves(BinTree bt, const float *__restrict__ tlo, const float *__restrict__ thi, int *cid) {
+    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < bt.n) { ploc_leaf(bt, tlo, thi, j); cid[j] = (bt.n - 1) + j; }
+}
+__global__ void k_ploc_nearest(BinTree bt, const int *__restrict__ cid, int m, int radius, int *nn) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < m) nn[i] = ploc_nearest(bt, cid, m, i, radius);
+}
+// flags: low word = 1 for a left partner (one new node), high word = 1 for a cluster that survives the pass
+__global__ void k_ploc_flags(const int *__restrict__ nn, int m, unsigned long long *flags) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < m) { const int r = ploc_role(nn, i); flags[i] = (r == 1 ? 1ull : 0ull) | (r != 2 ? 1ull << 32 : 0ull); }
+}
+__global__ void k_ploc_apply(BinTree bt, const int *__restrict__ cid, const int *__restrict__ nn, const unsigned long long *__restrict__ scan, int m,
+                             int created, int *cid_out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    const int r = ploc_role(nn, i);
+    if (r == 2) return;
+    const int pos = (int) (scan[i] >> 32);
+    if (r == 1) {
+        const int node = bt.n - 2 - (created + (int) (uint32_t) scan[i]);      // the last merge of the build creates node 0, the root
+        ploc_merge(bt, cid[i], cid[nn[i]], node);
+        cid_out[pos] = node;
+    } else cid_out[pos] = cid[i];
+}
 __global__ void k_collapse_pick(BinTree bt, const CollapseItem *__restrict__ items, int m, int max_leaf, CollapseOut *outs, int *nint, int *ntri) {
     int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k < m) collapse_pick(bt, items[k].bin_node, max_leaf, outs[k], nint[k], ntri[k]);
@@ -62,7 +89,7 @@ __global__ void k_pack_tris(const BuildTri *__restrict__ in, const int *__restri
 
 }  // namespace
 
-int b2_build_bvh_device(const BuildTri *d_in, int n, float pad, int max_leaf, cudaStream_t st, DeviceBvh &out) {
+int b2_build_bvh_device(const BuildTri *d_in, int n, float pad, int max_leaf, int builder, int ploc_radius, cudaStream_t st, DeviceBvh &out) {
     out.release();
     if (n <= 0) return B2_OK;
     cudaEvent_t ev0, ev1;
@@ -72,7 +99,8 @@ int b2_build_bvh_device(const BuildTri *d_in, int n, float pad, int max_leaf, cu
     DevBuf<float> tlo, thi, lo, hi;
     DevBuf<uint32_t> cb, visit;
     DevBuf<uint64_t> keys, skeys;
-    DevBuf<int> vals, sorted, left, right, parent, first, last, leaf_parent, perm, nint, ntri, ioff, toff;
+    DevBuf<int> vals, sorted, left, right, parent, first, last, leaf_parent, perm, nint, ntri, ioff, toff, count, cid_a, cid_b, nn;
+    DevBuf<unsigned long long> pflags, pscan;
     DevBuf<unsigned char> tmp;
     DevBuf<CollapseItem> items_a, items_b;
     DevBuf<CollapseOut> outs;
@@ -97,16 +125,46 @@ int b2_build_bvh_device(const BuildTri *d_in, int n, float pad, int max_leaf, cu
     B2_CUDA(cub::DeviceRadixSort::SortPairs(tmp.p, tmp_bytes, keys.p, skeys.p, vals.p, sorted.p, n, 0, 63, st));
     keys.release(); vals.release();
 
-    B2_TRY(left.alloc(n)); B2_TRY(right.alloc(n)); B2_TRY(parent.alloc(n)); B2_TRY(first.alloc(n)); B2_TRY(last.alloc(n)); B2_TRY(leaf_parent.alloc(n));
-    B2_TRY(lo.alloc(6 * (size_t) n)); B2_TRY(hi.alloc(6 * (size_t) n)); B2_TRY(visit.alloc(n));
-    B2_CUDA(cudaMemsetAsync(visit.p, 0, sizeof(uint32_t) * n, st));
-    B2_CUDA(cudaMemsetAsync(leaf_parent.p, 0xff, sizeof(int) * n, st));
-    BinTree bt{ n, skeys.p, sorted.p, left.p, right.p, parent.p, first.p, last.p, leaf_parent.p, lo.p, hi.p, visit.p };
-    if (n >= 2) {
+    B2_TRY(left.alloc(n)); B2_TRY(right.alloc(n));
+    B2_TRY(lo.alloc(6 * (size_t) n)); B2_TRY(hi.alloc(6 * (size_t) n));
+    int ploc_passes = 0;
+    BinTree bt{ n, skeys.p, sorted.p, left.p, right.p, nullptr, nullptr, nullptr, nullptr, lo.p, hi.p, nullptr, nullptr };
+    if (n < 2) {
+        k_single_leaf_box<<<1, 1, 0, st>>>(bt, tlo.p, thi.p);
+    } else if (builder == B2_BUILDER_LBVH) {
+        B2_TRY(parent.alloc(n)); B2_TRY(first.alloc(n)); B2_TRY(last.alloc(n)); B2_TRY(leaf_parent.alloc(n)); B2_TRY(visit.alloc(n));
+        B2_CUDA(cudaMemsetAsync(visit.p, 0, sizeof(uint32_t) * n, st));
+        B2_CUDA(cudaMemsetAsync(leaf_parent.p, 0xff, sizeof(int) * n, st));
+        bt.parent = parent.p; bt.first = first.p; bt.last = last.p; bt.leaf_parent = leaf_parent.p; bt.visit = visit.p;
         k_karras<<<blocks_for(n - 1, T), T, 0, st>>>(bt);
         k_refit<<<blocks_for(n, T), T, 0, st>>>(bt, tlo.p, thi.p);
     } else {
-        k_single_leaf_box<<<1, 1, 0, st>>>(bt, tlo.p, thi.p);
+        // PLOC: nearest neighbour within `radius` positions of the Morton order, mutual pairs merge, survivors are compacted in
+        // order (one 64-bit exclusive scan gives both the new node index and the new position); one host read per pass
+        B2_TRY(count.alloc(2 * (size_t) n)); B2_TRY(cid_a.alloc(n)); B2_TRY(cid_b.alloc(n)); B2_TRY(nn.alloc(n)); B2_TRY(pflags.alloc(n)); B2_TRY(pscan.alloc(n));
+        bt.count = count.p;
+        size_t pscan_bytes = 0;
+        B2_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, pscan_bytes, pflags.p, pscan.p, n, st));
+        B2_TRY(tmp.ensure(pscan_bytes));
+        k_ploc_leaves<<<blocks_for(n, T), T, 0, st>>>(bt, tlo.p, thi.p, cid_a.p);
+        int *cur_c = cid_a.p, *nxt_c = cid_b.p;
+        int m = n, created = 0;
+        while (m > 1) {
+            k_ploc_nearest<<<blocks_for(m, 128), 128, 0, st>>>(bt, cur_c, m, ploc_radius, nn.p);
+            k_ploc_flags<<<blocks_for(m, T), T, 0, st>>>(nn.p, m, pflags.p);
+            B2_CUDA(cub::DeviceScan::ExclusiveSum(tmp.p, pscan_bytes, pflags.p, pscan.p, m, st));
+            unsigned long long tail[2];
+            B2_CUDA(cudaMemcpyAsync(&tail[0], pflags.p + (m - 1), sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+            B2_CUDA(cudaMemcpyAsync(&tail[1], pscan.p + (m - 1), sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+            k_ploc_apply<<<blocks_for(m, T), T, 0, st>>>(bt, cur_c, nn.p, pscan.p, m, created, nxt_c);
+            B2_CUDA(cudaStreamSynchronize(st));
+            const unsigned long long tot = tail[0] + tail[1];
+            const int merged = (int) (uint32_t) tot, alive = (int) (tot >> 32);
+            if (merged <= 0 || alive != m - merged) { b2_set_error("PLOC pass made no progress (internal error: m %d merged %d alive %d)", m, merged, alive); return B2_ERR_STATE; }
+            created += merged; m = alive;
+            int *t = cur_c; cur_c = nxt_c; nxt_c = t;
+            ploc_passes++;
+        }
     }
     B2_CUDA(cudaGetLastError());
 
@@ -157,6 +215,6 @@ int b2_build_bvh_device(const BuildTri *d_in, int n, float pad, int max_leaf, cu
     float ms = 0.f;
     cudaEventElapsedTime(&ms, ev0, ev1);
     cudaEventDestroy(ev0); cudaEventDestroy(ev1);
-    out.n_tris = n; out.n_nodes = (int) n_nodes; out.depth = depth; out.build_ms = ms;
+    out.n_tris = n; out.n_nodes = (int) n_nodes; out.depth = depth; out.build_ms = ms; out.build_passes = ploc_passes;
     return B2_OK;
 }

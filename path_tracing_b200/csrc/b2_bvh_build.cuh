@@ -1,9 +1,14 @@
 // b2_bvh_build.cuh -- per-item bodies of the GPU BVH build (the __global__ wrappers and the level loop
 // live in b2_bvh_build.cu; tests/hostsim runs the same bodies sequentially on the host).
 //
-// Pipeline: padded triangle boxes + centroid bounds -> 63-bit Morton keys -> radix sort ->
-// Karras (HPG 2012) binary radix tree -> bottom-up refit -> level-synchronous collapse into 8-wide nodes
-// with 8-bit quantised child boxes (b2_scene.cuh) and leaf-contiguous triangle reordering.
+// Pipeline: padded triangle boxes + centroid bounds -> 63-bit Morton keys -> radix sort -> binary tree ->
+// level-synchronous collapse into 8-wide nodes with 8-bit quantised child boxes (b2_scene.cuh) and leaf-contiguous
+// triangle reordering.  Two binary-tree builders over the Morton order:
+//   PLOC (default)  parallel locally-ordered clustering (Meister & Bittner 2018): every cluster looks `radius` positions
+//                   left and right along the Morton curve for the neighbour whose union has the smallest surface area;
+//                   mutual nearest neighbours merge; repeat until one cluster is left.  Agglomerative, area-driven: the
+//                   tree quality of a surface-area-heuristic build at a few dozen passes over a shrinking array.
+//   LBVH            Karras (HPG 2012) binary radix tree + bottom-up refit: splits by Morton bits only (A/B baseline).
 // Every step is deterministic (no atomics decide an ordering), so all GPUs build identical trees.
 #pragma once
 #include "b2_scene.cuh"
@@ -18,6 +23,8 @@ struct BinTree {             // binary radix tree over n sorted triangles: inter
     int *leaf_parent;
     float *lo, *hi;          // 3 floats per node, 2n-1 nodes
     uint32_t *visit;         // refit arrival counters (internal nodes)
+    int *count;              // PLOC: leaves under each node (2n-1 entries; a subtree is NOT a contiguous range of sorted
+                             // leaves there); nullptr for the radix tree, whose nodes cover [first, last]
 };
 
 B2_HD void tri_bounds(const BuildTri &t, float pad, float lo[3], float hi[3]) {
@@ -105,8 +112,63 @@ B2_HD void refit_from_leaf(const BinTree &bt, const float *tri_lo, const float *
     }
 }
 
-B2_HD int bin_count(const BinTree &bt, int node) { return node >= bt.n - 1 ? 1 : bt.last[node] - bt.first[node] + 1; }
-B2_HD int bin_first(const BinTree &bt, int node) { return node >= bt.n - 1 ? node - (bt.n - 1) : bt.first[node]; }
+B2_HD int bin_count(const BinTree &bt, int node) { return node >= bt.n - 1 ? 1 : (bt.count ? bt.count[node] : bt.last[node] - bt.first[node] + 1); }
+// sorted positions of the (at most 3) leaves under a node that becomes a leaf child of a wide node
+B2_HD int bin_leaves(const BinTree &bt, int node, int out[3]) {
+    if (!bt.count) {
+        const int f = node >= bt.n - 1 ? node - (bt.n - 1) : bt.first[node], c = bin_count(bt, node);
+        for (int j = 0; j < c && j < 3; ++j) out[j] = f + j;
+        return c;
+    }
+    int stack[4], sp = 0, k = 0;
+    stack[sp++] = node;
+    while (sp > 0) {
+        const int x = stack[--sp];
+        if (x >= bt.n - 1) { if (k < 3) out[k] = x - (bt.n - 1); k++; }
+        else { stack[sp++] = bt.right[x]; stack[sp++] = bt.left[x]; }
+    }
+    return k;
+}
+
+// ---- PLOC ----
+// Clusters live in an array `cid` (node ids) in Morton order.  Search key = (surface area of the union box, i ^ j): the
+// second component is symmetric in (i, j) and unique among the candidates of one cluster, so the pair that minimises the
+// key globally is always mutual (the loop makes progress) and equal boxes pair up as (0,1), (2,3), ... instead of chaining.
+B2_HD float ploc_union_area(const BinTree &bt, int a, int b) {
+    const float dx = fmaxf(bt.hi[3 * a], bt.hi[3 * b]) - fminf(bt.lo[3 * a], bt.lo[3 * b]);
+    const float dy = fmaxf(bt.hi[3 * a + 1], bt.hi[3 * b + 1]) - fminf(bt.lo[3 * a + 1], bt.lo[3 * b + 1]);
+    const float dz = fmaxf(bt.hi[3 * a + 2], bt.hi[3 * b + 2]) - fminf(bt.lo[3 * a + 2], bt.lo[3 * b + 2]);
+    return dx * dy + dy * dz + dz * dx;
+}
+B2_HD int ploc_nearest(const BinTree &bt, const int *cid, int m, int i, int radius) {
+    const int a = cid[i];
+    const float alx = bt.lo[3 * a], aly = bt.lo[3 * a + 1], alz = bt.lo[3 * a + 2], ahx = bt.hi[3 * a], ahy = bt.hi[3 * a + 1], ahz = bt.hi[3 * a + 2];
+    int best = -1; float best_area = 3.0e38f; uint32_t best_x = 0xffffffffu;
+    const int j0 = i - radius > 0 ? i - radius : 0, j1 = i + radius < m - 1 ? i + radius : m - 1;
+    for (int j = j0; j <= j1; ++j) {
+        if (j == i) continue;
+        const int b = cid[j];
+        const float dx = fmaxf(ahx, bt.hi[3 * b]) - fminf(alx, bt.lo[3 * b]);
+        const float dy = fmaxf(ahy, bt.hi[3 * b + 1]) - fminf(aly, bt.lo[3 * b + 1]);
+        const float dz = fmaxf(ahz, bt.hi[3 * b + 2]) - fminf(alz, bt.lo[3 * b + 2]);
+        const float area = dx * dy + dy * dz + dz * dx;
+        const uint32_t x = (uint32_t) i ^ (uint32_t) j;
+        if (area < best_area || (area == best_area && x < best_x)) { best_area = area; best_x = x; best = j; }
+    }
+    return best;
+}
+// 1 = cluster i is the left partner of a merging pair, 2 = the right partner (it disappears), 0 = it stays
+B2_HD int ploc_role(const int *nn, int i) { const int j = nn[i]; return (j >= 0 && nn[j] == i) ? (i < j ? 1 : 2) : 0; }
+B2_HD void ploc_merge(const BinTree &bt, int l, int r, int node) {
+    bt.left[node] = l; bt.right[node] = r;
+    for (int a = 0; a < 3; ++a) { bt.lo[3 * node + a] = fminf(bt.lo[3 * l + a], bt.lo[3 * r + a]); bt.hi[3 * node + a] = fmaxf(bt.hi[3 * l + a], bt.hi[3 * r + a]); }
+    bt.count[node] = bt.count[l] + bt.count[r];
+}
+B2_HD void ploc_leaf(const BinTree &bt, const float *tri_lo, const float *tri_hi, int j) {
+    const int src = bt.sorted[j], node = (bt.n - 1) + j;
+    for (int a = 0; a < 3; ++a) { bt.lo[3 * node + a] = tri_lo[3 * src + a]; bt.hi[3 * node + a] = tri_hi[3 * src + a]; }
+    bt.count[node] = 1;
+}
 B2_HD float bin_area(const BinTree &bt, int node) {
     float dx = bt.hi[3 * node] - bt.lo[3 * node], dy = bt.hi[3 * node + 1] - bt.lo[3 * node + 1], dz = bt.hi[3 * node + 2] - bt.lo[3 * node + 2];
     return dx * dy + dy * dz + dz * dx;
@@ -218,8 +280,9 @@ B2_HD void collapse_emit(const BinTree &bt, int X, const CollapseOut &in, int ma
             n_int++;
         } else {
             meta[s] = ((uint32_t) c << 5) | (uint32_t) tri_off;
-            int f = bin_first(bt, nd);
-            for (int j = 0; j < c; ++j) perm[tri_base + tri_off + j] = f + j;
+            int lv[3];
+            bin_leaves(bt, nd, lv);
+            for (int j = 0; j < c; ++j) perm[tri_base + tri_off + j] = lv[j];
             tri_off += c;
         }
     }

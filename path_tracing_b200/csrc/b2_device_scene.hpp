@@ -10,7 +10,8 @@ struct DeviceBvh {
     DevBuf<int32_t> tri_obj;
     int n_tris = 0, n_nodes = 0, depth = 0;
     float build_ms = 0.f;
-    void release() { nodes.release(); tri.release(); tri_obj.release(); n_tris = n_nodes = depth = 0; build_ms = 0.f; }
+    int build_passes = 0;          // PLOC passes of the last build
+    void release() { nodes.release(); tri.release(); tri_obj.release(); n_tris = n_nodes = depth = 0; build_ms = 0.f; build_passes = 0; }
 };
 
-int b2_build_bvh_device(const BuildTri *d_in, int n, float pad, int max_leaf, cudaStream_t st, DeviceBvh &out);
+int b2_build_bvh_device(const BuildTri *d_in, int n, float pad, int max_leaf, int builder, int ploc_radius, cudaStream_t st, DeviceBvh &out);

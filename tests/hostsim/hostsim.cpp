@@ -28,7 +28,11 @@ void *hs_scene_create(const B2Tri *tris, size_t n_tris, const B2Sphere *sph, siz
     HsScene *s = new HsScene;
     const char *err = nullptr;
     if (!flatten_scene(tris, n_tris, sph, n_sph, mats, n_mats, lights, n_lights, s->hs, &err)) { fprintf(stderr, "hostsim: %s\n", err); delete s; return nullptr; }
-    host_build_bvh(s->hs, max_leaf > 0 ? max_leaf : 3, pad_rel > 0 ? pad_rel : 3.8146973e-6f, s->bvh);
+    // max_leaf: 1..3; + 16 selects the radix-tree builder (B2_BUILDER_LBVH) instead of PLOC
+    const int builder = (max_leaf & 16) ? B2_BUILDER_LBVH : B2_BUILDER_PLOC;
+    const int radius = (max_leaf >> 8) & 0xff;                     // bits 8..15: PLOC search radius (0 = default 2)
+    max_leaf &= 15;
+    host_build_bvh(s->hs, max_leaf > 0 ? max_leaf : 3, pad_rel > 0 ? pad_rel : 3.8146973e-6f, s->bvh, builder, radius > 0 ? radius : 2);
     hs_make_view(s);
     return s;
 }

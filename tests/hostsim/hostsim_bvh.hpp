@@ -15,7 +15,7 @@ struct HostBvh {
     int depth = 0;
 };
 
-inline void host_build_bvh(const HostScene &hs, int max_leaf, float pad_rel, HostBvh &out) {
+inline void host_build_bvh(const HostScene &hs, int max_leaf, float pad_rel, HostBvh &out, int builder = B2_BUILDER_PLOC, int ploc_radius = 2) {
     const int n = (int) hs.tris.size();
     out.nodes.clear(); out.tri.assign(3 * (size_t) n, make_float4(0, 0, 0, 0)); out.tri_obj.assign(n, 0); out.depth = 0;
     if (n == 0) return;
@@ -35,15 +35,35 @@ inline void host_build_bvh(const HostScene &hs, int max_leaf, float pad_rel, Hos
     std::stable_sort(sorted.begin(), sorted.end(), [&](int a, int b) { return keys[a] < keys[b]; });
     std::vector<uint64_t> skeys(n);
     for (int i = 0; i < n; ++i) skeys[i] = keys[sorted[i]];
-    std::vector<int> left(n), right(n), parent(n), first(n), last(n), leaf_parent(n, -1);
+    std::vector<int> left(n), right(n), parent(n), first(n), last(n), leaf_parent(n, -1), count(2 * (size_t) n, 0);
     std::vector<float> lo(3 * (2 * (size_t) n)), hi(3 * (2 * (size_t) n));
     std::vector<uint32_t> visit(n, 0);
-    BinTree bt{ n, skeys.data(), sorted.data(), left.data(), right.data(), parent.data(), first.data(), last.data(), leaf_parent.data(), lo.data(), hi.data(), visit.data() };
-    if (n >= 2) {
+    BinTree bt{ n, skeys.data(), sorted.data(), left.data(), right.data(), parent.data(), first.data(), last.data(), leaf_parent.data(), lo.data(), hi.data(), visit.data(), nullptr };
+    if (n < 2) {
+        for (int a = 0; a < 3; ++a) { lo[a] = tlo[a]; hi[a] = thi[a]; }   // node id (n-1)+0 = 0
+    } else if (builder == B2_BUILDER_LBVH) {
         for (int i = 0; i < n - 1; ++i) karras_node(bt, i);
         for (int j = 0; j < n; ++j) refit_from_leaf(bt, tlo.data(), thi.data(), j);
-    } else {
-        for (int a = 0; a < 3; ++a) { lo[a] = tlo[a]; hi[a] = thi[a]; }   // node id (n-1)+0 = 0
+    } else {                                                                // the pass loop of b2_bvh_build.cu, one "thread" at a time
+        bt.count = count.data();
+        std::vector<int> cid(n), nxt, nn;
+        for (int j = 0; j < n; ++j) { ploc_leaf(bt, tlo.data(), thi.data(), j); cid[j] = (n - 1) + j; }
+        int created = 0;
+        while (cid.size() > 1) {
+            const int m = (int) cid.size();
+            nn.assign(m, -1);
+            for (int i = 0; i < m; ++i) nn[i] = ploc_nearest(bt, cid.data(), m, i, ploc_radius);
+            nxt.clear();
+            int merged = 0;
+            for (int i = 0; i < m; ++i) {
+                const int r = ploc_role(nn.data(), i);
+                if (r == 2) continue;
+                if (r == 1) { const int node = n - 2 - (created + merged); ploc_merge(bt, cid[i], cid[nn[i]], node); nxt.push_back(node); merged++; }
+                else nxt.push_back(cid[i]);
+            }
+            created += merged;
+            cid.swap(nxt);
+        }
     }
     std::vector<int> perm(n, -1);
     std::vector<CollapseItem> items(1), next;

@@ -25,7 +25,7 @@ def test_library_exports_every_declared_symbol():
 
 
 def test_pod_layouts_match_header():
-    assert C.sizeof(A.RenderParams) == 80 and C.sizeof(A.BvhParams) == 8 and C.sizeof(A.BvhInfo) == 48
+    assert C.sizeof(A.RenderParams) == 80 and C.sizeof(A.BvhParams) == 16 and C.sizeof(A.BvhInfo) == 56
     assert C.sizeof(A.Stats) == 12 * 8 + 7 * 4 + 4    # 7 floats, padded to 8-byte alignment
     assert C.sizeof(A.ParsedScene) == 4 * 8 + 4 * 8 + 40 + 8
 
