@@ -116,6 +116,63 @@ B2_HD HitRec closest_hit_bvh(const DevScene &sc, float3 ro, float3 rd, uint2 *st
     return best;
 }
 
+// Closest-hit traversal as a resumable state machine, for kernels that hand a finished lane its next ray while the other
+// lanes of the warp keep walking (k_intersect): same node / triangle arithmetic and acceptance rule as closest_hit_bvh.
+struct ClosestTrav { RayPre r; HitRec best; uint32_t best_order; int sp; uint2 grp; uint32_t node; bool have; };
+B2_HD void closest_init(ClosestTrav &t, const DevScene &sc, float3 ro, float3 rd) {
+    t.r = ray_pre(ro, rd); t.best.prim = B2_PRIM_MISS; t.best.t = B2_T_INF; t.best_order = 0u;
+    t.sp = 0; t.grp = make_uint2(0u, 0u); t.node = 0u; t.have = sc.n_nodes > 0;
+}
+// The node half of a step: pops the next wide node, tests its 8 children, stacks the hit internal ones and returns the hit
+// leaf triangles as (tri_base, 24-bit mask).  Returns false when the tree is exhausted (spheres / light balls: closest_finish).
+template <bool COUNT>
+B2_HD bool closest_node_step(const DevScene &sc, ClosestTrav &t, uint2 *stack, int sstride, TravCounters *cnt, uint32_t &tribits, uint32_t &tri_base) {
+    tribits = 0u; tri_base = 0u;
+    if (!t.have) {
+        if ((t.grp.y >> 8) == 0u) { if (t.sp == 0) return false; t.grp = stack[(--t.sp) * sstride]; }
+        const int p = ffs32(t.grp.y >> 8) - 1;
+        t.grp.y &= ~(1u << (8 + p));
+        const uint32_t slot = (uint32_t) p ^ t.r.oct;
+        t.node = t.grp.x + popc32(t.grp.y & 0xffu & ((1u << slot) - 1u));
+    }
+    t.have = false;
+    uint32_t hits_p, child_base, imask;
+    node_test(sc.nodes, t.node, t.r, 1e-4f, t.best.t, hits_p, tribits, child_base, tri_base, imask);
+    if (COUNT) cnt->nodes++;
+    if (hits_p) {
+        if ((t.grp.y >> 8) != 0u && t.sp < B2_STACK_CAP) stack[(t.sp++) * sstride] = t.grp;
+        t.grp = make_uint2(child_base, (hits_p << 8) | imask);
+    }
+    return true;
+}
+// One wide node and its leaf triangles, all by the ray's own lane.
+template <bool COUNT>
+B2_HD bool closest_step(const DevScene &sc, ClosestTrav &t, uint2 *stack, int sstride, TravCounters *cnt) {
+    uint32_t tribits, tri_base;
+    if (!closest_node_step<COUNT>(sc, t, stack, sstride, cnt, tribits, tri_base)) return false;
+    while (tribits) {
+        const int bit = ffs32(tribits) - 1;
+        tribits &= tribits - 1u;
+        const int ti = (int) tri_base + bit;
+        const float4 a = sc.tri[3 * ti], b = sc.tri[3 * ti + 1], c = sc.tri[3 * ti + 2];
+        if (COUNT) cnt->tris++;
+        float tt;
+        if (tri_test(t.r.o, t.r.d, mk3(a), mk3(b), mk3(c), 1e-4f, t.best.t, tt)) {
+            const uint32_t order = f2u(a.w);
+            if ((t.best.prim == B2_PRIM_MISS || closer(tt, order, t.best.t, t.best_order)) &&
+                group_pass(sc, (int) f2u(c.w), t.r.o, t.r.d, 1e-4f, B2_T_INF)) {
+                t.best.t = tt; t.best.prim = prim_make(B2_KIND_TRI, ti); t.best_order = order;
+            }
+        }
+    }
+    return true;
+}
+B2_HD HitRec closest_finish(const DevScene &sc, ClosestTrav &t) {
+    closest_spheres(sc, t.r.o, t.r.d, t.best, t.best_order);
+    closest_lights(sc, t.r.o, t.r.d, t.best);
+    return t.best;
+}
+
 // Any-hit traversal as a resumable state machine: the connection stage keeps one of these per lane and hands a finished
 // lane its next shadow ray while the other lanes of the warp are still walking the tree (k_connect, trace phase).
 struct AnyTrav { RayPre r; float tmax; int sp; uint2 grp; uint32_t node; bool have; };

@@ -22,30 +22,166 @@ __device__ __forceinline__ void warp_add64(unsigned long long *p, uint32_t v) {
 __device__ __forceinline__ float3 ld3(const float *p, size_t i) { return make_float3(p[3 * i], p[3 * i + 1], p[3 * i + 2]); }
 __device__ __forceinline__ void st3(float *p, size_t i, float3 v) { p[3 * i] = v.x; p[3 * i + 1] = v.y; p[3 * i + 2] = v.z; }
 
-// MODE bit 0: any-hit; BRUTE: exhaustive kernels; COUNT: visit counters
+// MODE bit 0: any-hit; BRUTE: exhaustive kernels; COUNT: visit counters.
+// BVH variants: ONE loop per thread in which a lane whose ray is decided stores its result and loads its next ray at once,
+// while the other lanes of the warp keep walking.  With a ray loop around a traversal loop a warp waited for its longest ray
+// every round: ncu on C5 showed 9.9 of 32 lanes active (incoherent rays, 40 wide nodes per ray on average, several
+// times that for the longest).  B2_QUERY_REFILL=0 restores the nested loops for A/B runs.
+#ifndef B2_QUERY_REFILL
+#define B2_QUERY_REFILL 1
+#endif
 template <bool ANY, bool BRUTE, bool COUNT>
 __global__ void __launch_bounds__(Q_THREADS) k_intersect(DevScene sc, const float *__restrict__ org, const float *__restrict__ dir, size_t n,
                                                          int32_t *__restrict__ prim_id, float *__restrict__ t_out, unsigned long long *counters) {
     extern __shared__ uint2 s_stack[];
     TravCounters tc{ 0u, 0u };
     uint32_t rays = 0;
-    for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
-        const float3 a = ld3(org, i), b = ld3(dir, i);
-        rays++;
-        if (!ANY) {
-            const HitRec h = BRUTE ? closest_hit_brute(sc, a, b) : closest_hit_bvh<COUNT>(sc, a, b, s_stack + threadIdx.x, blockDim.x, &tc);
-            prim_id[i] = public_id(sc, h.prim);
-            if (t_out) t_out[i] = h.t;
-        } else {
-            const ShadowRay sr = make_shadow_ray(a, b);
-            const bool occ = BRUTE ? occluded_brute(sc, sr.o, sr.d, sr.tmax) : occluded_bvh<COUNT>(sc, sr.o, sr.d, sr.tmax, s_stack + threadIdx.x, blockDim.x, &tc);
-            prim_id[i] = occ ? 0 : 1;
+    const size_t stride = (size_t) gridDim.x * blockDim.x;
+    size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (!BRUTE && B2_QUERY_REFILL) {
+        uint2 *stack = s_stack + threadIdx.x;
+        bool busy = false;
+        ClosestTrav ct; AnyTrav at;
+        for (;;) {
+            if (!busy) {
+                if (i >= n) break;
+                const float3 a = ld3(org, i), b = ld3(dir, i);
+                rays++;
+                if (!ANY) closest_init(ct, sc, a, b);
+                else { const ShadowRay sr = make_shadow_ray(a, b); any_init(at, sc, sr.o, sr.d, sr.tmax); }
+                busy = true;
+            }
+            if (!ANY) {
+                if (!closest_step<COUNT>(sc, ct, stack, blockDim.x, &tc)) {
+                    const HitRec h = closest_finish(sc, ct);
+                    prim_id[i] = public_id(sc, h.prim);
+                    if (t_out) t_out[i] = h.t;
+                    i += stride; busy = false;
+                }
+            } else {
+                int r = any_step<COUNT>(sc, at, stack, blockDim.x, &tc);
+                if (r != B2_TRAV_CONTINUE) {
+                    if (r == B2_TRAV_EXHAUSTED && occluded_spheres(sc, at.r.o, at.r.d, 1e-3f, at.tmax)) r = B2_TRAV_HIT;
+                    prim_id[i] = r == B2_TRAV_HIT ? 0 : 1;
+                    i += stride; busy = false;
+                }
+            }
+        }
+    } else {
+        for (; i < n; i += stride) {
+            const float3 a = ld3(org, i), b = ld3(dir, i);
+            rays++;
+            if (!ANY) {
+                const HitRec h = BRUTE ? closest_hit_brute(sc, a, b) : closest_hit_bvh<COUNT>(sc, a, b, s_stack + threadIdx.x, blockDim.x, &tc);
+                prim_id[i] = public_id(sc, h.prim);
+                if (t_out) t_out[i] = h.t;
+            } else {
+                const ShadowRay sr = make_shadow_ray(a, b);
+                const bool occ = BRUTE ? occluded_brute(sc, sr.o, sr.d, sr.tmax) : occluded_bvh<COUNT>(sc, sr.o, sr.d, sr.tmax, s_stack + threadIdx.x, blockDim.x, &tc);
+                prim_id[i] = occ ? 0 : 1;
+            }
         }
     }
     if (COUNT) {
-        // every thread of a warp reaches here (the loop above has no early return)
+        // every thread of a warp reaches here (the loops above have no early return)
         warp_add64(&counters[0], rays); warp_add64(&counters[1], tc.nodes); warp_add64(&counters[2], tc.tris);
     }
+}
+
+// Closest hit with the leaf triangles of a whole warp POOLED: every lane walks its own ray through the wide nodes, but the
+// (ray, triangle) pairs the 32 node tests produce are numbered with a warp prefix sum and tested 32 at a time, whichever
+// lane the ray belongs to.  ncu on C5 before (per-lane triangle loop): the triangle fetch + exact Moeller-Trumbore were 51 %
+// of the executed warp instructions and 60 % of the stall samples at 2.6 - 4.9 active lanes, most of them waiting on three
+// dependent 128-bit loads of one lane.  A candidate goes back to its ray through a 64-bit shared-memory atomicMin on
+// {t bits, ~order}: min t, ties -> the later object, the acceptance rule of the per-lane loop (closer()), so ids and t stay
+// bit-identical (the tests are the same tri_test calls against a tMax that is at least the final one).
+// C5: 511 -> 557 Mrays/s, 9.9 -> 17.1 active lanes per instruction; what remains is load latency (long_scoreboard 4.7 per
+// issue on the node and triangle fetches, DRAM at 1.9 TB/s of random 32-byte sectors, L2 hit rate 41 %).  A prefetch of the
+// next node into L1 (CCTL.E.PF1 right after the node test) changed nothing (554) and was removed.
+#ifndef B2_QUERY_POOL
+#define B2_QUERY_POOL 1
+#endif
+template <bool COUNT>
+__global__ void __launch_bounds__(Q_THREADS) k_closest_pooled(DevScene sc, const float *__restrict__ org, const float *__restrict__ dir, size_t n,
+                                                              int32_t *__restrict__ prim_id, float *__restrict__ t_out, unsigned long long *counters) {
+    extern __shared__ uint2 s_stack[];
+    __shared__ unsigned long long s_key[Q_THREADS];
+    __shared__ int s_ti[Q_THREADS];
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31, wbase = threadIdx.x & ~31;
+    TravCounters tc{ 0u, 0u };
+    uint32_t rays = 0;
+    const size_t stride = (size_t) gridDim.x * blockDim.x;
+    size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    uint2 *stack = s_stack + threadIdx.x;
+    bool busy = false;
+    ClosestTrav ct;
+    ct.r.o = ct.r.d = make_float3(0.f, 0.f, 0.f); ct.best.t = 0.0f;
+    for (;;) {
+        if (!busy && i < n) {
+            closest_init(ct, sc, ld3(org, i), ld3(dir, i));
+            rays++;
+            busy = true;
+        }
+        if (!__any_sync(FULL, busy)) break;
+        uint32_t tribits = 0u, tri_base = 0u;
+        bool exhausted = false;
+        if (busy) exhausted = !closest_node_step<COUNT>(sc, ct, stack, blockDim.x, &tc, tribits, tri_base);
+        const int cnt = __popc(tribits);
+        int incl = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(FULL, incl, d); if (lane >= d) incl += v; }
+        const int total = __shfl_sync(FULL, incl, 31);
+        if (total > 0) {
+            s_key[threadIdx.x] = ~0ull;
+            __syncwarp();
+            for (int base = 0; base < total; base += 32) {
+                const int k = base + lane;
+                int owner = 0;                                  // first lane whose inclusive count exceeds k
+#pragma unroll
+                for (int step = 16; step >= 1; step >>= 1) { const int v = __shfl_sync(FULL, incl, owner + step - 1); if (v <= k) owner += step; }
+                owner = min(owner, 31);
+                const int o_excl = __shfl_sync(FULL, incl - cnt, owner);
+                const uint32_t o_bits = __shfl_sync(FULL, tribits, owner), o_base = __shfl_sync(FULL, tri_base, owner);
+                const float3 ro = make_float3(__shfl_sync(FULL, ct.r.o.x, owner), __shfl_sync(FULL, ct.r.o.y, owner), __shfl_sync(FULL, ct.r.o.z, owner));
+                const float3 rd = make_float3(__shfl_sync(FULL, ct.r.d.x, owner), __shfl_sync(FULL, ct.r.d.y, owner), __shfl_sync(FULL, ct.r.d.z, owner));
+                const float o_tmax = __shfl_sync(FULL, ct.best.t, owner);
+                unsigned long long key = ~0ull;
+                int ti = 0;
+                if (k < total) {
+                    ti = (int) o_base + (int) __fns(o_bits, 0u, k - o_excl + 1);
+                    const float4 a = sc.tri[3 * ti], b = sc.tri[3 * ti + 1], c = sc.tri[3 * ti + 2];
+                    if (COUNT) tc.tris++;
+                    float tt;
+                    if (tri_test(ro, rd, mk3(a), mk3(b), mk3(c), 1e-4f, o_tmax, tt) && group_pass(sc, (int) f2u(c.w), ro, rd, 1e-4f, B2_T_INF)) {
+                        key = ((unsigned long long) __float_as_uint(tt) << 32) | (unsigned long long) (~f2u(a.w));
+                        atomicMin(&s_key[wbase + owner], key);
+                    }
+                }
+                __syncwarp();
+                if (key != ~0ull && s_key[wbase + owner] == key) s_ti[wbase + owner] = ti;      // one object = one order: the winner is unique
+                __syncwarp();
+            }
+            if (cnt > 0) {
+                const unsigned long long key = s_key[threadIdx.x];
+                if (key != ~0ull) {
+                    const float tt = __uint_as_float((uint32_t) (key >> 32));
+                    const uint32_t order = ~(uint32_t) key;
+                    if (ct.best.prim == B2_PRIM_MISS || closer(tt, order, ct.best.t, ct.best_order)) {
+                        ct.best.t = tt; ct.best.prim = prim_make(B2_KIND_TRI, s_ti[threadIdx.x]); ct.best_order = order;
+                    }
+                }
+            }
+            __syncwarp();
+        }
+        if (busy && exhausted) {
+            const HitRec h = closest_finish(sc, ct);
+            prim_id[i] = public_id(sc, h.prim);
+            if (t_out) t_out[i] = h.t;
+            i += stride; busy = false;
+        }
+    }
+    if (COUNT) { warp_add64(&counters[0], rays); warp_add64(&counters[1], tc.nodes); warp_add64(&counters[2], tc.tris); }
 }
 
 __device__ __forceinline__ Mat ld_mat(const float *m, size_t i) {
@@ -117,7 +253,11 @@ int launch_isect(const DevScene &sc, int bvh_depth, const float *o, const float 
     // grid: enough blocks to fill 148 SMs x resident CTAs, grid-stride beyond that
     const size_t want = (n + Q_THREADS - 1) / Q_THREADS;
     const unsigned grid = (unsigned) std::min<size_t>(want, (size_t) 148 * 64);
-    k_intersect<ANY, BRUTE, COUNT><<<grid, Q_THREADS, sb, st>>>(sc, o, d, n, id, t, cnt);
+    if (!ANY && !BRUTE && B2_QUERY_POOL) {
+        if (sb + 2048 > 48 * 1024) B2_CUDA(cudaFuncSetAttribute(k_closest_pooled<COUNT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb));
+        k_closest_pooled<COUNT><<<grid, Q_THREADS, sb, st>>>(sc, o, d, n, id, t, cnt);
+    } else
+        k_intersect<ANY, BRUTE, COUNT><<<grid, Q_THREADS, sb, st>>>(sc, o, d, n, id, t, cnt);
     B2_CUDA(cudaGetLastError());
     return B2_OK;
 }
