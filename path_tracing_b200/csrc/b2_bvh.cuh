@@ -214,6 +214,29 @@ B2_HD int any_step(const DevScene &sc, AnyTrav &t, uint2 *stack, int sstride, Tr
     return B2_TRAV_CONTINUE;
 }
 
+// The node half of any_step: the hit leaf triangles come back as (tri_base, 24-bit mask) for a caller that tests the
+// triangles of a whole warp together (k_connect's trace phase).  false = the tree is exhausted.
+template <bool COUNT>
+B2_HD bool any_node_step(const DevScene &sc, AnyTrav &t, uint2 *stack, int sstride, TravCounters *cnt, uint32_t &tribits, uint32_t &tri_base) {
+    tribits = 0u; tri_base = 0u;
+    if (!t.have) {
+        if ((t.grp.y >> 8) == 0u) { if (t.sp == 0) return false; t.grp = stack[(--t.sp) * sstride]; }
+        const int p = ffs32(t.grp.y >> 8) - 1;
+        t.grp.y &= ~(1u << (8 + p));
+        const uint32_t slot = (uint32_t) p ^ t.r.oct;
+        t.node = t.grp.x + popc32(t.grp.y & 0xffu & ((1u << slot) - 1u));
+    }
+    t.have = false;
+    uint32_t hits_p, child_base, imask;
+    node_test(sc.nodes, t.node, t.r, 1e-3f, t.tmax, hits_p, tribits, child_base, tri_base, imask);
+    if (COUNT) cnt->nodes++;
+    if (hits_p) {
+        if ((t.grp.y >> 8) != 0u && t.sp < B2_STACK_CAP) stack[(t.sp++) * sstride] = t.grp;
+        t.grp = make_uint2(child_base, (hits_p << 8) | imask);
+    }
+    return true;
+}
+
 // true = blocked by an opaque object within [1e-3, tMax] (cpu_check_visibility, cpu_bdpt.cpp:82-107).  The plain loop
 // (state in registers, no resumable struct): b2_intersect's any-hit kernel measured 629 vs 485 Mrays/s against a loop
 // over any_step on the 10 M-triangle soup.

@@ -135,6 +135,10 @@ constexpr int CONN_MQ = 64;           // visible-pair queue: < 32 left + 32 new 
 #ifndef B2_DEFAULT_BATCH_LOG2
 #define B2_DEFAULT_BATCH_LOG2 26      // most eye samples in flight per batch when the caller leaves max_batch_paths at 0
 #endif
+#ifndef B2_CONN_POOL_MIN_TRIS
+#define B2_CONN_POOL_MIN_TRIS 2048    // scenes with at least this many triangles run the trace phase with the leaf triangles of the
+#endif                                // whole warp pooled (C3 spl 8: 882 -> 820 ms); below it the per-lane loop of any_step wins
+                                      // (C2, 48 triangles, 1.5 triangle tests per ray: connect stage 2.94 ms vs 3.51 ms pooled)
 #ifndef B2_REFILL_MIN
 #define B2_REFILL_MIN 20              // idle lanes that trigger a refill (connect_prepare then runs at >= this occupancy)
 #endif
@@ -143,7 +147,7 @@ struct ConnSmem {
     float mq_px[CONN_MQ], mq_py[CONN_MQ], mq_pz[CONN_MQ]; uint32_t mq_e[CONN_MQ];
     float acc[3][32];
 };
-template <bool COUNT>
+template <bool COUNT, bool POOL>
 __global__ void __launch_bounds__(CONN_THREADS, CONN_BLOCKS_PER_SM) k_connect(RenderCtx c) {
     extern __shared__ uint2 s_stack[];                    // CONN_THREADS x stack depth
     __shared__ ConnSmem s_q[CONN_WARPS];
@@ -252,13 +256,58 @@ __global__ void __launch_bounds__(CONN_THREADS, CONN_BLOCKS_PER_SM) k_connect(Re
             } else if (busy_m != 0u) {
                 // ---- trace: one step per lane that holds a ray ----
                 bool visible = false;
+              if (POOL) {
+                // node tests per lane; the leaf triangles of the whole warp are numbered with a prefix sum and tested 32 at a
+                // time by whichever lanes are free (per-lane triangle loops ran at ~4 active lanes, profiles/r01_v11_summary.md)
+                uint32_t tribits = 0u, tri_base = 0u;
+                bool exhausted = false;
+                if (busy) exhausted = !any_node_step<COUNT>(c.sc, tv, stack, CONN_THREADS, &tc, tribits, tri_base);
+                const int cnt = __popc(tribits);
+                int incl = cnt;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += v; }
+                const int total = __shfl_sync(0xffffffffu, incl, 31);
+                uint32_t blocked = 0u;                          // bit j: the ray of lane j hit an opaque triangle
+                for (int base = 0; base < total; base += 32) {
+                    const int k = base + lane;
+                    int owner = 0;
+#pragma unroll
+                    for (int step = 16; step >= 1; step >>= 1) { const int v = __shfl_sync(0xffffffffu, incl, owner + step - 1); if (v <= k) owner += step; }
+                    owner = min(owner, 31);
+                    const int o_excl = __shfl_sync(0xffffffffu, incl - cnt, owner);
+                    const uint32_t o_bits = __shfl_sync(0xffffffffu, tribits, owner), o_base = __shfl_sync(0xffffffffu, tri_base, owner);
+                    const float3 ro = mk3(__shfl_sync(0xffffffffu, tv.r.o.x, owner), __shfl_sync(0xffffffffu, tv.r.o.y, owner), __shfl_sync(0xffffffffu, tv.r.o.z, owner));
+                    const float3 rd = mk3(__shfl_sync(0xffffffffu, tv.r.d.x, owner), __shfl_sync(0xffffffffu, tv.r.d.y, owner), __shfl_sync(0xffffffffu, tv.r.d.z, owner));
+                    const float o_tmax = __shfl_sync(0xffffffffu, tv.tmax, owner);
+                    bool hit = false;
+                    if (k < total) {
+                        const int ti = (int) o_base + (int) __fns(o_bits, 0u, k - o_excl + 1);
+                        const float4 b = c.sc.tri[3 * ti + 1];
+                        if (!(f2u(b.w) & B2_MAT_TRANSPARENT)) {
+                            const float4 a = c.sc.tri[3 * ti], cc = c.sc.tri[3 * ti + 2];
+                            if (COUNT) tc.tris++;
+                            float tt;
+                            hit = (B2_FAST_SHADOW_TRI != 0 ? tri_test_fast(ro, rd, mk3(a), mk3(b), mk3(cc), 1e-3f, o_tmax) : tri_test(ro, rd, mk3(a), mk3(b), mk3(cc), 1e-3f, o_tmax, tt)) &&
+                                  group_pass(c.sc, (int) f2u(cc.w), ro, rd, 1e-3f, o_tmax);
+                        }
+                    }
+                    // every lane learns which owners were hit: OR of (1 << owner) over the lanes that hit
+                    blocked |= __reduce_or_sync(0xffffffffu, hit ? 1u << owner : 0u);
+                }
                 if (busy) {
+                    if ((blocked >> lane) & 1u) busy = false;
+                    else if (exhausted) {
+                        if (!occluded_spheres(c.sc, tv.r.o, tv.r.d, 1e-3f, tv.tmax)) visible = true;
+                        busy = false;
+                    }
+                }
+              } else if (busy) {
                     int r = any_step<COUNT, B2_FAST_SHADOW_TRI != 0>(c.sc, tv, stack, CONN_THREADS, &tc);
                     if (r == B2_TRAV_EXHAUSTED) {
                         if (occluded_spheres(c.sc, tv.r.o, tv.r.d, 1e-3f, tv.tmax)) r = B2_TRAV_HIT; else visible = true;
                     }
                     if (r != B2_TRAV_CONTINUE) busy = false;
-                }
+              }
                 const uint32_t vm = __ballot_sync(0xffffffffu, visible);
                 if (vm) {
                     if (visible) {
@@ -470,8 +519,10 @@ static int set_smem_limits(int bvh_depth) {
     B2_CUDA(cudaFuncSetAttribute(k_extend<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_t));
     B2_CUDA(cudaFuncSetAttribute(k_extend<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_t));
     B2_CUDA(cudaFuncSetAttribute(k_extend<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_t));
-    B2_CUDA(cudaFuncSetAttribute(k_connect<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_c));
-    B2_CUDA(cudaFuncSetAttribute(k_connect<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_c));
+    B2_CUDA(cudaFuncSetAttribute(k_connect<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_c));
+    B2_CUDA(cudaFuncSetAttribute(k_connect<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_c));
+    B2_CUDA(cudaFuncSetAttribute(k_connect<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_c));
+    B2_CUDA(cudaFuncSetAttribute(k_connect<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_c));
     B2_CUDA(cudaFuncSetAttribute(k_light_trace<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_t));
     B2_CUDA(cudaFuncSetAttribute(k_light_trace<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_t));
     B2_CUDA(cudaFuncSetAttribute(k_nee<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_t));
@@ -570,8 +621,9 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
                 const unsigned gc = (unsigned) std::min<long long>(148ll * CONN_BLOCKS_PER_SM, std::max<long long>(1, ((long long) n_live * 8 + CONN_THREADS - 1) / CONN_THREADS));
                 tm.begin(StageTimer::CONNECT);
                 if (ref_set) {
-                    if (count) k_connect<true><<<gc, CONN_THREADS, sb_c, st>>>(c);
-                    else k_connect<false><<<gc, CONN_THREADS, sb_c, st>>>(c);
+                    const bool pool = sc.n_tris >= B2_CONN_POOL_MIN_TRIS;
+                    if (pool) { if (count) k_connect<true, true><<<gc, CONN_THREADS, sb_c, st>>>(c); else k_connect<false, true><<<gc, CONN_THREADS, sb_c, st>>>(c); }
+                    else { if (count) k_connect<true, false><<<gc, CONN_THREADS, sb_c, st>>>(c); else k_connect<false, false><<<gc, CONN_THREADS, sb_c, st>>>(c); }
                 } else {
                     const unsigned gn = (unsigned) std::min<long long>(148ll * 8, blocks_for(n_live, EXT_THREADS));
                     if (count) k_nee<true><<<gn, EXT_THREADS, sb_t, st>>>(c, w_mix);
