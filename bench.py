@@ -249,9 +249,11 @@ def gpu_arm(args):
             "ms_connect": sp["pairs_tested"] * 48 / 32 + sp["shadow_rays"] * (80 + 80) + trav_bytes * (1 - closest_share),
         }[dom]
         hbm, hbm_src = peaks()
-        traffic, traffic_src = measured_traffic({"ms_primary": "k_extend<1, 0>", "ms_extend": "k_extend<0, 0>", "ms_connect": "k_connect<0>"}[dom])
+        traffic, traffic_src = measured_traffic({"ms_primary": "k_extend<1, 0>", "ms_extend": "k_extend<0, 0>", "ms_connect": "k_connect<0, 0>"}[dom])
         # e2e: public host-buffer call; scene upload + BVH build + render + film read-back inside the timed region
-        host_film = np.zeros((H, W, 3), np.float32)
+        # the caller's film buffer is page-locked host memory (the contract's "pinned host memory"): b2_render_bdpt then reads
+        # the film straight into it; a pageable numpy array works too and goes through the library's staging buffer
+        host_film = torch.zeros((H, W, 3), dtype=torch.float32, pin_memory=True).numpy()
         e2e_ms = []
         for i in range(max(2, min(args.steps, 5)) + 1):
             torch.cuda.synchronize()

@@ -10,6 +10,7 @@
 #include "b2_queries.hpp"
 #include "b2_render.hpp"
 #include "b2_scene_handle.hpp"
+#include <vector>
 
 static thread_local char g_err[512] = "";
 void b2_set_error(const char *fmt, ...) {
@@ -190,10 +191,32 @@ int b2_render_bdpt(B2Scene *s, const B2Camera *cam, const B2RenderParams *params
     RenderWorkspace &ws = s->ws_ref();
     B2_TRY(ws.ensure_out(nf));
     B2_TRY(b2_render_device_impl(s->view(), s->bvh.depth, ws, *cam, *params, ws.film_out.p, s->stream, stats));
-    // device -> pinned staging (full PCIe rate) -> the caller's pageable buffer
-    B2_CUDA(cudaMemcpyAsync(ws.h_film, ws.film_out.p, nf * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
-    B2_CUDA(cudaStreamSynchronize(s->stream));
-    memcpy(film_rgb_host, ws.h_film, nf * sizeof(float));
+    // a caller buffer that is already page-locked (cudaHostAlloc / cudaHostRegister, e.g. a pinned torch tensor) takes the film
+    // straight from the device; a pageable one goes through the pinned staging buffer in slices, so that the host copy of
+    // slice k overlaps the PCIe transfer of slice k + 1 (one 12.6 MB memcpy after the whole transfer cost 1.2 ms of the 8.7 ms C2 step)
+    cudaPointerAttributes attr;
+    const bool pinned = cudaPointerGetAttributes(&attr, film_rgb_host) == cudaSuccess && attr.type == cudaMemoryTypeHost;
+    cudaGetLastError();                                        // a pageable pointer is not an error for us
+    if (pinned) {
+        B2_CUDA(cudaMemcpyAsync(film_rgb_host, ws.film_out.p, nf * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
+        B2_CUDA(cudaStreamSynchronize(s->stream));
+        return B2_OK;
+    }
+    const size_t slice = (size_t) 1 << 19;                     // 2 MB of floats
+    const size_t n_slices = (nf + slice - 1) / slice;
+    std::vector<cudaEvent_t> done(n_slices);
+    for (size_t k = 0; k < n_slices; ++k) {
+        const size_t o = k * slice, m = std::min(slice, nf - o);
+        B2_CUDA(cudaMemcpyAsync(ws.h_film + o, ws.film_out.p + o, m * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
+        B2_CUDA(cudaEventCreateWithFlags(&done[k], cudaEventDisableTiming));
+        B2_CUDA(cudaEventRecord(done[k], s->stream));
+    }
+    for (size_t k = 0; k < n_slices; ++k) {
+        const size_t o = k * slice, m = std::min(slice, nf - o);
+        B2_CUDA(cudaEventSynchronize(done[k]));
+        memcpy(film_rgb_host + o, ws.h_film + o, m * sizeof(float));
+        cudaEventDestroy(done[k]);
+    }
     return B2_OK;
 }
 

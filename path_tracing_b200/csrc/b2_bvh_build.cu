@@ -2,6 +2,7 @@
 // Sorting and the two per-level exclusive scans use CUB (shipped with CUDA; plain library primitives off
 // the hot path).  See the header for the pipeline.
 #include <cub/cub.cuh>
+#include <mutex>
 #include "b2_bvh_build.cuh"
 #include "b2_cuda_util.hpp"
 #include "b2_device_scene.hpp"
@@ -87,6 +88,73 @@ __global__ void k_pack_tris(const BuildTri *__restrict__ in, const int *__restri
     if (s < n) pack_tri(in, sorted, perm, s, tri, obj);
 }
 
+// Build temporaries come out of ONE device allocation (bump-allocated; kept per device between builds while it is small):
+// two dozen cudaMalloc / cudaFree pairs cost more than the kernels of a small build (48 triangles: 0.9 ms per build, most of
+// it allocation), and the end-to-end step of the bench creates and builds its scene every time.
+struct BuildArena {
+    char *base = nullptr; size_t cap = 0, off = 0; int dev = 0;
+    static constexpr size_t KEEP = (size_t) 256 << 20;
+    static std::mutex &mtx() { static std::mutex m; return m; }
+    static BuildArena *cache() { static BuildArena c[64]; return c; }
+    int acquire(size_t need) {
+        cudaGetDevice(&dev);
+        {
+            std::lock_guard<std::mutex> lk(mtx());
+            BuildArena &c = cache()[dev & 63];
+            if (c.base) { base = c.base; cap = c.cap; c.base = nullptr; c.cap = 0; }
+        }
+        if (cap < need) {
+            if (base) cudaFree(base);
+            base = nullptr; cap = 0;
+            cudaError_t e = cudaMalloc((void **) &base, need);
+            if (e != cudaSuccess) { base = nullptr; b2_set_error("cudaMalloc(%zu bytes) for the BVH build failed: %s", need, cudaGetErrorString(e)); return B2_ERR_OOM; }
+            cap = need;
+        }
+        off = 0;
+        return B2_OK;
+    }
+    void *take(size_t bytes) {
+        const size_t o = (off + 255) & ~(size_t) 255;
+        if (!base || o + bytes > cap) return nullptr;
+        off = o + bytes;
+        return base + o;
+    }
+    ~BuildArena() {
+        if (!base) return;
+        if (cap <= KEEP) {
+            std::lock_guard<std::mutex> lk(mtx());
+            BuildArena &c = cache()[dev & 63];
+            if (!c.base) { c.base = base; c.cap = cap; base = nullptr; }
+        }
+        if (base) cudaFree(base);
+        base = nullptr;
+    }
+};
+thread_local BuildArena *t_arena = nullptr;
+// DevBuf's interface over the arena (falls back to its own cudaMalloc if the arena is exhausted)
+template <class T>
+struct ArenaBuf {
+    T *p = nullptr; size_t n = 0; bool own = false;
+    ArenaBuf() = default;
+    ArenaBuf(const ArenaBuf &) = delete;
+    ArenaBuf &operator=(const ArenaBuf &) = delete;
+    ~ArenaBuf() { release(); }
+    void release() { if (own && p) cudaFree(p); p = nullptr; n = 0; own = false; }
+    int alloc(size_t count) {
+        release();
+        if (count == 0) count = 1;
+        if (t_arena) p = (T *) t_arena->take(count * sizeof(T));
+        if (!p) {
+            cudaError_t e = cudaMalloc((void **) &p, count * sizeof(T));
+            if (e != cudaSuccess) { p = nullptr; b2_set_error("cudaMalloc(%zu bytes) failed: %s", count * sizeof(T), cudaGetErrorString(e)); return B2_ERR_OOM; }
+            own = true;
+        }
+        n = count;
+        return B2_OK;
+    }
+    int ensure(size_t count) { return (count <= n && p) ? B2_OK : alloc(count); }
+};
+
 }  // namespace
 
 int b2_build_bvh_device(const BuildTri *d_in, int n, float pad, int max_leaf, int builder, int ploc_radius, cudaStream_t st, DeviceBvh &out) {
@@ -96,15 +164,20 @@ int b2_build_bvh_device(const BuildTri *d_in, int n, float pad, int max_leaf, in
     B2_CUDA(cudaEventCreate(&ev0)); B2_CUDA(cudaEventCreate(&ev1));
     B2_CUDA(cudaEventRecord(ev0, st));
     const unsigned T = 256;
-    DevBuf<float> tlo, thi, lo, hi;
-    DevBuf<uint32_t> cb, visit;
-    DevBuf<uint64_t> keys, skeys;
-    DevBuf<int> vals, sorted, left, right, parent, first, last, leaf_parent, perm, nint, ntri, ioff, toff, count, cid_a, cid_b, nn;
-    DevBuf<unsigned long long> pflags, pscan;
-    DevBuf<unsigned char> tmp;
-    DevBuf<CollapseItem> items_a, items_b;
-    DevBuf<CollapseOut> outs;
-    DevBuf<uint4> nodes_tmp;
+    size_t sort_bytes = 0;
+    B2_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, (uint64_t *) nullptr, (uint64_t *) nullptr, (int *) nullptr, (int *) nullptr, n, 0, 63, st));
+    BuildArena arena;                                    // ~330 B of temporaries per triangle, all live at once
+    B2_TRY(arena.acquire((size_t) 400 * (size_t) n + sort_bytes + ((size_t) 1 << 20)));
+    struct ArenaScope { ArenaScope(BuildArena *a) { t_arena = a; } ~ArenaScope() { t_arena = nullptr; } } arena_scope(&arena);
+    ArenaBuf<float> tlo, thi, lo, hi;
+    ArenaBuf<uint32_t> cb, visit;
+    ArenaBuf<uint64_t> keys, skeys;
+    ArenaBuf<int> vals, sorted, left, right, parent, first, last, leaf_parent, perm, nint, ntri, ioff, toff, count, cid_a, cid_b, nn;
+    ArenaBuf<unsigned long long> pflags, pscan;
+    ArenaBuf<unsigned char> tmp;
+    ArenaBuf<CollapseItem> items_a, items_b;
+    ArenaBuf<CollapseOut> outs;
+    ArenaBuf<uint4> nodes_tmp;
     B2_TRY(tlo.alloc(3 * (size_t) n)); B2_TRY(thi.alloc(3 * (size_t) n));
     B2_TRY(cb.alloc(6));
     uint32_t cb_init[6] = { 0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u };
