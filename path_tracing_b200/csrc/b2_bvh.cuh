@@ -181,7 +181,7 @@ B2_HD void any_init(AnyTrav &t, const DevScene &sc, float3 ro, float3 rd, float 
     t.r = ray_pre(ro, rd); t.tmax = tmax; t.sp = 0; t.grp = make_uint2(0u, 0u); t.node = 0u; t.have = sc.n_nodes > 0;
 }
 // One wide node (+ its leaf triangles).  B2_TRAV_EXHAUSTED: no triangle blocks the segment (spheres are the caller's).
-template <bool COUNT, bool FAST_TRI = false>
+template <bool COUNT, bool FAST_TRI = false, bool OPAQUE = false>     // OPAQUE: every triangle blocks, no group cull (sc.gpu_sem callers)
 B2_HD int any_step(const DevScene &sc, AnyTrav &t, uint2 *stack, int sstride, TravCounters *cnt) {
     const float tMin = 1e-3f;
     if (!t.have) {
@@ -200,12 +200,12 @@ B2_HD int any_step(const DevScene &sc, AnyTrav &t, uint2 *stack, int sstride, Tr
         tribits &= tribits - 1u;
         const int ti = (int) tri_base + bit;
         const float4 b = sc.tri[3 * ti + 1];
-        if (f2u(b.w) & B2_MAT_TRANSPARENT) continue;
+        if (!OPAQUE && (f2u(b.w) & B2_MAT_TRANSPARENT)) continue;
         const float4 a = sc.tri[3 * ti], c = sc.tri[3 * ti + 2];
         if (COUNT) cnt->tris++;
         float tt;
         const bool hit = FAST_TRI ? tri_test_fast(t.r.o, t.r.d, mk3(a), mk3(b), mk3(c), tMin, t.tmax) : tri_test(t.r.o, t.r.d, mk3(a), mk3(b), mk3(c), tMin, t.tmax, tt);
-        if (hit && group_pass(sc, (int) f2u(c.w), t.r.o, t.r.d, tMin, t.tmax)) return B2_TRAV_HIT;
+        if (hit && (OPAQUE || group_pass(sc, (int) f2u(c.w), t.r.o, t.r.d, tMin, t.tmax))) return B2_TRAV_HIT;
     }
     if (hits_p) {
         if ((t.grp.y >> 8) != 0u && t.sp < B2_STACK_CAP) stack[(t.sp++) * sstride] = t.grp;

@@ -120,8 +120,12 @@ B2_HD bool pt_shade(const RenderCtx &c, PtState &ps, HitRec h, float3 &add, EyeV
 // Next-event estimation of one vertex (:125-208): one light chosen uniformly; a parallel light is a direction, any other a
 // point on its ball with the power heuristic against the BSDF density.  The draw is keyed by the vertex's depth: a
 // vertex that takes direct light is never a delta bounce, so (pixel, sample, depth) names it uniquely.
-template <bool COUNT>
-B2_HD float3 pt_nee(const RenderCtx &c, const EyeVtx &ev, uint2 *stack, int sstride, TravCounters *tc, uint32_t &n_shadow, uint32_t &n_path) {
+// Three steps, so that the wavefront kernel can trace the shadow rays of many vertices together (k_pt_nee):
+//   pt_nee_prepare : light sample, cosine / spot-cone tests -> shadow ray + what pt_nee_finish needs (false: no contribution)
+//   (visibility)   : any-hit, every object opaque
+//   pt_nee_finish  : BSDF value and density, power heuristic, validity + clamp
+struct NeeSample { float3 wi; float dist2, cos_s, cos_l; int light; };          // light < 0: parallel light -(light + 1)
+B2_HD bool pt_nee_prepare(const RenderCtx &c, const EyeVtx &ev, ShadowRay &sr, NeeSample &ns) {
     const DevScene &sc = c.sc;
     float ul, u1, u2, unused;
     rng_draw4(c.key, B2_RNG_PT_NEE, ev.pixel, (uint32_t) ev.path, 1u + (uint32_t) ev.depth, ul, u1, u2, unused);
@@ -130,16 +134,11 @@ B2_HD float3 pt_nee(const RenderCtx &c, const EyeVtx &ev, uint2 *stack, int sstr
     const float4 l0 = sc.lights[4 * li], l1 = sc.lights[4 * li + 1], l2 = sc.lights[4 * li + 2], l3 = sc.lights[4 * li + 3];
     const float3 p1 = x3_add(ev.pos, x3_muls(ev.n, B2_EPSILON));
     if (l2.w != 0.0f) {                                                   // parallel light, :131-151
-        const float3 ldir = mk3(l3) * -1.0f;
-        const float cos_s = fmaxf(0.0f, dot3(ev.n, ldir));
-        if (!(cos_s > 0.0f)) return mk3(0, 0, 0);
-        const ShadowRay sr = make_shadow_ray(p1, ev.pos + ldir * 1e4f);
-        n_shadow++;
-        if (occluded_bvh<COUNT, true>(sc, sr.o, sr.d, sr.tmax, stack, sstride, tc)) return mk3(0, 0, 0);
-        const float3 contrib = ev.thr * bsdf_evaluate(ev.mtl, ev.wo, ldir, ev.n) * mk3(l2) * (cos_s * (float) sc.n_lights);
-        if (!valid_color(contrib)) return mk3(0, 0, 0);
-        n_path++;
-        return clamp_radiance(contrib, 15.0f);
+        ns.wi = mk3(l3) * -1.0f; ns.light = -(li + 1); ns.dist2 = 0.0f; ns.cos_l = 1.0f;
+        ns.cos_s = fmaxf(0.0f, dot3(ev.n, ns.wi));
+        if (!(ns.cos_s > 0.0f)) return false;
+        sr = make_shadow_ray(p1, ev.pos + ns.wi * 1e4f);
+        return true;
     }
     const float z = 1.0f - 2.0f * u1, r = fast_sqrt(fmaxf(0.0f, 1.0f - z * z));      // point on the light ball, :152-206
     float sphi, cphi;
@@ -147,22 +146,40 @@ B2_HD float3 pt_nee(const RenderCtx &c, const EyeVtx &ev, uint2 *stack, int sstr
     const float3 dl = mk3(r * cphi, r * sphi, z);
     const float3 lpos = mk3(l0) + dl * l0.w;
     float3 wi = lpos - ev.pos;
-    const float dist2 = dot3(wi, wi);
-    wi = div_sqrt3(wi, dist2);
-    const float cos_s = fmaxf(0.0f, dot3(ev.n, wi)), cos_l = fmaxf(0.0f, -dot3(dl, wi));
-    if (!(cos_s > 0.0f && cos_l > 0.0f) || (l1.w > 0.0f && -dot3(mk3(l3), wi) < l3.w)) return mk3(0, 0, 0);
-    const ShadowRay sr = make_shadow_ray(p1, x3_add(lpos, x3_muls(dl, B2_EPSILON)));
-    n_shadow++;
-    if (occluded_bvh<COUNT, true>(sc, sr.o, sr.d, sr.tmax, stack, sstride, tc)) return mk3(0, 0, 0);
-    const float area = 4.0f * B2_PI * l0.w * l0.w;
-    const float pdf_l = fast_div(dist2, (float) sc.n_lights * area * fmaxf(cos_l, 1e-6f));
-    const float pdf_b = bsdf_pdf(ev.mtl, ev.wo, wi, ev.n);
-    const float pl2 = pdf_l * pdf_l, pb2 = pdf_b * pdf_b;
-    const float w = fast_div(pl2, fmaxf(pl2 + pb2, 1e-8f));              // power heuristic, :192-194
-    const float3 contrib = ev.thr * bsdf_evaluate(ev.mtl, ev.wo, wi, ev.n) * mk3(l2) * (fast_div(cos_s, pdf_l) * w);
+    ns.dist2 = dot3(wi, wi);
+    wi = div_sqrt3(wi, ns.dist2);
+    ns.wi = wi; ns.light = li;
+    ns.cos_s = fmaxf(0.0f, dot3(ev.n, wi)); ns.cos_l = fmaxf(0.0f, -dot3(dl, wi));
+    if (!(ns.cos_s > 0.0f && ns.cos_l > 0.0f) || (l1.w > 0.0f && -dot3(mk3(l3), wi) < l3.w)) return false;
+    sr = make_shadow_ray(p1, x3_add(lpos, x3_muls(dl, B2_EPSILON)));
+    return true;
+}
+B2_HD float3 pt_nee_finish(const RenderCtx &c, const EyeVtx &ev, const NeeSample &ns, uint32_t &n_path) {
+    const DevScene &sc = c.sc;
+    float3 contrib;
+    if (ns.light < 0) {
+        const float4 l2 = sc.lights[4 * (-ns.light - 1) + 2];
+        contrib = ev.thr * bsdf_evaluate(ev.mtl, ev.wo, ns.wi, ev.n) * mk3(l2) * (ns.cos_s * (float) sc.n_lights);
+    } else {
+        const float4 l0 = sc.lights[4 * ns.light], l2 = sc.lights[4 * ns.light + 2];
+        const float area = 4.0f * B2_PI * l0.w * l0.w;
+        const float pdf_l = fast_div(ns.dist2, (float) sc.n_lights * area * fmaxf(ns.cos_l, 1e-6f));
+        const float pdf_b = bsdf_pdf(ev.mtl, ev.wo, ns.wi, ev.n);
+        const float pl2 = pdf_l * pdf_l, pb2 = pdf_b * pdf_b;
+        const float w = fast_div(pl2, fmaxf(pl2 + pb2, 1e-8f));          // power heuristic, :192-194
+        contrib = ev.thr * bsdf_evaluate(ev.mtl, ev.wo, ns.wi, ev.n) * mk3(l2) * (fast_div(ns.cos_s, pdf_l) * w);
+    }
     if (!valid_color(contrib)) return mk3(0, 0, 0);
     n_path++;
     return clamp_radiance(contrib, 15.0f);
+}
+template <bool COUNT>
+B2_HD float3 pt_nee(const RenderCtx &c, const EyeVtx &ev, uint2 *stack, int sstride, TravCounters *tc, uint32_t &n_shadow, uint32_t &n_path) {
+    ShadowRay sr; NeeSample ns;
+    if (!pt_nee_prepare(c, ev, sr, ns)) return mk3(0, 0, 0);
+    n_shadow++;
+    if (occluded_bvh<COUNT, true>(c.sc, sr.o, sr.d, sr.tmax, stack, sstride, tc)) return mk3(0, 0, 0);
+    return pt_nee_finish(c, ev, ns, n_path);
 }
 // Both parts for one path (the sequential host driver of tests/hostsim).
 template <bool COUNT>
