@@ -64,10 +64,11 @@ class HostSim:
         names = ["eye_samples", "closest_rays", "shadow_rays", "path_samples", "delta_cap_hits", "nodes", "tris", "pairs", "pretest_mismatch"]
         return film, {k: int(cnt[i]) for i, k in enumerate(names)}
 
-    def render_other(self, integrator, W, H, spp=1, spl=8, eye_depth=8, light_depth=8, seed=1, ppm_radius=0.0, camera=None):
+    def render_other(self, integrator, W, H, spp=1, spl=8, eye_depth=8, light_depth=8, seed=1, ppm_radius=0.0, camera=None,
+                     sample_offset=0, sample_stride=1, film_mode=0):
         """integrator 1 = pt (eye_depth = max_depth), 2 = ppm."""
         cam = np.ascontiguousarray(self.data.camera if camera is None else camera, dtype=A.Camera).reshape(())
-        p = A.RenderParams(W, H, spp, spl, eye_depth, light_depth, seed, 0, 1, 0, 0, 0, 0, 1, 0, integrator, ppm_radius)
+        p = A.RenderParams(W, H, spp, spl, eye_depth, light_depth, seed, sample_offset, sample_stride, film_mode, 0, 0, 0, 1, 0, integrator, ppm_radius)
         film = np.zeros((H, W, 3), np.float32); cnt = np.zeros(16, np.uint64)
         self.L.hs_render_other(self.h, cam.ctypes.data_as(C.c_void_p), C.byref(p), A.ptr(film), A.ptr(cnt))
         names = ["eye_samples", "closest_rays", "shadow_rays", "path_samples", "delta_cap_hits", "nodes", "tris"]

@@ -21,7 +21,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, out_path):
+def _worker(rank, world, port, out_path, integrator=0):
     sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
     os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -32,6 +32,8 @@ def _worker(rank, world, port, out_path):
     c = CFG
 
     def render(off, stride):
+        if integrator == 1:                                     # the pt mode shards its samples the same way (csrc/b2_integrators.cu)
+            return hs.render_other(1, c["W"], c["H"], spp=c["spp"], eye_depth=c["depth"], seed=c["seed"], sample_offset=off, sample_stride=stride, film_mode=1)[0]
         film, _ = hs.render(c["W"], c["H"], c["spp"], c["spl"], c["depth"], c["depth"], seed=c["seed"], sample_offset=off,
                             sample_stride=stride, film_mode=1)
         return film
@@ -61,6 +63,23 @@ def test_sharded_render_and_reduce_equal_the_single_process_film(tmp_path, world
     want = P.render(h, d.cam, c["depth"], c["depth"], c["W"], c["H"], c["spp"], c["spl"], P.opts(rng_mode=P.PHILOX, seed=c["seed"], max_delta=256))
     assert got.shape == want.shape and want.mean() > 0
     assert np.allclose(got, want, rtol=1e-4, atol=1e-6)
+
+
+def test_sharded_pt_render_equals_the_single_process_film(tmp_path):
+    from hostsim_py import build
+    build()
+    out = str(tmp_path / "film_pt.npy")
+    mp.spawn(_worker, args=(2, _free_port(), out, 1), nprocs=2, join=True)
+    got = np.load(out)
+    from oracle import oracle_py as O
+    from path_tracing_b200.scene import reference_scene
+    f = reference_scene("cornell").to_flat()
+    d = O.SceneDesc(f["kind"], f["group"], f["geom"], f["mtl"], f["lights"], f["cam"], f["W"], f["H"])
+    P = O.Port(); h = P.scene(d); c = CFG
+    want = P.render_pt(h, d.cam, c["depth"], c["W"], c["H"], c["spp"], P.opts(rng_mode=P.PHILOX, seed=c["seed"], max_delta=256))
+    assert got.shape == want.shape and want.mean() > 0
+    assert np.allclose(got.mean(axis=(0, 1)), want.mean(axis=(0, 1)), rtol=2e-3)
+    assert (np.abs(got - want).max(axis=2) <= 1e-3 * want.mean()).mean() >= 0.99
 
 
 def test_shard_plan():
