@@ -1,7 +1,10 @@
 """Summarise an `ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --csv` launch list:
 per kernel: launches, total time (cold-cache, serialised: use the SHARE), DRAM bytes.  With --last-half only the second
 half of the launches is used (tools/render_once.py renders twice: warm-up, then the render that counts).
-usage: ncu_traffic.py launches.csv out.json [--last-half]"""
+With --from-last NAME only the launches from the last launch whose kernel name contains NAME onward are used (the scene's BVH
+build precedes the renders in the list, so halving the list no longer separates them: --from-last k_light_paths = the
+second render).
+usage: ncu_traffic.py launches.csv out.json [--last-half | --from-last NAME]"""
 import csv, json, sys, collections
 rows = list(csv.reader(open(sys.argv[1])))
 i = [k for k, r in enumerate(rows) if r and r[0] == "ID"][0]
@@ -14,6 +17,9 @@ for r in rows[i + 1:]:
     d[r[h["Metric Name"]]] = float(r[h["Metric Value"]].replace(",", "")) * scale.get(r[h["Metric Unit"]], 1.0)
 launches = list(recs.values())
 if "--last-half" in sys.argv: launches = launches[len(launches) // 2:]
+if "--from-last" in sys.argv:
+    name = sys.argv[sys.argv.index("--from-last") + 1]
+    launches = launches[max(k for k, d in enumerate(launches) if name in d["name"]):]
 out = collections.OrderedDict(); tot = 0.0
 for d in launches:
     n = d["name"].replace("void <unnamed>::", "").replace("void ", "").split("(")[0]
