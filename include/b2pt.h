@@ -76,6 +76,8 @@ typedef struct B2BvhInfo {
 #define B2_STRATEGIES_FULL           1 /* 1/2 next-event estimation (s=1) + 1/2 light tracing with t=1 film splats + emitter hits */
 #define B2_STRATEGIES_LIGHT_TRACING  2 /* only the t=1 splats: W*H*spp light subpaths, atomicAdd into the film */
 #define B2_STRATEGIES_NEE            3 /* only the eye subpaths with next-event estimation (the estimator the splats are validated against) */
+#define B2_STRATEGIES_MIS            4 /* one light subpath per eye sample, every s/t strategy (next-event, connections, t=1 splats),
+                                         balance heuristic over real area densities: SURVEY 8(f) rank 2, csrc/b2_mis.cuh */
 
 /* The other two integrators of the reference's command line (src/main_cli.cpp:201-213); every
  * render entry point below takes them through B2RenderParams.integrator:

@@ -15,7 +15,7 @@ from .scene import SceneData
 
 CLOSEST, ANY, BRUTE_FORCE, COUNT_VISITS = 0, 1, 16, 32
 FILM_MEAN, FILM_SUM = 0, 1
-STRATEGIES_REFERENCE, STRATEGIES_FULL, STRATEGIES_LIGHT_TRACING, STRATEGIES_NEE = 0, 1, 2, 3
+STRATEGIES_REFERENCE, STRATEGIES_FULL, STRATEGIES_LIGHT_TRACING, STRATEGIES_NEE, STRATEGIES_MIS = 0, 1, 2, 3, 4
 INTEGRATOR_BDPT, INTEGRATOR_PT, INTEGRATOR_PPM = 0, 1, 2      # main_cli's --mode (src/main_cli.cpp:201-213)
 
 

@@ -292,6 +292,7 @@ B2_HD void shade_step(const RenderCtx &c, PathState &ps, HitRec h, ShadeOut &o) 
         o.emitter_hit = true; o.emitted = s.mtl.base;
         return;
     }
+    if (s.is_light && c.sc.ggx_fix) return;                                // outside parity mode a light ball is only ever seen directly (b2_strategies.cuh)
     const float3 wo = ps.rd * -1.0f;
     float pdf_fwd = 1.0f;
     const float3 dp = s.pos - ps.last_pos;

@@ -13,6 +13,7 @@
 //       adds its flux to the hit points of the 27 neighbouring cells with a 128-bit vector atomic; resolve per hit point.
 #include "b2_render.hpp"
 #include "b2_pt.cuh"
+#include "b2_mis.cuh"
 #include "b2_warp.cuh"
 #include <algorithm>
 #include <cub/cub.cuh>
@@ -100,6 +101,26 @@ __global__ void __launch_bounds__(PT_THREADS) k_pt_nee(RenderCtx c) {
     }
     warp_count_add(&c.counters[B2_CNT_SHADOW], n_shadow);
     warp_count_add(&c.counters[B2_CNT_PATH_SAMPLES], n_path);
+    if (COUNT) { warp_count_add(&c.counters[B2_CNT_NODES], tc.nodes); warp_count_add(&c.counters[B2_CNT_TRIS], tc.tris); }
+}
+
+// ---- B2_STRATEGIES_MIS (b2_mis.cuh): one thread per eye sample, its light subpath in local memory ----
+template <bool COUNT>
+__global__ void __launch_bounds__(PT_THREADS) k_bdpt_mis(RenderCtx c, CamFrame cf, int n_items, uint32_t pix0, int s0) {
+    extern __shared__ uint2 s_stack[];
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    TravCounters tc{ 0u, 0u };
+    MisCounters cnt{ 0u, 0u, 0u };
+    if (q < n_items) {
+        uint32_t pixel;
+        const uint32_t ds = udiv_magic(pix0 + (uint32_t) q, (uint32_t) (c.W * c.H), c.npix_magic, pixel);
+        const uint32_t sidx = (uint32_t) (c.sample_offset + (s0 + (int) ds) * c.sample_stride);
+        MisVtx lv[B2_MIS_MAXV];
+        mis_sample_body<COUNT>(c, cf, pixel, sidx, lv, s_stack + threadIdx.x, blockDim.x, &tc, cnt);
+    }
+    warp_count_add(&c.counters[B2_CNT_CLOSEST], cnt.closest);
+    warp_count_add(&c.counters[B2_CNT_SHADOW], cnt.shadow);
+    warp_count_add(&c.counters[B2_CNT_PATH_SAMPLES], cnt.paths);
     if (COUNT) { warp_count_add(&c.counters[B2_CNT_NODES], tc.nodes); warp_count_add(&c.counters[B2_CNT_TRIS], tc.tris); }
 }
 
@@ -208,6 +229,8 @@ int set_limits(int bvh_depth) {
     B2_CUDA(cudaFuncSetAttribute(k_pt_extend<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
     B2_CUDA(cudaFuncSetAttribute(k_pt_nee<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
     B2_CUDA(cudaFuncSetAttribute(k_pt_nee<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
+    B2_CUDA(cudaFuncSetAttribute(k_bdpt_mis<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
+    B2_CUDA(cudaFuncSetAttribute(k_bdpt_mis<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
     B2_CUDA(cudaFuncSetAttribute(k_ppm_eye<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
     B2_CUDA(cudaFuncSetAttribute(k_ppm_eye<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
     B2_CUDA(cudaFuncSetAttribute(k_ppm_photons<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
@@ -328,6 +351,56 @@ int b2_render_pt_impl(const DevScene &sc_in, int bvh_depth, RenderWorkspace &ws,
     float ms = 0.f;
     cudaEventElapsedTime(&ms, ev0, ev1);
     fill_stats(stats, h_cnt, eye_samples, closest_host, n_batches, n_waves, n_launches, ms);
+    cudaEventDestroy(ev0); cudaEventDestroy(ev1);
+    return B2_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// B2_STRATEGIES_MIS: every s/t strategy with real densities (b2_mis.cuh).  Batches of 2^22 eye samples, one launch each.
+// ---------------------------------------------------------------------------------------------------------
+int b2_render_mis_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws, const B2Camera &cam, const B2RenderParams &p,
+                       float *d_film_out, cudaStream_t st, B2Stats *stats) {
+    const int npix = p.width * p.height;
+    const size_t film_floats = (size_t) 3 * npix;
+    const int stride = p.sample_stride > 0 ? p.sample_stride : 1;
+    int n_my = 0;
+    for (long long s = p.sample_offset; s < p.spp; s += stride) n_my++;
+    const long long total = (long long) npix * n_my;
+    if (p.eye_depth > 64 || p.light_depth > 65) { b2_set_error("B2_STRATEGIES_MIS supports eye_depth <= 64 and light_depth <= 65"); return B2_ERR_INVALID; }
+    B2_TRY(ws.film.ensure(film_floats));
+    if (!ws.ints.p) B2_TRY(ws.ints.alloc(8));
+    if (!ws.counters.p) B2_TRY(ws.counters.alloc(B2_CNT_N));
+    B2_TRY(set_limits(bvh_depth));
+    RenderCtx c; b2_setup_ctx(c, sc, cam, p, ws, 1);
+    const bool count = p.count_traversal != 0;
+    uint64_t n_launches = 0, n_batches = 0;
+    cudaEvent_t ev0, ev1;
+    B2_CUDA(cudaEventCreate(&ev0)); B2_CUDA(cudaEventCreate(&ev1));
+    B2_CUDA(cudaEventRecord(ev0, st));
+    B2_CUDA(cudaMemsetAsync(ws.film.p, 0, sizeof(float) * film_floats, st));
+    B2_CUDA(cudaMemsetAsync(ws.counters.p, 0, sizeof(unsigned long long) * B2_CNT_N, st));
+    const size_t sb = stack_bytes(PT_THREADS, bvh_depth);
+    const CamFrame cf = cam_frame(c.cdx, c.cdy);
+    const long long batch = p.max_batch_paths > 0 ? p.max_batch_paths : (1ll << 22);
+    for (long long w0 = 0; w0 < total && sc.n_lights > 0; w0 += batch) {
+        const int n = (int) std::min<long long>(batch, total - w0);
+        const uint32_t pix0 = (uint32_t) (w0 % npix); const int s0 = (int) (w0 / npix);
+        if (count) k_bdpt_mis<true><<<blocks_for(n, PT_THREADS), PT_THREADS, sb, st>>>(c, cf, n, pix0, s0);
+        else k_bdpt_mis<false><<<blocks_for(n, PT_THREADS), PT_THREADS, sb, st>>>(c, cf, n, pix0, s0);
+        n_launches++; n_batches++;
+    }
+    B2_CUDA(cudaGetLastError());
+    const float inv = p.film_mode == B2_FILM_SUM ? 1.0f : 1.0f / (float) p.spp;
+    k_film_out<<<blocks_for(film_floats, 256), 256, 0, st>>>(ws.film.p, d_film_out, film_floats, inv, p.film_mode == B2_FILM_ACCUMULATE);
+    n_launches++;
+    B2_CUDA(cudaGetLastError());
+    B2_CUDA(cudaEventRecord(ev1, st));
+    unsigned long long h_cnt[B2_CNT_N];
+    B2_CUDA(cudaMemcpyAsync(h_cnt, ws.counters.p, sizeof(h_cnt), cudaMemcpyDeviceToHost, st));
+    B2_CUDA(cudaStreamSynchronize(st));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ev0, ev1);
+    fill_stats(stats, h_cnt, (unsigned long long) total, 0ull, n_batches, n_batches, n_launches, ms);
     cudaEventDestroy(ev0); cudaEventDestroy(ev1);
     return B2_OK;
 }

@@ -1,0 +1,285 @@
+// b2_mis.cuh -- B2_STRATEGIES_MIS: bidirectional path tracing with the full strategy set and real densities
+// (SURVEY.md 8(f) rank 2).  What cpu_bdpt.cpp leaves out or gets wrong is done here the textbook way (Veach 1997, ch. 10):
+//
+//   * one light subpath PER EYE SAMPLE (the reference shares one pool of n_lights * spl subpaths between all pixels,
+//     cpu_bdpt.cpp:218-325, so its pool noise never averages out);
+//   * every strategy of a path x_0 (light) x_1 .. x_n (surfaces) x_{n+1} (pinhole): m = 0 next-event estimation,
+//     0 < m < n connection of light vertex x_m with eye vertex x_{m+1}, m = n light tracing with a film splat (the
+//     reference has neither m = 0 nor m = n);
+//   * area densities of BOTH directions at every vertex when a connection is weighted (the reference weights with the
+//     placeholder pdf_fwd = 0 of the vertex being connected, :385, and an unnormalised direction, :431);
+//   * balance heuristic over exactly the strategies that can produce the path under the depth limits and delta surfaces.
+//
+// Same light model, BSDF (normalised GGX, transport order) and camera measurement as b2_strategies.cuh, so the image has the
+// same expectation as B2_STRATEGIES_NEE at equal eye_depth -- that is the test (tests/test_gpu_strategies.py): there is
+// no oracle for a mode the reference does not have.
+//
+// Path space of the mode: at most `eye_depth` non-delta surface vertices per path (delta vertices are free, capped by
+// max_delta); a light subpath carries at most light_depth - 1 of them (vertex 0 of a reference light path is the light).
+// Shadow rays are blocked by every object (the reference lets them through eta > 0 surfaces, cpu_bdpt.cpp:97; with real
+// light subpaths that energy arrives through the refracting light paths instead).  Lights: one of the n_lights is drawn
+// uniformly per light subpath; next-event estimation visits every light.  Parallel lights are ignored, as in
+// b2_strategies.cuh.
+//
+// Weights.  Strategy m produces the path with density  q_m = c_m * prod_{i<=m} pL_i * prod_{i>m} pE_i ,  pL_i / pE_i = area
+// density of x_i when it is generated from the light / eye side, c_m = (m ? 1/n_lights : 1) * (m == n ? W*H : 1): the
+// W*H*spp light subpaths of a render may all splat into the pixel, its own spp eye samples carry the other strategies.
+// A density through a delta surface is a Dirac factor that appears once in either direction and is replaced by 1 in both
+// (any function of the PATH that is positive exactly on the feasible strategies keeps the estimator unbiased; q only has
+// to be the same whichever strategy evaluates it).  w_k = q_k / sum_m q_m, accumulated as ratios from k outwards.
+#pragma once
+#include "b2_strategies.cuh"
+
+#define B2_RNG_MIS_LIGHT 6u
+#define B2_MIS_MAXV 24                   /* stored vertices per subpath, delta ones included */
+
+struct MisVtx { float3 pos, n, wo, beta; Mat mtl; float pdf_fwd, pdf_rev; int delta, nd; };   // nd = non-delta vertices up to and including this one
+
+// w_k of a path of n surface vertices: pL / pE / dl indexed 1..n (index 0 and n + 1 unused).
+B2_HD float mis_balance(const float *pL, const float *pE, const unsigned char *dl, int n, int k, int l_cap, float inv_nl, float wh) {
+    const float ck = (k ? inv_nl : 1.0f) * (k == n ? wh : 1.0f);
+    float sum = 1.0f, r = 1.0f;
+    int nd = 0;
+    for (int i = 1; i <= k; ++i) nd += dl[i] ? 0 : 1;
+    for (int m = k + 1; m <= n; ++m) {                                 // more light vertices
+        const float a = (m >= 2 && dl[m - 1]) ? 1.0f : pL[m], b = (m + 1 <= n && dl[m + 1]) ? 1.0f : pE[m];
+        if (!(a > 0.0f)) break;
+        if (!(b > 0.0f)) return 0.0f;
+        r *= a / b;
+        if (!dl[m] && ++nd > l_cap) break;
+        if (!dl[m] && (m == n || !dl[m + 1])) sum += r * ((m == n ? inv_nl * wh : inv_nl) / ck);
+    }
+    r = 1.0f;
+    for (int m = k - 1; m >= 0; --m) {                                 // more eye vertices
+        const int i = m + 1;
+        const float a = (i + 1 <= n && dl[i + 1]) ? 1.0f : pE[i], b = (i >= 2 && dl[i - 1]) ? 1.0f : pL[i];
+        if (!(a > 0.0f)) break;
+        if (!(b > 0.0f)) return 0.0f;
+        r *= a / b;
+        if ((m == 0 || !dl[m]) && !dl[m + 1]) sum += r * ((m ? inv_nl : 1.0f) / ck);
+    }
+    const float w = 1.0f / sum;
+    return (w > 0.0f && w <= 1.0f) ? w : 0.0f;                          // NaN / Inf / overflowed ratios drop the sample
+}
+
+B2_HD float area_pdf(float pdf_omega, float3 n_to, float3 dir, float d2) { return pdf_omega * fabsf(dot3(n_to, dir)) / fmaxf(d2, 1e-12f); }
+B2_HD void film_add(const RenderCtx &c, uint32_t pixel, float3 v) {
+    if (v.x != 0.0f) atomic_add_f32(&c.film[3 * pixel], v.x);
+    if (v.y != 0.0f) atomic_add_f32(&c.film[3 * pixel + 1], v.y);
+    if (v.z != 0.0f) atomic_add_f32(&c.film[3 * pixel + 2], v.z);
+}
+// camera density of a surface point seen from the pinhole, per unit area: the pixel footprint (b2_strategies.cuh / DESIGN 9)
+B2_HD float camera_area_pdf(const CamFrame &cf, float cos_y, float cos_c, float d2) { return cos_y / fmaxf(d2 * cos_c * cos_c * cos_c * cf.pix_area, 1e-20f); }
+
+struct MisCounters { uint32_t closest, shadow, paths; };
+
+// One eye sample (pixel, sidx): its light subpath with the m = n splats, its eye subpath with the m = 0 .. n - 1 strategies.
+template <bool COUNT>
+B2_HD void mis_sample_body(const RenderCtx &c, const CamFrame &cf, uint32_t pixel, uint32_t sidx, MisVtx *lv, uint2 *stack, int sstride,
+                           TravCounters *tc, MisCounters &cnt) {
+    const DevScene &sc = c.sc;
+    const int n_cap = c.eye_depth, l_cap = c.light_depth - 1;
+    const float inv_nl = 1.0f / (float) sc.n_lights, wh = (float) c.W * (float) c.H;
+    float pL[2 * B2_MIS_MAXV + 2], pE[2 * B2_MIS_MAXV + 2];
+    unsigned char dl[2 * B2_MIS_MAXV + 2];
+    BsdfSample bs; bs.wi = mk3(0, 0, 0); bs.f = mk3(0, 0, 0); bs.pdf = 0.0f;
+
+    // ---------------- light subpath ----------------
+    int S = 0, light_of_path = -1;
+    if (l_cap > 0 && n_cap > 0) {
+        const uint4 o = philox4x32_10(make_uint4(pixel, sidx, 0u, B2_RNG_MIS_LIGHT), c.key);
+        const float r1 = u32_to_unit(o.x), r2 = u32_to_unit(o.y), r3 = u32_to_unit(o.z);
+        int li = (int) (r3 * (float) sc.n_lights);
+        if (li > sc.n_lights - 1) li = sc.n_lights - 1;
+        const SpotLight L = spot_light(sc, li);
+        const float omega = 2.0f * B2_PI * (1.0f - L.cos_cut);
+        if (!L.parallel && omega > 0.0f) {
+            light_of_path = li;
+            float3 u_vec = (fabsf(L.dir.x) > 0.9f) ? mk3(0, 1, 0) : mk3(1, 0, 0);
+            const float3 v_vec = normalize3(cross3(L.dir, u_vec));
+            u_vec = normalize3(cross3(v_vec, L.dir));
+            const float ct = 1.0f - r1 * (1.0f - L.cos_cut), st = fast_sqrt(fmaxf(0.0f, 1.0f - ct * ct));
+            float sphi, cphi;
+            sincos_2pi(r2, sphi, cphi);
+            float3 rd = normalize3(u_vec * (st * cphi) + v_vec * (st * sphi) + L.dir * ct);
+            float3 ro = L.pos + rd * L.r;
+            float3 alpha = mk3(sc.lights[4 * li + 2]) * (float) sc.n_lights;         // illum / (pdf_omega = 1/Omega ... * I = illum/Omega) / P(light)
+            float eta = 1.0f, last_pdf = 1.0f / omega, first_off = L.r;
+            bool prev_delta = false;
+            int nd = 0, n_delta = 0;
+            for (int step = 0; S < B2_MIS_MAXV; ++step) {
+                const HitRec h = closest_hit_bvh<COUNT>(sc, ro, rd, stack, sstride, tc);
+                cnt.closest++;
+                if (h.prim == B2_PRIM_MISS) break;
+                const Surface s = surface_at(sc, ro, rd, h);
+                if (s.is_light) break;
+                MisVtx v;
+                v.pos = s.pos; v.n = s.n; v.wo = rd * -1.0f; v.beta = alpha; v.mtl = s.mtl; v.delta = is_delta_material(s.mtl) ? 1 : 0;
+                if (!v.delta && nd + 1 > l_cap) break;
+                nd += v.delta ? 0 : 1; v.nd = nd;
+                const float dist = h.t + first_off;
+                v.pdf_fwd = prev_delta ? 1.0f : area_pdf(last_pdf, s.n, rd, dist * dist);
+                v.pdf_rev = 0.0f;
+                lv[S++] = v;
+                // ---- m = n: connect to the pinhole and splat ----
+                if (!v.delta && nd <= n_cap) {
+                    uint32_t px; float cos_c, d2; float3 to_eye;
+                    if (camera_project(c, cf, v.pos, px, cos_c, d2, to_eye)) {
+                        const float cos_y = dot3(v.n, to_eye);
+                        if (cos_y > 0.0f) {
+                            const float3 f = bsdf_evaluate(v.mtl, to_eye, v.wo, v.n);
+                            if (f.x > 0.0f || f.y > 0.0f || f.z > 0.0f) {
+                                const int n = S;
+                                for (int i = 1; i <= n; ++i) { pL[i] = lv[i - 1].pdf_fwd; pE[i] = lv[i - 1].pdf_rev; dl[i] = (unsigned char) lv[i - 1].delta; }
+                                pE[n] = camera_area_pdf(cf, cos_y, cos_c, d2);
+                                if (n >= 2) { const float3 dv = lv[n - 2].pos - v.pos; pE[n - 1] = area_pdf(bsdf_pdf(v.mtl, to_eye, v.wo, v.n), lv[n - 2].n, v.wo, dot3(dv, dv)); }
+                                const float w = mis_balance(pL, pE, dl, n, n, l_cap, inv_nl, wh);
+                                if (w > 0.0f) {
+                                    const ShadowRay sr = make_shadow_ray(x3_add(v.pos, x3_muls(v.n, B2_EPSILON)), c.cam_eye);
+                                    cnt.shadow++;
+                                    if (!occluded_bvh<COUNT, true>(sc, sr.o, sr.d, sr.tmax, stack, sstride, tc)) {
+                                        const float3 val = alpha * f * (w * camera_area_pdf(cf, cos_y, cos_c, d2) / wh);
+                                        if (valid_color(val)) { film_add(c, px, val); cnt.paths++; }
+                                    }
+                                }
+                            }
+                        }
+                    }
+                }
+                if (!v.delta && nd == l_cap) break;                                    // nothing behind the last allowed vertex can connect
+                float u_rr, u1, u2;
+                rng_draw3(c.key, B2_RNG_MIS_LIGHT, pixel, sidx, (uint32_t) step, u_rr, u1, u2);
+                bsdf_sample(s.mtl, v.wo, s.n, u_rr, u1, u2, eta, bs);
+                if (bs.pdf <= 0.0f) break;
+                if (S >= 2) {                                                           // density of the previous vertex seen from this one
+                    const float3 dv = lv[S - 2].pos - v.pos;
+                    lv[S - 2].pdf_rev = bs.is_delta ? 1.0f : area_pdf(bsdf_pdf(s.mtl, bs.wi, v.wo, s.n), lv[S - 2].n, v.wo, dot3(dv, dv));
+                }
+                first_off = 0.0f;
+                if (bs.is_delta) {
+                    alpha = alpha * bs.f;
+                    rd = bs.wi; eta = bs.new_eta;
+                    ro = s.pos + s.n * (dot3(bs.wi, s.n) < 0.0f ? -B2_EPSILON : B2_EPSILON);
+                    prev_delta = true;
+                    if (++n_delta >= c.max_delta) break;
+                    continue;
+                }
+                const float3 f_adj = bsdf_evaluate(s.mtl, bs.wi, v.wo, s.n);            // transport order: wo = towards the eye side
+                alpha = alpha * f_adj * fabsf(dot3(s.n, bs.wi)) / bs.pdf;
+                if (!valid_color(alpha) || (alpha.x <= 0.0f && alpha.y <= 0.0f && alpha.z <= 0.0f)) break;
+                rd = bs.wi; ro = s.pos + s.n * B2_EPSILON;
+                last_pdf = bs.pdf; prev_delta = false;
+            }
+        }
+    }
+
+    // ---------------- eye subpath ----------------
+    if (n_cap <= 0) return;
+    float e_fwd[B2_MIS_MAXV], e_rev[B2_MIS_MAXV];
+    unsigned char e_dl[B2_MIS_MAXV];
+    float3 own = mk3(0, 0, 0);
+    float jx, jy;
+    rng_draw2(c.key, B2_RNG_EYE, pixel, sidx, jx, jy);
+    uint32_t col;
+    const uint32_t row = udiv_magic(pixel, (uint32_t) c.W, c.w_magic, col);
+    const float3 pp = c.cUL + c.cdx * ((float) col + jx) + c.cdy * ((float) row + jy);
+    float3 rd = normalize3(pp - c.cam_eye), ro = c.cam_eye;
+    const float cos_cam = dot3(rd, cf.fwd);
+    float3 thr = mk3(1.0f, 1.0f, 1.0f), prev_pos = c.cam_eye, prev_n = rd;
+    float eta = 1.0f, last_pdf = 1.0f;
+    bool prev_delta = false;
+    int T = 0, nd_e = 0, n_delta = 0;
+    for (int step = 0; T < B2_MIS_MAXV; ++step) {
+        const HitRec h = closest_hit_bvh<COUNT>(sc, ro, rd, stack, sstride, tc);
+        cnt.closest++;
+        if (h.prim == B2_PRIM_MISS) break;
+        const Surface s = surface_at(sc, ro, rd, h);
+        if (s.is_light) { if (T == 0) { own = own + s.mtl.base; cnt.paths++; } break; }      // the ball of a light is only ever seen directly
+        const bool delta = is_delta_material(s.mtl);
+        if (!delta && nd_e + 1 > n_cap) break;
+        nd_e += delta ? 0 : 1;
+        const float3 wo = rd * -1.0f;
+        const float3 dprev = s.pos - prev_pos;
+        const float d2prev = dot3(dprev, dprev);
+        e_fwd[T] = T == 0 ? camera_area_pdf(cf, fabsf(dot3(s.n, wo)), cos_cam, d2prev) : (prev_delta ? 1.0f : area_pdf(last_pdf, s.n, rd, d2prev));
+        e_rev[T] = 0.0f; e_dl[T] = delta ? 1 : 0;
+        const int t = ++T;                                                               // this is eye vertex z_t
+        if (!delta) {
+            // ---- m = 0: next-event estimation, every light ----
+            for (int li = 0; li < sc.n_lights; ++li) {
+                const SpotLight L = spot_light(sc, li);
+                if (L.parallel) continue;
+                const float3 d = s.pos - L.pos;
+                const float d2 = dot3(d, d);
+                if (d2 < 1e-12f) continue;
+                const float3 om = d * fast_rsqrt(d2);
+                if (dot3(om, L.dir) < L.cos_cut) continue;
+                const float3 wi = om * -1.0f;
+                const float cos_x = dot3(s.n, wi);
+                if (cos_x <= 0.0f) continue;
+                const float3 f = bsdf_evaluate(s.mtl, wo, wi, s.n);
+                if (f.x <= 0.0f && f.y <= 0.0f && f.z <= 0.0f) continue;
+                const int n = t;                                                         // x_i = z_{n + 1 - i}
+                for (int i = 1; i <= n; ++i) { pE[i] = e_fwd[n - i]; pL[i] = e_rev[n - i]; dl[i] = e_dl[n - i]; }
+                pL[1] = area_pdf(1.0f / (2.0f * B2_PI * (1.0f - L.cos_cut)), s.n, om, d2);
+                if (n >= 2) pL[2] = area_pdf(bsdf_pdf(s.mtl, wi, wo, s.n), prev_n, rd, d2prev);
+                const float w = mis_balance(pL, pE, dl, n, 0, l_cap, inv_nl, wh);
+                if (!(w > 0.0f)) continue;
+                const ShadowRay sr = make_shadow_ray(x3_add(s.pos, x3_muls(s.n, B2_EPSILON)), L.pos + om * L.r);
+                cnt.shadow++;
+                if (occluded_bvh<COUNT, true>(sc, sr.o, sr.d, sr.tmax, stack, sstride, tc)) continue;
+                const float3 val = thr * f * L.intensity * (w * cos_x / d2);
+                if (valid_color(val)) { own = own + val; cnt.paths++; }
+            }
+            // ---- 0 < m < n: this vertex against every light vertex ----
+            for (int sI = 0; sI < S; ++sI) {
+                const MisVtx y = lv[sI];
+                if (y.delta || y.nd + nd_e > n_cap) continue;
+                const float3 dv = y.pos - s.pos;
+                const float d2 = dot3(dv, dv);
+                if (d2 < 1e-10f) continue;
+                const float3 wz = dv * fast_rsqrt(d2), wy = wz * -1.0f;               // z -> y, y -> z
+                const float cos_z = dot3(s.n, wz), cos_y = dot3(y.n, wy);
+                if (cos_z <= 0.0f || cos_y <= 0.0f) continue;
+                const float3 fz = bsdf_evaluate(s.mtl, wo, wz, s.n);
+                const float3 fy = bsdf_evaluate(y.mtl, wy, y.wo, y.n);
+                if ((fz.x <= 0.0f && fz.y <= 0.0f && fz.z <= 0.0f) || (fy.x <= 0.0f && fy.y <= 0.0f && fy.z <= 0.0f)) continue;
+                const int m = sI + 1, n = m + t;
+                for (int i = 1; i <= m; ++i) { pL[i] = lv[i - 1].pdf_fwd; pE[i] = lv[i - 1].pdf_rev; dl[i] = (unsigned char) lv[i - 1].delta; }
+                for (int i = m + 1; i <= n; ++i) { pE[i] = e_fwd[n - i]; pL[i] = e_rev[n - i]; dl[i] = e_dl[n - i]; }
+                pL[m + 1] = area_pdf(bsdf_pdf(y.mtl, y.wo, wy, y.n), s.n, wz, d2);                  // y generates z
+                if (m + 2 <= n) pL[m + 2] = area_pdf(bsdf_pdf(s.mtl, wz, wo, s.n), prev_n, rd, d2prev);   // z, lit from y, generates its eye-side neighbour
+                pE[m] = area_pdf(bsdf_pdf(s.mtl, wo, wz, s.n), y.n, wy, d2);                          // z generates y
+                if (m >= 2) { const float3 dy = lv[m - 2].pos - y.pos; pE[m - 1] = area_pdf(bsdf_pdf(y.mtl, wy, y.wo, y.n), lv[m - 2].n, y.wo, dot3(dy, dy)); }
+                const float w = mis_balance(pL, pE, dl, n, m, l_cap, inv_nl, wh);
+                if (!(w > 0.0f)) continue;
+                const ShadowRay sr = make_shadow_ray(x3_add(s.pos, x3_muls(s.n, B2_EPSILON)), x3_add(y.pos, x3_muls(y.n, B2_EPSILON)));
+                cnt.shadow++;
+                if (occluded_bvh<COUNT, true>(sc, sr.o, sr.d, sr.tmax, stack, sstride, tc)) continue;
+                const float3 val = thr * fz * fy * y.beta * (w * cos_z * cos_y / d2);
+                if (valid_color(val)) { own = own + val; cnt.paths++; }
+            }
+            if (nd_e == n_cap) break;
+        }
+        float u_rr, u1, u2;
+        rng_draw3(c.key, B2_RNG_EYE, pixel, sidx, (uint32_t) step, u_rr, u1, u2);
+        bsdf_sample(s.mtl, wo, s.n, u_rr, u1, u2, eta, bs);
+        if (bs.pdf <= 0.0f) break;
+        if (t >= 2) e_rev[t - 2] = bs.is_delta ? 1.0f : area_pdf(bsdf_pdf(s.mtl, bs.wi, wo, s.n), prev_n, rd, d2prev);
+        prev_pos = s.pos; prev_n = s.n;
+        if (bs.is_delta) {
+            thr = thr * bs.f;
+            rd = bs.wi; eta = bs.new_eta;
+            ro = s.pos + s.n * (dot3(bs.wi, s.n) < 0.0f ? -B2_EPSILON : B2_EPSILON);
+            prev_delta = true;
+            if (++n_delta >= c.max_delta) break;
+            continue;
+        }
+        thr = thr * bs.f * fabsf(dot3(s.n, bs.wi)) / bs.pdf;
+        if (!valid_color(thr) || (thr.x <= 0.0f && thr.y <= 0.0f && thr.z <= 0.0f)) break;
+        rd = bs.wi; ro = s.pos + s.n * B2_EPSILON;
+        last_pdf = bs.pdf; prev_delta = false;
+    }
+    (void) light_of_path;
+    film_add(c, pixel, own);
+}

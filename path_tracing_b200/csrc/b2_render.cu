@@ -442,7 +442,7 @@ static int validate_params(const B2RenderParams &p) {
     if (p.eye_depth > 255) { b2_set_error("eye_depth > 255 is not supported"); return B2_ERR_INVALID; }
     if ((long long) p.width * p.height > (1ll << 24)) { b2_set_error("film larger than 2^24 pixels is not supported"); return B2_ERR_INVALID; }
     if (p.sample_offset < 0 || p.sample_stride < 0) { b2_set_error("invalid sample_offset / sample_stride"); return B2_ERR_INVALID; }
-    if (p.strategies < B2_STRATEGIES_REFERENCE || p.strategies > B2_STRATEGIES_NEE) { b2_set_error("unknown strategies value %d", p.strategies); return B2_ERR_INVALID; }
+    if (p.strategies < B2_STRATEGIES_REFERENCE || p.strategies > B2_STRATEGIES_MIS) { b2_set_error("unknown strategies value %d", p.strategies); return B2_ERR_INVALID; }
     if (p.integrator < B2_INTEGRATOR_BDPT || p.integrator > B2_INTEGRATOR_PPM) { b2_set_error("unknown integrator value %d", p.integrator); return B2_ERR_INVALID; }
     if (p.integrator != B2_INTEGRATOR_BDPT && p.strategies != B2_STRATEGIES_REFERENCE) { b2_set_error("strategies apply to the bdpt integrator only"); return B2_ERR_INVALID; }
     if (!(p.ppm_radius >= 0.0f)) { b2_set_error("invalid ppm_radius"); return B2_ERR_INVALID; }
@@ -536,6 +536,7 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
     B2_TRY(validate_params(p));
     if (p.integrator == B2_INTEGRATOR_PT) return b2_render_pt_impl(sc, bvh_depth, ws, cam, p, d_film_out, st, stats);
     if (p.integrator == B2_INTEGRATOR_PPM) return b2_render_ppm_impl(sc, bvh_depth, ws, cam, p, d_film_out, st, stats);
+    if (p.strategies == B2_STRATEGIES_MIS) return b2_render_mis_impl(sc, bvh_depth, ws, cam, p, d_film_out, st, stats);
     const int npix = p.width * p.height;
     const size_t film_floats = (size_t) 3 * npix;
     const int stride = p.sample_stride > 0 ? p.sample_stride : 1;

@@ -34,6 +34,8 @@ int b2_render_pt_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws, co
                       float *d_film_out, cudaStream_t st, B2Stats *stats);
 int b2_render_ppm_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws, const B2Camera &cam, const B2RenderParams &p,
                        float *d_film_out, cudaStream_t st, B2Stats *stats);
+int b2_render_mis_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws, const B2Camera &cam, const B2RenderParams &p,
+                       float *d_film_out, cudaStream_t st, B2Stats *stats);      // B2_STRATEGIES_MIS (b2_mis.cuh)
 
 // d_film_out: W*H*3 floats on the device.  Blocks until `st` has drained the render (the counters are read back).
 int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws, const B2Camera &cam, const B2RenderParams &p,

@@ -33,7 +33,8 @@ static void usage() {
            "  --eye-depth/--light-depth <int>   Subpath depths (default: 4)\n"
            "  --seed <int>         Philox key (default: 1)\n"
            "  --gpus <int>         GPUs of this node to shard the samples over (default: 1)\n"
-           "  --strategies <string> reference (cpu_bdpt.cpp's set, default) | full (next-event + t=1 splats) | light | nee\n"
+           "  --strategies <string> reference (cpu_bdpt.cpp's set, default) | full (next-event + t=1 splats) | light | nee |\n"
+           "                        mis (one light subpath per sample, every s/t strategy, balance heuristic)\n"
            "  --passes <int>       Progressive passes of --spp samples each, averaged (default: 1)\n"
            "  --dump-every <int>   Write the running average every K passes (default: 0 = only the final image)\n");
 }
@@ -72,6 +73,7 @@ int main(int argc, char **argv) {
                 const std::string sv = v;
                 if (sv == "reference") strategies = B2_STRATEGIES_REFERENCE; else if (sv == "full") strategies = B2_STRATEGIES_FULL;
                 else if (sv == "light") strategies = B2_STRATEGIES_LIGHT_TRACING; else if (sv == "nee") strategies = B2_STRATEGIES_NEE;
+                else if (sv == "mis") strategies = B2_STRATEGIES_MIS;
                 else { fprintf(stderr, "[Error] unknown --strategies '%s'\n", v); return 2; }
             }
         }

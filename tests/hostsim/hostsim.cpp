@@ -74,12 +74,20 @@ void hs_intersect(void *h, const float *org, const float *dir, size_t n, int mod
 
 #include "hostsim_render.hpp"
 #include "hostsim_pt.hpp"
+#include "hostsim_strategies.hpp"
 extern "C" {
 // integrator 1 = pt, 2 = ppm (B2RenderParams.integrator)
 void hs_render_other(void *h, const B2Camera *cam, const B2RenderParams *p, float *film, unsigned long long *counters) {
     HsScene *s = (HsScene *) h;
     HsRenderOut out;
     if (p->integrator == B2_INTEGRATOR_PPM) hs_render_ppm(s->view, *cam, *p, film, out); else hs_render_pt(s->view, *cam, *p, film, out);
+    if (counters) memcpy(counters, out.counters, sizeof(out.counters));
+}
+// B2RenderParams.strategies 1..4 (b2_strategies.cuh, b2_mis.cuh)
+void hs_render_strategies_c(void *h, const B2Camera *cam, const B2RenderParams *p, float *film, unsigned long long *counters) {
+    HsScene *s = (HsScene *) h;
+    HsRenderOut out;
+    hs_render_strategies(s->view, *cam, *p, film, out);
     if (counters) memcpy(counters, out.counters, sizeof(out.counters));
 }
 void hs_render_bdpt(void *h, const B2Camera *cam, const B2RenderParams *p, float *film, unsigned long long *counters) {

@@ -35,6 +35,7 @@ class HostSim:
         L.hs_render_bdpt.argtypes = [vp, vp, C.POINTER(A.RenderParams), vp, vp]
         L.hs_light_pool.argtypes = [vp, C.POINTER(A.RenderParams), vp]
         L.hs_render_other.argtypes = [vp, vp, C.POINTER(A.RenderParams), vp, vp]
+        L.hs_render_strategies_c.argtypes = [vp, vp, C.POINTER(A.RenderParams), vp, vp]
         self.data = data
         self.h = L.hs_scene_create(A.ptr(data.tris), len(data.tris), A.ptr(data.spheres), len(data.spheres), A.ptr(data.materials),
                                    len(data.materials), A.ptr(data.lights), len(data.lights), max_leaf, pad_rel)
@@ -71,6 +72,15 @@ class HostSim:
         p = A.RenderParams(W, H, spp, spl, eye_depth, light_depth, seed, sample_offset, sample_stride, film_mode, 0, 0, 0, 1, 0, integrator, ppm_radius)
         film = np.zeros((H, W, 3), np.float32); cnt = np.zeros(16, np.uint64)
         self.L.hs_render_other(self.h, cam.ctypes.data_as(C.c_void_p), C.byref(p), A.ptr(film), A.ptr(cnt))
+        names = ["eye_samples", "closest_rays", "shadow_rays", "path_samples", "delta_cap_hits", "nodes", "tris"]
+        return film, {k: int(cnt[i]) for i, k in enumerate(names)}
+
+    def render_strategies(self, strategies, W, H, spp=1, eye_depth=8, light_depth=8, seed=1, camera=None, sample_offset=0, sample_stride=1, film_mode=0):
+        """strategies 1 = 1/2 nee + 1/2 light tracing, 2 = light tracing, 3 = nee, 4 = every s/t strategy with the balance heuristic."""
+        cam = np.ascontiguousarray(self.data.camera if camera is None else camera, dtype=A.Camera).reshape(())
+        p = A.RenderParams(W, H, spp, 1, eye_depth, light_depth, seed, sample_offset, sample_stride, film_mode, strategies, 0, 0, 1, 0, 0, 0.0)
+        film = np.zeros((H, W, 3), np.float32); cnt = np.zeros(16, np.uint64)
+        self.L.hs_render_strategies_c(self.h, cam.ctypes.data_as(C.c_void_p), C.byref(p), A.ptr(film), A.ptr(cnt))
         names = ["eye_samples", "closest_rays", "shadow_rays", "path_samples", "delta_cap_hits", "nodes", "tris"]
         return film, {k: int(cnt[i]) for i, k in enumerate(names)}
 

@@ -97,3 +97,42 @@ def test_strategies_shard_like_the_reference_set_and_reject_unknown_values(tmp_p
     ref, _ = sc.render_bdpt(width=48, height=48, spp=8, spl=4, eye_depth=3, light_depth=4, seed=5)   # parity mode is the default and untouched
     assert np.isfinite(ref).all()
     sc.close()
+
+
+def test_mis_mode_has_the_expectation_of_next_event_estimation_and_less_noise(tmp_path):
+    """B2_STRATEGIES_MIS (csrc/b2_mis.cuh): all s/t strategies with balance-heuristic weights over real area
+    densities.  Weights that sum to one over the strategies of every path <=> same expectation as any complete single
+    strategy; on a scene without specular surfaces that is next-event estimation."""
+    sd = box_scene(tmp_path)
+    sc = api.Scene(sd)
+    for eye_depth, light_depth in ((1, 2), (3, 4), (5, 3), (4, 9)):
+        kw = dict(width=48, height=48, spl=1, eye_depth=eye_depth, light_depth=light_depth)
+        nee, _ = sc.render_bdpt(strategies=api.STRATEGIES_NEE, spp=1024, seed=3, **kw)
+        mis, st = sc.render_bdpt(strategies=api.STRATEGIES_MIS, spp=512, seed=4, **kw)
+        mis2, _ = sc.render_bdpt(strategies=api.STRATEGIES_MIS, spp=512, seed=5, **kw)
+        nee2, _ = sc.render_bdpt(strategies=api.STRATEGIES_NEE, spp=512, seed=6, **kw)
+        assert np.isfinite(mis).all() and (mis >= 0).all() and st["eye_samples"] == 48 * 48 * 512 and st["path_samples"] > 48 * 48 * 256
+        tn, tm = nee.sum(axis=(0, 1)), (0.5 * (mis + mis2)).sum(axis=(0, 1))
+        assert np.allclose(tm, tn, rtol=0.006), (eye_depth, light_depth, tm / tn)
+        bn, bm = blocks(nee), blocks(0.5 * (mis + mis2))
+        rel = np.abs(bm - bn).mean(axis=2) / np.maximum(bn.mean(axis=2), 0.25 * bn.mean())
+        assert np.median(rel) < 0.015 and rel.max() < 0.08, (eye_depth, light_depth, np.median(rel), rel.max())
+        if light_depth > 2 and eye_depth > 1:                           # the point of the exercise: less variance per sample than one strategy alone
+            assert np.mean((mis - mis2) ** 2) / 2.0 < np.mean((nee2 - nee) ** 2) / 1.5, (eye_depth, light_depth)      # var at 512 spp: 2 v_mis vs v_nee (1 + 1/2)
+    sc.close()
+
+
+def test_mis_mode_equals_its_host_compilation_and_shards(tmp_path):
+    from hostsim_py import HostSim
+    sd = box_scene(tmp_path)
+    sc = api.Scene(sd)
+    hs = HostSim(sd)
+    kw = dict(width=32, height=32, spp=8, eye_depth=4, light_depth=5, seed=9)
+    want, cw = hs.render_strategies(4, 32, 32, spp=8, eye_depth=4, light_depth=5, seed=9)
+    got, st = sc.render_bdpt(strategies=api.STRATEGIES_MIS, spl=1, **kw)
+    assert st["closest_rays"] == cw["closest_rays"] and abs(int(st["shadow_rays"]) - cw["shadow_rays"]) <= 2
+    assert (np.abs(got - want).max(axis=2) <= 2e-3 * want.mean()).mean() >= 0.99        # same Philox streams; libm vs device sin/cos, atomics reorder the splats
+    whole, _ = sc.render_bdpt(strategies=api.STRATEGIES_MIS, spl=1, film_mode=api.FILM_SUM, **kw)
+    parts = [sc.render_bdpt(strategies=api.STRATEGIES_MIS, spl=1, film_mode=api.FILM_SUM, sample_offset=g, sample_stride=2, **kw)[0] for g in range(2)]
+    assert np.allclose(parts[0] + parts[1], whole, rtol=1e-4, atol=1e-5)
+    hs.close(); sc.close()
