@@ -111,13 +111,12 @@ __global__ void __launch_bounds__(PT_THREADS) k_bdpt_mis(RenderCtx c, CamFrame c
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
     TravCounters tc{ 0u, 0u };
     MisCounters cnt{ 0u, 0u, 0u };
-    if (q < n_items) {
-        uint32_t pixel;
-        const uint32_t ds = udiv_magic(pix0 + (uint32_t) q, (uint32_t) (c.W * c.H), c.npix_magic, pixel);
-        const uint32_t sidx = (uint32_t) (c.sample_offset + (s0 + (int) ds) * c.sample_stride);
-        MisVtx lv[B2_MIS_MAXV];
-        mis_sample_body<COUNT>(c, cf, pixel, sidx, lv, s_stack + threadIdx.x, blockDim.x, &tc, cnt);
-    }
+    const bool valid = q < n_items;                       // every lane runs the body: it votes per warp (b2_mis.cuh)
+    uint32_t pixel;
+    const uint32_t ds = udiv_magic(pix0 + (uint32_t) (valid ? q : 0), (uint32_t) (c.W * c.H), c.npix_magic, pixel);
+    const uint32_t sidx = (uint32_t) (c.sample_offset + (s0 + (int) ds) * c.sample_stride);
+    MisVtx lv[B2_MIS_MAXV];
+    mis_sample_body<COUNT>(c, cf, valid, pixel, sidx, lv, s_stack + threadIdx.x, blockDim.x, &tc, cnt);
     warp_count_add(&c.counters[B2_CNT_CLOSEST], cnt.closest);
     warp_count_add(&c.counters[B2_CNT_SHADOW], cnt.shadow);
     warp_count_add(&c.counters[B2_CNT_PATH_SAMPLES], cnt.paths);

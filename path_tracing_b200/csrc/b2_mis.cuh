@@ -73,9 +73,21 @@ B2_HD float camera_area_pdf(const CamFrame &cf, float cos_y, float cos_c, float 
 
 struct MisCounters { uint32_t closest, shadow, paths; };
 
+// The body is written warp-synchronously: every lane of a warp runs every loop until no lane has work left (B2_WARP_ANY),
+// lanes without work are predicated off, and the expensive parts (closest hit, BSDF + weight, shadow ray) sit at one place of
+// the loop each so that the lanes that need them run them together.  A first version with per-lane `break` / `continue`
+// through nested loops ran with 3.7 of 32 lanes active (ncu: smsp__thread_inst_executed_per_inst_executed, profiles/
+// r01_mis_summary.md).  On the host (tests/hostsim) a "warp" is one lane.
+#if defined(__CUDA_ARCH__)
+#define B2_WARP_ANY(p) (__any_sync(0xffffffffu, (p)) != 0)
+#else
+#define B2_WARP_ANY(p) (p)
+#endif
+
 // One eye sample (pixel, sidx): its light subpath with the m = n splats, its eye subpath with the m = 0 .. n - 1 strategies.
+// `valid` = false for the lanes past the end of a batch: they only take part in the warp votes.
 template <bool COUNT>
-B2_HD void mis_sample_body(const RenderCtx &c, const CamFrame &cf, uint32_t pixel, uint32_t sidx, MisVtx *lv, uint2 *stack, int sstride,
+B2_HD void mis_sample_body(const RenderCtx &c, const CamFrame &cf, bool valid, uint32_t pixel, uint32_t sidx, MisVtx *lv, uint2 *stack, int sstride,
                            TravCounters *tc, MisCounters &cnt) {
     const DevScene &sc = c.sc;
     const int n_cap = c.eye_depth, l_cap = c.light_depth - 1;
@@ -83,203 +95,249 @@ B2_HD void mis_sample_body(const RenderCtx &c, const CamFrame &cf, uint32_t pixe
     float pL[2 * B2_MIS_MAXV + 2], pE[2 * B2_MIS_MAXV + 2];
     unsigned char dl[2 * B2_MIS_MAXV + 2];
     BsdfSample bs; bs.wi = mk3(0, 0, 0); bs.f = mk3(0, 0, 0); bs.pdf = 0.0f;
+    float3 ro = mk3(0, 0, 0), rd = mk3(0, 0, 1);
 
     // ---------------- light subpath ----------------
-    int S = 0, light_of_path = -1;
-    if (l_cap > 0 && n_cap > 0) {
-        const uint4 o = philox4x32_10(make_uint4(pixel, sidx, 0u, B2_RNG_MIS_LIGHT), c.key);
-        const float r1 = u32_to_unit(o.x), r2 = u32_to_unit(o.y), r3 = u32_to_unit(o.z);
-        int li = (int) (r3 * (float) sc.n_lights);
-        if (li > sc.n_lights - 1) li = sc.n_lights - 1;
-        const SpotLight L = spot_light(sc, li);
-        const float omega = 2.0f * B2_PI * (1.0f - L.cos_cut);
-        if (!L.parallel && omega > 0.0f) {
-            light_of_path = li;
+    int S = 0;
+    {
+        bool alive = valid && l_cap > 0 && n_cap > 0;
+        float3 alpha = mk3(0, 0, 0);
+        float eta = 1.0f, last_pdf = 0.0f, first_off = 0.0f;
+        if (alive) {
+            const uint4 o = philox4x32_10(make_uint4(pixel, sidx, 0u, B2_RNG_MIS_LIGHT), c.key);
+            const float r1 = u32_to_unit(o.x), r2 = u32_to_unit(o.y), r3 = u32_to_unit(o.z);
+            int li = (int) (r3 * (float) sc.n_lights);
+            if (li > sc.n_lights - 1) li = sc.n_lights - 1;
+            const SpotLight L = spot_light(sc, li);
+            const float omega = 2.0f * B2_PI * (1.0f - L.cos_cut);
+            alive = !L.parallel && omega > 0.0f;
             float3 u_vec = (fabsf(L.dir.x) > 0.9f) ? mk3(0, 1, 0) : mk3(1, 0, 0);
             const float3 v_vec = normalize3(cross3(L.dir, u_vec));
             u_vec = normalize3(cross3(v_vec, L.dir));
             const float ct = 1.0f - r1 * (1.0f - L.cos_cut), st = fast_sqrt(fmaxf(0.0f, 1.0f - ct * ct));
             float sphi, cphi;
             sincos_2pi(r2, sphi, cphi);
-            float3 rd = normalize3(u_vec * (st * cphi) + v_vec * (st * sphi) + L.dir * ct);
-            float3 ro = L.pos + rd * L.r;
-            float3 alpha = mk3(sc.lights[4 * li + 2]) * (float) sc.n_lights;         // illum / (pdf_omega = 1/Omega ... * I = illum/Omega) / P(light)
-            float eta = 1.0f, last_pdf = 1.0f / omega, first_off = L.r;
-            bool prev_delta = false;
-            int nd = 0, n_delta = 0;
-            for (int step = 0; S < B2_MIS_MAXV; ++step) {
-                const HitRec h = closest_hit_bvh<COUNT>(sc, ro, rd, stack, sstride, tc);
-                cnt.closest++;
-                if (h.prim == B2_PRIM_MISS) break;
-                const Surface s = surface_at(sc, ro, rd, h);
-                if (s.is_light) break;
-                MisVtx v;
+            rd = normalize3(u_vec * (st * cphi) + v_vec * (st * sphi) + L.dir * ct);
+            ro = L.pos + rd * L.r;
+            alpha = mk3(sc.lights[4 * li + 2]) * (float) sc.n_lights;                 // I / (pdf_omega = 1 / Omega) / P(light) = illum * n_lights
+            last_pdf = alive ? 1.0f / omega : 0.0f; first_off = L.r;
+        }
+        bool prev_delta = false;
+        int nd = 0, n_delta = 0;
+        for (int step = 0; B2_WARP_ANY(alive); ++step) {
+            HitRec h; h.prim = B2_PRIM_MISS; h.t = 0.0f;
+            if (alive) { h = closest_hit_bvh<COUNT>(sc, ro, rd, stack, sstride, tc); cnt.closest++; }
+            Surface s; s.is_light = false; s.pos = s.n = mk3(0, 0, 0); s.mtl.base = mk3(0, 0, 0); s.mtl.roughness = s.mtl.metallic = s.mtl.eta = 0.0f;
+            if (alive && h.prim == B2_PRIM_MISS) alive = false;
+            if (alive) { s = surface_at(sc, ro, rd, h); if (s.is_light) alive = false; }
+            MisVtx v; v.delta = 0; v.nd = 0; v.pos = v.n = v.wo = v.beta = mk3(0, 0, 0); v.mtl = s.mtl; v.pdf_fwd = v.pdf_rev = 0.0f;
+            if (alive) {
                 v.pos = s.pos; v.n = s.n; v.wo = rd * -1.0f; v.beta = alpha; v.mtl = s.mtl; v.delta = is_delta_material(s.mtl) ? 1 : 0;
-                if (!v.delta && nd + 1 > l_cap) break;
+                if (!v.delta && nd + 1 > l_cap) alive = false;
+            }
+            // ---- m = n: connect to the pinhole and splat ----
+            bool splat = false;
+            uint32_t px = 0; float cos_c = 1.0f, d2c = 1.0f, cos_y = 0.0f; float3 to_eye = mk3(0, 0, 1);
+            if (alive) {
                 nd += v.delta ? 0 : 1; v.nd = nd;
                 const float dist = h.t + first_off;
                 v.pdf_fwd = prev_delta ? 1.0f : area_pdf(last_pdf, s.n, rd, dist * dist);
                 v.pdf_rev = 0.0f;
                 lv[S++] = v;
-                // ---- m = n: connect to the pinhole and splat ----
-                if (!v.delta && nd <= n_cap) {
-                    uint32_t px; float cos_c, d2; float3 to_eye;
-                    if (camera_project(c, cf, v.pos, px, cos_c, d2, to_eye)) {
-                        const float cos_y = dot3(v.n, to_eye);
-                        if (cos_y > 0.0f) {
-                            const float3 f = bsdf_evaluate(v.mtl, to_eye, v.wo, v.n);
-                            if (f.x > 0.0f || f.y > 0.0f || f.z > 0.0f) {
-                                const int n = S;
-                                for (int i = 1; i <= n; ++i) { pL[i] = lv[i - 1].pdf_fwd; pE[i] = lv[i - 1].pdf_rev; dl[i] = (unsigned char) lv[i - 1].delta; }
-                                pE[n] = camera_area_pdf(cf, cos_y, cos_c, d2);
-                                if (n >= 2) { const float3 dv = lv[n - 2].pos - v.pos; pE[n - 1] = area_pdf(bsdf_pdf(v.mtl, to_eye, v.wo, v.n), lv[n - 2].n, v.wo, dot3(dv, dv)); }
-                                const float w = mis_balance(pL, pE, dl, n, n, l_cap, inv_nl, wh);
-                                if (w > 0.0f) {
-                                    const ShadowRay sr = make_shadow_ray(x3_add(v.pos, x3_muls(v.n, B2_EPSILON)), c.cam_eye);
-                                    cnt.shadow++;
-                                    if (!occluded_bvh<COUNT, true>(sc, sr.o, sr.d, sr.tmax, stack, sstride, tc)) {
-                                        const float3 val = alpha * f * (w * camera_area_pdf(cf, cos_y, cos_c, d2) / wh);
-                                        if (valid_color(val)) { film_add(c, px, val); cnt.paths++; }
-                                    }
-                                }
-                            }
-                        }
-                    }
+                if (!v.delta && nd <= n_cap && camera_project(c, cf, v.pos, px, cos_c, d2c, to_eye)) { cos_y = dot3(v.n, to_eye); splat = cos_y > 0.0f; }
+            }
+            float w = 0.0f;
+            float3 f = mk3(0, 0, 0);
+            if (splat) {
+                f = bsdf_evaluate(v.mtl, to_eye, v.wo, v.n);
+                if (f.x > 0.0f || f.y > 0.0f || f.z > 0.0f) {
+                    const int n = S;
+                    for (int i = 1; i <= n; ++i) { pL[i] = lv[i - 1].pdf_fwd; pE[i] = lv[i - 1].pdf_rev; dl[i] = (unsigned char) lv[i - 1].delta; }
+                    pE[n] = camera_area_pdf(cf, cos_y, cos_c, d2c);
+                    if (n >= 2) { const float3 dv = lv[n - 2].pos - v.pos; pE[n - 1] = area_pdf(bsdf_pdf(v.mtl, to_eye, v.wo, v.n), lv[n - 2].n, v.wo, dot3(dv, dv)); }
+                    w = mis_balance(pL, pE, dl, n, n, l_cap, inv_nl, wh);
                 }
-                if (!v.delta && nd == l_cap) break;                                    // nothing behind the last allowed vertex can connect
+            }
+            if (w > 0.0f) {
+                const ShadowRay sr = make_shadow_ray(x3_add(v.pos, x3_muls(v.n, B2_EPSILON)), c.cam_eye);
+                cnt.shadow++;
+                if (!occluded_bvh<COUNT, true>(sc, sr.o, sr.d, sr.tmax, stack, sstride, tc)) {
+                    const float3 val = alpha * f * (w * camera_area_pdf(cf, cos_y, cos_c, d2c) / wh);
+                    if (valid_color(val)) { film_add(c, px, val); cnt.paths++; }
+                }
+            }
+            if (alive && ((!v.delta && nd == l_cap) || S >= B2_MIS_MAXV)) alive = false;   // nothing behind the last allowed vertex can connect
+            if (alive) {
                 float u_rr, u1, u2;
                 rng_draw3(c.key, B2_RNG_MIS_LIGHT, pixel, sidx, (uint32_t) step, u_rr, u1, u2);
                 bsdf_sample(s.mtl, v.wo, s.n, u_rr, u1, u2, eta, bs);
-                if (bs.pdf <= 0.0f) break;
+                if (bs.pdf <= 0.0f) alive = false;
+            }
+            if (alive) {
                 if (S >= 2) {                                                           // density of the previous vertex seen from this one
                     const float3 dv = lv[S - 2].pos - v.pos;
                     lv[S - 2].pdf_rev = bs.is_delta ? 1.0f : area_pdf(bsdf_pdf(s.mtl, bs.wi, v.wo, s.n), lv[S - 2].n, v.wo, dot3(dv, dv));
                 }
                 first_off = 0.0f;
+                rd = bs.wi;
                 if (bs.is_delta) {
                     alpha = alpha * bs.f;
-                    rd = bs.wi; eta = bs.new_eta;
+                    eta = bs.new_eta;
                     ro = s.pos + s.n * (dot3(bs.wi, s.n) < 0.0f ? -B2_EPSILON : B2_EPSILON);
                     prev_delta = true;
-                    if (++n_delta >= c.max_delta) break;
-                    continue;
+                    if (++n_delta >= c.max_delta) alive = false;
+                } else {
+                    const float3 f_adj = bsdf_evaluate(s.mtl, bs.wi, v.wo, s.n);        // transport order: wo = towards the eye side
+                    alpha = alpha * f_adj * fabsf(dot3(s.n, bs.wi)) / bs.pdf;
+                    if (!valid_color(alpha) || (alpha.x <= 0.0f && alpha.y <= 0.0f && alpha.z <= 0.0f)) alive = false;
+                    ro = s.pos + s.n * B2_EPSILON;
+                    last_pdf = bs.pdf; prev_delta = false;
                 }
-                const float3 f_adj = bsdf_evaluate(s.mtl, bs.wi, v.wo, s.n);            // transport order: wo = towards the eye side
-                alpha = alpha * f_adj * fabsf(dot3(s.n, bs.wi)) / bs.pdf;
-                if (!valid_color(alpha) || (alpha.x <= 0.0f && alpha.y <= 0.0f && alpha.z <= 0.0f)) break;
-                rd = bs.wi; ro = s.pos + s.n * B2_EPSILON;
-                last_pdf = bs.pdf; prev_delta = false;
             }
         }
     }
 
     // ---------------- eye subpath ----------------
-    if (n_cap <= 0) return;
     float e_fwd[B2_MIS_MAXV], e_rev[B2_MIS_MAXV];
     unsigned char e_dl[B2_MIS_MAXV];
     float3 own = mk3(0, 0, 0);
-    float jx, jy;
-    rng_draw2(c.key, B2_RNG_EYE, pixel, sidx, jx, jy);
-    uint32_t col;
-    const uint32_t row = udiv_magic(pixel, (uint32_t) c.W, c.w_magic, col);
-    const float3 pp = c.cUL + c.cdx * ((float) col + jx) + c.cdy * ((float) row + jy);
-    float3 rd = normalize3(pp - c.cam_eye), ro = c.cam_eye;
-    const float cos_cam = dot3(rd, cf.fwd);
+    bool alive = valid && n_cap > 0;
+    float cos_cam = 1.0f;
+    if (alive) {
+        float jx, jy;
+        rng_draw2(c.key, B2_RNG_EYE, pixel, sidx, jx, jy);
+        uint32_t col;
+        const uint32_t row = udiv_magic(pixel, (uint32_t) c.W, c.w_magic, col);
+        const float3 pp = c.cUL + c.cdx * ((float) col + jx) + c.cdy * ((float) row + jy);
+        rd = normalize3(pp - c.cam_eye); ro = c.cam_eye;
+        cos_cam = dot3(rd, cf.fwd);
+    }
     float3 thr = mk3(1.0f, 1.0f, 1.0f), prev_pos = c.cam_eye, prev_n = rd;
     float eta = 1.0f, last_pdf = 1.0f;
     bool prev_delta = false;
     int T = 0, nd_e = 0, n_delta = 0;
-    for (int step = 0; T < B2_MIS_MAXV; ++step) {
-        const HitRec h = closest_hit_bvh<COUNT>(sc, ro, rd, stack, sstride, tc);
-        cnt.closest++;
-        if (h.prim == B2_PRIM_MISS) break;
-        const Surface s = surface_at(sc, ro, rd, h);
-        if (s.is_light) { if (T == 0) { own = own + s.mtl.base; cnt.paths++; } break; }      // the ball of a light is only ever seen directly
-        const bool delta = is_delta_material(s.mtl);
-        if (!delta && nd_e + 1 > n_cap) break;
-        nd_e += delta ? 0 : 1;
+    const int J = sc.n_lights + S;                                                          // candidates of an eye vertex: the lights, then the light vertices
+    for (int step = 0; B2_WARP_ANY(alive); ++step) {
+        HitRec h; h.prim = B2_PRIM_MISS; h.t = 0.0f;
+        if (alive) { h = closest_hit_bvh<COUNT>(sc, ro, rd, stack, sstride, tc); cnt.closest++; }
+        Surface s; s.is_light = false; s.pos = s.n = mk3(0, 0, 0); s.mtl.base = mk3(0, 0, 0); s.mtl.roughness = s.mtl.metallic = s.mtl.eta = 0.0f;
+        if (alive && h.prim == B2_PRIM_MISS) alive = false;
+        if (alive) {
+            s = surface_at(sc, ro, rd, h);
+            if (s.is_light) { if (T == 0) { own = own + s.mtl.base; cnt.paths++; } alive = false; }   // the ball of a light is only ever seen directly
+        }
+        bool delta = false;
+        if (alive) { delta = is_delta_material(s.mtl); if (!delta && nd_e + 1 > n_cap) alive = false; }
         const float3 wo = rd * -1.0f;
-        const float3 dprev = s.pos - prev_pos;
-        const float d2prev = dot3(dprev, dprev);
-        e_fwd[T] = T == 0 ? camera_area_pdf(cf, fabsf(dot3(s.n, wo)), cos_cam, d2prev) : (prev_delta ? 1.0f : area_pdf(last_pdf, s.n, rd, d2prev));
-        e_rev[T] = 0.0f; e_dl[T] = delta ? 1 : 0;
-        const int t = ++T;                                                               // this is eye vertex z_t
-        if (!delta) {
-            // ---- m = 0: next-event estimation, every light ----
-            for (int li = 0; li < sc.n_lights; ++li) {
-                const SpotLight L = spot_light(sc, li);
-                if (L.parallel) continue;
-                const float3 d = s.pos - L.pos;
-                const float d2 = dot3(d, d);
-                if (d2 < 1e-12f) continue;
-                const float3 om = d * fast_rsqrt(d2);
-                if (dot3(om, L.dir) < L.cos_cut) continue;
-                const float3 wi = om * -1.0f;
-                const float cos_x = dot3(s.n, wi);
-                if (cos_x <= 0.0f) continue;
-                const float3 f = bsdf_evaluate(s.mtl, wo, wi, s.n);
-                if (f.x <= 0.0f && f.y <= 0.0f && f.z <= 0.0f) continue;
-                const int n = t;                                                         // x_i = z_{n + 1 - i}
-                for (int i = 1; i <= n; ++i) { pE[i] = e_fwd[n - i]; pL[i] = e_rev[n - i]; dl[i] = e_dl[n - i]; }
-                pL[1] = area_pdf(1.0f / (2.0f * B2_PI * (1.0f - L.cos_cut)), s.n, om, d2);
-                if (n >= 2) pL[2] = area_pdf(bsdf_pdf(s.mtl, wi, wo, s.n), prev_n, rd, d2prev);
-                const float w = mis_balance(pL, pE, dl, n, 0, l_cap, inv_nl, wh);
-                if (!(w > 0.0f)) continue;
-                const ShadowRay sr = make_shadow_ray(x3_add(s.pos, x3_muls(s.n, B2_EPSILON)), L.pos + om * L.r);
-                cnt.shadow++;
-                if (occluded_bvh<COUNT, true>(sc, sr.o, sr.d, sr.tmax, stack, sstride, tc)) continue;
-                const float3 val = thr * f * L.intensity * (w * cos_x / d2);
-                if (valid_color(val)) { own = own + val; cnt.paths++; }
+        float d2prev = 1.0f;
+        int t = T;
+        if (alive) {
+            nd_e += delta ? 0 : 1;
+            const float3 dprev = s.pos - prev_pos;
+            d2prev = dot3(dprev, dprev);
+            e_fwd[T] = T == 0 ? camera_area_pdf(cf, fabsf(dot3(s.n, wo)), cos_cam, d2prev) : (prev_delta ? 1.0f : area_pdf(last_pdf, s.n, rd, d2prev));
+            e_rev[T] = 0.0f; e_dl[T] = delta ? 1 : 0;
+            t = ++T;                                                                         // this is eye vertex z_t
+        }
+        // ---- this vertex against every light (m = 0) and every light vertex (0 < m < n) ----
+        const bool connects = alive && !delta;
+        int j = 0;
+        for (;;) {
+            // cheap part: the next candidate that passes the geometric tests
+            bool have = false;
+            int m = 0; float d2 = 1.0f, cos_z = 0.0f, cos_y = 0.0f; float3 wz = mk3(0, 0, 1), target = mk3(0, 0, 0), scale = mk3(0, 0, 0);
+            while (connects && j < J && !have) {
+                const int cand = j++;
+                if (cand < sc.n_lights) {
+                    const SpotLight L = spot_light(sc, cand);
+                    if (L.parallel) continue;
+                    const float3 d = s.pos - L.pos;
+                    d2 = dot3(d, d);
+                    if (d2 < 1e-12f) continue;
+                    const float3 om = d * fast_rsqrt(d2);
+                    if (dot3(om, L.dir) < L.cos_cut) continue;
+                    wz = om * -1.0f;
+                    cos_z = dot3(s.n, wz);
+                    if (cos_z <= 0.0f) continue;
+                    m = 0; target = L.pos + om * L.r; scale = L.intensity;
+                    cos_y = 1.0f / (2.0f * B2_PI * (1.0f - L.cos_cut));                        // m = 0: the emission density rides in cos_y
+                    have = true;
+                } else {
+                    const MisVtx &y = lv[cand - sc.n_lights];
+                    if (y.delta || y.nd + nd_e > n_cap) continue;
+                    const float3 dv = y.pos - s.pos;
+                    d2 = dot3(dv, dv);
+                    if (d2 < 1e-10f) continue;
+                    wz = dv * fast_rsqrt(d2);
+                    cos_z = dot3(s.n, wz); cos_y = dot3(y.n, wz * -1.0f);
+                    if (cos_z <= 0.0f || cos_y <= 0.0f) continue;
+                    m = cand - sc.n_lights + 1; target = x3_add(y.pos, x3_muls(y.n, B2_EPSILON)); scale = y.beta;
+                    have = true;
+                }
             }
-            // ---- 0 < m < n: this vertex against every light vertex ----
-            for (int sI = 0; sI < S; ++sI) {
-                const MisVtx y = lv[sI];
-                if (y.delta || y.nd + nd_e > n_cap) continue;
-                const float3 dv = y.pos - s.pos;
-                const float d2 = dot3(dv, dv);
-                if (d2 < 1e-10f) continue;
-                const float3 wz = dv * fast_rsqrt(d2), wy = wz * -1.0f;               // z -> y, y -> z
-                const float cos_z = dot3(s.n, wz), cos_y = dot3(y.n, wy);
-                if (cos_z <= 0.0f || cos_y <= 0.0f) continue;
+            if (!B2_WARP_ANY(have)) break;
+            // expensive part, lanes with a candidate together: BSDFs, weight, shadow ray
+            float w = 0.0f;
+            float3 val = mk3(0, 0, 0);
+            if (have) {
                 const float3 fz = bsdf_evaluate(s.mtl, wo, wz, s.n);
-                const float3 fy = bsdf_evaluate(y.mtl, wy, y.wo, y.n);
-                if ((fz.x <= 0.0f && fz.y <= 0.0f && fz.z <= 0.0f) || (fy.x <= 0.0f && fy.y <= 0.0f && fy.z <= 0.0f)) continue;
-                const int m = sI + 1, n = m + t;
-                for (int i = 1; i <= m; ++i) { pL[i] = lv[i - 1].pdf_fwd; pE[i] = lv[i - 1].pdf_rev; dl[i] = (unsigned char) lv[i - 1].delta; }
-                for (int i = m + 1; i <= n; ++i) { pE[i] = e_fwd[n - i]; pL[i] = e_rev[n - i]; dl[i] = e_dl[n - i]; }
-                pL[m + 1] = area_pdf(bsdf_pdf(y.mtl, y.wo, wy, y.n), s.n, wz, d2);                  // y generates z
-                if (m + 2 <= n) pL[m + 2] = area_pdf(bsdf_pdf(s.mtl, wz, wo, s.n), prev_n, rd, d2prev);   // z, lit from y, generates its eye-side neighbour
-                pE[m] = area_pdf(bsdf_pdf(s.mtl, wo, wz, s.n), y.n, wy, d2);                          // z generates y
-                if (m >= 2) { const float3 dy = lv[m - 2].pos - y.pos; pE[m - 1] = area_pdf(bsdf_pdf(y.mtl, wy, y.wo, y.n), lv[m - 2].n, y.wo, dot3(dy, dy)); }
-                const float w = mis_balance(pL, pE, dl, n, m, l_cap, inv_nl, wh);
-                if (!(w > 0.0f)) continue;
-                const ShadowRay sr = make_shadow_ray(x3_add(s.pos, x3_muls(s.n, B2_EPSILON)), x3_add(y.pos, x3_muls(y.n, B2_EPSILON)));
-                cnt.shadow++;
-                if (occluded_bvh<COUNT, true>(sc, sr.o, sr.d, sr.tmax, stack, sstride, tc)) continue;
-                const float3 val = thr * fz * fy * y.beta * (w * cos_z * cos_y / d2);
-                if (valid_color(val)) { own = own + val; cnt.paths++; }
+                const int n = m + t;
+                if (fz.x > 0.0f || fz.y > 0.0f || fz.z > 0.0f) {
+                    for (int i = m + 1; i <= n; ++i) { pE[i] = e_fwd[n - i]; pL[i] = e_rev[n - i]; dl[i] = e_dl[n - i]; }    // x_i = z_{n + 1 - i}
+                    if (m + 2 <= n) pL[m + 2] = area_pdf(bsdf_pdf(s.mtl, wz, wo, s.n), prev_n, rd, d2prev);                  // z, lit from the light side, generates its eye-side neighbour
+                    if (m == 0) {
+                        pL[1] = area_pdf(cos_y, s.n, wz, d2);
+                        val = thr * fz * scale * (cos_z / d2);
+                        w = 1.0f;
+                    } else {
+                        const MisVtx &y = lv[m - 1];
+                        const float3 wy = wz * -1.0f;
+                        const float3 fy = bsdf_evaluate(y.mtl, wy, y.wo, y.n);
+                        if (fy.x > 0.0f || fy.y > 0.0f || fy.z > 0.0f) {
+                            for (int i = 1; i <= m; ++i) { pL[i] = lv[i - 1].pdf_fwd; pE[i] = lv[i - 1].pdf_rev; dl[i] = (unsigned char) lv[i - 1].delta; }
+                            pL[m + 1] = area_pdf(bsdf_pdf(y.mtl, y.wo, wy, y.n), s.n, wz, d2);                                // y generates z
+                            pE[m] = area_pdf(bsdf_pdf(s.mtl, wo, wz, s.n), y.n, wy, d2);                                      // z generates y
+                            if (m >= 2) { const float3 dy = lv[m - 2].pos - y.pos; pE[m - 1] = area_pdf(bsdf_pdf(y.mtl, wy, y.wo, y.n), lv[m - 2].n, y.wo, dot3(dy, dy)); }
+                            val = thr * fz * fy * scale * (cos_z * cos_y / d2);
+                            w = 1.0f;
+                        }
+                    }
+                    if (w > 0.0f) w = mis_balance(pL, pE, dl, n, m, l_cap, inv_nl, wh);
+                }
             }
-            if (nd_e == n_cap) break;
+            if (w > 0.0f) {
+                const ShadowRay sr = make_shadow_ray(x3_add(s.pos, x3_muls(s.n, B2_EPSILON)), target);
+                cnt.shadow++;
+                if (!occluded_bvh<COUNT, true>(sc, sr.o, sr.d, sr.tmax, stack, sstride, tc)) {
+                    val = val * w;
+                    if (valid_color(val)) { own = own + val; cnt.paths++; }
+                }
+            }
         }
-        float u_rr, u1, u2;
-        rng_draw3(c.key, B2_RNG_EYE, pixel, sidx, (uint32_t) step, u_rr, u1, u2);
-        bsdf_sample(s.mtl, wo, s.n, u_rr, u1, u2, eta, bs);
-        if (bs.pdf <= 0.0f) break;
-        if (t >= 2) e_rev[t - 2] = bs.is_delta ? 1.0f : area_pdf(bsdf_pdf(s.mtl, bs.wi, wo, s.n), prev_n, rd, d2prev);
-        prev_pos = s.pos; prev_n = s.n;
-        if (bs.is_delta) {
-            thr = thr * bs.f;
-            rd = bs.wi; eta = bs.new_eta;
-            ro = s.pos + s.n * (dot3(bs.wi, s.n) < 0.0f ? -B2_EPSILON : B2_EPSILON);
-            prev_delta = true;
-            if (++n_delta >= c.max_delta) break;
-            continue;
+        if (alive && ((!delta && nd_e == n_cap) || T >= B2_MIS_MAXV)) alive = false;
+        if (alive) {
+            float u_rr, u1, u2;
+            rng_draw3(c.key, B2_RNG_EYE, pixel, sidx, (uint32_t) step, u_rr, u1, u2);
+            bsdf_sample(s.mtl, wo, s.n, u_rr, u1, u2, eta, bs);
+            if (bs.pdf <= 0.0f) alive = false;
         }
-        thr = thr * bs.f * fabsf(dot3(s.n, bs.wi)) / bs.pdf;
-        if (!valid_color(thr) || (thr.x <= 0.0f && thr.y <= 0.0f && thr.z <= 0.0f)) break;
-        rd = bs.wi; ro = s.pos + s.n * B2_EPSILON;
-        last_pdf = bs.pdf; prev_delta = false;
+        if (alive) {
+            if (t >= 2) e_rev[t - 2] = bs.is_delta ? 1.0f : area_pdf(bsdf_pdf(s.mtl, bs.wi, wo, s.n), prev_n, rd, d2prev);
+            prev_pos = s.pos; prev_n = s.n;
+            rd = bs.wi;
+            if (bs.is_delta) {
+                thr = thr * bs.f;
+                eta = bs.new_eta;
+                ro = s.pos + s.n * (dot3(bs.wi, s.n) < 0.0f ? -B2_EPSILON : B2_EPSILON);
+                prev_delta = true;
+                if (++n_delta >= c.max_delta) alive = false;
+            } else {
+                thr = thr * bs.f * fabsf(dot3(s.n, bs.wi)) / bs.pdf;
+                if (!valid_color(thr) || (thr.x <= 0.0f && thr.y <= 0.0f && thr.z <= 0.0f)) alive = false;
+                ro = s.pos + s.n * B2_EPSILON;
+                last_pdf = bs.pdf; prev_delta = false;
+            }
+        }
     }
-    (void) light_of_path;
-    film_add(c, pixel, own);
+    if (valid) film_add(c, pixel, own);
 }

@@ -27,7 +27,7 @@ inline void hs_render_strategies(const DevScene &sc_in, const B2Camera &cam, con
     for (long long w = 0; w < total; ++w) {
         const uint32_t pixel = (uint32_t) (w % npix);
         const uint32_t sidx = (uint32_t) (c.sample_offset + (int) (w / npix) * c.sample_stride);
-        if (p.strategies == B2_STRATEGIES_MIS) { mis_sample_body<true>(c, cf, pixel, sidx, lv.data(), stack, 1, &tc, mc); continue; }
+        if (p.strategies == B2_STRATEGIES_MIS) { mis_sample_body<true>(c, cf, true, pixel, sidx, lv.data(), stack, 1, &tc, mc); continue; }
         if (lt) light_trace_body<true>(c, cf, (unsigned long long) sidx * (unsigned long long) npix + pixel, (float) sc.n_lights / (float) npix * w_mix, stack, 1, &tc, ncl, nsh, npa);
         if (nee && p.eye_depth > 0) {
             PathState ps = primary_path(c, (uint32_t) (w % npix), (int) (w / npix), 0u);
