@@ -36,7 +36,7 @@
 struct MisVtx { float3 pos, n, wo, beta; Mat mtl; float pdf_fwd, pdf_rev; int delta, nd; };   // nd = non-delta vertices up to and including this one
 
 // w_k of a path of n surface vertices: pL / pE / dl indexed 1..n (index 0 and n + 1 unused).
-B2_HD float mis_balance(const float *pL, const float *pE, const unsigned char *dl, int n, int k, int l_cap, float inv_nl, float wh) {
+B2_NOINLINE float mis_balance(const float *pL, const float *pE, const unsigned char *dl, int n, int k, int l_cap, float inv_nl, float wh) {
     const float ck = (k ? inv_nl : 1.0f) * (k == n ? wh : 1.0f);
     float sum = 1.0f, r = 1.0f;
     int nd = 0;
@@ -72,6 +72,20 @@ B2_HD void film_add(const RenderCtx &c, uint32_t pixel, float3 v) {
 B2_HD float camera_area_pdf(const CamFrame &cf, float cos_y, float cos_c, float d2) { return cos_y / fmaxf(d2 * cos_c * cos_c * cos_c * cf.pix_area, 1e-20f); }
 
 struct MisCounters { uint32_t closest, shadow, paths; };
+
+// Out-of-line copies of the big pieces: the body needs each of them at two places (light walk, eye walk), and inlined the
+// kernel was 9 900 SASS instructions that did not fit the instruction cache (ncu: stall_no_instruction 18.3 per issue).
+template <bool COUNT>
+B2_NOINLINE HitRec mis_closest(const DevScene &sc, float3 ro, float3 rd, uint2 *stack, int sstride, TravCounters *tc) {
+    return closest_hit_bvh<COUNT>(sc, ro, rd, stack, sstride, tc);
+}
+template <bool COUNT>
+B2_NOINLINE bool mis_occluded(const DevScene &sc, float3 p1, float3 p2, uint2 *stack, int sstride, TravCounters *tc) {
+    const ShadowRay sr = make_shadow_ray(p1, p2);
+    return occluded_bvh<COUNT, true>(sc, sr.o, sr.d, sr.tmax, stack, sstride, tc);
+}
+B2_NOINLINE void mis_bsdf_sample(const Mat &m, float3 wo, float3 n, float u_rr, float u1, float u2, float eta, BsdfSample &bs) { bsdf_sample(m, wo, n, u_rr, u1, u2, eta, bs); }
+B2_NOINLINE Surface mis_surface(const DevScene &sc, float3 ro, float3 rd, HitRec h) { return surface_at(sc, ro, rd, h); }
 
 // The body is written warp-synchronously: every lane of a warp runs every loop until no lane has work left (B2_WARP_ANY),
 // lanes without work are predicated off, and the expensive parts (closest hit, BSDF + weight, shadow ray) sit at one place of
@@ -126,10 +140,10 @@ B2_HD void mis_sample_body(const RenderCtx &c, const CamFrame &cf, bool valid, u
         int nd = 0, n_delta = 0;
         for (int step = 0; B2_WARP_ANY(alive); ++step) {
             HitRec h; h.prim = B2_PRIM_MISS; h.t = 0.0f;
-            if (alive) { h = closest_hit_bvh<COUNT>(sc, ro, rd, stack, sstride, tc); cnt.closest++; }
+            if (alive) { h = mis_closest<COUNT>(sc, ro, rd, stack, sstride, tc); cnt.closest++; }
             Surface s; s.is_light = false; s.pos = s.n = mk3(0, 0, 0); s.mtl.base = mk3(0, 0, 0); s.mtl.roughness = s.mtl.metallic = s.mtl.eta = 0.0f;
             if (alive && h.prim == B2_PRIM_MISS) alive = false;
-            if (alive) { s = surface_at(sc, ro, rd, h); if (s.is_light) alive = false; }
+            if (alive) { s = mis_surface(sc, ro, rd, h); if (s.is_light) alive = false; }
             MisVtx v; v.delta = 0; v.nd = 0; v.pos = v.n = v.wo = v.beta = mk3(0, 0, 0); v.mtl = s.mtl; v.pdf_fwd = v.pdf_rev = 0.0f;
             if (alive) {
                 v.pos = s.pos; v.n = s.n; v.wo = rd * -1.0f; v.beta = alpha; v.mtl = s.mtl; v.delta = is_delta_material(s.mtl) ? 1 : 0;
@@ -159,9 +173,8 @@ B2_HD void mis_sample_body(const RenderCtx &c, const CamFrame &cf, bool valid, u
                 }
             }
             if (w > 0.0f) {
-                const ShadowRay sr = make_shadow_ray(x3_add(v.pos, x3_muls(v.n, B2_EPSILON)), c.cam_eye);
                 cnt.shadow++;
-                if (!occluded_bvh<COUNT, true>(sc, sr.o, sr.d, sr.tmax, stack, sstride, tc)) {
+                if (!mis_occluded<COUNT>(sc, x3_add(v.pos, x3_muls(v.n, B2_EPSILON)), c.cam_eye, stack, sstride, tc)) {
                     const float3 val = alpha * f * (w * camera_area_pdf(cf, cos_y, cos_c, d2c) / wh);
                     if (valid_color(val)) { film_add(c, px, val); cnt.paths++; }
                 }
@@ -170,7 +183,7 @@ B2_HD void mis_sample_body(const RenderCtx &c, const CamFrame &cf, bool valid, u
             if (alive) {
                 float u_rr, u1, u2;
                 rng_draw3(c.key, B2_RNG_MIS_LIGHT, pixel, sidx, (uint32_t) step, u_rr, u1, u2);
-                bsdf_sample(s.mtl, v.wo, s.n, u_rr, u1, u2, eta, bs);
+                mis_bsdf_sample(s.mtl, v.wo, s.n, u_rr, u1, u2, eta, bs);
                 if (bs.pdf <= 0.0f) alive = false;
             }
             if (alive) {
@@ -219,11 +232,11 @@ B2_HD void mis_sample_body(const RenderCtx &c, const CamFrame &cf, bool valid, u
     const int J = sc.n_lights + S;                                                          // candidates of an eye vertex: the lights, then the light vertices
     for (int step = 0; B2_WARP_ANY(alive); ++step) {
         HitRec h; h.prim = B2_PRIM_MISS; h.t = 0.0f;
-        if (alive) { h = closest_hit_bvh<COUNT>(sc, ro, rd, stack, sstride, tc); cnt.closest++; }
+        if (alive) { h = mis_closest<COUNT>(sc, ro, rd, stack, sstride, tc); cnt.closest++; }
         Surface s; s.is_light = false; s.pos = s.n = mk3(0, 0, 0); s.mtl.base = mk3(0, 0, 0); s.mtl.roughness = s.mtl.metallic = s.mtl.eta = 0.0f;
         if (alive && h.prim == B2_PRIM_MISS) alive = false;
         if (alive) {
-            s = surface_at(sc, ro, rd, h);
+            s = mis_surface(sc, ro, rd, h);
             if (s.is_light) { if (T == 0) { own = own + s.mtl.base; cnt.paths++; } alive = false; }   // the ball of a light is only ever seen directly
         }
         bool delta = false;
@@ -306,9 +319,8 @@ B2_HD void mis_sample_body(const RenderCtx &c, const CamFrame &cf, bool valid, u
                 }
             }
             if (w > 0.0f) {
-                const ShadowRay sr = make_shadow_ray(x3_add(s.pos, x3_muls(s.n, B2_EPSILON)), target);
                 cnt.shadow++;
-                if (!occluded_bvh<COUNT, true>(sc, sr.o, sr.d, sr.tmax, stack, sstride, tc)) {
+                if (!mis_occluded<COUNT>(sc, x3_add(s.pos, x3_muls(s.n, B2_EPSILON)), target, stack, sstride, tc)) {
                     val = val * w;
                     if (valid_color(val)) { own = own + val; cnt.paths++; }
                 }
@@ -318,7 +330,7 @@ B2_HD void mis_sample_body(const RenderCtx &c, const CamFrame &cf, bool valid, u
         if (alive) {
             float u_rr, u1, u2;
             rng_draw3(c.key, B2_RNG_EYE, pixel, sidx, (uint32_t) step, u_rr, u1, u2);
-            bsdf_sample(s.mtl, wo, s.n, u_rr, u1, u2, eta, bs);
+            mis_bsdf_sample(s.mtl, wo, s.n, u_rr, u1, u2, eta, bs);
             if (bs.pdf <= 0.0f) alive = false;
         }
         if (alive) {
