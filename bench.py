@@ -217,7 +217,15 @@ def gpu_arm(args):
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1) / args.steps
+    # K steps take ~70 ms and nvidia-smi needs longer than that to print its first row (several hundred ms with 8 GPUs on the
+    # box): when the timed region ended before two rows arrived, the same step keeps the GPU under the same load, untimed,
+    # until they have (at most 4 s)
+    n_timed, t_wait = len(sampler.rows), time.time()
+    while sampler.p and len(sampler.rows) < 2 and time.time() - t_wait < 4.0:
+        sc.render_bdpt(device_ptr=film.data_ptr(), stream=stream, **kw)      # the render alone: ranks leave this loop at different times, no collective here
+        torch.cuda.synchronize()
     clocks = sampler.stop()
+    clocks["samples_in_timed_region"] = n_timed
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
