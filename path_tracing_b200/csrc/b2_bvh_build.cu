@@ -29,9 +29,83 @@ __global__ void k_tri_bounds(const BuildTri *__restrict__ in, int n, float pad, 
         if ((threadIdx.x & 31) == 0) { atomicMin(&cbounds[a], f2ord(c[a])); atomicMax(&cbounds[3 + a], f2ord(C[a])); }
     }
 }
-__global__ void k_morton(int n, const float *__restrict__ tlo, const float *__restrict__ thi, float3 cmin, float3 cinv, uint64_t *keys, int *vals) {
+// ---- small scenes: PLOC passes and the collapse of one build in ONE CTA (no host round trip per pass / level) ----
+// Same bodies, same order of decisions, hence the same tree as the multi-launch path (tests/test_bvh_builders.py compares
+// both with the host mirror).  The 48-triangle scene of the C2 bench took 0.73 ms of host time for ~14 synchronisations.
+constexpr int SMALL_N = 1024;
+struct SmallBuildInfo { int n_nodes, depth, passes, tris_done, error; };
+__global__ void __launch_bounds__(SMALL_N) k_build_small(BinTree bt, const float *__restrict__ tlo, const float *__restrict__ thi, int radius, int max_leaf,
+                                                          int *cid_a, int *cid_b, int *nn, CollapseItem *items_a, CollapseItem *items_b, CollapseOut *outs,
+                                                          uint4 *nodes, int *perm, SmallBuildInfo *info) {
+    typedef cub::BlockScan<unsigned long long, SMALL_N> Scan64;
+    typedef cub::BlockScan<int, SMALL_N> Scan32;
+    __shared__ union { typename Scan64::TempStorage s64; typename Scan32::TempStorage s32; } tmp;
+    const int i = threadIdx.x, n = bt.n;
+    int passes = 0, error = 0;
+    if (n >= 2) {
+        if (i < n) { ploc_leaf(bt, tlo, thi, i); cid_a[i] = (n - 1) + i; }
+        __syncthreads();
+        int *cur = cid_a, *nxt = cid_b;
+        int m = n, created = 0;
+        while (m > 1) {
+            if (i < m) nn[i] = ploc_nearest(bt, cur, m, i, radius);
+            __syncthreads();
+            int r = 2;
+            unsigned long long f = 0ull, ex = 0ull, total = 0ull;
+            if (i < m) { r = ploc_role(nn, i); f = (r == 1 ? 1ull : 0ull) | (r != 2 ? 1ull << 32 : 0ull); }
+            Scan64(tmp.s64).ExclusiveSum(f, ex, total);
+            if (i < m && r != 2) {
+                const int pos = (int) (ex >> 32);
+                if (r == 1) {
+                    const int node = n - 2 - (created + (int) (uint32_t) ex);
+                    ploc_merge(bt, cur[i], cur[nn[i]], node);
+                    nxt[pos] = node;
+                } else nxt[pos] = cur[i];
+            }
+            __syncthreads();
+            const int merged = (int) (uint32_t) total, alive = (int) (total >> 32);
+            if (merged <= 0 || alive != m - merged) { error = 1; break; }              // uniform: `total` is the block aggregate
+            created += merged; m = alive;
+            int *t = cur; cur = nxt; nxt = t;
+            passes++;
+        }
+    } else if (i == 0) {
+        for (int a = 0; a < 3; ++a) { bt.lo[a] = tlo[a]; bt.hi[a] = thi[a]; }
+    }
+    __syncthreads();
+    CollapseItem *cur = items_a, *nxt = items_b;
+    if (i == 0) cur[0].bin_node = 0;
+    __syncthreads();
+    int m = error ? 0 : 1, depth = 0;
+    uint32_t level_start = 0, tris_done = 0;
+    while (m > 0) {
+        if (m > SMALL_N) { error = 2; break; }
+        int ni = 0, nt = 0, io = 0, to = 0, itot = 0, ttot = 0;
+        if (i < m) collapse_pick(bt, cur[i].bin_node, max_leaf, outs[i], ni, nt);
+        Scan32(tmp.s32).ExclusiveSum(ni, io, itot);
+        __syncthreads();
+        Scan32(tmp.s32).ExclusiveSum(nt, to, ttot);
+        const uint32_t next_start = level_start + (uint32_t) m;
+        if (i < m) collapse_emit(bt, cur[i].bin_node, outs[i], max_leaf, next_start + (uint32_t) io, tris_done + (uint32_t) to,
+                                 nodes + (size_t) (level_start + i) * B2_NODE_UINT4, nxt, io, perm);
+        __syncthreads();
+        level_start = next_start; tris_done += (uint32_t) ttot;
+        CollapseItem *t = cur; cur = nxt; nxt = t;
+        m = itot;
+        depth++;
+    }
+    if (i == 0) { info->n_nodes = (int) level_start; info->depth = depth; info->passes = passes; info->tris_done = (int) tris_done; info->error = error; }
+}
+// Morton keys with the centroid bounds read on the device (k_tri_bounds left them in cb as ordered uints)
+__global__ void k_morton_dev(int n, const float *__restrict__ tlo, const float *__restrict__ thi, const uint32_t *__restrict__ cb, uint64_t *keys, int *vals) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) { keys[i] = morton63(&tlo[3 * i], &thi[3 * i], cmin, cinv); vals[i] = i; }
+    if (i >= n) return;
+    float cmn[3], cmx[3];
+    for (int a = 0; a < 3; ++a) { cmn[a] = ord2f(cb[a]); cmx[a] = ord2f(cb[3 + a]); }
+    const float3 cmin = make_float3(cmn[0], cmn[1], cmn[2]);
+    const float3 cinv = make_float3(__fdiv_rn(2097152.0f, fmaxf(__fsub_rn(cmx[0], cmn[0]), 1e-30f)), __fdiv_rn(2097152.0f, fmaxf(__fsub_rn(cmx[1], cmn[1]), 1e-30f)),
+                                    __fdiv_rn(2097152.0f, fmaxf(__fsub_rn(cmx[2], cmn[2]), 1e-30f)));
+    keys[i] = morton63(&tlo[3 * i], &thi[3 * i], cmin, cinv); vals[i] = i;
 }
 __global__ void k_karras(BinTree bt) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -183,15 +257,8 @@ int b2_build_bvh_device(const BuildTri *d_in, int n, float pad, int max_leaf, in
     uint32_t cb_init[6] = { 0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u };
     B2_CUDA(cudaMemcpyAsync(cb.p, cb_init, sizeof(cb_init), cudaMemcpyHostToDevice, st));
     k_tri_bounds<<<blocks_for(n, T), T, 0, st>>>(d_in, n, pad, tlo.p, thi.p, cb.p);
-    uint32_t cb_h[6];
-    B2_CUDA(cudaMemcpyAsync(cb_h, cb.p, sizeof(cb_h), cudaMemcpyDeviceToHost, st));
-    B2_CUDA(cudaStreamSynchronize(st));
-    float cmn[3], cmx[3];
-    for (int a = 0; a < 3; ++a) { cmn[a] = ord2f(cb_h[a]); cmx[a] = ord2f(cb_h[3 + a]); }
-    float3 cmin = make_float3(cmn[0], cmn[1], cmn[2]);
-    float3 cinv = make_float3(2097152.0f / fmaxf(cmx[0] - cmn[0], 1e-30f), 2097152.0f / fmaxf(cmx[1] - cmn[1], 1e-30f), 2097152.0f / fmaxf(cmx[2] - cmn[2], 1e-30f));
     B2_TRY(keys.alloc(n)); B2_TRY(skeys.alloc(n)); B2_TRY(vals.alloc(n)); B2_TRY(sorted.alloc(n));
-    k_morton<<<blocks_for(n, T), T, 0, st>>>(n, tlo.p, thi.p, cmin, cinv, keys.p, vals.p);
+    k_morton_dev<<<blocks_for(n, T), T, 0, st>>>(n, tlo.p, thi.p, cb.p, keys.p, vals.p);      // centroid bounds stay on the device: no host read here
     size_t tmp_bytes = 0;
     B2_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys.p, skeys.p, vals.p, sorted.p, n, 0, 63, st));
     B2_TRY(tmp.alloc(tmp_bytes));
@@ -202,6 +269,39 @@ int b2_build_bvh_device(const BuildTri *d_in, int n, float pad, int max_leaf, in
     B2_TRY(lo.alloc(6 * (size_t) n)); B2_TRY(hi.alloc(6 * (size_t) n));
     int ploc_passes = 0;
     BinTree bt{ n, skeys.p, sorted.p, left.p, right.p, nullptr, nullptr, nullptr, nullptr, lo.p, hi.p, nullptr, nullptr };
+    const bool small = n <= SMALL_N && (builder != B2_BUILDER_LBVH || n < 2);
+    if (small) {
+        // one CTA runs every PLOC pass and every collapse level (k_build_small); one host read for the whole build
+        B2_TRY(count.alloc(2 * (size_t) n)); B2_TRY(cid_a.alloc(n)); B2_TRY(cid_b.alloc(n)); B2_TRY(nn.alloc(n));
+        bt.count = count.p;
+        B2_TRY(perm.alloc(n));
+        const size_t node_cap = (size_t) n + 1;
+        B2_TRY(nodes_tmp.alloc(node_cap * B2_NODE_UINT4));
+        B2_TRY(items_a.alloc(node_cap)); B2_TRY(items_b.alloc(node_cap)); B2_TRY(outs.alloc(node_cap));
+        ArenaBuf<SmallBuildInfo> info;
+        B2_TRY(info.alloc(1));
+        k_build_small<<<1, SMALL_N, 0, st>>>(bt, tlo.p, thi.p, ploc_radius, max_leaf, cid_a.p, cid_b.p, nn.p, items_a.p, items_b.p, outs.p, nodes_tmp.p, perm.p, info.p);
+        B2_CUDA(cudaGetLastError());
+        SmallBuildInfo hi_;
+        B2_CUDA(cudaMemcpyAsync(&hi_, info.p, sizeof(hi_), cudaMemcpyDeviceToHost, st));
+        B2_CUDA(cudaStreamSynchronize(st));
+        if (hi_.error) { b2_set_error("small BVH build failed (internal error %d)", hi_.error); return B2_ERR_STATE; }
+        if (hi_.tris_done != n) { b2_set_error("BVH collapse placed %d of %d triangles (internal error)", hi_.tris_done, n); return B2_ERR_STATE; }
+        if (hi_.depth + 2 > B2_STACK_CAP) { b2_set_error("BVH depth %d exceeds the traversal stack (%d)", hi_.depth, B2_STACK_CAP); return B2_ERR_STATE; }
+        const size_t n_nodes = (size_t) hi_.n_nodes;
+        B2_TRY(out.nodes.alloc(n_nodes * B2_NODE_UINT4));
+        B2_CUDA(cudaMemcpyAsync(out.nodes.p, nodes_tmp.p, n_nodes * B2_NODE_UINT4 * sizeof(uint4), cudaMemcpyDeviceToDevice, st));
+        B2_TRY(out.tri.alloc(3 * (size_t) n)); B2_TRY(out.tri_obj.alloc(n));
+        k_pack_tris<<<blocks_for(n, T), T, 0, st>>>(d_in, sorted.p, perm.p, n, out.tri.p, out.tri_obj.p);
+        B2_CUDA(cudaGetLastError());
+        B2_CUDA(cudaEventRecord(ev1, st));
+        B2_CUDA(cudaStreamSynchronize(st));
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, ev0, ev1);
+        cudaEventDestroy(ev0); cudaEventDestroy(ev1);
+        out.n_tris = n; out.n_nodes = (int) n_nodes; out.depth = hi_.depth; out.build_ms = ms; out.build_passes = hi_.passes;
+        return B2_OK;
+    }
     if (n < 2) {
         k_single_leaf_box<<<1, 1, 0, st>>>(bt, tlo.p, thi.p);
     } else if (builder == B2_BUILDER_LBVH) {

@@ -311,3 +311,31 @@ def test_in_process_multi_gpu_entry_point():
         for s in scenes[1:]:
             s.close()
     s0.close()
+
+
+@pytest.mark.parametrize("n", [7, 600, 1024, 1025])
+def test_single_cta_build_of_small_scenes_gives_the_tree_of_the_host_mirror(n):
+    """n <= 1024 triangles: every PLOC pass and collapse level runs in one CTA (k_build_small, csrc/b2_bvh_build.cu); above, one
+    launch set per pass.  Both must be the tree of the sequential host mirror (tests/hostsim): same node count and depth,
+    and the same nodes visited / triangles tested by every ray."""
+    from hostsim_py import HostSim
+    sd = random_soup(n, 100 + n)
+    sc = api.Scene(sd)
+    hs = HostSim(sd)
+    gi, hi = sc.bvh_info(), hs.bvh_info()
+    assert gi["n_nodes"] == hi["n_nodes"] and gi["depth"] == hi["depth"]
+    rng = np.random.default_rng(n)
+    m = 2000
+    org = rng.uniform(-1.2, 1.2, (m, 3)).astype(np.float32)
+    dr = rng.normal(size=(m, 3)).astype(np.float32); dr /= np.linalg.norm(dr, axis=1, keepdims=True)
+    a_id, a_t = sc.closest_hit(org, dr)
+    h_id, h_t, _ = hs.intersect(org, dr, 0)
+    assert np.array_equal(a_id, h_id) and np.array_equal(bits(a_t), bits(h_t))
+    p2 = rng.uniform(-1.2, 1.2, (m, 3)).astype(np.float32)       # the any-hit walk is sequential per ray on both sides: equal trees <=> equal counts
+    sc.intersect_counters()
+    vis = sc.visibility(org, p2, count=True)
+    cnt = sc.intersect_counters()
+    h_vis, _, h_cnt = hs.intersect(org, p2, 1)
+    assert np.array_equal(vis, h_vis)
+    assert cnt["nodes"] == int(h_cnt[0]) and cnt["tris"] == int(h_cnt[1])
+    hs.close(); sc.close()
