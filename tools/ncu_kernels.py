@@ -9,7 +9,7 @@ def g(r, n):
     try: return float(r[h[n]].replace(",", ""))
     except Exception: return float("nan")
 stalls = [n for n in h if n.startswith("smsp__average_warps_issue_stalled_") and n.endswith("_per_issue_active.ratio") and "not_issued" not in n]
-print(f"{'kernel':34s} {'grid':>8s} {'us':>8s} {'rdMB':>7s} {'wrMB':>7s} {'Minst':>7s} {'thr/i':>5s} {'issue%':>6s} {'warps%':>6s} {'regs':>4s}  top stalls")
+print(f"{'kernel':34s} {'grid':>8s} {'ms':>8s} {'rdMB':>7s} {'wrMB':>7s} {'Minst':>7s} {'thr/i':>5s} {'issue%':>6s} {'warps%':>6s} {'regs':>4s}  top stalls")
 for r in rows[i + 2:]:
     name = r[h["Kernel Name"]].replace("void <unnamed>::", "").split("(RenderCtx")[0]
     rd, wr = g(r, "dram__bytes_read.sum"), g(r, "dram__bytes_write.sum")
