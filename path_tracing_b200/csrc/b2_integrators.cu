@@ -105,8 +105,15 @@ __global__ void __launch_bounds__(PT_THREADS) k_pt_nee(RenderCtx c) {
 }
 
 // ---- B2_STRATEGIES_MIS (b2_mis.cuh): one thread per eye sample, its light subpath in local memory ----
+#ifndef B2_MIS_THREADS
+#define B2_MIS_THREADS 128
+#endif
+#ifndef B2_MIS_MIN_BLOCKS
+#define B2_MIS_MIN_BLOCKS 12         // 40 registers: the kernel waits on instruction fetch and local memory, more resident warps hide both (tools/mis_ab.sh:
+#endif                               // Cornell 256x256x16: 1 block 53.5 ms, 5: 52.5, 8: 47.5, 10: 46.8, 12: 45.0; 64 or 256 threads per block: no better)
+constexpr int MIS_THREADS = B2_MIS_THREADS;
 template <bool COUNT>
-__global__ void __launch_bounds__(PT_THREADS) k_bdpt_mis(RenderCtx c, CamFrame cf, int n_items, uint32_t pix0, int s0) {
+__global__ void __launch_bounds__(MIS_THREADS, B2_MIS_MIN_BLOCKS) k_bdpt_mis(RenderCtx c, CamFrame cf, int n_items, uint32_t pix0, int s0) {
     extern __shared__ uint2 s_stack[];
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
     TravCounters tc{ 0u, 0u };
@@ -228,8 +235,8 @@ int set_limits(int bvh_depth) {
     B2_CUDA(cudaFuncSetAttribute(k_pt_extend<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
     B2_CUDA(cudaFuncSetAttribute(k_pt_nee<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
     B2_CUDA(cudaFuncSetAttribute(k_pt_nee<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
-    B2_CUDA(cudaFuncSetAttribute(k_bdpt_mis<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
-    B2_CUDA(cudaFuncSetAttribute(k_bdpt_mis<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
+    B2_CUDA(cudaFuncSetAttribute(k_bdpt_mis<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) stack_bytes(MIS_THREADS, bvh_depth)));
+    B2_CUDA(cudaFuncSetAttribute(k_bdpt_mis<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) stack_bytes(MIS_THREADS, bvh_depth)));
     B2_CUDA(cudaFuncSetAttribute(k_ppm_eye<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
     B2_CUDA(cudaFuncSetAttribute(k_ppm_eye<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
     B2_CUDA(cudaFuncSetAttribute(k_ppm_photons<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sb));
@@ -378,14 +385,14 @@ int b2_render_mis_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws, c
     B2_CUDA(cudaEventRecord(ev0, st));
     B2_CUDA(cudaMemsetAsync(ws.film.p, 0, sizeof(float) * film_floats, st));
     B2_CUDA(cudaMemsetAsync(ws.counters.p, 0, sizeof(unsigned long long) * B2_CNT_N, st));
-    const size_t sb = stack_bytes(PT_THREADS, bvh_depth);
+    const size_t sb = stack_bytes(MIS_THREADS, bvh_depth);
     const CamFrame cf = cam_frame(c.cdx, c.cdy);
     const long long batch = p.max_batch_paths > 0 ? p.max_batch_paths : (1ll << 22);
     for (long long w0 = 0; w0 < total && sc.n_lights > 0; w0 += batch) {
         const int n = (int) std::min<long long>(batch, total - w0);
         const uint32_t pix0 = (uint32_t) (w0 % npix); const int s0 = (int) (w0 / npix);
-        if (count) k_bdpt_mis<true><<<blocks_for(n, PT_THREADS), PT_THREADS, sb, st>>>(c, cf, n, pix0, s0);
-        else k_bdpt_mis<false><<<blocks_for(n, PT_THREADS), PT_THREADS, sb, st>>>(c, cf, n, pix0, s0);
+        if (count) k_bdpt_mis<true><<<blocks_for(n, MIS_THREADS), MIS_THREADS, sb, st>>>(c, cf, n, pix0, s0);
+        else k_bdpt_mis<false><<<blocks_for(n, MIS_THREADS), MIS_THREADS, sb, st>>>(c, cf, n, pix0, s0);
         n_launches++; n_batches++;
     }
     B2_CUDA(cudaGetLastError());
