@@ -372,7 +372,9 @@ int b2_render_mis_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws, c
     int n_my = 0;
     for (long long s = p.sample_offset; s < p.spp; s += stride) n_my++;
     const long long total = (long long) npix * n_my;
-    if (p.eye_depth > 64 || p.light_depth > 65) { b2_set_error("B2_STRATEGIES_MIS supports eye_depth <= 64 and light_depth <= 65"); return B2_ERR_INVALID; }
+    if (p.eye_depth > B2_MIS_MAXV || p.light_depth - 1 > B2_MIS_MAXV) {          // a subpath stores at most B2_MIS_MAXV vertices, delta ones included
+        b2_set_error("B2_STRATEGIES_MIS supports eye_depth <= %d and light_depth <= %d", B2_MIS_MAXV, B2_MIS_MAXV + 1); return B2_ERR_INVALID;
+    }
     B2_TRY(ws.film.ensure(film_floats));
     if (!ws.ints.p) B2_TRY(ws.ints.alloc(8));
     if (!ws.counters.p) B2_TRY(ws.counters.alloc(B2_CNT_N));

@@ -31,7 +31,9 @@
 #include "b2_strategies.cuh"
 
 #define B2_RNG_MIS_LIGHT 6u
+#ifndef B2_MIS_MAXV
 #define B2_MIS_MAXV 24                   /* stored vertices per subpath, delta ones included */
+#endif
 
 struct MisVtx { float3 pos, n, wo, beta; Mat mtl; float pdf_fwd, pdf_rev; int delta, nd; };   // nd = non-delta vertices up to and including this one
 

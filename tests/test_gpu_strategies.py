@@ -135,4 +135,6 @@ def test_mis_mode_equals_its_host_compilation_and_shards(tmp_path):
     whole, _ = sc.render_bdpt(strategies=api.STRATEGIES_MIS, spl=1, film_mode=api.FILM_SUM, **kw)
     parts = [sc.render_bdpt(strategies=api.STRATEGIES_MIS, spl=1, film_mode=api.FILM_SUM, sample_offset=g, sample_stride=2, **kw)[0] for g in range(2)]
     assert np.allclose(parts[0] + parts[1], whole, rtol=1e-4, atol=1e-5)
+    with pytest.raises(RuntimeError, match="eye_depth"):                  # a subpath stores at most 24 vertices
+        sc.render_bdpt(width=8, height=8, spp=1, eye_depth=25, light_depth=4, strategies=api.STRATEGIES_MIS)
     hs.close(); sc.close()
