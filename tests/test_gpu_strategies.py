@@ -138,3 +138,24 @@ def test_mis_mode_equals_its_host_compilation_and_shards(tmp_path):
     with pytest.raises(RuntimeError, match="eye_depth"):                  # a subpath stores at most 24 vertices
         sc.render_bdpt(width=8, height=8, spp=1, eye_depth=25, light_depth=4, strategies=api.STRATEGIES_MIS)
     hs.close(); sc.close()
+
+
+def test_pt_cli_strategies_flag_selects_the_mis_mode(tmp_path):
+    """`pt_cli --mode bdpt --strategies mis` == `render_bdpt(strategies=STRATEGIES_MIS)` on the same scene text and seed."""
+    import subprocess
+    import __graft_entry__ as g
+    sd = box_scene(tmp_path)
+    scene_txt = tmp_path / "box.txt"; out = tmp_path / "o.ppm"
+    r = subprocess.run([g.CLI, "--input", str(scene_txt), "--output", str(out), "--mode", "bdpt", "--strategies", "mis", "--spp", "16",
+                        "--eye-depth", "3", "--light-depth", "4", "--width", "48", "--height", "48"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    b = open(out, "rb").read()
+    hdr = b"P6\n48 48\n255\n"
+    assert b.startswith(hdr)
+    img = np.frombuffer(b[len(hdr):], np.uint8).reshape(48, 48, 3)
+    sc = api.Scene(sd)
+    film, _ = sc.render_bdpt(width=48, height=48, spp=16, spl=8, eye_depth=3, light_depth=4, seed=1, strategies=api.STRATEGIES_MIS)
+    assert (np.abs(img.astype(int) - api.film_to_rgb8(film).astype(int)) <= 1).mean() > 0.995 and img.mean() > 5
+    r = subprocess.run([g.CLI, "--input", str(scene_txt), "--strategies", "veach"], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 2 and "unknown --strategies" in r.stderr
+    sc.close()
