@@ -32,6 +32,9 @@ def _worker(rank, world, port, out_path, integrator=0):
     c = CFG
 
     def render(off, stride):
+        if integrator == 4:                                     # B2_STRATEGIES_MIS: eye samples AND their light subpaths shard by sample index (csrc/b2_mis.cuh)
+            return hs.render_strategies(4, c["W"], c["H"], spp=c["spp"], eye_depth=c["depth"], light_depth=c["depth"] + 1, seed=c["seed"],
+                                        sample_offset=off, sample_stride=stride, film_mode=1)[0]
         if integrator == 1:                                     # the pt mode shards its samples the same way (csrc/b2_integrators.cu)
             return hs.render_other(1, c["W"], c["H"], spp=c["spp"], eye_depth=c["depth"], seed=c["seed"], sample_offset=off, sample_stride=stride, film_mode=1)[0]
         film, _ = hs.render(c["W"], c["H"], c["spp"], c["spl"], c["depth"], c["depth"], seed=c["seed"], sample_offset=off,
@@ -80,6 +83,21 @@ def test_sharded_pt_render_equals_the_single_process_film(tmp_path):
     assert got.shape == want.shape and want.mean() > 0
     assert np.allclose(got.mean(axis=(0, 1)), want.mean(axis=(0, 1)), rtol=2e-3)
     assert (np.abs(got - want).max(axis=2) <= 1e-3 * want.mean()).mean() >= 0.99
+
+
+def test_sharded_mis_render_equals_the_single_process_film(tmp_path):
+    """The t = 1 splats of a shard land in pixels of every other shard's samples: the film reduce has to be a SUM of raw films."""
+    from hostsim_py import build, HostSim
+    from path_tracing_b200.scene import reference_scene
+    build()
+    out = str(tmp_path / "film_mis.npy")
+    mp.spawn(_worker, args=(2, _free_port(), out, 4), nprocs=2, join=True)
+    got = np.load(out)
+    hs = HostSim(reference_scene("cornell")); c = CFG
+    want, _ = hs.render_strategies(4, c["W"], c["H"], spp=c["spp"], eye_depth=c["depth"], light_depth=c["depth"] + 1, seed=c["seed"])
+    hs.close()
+    assert got.shape == want.shape and want.mean() > 0
+    assert np.allclose(got, want, rtol=1e-4, atol=1e-5 * want.mean())
 
 
 def test_shard_plan():
