@@ -204,17 +204,24 @@ void b2_parsed_scene_free(B2ParsedScene *p);
 
 /* ---- OBJ / MTL meshes (north_star: tiny_obj_loader surface).  The reference vendors include/tiny_obj_loader.h (v2.0.0)
  * but has no call site and no OBJ -> Triangle adapter; this is that adapter (semantics in csrc/b2_obj.cpp, SURVEY.md
- * appendix D): faces -> Triangle objects in file order, Kd * map_Kd texel baked per triangle into Material.base_color,
- * Pr -> roughness, Pm -> metallic, Ni -> eta for transparent illum models, triangles binned into spatial `G` groups. */
+ * appendix D): the file is read by tinyobj::ObjReader::ParseFromFile (tiny_obj_loader.h:546, compiled from where the
+ * header lies into csrc/b2_tinyobj.cpp), faces -> Triangle objects in file order, Kd * map_Kd texel baked per triangle
+ * into Material.base_color, Pr -> roughness, Pm -> metallic, Ni -> eta for transparent illum models, triangles binned
+ * into spatial `G` groups. */
+#define B2_OBJ_READER_AUTO    0  /* tinyobjloader when the library was built with it (b2_obj_has_tinyobj()), else the own reader */
+#define B2_OBJ_READER_OWN     1  /* the repo's own small OBJ / MTL reader (pinned against tinyobjloader in tests/test_obj.py) */
+#define B2_OBJ_READER_TINYOBJ 2  /* tinyobjloader, error if it was not compiled in */
 typedef struct B2ObjOptions {
     int32_t first_obj_id;     /* obj_id of the first face */
     int32_t first_group;      /* `G` key of the first spatial group; the mesh uses first_group .. first_group + grid*grid - 1 */
-    int32_t group_grid;       /* g: triangles are binned into g x g groups over the x-z extent; 0 = round(sqrt(sqrt(n) / 4)) */
+    int32_t group_grid;       /* g: triangles are binned into g x g groups over the x-z extent; 0 = round(cbrt(n / 2)), <= 256 */
     float   default_color[3]; /* faces without a usemtl material */
     float   default_roughness;
-    int32_t reserved[4];
+    int32_t reader;           /* B2_OBJ_READER_* */
+    int32_t reserved[3];
 } B2ObjOptions;
 void b2_obj_default_options(B2ObjOptions *opt);
+int b2_obj_has_tinyobj(void); /* 1 if libb2pt.so was built with the reference's vendored tiny_obj_loader.h */
 /* Triangles + materials of one OBJ file (camera, lights, spheres of the result are empty). */
 int b2_load_obj(const char *obj_path, const B2ObjOptions *opt, B2ParsedScene **out);
 /* The reference grammar plus one directive, `O <path.obj>` (path relative to the scene file): the mesh is spliced in at

@@ -59,7 +59,7 @@ class ParsedScene(C.Structure):
 # every symbol include/b2pt.h declares (tests check that the built library exports all of them)
 class ObjOptions(C.Structure):
     _fields_ = [("first_obj_id", C.c_int32), ("first_group", C.c_int32), ("group_grid", C.c_int32),
-                ("default_color", C.c_float * 3), ("default_roughness", C.c_float), ("reserved", C.c_int32 * 4)]
+                ("default_color", C.c_float * 3), ("default_roughness", C.c_float), ("reader", C.c_int32), ("reserved", C.c_int32 * 3)]
 
 
 PARSE_OBJ_DIRECTIVE = 1
@@ -69,7 +69,7 @@ SYMBOLS = [
     "b2_scene_destroy", "b2_intersect", "b2_intersect_device", "b2_intersect_counters", "b2_render_bdpt",
     "b2_render_bdpt_device", "b2_render_bdpt_multi", "b2_light_pool", "b2_bsdf_evaluate", "b2_bsdf_pdf", "b2_bsdf_sample", "b2_mis_weight",
     "b2_philox", "b2_parse_scene_file", "b2_parsed_scene_free", "b2_film_to_rgb8", "b2_write_image",
-    "b2_obj_default_options", "b2_load_obj", "b2_parse_scene_file_ex", "b2_render_bdpt_progressive", "b2_frame_rms",
+    "b2_obj_default_options", "b2_obj_has_tinyobj", "b2_load_obj", "b2_parse_scene_file_ex", "b2_render_bdpt_progressive", "b2_frame_rms",
 ]
 
 _lib = None

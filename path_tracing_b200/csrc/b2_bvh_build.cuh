@@ -256,13 +256,14 @@ B2_HD void collapse_emit(const BinTree &bt, int X, const CollapseOut &in, int ma
         }
         ebits[a] = e; scale[a] = u2f(e << 23);
     }
-    uint32_t imask = 0, meta[8], q[6][8];
+    uint32_t imask = 0, vmask = 0, q[6][8];
     int n_int = 0, tri_off = 0;
     for (int s = 0; s < 8; ++s) {
-        meta[s] = 0;
-        for (int a = 0; a < 6; ++a) q[a][s] = 0;
         int k = kid_at[s];
-        if (k < 0) continue;
+        if (k < 0) {                                 // empty slot: an inverted box (lo 255, hi 0) that no ray can hit
+            for (int a = 0; a < 3; ++a) { q[a][s] = 255u; q[3 + a][s] = 0u; }
+            continue;
+        }
         int nd = in.kids[k];
         for (int a = 0; a < 3; ++a) {
             float ql = floorf((bt.lo[3 * nd + a] - nlo[a]) / scale[a]);
@@ -276,10 +277,9 @@ B2_HD void collapse_emit(const BinTree &bt, int X, const CollapseOut &in, int ma
         int c = bin_count(bt, nd);
         if (c > max_leaf) {
             imask |= 1u << s;
-            meta[s] = (B2_META_INTERNAL << 5) | (uint32_t) s;
             n_int++;
         } else {
-            meta[s] = ((uint32_t) c << 5) | (uint32_t) tri_off;
+            vmask |= ((1u << c) - 1u) << (3 * s);    // leaf slot s owns bits 3s .. 3s+2; its triangles sit compactly in slot order
             int lv[3];
             bin_leaves(bt, nd, lv);
             for (int j = 0; j < c; ++j) perm[tri_base + tri_off + j] = lv[j];
@@ -290,7 +290,7 @@ B2_HD void collapse_emit(const BinTree &bt, int X, const CollapseOut &in, int ma
     for (int s = 0; s < 8; ++s)
         if (imask & (1u << s)) next_items[next_local_base + popc32(imask & ((1u << s) - 1u))].bin_node = in.kids[kid_at[s]];
     node_out[0] = make_uint4(f2u(nlo[0]), f2u(nlo[1]), f2u(nlo[2]), ebits[0] | (ebits[1] << 8) | (ebits[2] << 16) | (imask << 24));
-    node_out[1] = make_uint4(child_base, tri_base, pack4(meta), pack4(meta + 4));
+    node_out[1] = make_uint4(child_base, tri_base, vmask, 0u);
     node_out[2] = make_uint4(pack4(q[0]), pack4(q[0] + 4), pack4(q[1]), pack4(q[1] + 4));
     node_out[3] = make_uint4(pack4(q[2]), pack4(q[2] + 4), pack4(q[3]), pack4(q[3] + 4));
     node_out[4] = make_uint4(pack4(q[4]), pack4(q[4] + 4), pack4(q[5]), pack4(q[5] + 4));

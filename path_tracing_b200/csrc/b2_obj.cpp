@@ -1,20 +1,24 @@
 // b2_obj.cpp -- Wavefront OBJ / MTL -> the reference's object model (Triangle + Material + `G` groups), host only.
 //
 // The reference vendors tinyobjloader v2.0.0 (include/tiny_obj_loader.h) but never calls it (src/tiny_obj_loader.cpp
-// is its only mention), so there is no adapter to mirror: this file defines one on top of an
-// own, small OBJ/MTL reader -- third-party sources are not copied into this tree.  The reader is cross-checked against
-// the reference's vendored loader in tests/test_obj.py (golden vectors generated by oracle/obj_ref.cpp, which compiles
-// tiny_obj_loader.h from /root/reference where that exists).
+// is its only mention), so there is no adapter to mirror: this file defines one.  The file is READ
+// by the reference's vendored loader -- tinyobj::ObjReader::ParseFromFile (tiny_obj_loader.h:546), compiled from where the
+// header lies into b2_tinyobj.cpp -- whenever that header was there at build time (B2_OBJ_READER_AUTO / _TINYOBJ).  A
+// small own reader (own_read below) stays as the fallback for builds without the header and as B2_OBJ_READER_OWN; it is
+// pinned against the loader face for face and material for material on the fixtures AND on the 1 M-triangle C3 mesh
+// (tests/test_obj.py).  Both fill the same ObjMesh (b2_obj_mesh.hpp); everything below the readers is shared.
 //
 // Adapter semantics (all new; chosen so that the UNMODIFIED CPU oracle renders the same scene):
 //   * every face becomes Triangle objects in file order, obj_id = running counter; polygons with n > 3 vertices are
-//     fanned (v0, v_i, v_i+1)  [tinyobj splits quads along the shorter diagonal: feed triangles when that matters]
+//     triangulated by the reader (tinyobj: its own triangulation; own reader: fan (v0, v_i, v_i+1))
 //   * Material{base_color, roughness, metallic, eta}: base_color = Kd * texel(map_Kd at the triangle's centroid uv)
-//     (nearest texel, v flipped; baked per triangle: the reference Material has no texture slot), roughness = Pr, or
-//     sqrt(2 / (Ns + 2)) clamped to [0, 1] when the MTL has no Pr, metallic = Pm, eta = Ni if illum in {4, 6, 7} or
+//     (nearest texel, v flipped; baked per triangle: the reference Material has no texture slot); roughness = Pr when
+//     Pr > 0 or no Ns was given, else sqrt(2 / (Ns + 2)) clamped to [0, 1] (tinyobj's material_t cannot tell an absent
+//     Pr from `Pr 0`: both are 0, and an absent Ns is its default 1); metallic = Pm; eta = Ni if illum in {4, 6, 7} or
 //     d < 1, else 0 (opaque)
-//   * triangles are binned into a g x g grid of spatial `G` groups over the mesh's x-z extent (g*g ~ sqrt(n) / 4), so
-//     that the reference's own group-AABB cull (cpu_bdpt.cpp:43-44) keeps the brute-force oracle usable on big meshes
+//   * triangles are binned into a g x g grid of spatial `G` groups over the mesh's x-z extent, g = cbrt(n / 2): the
+//     reference's own group-AABB cull (cpu_bdpt.cpp:43-44) then costs g*g box tests + ~g/2 groups of n/(g*g) triangles
+//     per ray, which that g minimises -- it is what keeps the brute-force CPU oracle usable on big meshes
 //   * textures: binary PPM (P6, maxval <= 255) and PFM (PF); anything else is an error, not a silent white
 #include <cmath>
 #include <cstdio>
@@ -24,20 +28,14 @@
 #include <unordered_map>
 #include <vector>
 #include "../../include/b2pt.h"
+#include "b2_obj_mesh.hpp"
 
 void b2_set_error(const char *fmt, ...);
 
 namespace {
 
 struct Tex { int w = 0, h = 0; std::vector<float> rgb; };
-struct Mtl {
-    std::string name, map_kd;
-    float kd[3] = { 0.0f, 0.0f, 0.0f };      // like tinyobj's material_t: zero until a Kd line sets it
-    float pr = -1.0f, pm = 0.0f, ni = 1.0f, ns = -1.0f, d = 1.0f;
-    int illum = 0;
-    bool has_kd = false;
-    int tex = -1;
-};
+typedef ObjMtl Mtl;
 
 bool read_file(const std::string &path, std::string &out) {
     FILE *f = fopen(path.c_str(), "rb");
@@ -145,7 +143,7 @@ bool load_mtl(const std::string &path, std::vector<Mtl> &mtls, std::unordered_ma
             cur->kd[0] = cur->kd[1] = cur->kd[2] = 0.0f;     // tinyobj: material_t starts zeroed
             by_name[cur->name] = (int) mtls.size() - 1;
         } else if (cur) {
-            if (key == "Kd") { cur->has_kd = parse_f(a, le, cur->kd[0]) && parse_f(a, le, cur->kd[1]) && parse_f(a, le, cur->kd[2]); }
+            if (key == "Kd") { parse_f(a, le, cur->kd[0]) && parse_f(a, le, cur->kd[1]) && parse_f(a, le, cur->kd[2]); }
             else if (key == "Pr") parse_f(a, le, cur->pr);
             else if (key == "Pm") parse_f(a, le, cur->pm);
             else if (key == "Ni") parse_f(a, le, cur->ni);
@@ -179,19 +177,21 @@ struct MatHash {
 
 }  // namespace
 
-// Appends the mesh to the vectors (so the scene-file parser can splice an `O file.obj` directive into a scene).
-bool b2_obj_append(const std::string &obj_path, const B2ObjOptions &opt, std::vector<B2Tri> &tris, std::vector<B2Material> &mats,
-                   int &obj_id, int &next_group) {
+#ifndef B2_HAVE_TINYOBJ        // built without the loader's header (no /root/reference at build time): own reader only
+bool b2_tinyobj_available() { return false; }
+bool b2_tinyobj_read(const std::string &, ObjMesh &, std::string &err) { err = "tinyobjloader was not compiled into this libb2pt.so"; return false; }
+#endif
+
+namespace {
+// The own reader: v / vt / f / usemtl / mtllib, every index form (v, v/vt, v/vt/vn, v//vn, negative), polygons fanned.
+bool own_read(const std::string &obj_path, ObjMesh &out) {
     std::string s;
     if (!read_file(obj_path, s)) { b2_set_error("cannot open OBJ file: %s", obj_path.c_str()); return false; }
     const std::string base = dir_of(obj_path);
-    std::vector<float> pos, uv;
-    std::vector<Mtl> mtls;
+    std::vector<float> &pos = out.pos, &uv = out.uv;
+    std::vector<Mtl> &mtls = out.mtls;
     std::unordered_map<std::string, int> by_name;
-    std::vector<Tex> texs;
-    std::unordered_map<std::string, int> tex_by_name;
-    struct Face { int v[3]; int t[3]; int m; };
-    std::vector<Face> faces;
+    std::vector<ObjFace> &faces = out.faces;
     int cur_m = -1;
     std::vector<long> fv, ft;
     const char *p = s.data(), *e = p + s.size();
@@ -231,7 +231,7 @@ bool b2_obj_append(const std::string &obj_path, const B2ObjOptions &opt, std::ve
             }
             if (fv.size() < 3) { b2_set_error("%s:%zu: face with fewer than 3 vertices", obj_path.c_str(), line_no); return false; }
             for (size_t k = 1; k + 1 < fv.size(); ++k)
-                faces.push_back(Face{ { (int) fv[0], (int) fv[k], (int) fv[k + 1] }, { (int) ft[0], (int) ft[k], (int) ft[k + 1] }, cur_m });
+                faces.push_back(ObjFace{ { (int) fv[0], (int) fv[k], (int) fv[k + 1] }, { (int) ft[0], (int) ft[k], (int) ft[k + 1] }, cur_m });
         } else if (le - q > 7 && memcmp(q, "usemtl", 6) == 0 && is_sp(q[6])) {
             const char *a = skip_sp(q + 6, le), *b = le; while (b > a && is_sp(b[-1])) --b;
             auto it = by_name.find(std::string(a, b));
@@ -242,6 +242,29 @@ bool b2_obj_append(const std::string &obj_path, const B2ObjOptions &opt, std::ve
         }
         p = le < e ? le + 1 : e;
     }
+    return true;
+}
+}  // namespace
+
+// Appends the mesh to the vectors (so the scene-file parser can splice an `O file.obj` directive into a scene).
+bool b2_obj_append(const std::string &obj_path, const B2ObjOptions &opt, std::vector<B2Tri> &tris, std::vector<B2Material> &mats,
+                   int &obj_id, int &next_group) {
+    ObjMesh mesh;
+    const int reader = opt.reader;
+    if (reader < B2_OBJ_READER_AUTO || reader > B2_OBJ_READER_TINYOBJ) { b2_set_error("unknown OBJ reader %d", reader); return false; }
+    if (reader == B2_OBJ_READER_TINYOBJ || (reader == B2_OBJ_READER_AUTO && b2_tinyobj_available())) {
+        FILE *probe = fopen(obj_path.c_str(), "rb");
+        if (!probe) { b2_set_error("cannot open OBJ file: %s", obj_path.c_str()); return false; }
+        fclose(probe);
+        std::string err;
+        if (!b2_tinyobj_read(obj_path, mesh, err)) { b2_set_error("tinyobj: %s (%s)", err.c_str(), obj_path.c_str()); return false; }
+    } else if (!own_read(obj_path, mesh)) return false;
+    const std::string base = dir_of(obj_path);
+    std::vector<float> &pos = mesh.pos, &uv = mesh.uv;
+    std::vector<Mtl> &mtls = mesh.mtls;
+    std::vector<ObjFace> &faces = mesh.faces;
+    std::vector<Tex> texs;
+    std::unordered_map<std::string, int> tex_by_name;
     for (Mtl &m : mtls)
         if (!m.map_kd.empty()) {
             auto it = tex_by_name.find(m.map_kd);
@@ -254,7 +277,7 @@ bool b2_obj_append(const std::string &obj_path, const B2ObjOptions &opt, std::ve
         }
     // spatial groups over the x-z extent
     const size_t n = faces.size();
-    int g = opt.group_grid > 0 ? opt.group_grid : (int) std::lround(std::sqrt(std::sqrt((double) n) / 4.0));
+    int g = opt.group_grid > 0 ? opt.group_grid : (int) std::lround(std::cbrt((double) n / 2.0));
     g = g < 1 ? 1 : (g > 256 ? 256 : g);
     float mn[3] = { 1e30f, 1e30f, 1e30f }, mx[3] = { -1e30f, -1e30f, -1e30f };
     for (size_t i = 0; i < pos.size(); ++i) { const int a = (int) (i % 3); mn[a] = std::fmin(mn[a], pos[i]); mx[a] = std::fmax(mx[a], pos[i]); }
@@ -268,7 +291,7 @@ bool b2_obj_append(const std::string &obj_path, const B2ObjOptions &opt, std::ve
     const int group0 = next_group;
     tris.reserve(tris.size() + n);
     for (size_t i = 0; i < n; ++i) {
-        const Face &f = faces[i];
+        const ObjFace &f = faces[i];
         B2Tri t; memset(&t, 0, sizeof(t));
         memcpy(t.v0, &pos[3 * (size_t) f.v[0]], 12); memcpy(t.v1, &pos[3 * (size_t) f.v[1]], 12); memcpy(t.v2, &pos[3 * (size_t) f.v[2]], 12);
         MatKey k;
@@ -280,7 +303,7 @@ bool b2_obj_append(const std::string &obj_path, const B2ObjOptions &opt, std::ve
                 const float v = (uv[2 * (size_t) f.t[0] + 1] + uv[2 * (size_t) f.t[1] + 1] + uv[2 * (size_t) f.t[2] + 1]) / 3.0f;
                 sample_tex(texs[(size_t) m.tex], u, v, tx);
             }
-            float rough = m.pr >= 0.0f ? m.pr : (m.ns >= 0.0f ? std::sqrt(2.0f / (m.ns + 2.0f)) : 1.0f);
+            float rough = (m.pr > 0.0f || m.ns == 1.0f) ? m.pr : std::sqrt(2.0f / (m.ns + 2.0f));
             rough = rough < 0.0f ? 0.0f : (rough > 1.0f ? 1.0f : rough);
             const bool transparent = m.illum == 4 || m.illum == 6 || m.illum == 7 || m.d < 1.0f;
             k = MatKey{ { m.kd[0] * tx[0], m.kd[1] * tx[1], m.kd[2] * tx[2], rough, m.pm, transparent ? m.ni : 0.0f } };
@@ -323,6 +346,8 @@ extern "C" void b2_obj_default_options(B2ObjOptions *opt) {
     opt->default_color[0] = opt->default_color[1] = opt->default_color[2] = 0.8f;
     opt->default_roughness = 1.0f;
 }
+
+extern "C" int b2_obj_has_tinyobj(void) { return b2_tinyobj_available() ? 1 : 0; }
 
 extern "C" int b2_load_obj(const char *obj_path, const B2ObjOptions *opt, B2ParsedScene **out) {
     if (!obj_path || !out) { b2_set_error("NULL argument"); return B2_ERR_INVALID; }

@@ -101,6 +101,10 @@ __global__ void __launch_bounds__(Q_THREADS) k_intersect(DevScene sc, const floa
 #ifndef B2_QUERY_POOL
 #define B2_QUERY_POOL 1
 #endif
+__device__ __forceinline__ int nth_bit(uint32_t bits, int j) {          // position of the (j+1)-th set bit (j is small)
+    for (; j > 0; --j) bits &= bits - 1u;
+    return __ffs((int) bits) - 1;
+}
 template <bool COUNT>
 __global__ void __launch_bounds__(Q_THREADS) k_closest_pooled(DevScene sc, const float *__restrict__ org, const float *__restrict__ dir, size_t n,
                                                               int32_t *__restrict__ prim_id, float *__restrict__ t_out, unsigned long long *counters) {
@@ -124,9 +128,9 @@ __global__ void __launch_bounds__(Q_THREADS) k_closest_pooled(DevScene sc, const
             busy = true;
         }
         if (!__any_sync(FULL, busy)) break;
-        uint32_t tribits = 0u, tri_base = 0u;
+        uint32_t tribits = 0u, tri_base = 0u, vmask = 0u;
         bool exhausted = false;
-        if (busy) exhausted = !closest_node_step<COUNT>(sc, ct, stack, blockDim.x, &tc, tribits, tri_base);
+        if (busy) exhausted = !closest_node_step<COUNT>(sc, ct, stack, blockDim.x, &tc, tribits, tri_base, vmask);
         const int cnt = __popc(tribits);
         int incl = cnt;
 #pragma unroll
@@ -142,14 +146,14 @@ __global__ void __launch_bounds__(Q_THREADS) k_closest_pooled(DevScene sc, const
                 for (int step = 16; step >= 1; step >>= 1) { const int v = __shfl_sync(FULL, incl, owner + step - 1); if (v <= k) owner += step; }
                 owner = min(owner, 31);
                 const int o_excl = __shfl_sync(FULL, incl - cnt, owner);
-                const uint32_t o_bits = __shfl_sync(FULL, tribits, owner), o_base = __shfl_sync(FULL, tri_base, owner);
+                const uint32_t o_bits = __shfl_sync(FULL, tribits, owner), o_base = __shfl_sync(FULL, tri_base, owner), o_vmask = __shfl_sync(FULL, vmask, owner);
                 const float3 ro = make_float3(__shfl_sync(FULL, ct.r.o.x, owner), __shfl_sync(FULL, ct.r.o.y, owner), __shfl_sync(FULL, ct.r.o.z, owner));
                 const float3 rd = make_float3(__shfl_sync(FULL, ct.r.d.x, owner), __shfl_sync(FULL, ct.r.d.y, owner), __shfl_sync(FULL, ct.r.d.z, owner));
                 const float o_tmax = __shfl_sync(FULL, ct.best.t, owner);
                 unsigned long long key = ~0ull;
                 int ti = 0;
                 if (k < total) {
-                    ti = (int) o_base + (int) __fns(o_bits, 0u, k - o_excl + 1);
+                    ti = tri_of_bit(o_base, o_vmask, nth_bit(o_bits, k - o_excl));
                     const float4 a = sc.tri[3 * ti], b = sc.tri[3 * ti + 1], c = sc.tri[3 * ti + 2];
                     if (COUNT) tc.tris++;
                     float tt;

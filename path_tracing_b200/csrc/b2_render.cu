@@ -115,20 +115,25 @@ __global__ void __launch_bounds__(EXT_THREADS) k_extend(RenderCtx c, int n_items
 // Connection stage.  Work item = (group of 32 eye-vertex records) x (slice of the active pool, whole chunks);
 // persistent warps claim items from a global cursor.  The pool is sliced only when there are too few eye vertices to
 // fill the machine (late waves), so that the serial latency of a nearly empty wave stays short.  No block-level
-// synchronisation.  Per item a warp runs ONE loop that picks, warp-uniformly, the next of four phases:
+// synchronisation.  Per item a warp runs ONE loop that picks, warp-uniformly, the next of four phases; three per-warp
+// queues in shared memory decouple them, so that each phase runs at (nearly) full lane occupancy:
 //   weight   : >= 32 visible pairs queued: MIS weight, clamp, per-owner sums in shared memory (connect_weight)
-//   pre-test : the pair stack runs low and pool chunks remain: every lane tests ITS eye vertex against CONN_CHUNK pool
+//   prepare  : fewer than 32 READY rays and >= 32 pairs stacked (or the pool slice is exhausted): 32 pairs at a time run
+//              connect_prepare (both BSDFs, black skip, shadow ray, contribution without the MIS weight); survivors are
+//              appended to the ready queue (ray + contribution, 44 B each)
+//   pre-test : fewer than 32 pairs stacked and pool chunks remain: every lane tests ITS eye vertex against CONN_CHUNK pool
 //              records (warp-uniform addresses, fully unrolled: 2 broadcast loads + ~16 FP instructions per pair), one
 //              bit per record; survivors go on the PAIR stack (owner lane, pool index), pool vertex by pool vertex
-//   refill   : >= B2_REFILL_MIN lanes have no shadow ray: they pop pairs and run connect_prepare (BSDFs, black skip,
-//              shadow ray, contribution without the MIS weight); the ray stays in the lane's registers
-//   trace    : one any-hit step (wide node + its leaf triangles) for every lane holding a ray; an occluded ray frees
-//              its lane, a visible one is queued for the weight phase
-// so a lane whose ray is decided gets the next pair while the others keep walking (occluded rays end after a few
-// steps, visible ones walk the whole segment; with prepare -> trace -> weight done per 32 pairs ncu showed 13 of 32
-// lanes active in the node tests of the 1 M-triangle scene).  One film atomicAdd per eye vertex and channel per item.
+//   trace    : every idle lane first takes a ready ray (7 shared-memory loads), then one any-hit step (wide node + its
+//              leaf triangles) for every lane holding a ray; an occluded ray frees its lane, a visible one is queued
+//              for the weight phase
+// so a lane whose ray is decided gets the next ray in the very next step while the others keep walking (occluded rays
+// end after a few steps, visible ones walk the whole segment).  Round 1 refilled lanes by running connect_prepare on the
+// idle lanes only once >= 20 of them were idle: ncu on the 1 M-triangle scene showed 21 of 32 lanes active in the node
+// tests and 20 in the BSDFs (profiles/r02_connect_summary.md).  One film atomicAdd per eye vertex and channel per item.
 constexpr int CONN_LOW = 32;          // pre-test another chunk while fewer pairs than this are stacked
 constexpr int CONN_MQ = 64;           // visible-pair queue: < 32 left + 32 new per trace step
+constexpr int CONN_RQ = 64;           // ready-ray queue: < 32 left + 32 new per prepare round
 #ifndef B2_FAST_SHADOW_TRI
 #define B2_FAST_SHADOW_TRI 1          // contracted Moeller-Trumbore for the shadow rays of the connection stage (b2_isect.cuh)
 #endif
@@ -139,14 +144,19 @@ constexpr int CONN_MQ = 64;           // visible-pair queue: < 32 left + 32 new 
 #define B2_CONN_POOL_MIN_TRIS 2048    // scenes with at least this many triangles run the trace phase with the leaf triangles of the
 #endif                                // whole warp pooled (C3 spl 8: 882 -> 820 ms); below it the per-lane loop of any_step wins
                                       // (C2, 48 triangles, 1.5 triangle tests per ray: connect stage 2.94 ms vs 3.51 ms pooled)
-#ifndef B2_REFILL_MIN
-#define B2_REFILL_MIN 20              // idle lanes that trigger a refill (connect_prepare then runs at >= this occupancy)
-#endif
 struct ConnSmem {
     uint32_t pair[CONN_LOW + 32 * CONN_CHUNK];
+    float rq_ox[CONN_RQ], rq_oy[CONN_RQ], rq_oz[CONN_RQ], rq_dx[CONN_RQ], rq_dy[CONN_RQ], rq_dz[CONN_RQ], rq_tmax[CONN_RQ];
+    float rq_px[CONN_RQ], rq_py[CONN_RQ], rq_pz[CONN_RQ]; uint32_t rq_e[CONN_RQ];
     float mq_px[CONN_MQ], mq_py[CONN_MQ], mq_pz[CONN_MQ]; uint32_t mq_e[CONN_MQ];
     float acc[3][32];
 };
+// position of the (j+1)-th set bit of a non-empty mask with more than j bits (j is small: a lane has 0.5 candidate
+// triangles per step on average; the generic __fns costs ~25 instructions whatever j is)
+__device__ __forceinline__ int nth_bit(uint32_t bits, int j) {
+    for (; j > 0; --j) bits &= bits - 1u;
+    return __ffs((int) bits) - 1;
+}
 template <bool COUNT, bool POOL>
 __global__ void __launch_bounds__(CONN_THREADS, CONN_BLOCKS_PER_SM) k_connect(RenderCtx c) {
     extern __shared__ uint2 s_stack[];                    // CONN_THREADS x stack depth
@@ -186,14 +196,15 @@ __global__ void __launch_bounds__(CONN_THREADS, CONN_BLOCKS_PER_SM) k_connect(Re
         if (valid) { const float4 f0 = c.cv[B2_CV_F4 * q]; my_pos = mk3(f0); my_pixel = __float_as_uint(f0.w) >> 8; my_n = mk3(c.cv[B2_CV_F4 * q + 1]); }
         Q.acc[0][lane] = 0.0f; Q.acc[1][lane] = 0.0f; Q.acc[2][lane] = 0.0f;
         __syncwarp();
-        int n_buf = 0, n_mq = 0, ch = ch_begin;            // warp-uniform
+        int n_buf = 0, n_rq = 0, n_mq = 0, ch = ch_begin;  // warp-uniform
         bool busy = false;                                 // this lane holds a shadow ray: tv, pc, e
         AnyTrav tv; float3 pc = mk3(0, 0, 0); uint32_t e = 0u;
+        tv.r.o = tv.r.d = mk3(0, 0, 0); tv.tmax = 0.0f;
 
         for (;;) {
             const uint32_t busy_m = __ballot_sync(0xffffffffu, busy);
-            const int n_idle = 32 - __popc(busy_m);
-            if (n_mq >= 32 || (n_mq > 0 && busy_m == 0u && n_buf == 0 && ch >= ch_end)) {
+            const bool pairs_done = ch >= ch_end;
+            if (n_mq >= 32 || (n_mq > 0 && busy_m == 0u && n_rq == 0 && n_buf == 0 && pairs_done)) {
                 // ---- weight: top min(32, n_mq) visible pairs ----
                 const int count = min(32, n_mq);
                 if (lane < count) {
@@ -209,7 +220,28 @@ __global__ void __launch_bounds__(CONN_THREADS, CONN_BLOCKS_PER_SM) k_connect(Re
                 }
                 n_mq -= count;
                 __syncwarp();
-            } else if (n_buf < CONN_LOW && ch < ch_end) {
+            } else if (n_rq < 32 && (n_buf >= 32 || (n_buf > 0 && pairs_done))) {
+                // ---- prepare: the top min(32, n_buf) pairs become ready shadow rays ----
+                const int count = min(32, n_buf);
+                bool ok = false;
+                ShadowRay sr; float3 ppc = mk3(0, 0, 0); uint32_t pe = 0u;
+                sr.o = sr.d = mk3(0, 0, 0); sr.tmax = 0.0f;
+                if (lane < count) {
+                    pe = Q.pair[n_buf - 1 - lane];
+                    const EyeVtx ev = load_cv(c.cv, q0 + (int) (pe >> 27));
+                    ok = connect_prepare(c, ev, (int) (pe & 0x7ffffffu), sr, ppc);
+                }
+                n_buf -= count;
+                const uint32_t okm = __ballot_sync(0xffffffffu, ok);
+                if (ok) {
+                    const int k = n_rq + __popc(okm & lt);
+                    Q.rq_ox[k] = sr.o.x; Q.rq_oy[k] = sr.o.y; Q.rq_oz[k] = sr.o.z; Q.rq_dx[k] = sr.d.x; Q.rq_dy[k] = sr.d.y; Q.rq_dz[k] = sr.d.z;
+                    Q.rq_tmax[k] = sr.tmax; Q.rq_px[k] = ppc.x; Q.rq_py[k] = ppc.y; Q.rq_pz[k] = ppc.z; Q.rq_e[k] = pe;
+                    n_shadow++;
+                }
+                n_rq += __popc(okm);
+                __syncwarp();
+            } else if (n_rq < 32 && n_buf < CONN_LOW && !pairs_done) {
                 // ---- pre-test one chunk of pool records ----
                 const float4 *__restrict__ rec = pre + (size_t) B2_PRE_F4 * CONN_CHUNK * ch;
                 ++ch;
@@ -238,30 +270,26 @@ __global__ void __launch_bounds__(CONN_THREADS, CONN_BLOCKS_PER_SM) k_connect(Re
                     }
                     __syncwarp();
                 }
-            } else if (n_buf > 0 && (n_idle >= B2_REFILL_MIN || busy_m == 0u)) {
-                // ---- refill: idle lanes pop pairs and prepare their shadow rays ----
-                const int rank = __popc(~busy_m & lt);
-                if (!busy && rank < n_buf) {
-                    e = Q.pair[n_buf - 1 - rank];
-                    const EyeVtx ev = load_cv(c.cv, q0 + (int) (e >> 27));
-                    ShadowRay sr;
-                    if (connect_prepare(c, ev, (int) (e & 0x7ffffffu), sr, pc)) {
-                        n_shadow++;
-                        any_init(tv, c.sc, sr.o, sr.d, sr.tmax);
+            } else if (busy_m != 0u || n_rq > 0) {
+                // ---- trace: idle lanes take a ready ray, then one step per lane that holds a ray ----
+                if (n_rq > 0 && busy_m != 0xffffffffu) {
+                    const int rank = __popc(~busy_m & lt);
+                    if (!busy && rank < n_rq) {
+                        const int k = n_rq - 1 - rank;
+                        e = Q.rq_e[k]; pc = mk3(Q.rq_px[k], Q.rq_py[k], Q.rq_pz[k]);
+                        any_init(tv, c.sc, mk3(Q.rq_ox[k], Q.rq_oy[k], Q.rq_oz[k]), mk3(Q.rq_dx[k], Q.rq_dy[k], Q.rq_dz[k]), Q.rq_tmax[k]);
                         busy = true;
                     }
+                    n_rq -= min(32 - __popc(busy_m), n_rq);
+                    __syncwarp();
                 }
-                n_buf -= min(n_idle, n_buf);
-                __syncwarp();
-            } else if (busy_m != 0u) {
-                // ---- trace: one step per lane that holds a ray ----
                 bool visible = false;
               if (POOL) {
                 // node tests per lane; the leaf triangles of the whole warp are numbered with a prefix sum and tested 32 at a
                 // time by whichever lanes are free (per-lane triangle loops ran at ~4 active lanes, profiles/r01_v11_summary.md)
-                uint32_t tribits = 0u, tri_base = 0u;
+                uint32_t tribits = 0u, tri_base = 0u, vmask = 0u;
                 bool exhausted = false;
-                if (busy) exhausted = !any_node_step<COUNT>(c.sc, tv, stack, CONN_THREADS, &tc, tribits, tri_base);
+                if (busy) exhausted = !any_node_step<COUNT>(c.sc, tv, stack, CONN_THREADS, &tc, tribits, tri_base, vmask);
                 const int cnt = __popc(tribits);
                 int incl = cnt;
 #pragma unroll
@@ -276,19 +304,24 @@ __global__ void __launch_bounds__(CONN_THREADS, CONN_BLOCKS_PER_SM) k_connect(Re
                     owner = min(owner, 31);
                     const int o_excl = __shfl_sync(0xffffffffu, incl - cnt, owner);
                     const uint32_t o_bits = __shfl_sync(0xffffffffu, tribits, owner), o_base = __shfl_sync(0xffffffffu, tri_base, owner);
+                    const uint32_t o_vmask = __shfl_sync(0xffffffffu, vmask, owner);
                     const float3 ro = mk3(__shfl_sync(0xffffffffu, tv.r.o.x, owner), __shfl_sync(0xffffffffu, tv.r.o.y, owner), __shfl_sync(0xffffffffu, tv.r.o.z, owner));
                     const float3 rd = mk3(__shfl_sync(0xffffffffu, tv.r.d.x, owner), __shfl_sync(0xffffffffu, tv.r.d.y, owner), __shfl_sync(0xffffffffu, tv.r.d.z, owner));
                     const float o_tmax = __shfl_sync(0xffffffffu, tv.tmax, owner);
                     bool hit = false;
                     if (k < total) {
-                        const int ti = (int) o_base + (int) __fns(o_bits, 0u, k - o_excl + 1);
+                        const int ti = tri_of_bit(o_base, o_vmask, nth_bit(o_bits, k - o_excl));
                         const float4 b = c.sc.tri[3 * ti + 1];
                         if (!(f2u(b.w) & B2_MAT_TRANSPARENT)) {
                             const float4 a = c.sc.tri[3 * ti], cc = c.sc.tri[3 * ti + 2];
                             if (COUNT) tc.tris++;
                             float tt;
-                            hit = (B2_FAST_SHADOW_TRI != 0 ? tri_test_fast(ro, rd, mk3(a), mk3(b), mk3(cc), 1e-3f, o_tmax) : tri_test(ro, rd, mk3(a), mk3(b), mk3(cc), 1e-3f, o_tmax, tt)) &&
-                                  group_pass(c.sc, (int) f2u(cc.w), ro, rd, 1e-3f, o_tmax);
+                            if (B2_FAST_SHADOW_TRI != 0) {
+                                if (tri_test_fast(ro, rd, mk3(a), mk3(b), mk3(cc), 1e-3f, o_tmax)) {
+                                    const RayPre rp = ray_pre(ro, rd);
+                                    hit = group_pass_fast(c.sc, (int) f2u(cc.w), rp, 1e-3f, o_tmax);
+                                }
+                            } else hit = tri_test(ro, rd, mk3(a), mk3(b), mk3(cc), 1e-3f, o_tmax, tt) && group_pass(c.sc, (int) f2u(cc.w), ro, rd, 1e-3f, o_tmax);
                         }
                     }
                     // every lane learns which owners were hit: OR of (1 << owner) over the lanes that hit
@@ -317,7 +350,7 @@ __global__ void __launch_bounds__(CONN_THREADS, CONN_BLOCKS_PER_SM) k_connect(Re
                     n_mq += __popc(vm);
                     __syncwarp();
                 }
-            } else break;                                  // nothing stacked, nothing in flight, no chunk left, queue empty
+            } else break;                                  // nothing stacked, nothing ready, nothing in flight, no chunk left, queue empty
         }
         if (valid) {
             const float3 r = mk3(Q.acc[0][lane], Q.acc[1][lane], Q.acc[2][lane]);

@@ -21,18 +21,20 @@ B2_HD int prim_index(int prim) { return prim & 0x0fffffff; }
 #define B2_MAT_TRANSPARENT 0x80000000u   // material eta > 0: never blocks shadow rays (cpu_bdpt.cpp:102)
 
 // 8-wide node, 80 bytes.  w0 = {origin.x, origin.y, origin.z, ex | ey<<8 | ez<<16 | imask<<24}
-//   w1 = {child_base, tri_base, meta[0..3], meta[4..7]}
+//   w1 = {child_base, tri_base, vmask, 0}
 //   w2 = {qlo_x[0..3], qlo_x[4..7], qlo_y[0..3], qlo_y[4..7]}
 //   w3 = {qlo_z[0..3], qlo_z[4..7], qhi_x[0..3], qhi_x[4..7]}
 //   w4 = {qhi_y[0..3], qhi_y[4..7], qhi_z[0..3], qhi_z[4..7]}
-// child box = origin + q * 2^(e-127) per axis (e = biased IEEE exponent byte).  meta[i]: 0 = empty slot;
-// (7<<5)|slot = internal child (its node index = child_base + popc(imask & ((1<<slot)-1)));
-// (cnt<<5)|off, cnt in 1..3 = leaf with triangles [tri_base+off, tri_base+off+cnt).
+// child box of slot s = origin + q[s] * 2^(e-127) per axis (e = biased IEEE exponent byte).  An empty slot has the
+// inverted box qlo = 255, qhi = 0 (never hit).  imask bit s: slot s is an internal child, its node index is
+// child_base + popc(imask & ((1<<s)-1)).  vmask bits 3s .. 3s+2: leaf slot s holds 1..3 triangles (the low cnt bits
+// of its field are set); the node's triangles sit compactly from tri_base in slot order, so the triangle of vmask
+// bit b is tri_base + popc(vmask & ((1<<b)-1)).  The traversal gets one hit bit per slot from eight branch-free slab
+// tests and derives both child lists from it with a handful of logic operations (b2_bvh.cuh: node_test).
 // Slot s sits towards the (s&1 ? +x : -x, s&2 ? +y : -y, s&4 ? +z : -z) corner of the node, so a ray with
 // octant bits `oct` (bit set where dir < 0) meets slots in roughly increasing (s ^ oct).
 struct WideNode { uint4 w[5]; };
 #define B2_NODE_UINT4 5
-#define B2_META_INTERNAL 7u
 
 struct DevScene {
     const float4 *tri;      // 3 per triangle
@@ -45,6 +47,7 @@ struct DevScene {
     int n_tris, n_nodes, n_sph, n_lights, n_mats, n_groups;
     float3 scene_min, scene_max;   // union of the group boxes (cpu_bdpt.cpp:181-187)
     int ggx_fix;                   // != 0: materials are marked for the normalised GGX D (mat_mark_fix); 0 in parity mode
+    uint32_t cvt_magic;            // 0x4B000000 = 2^23 as float bits, for the PRMT byte -> float conversion of b2_bvh.cuh (kept a runtime value on purpose)
     int gpu_sem;                   // != 0: intersection semantics of the reference's GPU integrators (pt_cu / ppm_cu through
                                    // geometric.cuh:240-390) instead of cpu_bdpt.cpp's: two-root spheres, opaque shadow rays
 };

@@ -27,6 +27,7 @@ struct B2Scene {
         v.sph = sph.p; v.lights = lights.p; v.mats = mats.p; v.groups = groups.p;
         v.n_tris = bvh.n_tris; v.n_nodes = bvh.n_nodes; v.n_sph = hs.n_sph; v.n_lights = hs.n_lights; v.n_mats = hs.n_mats; v.n_groups = hs.n_groups;
         v.scene_min = hs.scene_min; v.scene_max = hs.scene_max;
+        v.cvt_magic = 0x4B000000u;
         return v;
     }
 };

@@ -26,14 +26,16 @@ class SceneData:
         return cls._from_parsed(pp)
 
     @classmethod
-    def from_obj(cls, path, group_grid=0, first_obj_id=0, first_group=0, default_color=(0.8, 0.8, 0.8), default_roughness=1.0):
-        """Triangles + materials of a Wavefront OBJ (+ MTL, PPM/PFM map_Kd) through b2_load_obj; no camera / lights."""
+    def from_obj(cls, path, group_grid=0, first_obj_id=0, first_group=0, default_color=(0.8, 0.8, 0.8), default_roughness=1.0, reader=0):
+        """Triangles + materials of a Wavefront OBJ (+ MTL, PPM/PFM map_Kd) through b2_load_obj; no camera / lights.
+        reader: 0 = tinyobjloader when compiled in (else the own reader), 1 = own reader, 2 = tinyobjloader or error."""
         L = A.lib()
         o = A.ObjOptions()
         L.b2_obj_default_options(C.byref(o))
         o.group_grid, o.first_obj_id, o.first_group = int(group_grid), int(first_obj_id), int(first_group)
         o.default_color[0], o.default_color[1], o.default_color[2] = [float(x) for x in default_color]
         o.default_roughness = float(default_roughness)
+        o.reader = int(reader)
         pp = C.POINTER(A.ParsedScene)()
         A.check(L.b2_load_obj(str(path).encode(), C.byref(o), C.byref(pp)))
         return cls._from_parsed(pp)

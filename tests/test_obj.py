@@ -1,14 +1,20 @@
-"""OBJ / MTL surface (b2_load_obj, `O` directive): the repo's own reader pinned against the reference's vendored
-tinyobjloader v2.0.0 -- through the committed dump tests/golden/obj/small_tinyobj.txt (made by oracle/obj_ref.cpp, see
-tests/golden/make_obj_golden.sh) and, where oracle/_ref/obj_ref exists, live on a generated 20 k-triangle mesh.
-Host-only: no GPU needed."""
+"""OBJ / MTL surface (b2_load_obj, `O` directive).  The library reads OBJ files through the reference's vendored
+tinyobjloader v2.0.0 (csrc/b2_tinyobj.cpp calls tinyobj::ObjReader::ParseFromFile) whenever it was built with that header,
+and keeps a small own reader for builds without it.  Both readers and the adapter above them are pinned here: against the
+committed dump tests/golden/obj/small_tinyobj.txt (made by oracle/obj_ref.cpp, a separate program around the same loader,
+see tests/golden/make_obj_golden.sh), live against oracle/_ref/obj_ref on a generated 20 k-triangle mesh, and against each
+other on the 1 M-triangle C3 mesh itself (faces, materials, groups bit-identical).  Host-only: no GPU needed."""
 import os
 import subprocess
 import numpy as np
 import pytest
 
-from path_tracing_b200 import gen
+from path_tracing_b200 import gen, _abi as A
 from path_tracing_b200.scene import SceneData
+
+OWN, TINYOBJ = 1, 2
+HAVE_TINYOBJ = bool(A.lib().b2_obj_has_tinyobj())
+READERS = [OWN] + ([TINYOBJ] if HAVE_TINYOBJ else [])
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 FIX = os.path.join(HERE, "golden", "obj")
@@ -80,9 +86,18 @@ def expected_materials(uv, has_uv, mid, mats, rough_of, texdir, default=(0.8, 0.
     return out
 
 
-def test_obj_reader_matches_tinyobj_golden():
+def test_default_reader_is_tinyobj_when_the_reference_header_was_there_at_build_time():
+    if os.path.exists("/root/reference/include/tiny_obj_loader.h"):
+        assert HAVE_TINYOBJ, "libb2pt.so was built without the vendored loader although its header is present"
+    if not HAVE_TINYOBJ:
+        with pytest.raises(RuntimeError, match="not compiled"):
+            SceneData.from_obj(os.path.join(FIX, "small.obj"), reader=TINYOBJ)
+
+
+@pytest.mark.parametrize("reader", READERS)
+def test_obj_reader_matches_tinyobj_golden(reader):
     pos, uv, has_uv, mid, mats = parse_dump(open(os.path.join(FIX, "small_tinyobj.txt")).read())
-    sd = SceneData.from_obj(os.path.join(FIX, "small.obj"), group_grid=1, first_obj_id=5, first_group=7)
+    sd = SceneData.from_obj(os.path.join(FIX, "small.obj"), group_grid=1, first_obj_id=5, first_group=7, reader=reader)
     assert len(sd.tris) == len(pos) == 11
     got = np.stack([sd.tris["v0"], sd.tris["v1"], sd.tris["v2"]], 1)
     assert np.array_equal(got.view(np.uint32), pos.view(np.uint32))          # same faces, same order, same float bits
@@ -116,7 +131,19 @@ def test_generated_mesh_against_live_tinyobj(tmp_path):
     assert np.allclose(gotm, exp, rtol=0, atol=1e-7)
     assert len(sd.lights) == 3 and (sd.width, sd.height) == (1920, 1080)
     g = np.unique(sd.tris["group"])
-    assert g.min() == 0 and len(g) > 4                                            # spatial G groups for the CPU oracle's cull
+    assert g.min() >= 0 and len(g) > 4                                            # spatial G groups for the CPU oracle's cull
+
+
+@pytest.mark.skipif(not HAVE_TINYOBJ, reason="libb2pt.so built without tiny_obj_loader.h")
+def test_own_reader_equals_tinyobj_on_the_c3_mesh(tmp_path):
+    """The 1 M-triangle OBJ of BASELINE config 3 itself, through both readers: same faces in the same order (float bits),
+    same materials, same groups."""
+    gen.write_obj_scene(str(tmp_path), n_tris=1 << 20)
+    a = SceneData.from_obj(str(tmp_path / "mesh.obj"), reader=TINYOBJ)
+    b = SceneData.from_obj(str(tmp_path / "mesh.obj"), reader=OWN)
+    assert len(a.tris) == len(b.tris) > 1_000_000
+    assert a.tris.tobytes() == b.tris.tobytes()
+    assert a.materials.tobytes() == b.materials.tobytes()
 
 
 def test_scene_directive_splices_the_mesh(tmp_path):
@@ -131,16 +158,23 @@ def test_scene_directive_splices_the_mesh(tmp_path):
     assert len(sd.lights) == 1 and (sd.width, sd.height) == (64, 48)
 
 
-def test_polygons_are_fanned_and_errors_are_loud(tmp_path):
+def test_polygons_are_triangulated_and_errors_are_loud(tmp_path):
     (tmp_path / "q.obj").write_text("v 0 0 0\nv 1 0 0\nv 1 1 0\nv 0 1 0\nv -1 0.5 0\nf 1 2 3 4 5\n")
-    sd = SceneData.from_obj(str(tmp_path / "q.obj"))
+    sd = SceneData.from_obj(str(tmp_path / "q.obj"), reader=OWN)                      # own reader: a fan around the first vertex
     assert len(sd.tris) == 3
     assert np.allclose(sd.tris["v0"], [[0, 0, 0]] * 3) and np.allclose(sd.tris["v1"][:, :2], [[1, 0], [1, 1], [0, 1]])
-    with pytest.raises(RuntimeError, match="cannot open OBJ"):
-        SceneData.from_obj(str(tmp_path / "nope.obj"))
+    for reader in READERS:                                                            # any triangulation covers the polygon's area
+        sd = SceneData.from_obj(str(tmp_path / "q.obj"), reader=reader)
+        area = 0.5 * np.linalg.norm(np.cross(sd.tris["v1"] - sd.tris["v0"], sd.tris["v2"] - sd.tris["v0"]), axis=1).sum()
+        assert len(sd.tris) == 3 and abs(area - 1.5) < 1e-6
+        with pytest.raises(RuntimeError, match="cannot open OBJ"):
+            SceneData.from_obj(str(tmp_path / "nope.obj"), reader=reader)
     (tmp_path / "bad.obj").write_text("v 0 0 0\nv 1 0 0\nv 1 1 0\nf 1 2 9\n")
     with pytest.raises(RuntimeError, match="out of range"):
-        SceneData.from_obj(str(tmp_path / "bad.obj"))
+        SceneData.from_obj(str(tmp_path / "bad.obj"), reader=OWN)
+    if HAVE_TINYOBJ:                                                                  # tinyobj reports it in its own words
+        with pytest.raises(RuntimeError, match="tinyobj"):
+            SceneData.from_obj(str(tmp_path / "bad.obj"), reader=TINYOBJ)
     (tmp_path / "t.mtl").write_text("newmtl a\nKd 1 1 1\nmap_Kd t.png\n")
     (tmp_path / "t.png").write_bytes(b"\x89PNG....")
     (tmp_path / "t.obj").write_text("mtllib t.mtl\nv 0 0 0\nv 1 0 0\nv 1 1 0\nvt 0 0\nusemtl a\nf 1/1 2/1 3/1\n")
