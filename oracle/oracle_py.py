@@ -102,8 +102,8 @@ class _Lib:
         self._g("scene_destroy")(h)
 
     def group_bounds(self, h):
-        out = np.zeros((4096, 7), np.float32)
-        n = self._g("group_bounds")(h, out.reshape(-1), 4096)
+        out = np.zeros((65536, 7), np.float32)
+        n = min(self._g("group_bounds")(h, out.reshape(-1), 65536), 65536)
         return out[:n]
 
     def closest_hit(self, h, org, dirs):

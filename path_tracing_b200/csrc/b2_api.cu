@@ -74,6 +74,7 @@ int b2_scene_create(const B2Tri *tris, size_t n_tris, const B2Sphere *spheres, s
     B2_TRY(need_device(device));
     B2Scene *s = new B2Scene;
     s->device = device;
+    if (cudaDeviceGetAttribute(&s->n_sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || s->n_sms <= 0) s->n_sms = 148;   // B200
     const char *err = nullptr;
     if (!flatten_scene(tris, n_tris, spheres, n_spheres, materials, n_materials, lights, n_lights, s->hs, &err)) { b2_set_error("%s", err ? err : "bad scene"); delete s; return B2_ERR_INVALID; }
     int rc = B2_OK;

@@ -38,4 +38,15 @@ struct DevBuf {
     T *release_ptr() { T *q = p; p = nullptr; n = 0; return q; }
 };
 
+// RAII CUDA event: destroyed on every return path (error returns used to leak the timing events of a render)
+struct CudaEvent {
+    cudaEvent_t e = nullptr;
+    CudaEvent() = default;
+    CudaEvent(const CudaEvent &) = delete;
+    CudaEvent &operator=(const CudaEvent &) = delete;
+    ~CudaEvent() { if (e) cudaEventDestroy(e); }
+    cudaError_t create(unsigned flags = cudaEventDefault) { return e ? cudaSuccess : cudaEventCreateWithFlags(&e, flags); }
+    operator cudaEvent_t() const { return e; }
+};
+
 static inline unsigned blocks_for(size_t n, unsigned threads) { return (unsigned) ((n + threads - 1) / threads); }

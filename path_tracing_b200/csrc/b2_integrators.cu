@@ -308,8 +308,8 @@ int b2_render_pt_impl(const DevScene &sc_in, int bvh_depth, RenderWorkspace &ws,
     const bool count = p.count_traversal != 0;
     uint64_t n_launches = 0, n_batches = 0, n_waves = 0;
     unsigned long long eye_samples = 0, closest_host = 0;
-    cudaEvent_t ev0, ev1;
-    B2_CUDA(cudaEventCreate(&ev0)); B2_CUDA(cudaEventCreate(&ev1));
+    CudaEvent ev0, ev1, ev_wave;
+    B2_CUDA(ev0.create()); B2_CUDA(ev1.create()); B2_CUDA(ev_wave.create(cudaEventDisableTiming));
     B2_CUDA(cudaEventRecord(ev0, st));
     B2_CUDA(cudaMemsetAsync(ws.film.p, 0, sizeof(float) * film_floats, st));
     B2_CUDA(cudaMemsetAsync(ws.counters.p, 0, sizeof(unsigned long long) * B2_CNT_N, st));
@@ -334,12 +334,13 @@ int b2_render_pt_impl(const DevScene &sc_in, int bvh_depth, RenderWorkspace &ws,
                 else k_pt_extend<false, false><<<gb, PT_THREADS, sb, st>>>(c, n_live, 0u, 0);
             }
             B2_CUDA(cudaMemcpyAsync(ws.h_ints, c.n_live_next, sizeof(int), cudaMemcpyDeviceToHost, st));
-            const unsigned gn = (unsigned) std::min<long long>(148ll * 16, gb);
+            B2_CUDA(cudaEventRecord(ev_wave, st));                 // the host waits for the wave size only, not for k_pt_nee (b2_render.cu)
+            const unsigned gn = (unsigned) std::min<long long>((long long) sc.n_sms * 16, gb);
             if (count) k_pt_nee<true><<<gn, PT_THREADS, sb, st>>>(c);
             else k_pt_nee<false><<<gn, PT_THREADS, sb, st>>>(c);
             n_launches += 2; n_waves++;
-            B2_CUDA(cudaStreamSynchronize(st));
             B2_CUDA(cudaGetLastError());
+            B2_CUDA(cudaEventSynchronize(ev_wave));
             closest_host += (unsigned long long) n_live;
             n_live = ws.h_ints[0];
             std::swap(c.live, c.live_next);
@@ -357,7 +358,6 @@ int b2_render_pt_impl(const DevScene &sc_in, int bvh_depth, RenderWorkspace &ws,
     float ms = 0.f;
     cudaEventElapsedTime(&ms, ev0, ev1);
     fill_stats(stats, h_cnt, eye_samples, closest_host, n_batches, n_waves, n_launches, ms);
-    cudaEventDestroy(ev0); cudaEventDestroy(ev1);
     return B2_OK;
 }
 
@@ -382,8 +382,8 @@ int b2_render_mis_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws, c
     RenderCtx c; b2_setup_ctx(c, sc, cam, p, ws, 1);
     const bool count = p.count_traversal != 0;
     uint64_t n_launches = 0, n_batches = 0;
-    cudaEvent_t ev0, ev1;
-    B2_CUDA(cudaEventCreate(&ev0)); B2_CUDA(cudaEventCreate(&ev1));
+    CudaEvent ev0, ev1, ev_wave;
+    B2_CUDA(ev0.create()); B2_CUDA(ev1.create()); B2_CUDA(ev_wave.create(cudaEventDisableTiming));
     B2_CUDA(cudaEventRecord(ev0, st));
     B2_CUDA(cudaMemsetAsync(ws.film.p, 0, sizeof(float) * film_floats, st));
     B2_CUDA(cudaMemsetAsync(ws.counters.p, 0, sizeof(unsigned long long) * B2_CNT_N, st));
@@ -409,7 +409,6 @@ int b2_render_mis_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws, c
     float ms = 0.f;
     cudaEventElapsedTime(&ms, ev0, ev1);
     fill_stats(stats, h_cnt, (unsigned long long) total, 0ull, n_batches, n_batches, n_launches, ms);
-    cudaEventDestroy(ev0); cudaEventDestroy(ev1);
     return B2_OK;
 }
 
@@ -442,8 +441,8 @@ int b2_render_ppm_impl(const DevScene &sc_in, int bvh_depth, RenderWorkspace &ws
     pc.n_hp = ws.ints.p + 5;
     const bool count = p.count_traversal != 0;
     uint64_t n_launches = 0;
-    cudaEvent_t ev0, ev1;
-    B2_CUDA(cudaEventCreate(&ev0)); B2_CUDA(cudaEventCreate(&ev1));
+    CudaEvent ev0, ev1, ev_wave;
+    B2_CUDA(ev0.create()); B2_CUDA(ev1.create()); B2_CUDA(ev_wave.create(cudaEventDisableTiming));
     B2_CUDA(cudaEventRecord(ev0, st));
     B2_CUDA(cudaMemsetAsync(ws.counters.p, 0, sizeof(unsigned long long) * B2_CNT_N, st));
     B2_CUDA(cudaMemsetAsync(ws.ints.p, 0, sizeof(int) * 8, st));
@@ -486,6 +485,5 @@ int b2_render_ppm_impl(const DevScene &sc_in, int bvh_depth, RenderWorkspace &ws
     cudaEventElapsedTime(&ms, ev0, ev1);
     fill_stats(stats, h_cnt, (unsigned long long) npix, 0ull, 1, 1, n_launches, ms);
     if (stats) { stats->eye_vertices = (unsigned long long) n_hp; stats->pairs_tested = (unsigned long long) n_photons; }
-    cudaEventDestroy(ev0); cudaEventDestroy(ev1);
     return B2_OK;
 }

@@ -254,9 +254,9 @@ int launch_isect(const DevScene &sc, int bvh_depth, const float *o, const float 
     if (sb > 48 * 1024 && sb > configured) {
         B2_CUDA(cudaFuncSetAttribute(k_intersect<ANY, BRUTE, COUNT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb));
     }
-    // grid: enough blocks to fill 148 SMs x resident CTAs, grid-stride beyond that
+    // grid: enough blocks to fill every SM's resident CTAs, grid-stride beyond that
     const size_t want = (n + Q_THREADS - 1) / Q_THREADS;
-    const unsigned grid = (unsigned) std::min<size_t>(want, (size_t) 148 * 64);
+    const unsigned grid = (unsigned) std::min<size_t>(want, (size_t) (sc.n_sms > 0 ? sc.n_sms : 148) * 64);
     if (!ANY && !BRUTE && B2_QUERY_POOL) {
         if (sb + 2048 > 48 * 1024) B2_CUDA(cudaFuncSetAttribute(k_closest_pooled<COUNT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb));
         k_closest_pooled<COUNT><<<grid, Q_THREADS, sb, st>>>(sc, o, d, n, id, t, cnt);

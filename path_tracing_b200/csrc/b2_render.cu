@@ -601,8 +601,8 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
     const bool count = p.count_traversal != 0;
     uint64_t n_launches = 0, n_batches = 0, n_waves = 0;
     StageTimer tm; tm.on = p.profile_stages != 0; tm.st = st;
-    cudaEvent_t ev0, ev1, ev2;
-    B2_CUDA(cudaEventCreate(&ev0)); B2_CUDA(cudaEventCreate(&ev1)); B2_CUDA(cudaEventCreate(&ev2));
+    CudaEvent ev0, ev1, ev2, ev_wave;
+    B2_CUDA(ev0.create()); B2_CUDA(ev1.create()); B2_CUDA(ev2.create()); B2_CUDA(ev_wave.create(cudaEventDisableTiming));
     B2_CUDA(cudaEventRecord(ev0, st));
     B2_CUDA(cudaMemsetAsync(ws.film.p, 0, sizeof(float) * film_floats, st));
     B2_CUDA(cudaMemsetAsync(ws.counters.p, 0, sizeof(unsigned long long) * B2_CNT_N, st));
@@ -650,24 +650,28 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
                     else k_extend<false, false><<<gb, EXT_THREADS, sb_t, st>>>(c, n_live, 0u, 0);
                 }
                 tm.end();
+                // the size of the next wave is read back BEHIND the extend kernel and AHEAD of the connection stage: the host waits
+                // on this event, not on the stream, so it learns n_live while k_connect still runs and queues the next extend
+                // behind it -- no idle gap between waves (round 1 synchronised the stream here: 128 bubbles per C3 render)
                 B2_CUDA(cudaMemcpyAsync(ws.h_ints, c.n_live_next, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
-                // persistent warps: one CTA wave over the 148 SMs (grid-stride over the work items computed on the device)
-                const unsigned gc = (unsigned) std::min<long long>(148ll * CONN_BLOCKS_PER_SM, std::max<long long>(1, ((long long) n_live * 8 + CONN_THREADS - 1) / CONN_THREADS));
+                B2_CUDA(cudaEventRecord(ev_wave, st));
+                // persistent warps: one CTA wave over the SMs (work items claimed from a cursor on the device)
+                const unsigned gc = (unsigned) std::min<long long>((long long) sc.n_sms * CONN_BLOCKS_PER_SM, std::max<long long>(1, ((long long) n_live * 8 + CONN_THREADS - 1) / CONN_THREADS));
                 tm.begin(StageTimer::CONNECT);
                 if (ref_set) {
                     const bool pool = sc.n_tris >= B2_CONN_POOL_MIN_TRIS;
                     if (pool) { if (count) k_connect<true, true><<<gc, CONN_THREADS, sb_c, st>>>(c); else k_connect<false, true><<<gc, CONN_THREADS, sb_c, st>>>(c); }
                     else { if (count) k_connect<true, false><<<gc, CONN_THREADS, sb_c, st>>>(c); else k_connect<false, false><<<gc, CONN_THREADS, sb_c, st>>>(c); }
                 } else {
-                    const unsigned gn = (unsigned) std::min<long long>(148ll * 8, blocks_for(n_live, EXT_THREADS));
+                    const unsigned gn = (unsigned) std::min<long long>((long long) sc.n_sms * 8, blocks_for(n_live, EXT_THREADS));
                     if (count) k_nee<true><<<gn, EXT_THREADS, sb_t, st>>>(c, w_mix);
                     else k_nee<false><<<gn, EXT_THREADS, sb_t, st>>>(c, w_mix);
                 }
                 tm.end();
                 n_launches += 2; n_waves++;
-                B2_CUDA(cudaStreamSynchronize(st));
                 B2_CUDA(cudaGetLastError());
-                tm.collect();
+                if (tm.on) { B2_CUDA(cudaStreamSynchronize(st)); tm.collect(); }
+                B2_CUDA(cudaEventSynchronize(ev_wave));
                 ws.closest_rays_host += (unsigned long long) n_live;
                 n_live = ws.h_ints[0];
                 eye_vertices += (unsigned long long) ws.h_ints[1];
@@ -705,7 +709,6 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
         stats->ms_primary = tm.ms[StageTimer::PRIMARY]; stats->ms_extend = tm.ms[StageTimer::EXTEND]; stats->ms_connect = tm.ms[StageTimer::CONNECT];
     }
     ws.closest_rays_host = 0;
-    cudaEventDestroy(ev0); cudaEventDestroy(ev1); cudaEventDestroy(ev2);
     return B2_OK;
 }
 

@@ -47,6 +47,7 @@ struct DevScene {
     int n_tris, n_nodes, n_sph, n_lights, n_mats, n_groups;
     float3 scene_min, scene_max;   // union of the group boxes (cpu_bdpt.cpp:181-187)
     int ggx_fix;                   // != 0: materials are marked for the normalised GGX D (mat_mark_fix); 0 in parity mode
+    int n_sms;                     // SMs of the device the scene lives on (host side: sizes the persistent grids)
     uint32_t cvt_magic;            // 0x4B000000 = 2^23 as float bits, for the PRMT byte -> float conversion of b2_bvh.cuh (kept a runtime value on purpose)
     int gpu_sem;                   // != 0: intersection semantics of the reference's GPU integrators (pt_cu / ppm_cu through
                                    // geometric.cuh:240-390) instead of cpu_bdpt.cpp's: two-root spheres, opaque shadow rays

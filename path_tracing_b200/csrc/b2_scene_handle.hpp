@@ -9,6 +9,7 @@
 
 struct B2Scene {
     int device = 0;
+    int n_sms = 148;                      // multiProcessorCount of `device`, read once at scene creation: every persistent grid is sized from it
     HostScene hs;
     DevBuf<BuildTri> d_in;
     DevBuf<float4> sph, lights, mats, groups;
@@ -27,7 +28,7 @@ struct B2Scene {
         v.sph = sph.p; v.lights = lights.p; v.mats = mats.p; v.groups = groups.p;
         v.n_tris = bvh.n_tris; v.n_nodes = bvh.n_nodes; v.n_sph = hs.n_sph; v.n_lights = hs.n_lights; v.n_mats = hs.n_mats; v.n_groups = hs.n_groups;
         v.scene_min = hs.scene_min; v.scene_max = hs.scene_max;
-        v.cvt_magic = 0x4B000000u;
+        v.cvt_magic = 0x4B000000u; v.n_sms = n_sms;
         return v;
     }
 };
