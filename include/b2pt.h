@@ -181,6 +181,16 @@ int b2_frame_rms(const uint8_t *cur_rgb8, const uint8_t *last_rgb8, size_t n, fl
 /* The light-vertex pool the render would use: n_lights*spl*light_depth vertices x 20 floats
  * (pos3 normal3 thr3 mtl6 is_light_source is_parallel source_cutoff pdf_fwd pdf_rev), cpu_bdpt.cpp:202-325. */
 int b2_light_pool(B2Scene *scene, const B2RenderParams *params, float *pool20_host);
+/* The same pool for callers that must not allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Calls no cudaMalloc /
+ * cudaFree / allocating library routine: the scratch b2_light_pool keeps in the scene's workspace (80-byte pool records +
+ * counters) is one file-scope device array of B2_NOALLOC_MAX_POOL_VERTICES records (2.6 MB) that every GPU that loads the
+ * library holds until exit.  d_pool20: DEVICE buffer of n_lights*spl*light_depth x 20 floats (layout as above), caller-owned.
+ * cuda_stream: the caller's stream (the call is asynchronous on it), or NULL = the scene's own stream, blocking.
+ * A pool larger than the maximum is rejected with B2_ERR_INVALID (use b2_light_pool).  Every call shares the array and
+ * clears the part it uses first; calls that overlap on the GPU (other streams, other handles on the device) race on it. */
+#define B2_NOALLOC_MAX_POOL_VERTICES 32768
+int b2_light_pool_device_noalloc(B2Scene *scene, const B2RenderParams *params, float *d_pool20, void *cuda_stream);
 
 /* ---- BSDF / MIS / RNG tables (device kernels over host arrays; parity tests) ---- */
 int b2_bsdf_evaluate(size_t n, const float *mtl6, const float *wo, const float *wi, const float *N, float *out3);

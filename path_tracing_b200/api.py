@@ -16,6 +16,7 @@ from .scene import SceneData
 CLOSEST, ANY, BRUTE_FORCE, COUNT_VISITS = 0, 1, 16, 32
 FILM_MEAN, FILM_SUM = 0, 1
 STRATEGIES_REFERENCE, STRATEGIES_FULL, STRATEGIES_LIGHT_TRACING, STRATEGIES_NEE, STRATEGIES_MIS = 0, 1, 2, 3, 4
+NOALLOC_MAX_POOL_VERTICES = 32768                            # B2_NOALLOC_MAX_POOL_VERTICES
 INTEGRATOR_BDPT, INTEGRATOR_PT, INTEGRATOR_PPM = 0, 1, 2      # main_cli's --mode (src/main_cli.cpp:201-213)
 
 
@@ -148,6 +149,12 @@ class Scene:
         A.check(A.lib().b2_render_bdpt_progressive(self._h, cam.ctypes.data_as(C.c_void_p), C.byref(p), int(passes), A.ptr(film),
                                                    A.ptr(rms) if rms is not None else None, C.cast(cb, C.c_void_p) if cb else None, None, C.byref(st)))
         return film, rms, st.as_dict()
+
+    def light_pool_device_noalloc(self, device_ptr, spl=8, light_depth=4, seed=1, max_delta=0, stream=0):
+        """b2_light_pool_device_noalloc: the pool into a caller-owned DEVICE buffer (int pointer, n_lights*spl*light_depth x 20
+        floats); no allocation inside the library (static device scratch, at most NOALLOC_MAX_POOL_VERTICES vertices)."""
+        p = self._params(1, 1, 1, spl, 1, light_depth, seed, 0, 1, 0, max_delta, 0, False)
+        A.check(A.lib().b2_light_pool_device_noalloc(self._h, C.byref(p), C.c_void_p(int(device_ptr)), C.c_void_p(stream) if stream else None))
 
     def light_pool(self, spl=8, light_depth=4, seed=1, max_delta=0):
         n = len(self.data.lights) * spl * light_depth
