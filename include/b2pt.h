@@ -202,6 +202,11 @@ int b2_mis_weight(size_t n, const float *eye17, const int32_t *n_eye, const int3
                   const float *cam_pos, int32_t max_verts, float *out);
 int b2_philox(size_t n, const uint32_t *ctr4, const uint32_t *key2, uint32_t *out4, float *unit_out4);
 
+/* ---- roofline denominators measured in the run: non-tensor FP32 FMA peak of `device` in TFLOP/s, and the
+ * read bandwidth of a buffer of `bytes` (0 = 32 MiB) that stays resident in L2, in GB/s.  A few milliseconds each. ---- */
+int b2_measure_fp32_peak(int device, float *tflops);
+int b2_measure_l2_bandwidth(int device, size_t bytes, float *gbs);
+
 /* ---- host-side surface kept from the reference (no GPU needed) ---- */
 typedef struct B2ParsedScene {
     size_t n_tris, n_spheres, n_materials, n_lights;

@@ -70,6 +70,7 @@ SYMBOLS = [
     "b2_render_bdpt_device", "b2_render_bdpt_multi", "b2_light_pool", "b2_light_pool_device_noalloc", "b2_bsdf_evaluate", "b2_bsdf_pdf", "b2_bsdf_sample", "b2_mis_weight",
     "b2_philox", "b2_parse_scene_file", "b2_parsed_scene_free", "b2_film_to_rgb8", "b2_write_image",
     "b2_obj_default_options", "b2_obj_has_tinyobj", "b2_load_obj", "b2_parse_scene_file_ex", "b2_render_bdpt_progressive", "b2_frame_rms",
+    "b2_measure_fp32_peak", "b2_measure_l2_bandwidth",
 ]
 
 _lib = None
@@ -119,6 +120,9 @@ def lib():
         L.b2_parse_scene_file_ex.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.POINTER(ParsedScene))]
         L.b2_film_to_rgb8.argtypes = [vp, C.c_int32, C.c_int32, vp]
         L.b2_write_image.argtypes = [C.c_char_p, vp, C.c_int32, C.c_int32]
+        L.b2_measure_fp32_peak.argtypes = [i32, C.POINTER(C.c_float)]
+        L.b2_measure_l2_bandwidth.argtypes = [i32, sz, C.POINTER(C.c_float)]
+        L.b2_obj_has_tinyobj.restype = C.c_int
         _lib = L
     return _lib
 

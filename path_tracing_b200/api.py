@@ -26,6 +26,20 @@ def device_count():
     return n.value
 
 
+def measure_fp32_peak(device=0):
+    """Non-tensor FP32 FMA peak of `device` in TFLOP/s (in-run microbenchmark)."""
+    v = C.c_float(0)
+    A.check(A.lib().b2_measure_fp32_peak(int(device), C.byref(v)))
+    return v.value
+
+
+def measure_l2_bandwidth(device=0, nbytes=0):
+    """Read bandwidth of an L2-resident buffer in GB/s (the roof of traversals whose nodes + triangles fit in L2)."""
+    v = C.c_float(0)
+    A.check(A.lib().b2_measure_l2_bandwidth(int(device), int(nbytes), C.byref(v)))
+    return v.value
+
+
 def _f32(a, shape=None):
     a = np.ascontiguousarray(a, dtype=np.float32)
     return a if shape is None else a.reshape(shape)
