@@ -63,7 +63,7 @@ typedef struct B2BvhInfo {
     uint64_t n_tris, n_nodes, node_bytes, tri_bytes;
     int32_t  depth;
     float    build_ms;      /* device time of the last build (CUDA events) */
-    float    sah_cost;      /* SAH cost of the wide tree (root area normalised) */
+    float    sah_cost;      /* SAH cost of the wide tree over exact boxes, root area normalised: one wide-node test = 1, one triangle test = 0.3 */
     int32_t  build_passes;  /* PLOC clustering passes of the last build */
     int32_t  reserved;
 } B2BvhInfo;

@@ -127,7 +127,7 @@ int b2_scene_bvh_info(const B2Scene *s, B2BvhInfo *info) {
     memset(info, 0, sizeof(*info));
     info->n_tris = (uint64_t) s->bvh.n_tris; info->n_nodes = (uint64_t) s->bvh.n_nodes;
     info->node_bytes = (uint64_t) s->bvh.n_nodes * sizeof(uint4) * B2_NODE_UINT4; info->tri_bytes = (uint64_t) s->bvh.n_tris * 48u;
-    info->depth = s->bvh.depth; info->build_ms = s->bvh.build_ms; info->sah_cost = 0.0f; info->build_passes = s->bvh.build_passes;
+    info->depth = s->bvh.depth; info->build_ms = s->bvh.build_ms; info->sah_cost = s->bvh.sah_cost; info->build_passes = s->bvh.build_passes;
     return B2_OK;
 }
 

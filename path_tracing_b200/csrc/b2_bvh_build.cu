@@ -231,6 +231,21 @@ struct ArenaBuf {
 
 }  // namespace
 
+// SAH cost of the chosen wide tree, root area normalised, in units of one wide-node test (B2_SAH_C_NODE = 1): the root's
+// C_internal of the cost tables (exact boxes).  One 40-byte read.
+static int read_sah_cost(const BinTree &bt, cudaStream_t st, float &out) {
+    out = 0.0f;
+    if (bt.n < 2 || !bt.sah) return B2_OK;
+    float c = 0.f, lo[3], hi[3];
+    B2_CUDA(cudaMemcpyAsync(&c, bt.sah, sizeof(float), cudaMemcpyDeviceToHost, st));
+    B2_CUDA(cudaMemcpyAsync(lo, bt.lo, sizeof(lo), cudaMemcpyDeviceToHost, st));
+    B2_CUDA(cudaMemcpyAsync(hi, bt.hi, sizeof(hi), cudaMemcpyDeviceToHost, st));
+    B2_CUDA(cudaStreamSynchronize(st));
+    const float dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2], a = dx * dy + dy * dz + dz * dx;
+    out = a > 0.0f ? c / a : 0.0f;
+    return B2_OK;
+}
+
 int b2_build_bvh_device(const BuildTri *d_in, int n, float pad, int max_leaf, int builder, int ploc_radius, cudaStream_t st, DeviceBvh &out) {
     out.release();
     if (n <= 0) return B2_OK;
@@ -240,8 +255,8 @@ int b2_build_bvh_device(const BuildTri *d_in, int n, float pad, int max_leaf, in
     const unsigned T = 256;
     size_t sort_bytes = 0;
     B2_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, (uint64_t *) nullptr, (uint64_t *) nullptr, (int *) nullptr, (int *) nullptr, n, 0, 63, st));
-    BuildArena arena;                                    // ~330 B of temporaries per triangle, all live at once
-    B2_TRY(arena.acquire((size_t) 400 * (size_t) n + sort_bytes + ((size_t) 1 << 20)));
+    BuildArena arena;                                    // ~410 B of temporaries per triangle, all live at once
+    B2_TRY(arena.acquire((size_t) 500 * (size_t) n + sort_bytes + ((size_t) 1 << 20)));
     struct ArenaScope { ArenaScope(BuildArena *a) { t_arena = a; } ~ArenaScope() { t_arena = nullptr; } } arena_scope(&arena);
     ArenaBuf<float> tlo, thi, lo, hi;
     ArenaBuf<uint32_t> cb, visit;
@@ -268,7 +283,9 @@ int b2_build_bvh_device(const BuildTri *d_in, int n, float pad, int max_leaf, in
     B2_TRY(left.alloc(n)); B2_TRY(right.alloc(n));
     B2_TRY(lo.alloc(6 * (size_t) n)); B2_TRY(hi.alloc(6 * (size_t) n));
     int ploc_passes = 0;
-    BinTree bt{ n, skeys.p, sorted.p, left.p, right.p, nullptr, nullptr, nullptr, nullptr, lo.p, hi.p, nullptr, nullptr };
+    ArenaBuf<float> sah; ArenaBuf<unsigned char> dec;           // cost tables of the SAH-optimal collapse: 8 floats + 8 bytes per binary node
+    B2_TRY(sah.alloc(16 * (size_t) n)); B2_TRY(dec.alloc(16 * (size_t) n));
+    BinTree bt{ n, skeys.p, sorted.p, left.p, right.p, nullptr, nullptr, nullptr, nullptr, lo.p, hi.p, nullptr, nullptr, sah.p, dec.p, max_leaf };
     const bool small = n <= SMALL_N && (builder != B2_BUILDER_LBVH || n < 2);
     if (small) {
         // one CTA runs every PLOC pass and every collapse level (k_build_small); one host read for the whole build
@@ -300,6 +317,7 @@ int b2_build_bvh_device(const BuildTri *d_in, int n, float pad, int max_leaf, in
         cudaEventElapsedTime(&ms, ev0, ev1);
         cudaEventDestroy(ev0); cudaEventDestroy(ev1);
         out.n_tris = n; out.n_nodes = (int) n_nodes; out.depth = hi_.depth; out.build_ms = ms; out.build_passes = hi_.passes;
+        B2_TRY(read_sah_cost(bt, st, out.sah_cost));
         return B2_OK;
     }
     if (n < 2) {
@@ -389,5 +407,6 @@ int b2_build_bvh_device(const BuildTri *d_in, int n, float pad, int max_leaf, in
     cudaEventElapsedTime(&ms, ev0, ev1);
     cudaEventDestroy(ev0); cudaEventDestroy(ev1);
     out.n_tris = n; out.n_nodes = (int) n_nodes; out.depth = depth; out.build_ms = ms; out.build_passes = ploc_passes;
+    B2_TRY(read_sah_cost(bt, st, out.sah_cost));
     return B2_OK;
 }

@@ -9,6 +9,12 @@
 //                   mutual nearest neighbours merge; repeat until one cluster is left.  Agglomerative, area-driven: the
 //                   tree quality of a surface-area-heuristic build at a few dozen passes over a shrinking array.
 //   LBVH            Karras (HPG 2012) binary radix tree + bottom-up refit: splits by Morton bits only (A/B baseline).
+// The collapse is SAH-optimal for the given binary tree (Ylitie, Karras, Laine 2017, section 3.1): while the binary tree is
+// built bottom-up, every node n gets the table C(n, i), i = 1..7 = the smallest cost of representing its subtree with at most
+// i child slots of a wide node (a slot is a leaf of <= max_leaf triangles, cost area * count * B2_SAH_C_PRIM, or a wide node,
+// cost area * B2_SAH_C_NODE + the best distribution of its two children over 8 slots), plus the decisions that reach it;
+// the level-synchronous collapse then only follows the decisions.  Round 1 opened the largest-area child greedily: on the
+// 1 M-triangle scene the bottom wide nodes held 6.4 of 24 possible triangles (tools/bvh_quality.py, profiles/r02_bvh.md).
 // Every step is deterministic (no atomics decide an ordering), so all GPUs build identical trees.
 #pragma once
 #include "b2_scene.cuh"
@@ -25,7 +31,17 @@ struct BinTree {             // binary radix tree over n sorted triangles: inter
     uint32_t *visit;         // refit arrival counters (internal nodes)
     int *count;              // PLOC: leaves under each node (2n-1 entries; a subtree is NOT a contiguous range of sorted
                              // leaves there); nullptr for the radix tree, whose nodes cover [first, last]
+    float *sah;              // 8 per node: [i] = C(node, i) for i = 1..7, [0] = cost of the node as a wide node (C_internal)
+    unsigned char *dec;      // 8 per node: [1] = 1 if C(node,1) is the leaf, [i] (i = 2..7) = slots given to the left child, 0 = "i-1
+                             // slots are as good"; [0] = slots of the left child when the node becomes a wide node
+    int max_leaf;            // most triangles in a leaf slot (1..3)
 };
+#ifndef B2_SAH_C_NODE
+#define B2_SAH_C_NODE 1.0f   // one wide-node test (80 B, ~260 instructions)
+#endif
+#ifndef B2_SAH_C_PRIM
+#define B2_SAH_C_PRIM 0.3f   // one triangle test (48 B, 40 - 75 instructions)
+#endif
 
 B2_HD void tri_bounds(const BuildTri &t, float pad, float lo[3], float hi[3]) {
     for (int a = 0; a < 3; ++a) {
@@ -49,6 +65,46 @@ B2_HD uint64_t morton63(const float lo[3], const float hi[3], float3 cmin, float
     float fy = fminf(fmaxf((cy - cmin.y) * cinv.y, 0.0f), 2097151.0f);
     float fz = fminf(fmaxf((cz - cmin.z) * cinv.z, 0.0f), 2097151.0f);
     return (expand21((uint32_t) fx) << 2) | (expand21((uint32_t) fy) << 1) | expand21((uint32_t) fz);
+}
+
+B2_HD float bin_area(const BinTree &bt, int node) {
+    float dx = bt.hi[3 * node] - bt.lo[3 * node], dy = bt.hi[3 * node + 1] - bt.lo[3 * node + 1], dz = bt.hi[3 * node + 2] - bt.lo[3 * node + 2];
+    return dx * dy + dy * dz + dz * dx;
+}
+// ---- SAH-optimal collapse: cost tables (bottom-up, fused into the binary-tree construction) ----
+B2_HD float sah_ld(const float *p) {
+#if defined(__CUDA_ARCH__)
+    return __ldcg(p);
+#else
+    return *p;
+#endif
+}
+B2_HD void sah_leaf(const BinTree &bt, int node) {            // a single triangle: one leaf slot whatever the budget
+    if (!bt.sah) return;
+    const float c = bin_area(bt, node) * B2_SAH_C_PRIM;
+    for (int i = 0; i < 8; ++i) { bt.sah[8 * (size_t) node + i] = c; bt.dec[8 * (size_t) node + i] = 0; }
+    bt.dec[8 * (size_t) node + 1] = 1;
+}
+B2_HD void sah_combine(const BinTree &bt, int node, int l, int r, int count) {
+    if (!bt.sah) return;
+    // the children's tables may have been written by other threads of this launch (radix-tree refit): L2 loads, like the boxes
+    float lc[8], rc[8];
+    for (int i = 1; i < 8; ++i) { lc[i] = sah_ld(bt.sah + 8 * (size_t) l + i); rc[i] = sah_ld(bt.sah + 8 * (size_t) r + i); }
+    float *c = bt.sah + 8 * (size_t) node; unsigned char *d = bt.dec + 8 * (size_t) node;
+    const float area = bin_area(bt, node);
+    float dist[9]; unsigned char dk[9];
+    for (int j = 2; j <= 8; ++j) {                               // best distribution of j slots over the two children
+        float best = 3.0e38f; int bk = 1;
+        for (int k = (j - 7 > 1 ? j - 7 : 1); k <= j - 1 && k <= 7; ++k) { const float v = lc[k] + rc[j - k]; if (v < best) { best = v; bk = k; } }
+        dist[j] = best; dk[j] = (unsigned char) bk;
+    }
+    const float c_int = dist[8] + area * B2_SAH_C_NODE;
+    const float c_leaf = count <= bt.max_leaf ? area * (float) count * B2_SAH_C_PRIM : 3.0e38f;
+    c[0] = c_int; d[0] = dk[8];
+    if (c_leaf <= c_int) { c[1] = c_leaf; d[1] = 1; } else { c[1] = c_int; d[1] = 0; }
+    for (int i = 2; i <= 7; ++i) {
+        if (dist[i] < c[i - 1]) { c[i] = dist[i]; d[i] = dk[i]; } else { c[i] = c[i - 1]; d[i] = 0; }
+    }
 }
 
 B2_HD int karras_delta(const uint64_t *keys, int n, int i, int j) {
@@ -89,6 +145,7 @@ B2_HD void refit_from_leaf(const BinTree &bt, const float *tri_lo, const float *
     int src = bt.sorted[j];
     int node = (n - 1) + j;
     for (int a = 0; a < 3; ++a) { bt.lo[3 * node + a] = tri_lo[3 * src + a]; bt.hi[3 * node + a] = tri_hi[3 * src + a]; }
+    sah_leaf(bt, node);
     int p = bt.leaf_parent[j];
     while (p >= 0) {
 #if defined(__CUDA_ARCH__)
@@ -108,6 +165,7 @@ B2_HD void refit_from_leaf(const BinTree &bt, const float *tri_lo, const float *
             bt.lo[3 * p + a] = fminf(l0, l1);
             bt.hi[3 * p + a] = fmaxf(h0, h1);
         }
+        sah_combine(bt, p, L, R, bt.last[p] - bt.first[p] + 1);
         p = bt.parent[p];
     }
 }
@@ -163,46 +221,58 @@ B2_HD void ploc_merge(const BinTree &bt, int l, int r, int node) {
     bt.left[node] = l; bt.right[node] = r;
     for (int a = 0; a < 3; ++a) { bt.lo[3 * node + a] = fminf(bt.lo[3 * l + a], bt.lo[3 * r + a]); bt.hi[3 * node + a] = fmaxf(bt.hi[3 * l + a], bt.hi[3 * r + a]); }
     bt.count[node] = bt.count[l] + bt.count[r];
+    sah_combine(bt, node, l, r, bt.count[node]);
 }
 B2_HD void ploc_leaf(const BinTree &bt, const float *tri_lo, const float *tri_hi, int j) {
     const int src = bt.sorted[j], node = (bt.n - 1) + j;
     for (int a = 0; a < 3; ++a) { bt.lo[3 * node + a] = tri_lo[3 * src + a]; bt.hi[3 * node + a] = tri_hi[3 * src + a]; }
     bt.count[node] = 1;
-}
-B2_HD float bin_area(const BinTree &bt, int node) {
-    float dx = bt.hi[3 * node] - bt.lo[3 * node], dy = bt.hi[3 * node + 1] - bt.lo[3 * node + 1], dz = bt.hi[3 * node + 2] - bt.lo[3 * node + 2];
-    return dx * dy + dy * dz + dz * dx;
+    sah_leaf(bt, node);
 }
 
 B2_HD uint32_t pack4(const uint32_t *b) { return b[0] | (b[1] << 8) | (b[2] << 16) | (b[3] << 24); }
 
 struct CollapseItem { int bin_node; };          // one per wide node of the current level
-struct CollapseOut { int kids[8]; int n_kids; };
+struct CollapseOut { int kids[8]; int n_kids; uint32_t leaf_mask; };      // leaf_mask bit k: kids[k] is a leaf slot
 
-// Pass 1: choose up to 8 children of the wide node rooted at binary node X by repeatedly opening the
-// largest-area child that still holds more than max_leaf triangles.
+// Pass 1: the (up to 8) children of the wide node rooted at binary node X, read off the decisions of the cost tables:
+// X's best split of 8 slots over its two children, then every child either keeps its budget, gives a slot back (a smaller
+// budget is as good) or splits it again, until every part has one slot -- a leaf or the root of a wide node of the next level.
 B2_HD void collapse_pick(const BinTree &bt, int X, int max_leaf, CollapseOut &out, int &n_internal, int &n_tris) {
-    int kids[8], nk = 0;
-    if (bin_count(bt, X) <= max_leaf) { kids[nk++] = X; }      // whole tree is one leaf (n <= max_leaf)
-    else { kids[nk++] = bt.left[X]; kids[nk++] = bt.right[X]; }
-    while (nk < 8) {
-        int best = -1; float best_a = -1.0f;
-        for (int k = 0; k < nk; ++k) {
-            if (bin_count(bt, kids[k]) <= max_leaf) continue;
-            float a = bin_area(bt, kids[k]);
-            if (a > best_a) { best_a = a; best = k; }
+    int kids[8], nk = 0; uint32_t leaf_mask = 0u;
+    if (X >= bt.n - 1 || !bt.sah) {
+        if (X >= bt.n - 1 || bin_count(bt, X) <= max_leaf) { kids[nk] = X; leaf_mask |= 1u << nk; nk++; }      // the whole tree is one leaf
+        else {                                                  // no cost tables (not used by the builders): greedy by area
+            kids[nk++] = bt.left[X]; kids[nk++] = bt.right[X];
+            while (nk < 8) {
+                int best = -1; float best_a = -1.0f;
+                for (int k = 0; k < nk; ++k) { if (bin_count(bt, kids[k]) <= max_leaf) continue; const float a = bin_area(bt, kids[k]); if (a > best_a) { best_a = a; best = k; } }
+                if (best < 0) break;
+                const int nd = kids[best]; kids[best] = bt.left[nd]; kids[nk++] = bt.right[nd];
+            }
+            for (int k = 0; k < nk; ++k) if (bin_count(bt, kids[k]) <= max_leaf) leaf_mask |= 1u << k;
         }
-        if (best < 0) break;
-        int nd = kids[best];
-        kids[best] = bt.left[nd];
-        kids[nk++] = bt.right[nd];
+    } else {
+        int st_node[8], st_budget[8], sp = 0;
+        const int k0 = bt.dec[8 * (size_t) X];
+        st_node[sp] = bt.right[X]; st_budget[sp++] = 8 - k0;
+        st_node[sp] = bt.left[X]; st_budget[sp++] = k0;
+        while (sp > 0) {
+            const int nd = st_node[--sp]; int i = st_budget[sp];
+            if (nd >= bt.n - 1) { kids[nk] = nd; leaf_mask |= 1u << nk; nk++; continue; }
+            const unsigned char *d = bt.dec + 8 * (size_t) nd;
+            while (i >= 2 && d[i] == 0) --i;
+            if (i <= 1) { kids[nk] = nd; if (d[1]) leaf_mask |= 1u << nk; nk++; continue; }
+            st_node[sp] = bt.right[nd]; st_budget[sp++] = i - d[i];
+            st_node[sp] = bt.left[nd]; st_budget[sp++] = d[i];
+        }
     }
     n_internal = 0; n_tris = 0;
     for (int k = 0; k < 8; ++k) {
         out.kids[k] = k < nk ? kids[k] : -1;
-        if (k < nk) { int c = bin_count(bt, kids[k]); if (c > max_leaf) n_internal++; else n_tris += c; }
+        if (k < nk) { if ((leaf_mask >> k) & 1u) n_tris += bin_count(bt, kids[k]); else n_internal++; }
     }
-    out.n_kids = nk;
+    out.n_kids = nk; out.leaf_mask = leaf_mask;
 }
 
 // Pass 2: slot assignment, quantisation, node write-out, next-level work items and the leaf-order permutation.
@@ -275,7 +345,7 @@ B2_HD void collapse_emit(const BinTree &bt, int X, const CollapseOut &in, int ma
             q[3 + a][s] = (uint32_t) fminf(fmaxf(qh, 0.0f), 255.0f);
         }
         int c = bin_count(bt, nd);
-        if (c > max_leaf) {
+        if (!((in.leaf_mask >> k) & 1u)) {
             imask |= 1u << s;
             n_int++;
         } else {

@@ -13,6 +13,7 @@ struct HostBvh {
     std::vector<float4> tri;
     std::vector<int32_t> tri_obj;
     int depth = 0;
+    float sah_cost = 0.0f;      // cost of the chosen wide tree / root area (C_node = 1)
 };
 
 inline void host_build_bvh(const HostScene &hs, int max_leaf, float pad_rel, HostBvh &out, int builder = B2_BUILDER_PLOC, int ploc_radius = 2) {
@@ -38,7 +39,10 @@ inline void host_build_bvh(const HostScene &hs, int max_leaf, float pad_rel, Hos
     std::vector<int> left(n), right(n), parent(n), first(n), last(n), leaf_parent(n, -1), count(2 * (size_t) n, 0);
     std::vector<float> lo(3 * (2 * (size_t) n)), hi(3 * (2 * (size_t) n));
     std::vector<uint32_t> visit(n, 0);
-    BinTree bt{ n, skeys.data(), sorted.data(), left.data(), right.data(), parent.data(), first.data(), last.data(), leaf_parent.data(), lo.data(), hi.data(), visit.data(), nullptr };
+    std::vector<float> sah(16 * (size_t) n); std::vector<unsigned char> dec(16 * (size_t) n);
+    BinTree bt{ n, skeys.data(), sorted.data(), left.data(), right.data(), parent.data(), first.data(), last.data(), leaf_parent.data(), lo.data(), hi.data(), visit.data(), nullptr,
+                sah.data(), dec.data(), max_leaf };
+    out.sah_cost = 0.0f;
     if (n < 2) {
         for (int a = 0; a < 3; ++a) { lo[a] = tlo[a]; hi[a] = thi[a]; }   // node id (n-1)+0 = 0
     } else if (builder == B2_BUILDER_LBVH) {
@@ -65,6 +69,7 @@ inline void host_build_bvh(const HostScene &hs, int max_leaf, float pad_rel, Hos
             cid.swap(nxt);
         }
     }
+    if (n >= 2) out.sah_cost = sah[0] / std::max(bin_area(bt, 0), 1e-30f);
     std::vector<int> perm(n, -1);
     std::vector<CollapseItem> items(1), next;
     items[0].bin_node = 0;     // root: internal node 0 (or the only leaf when n == 1)
