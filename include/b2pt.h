@@ -148,6 +148,8 @@ void b2_scene_destroy(B2Scene *scene);
 #define B2_ANY 1
 #define B2_BRUTE_FORCE 16
 #define B2_COUNT_VISITS 32
+#define B2_FAST_SHADOW 64   /* with B2_ANY: the arithmetic the RENDER's shadow rays use (contracted Moeller-Trumbore, approximate reciprocals,
+                            * csrc/b2_isect.cuh tri_test_fast) instead of the bit-exact test -- exposed so that tests can count where the two differ */
 int b2_intersect(B2Scene *scene, const float *org, const float *dir, size_t n, int mode, int32_t *prim_id, float *t);
 /* Same on device pointers (float3-packed arrays already resident in HBM), asynchronous on `stream` (cudaStream_t). */
 int b2_intersect_device(B2Scene *scene, const float *d_org, const float *d_dir, size_t n, int mode,

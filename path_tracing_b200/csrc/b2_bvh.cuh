@@ -123,7 +123,7 @@ B2_HD void trav_push(TravPos &p, uint32_t hits_p, uint32_t child_base, uint32_t 
 
 template <bool COUNT>
 B2_HD HitRec closest_hit_bvh(const DevScene &sc, float3 ro, float3 rd, uint2 *stack, int sstride, TravCounters *cnt) {
-    HitRec best; best.prim = B2_PRIM_MISS; best.t = B2_T_INF;
+    HitRec best; best.prim = B2_PRIM_MISS; best.t = B2_T_INF; best.cls = 1;
     uint32_t best_order = 0;
     if (sc.n_nodes > 0) {
         const RayPre r = ray_pre(ro, rd);
@@ -141,9 +141,9 @@ B2_HD HitRec closest_hit_bvh(const DevScene &sc, float3 ro, float3 rd, uint2 *st
                 float t;
                 if (tri_test(ro, rd, mk3(a), mk3(b), mk3(c), 1e-4f, best.t, t)) {
                     const uint32_t order = f2u(a.w);
-                    if ((best.prim == B2_PRIM_MISS || closer(t, order, best.t, best_order)) &&
-                        group_pass(sc, (int) f2u(c.w), ro, rd, 1e-4f, B2_T_INF)) {
-                        best.t = t; best.prim = prim_make(B2_KIND_TRI, ti); best_order = order;
+                    const int cls = group_tie_class(sc, (int) f2u(c.w), ro, rd, 1e-4f, t);
+                    if (cls != 0 && (best.prim == B2_PRIM_MISS || closer(t, order, cls, best.t, best_order, best.cls))) {
+                        best.t = t; best.prim = prim_make(B2_KIND_TRI, ti); best_order = order; best.cls = cls;
                     }
                 }
             }
@@ -159,7 +159,7 @@ B2_HD HitRec closest_hit_bvh(const DevScene &sc, float3 ro, float3 rd, uint2 *st
 // lanes of the warp keep walking (k_intersect): same node / triangle arithmetic and acceptance rule as closest_hit_bvh.
 struct ClosestTrav { RayPre r; HitRec best; uint32_t best_order; TravPos p; };
 B2_HD void closest_init(ClosestTrav &t, const DevScene &sc, float3 ro, float3 rd) {
-    t.r = ray_pre(ro, rd); t.best.prim = B2_PRIM_MISS; t.best.t = B2_T_INF; t.best_order = 0u;
+    t.r = ray_pre(ro, rd); t.best.prim = B2_PRIM_MISS; t.best.t = B2_T_INF; t.best.cls = 1; t.best_order = 0u;
     trav_reset(t.p, sc.n_nodes > 0);
 }
 // The node half of a step: pops the next wide node, tests its 8 children, stacks the hit internal ones and returns the hit
@@ -189,9 +189,9 @@ B2_HD bool closest_step(const DevScene &sc, ClosestTrav &t, uint2 *stack, int ss
         float tt;
         if (tri_test(t.r.o, t.r.d, mk3(a), mk3(b), mk3(c), 1e-4f, t.best.t, tt)) {
             const uint32_t order = f2u(a.w);
-            if ((t.best.prim == B2_PRIM_MISS || closer(tt, order, t.best.t, t.best_order)) &&
-                group_pass(sc, (int) f2u(c.w), t.r.o, t.r.d, 1e-4f, B2_T_INF)) {
-                t.best.t = tt; t.best.prim = prim_make(B2_KIND_TRI, ti); t.best_order = order;
+            const int cls = group_tie_class(sc, (int) f2u(c.w), t.r.o, t.r.d, 1e-4f, tt);
+            if (cls != 0 && (t.best.prim == B2_PRIM_MISS || closer(tt, order, cls, t.best.t, t.best_order, t.best.cls))) {
+                t.best.t = tt; t.best.prim = prim_make(B2_KIND_TRI, ti); t.best_order = order; t.best.cls = cls;
             }
         }
     }

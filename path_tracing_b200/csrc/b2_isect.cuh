@@ -93,13 +93,44 @@ B2_HD bool group_pass(const DevScene &sc, int g, float3 ro, float3 rd, float tmi
     return group_slab(ro, rd, mk3(sc.groups[2 * g]), mk3(sc.groups[2 * g + 1]), tmin, tmax);
 }
 
-struct HitRec { int prim; float t; };
+// The reference visits groups in key order and culls group g with intersectAABB(ray, 1e-4, best.t) (cpu_bdpt.cpp:43-44),
+// best.t being the closest hit of the EARLIER groups.  For an order-free traversal that only matters on exact ties: a hit
+// at t in group g loses against an equal-t hit of an earlier group iff that cull rejects g with tMax = t, i.e. iff the hit
+// lies exactly on the near face of g's box (min(exit, t) <= max(entry, 1e-4)).  Class of a candidate hit:
+//   0 = its group's box is missed altogether (tMax = infinity): no hit
+//   1 = "pass": on a tie it behaves like the reference's t <= best.t acceptance -- the later object wins
+//   2 = "fail": its group would be culled behind an equal-t hit of an earlier group -- it loses ties against every pass
+//       hit, and among fail hits the EARLIEST wins (the first tied group is never culled, the later ones are)
+B2_HD int group_tie_class(const DevScene &sc, int g, float3 ro, float3 rd, float tmin, float t) {
+    const float4 mn4 = sc.groups[2 * g], mx4 = sc.groups[2 * g + 1];
+    const float p[3] = { ro.x, ro.y, ro.z }, d[3] = { rd.x, rd.y, rd.z };
+    const float lo[3] = { mn4.x, mn4.y, mn4.z }, hi[3] = { mx4.x, mx4.y, mx4.z };
+    float tmax_inf = B2_T_INF, tmax_t = t;
+    bool dead_inf = false, dead_t = false;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {                       // the arithmetic of group_slab (AABB::intersectAABB, object.cpp:104-121)
+        float invD = x_div(1.0f, d[a]);
+        float t0 = x_mul(x_sub(lo[a], p[a]), invD);
+        float t1 = x_mul(x_sub(hi[a], p[a]), invD);
+        if (invD < 0) { float tmp = t0; t0 = t1; t1 = tmp; }
+        tmin = t0 > tmin ? t0 : tmin;
+        tmax_inf = t1 < tmax_inf ? t1 : tmax_inf;
+        tmax_t = t1 < tmax_t ? t1 : tmax_t;
+        if (tmax_inf <= tmin) dead_inf = true;
+        if (tmax_t <= tmin) dead_t = true;
+    }
+    return dead_inf ? 0 : (dead_t ? 2 : 1);
+}
+
+struct HitRec { int prim; float t; int cls; };          // cls: tie class of the hit (group_tie_class), 1 for light balls
 struct TravCounters { uint32_t nodes, tris; };
 
 // Candidate acceptance in an order-free traversal: the reference visits objects in `order` and accepts
 // t <= best (object.cpp:92), so the winner is min t, ties -> highest order.
-B2_HD bool closer(float t, uint32_t order, float best_t, uint32_t best_order) {
-    return t < best_t || (t == best_t && order > best_order);
+B2_HD bool closer(float t, uint32_t order, int cls, float best_t, uint32_t best_order, int best_cls) {
+    if (t != best_t) return t < best_t;
+    if (cls != best_cls) return cls == 1;                // a pass hit beats a fail hit (group_tie_class)
+    return cls == 1 ? order > best_order : order < best_order;
 }
 
 // ---- spheres + light balls (short tables, tested after the triangles) ----
@@ -110,14 +141,14 @@ B2_HD void closest_spheres(const DevScene &sc, float3 ro, float3 rd, HitRec &bes
         float4 a = sc.sph[2 * i], b = sc.sph[2 * i + 1];
         float t;
         if (sc.gpu_sem) {
-            if (light_ball_test(ro, rd, mk3(a), a.w, best.t, t)) { best.t = t; best.prim = prim_make(B2_KIND_SPHERE, i); best_order = f2u(b.x); }
+            if (light_ball_test(ro, rd, mk3(a), a.w, best.t, t)) { best.t = t; best.prim = prim_make(B2_KIND_SPHERE, i); best_order = f2u(b.x); best.cls = 1; }
             continue;
         }
         if (sphere_test(ro, rd, mk3(a), a.w, 1e-4f, best.t, t)) {
             uint32_t order = f2u(b.x);
-            if ((best.prim == B2_PRIM_MISS || closer(t, order, best.t, best_order)) &&
-                group_pass(sc, (int) f2u(b.z), ro, rd, 1e-4f, B2_T_INF)) {
-                best.t = t; best.prim = prim_make(B2_KIND_SPHERE, i); best_order = order;
+            const int cls = group_tie_class(sc, (int) f2u(b.z), ro, rd, 1e-4f, t);
+            if (cls != 0 && (best.prim == B2_PRIM_MISS || closer(t, order, cls, best.t, best_order, best.cls))) {
+                best.t = t; best.prim = prim_make(B2_KIND_SPHERE, i); best_order = order; best.cls = cls;
             }
         }
     }
@@ -126,7 +157,7 @@ B2_HD void closest_lights(const DevScene &sc, float3 ro, float3 rd, HitRec &best
     for (int k = 0; k < sc.n_lights; ++k) {                      // cpu_bdpt.cpp:64-78
         float4 a = sc.lights[4 * k];
         float t;
-        if (light_ball_test(ro, rd, mk3(a), a.w, best.t, t)) { best.t = t; best.prim = prim_make(B2_KIND_LIGHT, k); }
+        if (light_ball_test(ro, rd, mk3(a), a.w, best.t, t)) { best.t = t; best.prim = prim_make(B2_KIND_LIGHT, k); best.cls = 1; }
     }
 }
 // sc.gpu_sem: check_visibility of geometric.cuh:293-325 -- intersect_sphere within (EPSILON, tMax) and t > tMin, every
@@ -147,16 +178,16 @@ B2_HD bool occluded_spheres(const DevScene &sc, float3 ro, float3 rd, float tMin
 
 // ---- exhaustive reference kernels' bodies (parity cross-check of the BVH path) ----
 B2_HD HitRec closest_hit_brute(const DevScene &sc, float3 ro, float3 rd) {
-    HitRec best; best.prim = B2_PRIM_MISS; best.t = B2_T_INF;
+    HitRec best; best.prim = B2_PRIM_MISS; best.t = B2_T_INF; best.cls = 1;
     uint32_t best_order = 0;
     for (int i = 0; i < sc.n_tris; ++i) {
         float4 a = sc.tri[3 * i], b = sc.tri[3 * i + 1], c = sc.tri[3 * i + 2];
         float t;
         if (tri_test(ro, rd, mk3(a), mk3(b), mk3(c), 1e-4f, best.t, t)) {
             uint32_t order = f2u(a.w);
-            if ((best.prim == B2_PRIM_MISS || closer(t, order, best.t, best_order)) &&
-                group_pass(sc, (int) f2u(c.w), ro, rd, 1e-4f, B2_T_INF)) {
-                best.t = t; best.prim = prim_make(B2_KIND_TRI, i); best_order = order;
+            const int cls = group_tie_class(sc, (int) f2u(c.w), ro, rd, 1e-4f, t);
+            if (cls != 0 && (best.prim == B2_PRIM_MISS || closer(t, order, cls, best.t, best_order, best.cls))) {
+                best.t = t; best.prim = prim_make(B2_KIND_TRI, i); best_order = order; best.cls = cls;
             }
         }
     }

@@ -30,7 +30,7 @@ __device__ __forceinline__ void st3(float *p, size_t i, float3 v) { p[3 * i] = v
 #ifndef B2_QUERY_REFILL
 #define B2_QUERY_REFILL 1
 #endif
-template <bool ANY, bool BRUTE, bool COUNT>
+template <bool ANY, bool BRUTE, bool COUNT, bool FAST = false>     // FAST: the render's shadow-ray arithmetic (tri_test_fast + group_pass_fast)
 __global__ void __launch_bounds__(Q_THREADS) k_intersect(DevScene sc, const float *__restrict__ org, const float *__restrict__ dir, size_t n,
                                                          int32_t *__restrict__ prim_id, float *__restrict__ t_out, unsigned long long *counters) {
     extern __shared__ uint2 s_stack[];
@@ -59,7 +59,7 @@ __global__ void __launch_bounds__(Q_THREADS) k_intersect(DevScene sc, const floa
                     i += stride; busy = false;
                 }
             } else {
-                int r = any_step<COUNT>(sc, at, stack, blockDim.x, &tc);
+                int r = any_step<COUNT, FAST>(sc, at, stack, blockDim.x, &tc);
                 if (r != B2_TRAV_CONTINUE) {
                     if (r == B2_TRAV_EXHAUSTED && occluded_spheres(sc, at.r.o, at.r.d, 1e-3f, at.tmax)) r = B2_TRAV_HIT;
                     prim_id[i] = r == B2_TRAV_HIT ? 0 : 1;
@@ -157,9 +157,15 @@ __global__ void __launch_bounds__(Q_THREADS) k_closest_pooled(DevScene sc, const
                     const float4 a = sc.tri[3 * ti], b = sc.tri[3 * ti + 1], c = sc.tri[3 * ti + 2];
                     if (COUNT) tc.tris++;
                     float tt;
-                    if (tri_test(ro, rd, mk3(a), mk3(b), mk3(c), 1e-4f, o_tmax, tt) && group_pass(sc, (int) f2u(c.w), ro, rd, 1e-4f, B2_T_INF)) {
-                        key = ((unsigned long long) __float_as_uint(tt) << 32) | (unsigned long long) (~f2u(a.w));
-                        atomicMin(&s_key[wbase + owner], key);
+                    if (tri_test(ro, rd, mk3(a), mk3(b), mk3(c), 1e-4f, o_tmax, tt)) {
+                        // low word = the tie order of closer(): pass hits (class 1) before fail hits, later objects first among
+                        // the pass hits, earlier objects first among the fail hits
+                        const int cls = group_tie_class(sc, (int) f2u(c.w), ro, rd, 1e-4f, tt);
+                        if (cls != 0) {
+                            const uint32_t low = cls == 1 ? 0x7fffffffu - f2u(a.w) : 0x80000000u | f2u(a.w);
+                            key = ((unsigned long long) __float_as_uint(tt) << 32) | (unsigned long long) low;
+                            atomicMin(&s_key[wbase + owner], key);
+                        }
                     }
                 }
                 __syncwarp();
@@ -170,9 +176,11 @@ __global__ void __launch_bounds__(Q_THREADS) k_closest_pooled(DevScene sc, const
                 const unsigned long long key = s_key[threadIdx.x];
                 if (key != ~0ull) {
                     const float tt = __uint_as_float((uint32_t) (key >> 32));
-                    const uint32_t order = ~(uint32_t) key;
-                    if (ct.best.prim == B2_PRIM_MISS || closer(tt, order, ct.best.t, ct.best_order)) {
-                        ct.best.t = tt; ct.best.prim = prim_make(B2_KIND_TRI, s_ti[threadIdx.x]); ct.best_order = order;
+                    const uint32_t low = (uint32_t) key;
+                    const int cls = (low & 0x80000000u) ? 2 : 1;
+                    const uint32_t order = cls == 1 ? 0x7fffffffu - low : low & 0x7fffffffu;
+                    if (ct.best.prim == B2_PRIM_MISS || closer(tt, order, cls, ct.best.t, ct.best_order, ct.best.cls)) {
+                        ct.best.t = tt; ct.best.prim = prim_make(B2_KIND_TRI, s_ti[threadIdx.x]); ct.best_order = order; ct.best.cls = cls;
                     }
                 }
             }
@@ -247,12 +255,12 @@ __global__ void k_philox(size_t n, const uint32_t *ctr4, const uint32_t *key2, u
     if (unit4) { unit4[4 * i] = u32_to_unit(o.x); unit4[4 * i + 1] = u32_to_unit(o.y); unit4[4 * i + 2] = u32_to_unit(o.z); unit4[4 * i + 3] = u32_to_unit(o.w); }
 }
 
-template <bool ANY, bool BRUTE, bool COUNT>
+template <bool ANY, bool BRUTE, bool COUNT, bool FAST = false>
 int launch_isect(const DevScene &sc, int bvh_depth, const float *o, const float *d, size_t n, int32_t *id, float *t, unsigned long long *cnt, cudaStream_t st) {
     const size_t sb = (size_t) Q_THREADS * (size_t) (bvh_depth + 2) * sizeof(uint2);
     static size_t configured = 0;
     if (sb > 48 * 1024 && sb > configured) {
-        B2_CUDA(cudaFuncSetAttribute(k_intersect<ANY, BRUTE, COUNT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb));
+        B2_CUDA(cudaFuncSetAttribute(k_intersect<ANY, BRUTE, COUNT, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb));
     }
     // grid: enough blocks to fill every SM's resident CTAs, grid-stride beyond that
     const size_t want = (n + Q_THREADS - 1) / Q_THREADS;
@@ -261,7 +269,7 @@ int launch_isect(const DevScene &sc, int bvh_depth, const float *o, const float 
         if (sb + 2048 > 48 * 1024) B2_CUDA(cudaFuncSetAttribute(k_closest_pooled<COUNT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb));
         k_closest_pooled<COUNT><<<grid, Q_THREADS, sb, st>>>(sc, o, d, n, id, t, cnt);
     } else
-        k_intersect<ANY, BRUTE, COUNT><<<grid, Q_THREADS, sb, st>>>(sc, o, d, n, id, t, cnt);
+        k_intersect<ANY, BRUTE, COUNT, FAST><<<grid, Q_THREADS, sb, st>>>(sc, o, d, n, id, t, cnt);
     B2_CUDA(cudaGetLastError());
     return B2_OK;
 }
@@ -278,6 +286,7 @@ int b2_intersect_launch(const DevScene &sc, int bvh_depth, const float *d_org, c
         return launch_isect<false, false, false>(sc, bvh_depth, d_org, d_dir, n, d_prim_id, d_t, d_counters, st);
     }
     if (brute) return launch_isect<true, true, false>(sc, bvh_depth, d_org, d_dir, n, d_prim_id, d_t, d_counters, st);
+    if (mode & B2_FAST_SHADOW) return launch_isect<true, false, false, true>(sc, bvh_depth, d_org, d_dir, n, d_prim_id, d_t, d_counters, st);
     if (count) return launch_isect<true, false, true>(sc, bvh_depth, d_org, d_dir, n, d_prim_id, d_t, d_counters, st);
     return launch_isect<true, false, false>(sc, bvh_depth, d_org, d_dir, n, d_prim_id, d_t, d_counters, st);
 }
