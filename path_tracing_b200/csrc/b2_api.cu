@@ -55,7 +55,7 @@ template <class T> static int upload(DevBuf<T> &d, const std::vector<T> &h, cuda
 extern "C" {
 
 const char *b2_last_error(void) { return g_err; }
-const char *b2_version(void) { return "b2pt 0.1 (sm_100a)"; }
+const char *b2_version(void) { return "b2pt 0.2.0 (sm_100a)"; }     // bump with every kernel change: profiles/*_traffic.json are tied to it
 int b2_device_count(int *count) {
     if (!count) { b2_set_error("count is NULL"); return B2_ERR_INVALID; }
     int n = 0;
@@ -118,6 +118,24 @@ int b2_scene_build_bvh(B2Scene *s, const B2BvhParams *params) {
     const int radius = (params && params->ploc_radius > 0) ? std::min(params->ploc_radius, 64) : 2;   // measured on C3 / C5: radius 2 > 3 > 4 > 8 (profiles/r01_ploc_summary.md)
     B2_TRY(b2_build_bvh_device(s->d_in.p, (int) hs.tris.size(), pad, max_leaf, builder, radius, s->stream, s->bvh));
     s->built = true; s->max_leaf = max_leaf;
+    // persisting-L2 carve-out for the top of the node array: at most half of the L2 and at most what the device allows;
+    // B2_L2_PERSIST_MB overrides (0 = no window) for A/B measurements (profiles/r02_l2_window.md)
+    {
+        int max_persist = 0, max_window = 0, l2 = 0;
+        cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, s->device);
+        cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, s->device);
+        cudaDeviceGetAttribute(&l2, cudaDevAttrL2CacheSize, s->device);
+        size_t budget = std::min<size_t>((size_t) std::max(max_persist, 0), (size_t) std::max(l2, 0) / 2);
+        if (const char *e = getenv("B2_L2_PERSIST_MB")) budget = std::min<size_t>((size_t) std::max(max_persist, 0), (size_t) std::max(atol(e), 0l) << 20);
+        const size_t node_bytes = (size_t) s->bvh.n_nodes * sizeof(uint4) * B2_NODE_UINT4;
+        s->l2_window_bytes = 0; s->l2_hit_ratio = 1.0f;
+        if (budget > 0 && node_bytes > 0 && max_window > 0) {
+            size_t cur = 0;
+            cudaDeviceGetLimit(&cur, cudaLimitPersistingL2CacheSize);
+            if (cur < budget && cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, budget) != cudaSuccess) { cudaGetLastError(); budget = cur; }
+            s->l2_window_bytes = std::min<size_t>(std::min<size_t>(node_bytes, budget), (size_t) max_window);
+        }
+    }
     return B2_OK;
 }
 
@@ -141,6 +159,7 @@ int b2_intersect_device(B2Scene *s, const float *d_org, const float *d_dir, size
     B2_TRY(b2_check_built(s));
     if (n && (!d_org || !d_dir || !d_prim_id)) { b2_set_error("NULL ray / result buffer"); return B2_ERR_INVALID; }
     B2_CUDA(cudaSetDevice(s->device));
+    L2Window l2w(s, (cudaStream_t) stream);
     return b2_intersect_launch(s->view(), s->bvh.depth, d_org, d_dir, n, mode, d_prim_id, d_t, s->isect_counters.p, (cudaStream_t) stream);
 }
 
@@ -156,6 +175,7 @@ int b2_intersect(B2Scene *s, const float *org, const float *dir, size_t n, int m
     if (want_t) B2_TRY(d_t.alloc(n));
     B2_CUDA(cudaMemcpyAsync(d_o.p, org, 3 * n * sizeof(float), cudaMemcpyHostToDevice, s->stream));
     B2_CUDA(cudaMemcpyAsync(d_d.p, dir, 3 * n * sizeof(float), cudaMemcpyHostToDevice, s->stream));
+    L2Window l2w(s, s->stream);
     B2_TRY(b2_intersect_launch(s->view(), s->bvh.depth, d_o.p, d_d.p, n, mode, d_id.p, want_t ? d_t.p : nullptr, s->isect_counters.p, s->stream));
     B2_CUDA(cudaMemcpyAsync(prim_id, d_id.p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, s->stream));
     if (want_t) B2_CUDA(cudaMemcpyAsync(t, d_t.p, n * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
@@ -179,6 +199,7 @@ int b2_render_bdpt_device(B2Scene *s, const B2Camera *cam, const B2RenderParams 
     if (!cam || !params || !d_film_rgb) { b2_set_error("NULL argument"); return B2_ERR_INVALID; }
     std::lock_guard<std::mutex> lk(s->mtx);
     B2_CUDA(cudaSetDevice(s->device));
+    L2Window l2w(s, stream ? (cudaStream_t) stream : s->stream);
     return b2_render_device_impl(s->view(), s->bvh.depth, s->ws_ref(), *cam, *params, d_film_rgb, stream ? (cudaStream_t) stream : s->stream, stats);
 }
 
@@ -191,6 +212,7 @@ int b2_render_bdpt(B2Scene *s, const B2Camera *cam, const B2RenderParams *params
     const size_t nf = (size_t) 3 * params->width * params->height;
     RenderWorkspace &ws = s->ws_ref();
     B2_TRY(ws.ensure_out(nf));
+    L2Window l2w(s, s->stream);
     B2_TRY(b2_render_device_impl(s->view(), s->bvh.depth, ws, *cam, *params, ws.film_out.p, s->stream, stats));
     // a caller buffer that is already page-locked (cudaHostAlloc / cudaHostRegister, e.g. a pinned torch tensor) takes the film
     // straight from the device; a pageable one goes through the pinned staging buffer in slices, so that the host copy of
@@ -240,6 +262,7 @@ int b2_render_bdpt_progressive(B2Scene *s, const B2Camera *cam, const B2RenderPa
         p.seed = params->seed + (uint64_t) k;
         p.film_mode = k == 0 ? B2_FILM_MEAN : B2_FILM_ACCUMULATE;
         B2Stats st;
+        L2Window l2w(s, s->stream);
         B2_TRY(b2_render_device_impl(s->view(), s->bvh.depth, ws, *cam, p, ws.film_out.p, s->stream, &st));
         tot.eye_samples += st.eye_samples; tot.closest_rays += st.closest_rays; tot.shadow_rays += st.shadow_rays; tot.path_samples += st.path_samples;
         tot.delta_cap_hits += st.delta_cap_hits; tot.nodes_visited += st.nodes_visited; tot.tris_tested += st.tris_tested;

@@ -123,7 +123,7 @@ B2_HD void trav_push(TravPos &p, uint32_t hits_p, uint32_t child_base, uint32_t 
 
 template <bool COUNT>
 B2_HD HitRec closest_hit_bvh(const DevScene &sc, float3 ro, float3 rd, uint2 *stack, int sstride, TravCounters *cnt) {
-    HitRec best; best.prim = B2_PRIM_MISS; best.t = B2_T_INF; best.cls = 1;
+    HitRec best; best.prim = B2_PRIM_MISS; best.t = B2_T_INF;
     uint32_t best_order = 0;
     if (sc.n_nodes > 0) {
         const RayPre r = ray_pre(ro, rd);
@@ -141,10 +141,7 @@ B2_HD HitRec closest_hit_bvh(const DevScene &sc, float3 ro, float3 rd, uint2 *st
                 float t;
                 if (tri_test(ro, rd, mk3(a), mk3(b), mk3(c), 1e-4f, best.t, t)) {
                     const uint32_t order = f2u(a.w);
-                    const int cls = group_tie_class(sc, (int) f2u(c.w), ro, rd, 1e-4f, t);
-                    if (cls != 0 && (best.prim == B2_PRIM_MISS || closer(t, order, cls, best.t, best_order, best.cls))) {
-                        best.t = t; best.prim = prim_make(B2_KIND_TRI, ti); best_order = order; best.cls = cls;
-                    }
+                    if (accept_hit(sc, ro, rd, t, order, (int) f2u(c.w), best, best_order)) { best.t = t; best.prim = prim_make(B2_KIND_TRI, ti); best_order = order; }
                 }
             }
             trav_push(p, hits_p, child_base, imask, stack, sstride);
@@ -159,7 +156,7 @@ B2_HD HitRec closest_hit_bvh(const DevScene &sc, float3 ro, float3 rd, uint2 *st
 // lanes of the warp keep walking (k_intersect): same node / triangle arithmetic and acceptance rule as closest_hit_bvh.
 struct ClosestTrav { RayPre r; HitRec best; uint32_t best_order; TravPos p; };
 B2_HD void closest_init(ClosestTrav &t, const DevScene &sc, float3 ro, float3 rd) {
-    t.r = ray_pre(ro, rd); t.best.prim = B2_PRIM_MISS; t.best.t = B2_T_INF; t.best.cls = 1; t.best_order = 0u;
+    t.r = ray_pre(ro, rd); t.best.prim = B2_PRIM_MISS; t.best.t = B2_T_INF; t.best_order = 0u;
     trav_reset(t.p, sc.n_nodes > 0);
 }
 // The node half of a step: pops the next wide node, tests its 8 children, stacks the hit internal ones and returns the hit
@@ -175,11 +172,9 @@ B2_HD bool closest_node_step(const DevScene &sc, ClosestTrav &t, uint2 *stack, i
     trav_push(t.p, hits_p, child_base, imask, stack, sstride);
     return true;
 }
-// One wide node and its leaf triangles, all by the ray's own lane.
+// The hit leaf triangles of one node test, by the ray's own lane, with the full acceptance rule (accept_hit).
 template <bool COUNT>
-B2_HD bool closest_step(const DevScene &sc, ClosestTrav &t, uint2 *stack, int sstride, TravCounters *cnt) {
-    uint32_t tribits, tri_base, vmask;
-    if (!closest_node_step<COUNT>(sc, t, stack, sstride, cnt, tribits, tri_base, vmask)) return false;
+B2_HD void closest_test_tris(const DevScene &sc, ClosestTrav &t, uint32_t tribits, uint32_t tri_base, uint32_t vmask, TravCounters *cnt) {
     while (tribits) {
         const int bit = ffs32(tribits) - 1;
         tribits &= tribits - 1u;
@@ -189,12 +184,16 @@ B2_HD bool closest_step(const DevScene &sc, ClosestTrav &t, uint2 *stack, int ss
         float tt;
         if (tri_test(t.r.o, t.r.d, mk3(a), mk3(b), mk3(c), 1e-4f, t.best.t, tt)) {
             const uint32_t order = f2u(a.w);
-            const int cls = group_tie_class(sc, (int) f2u(c.w), t.r.o, t.r.d, 1e-4f, tt);
-            if (cls != 0 && (t.best.prim == B2_PRIM_MISS || closer(tt, order, cls, t.best.t, t.best_order, t.best.cls))) {
-                t.best.t = tt; t.best.prim = prim_make(B2_KIND_TRI, ti); t.best_order = order; t.best.cls = cls;
-            }
+            if (accept_hit(sc, t.r.o, t.r.d, tt, order, (int) f2u(c.w), t.best, t.best_order)) { t.best.t = tt; t.best.prim = prim_make(B2_KIND_TRI, ti); t.best_order = order; }
         }
     }
+}
+// One wide node and its leaf triangles, all by the ray's own lane.
+template <bool COUNT>
+B2_HD bool closest_step(const DevScene &sc, ClosestTrav &t, uint2 *stack, int sstride, TravCounters *cnt) {
+    uint32_t tribits, tri_base, vmask;
+    if (!closest_node_step<COUNT>(sc, t, stack, sstride, cnt, tribits, tri_base, vmask)) return false;
+    closest_test_tris<COUNT>(sc, t, tribits, tri_base, vmask, cnt);
     return true;
 }
 B2_HD HitRec closest_finish(const DevScene &sc, ClosestTrav &t) {

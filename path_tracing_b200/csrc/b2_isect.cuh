@@ -122,7 +122,7 @@ B2_HD int group_tie_class(const DevScene &sc, int g, float3 ro, float3 rd, float
     return dead_inf ? 0 : (dead_t ? 2 : 1);
 }
 
-struct HitRec { int prim; float t; int cls; };          // cls: tie class of the hit (group_tie_class), 1 for light balls
+struct HitRec { int prim; float t; };
 struct TravCounters { uint32_t nodes, tris; };
 
 // Candidate acceptance in an order-free traversal: the reference visits objects in `order` and accepts
@@ -131,6 +131,26 @@ B2_HD bool closer(float t, uint32_t order, int cls, float best_t, uint32_t best_
     if (t != best_t) return t < best_t;
     if (cls != best_cls) return cls == 1;                // a pass hit beats a fail hit (group_tie_class)
     return cls == 1 ? order > best_order : order < best_order;
+}
+// group of a stored hit (-1: light ball, or no group cull in the pt / ppm semantics)
+B2_HD int group_of_prim(const DevScene &sc, int prim) {
+    if (prim == B2_PRIM_MISS || sc.gpu_sem) return -1;
+    const int k = prim_kind(prim), i = prim_index(prim);
+    if (k == B2_KIND_TRI) return (int) f2u(sc.tri[3 * i + 2].w);
+    if (k == B2_KIND_SPHERE) return (int) f2u(sc.sph[2 * i + 1].z);
+    return -1;
+}
+// A primitive test reported a hit at t <= best.t for object (order, group g): does it replace `best`?  Strictly closer hits
+// (the common case) only need the reference's group cull with tMax = infinity; exact ties compare tie classes, which are pure
+// functions of (group, ray, t) and are computed only then -- nothing is carried along in the traversal state.
+B2_HD bool accept_hit(const DevScene &sc, float3 ro, float3 rd, float t, uint32_t order, int g, const HitRec &best, uint32_t best_order) {
+    if (best.prim == B2_PRIM_MISS || t < best.t) return group_pass(sc, g, ro, rd, 1e-4f, B2_T_INF);
+    if (t > best.t) return false;
+    const int cls = group_tie_class(sc, g, ro, rd, 1e-4f, t);
+    if (cls == 0) return false;
+    const int bg = group_of_prim(sc, best.prim);
+    const int best_cls = bg >= 0 ? group_tie_class(sc, bg, ro, rd, 1e-4f, best.t) : 1;
+    return closer(t, order, cls, best.t, best_order, best_cls);
 }
 
 // ---- spheres + light balls (short tables, tested after the triangles) ----
@@ -141,15 +161,12 @@ B2_HD void closest_spheres(const DevScene &sc, float3 ro, float3 rd, HitRec &bes
         float4 a = sc.sph[2 * i], b = sc.sph[2 * i + 1];
         float t;
         if (sc.gpu_sem) {
-            if (light_ball_test(ro, rd, mk3(a), a.w, best.t, t)) { best.t = t; best.prim = prim_make(B2_KIND_SPHERE, i); best_order = f2u(b.x); best.cls = 1; }
+            if (light_ball_test(ro, rd, mk3(a), a.w, best.t, t)) { best.t = t; best.prim = prim_make(B2_KIND_SPHERE, i); best_order = f2u(b.x); }
             continue;
         }
         if (sphere_test(ro, rd, mk3(a), a.w, 1e-4f, best.t, t)) {
             uint32_t order = f2u(b.x);
-            const int cls = group_tie_class(sc, (int) f2u(b.z), ro, rd, 1e-4f, t);
-            if (cls != 0 && (best.prim == B2_PRIM_MISS || closer(t, order, cls, best.t, best_order, best.cls))) {
-                best.t = t; best.prim = prim_make(B2_KIND_SPHERE, i); best_order = order; best.cls = cls;
-            }
+            if (accept_hit(sc, ro, rd, t, order, (int) f2u(b.z), best, best_order)) { best.t = t; best.prim = prim_make(B2_KIND_SPHERE, i); best_order = order; }
         }
     }
 }
@@ -157,7 +174,7 @@ B2_HD void closest_lights(const DevScene &sc, float3 ro, float3 rd, HitRec &best
     for (int k = 0; k < sc.n_lights; ++k) {                      // cpu_bdpt.cpp:64-78
         float4 a = sc.lights[4 * k];
         float t;
-        if (light_ball_test(ro, rd, mk3(a), a.w, best.t, t)) { best.t = t; best.prim = prim_make(B2_KIND_LIGHT, k); best.cls = 1; }
+        if (light_ball_test(ro, rd, mk3(a), a.w, best.t, t)) { best.t = t; best.prim = prim_make(B2_KIND_LIGHT, k); }
     }
 }
 // sc.gpu_sem: check_visibility of geometric.cuh:293-325 -- intersect_sphere within (EPSILON, tMax) and t > tMin, every
@@ -178,17 +195,14 @@ B2_HD bool occluded_spheres(const DevScene &sc, float3 ro, float3 rd, float tMin
 
 // ---- exhaustive reference kernels' bodies (parity cross-check of the BVH path) ----
 B2_HD HitRec closest_hit_brute(const DevScene &sc, float3 ro, float3 rd) {
-    HitRec best; best.prim = B2_PRIM_MISS; best.t = B2_T_INF; best.cls = 1;
+    HitRec best; best.prim = B2_PRIM_MISS; best.t = B2_T_INF;
     uint32_t best_order = 0;
     for (int i = 0; i < sc.n_tris; ++i) {
         float4 a = sc.tri[3 * i], b = sc.tri[3 * i + 1], c = sc.tri[3 * i + 2];
         float t;
         if (tri_test(ro, rd, mk3(a), mk3(b), mk3(c), 1e-4f, best.t, t)) {
             uint32_t order = f2u(a.w);
-            const int cls = group_tie_class(sc, (int) f2u(c.w), ro, rd, 1e-4f, t);
-            if (cls != 0 && (best.prim == B2_PRIM_MISS || closer(t, order, cls, best.t, best_order, best.cls))) {
-                best.t = t; best.prim = prim_make(B2_KIND_TRI, i); best_order = order; best.cls = cls;
-            }
+            if (accept_hit(sc, ro, rd, t, order, (int) f2u(c.w), best, best_order)) { best.t = t; best.prim = prim_make(B2_KIND_TRI, i); best_order = order; }
         }
     }
     closest_spheres(sc, ro, rd, best, best_order);

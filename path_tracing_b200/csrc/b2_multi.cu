@@ -92,6 +92,7 @@ extern "C" int b2_render_bdpt_multi(B2Scene **scenes, int n_gpus, const B2Camera
             B2RenderParams p = *params;
             const int stride = p.sample_stride > 0 ? p.sample_stride : 1;
             p.sample_offset = params->sample_offset + g * stride; p.sample_stride = stride * n_gpus; p.film_mode = B2_FILM_SUM;
+            L2Window l2w(s, s->stream);
             rc[g] = b2_render_device_impl(s->view(), s->bvh.depth, s->ws_ref(), *cam, p, d_film[g], s->stream, &st[g]);
             if (rc[g] != B2_OK) err[g] = b2_last_error();
         });

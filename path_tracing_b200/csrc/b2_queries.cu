@@ -111,6 +111,7 @@ __global__ void __launch_bounds__(Q_THREADS) k_closest_pooled(DevScene sc, const
     extern __shared__ uint2 s_stack[];
     __shared__ unsigned long long s_key[Q_THREADS];
     __shared__ int s_ti[Q_THREADS];
+    __shared__ int s_tie[Q_THREADS];
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31, wbase = threadIdx.x & ~31;
     TravCounters tc{ 0u, 0u };
@@ -137,7 +138,7 @@ __global__ void __launch_bounds__(Q_THREADS) k_closest_pooled(DevScene sc, const
         for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(FULL, incl, d); if (lane >= d) incl += v; }
         const int total = __shfl_sync(FULL, incl, 31);
         if (total > 0) {
-            s_key[threadIdx.x] = ~0ull;
+            s_key[threadIdx.x] = ~0ull; s_tie[threadIdx.x] = 0;
             __syncwarp();
             for (int base = 0; base < total; base += 32) {
                 const int k = base + lane;
@@ -157,15 +158,12 @@ __global__ void __launch_bounds__(Q_THREADS) k_closest_pooled(DevScene sc, const
                     const float4 a = sc.tri[3 * ti], b = sc.tri[3 * ti + 1], c = sc.tri[3 * ti + 2];
                     if (COUNT) tc.tris++;
                     float tt;
-                    if (tri_test(ro, rd, mk3(a), mk3(b), mk3(c), 1e-4f, o_tmax, tt)) {
-                        // low word = the tie order of closer(): pass hits (class 1) before fail hits, later objects first among
-                        // the pass hits, earlier objects first among the fail hits
-                        const int cls = group_tie_class(sc, (int) f2u(c.w), ro, rd, 1e-4f, tt);
-                        if (cls != 0) {
-                            const uint32_t low = cls == 1 ? 0x7fffffffu - f2u(a.w) : 0x80000000u | f2u(a.w);
-                            key = ((unsigned long long) __float_as_uint(tt) << 32) | (unsigned long long) low;
-                            atomicMin(&s_key[wbase + owner], key);
-                        }
+                    if (tri_test(ro, rd, mk3(a), mk3(b), mk3(c), 1e-4f, o_tmax, tt) && group_pass(sc, (int) f2u(c.w), ro, rd, 1e-4f, B2_T_INF)) {
+                        key = ((unsigned long long) __float_as_uint(tt) << 32) | (unsigned long long) (~f2u(a.w));
+                        const unsigned long long old = atomicMin(&s_key[wbase + owner], key);
+                        // an exact tie -- with the ray's current hit, or between two candidates of this step (whichever arrives second
+                        // sees the first in `old`) -- is resolved by the ray's own lane with the full rule (tie classes, accept_hit)
+                        if (tt == o_tmax || (old != ~0ull && (uint32_t) (old >> 32) == __float_as_uint(tt))) s_tie[wbase + owner] = 1;
                     }
                 }
                 __syncwarp();
@@ -173,14 +171,12 @@ __global__ void __launch_bounds__(Q_THREADS) k_closest_pooled(DevScene sc, const
                 __syncwarp();
             }
             if (cnt > 0) {
-                const unsigned long long key = s_key[threadIdx.x];
-                if (key != ~0ull) {
-                    const float tt = __uint_as_float((uint32_t) (key >> 32));
-                    const uint32_t low = (uint32_t) key;
-                    const int cls = (low & 0x80000000u) ? 2 : 1;
-                    const uint32_t order = cls == 1 ? 0x7fffffffu - low : low & 0x7fffffffu;
-                    if (ct.best.prim == B2_PRIM_MISS || closer(tt, order, cls, ct.best.t, ct.best_order, ct.best.cls)) {
-                        ct.best.t = tt; ct.best.prim = prim_make(B2_KIND_TRI, s_ti[threadIdx.x]); ct.best_order = order; ct.best.cls = cls;
+                if (s_tie[threadIdx.x]) closest_test_tris<false>(sc, ct, tribits, tri_base, vmask, &tc);
+                else {
+                    const unsigned long long key = s_key[threadIdx.x];
+                    if (key != ~0ull) {                          // strictly closer than the current hit, and alone at its t
+                        const int wi = s_ti[threadIdx.x];
+                        ct.best.t = __uint_as_float((uint32_t) (key >> 32)); ct.best.prim = prim_make(B2_KIND_TRI, wi); ct.best_order = ~(uint32_t) key;
                     }
                 }
             }

@@ -242,7 +242,9 @@ __global__ void __launch_bounds__(CONN_THREADS, CONN_BLOCKS_PER_SM) k_connect(Re
                 n_rq += __popc(okm);
                 __syncwarp();
             } else if (n_rq < 32 && n_buf < CONN_LOW && !pairs_done) {
-                // ---- pre-test one chunk of pool records ----
+                // ---- pre-test chunks of pool records until 32 pairs are stacked or the slice ends (one pass through the phase
+                //      selector per CHUNK cost ~30 of ~190 instructions on scenes where almost every pair is rejected: C2) ----
+              do {
                 const float4 *__restrict__ rec = pre + (size_t) B2_PRE_F4 * CONN_CHUNK * ch;
                 ++ch;
                 uint32_t mask = 0u;
@@ -270,6 +272,7 @@ __global__ void __launch_bounds__(CONN_THREADS, CONN_BLOCKS_PER_SM) k_connect(Re
                     }
                     __syncwarp();
                 }
+              } while (n_buf < CONN_LOW && ch < ch_end);
             } else if (busy_m != 0u || n_rq > 0) {
                 // ---- trace: idle lanes take a ready ray, then one step per lane that holds a ray ----
                 if (n_rq > 0 && busy_m != 0xffffffffu) {

@@ -22,6 +22,10 @@ struct B2Scene {
     RenderWorkspace &ws_ref();            // (allocating and freeing ~6 GB of wavefront state per scene handle is what made
                                           //  a create -> render -> destroy cycle 5x slower than the render itself)
     std::mutex mtx;                       // one call in flight per handle
+    // L2-resident top of the tree (the lever BASELINE.json's north_star names): the wide nodes are laid out level by level, so
+    // the first l2_window_bytes of the node array are the top levels (all of it when the array is small).  Every traversal
+    // launch runs with a persisting access-policy window over that range (L2Window below); sized by b2_scene_build_bvh.
+    size_t l2_window_bytes = 0; float l2_hit_ratio = 1.0f;
     DevScene view() const {
         DevScene v; memset(&v, 0, sizeof(v));
         v.tri = bvh.tri.p; v.tri_obj = bvh.tri_obj.p; v.nodes = bvh.nodes.p;
@@ -35,4 +39,22 @@ struct B2Scene {
 
 
 void b2_workspace_release(B2Scene *s);
+// RAII: persisting-L2 access-policy window over the top of s's node array on stream `st` for the launches in scope.
+struct L2Window {
+    cudaStream_t st = nullptr; bool on = false;
+    L2Window(const B2Scene *s, cudaStream_t stream) : st(stream) {
+        if (!s || s->l2_window_bytes == 0 || !s->bvh.nodes.p) return;
+        cudaStreamAttrValue v; memset(&v, 0, sizeof(v));
+        v.accessPolicyWindow.base_ptr = (void *) s->bvh.nodes.p; v.accessPolicyWindow.num_bytes = s->l2_window_bytes;
+        v.accessPolicyWindow.hitRatio = s->l2_hit_ratio; v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting; v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        on = cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &v) == cudaSuccess;
+        if (!on) cudaGetLastError();
+    }
+    ~L2Window() {
+        if (!on) return;
+        cudaStreamAttrValue v; memset(&v, 0, sizeof(v));       // num_bytes = 0 switches the window off for whatever the caller launches next
+        cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &v);
+    }
+    L2Window(const L2Window &) = delete; L2Window &operator=(const L2Window &) = delete;
+};
 extern "C" int b2_check_built(B2Scene *s);   // internal helper (not part of include/b2pt.h)

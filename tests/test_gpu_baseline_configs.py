@@ -184,9 +184,69 @@ def test_c5_hits_bit_exact_against_the_reference_and_the_host_bvh():
     assert 0.2 < hit.mean() < 1.0
     assert np.all(np.abs(t[hit] - g["t"][hit]) <= 1e-5 * np.abs(g["t"][hit])) and np.array_equal(bits(t), bits(g["t"]))
     assert np.array_equal(sc.visibility(org, p2), g["vis"].astype(np.int32))
+    p2s = (org + dr * np.float32(0.004)).astype(np.float32)          # short segments: about half are visible (box-to-box ones never are)
+    vs = sc.visibility(org, p2s)
+    assert np.array_equal(vs, g["vis_short"].astype(np.int32)) and 0.2 < vs.mean() < 0.8
     org, dr, p2 = gen.random_rays(1_000_000, 0.0, 1.0, seed=8)
     ids, t = sc.closest_hit(org, dr); vis = sc.visibility(org, p2)
     hs = HostSim(sd)
     hi, ht, _ = hs.intersect(org, dr, 0); hv, _, _ = hs.intersect(org, p2, 1)
     assert np.array_equal(ids, hi) and np.array_equal(bits(t), bits(ht)) and np.array_equal(vis, hv)
     hs.close(); sc.close()
+
+
+def _family_gates(G, A, k_box, tag):
+    """SURVEY.md 8(d) gates 1-3 for a family of GPU films G (different Philox seeds = different light pools) against films A of the
+    unmodified reference at the same configuration.  Both families are samples of one distribution if the GPU path is right, so
+    cross distances must look like within-family distances:
+      gate 1  raw HDR:               max relRMSE_c(G_k, A_i) <= 1.25 * floor,  floor = max over the pairs inside A and inside G
+      gate 2  k_box x k_box filter:  the same, <= max(1.25 * floor, 0.05); and again on films clamped to [0, 1] (the display range:
+              fireflies of up to 15 per connection dominate the raw statistic, cpu_bdpt.cpp:437)
+      gate 3  every reference film's channel means within 3 sigma (of the GPU family, whose seeds span the pool noise that one
+              reference run cannot show: its pool comes from seed 1337 + thread id) of the GPU family's mean"""
+    import itertools
+    def floors(f):
+        inside = [f(x, y) for fam in (A, G) for x, y in itertools.combinations(fam, 2)]
+        cross = [f(x, a) for x in G for a in A]
+        return np.max(inside, axis=0), np.max(cross, axis=0)
+    fl, cr = floors(rel_rmse)
+    assert np.all(cr <= 1.25 * fl), (tag, "gate 1", cr, fl)
+    fl, cr = floors(lambda x, y: rel_rmse(box(x, k_box), box(y, k_box)))
+    assert np.all(cr <= np.maximum(1.25 * fl, 0.05)), (tag, "gate 2", cr, fl)
+    fl, cr = floors(lambda x, y: rel_rmse(box(np.clip(x, 0, 1), k_box), box(np.clip(y, 0, 1), k_box)))
+    assert np.all(cr <= np.maximum(1.25 * fl, 0.05)), (tag, "gate 2 clamped", cr, fl)
+    gm = np.array([x.mean(axis=(0, 1)) for x in G]); mu, sigma = gm.mean(axis=0), gm.std(axis=0, ddof=1)
+    for a in A:
+        assert np.all(np.abs(a.mean(axis=(0, 1)) - mu) <= 3.0 * sigma * np.sqrt(1.0 + 1.0 / len(G)) + 1e-3 * mu), (tag, "gate 3", a.mean(axis=(0, 1)), mu, sigma)
+    for x in G:
+        assert np.isfinite(x).all() and x.min() >= 0.0
+
+
+def test_c1_full_size_against_films_of_the_unmodified_reference():
+    """BASELINE config 1 (the PR1 reference render): input.txt, 512 x 512, 16 spp, spl 8, depth 8/8 -- ~450 shadow rays per eye
+    sample, the loop-C workload.  Golden: two renders of oracle/_ref (cpu_bdpt.cpp unmodified, all host threads)."""
+    g = np.load(os.path.join(GOLD, "film_c1.npz"))
+    A = [g["a"].astype(np.float32), g["b"].astype(np.float32)]
+    W, H, spp, spl, de, dl = [int(x) for x in g["cfg"]]
+    assert (W, H, spp, spl, de, dl) == (512, 512, 16, 8, 8, 8)
+    sc = api.Scene(reference_scene("cornell"))
+    G = []
+    for seed in range(101, 109):
+        film, st = sc.render_bdpt(width=W, height=H, spp=spp, spl=spl, eye_depth=de, light_depth=dl, seed=seed)
+        G.append(film)
+    assert st["eye_samples"] == W * H * spp and st["shadow_rays"] > 300 * st["eye_samples"] and st["delta_cap_hits"] == 0
+    _family_gates(G, A, 8, "C1")
+    sc.close()
+
+
+def test_c3_reduced_film_against_films_of_the_unmodified_reference(c3):
+    """BASELINE config 3 at the reduced film BASELINE.md proposes: the generated 1 M-triangle OBJ scene, 120 x 68, 8 spp, spl 8,
+    depth 16/16, rendered by the unmodified reference (its own group-AABB cull over the adapter's spatial G groups keeps
+    cpu_find_closest_hit tractable) -- golden film_c3.npz."""
+    sd, sc = c3
+    g = np.load(os.path.join(GOLD, "film_c3.npz"))
+    assert len(sd.tris) == int(g["n_tris"])                 # the generator is deterministic: same mesh here and where the golden was made
+    A = [g["a"], g["b"]]
+    W, H, spp, spl, de, dl = [int(x) for x in g["cfg"]]
+    G = [sc.render_bdpt(width=W, height=H, spp=spp, spl=spl, eye_depth=de, light_depth=dl, seed=seed)[0] for seed in range(101, 109)]
+    _family_gates(G, A, 4, "C3")
