@@ -345,8 +345,13 @@ B2_HD float mis_weight_core(const EA &E, int s_idx, const LA &L, int t_idx, floa
     const float3 ev_pos = E.pos(s_idx), lv_pos = L.pos(t_idx);
     const float3 wo_s = normalize3(((s_idx == 0) ? cam_pos : E.pos(s_idx - 1)) - ev_pos);
     const float3 wo_t = (t_idx == 0) ? normalize3(L.cur_n()) : normalize3(L.pos(t_idx - 1) - lv_pos);
-    const float pdf_omega_s = fmaxf(bsdf_pdf(E.cur_mtl(), wo_s, d_vec, ns), 1e-6f);
-    const float pdf_omega_t = fmaxf(bsdf_pdf(L.cur_mtl(), wo_t, md, nt), 1e-6f);
+#if B2_MAT_LOCAL_COPY
+    const Mat m_s = E.cur_mtl(), m_t = L.cur_mtl();     // the noinline callee takes an address: of these 24 B, not of the whole vertex record
+#else
+    const Mat &m_s = E.cur_mtl(), &m_t = L.cur_mtl();
+#endif
+    const float pdf_omega_s = fmaxf(bsdf_pdf(m_s, wo_s, d_vec, ns), 1e-6f);
+    const float pdf_omega_t = fmaxf(bsdf_pdf(m_t, wo_t, md, nt), 1e-6f);
     const float inv_d2 = fast_rcp(dist2);
     const float pdf_s_to_t = pdf_omega_s * cos_t * inv_d2;
     const float pdf_t_to_s = pdf_omega_t * cos_s * inv_d2;
@@ -452,11 +457,16 @@ B2_HD bool connect_prepare(const RenderCtx &c, const EyeVtx &ev, int lv_index, S
     const float cosL = fmaxf(0.0f, dot3(lv.n, mwi));
     const int t_idx = lv_index % c.light_depth;
     const bool is_src = (lv.flags & B2_LV_SRC) != 0u;
-    const float3 fE = bsdf_evaluate(ev.mtl, ev.wo, wi, ev.n);                 // :411-412
+#if B2_MAT_LOCAL_COPY
+    const Mat m_e = ev.mtl, m_l = lv.mtl;
+#else
+    const Mat &m_e = ev.mtl, &m_l = lv.mtl;
+#endif
+    const float3 fE = bsdf_evaluate(m_e, ev.wo, wi, ev.n);                    // :411-412
     float3 fL = mk3(1.0f, 1.0f, 1.0f);
     if (!is_src && t_idx > 0) {                                               // :413-419 (previous STORED vertex)
         const float3 wo_l = normalize3(mk3(c.pool[B2_LV_F4 * (lv_index - 1)]) - lv.pos);
-        fL = bsdf_evaluate(lv.mtl, wo_l, mwi, lv.n);
+        fL = bsdf_evaluate(m_l, wo_l, mwi, lv.n);
     }
     if ((fE.x <= 0.0f && fE.y <= 0.0f && fE.z <= 0.0f) || (fL.x <= 0.0f && fL.y <= 0.0f && fL.z <= 0.0f)) return false;
     sr = make_shadow_ray(x3_add(ev.pos, x3_muls(ev.n, B2_EPSILON)), x3_add(lv.pos, x3_muls(lv.n, B2_EPSILON)));   // :424

@@ -115,11 +115,22 @@ B2_HD float bsdf_pdf_local(const Mat &m, float3 wo, float3 wi) {        // :464-
 }
 // The world-space entry points are deliberately NOT inlined on the device: the connect stage calls each of them twice
 // per pair, and inlining every copy made the kernel miss in the instruction cache (ncu: 41 % stall_no_inst).
-B2_NOINLINE float3 bsdf_evaluate(const Mat &m, float3 wo_w, float3 wi_w, float3 N) {
+#ifndef B2_MAT_LOCAL_COPY
+#define B2_MAT_LOCAL_COPY 0
+#endif
+#ifndef B2_MAT_BY_VALUE
+#define B2_MAT_BY_VALUE 0
+#endif
+#if B2_MAT_BY_VALUE
+typedef Mat MatArg;
+#else
+typedef const Mat &MatArg;
+#endif
+B2_NOINLINE float3 bsdf_evaluate(MatArg m, float3 wo_w, float3 wi_w, float3 N) {
     Frame f = make_frame(N);
     return bsdf_eval_local(m, to_local(f, wo_w), to_local(f, wi_w));
 }
-B2_NOINLINE float bsdf_pdf(const Mat &m, float3 wo_w, float3 wi_w, float3 N) {
+B2_NOINLINE float bsdf_pdf(MatArg m, float3 wo_w, float3 wi_w, float3 N) {
     Frame f = make_frame(N);
     return bsdf_pdf_local(m, to_local(f, wo_w), to_local(f, wi_w));
 }

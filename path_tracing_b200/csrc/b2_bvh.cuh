@@ -12,14 +12,14 @@
 
 #define B2_STACK_CAP 64
 
-struct RayPre { float3 o, d, idir, oid; uint32_t oct; };
+struct RayPre { float3 o, d, idir; uint32_t oct; };
 B2_HD float safe_rcp(float d) { return fabsf(d) > 1e-30f ? 1.0f / d : copysignf(1e30f, d); }
-B2_HD RayPre ray_pre(float3 o, float3 d) {
-    RayPre r; r.o = o; r.d = d;
-    r.idir = mk3(safe_rcp(d.x), safe_rcp(d.y), safe_rcp(d.z));
+B2_HD RayPre ray_pre(float3 o, float3 d, float3 idir) {          // idir = safe_rcp of d, computed elsewhere (k_connect's prepare phase)
+    RayPre r; r.o = o; r.d = d; r.idir = idir;
     r.oct = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
     return r;
 }
+B2_HD RayPre ray_pre(float3 o, float3 d) { return ray_pre(o, d, mk3(safe_rcp(d.x), safe_rcp(d.y), safe_rcp(d.z))); }
 // AABB::intersectAABB (object.cpp:104-121) with the ray's precomputed approximate reciprocals instead of three IEEE
 // divisions: only for the render's shadow rays, next to tri_test_fast (statistical parity; closest hits, b2_intersect
 // and every bit-exactness test keep group_pass).  Same accept / reject except for rays that graze a group box within rounding.
@@ -206,9 +206,8 @@ B2_HD HitRec closest_finish(const DevScene &sc, ClosestTrav &t) {
 // lane its next shadow ray while the other lanes of the warp are still walking the tree (k_connect, trace phase).
 struct AnyTrav { RayPre r; float tmax; TravPos p; };
 enum { B2_TRAV_CONTINUE = 0, B2_TRAV_HIT = 1, B2_TRAV_EXHAUSTED = 2 };
-B2_HD void any_init(AnyTrav &t, const DevScene &sc, float3 ro, float3 rd, float tmax) {
-    t.r = ray_pre(ro, rd); t.tmax = tmax; trav_reset(t.p, sc.n_nodes > 0);
-}
+B2_HD void any_init(AnyTrav &t, const DevScene &sc, const RayPre &r, float tmax) { t.r = r; t.tmax = tmax; trav_reset(t.p, sc.n_nodes > 0); }
+B2_HD void any_init(AnyTrav &t, const DevScene &sc, float3 ro, float3 rd, float tmax) { any_init(t, sc, ray_pre(ro, rd), tmax); }
 // One wide node (+ its leaf triangles).  B2_TRAV_EXHAUSTED: no triangle blocks the segment (spheres are the caller's).
 template <bool COUNT, bool FAST_TRI = false, bool OPAQUE = false>     // OPAQUE: every triangle blocks, no group cull (sc.gpu_sem callers)
 B2_HD int any_step(const DevScene &sc, AnyTrav &t, uint2 *stack, int sstride, TravCounters *cnt) {
@@ -221,9 +220,8 @@ B2_HD int any_step(const DevScene &sc, AnyTrav &t, uint2 *stack, int sstride, Tr
         const int bit = ffs32(tribits) - 1;
         tribits &= tribits - 1u;
         const int ti = tri_of_bit(tri_base, vmask, bit);
-        const float4 b = sc.tri[3 * ti + 1];
+        const float4 a = sc.tri[3 * ti], b = sc.tri[3 * ti + 1], c = sc.tri[3 * ti + 2];   // one round trip: all rows before the flag test
         if (!OPAQUE && (f2u(b.w) & B2_MAT_TRANSPARENT)) continue;
-        const float4 a = sc.tri[3 * ti], c = sc.tri[3 * ti + 2];
         if (COUNT) cnt->tris++;
         float tt;
         const bool hit = FAST_TRI ? tri_test_fast(t.r.o, t.r.d, mk3(a), mk3(b), mk3(c), tMin, t.tmax) : tri_test(t.r.o, t.r.d, mk3(a), mk3(b), mk3(c), tMin, t.tmax, tt);
@@ -263,9 +261,8 @@ B2_HD bool occluded_bvh(const DevScene &sc, float3 ro, float3 rd, float tMax, ui
                 const int bit = ffs32(tribits) - 1;
                 tribits &= tribits - 1u;
                 const int ti = tri_of_bit(tri_base, vmask, bit);
-                const float4 b = sc.tri[3 * ti + 1];
+                const float4 a = sc.tri[3 * ti], b = sc.tri[3 * ti + 1], c = sc.tri[3 * ti + 2];
                 if (!OPAQUE && (f2u(b.w) & B2_MAT_TRANSPARENT)) continue;
-                const float4 a = sc.tri[3 * ti], c = sc.tri[3 * ti + 2];
                 if (COUNT) cnt->tris++;
                 float t;
                 if (tri_test(ro, rd, mk3(a), mk3(b), mk3(c), tMin, tMax, t) && (OPAQUE || group_pass(sc, (int) f2u(c.w), ro, rd, tMin, tMax))) return true;

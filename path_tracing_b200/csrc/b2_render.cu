@@ -133,7 +133,8 @@ __global__ void __launch_bounds__(EXT_THREADS) k_extend(RenderCtx c, int n_items
 // tests and 20 in the BSDFs (profiles/r02_connect_summary.md).  One film atomicAdd per eye vertex and channel per item.
 constexpr int CONN_LOW = 32;          // pre-test another chunk while fewer pairs than this are stacked
 constexpr int CONN_MQ = 64;           // visible-pair queue: < 32 left + 32 new per trace step
-constexpr int CONN_RQ = 64;           // ready-ray queue: < 32 left + 32 new per prepare round
+constexpr int CONN_RQ = 48;           // ready-ray queue: < CONN_RQ_LOW left + 32 new per prepare round
+constexpr int CONN_RQ_LOW = 16;       // prepare another 32 pairs once fewer ready rays than this are queued (a trace step takes ~4)
 #ifndef B2_FAST_SHADOW_TRI
 #define B2_FAST_SHADOW_TRI 1          // contracted Moeller-Trumbore for the shadow rays of the connection stage (b2_isect.cuh)
 #endif
@@ -147,6 +148,8 @@ constexpr int CONN_RQ = 64;           // ready-ray queue: < 32 left + 32 new per
 struct ConnSmem {
     uint32_t pair[CONN_LOW + 32 * CONN_CHUNK];
     float rq_ox[CONN_RQ], rq_oy[CONN_RQ], rq_oz[CONN_RQ], rq_dx[CONN_RQ], rq_dy[CONN_RQ], rq_dz[CONN_RQ], rq_tmax[CONN_RQ];
+    float rq_ix[CONN_RQ], rq_iy[CONN_RQ], rq_iz[CONN_RQ];      // 1 / direction, computed by the prepare phase at full lane occupancy
+    float cur_ix[32], cur_iy[32], cur_iz[32];                  // ... of the ray each lane is tracing (read by the lane that finds a pooled triangle hit)
     float rq_px[CONN_RQ], rq_py[CONN_RQ], rq_pz[CONN_RQ]; uint32_t rq_e[CONN_RQ];
     float mq_px[CONN_MQ], mq_py[CONN_MQ], mq_pz[CONN_MQ]; uint32_t mq_e[CONN_MQ];
     float acc[3][32];
@@ -220,7 +223,7 @@ __global__ void __launch_bounds__(CONN_THREADS, CONN_BLOCKS_PER_SM) k_connect(Re
                 }
                 n_mq -= count;
                 __syncwarp();
-            } else if (n_rq < 32 && (n_buf >= 32 || (n_buf > 0 && pairs_done))) {
+            } else if (n_rq < CONN_RQ_LOW && (n_buf >= 32 || (n_buf > 0 && pairs_done))) {
                 // ---- prepare: the top min(32, n_buf) pairs become ready shadow rays ----
                 const int count = min(32, n_buf);
                 bool ok = false;
@@ -236,12 +239,13 @@ __global__ void __launch_bounds__(CONN_THREADS, CONN_BLOCKS_PER_SM) k_connect(Re
                 if (ok) {
                     const int k = n_rq + __popc(okm & lt);
                     Q.rq_ox[k] = sr.o.x; Q.rq_oy[k] = sr.o.y; Q.rq_oz[k] = sr.o.z; Q.rq_dx[k] = sr.d.x; Q.rq_dy[k] = sr.d.y; Q.rq_dz[k] = sr.d.z;
+                    Q.rq_ix[k] = safe_rcp(sr.d.x); Q.rq_iy[k] = safe_rcp(sr.d.y); Q.rq_iz[k] = safe_rcp(sr.d.z);
                     Q.rq_tmax[k] = sr.tmax; Q.rq_px[k] = ppc.x; Q.rq_py[k] = ppc.y; Q.rq_pz[k] = ppc.z; Q.rq_e[k] = pe;
                     n_shadow++;
                 }
                 n_rq += __popc(okm);
                 __syncwarp();
-            } else if (n_rq < 32 && n_buf < CONN_LOW && !pairs_done) {
+            } else if (n_rq < CONN_RQ_LOW && n_buf < CONN_LOW && !pairs_done) {
                 // ---- pre-test chunks of pool records until 32 pairs are stacked or the slice ends (one pass through the phase
                 //      selector per CHUNK cost ~30 of ~190 instructions on scenes where almost every pair is rejected: C2) ----
               do {
@@ -280,7 +284,9 @@ __global__ void __launch_bounds__(CONN_THREADS, CONN_BLOCKS_PER_SM) k_connect(Re
                     if (!busy && rank < n_rq) {
                         const int k = n_rq - 1 - rank;
                         e = Q.rq_e[k]; pc = mk3(Q.rq_px[k], Q.rq_py[k], Q.rq_pz[k]);
-                        any_init(tv, c.sc, mk3(Q.rq_ox[k], Q.rq_oy[k], Q.rq_oz[k]), mk3(Q.rq_dx[k], Q.rq_dy[k], Q.rq_dz[k]), Q.rq_tmax[k]);
+                        const float3 idir = mk3(Q.rq_ix[k], Q.rq_iy[k], Q.rq_iz[k]);
+                        any_init(tv, c.sc, ray_pre(mk3(Q.rq_ox[k], Q.rq_oy[k], Q.rq_oz[k]), mk3(Q.rq_dx[k], Q.rq_dy[k], Q.rq_dz[k]), idir), Q.rq_tmax[k]);
+                        if (POOL) { Q.cur_ix[lane] = idir.x; Q.cur_iy[lane] = idir.y; Q.cur_iz[lane] = idir.z; }
                         busy = true;
                     }
                     n_rq -= min(32 - __popc(busy_m), n_rq);
@@ -308,24 +314,27 @@ __global__ void __launch_bounds__(CONN_THREADS, CONN_BLOCKS_PER_SM) k_connect(Re
                     const int o_excl = __shfl_sync(0xffffffffu, incl - cnt, owner);
                     const uint32_t o_bits = __shfl_sync(0xffffffffu, tribits, owner), o_base = __shfl_sync(0xffffffffu, tri_base, owner);
                     const uint32_t o_vmask = __shfl_sync(0xffffffffu, vmask, owner);
+                    // the three rows of the triangle are requested together, BEFORE the owner's ray is fetched: round 2's first
+                    // version read row b, tested its transparency flag and only then asked for rows a and c - two dependent
+                    // L2 round trips, 15 % of the kernel's stall samples (profiles/r02_connect_summary.md)
+                    float4 a = mk4(mk3(0, 0, 0), 0.0f), b = a, cc = a;
+                    if (k < total) {
+                        const int ti = tri_of_bit(o_base, o_vmask, nth_bit(o_bits, k - o_excl));
+                        a = c.sc.tri[3 * ti]; b = c.sc.tri[3 * ti + 1]; cc = c.sc.tri[3 * ti + 2];
+                    }
                     const float3 ro = mk3(__shfl_sync(0xffffffffu, tv.r.o.x, owner), __shfl_sync(0xffffffffu, tv.r.o.y, owner), __shfl_sync(0xffffffffu, tv.r.o.z, owner));
                     const float3 rd = mk3(__shfl_sync(0xffffffffu, tv.r.d.x, owner), __shfl_sync(0xffffffffu, tv.r.d.y, owner), __shfl_sync(0xffffffffu, tv.r.d.z, owner));
                     const float o_tmax = __shfl_sync(0xffffffffu, tv.tmax, owner);
                     bool hit = false;
-                    if (k < total) {
-                        const int ti = tri_of_bit(o_base, o_vmask, nth_bit(o_bits, k - o_excl));
-                        const float4 b = c.sc.tri[3 * ti + 1];
-                        if (!(f2u(b.w) & B2_MAT_TRANSPARENT)) {
-                            const float4 a = c.sc.tri[3 * ti], cc = c.sc.tri[3 * ti + 2];
-                            if (COUNT) tc.tris++;
-                            float tt;
-                            if (B2_FAST_SHADOW_TRI != 0) {
-                                if (tri_test_fast(ro, rd, mk3(a), mk3(b), mk3(cc), 1e-3f, o_tmax)) {
-                                    const RayPre rp = ray_pre(ro, rd);
-                                    hit = group_pass_fast(c.sc, (int) f2u(cc.w), rp, 1e-3f, o_tmax);
-                                }
-                            } else hit = tri_test(ro, rd, mk3(a), mk3(b), mk3(cc), 1e-3f, o_tmax, tt) && group_pass(c.sc, (int) f2u(cc.w), ro, rd, 1e-3f, o_tmax);
-                        }
+                    if (k < total && !(f2u(b.w) & B2_MAT_TRANSPARENT)) {
+                        if (COUNT) tc.tris++;
+                        float tt;
+                        if (B2_FAST_SHADOW_TRI != 0) {
+                            if (tri_test_fast(ro, rd, mk3(a), mk3(b), mk3(cc), 1e-3f, o_tmax)) {
+                                const RayPre rp = ray_pre(ro, rd, mk3(Q.cur_ix[owner], Q.cur_iy[owner], Q.cur_iz[owner]));
+                                hit = group_pass_fast(c.sc, (int) f2u(cc.w), rp, 1e-3f, o_tmax);
+                            }
+                        } else hit = tri_test(ro, rd, mk3(a), mk3(b), mk3(cc), 1e-3f, o_tmax, tt) && group_pass(c.sc, (int) f2u(cc.w), ro, rd, 1e-3f, o_tmax);
                     }
                     // every lane learns which owners were hit: OR of (1 << owner) over the lanes that hit
                     blocked |= __reduce_or_sync(0xffffffffu, hit ? 1u << owner : 0u);
