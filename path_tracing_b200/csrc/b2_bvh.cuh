@@ -32,6 +32,15 @@ B2_HD bool group_pass_fast(const DevScene &sc, int g, const RayPre &r, float tmi
     tmax = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), tmax));
     return !(tmax <= tmin);
 }
+// occluded_spheres (b2_isect.cuh) with the fast sphere and group-box tests; cpu_bdpt.cpp semantics only (not sc.gpu_sem)
+B2_HD bool occluded_spheres_fast(const DevScene &sc, const RayPre &r, float tMin, float tMax) {
+    for (int i = 0; i < sc.n_sph; ++i) {
+        const float4 a = sc.sph[2 * i], b = sc.sph[2 * i + 1];
+        if (f2u(b.y) & B2_MAT_TRANSPARENT) continue;
+        if (sphere_test_fast(r.o, r.d, mk3(a), a.w, tMin, tMax) && group_pass_fast(sc, (int) f2u(b.z), r, tMin, tMax)) return true;
+    }
+    return false;
+}
 B2_HD uint32_t byte_of(uint32_t lo_word, uint32_t hi_word, int i) { return ((i < 4 ? lo_word : hi_word) >> (8 * (i & 3))) & 0xffu; }
 // (float) byte i of {lo_word, hi_word}.  Two exact forms on the device: I2F.U8 with a byte selector (one instruction on the
 // quarter-rate conversion pipe, 8 issue cycles per warp) or PRMT + FADD (one PRMT builds the float 2^23 + byte, one FADD

@@ -375,6 +375,8 @@ int b2_render_mis_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws, c
     if (p.eye_depth > B2_MIS_MAXV || p.light_depth - 1 > B2_MIS_MAXV) {          // a subpath stores at most B2_MIS_MAXV vertices, delta ones included
         b2_set_error("B2_STRATEGIES_MIS supports eye_depth <= %d and light_depth <= %d", B2_MIS_MAXV, B2_MIS_MAXV + 1); return B2_ERR_INVALID;
     }
+    // the wavefront (b2_mis_wave.cu) is the product path; B2_MIS_MEGAKERNEL=1 keeps the one-thread-per-sample kernel below for A/B runs
+    if (const char *e = getenv("B2_MIS_MEGAKERNEL"); !(e && atoi(e) != 0)) return b2_render_mis_wave_impl(sc, bvh_depth, ws, cam, p, d_film_out, st, stats);
     B2_TRY(ws.film.ensure(film_floats));
     if (!ws.ints.p) B2_TRY(ws.ints.alloc(8));
     if (!ws.counters.p) B2_TRY(ws.counters.alloc(B2_CNT_N));

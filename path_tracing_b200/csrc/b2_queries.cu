@@ -61,7 +61,7 @@ __global__ void __launch_bounds__(Q_THREADS) k_intersect(DevScene sc, const floa
             } else {
                 int r = any_step<COUNT, FAST>(sc, at, stack, blockDim.x, &tc);
                 if (r != B2_TRAV_CONTINUE) {
-                    if (r == B2_TRAV_EXHAUSTED && occluded_spheres(sc, at.r.o, at.r.d, 1e-3f, at.tmax)) r = B2_TRAV_HIT;
+                    if (r == B2_TRAV_EXHAUSTED && ((FAST && !sc.gpu_sem) ? occluded_spheres_fast(sc, at.r, 1e-3f, at.tmax) : occluded_spheres(sc, at.r.o, at.r.d, 1e-3f, at.tmax))) r = B2_TRAV_HIT;
                     prim_id[i] = r == B2_TRAV_HIT ? 0 : 1;
                     i += stride; busy = false;
                 }

@@ -133,8 +133,10 @@ __global__ void __launch_bounds__(EXT_THREADS) k_extend(RenderCtx c, int n_items
 // tests and 20 in the BSDFs (profiles/r02_connect_summary.md).  One film atomicAdd per eye vertex and channel per item.
 constexpr int CONN_LOW = 32;          // pre-test another chunk while fewer pairs than this are stacked
 constexpr int CONN_MQ = 64;           // visible-pair queue: < 32 left + 32 new per trace step
-constexpr int CONN_RQ = 48;           // ready-ray queue: < CONN_RQ_LOW left + 32 new per prepare round
-constexpr int CONN_RQ_LOW = 16;       // prepare another 32 pairs once fewer ready rays than this are queued (a trace step takes ~4)
+// ready-ray queue: < low left + 32 new per prepare round.  POOL (large scenes): a trace step frees ~4 lanes, 16 ready rays are
+// plenty and the shared memory goes to the traversal stacks; small scenes: every lane finishes its ray within the step (below),
+// so a step wants 32 ready rays
+template <bool POOL> struct ConnCfg { static constexpr int RQ = POOL ? 48 : 64, RQ_LOW = POOL ? 16 : 32; };
 #ifndef B2_FAST_SHADOW_TRI
 #define B2_FAST_SHADOW_TRI 1          // contracted Moeller-Trumbore for the shadow rays of the connection stage (b2_isect.cuh)
 #endif
@@ -145,7 +147,9 @@ constexpr int CONN_RQ_LOW = 16;       // prepare another 32 pairs once fewer rea
 #define B2_CONN_POOL_MIN_TRIS 2048    // scenes with at least this many triangles run the trace phase with the leaf triangles of the
 #endif                                // whole warp pooled (C3 spl 8: 882 -> 820 ms); below it the per-lane loop of any_step wins
                                       // (C2, 48 triangles, 1.5 triangle tests per ray: connect stage 2.94 ms vs 3.51 ms pooled)
+template <bool POOL>
 struct ConnSmem {
+    static constexpr int CONN_RQ = ConnCfg<POOL>::RQ;
     uint32_t pair[CONN_LOW + 32 * CONN_CHUNK];
     float rq_ox[CONN_RQ], rq_oy[CONN_RQ], rq_oz[CONN_RQ], rq_dx[CONN_RQ], rq_dy[CONN_RQ], rq_dz[CONN_RQ], rq_tmax[CONN_RQ];
     float rq_ix[CONN_RQ], rq_iy[CONN_RQ], rq_iz[CONN_RQ];      // 1 / direction, computed by the prepare phase at full lane occupancy
@@ -163,7 +167,8 @@ __device__ __forceinline__ int nth_bit(uint32_t bits, int j) {
 template <bool COUNT, bool POOL>
 __global__ void __launch_bounds__(CONN_THREADS, CONN_BLOCKS_PER_SM) k_connect(RenderCtx c) {
     extern __shared__ uint2 s_stack[];                    // CONN_THREADS x stack depth
-    __shared__ ConnSmem s_q[CONN_WARPS];
+    __shared__ ConnSmem<POOL> s_q[CONN_WARPS];
+    constexpr int CONN_RQ_LOW = ConnCfg<POOL>::RQ_LOW;
     const int n_cv = *c.n_cv, n_act = *c.n_pool_active;
     if (n_cv <= 0 || n_act <= 0) return;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -173,7 +178,7 @@ __global__ void __launch_bounds__(CONN_THREADS, CONN_BLOCKS_PER_SM) k_connect(Re
     const int total_warps = gridDim.x * CONN_WARPS;
     const int n_slices = max(1, min(total_warps / n_groups, n_chunks));
     const long long n_items = (long long) n_groups * n_slices;
-    ConnSmem &Q = s_q[warp];
+    ConnSmem<POOL> &Q = s_q[warp];
     uint2 *stack = s_stack + threadIdx.x;
     const float4 *__restrict__ pre = c.pre;
     uint32_t n_shadow = 0, n_path = 0;
@@ -342,16 +347,18 @@ __global__ void __launch_bounds__(CONN_THREADS, CONN_BLOCKS_PER_SM) k_connect(Re
                 if (busy) {
                     if ((blocked >> lane) & 1u) busy = false;
                     else if (exhausted) {
-                        if (!occluded_spheres(c.sc, tv.r.o, tv.r.d, 1e-3f, tv.tmax)) visible = true;
+                        if (!(B2_FAST_SHADOW_TRI != 0 ? occluded_spheres_fast(c.sc, tv.r, 1e-3f, tv.tmax) : occluded_spheres(c.sc, tv.r.o, tv.r.d, 1e-3f, tv.tmax))) visible = true;
                         busy = false;
                     }
                 }
               } else if (busy) {
-                    int r = any_step<COUNT, B2_FAST_SHADOW_TRI != 0>(c.sc, tv, stack, CONN_THREADS, &tc);
-                    if (r == B2_TRAV_EXHAUSTED) {
-                        if (occluded_spheres(c.sc, tv.r.o, tv.r.d, 1e-3f, tv.tmax)) r = B2_TRAV_HIT; else visible = true;
-                    }
-                    if (r != B2_TRAV_CONTINUE) busy = false;
+                    // small scenes (a ray visits 1-3 wide nodes): every lane walks its ray to the end, so the next step starts with
+                    // 32 free lanes and 32 ready rays.  One step per pass through the phase selector ran the node tests at 14 of 32
+                    // lanes and the sphere tests at 12 on C1 (profiles/r02_small_scenes.md)
+                    int r;
+                    do r = any_step<COUNT, B2_FAST_SHADOW_TRI != 0>(c.sc, tv, stack, CONN_THREADS, &tc); while (r == B2_TRAV_CONTINUE);
+                    if (r == B2_TRAV_EXHAUSTED) visible = !(B2_FAST_SHADOW_TRI != 0 ? occluded_spheres_fast(c.sc, tv.r, 1e-3f, tv.tmax) : occluded_spheres(c.sc, tv.r.o, tv.r.d, 1e-3f, tv.tmax));
+                    busy = false;
               }
                 const uint32_t vm = __ballot_sync(0xffffffffu, visible);
                 if (vm) {
@@ -476,6 +483,7 @@ void RenderWorkspace::release() {
     pool.release(); pre.release(); film.release(); ints.release(); counters.release();
     hp_in.release(); hp.release(); flux.release(); hp_keys.release(); hp_keys_sorted.release(); hp_order.release(); hp_order_sorted.release();
     cell_table.release(); sort_tmp.release();
+    mw_f4.release(); mw_i32.release(); mw_pairs.release();
     if (h_ints) { cudaFreeHost(h_ints); h_ints = nullptr; }
     cap_paths = cap_depth = cap_pool = 0;
 }
@@ -555,7 +563,7 @@ static int set_smem_limits(int bvh_depth) {
     B2_CUDA(cudaGetDevice(&dev));
     if (dev < 64 && bvh_depth + 1 <= configured[dev]) return B2_OK;
     const size_t sb_t = stack_bytes(EXT_THREADS, bvh_depth), sb_c = stack_bytes(CONN_THREADS, bvh_depth);
-    if (sb_c + sizeof(ConnSmem) * CONN_WARPS + 64 > 227 * 1024) {
+    if (sb_c + std::max(sizeof(ConnSmem<true>), sizeof(ConnSmem<false>)) * CONN_WARPS + 64 > 227 * 1024) {
         b2_set_error("BVH depth %d needs more shared memory for traversal stacks than a CTA has", bvh_depth); return B2_ERR_STATE;
     }
     B2_CUDA(cudaFuncSetAttribute(k_light_paths<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb_t));

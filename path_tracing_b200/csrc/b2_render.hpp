@@ -24,6 +24,9 @@ struct RenderWorkspace {
     DevBuf<ulonglong2> cell_table;
     DevBuf<unsigned char> sort_tmp;
     int ensure_ppm(int n_pix, size_t film_floats, size_t sort_tmp_bytes);
+    // B2_STRATEGIES_MIS as a wavefront (b2_mis_wave.cu): walk state, stored light vertices, eye history and records; counters + queues; pairs
+    DevBuf<float4> mw_f4; DevBuf<int> mw_i32; DevBuf<uint2> mw_pairs;
+    int ensure_mis_wave(int slots, int n_lights, size_t film_floats);
     void release();
     ~RenderWorkspace() { release(); }
 };
@@ -36,6 +39,8 @@ int b2_render_ppm_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws, c
                        float *d_film_out, cudaStream_t st, B2Stats *stats);
 int b2_render_mis_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws, const B2Camera &cam, const B2RenderParams &p,
                        float *d_film_out, cudaStream_t st, B2Stats *stats);      // B2_STRATEGIES_MIS (b2_mis.cuh)
+int b2_render_mis_wave_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws, const B2Camera &cam, const B2RenderParams &p,
+                            float *d_film_out, cudaStream_t st, B2Stats *stats); // ... as a wavefront (b2_mis_wave.cu), the default
 
 // d_film_out: W*H*3 floats on the device.  Blocks until `st` has drained the render (the counters are read back).
 int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws, const B2Camera &cam, const B2RenderParams &p,

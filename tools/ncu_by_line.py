@@ -1,6 +1,9 @@
 """Attribute the per-instruction counters of one `ncu --set full --import-source on` capture to source lines.
 
-    python tools/ncu_by_line.py <report.ncu-rep> <object.o> <kernel-substring> [--top N]
+    python tools/ncu_by_line.py <report.ncu-rep> <object.o> <mangled-kernel-substring> [--match <demangled substring>] [--top N]
+
+(<mangled-kernel-substring> selects the function in the object, e.g. k_connectILb0ELb1; --match selects the kernel in the
+report, e.g. "k_connect<(bool)0, (bool)1>"; default: the first kernel of the report)
 
 ncu's CSV source page carries counters only in its SASS view; this maps each SASS address back to source through
 `nvdisasm --print-line-info-inline` of the SAME object (build/obj/*.o, -lineinfo) and prints, for executed warp instructions and
@@ -46,7 +49,9 @@ def main():
     amap = line_map(obj, kernel)
     out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "sass"], capture_output=True, text=True).stdout
     blocks = out.split('"Kernel Name",')
-    blk = [b for b in blocks if kernel in b.split("\n", 1)[0] or "k_connect" in b.split("\n", 1)[0]]
+    match = sys.argv[sys.argv.index("--match") + 1] if "--match" in sys.argv else None
+    blk = [b for b in blocks[1:] if match is None or match in b.split("\n", 1)[0]]
+    print("report kernel:", blk[0].split("\n", 1)[0].strip().strip(",").strip('"'))
     rows = list(csv.reader(io.StringIO(blk[0].split("\n", 1)[1])))
     hdr = rows[0]
     ia, ii, isamp = hdr.index("Address"), hdr.index("Instructions Executed"), hdr.index("# Samples")
