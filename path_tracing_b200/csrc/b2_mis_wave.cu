@@ -492,8 +492,9 @@ int b2_render_mis_wave_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &
     int n_my = 0;
     for (long long s = p.sample_offset; s < p.spp; s += stride) n_my++;
     const long long total = (long long) npix * n_my;
-    // batch: 2^20 samples (3.1 GB of wave state) unless the caller says otherwise; halved until it fits half of the free memory
-    long long batch = p.max_batch_paths > 0 ? p.max_batch_paths : (1ll << 20);
+    // batch: 2^22 samples (12.4 GB of wave state; one host read per bounce, so few large batches) unless the caller says
+    // otherwise; halved until it fits half of the free memory
+    long long batch = p.max_batch_paths > 0 ? p.max_batch_paths : (1ll << 22);
     batch = std::max<long long>(1, std::min(batch, std::max<long long>(total, 1)));
     {
         size_t free_b = 0, total_b = 0;

@@ -140,6 +140,30 @@ def test_mis_mode_equals_its_host_compilation_and_shards(tmp_path):
     hs.close(); sc.close()
 
 
+def test_mis_wavefront_equals_the_one_thread_per_sample_kernel(tmp_path, monkeypatch):
+    """csrc/b2_mis_wave.cu (the product path: light / eye bounces, pre-test and connection as separate dense kernels over HBM
+    records) against csrc/b2_mis.cuh's kernel (B2_MIS_MEGAKERNEL=1) on the same Philox streams: the same paths, so the ray and
+    path counters are EQUAL (at most a weight that rounds differently moves one) and the films differ by the order of the film
+    atomics only; small batches force several batches and every queue swap."""
+    from path_tracing_b200.scene import reference_scene
+    for sd, kw in ((box_scene(tmp_path), dict(width=40, height=30, spp=8, eye_depth=4, light_depth=5, seed=3)),
+                   (reference_scene("cornell"), dict(width=64, height=64, spp=4, eye_depth=6, light_depth=7, seed=2, max_batch_paths=5000)),
+                   (reference_scene("mis_variant"), dict(width=64, height=64, spp=4, eye_depth=8, light_depth=9, seed=1))):
+        sc = api.Scene(sd)
+        monkeypatch.setenv("B2_MIS_MEGAKERNEL", "1")
+        mega, sm = sc.render_bdpt(strategies=api.STRATEGIES_MIS, spl=1, **kw)
+        monkeypatch.delenv("B2_MIS_MEGAKERNEL")
+        wave, sw = sc.render_bdpt(strategies=api.STRATEGIES_MIS, spl=1, **kw)
+        assert sw["n_launches"] > sm["n_launches"]                       # the wavefront really ran
+        for k in ("eye_samples", "closest_rays"):
+            assert sw[k] == sm[k], k
+        for k in ("shadow_rays", "path_samples"):
+            assert abs(int(sw[k]) - int(sm[k])) <= 2 + 1e-6 * int(sm[k]), (k, sw[k], sm[k])
+        d = np.abs(wave - mega)
+        assert (d <= 1e-4 * np.abs(mega) + 1e-6).mean() >= 0.999 and abs(wave.mean() - mega.mean()) <= 1e-5 * mega.mean()
+        sc.close()
+
+
 def test_pt_cli_strategies_flag_selects_the_mis_mode(tmp_path):
     """`pt_cli --mode bdpt --strategies mis` == `render_bdpt(strategies=STRATEGIES_MIS)` on the same scene text and seed."""
     import subprocess
