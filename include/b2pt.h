@@ -169,6 +169,9 @@ int b2_render_bdpt_device(B2Scene *scene, const B2Camera *cam, const B2RenderPar
  * reduce (NCCL is dlopen'ed on first use) and resolved per params->film_mode.  stats: counters summed, ms_total = max. */
 int b2_render_bdpt_multi(B2Scene **scenes, int n_gpus, const B2Camera *cam, const B2RenderParams *params,
                          float *film_rgb_host, B2Stats *stats);
+/* Optional: create the NCCL communicators for this device list ahead of the first b2_render_bdpt_multi (ncclCommInitAll
+ * takes seconds on an 8-GPU node; without this call the first multi-GPU render pays for it).  No reference counterpart. */
+int b2_multi_init(const int *devices, int n_gpus);
 /* Progressive rendering, the one non-graphics behaviour of the reference viewer (src/main.cpp:399-531), headless:
  * `passes` renders of params->spp samples per pixel, pass k with Philox key params->seed + k (so every pass draws a new
  * light pool), added into a running sum; film_rgb_host receives sum / passes.  rms (may be NULL, else `passes` floats):

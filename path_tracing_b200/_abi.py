@@ -67,7 +67,7 @@ PARSE_OBJ_DIRECTIVE = 1
 SYMBOLS = [
     "b2_last_error", "b2_device_count", "b2_version", "b2_scene_create", "b2_scene_build_bvh", "b2_scene_bvh_info",
     "b2_scene_destroy", "b2_intersect", "b2_intersect_device", "b2_intersect_counters", "b2_render_bdpt",
-    "b2_render_bdpt_device", "b2_render_bdpt_multi", "b2_light_pool", "b2_light_pool_device_noalloc", "b2_bsdf_evaluate", "b2_bsdf_pdf", "b2_bsdf_sample", "b2_mis_weight",
+    "b2_render_bdpt_device", "b2_render_bdpt_multi", "b2_multi_init", "b2_light_pool", "b2_light_pool_device_noalloc", "b2_bsdf_evaluate", "b2_bsdf_pdf", "b2_bsdf_sample", "b2_mis_weight",
     "b2_philox", "b2_parse_scene_file", "b2_parsed_scene_free", "b2_film_to_rgb8", "b2_write_image",
     "b2_obj_default_options", "b2_obj_has_tinyobj", "b2_load_obj", "b2_parse_scene_file_ex", "b2_render_bdpt_progressive", "b2_frame_rms",
     "b2_measure_fp32_peak", "b2_measure_l2_bandwidth",
@@ -102,6 +102,7 @@ def lib():
         L.b2_render_bdpt.argtypes = [vp, vp, C.POINTER(RenderParams), vp, C.POINTER(Stats)]
         L.b2_render_bdpt_device.argtypes = [vp, vp, C.POINTER(RenderParams), vp, vp, C.POINTER(Stats)]
         L.b2_render_bdpt_multi.argtypes = [C.POINTER(vp), i32, vp, C.POINTER(RenderParams), vp, C.POINTER(Stats)]
+        L.b2_multi_init.argtypes = [C.POINTER(i32), i32]
         L.b2_light_pool.argtypes = [vp, C.POINTER(RenderParams), vp]
         L.b2_light_pool_device_noalloc.argtypes = [vp, C.POINTER(RenderParams), vp, vp]
         L.b2_bsdf_evaluate.argtypes = [sz, vp, vp, vp, vp, vp]

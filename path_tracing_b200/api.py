@@ -178,6 +178,12 @@ class Scene:
         return out
 
 
+def multi_init(devices):
+    """NCCL communicators for `devices` ahead of the first render_bdpt_multi (b2_multi_init): seconds on an 8-GPU node."""
+    arr = (C.c_int32 * len(devices))(*[int(d) for d in devices])
+    A.check(A.lib().b2_multi_init(arr, len(devices)))
+
+
 def render_bdpt_multi(scenes, camera=None, width=None, height=None, spp=8, spl=8, eye_depth=4, light_depth=4, seed=1,
                       film_mode=FILM_MEAN, max_batch_paths=0, integrator=INTEGRATOR_BDPT):
     """One process, len(scenes) GPUs (b2_render_bdpt_multi): scenes[g] is the same SceneData created on device g."""

@@ -207,6 +207,8 @@ int b2_render_bdpt(B2Scene *s, const B2Camera *cam, const B2RenderParams *params
     B2_TRY(b2_check_built(s));
     if (!cam || !params || !film_rgb_host) { b2_set_error("NULL argument"); return B2_ERR_INVALID; }
     if (params->width <= 0 || params->height <= 0) { b2_set_error("invalid film size"); return B2_ERR_INVALID; }
+    // B2_FILM_ACCUMULATE adds into the caller's DEVICE film; here the film is a scratch buffer that still holds the previous call's image
+    if (params->film_mode != B2_FILM_MEAN && params->film_mode != B2_FILM_SUM) { b2_set_error("film_mode must be B2_FILM_MEAN or B2_FILM_SUM here (B2_FILM_ACCUMULATE: device entry point only)"); return B2_ERR_INVALID; }
     std::lock_guard<std::mutex> lk(s->mtx);
     B2_CUDA(cudaSetDevice(s->device));
     const size_t nf = (size_t) 3 * params->width * params->height;

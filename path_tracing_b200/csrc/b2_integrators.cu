@@ -299,6 +299,13 @@ int b2_render_pt_impl(const DevScene &sc_in, int bvh_depth, RenderWorkspace &ws,
     const long long total = (long long) npix * n_my;
     long long mp = p.max_batch_paths > 0 ? p.max_batch_paths : (1ll << 26);     // 72 B of state per path: 4.8 GB at 2^26
     mp = std::max<long long>(std::min<long long>(mp, std::max<long long>(total, 1)), 1);
+    {   // halve the batch until its state (4 float4 rows, two queues, the 80-byte vertex records) fits half of the free memory
+        size_t free_b = 0, total_b = 0;
+        B2_CUDA(cudaMemGetInfo(&free_b, &total_b));
+        const size_t per_path = 4 * sizeof(float4) + 2 * sizeof(int) + (size_t) B2_CV_F4 * sizeof(float4);
+        const size_t have = (ws.ray_o.n + ws.ray_d.n + ws.thr.n + ws.last_pos.n + ws.cv.n) * sizeof(float4) + (ws.live_a.n + ws.live_b.n) * sizeof(int);
+        while (mp > 4096 && per_path * (size_t) mp > (free_b + have) / 2) mp /= 2;
+    }
     const int max_paths = (int) mp;
     B2_TRY(ws.ensure_pt(max_paths, film_floats));
     B2_TRY(set_limits(bvh_depth));

@@ -5,12 +5,13 @@
 // (tests/hostsim) and the A/B switch B2_MIS_MEGAKERNEL=1 run.  Here the same arithmetic, the same Philox streams and the
 // same acceptance tests are cut into stages whose items are dense:
 //
-//   k_mw_light   one bounce of every LIVE light subpath: closest hit, vertex record to HBM, the m = n strategy (camera
-//                connection + splat), BSDF sample; survivors compacted with one atomic per warp
-//   k_mw_eye     one bounce of every LIVE eye subpath: closest hit, emitter, vertex record for the connection stage,
-//                BSDF sample; survivors compacted
-//   k_mw_pretest (eye vertex of this bounce) x (every light, every stored light vertex of ITS sample): the geometric tests
-//                only; surviving pairs appended to a compact list
+//   k_mw_light   one bounce of every LIVE light subpath: closest hit, vertex record to HBM, a (slot, vertex) record if the
+//                vertex projects into the film (m = n strategy), BSDF sample; survivors compacted with one atomic per warp
+//   k_mw_splat   once per batch, over the compact list of stored light vertices inside the camera frustum: BSDF, densities,
+//                balance weight, shadow ray to the pinhole, film splat
+//   k_mw_eye     one bounce of every LIVE eye subpath: closest hit, emitter, vertex record for the connection stage, the
+//                geometric tests of the vertex against every light and every stored light vertex of ITS sample (surviving
+//                pairs appended to a compact list), BSDF sample; survivors compacted
 //   k_mw_connect one thread per surviving pair: both BSDFs, the density arrays of the joined path, balance weight, shadow
 //                ray, film atomic
 //
@@ -81,7 +82,6 @@ __global__ void __launch_bounds__(MW_THREADS) k_mw_light(RenderCtx c, CamFrame c
     const int item = blockIdx.x * blockDim.x + threadIdx.x;
     const DevScene &sc = c.sc;
     const int n_cap = c.eye_depth, l_cap = c.light_depth - 1;
-    const float inv_nl = 1.0f / (float) sc.n_lights, wh = (float) c.W * (float) c.H;
     TravCounters tc{ 0u, 0u };
     MisCounters cnt{ 0u, 0u, 0u };
     bool alive = item < n_items;
@@ -144,31 +144,11 @@ __global__ void __launch_bounds__(MW_THREADS) k_mw_light(RenderCtx c, CamFrame c
         store_lv_vertex(w, S, slot, v); S++;
         if (!v.delta && nd <= n_cap && camera_project(c, cf, v.pos, px, cos_c, d2c, to_eye)) { cos_y = dot3(v.n, to_eye); splat = cos_y > 0.0f; }
     }
-    float wgt = 0.0f;
-    float3 f = mk3(0, 0, 0);
-    if (splat) {
-        f = bsdf_evaluate(v.mtl, to_eye, v.wo, v.n);
-        if (f.x > 0.0f || f.y > 0.0f || f.z > 0.0f) {
-            float pL[B2_MIS_MAXV + 2], pE[B2_MIS_MAXV + 2];
-            unsigned char dl[B2_MIS_MAXV + 2];
-            const int n = S;
-            light_densities(w, slot, n - 1, pL, pE, dl);
-            pL[n] = v.pdf_fwd; dl[n] = (unsigned char) v.delta;
-            pE[n] = camera_area_pdf(cf, cos_y, cos_c, d2c);
-            if (n >= 2) {
-                const float3 ppos = mk3(lvrow(w, n - 2, 0, slot)), pn = mk3(lvrow(w, n - 2, 1, slot));
-                const float3 dv = ppos - v.pos;
-                pE[n - 1] = area_pdf(bsdf_pdf(v.mtl, to_eye, v.wo, v.n), pn, v.wo, dot3(dv, dv));
-            }
-            wgt = mis_balance(pL, pE, dl, n, n, l_cap, inv_nl, wh);
-        }
-    }
-    if (wgt > 0.0f) {
-        cnt.shadow++;
-        if (!mis_occluded<COUNT>(sc, x3_add(v.pos, x3_muls(v.n, B2_EPSILON)), c.cam_eye, stack, blockDim.x, &tc)) {
-            const float3 val = alpha * f * (wgt * camera_area_pdf(cf, cos_y, cos_c, d2c) / wh);
-            if (valid_color(val)) { film_add(c, px, val); cnt.paths++; }
-        }
+    // the camera connection itself (BSDF, densities, weight, shadow ray, splat) runs in k_mw_splat over a compact list of
+    // (slot, vertex) records once the light phase is over: few lanes of a warp have a vertex inside the frustum
+    {
+        const int ri = warp_alloc(&w.ints[MW_N_PAIRS], splat);
+        if (splat) w.pairs[ri] = make_uint2((uint32_t) slot, (uint32_t) (S - 1));
     }
     if (alive && ((!v.delta && nd == l_cap) || S >= B2_MIS_MAXV)) alive = false;
     BsdfSample bs; bs.wi = mk3(0, 0, 0); bs.f = mk3(0, 0, 0); bs.pdf = 0.0f; bs.new_eta = eta; bs.is_delta = false;
@@ -215,6 +195,77 @@ __global__ void __launch_bounds__(MW_THREADS) k_mw_light(RenderCtx c, CamFrame c
     warp_count_add(&c.counters[B2_CNT_SHADOW], cnt.shadow);
     warp_count_add(&c.counters[B2_CNT_PATH_SAMPLES], cnt.paths);
     if (COUNT) { warp_count_add(&c.counters[B2_CNT_NODES], tc.nodes); warp_count_add(&c.counters[B2_CNT_TRIS], tc.tris); }
+}
+
+// ---------------- m = n: stored light vertex -> pinhole (the splat block of mis_sample_body's light walk) ----------------
+template <bool COUNT>
+__global__ void __launch_bounds__(MW_THREADS) k_mw_splat(RenderCtx c, CamFrame cf, MisWave w) {
+    extern __shared__ uint2 s_stack[];
+    uint2 *stack = s_stack + threadIdx.x;
+    const DevScene &sc = c.sc;
+    const int l_cap = c.light_depth - 1;
+    const float inv_nl = 1.0f / (float) sc.n_lights, wh = (float) c.W * (float) c.H;
+    const int n_rec = w.ints[MW_N_PAIRS];
+    TravCounters tc{ 0u, 0u };
+    MisCounters cnt{ 0u, 0u, 0u };
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_rec; i += gridDim.x * blockDim.x) {
+        const uint2 rec = w.pairs[i];
+        const int slot = (int) rec.x, n = (int) rec.y + 1;                    // the path has n surface vertices
+        const MisVtx v = load_lv_vertex(w, n - 1, slot);
+        uint32_t px = 0; float cos_c = 1.0f, d2c = 1.0f; float3 to_eye = mk3(0, 0, 1);
+        if (!camera_project(c, cf, v.pos, px, cos_c, d2c, to_eye)) continue;   // (it did in k_mw_light: same arithmetic)
+        const float cos_y = dot3(v.n, to_eye);
+        float wgt = 0.0f;
+        const float3 f = bsdf_evaluate(v.mtl, to_eye, v.wo, v.n);
+        if (f.x > 0.0f || f.y > 0.0f || f.z > 0.0f) {
+            float pL[B2_MIS_MAXV + 2], pE[B2_MIS_MAXV + 2];
+            unsigned char dl[B2_MIS_MAXV + 2];
+            light_densities(w, slot, n - 1, pL, pE, dl);
+            pL[n] = v.pdf_fwd; dl[n] = (unsigned char) v.delta;
+            pE[n] = camera_area_pdf(cf, cos_y, cos_c, d2c);
+            if (n >= 2) {
+                const float3 ppos = mk3(lvrow(w, n - 2, 0, slot)), pn = mk3(lvrow(w, n - 2, 1, slot));
+                const float3 dv = ppos - v.pos;
+                pE[n - 1] = area_pdf(bsdf_pdf(v.mtl, to_eye, v.wo, v.n), pn, v.wo, dot3(dv, dv));
+            }
+            wgt = mis_balance(pL, pE, dl, n, n, l_cap, inv_nl, wh);
+        }
+        if (wgt > 0.0f) {
+            cnt.shadow++;
+            if (!mis_occluded<COUNT>(sc, x3_add(v.pos, x3_muls(v.n, B2_EPSILON)), c.cam_eye, stack, blockDim.x, &tc)) {
+                const float3 val = v.beta * f * (wgt * camera_area_pdf(cf, cos_y, cos_c, d2c) / wh);
+                if (valid_color(val)) { film_add(c, px, val); cnt.paths++; }
+            }
+        }
+    }
+    warp_count_add(&c.counters[B2_CNT_SHADOW], cnt.shadow);
+    warp_count_add(&c.counters[B2_CNT_PATH_SAMPLES], cnt.paths);
+    if (COUNT) { warp_count_add(&c.counters[B2_CNT_NODES], tc.nodes); warp_count_add(&c.counters[B2_CNT_TRIS], tc.tris); }
+}
+
+// ---------------- connection stage, cheap part: does (eye vertex, candidate) pass the geometric tests ----------------
+// candidate j < n_lights: light j (m = 0, next-event estimation); else stored light vertex j - n_lights of the eye vertex's own sample
+__device__ __forceinline__ bool mw_candidate_passes(const RenderCtx &c, const MisWave &w, int slot, float3 pos, float3 n, int nd_e, int cand) {
+    const DevScene &sc = c.sc;
+    if (cand < sc.n_lights) {
+        const SpotLight L = spot_light(sc, cand);
+        if (L.parallel) return false;
+        const float3 d = pos - L.pos;
+        const float d2 = dot3(d, d);
+        if (d2 < 1e-12f) return false;
+        const float3 om = d * fast_rsqrt(d2);
+        if (dot3(om, L.dir) < L.cos_cut) return false;
+        return dot3(n, om * -1.0f) > 0.0f;
+    }
+    const int k = cand - sc.n_lights;
+    const uint32_t fl = f2u(lvrow(w, k, 2, slot).w);
+    if ((fl & 1u) || (int) (fl >> 1) + nd_e > c.eye_depth) return false;
+    const float3 ypos = mk3(lvrow(w, k, 0, slot)), yn = mk3(lvrow(w, k, 1, slot));
+    const float3 dv = ypos - pos;
+    const float d2 = dot3(dv, dv);
+    if (d2 < 1e-10f) return false;
+    const float3 wz = dv * fast_rsqrt(d2);
+    return dot3(n, wz) > 0.0f && dot3(yn, wz * -1.0f) > 0.0f;
 }
 
 // ---------------- eye subpaths: one bounce (the eye walk of mis_sample_body without its candidate loop) ----------------
@@ -287,6 +338,17 @@ __global__ void __launch_bounds__(MW_THREADS) k_mw_eye(RenderCtx c, CamFrame cf,
         w.cv[5 * N + q] = mk4(prev_n, s.mtl.metallic);
         w.cv[6 * N + q] = make_float4(s.mtl.eta, 0.0f, 0.0f, 0.0f);
     }
+    // the geometric tests of this vertex against its candidates, here, where the vertex is in registers and neighbouring
+    // threads hold neighbouring slots (a separate kernel over a (vertex, candidate) grid was 22 % of the render at 15 lanes
+    // and 17 % of the issue slots: most of the grid is empty and its loads stride by the batch size)
+    {
+        const int n_cand = connects ? sc.n_lights + w.l_count[slot] : 0;
+        for (int cand = 0; __any_sync(0xffffffffu, cand < n_cand); ++cand) {
+            const bool have = cand < n_cand && mw_candidate_passes(c, w, slot, s.pos, s.n, nd_e, cand);
+            const int pi = warp_alloc(&w.ints[MW_N_PAIRS], have);
+            if (have) w.pairs[pi] = make_uint2((uint32_t) q, (uint32_t) cand);
+        }
+    }
     if (alive && ((!delta && nd_e == n_cap) || T >= B2_MIS_MAXV)) alive = false;
     BsdfSample bs; bs.wi = mk3(0, 0, 0); bs.f = mk3(0, 0, 0); bs.pdf = 0.0f; bs.new_eta = eta; bs.is_delta = false;
     if (alive) {
@@ -324,52 +386,6 @@ __global__ void __launch_bounds__(MW_THREADS) k_mw_eye(RenderCtx c, CamFrame cf,
     if (COUNT) { warp_count_add(&c.counters[B2_CNT_NODES], tc.nodes); warp_count_add(&c.counters[B2_CNT_TRIS], tc.tris); }
 }
 
-// ---------------- connection stage, cheap part: which (eye vertex, candidate) pairs pass the geometric tests ----------------
-// candidate j < n_lights: light j (m = 0, next-event estimation); else stored light vertex j - n_lights of the eye vertex's own sample
-__global__ void __launch_bounds__(256) k_mw_pretest(RenderCtx c, MisWave w, int J) {
-    const DevScene &sc = c.sc;
-    const int n_cv = w.ints[MW_N_CV];
-    const long long total = (long long) n_cv * J;
-    const size_t N = (size_t) w.N;
-    for (long long idx = (long long) blockIdx.x * blockDim.x + threadIdx.x; idx - (long long) (threadIdx.x & 31) < total; idx += (long long) gridDim.x * blockDim.x) {
-        bool have = false;
-        int q = 0, cand = 0;
-        if (idx < total) {
-            q = (int) (idx / J); cand = (int) (idx % J);
-            const float4 r0 = w.cv[0 * N + q], r1 = w.cv[1 * N + q];
-            const float3 pos = mk3(r0), n = mk3(r1);
-            const int nd_e = (int) (f2u(r1.w) >> 8);
-            if (cand < sc.n_lights) {
-                const SpotLight L = spot_light(sc, cand);
-                if (!L.parallel) {
-                    const float3 d = pos - L.pos;
-                    const float d2 = dot3(d, d);
-                    if (!(d2 < 1e-12f)) {
-                        const float3 om = d * fast_rsqrt(d2);
-                        if (!(dot3(om, L.dir) < L.cos_cut)) have = dot3(n, om * -1.0f) > 0.0f;
-                    }
-                }
-            } else {
-                const int slot = (int) f2u(w.cv[2 * N + q].w), k = cand - sc.n_lights;
-                if (k < w.l_count[slot]) {
-                    const uint32_t fl = f2u(lvrow(w, k, 2, slot).w);
-                    if (!(fl & 1u) && (int) (fl >> 1) + nd_e <= c.eye_depth) {
-                        const float3 ypos = mk3(lvrow(w, k, 0, slot)), yn = mk3(lvrow(w, k, 1, slot));
-                        const float3 dv = ypos - pos;
-                        const float d2 = dot3(dv, dv);
-                        if (!(d2 < 1e-10f)) {
-                            const float3 wz = dv * fast_rsqrt(d2);
-                            have = dot3(n, wz) > 0.0f && dot3(yn, wz * -1.0f) > 0.0f;
-                        }
-                    }
-                }
-            }
-        }
-        const int pi = warp_alloc(&w.ints[MW_N_PAIRS], have);
-        if (have) w.pairs[pi] = make_uint2((uint32_t) q, (uint32_t) cand);
-    }
-}
-
 // ---------------- connection stage, expensive part: BSDFs, densities of the joined path, weight, shadow ray ----------------
 template <bool COUNT>
 __global__ void __launch_bounds__(MW_THREADS) k_mw_connect(RenderCtx c, MisWave w) {
@@ -393,7 +409,7 @@ __global__ void __launch_bounds__(MW_THREADS) k_mw_connect(RenderCtx c, MisWave 
         const float3 wo = mk3(r2), rd = wo * -1.0f, thr = mk3(r3), prev_n = mk3(r5);
         const int slot = (int) f2u(r2.w);
         const uint32_t pixel = f2u(r3.w);
-        // the candidate again (k_mw_pretest kept only the pair's indices)
+        // the candidate again (the eye bounce kept only the pair's indices)
         int m = 0; float d2 = 1.0f, cos_z = 0.0f, cos_y = 0.0f; float3 wz = mk3(0, 0, 1), target = mk3(0, 0, 0), scale = mk3(0, 0, 0);
         MisVtx y; y.pos = y.n = y.wo = y.beta = mk3(0, 0, 0); y.mtl = s.mtl; y.pdf_fwd = y.pdf_rev = 0.0f; y.delta = 0; y.nd = 0;
         if (cand < sc.n_lights) {
@@ -515,6 +531,8 @@ int b2_render_mis_wave_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &
             B2_CUDA(cudaFuncSetAttribute(k_mw_light<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb));
             B2_CUDA(cudaFuncSetAttribute(k_mw_eye<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb));
             B2_CUDA(cudaFuncSetAttribute(k_mw_eye<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb));
+            B2_CUDA(cudaFuncSetAttribute(k_mw_splat<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb));
+            B2_CUDA(cudaFuncSetAttribute(k_mw_splat<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb));
             B2_CUDA(cudaFuncSetAttribute(k_mw_connect<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb));
             B2_CUDA(cudaFuncSetAttribute(k_mw_connect<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb));
             if (dev < 64) configured[dev] = bvh_depth + 1;
@@ -568,6 +586,14 @@ int b2_render_mis_wave_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &
             n_live = h[MW_N_LIVE_NEXT];
             std::swap(w.live, w.live_next);
         }
+        {   // the camera connections of every stored light vertex that lies inside the frustum (records gathered by the light bounces)
+            const long long n_rec = h[MW_N_PAIRS];
+            if (n_rec > 0) {
+                if (count) k_mw_splat<true><<<(unsigned) std::min<long long>(blocks_of(n_rec, MW_THREADS), conn_grid), MW_THREADS, sb, st>>>(c, cf, w);
+                else k_mw_splat<false><<<(unsigned) std::min<long long>(blocks_of(n_rec, MW_THREADS), conn_grid), MW_THREADS, sb, st>>>(c, cf, w);
+                n_launches++;
+            }
+        }
         const int J = sc.n_lights + std::min(h[MW_S_MAX], B2_MIS_MAXV);
         // ---- eye subpaths: a bounce, then its vertices against the lights and the light vertices of their own samples ----
         n_live = n;
@@ -575,11 +601,10 @@ int b2_render_mis_wave_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &
             B2_CUDA(cudaMemsetAsync(w.ints, 0, 3 * sizeof(int), st));       // n_live_next, n_cv, n_pairs
             if (count) k_mw_eye<true><<<blocks_of(n_live, MW_THREADS), MW_THREADS, sb, st>>>(c, cf, w, n_live, step, pix0, s0);
             else k_mw_eye<false><<<blocks_of(n_live, MW_THREADS), MW_THREADS, sb, st>>>(c, cf, w, n_live, step, pix0, s0);
-            const long long cand = (long long) n_live * J;                   // n_cv <= n_live
-            k_mw_pretest<<<(unsigned) std::min<long long>(blocks_of(cand, 256), (long long) sc.n_sms * 32), 256, 0, st>>>(c, w, J);
+            const long long cand = (long long) n_live * J;                   // n_pairs <= n_cv * J <= n_live * J
             if (count) k_mw_connect<true><<<(unsigned) std::min<long long>(blocks_of(cand, MW_THREADS), conn_grid), MW_THREADS, sb, st>>>(c, w);
             else k_mw_connect<false><<<(unsigned) std::min<long long>(blocks_of(cand, MW_THREADS), conn_grid), MW_THREADS, sb, st>>>(c, w);
-            n_launches += 3; n_waves++;
+            n_launches += 2; n_waves++;
             B2_TRY(read_ints());
             n_live = h[MW_N_LIVE_NEXT];
             std::swap(w.live, w.live_next);

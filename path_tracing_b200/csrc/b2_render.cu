@@ -734,6 +734,7 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
 
 int b2_light_pool_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws, const B2RenderParams &p, float *pool20_host, cudaStream_t st) {
     if (p.spl < 0 || p.light_depth <= 0) { b2_set_error("invalid spl / light_depth"); return B2_ERR_INVALID; }
+    if ((long long) sc.n_lights * p.spl * p.light_depth >= (1ll << 27)) { b2_set_error("light pool larger than 2^27 vertices is not supported"); return B2_ERR_INVALID; }
     const int n_pool = sc.n_lights * p.spl * p.light_depth;
     if (n_pool == 0) return B2_OK;
     B2_TRY(ws.ensure(1, 1, n_pool, 3));

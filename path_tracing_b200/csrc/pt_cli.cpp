@@ -111,6 +111,11 @@ int main(int argc, char **argv) {
         rc = b2_scene_create(ps->tris, ps->n_tris, ps->spheres, ps->n_spheres, ps->materials, ps->n_materials, ps->lights, ps->n_lights, g, &scenes[g]);
         if (rc == B2_OK) rc = b2_scene_build_bvh(scenes[g], nullptr);
     }
+    if (rc == B2_OK && gpus > 1) {                       // NCCL communicators before the clock of the render starts
+        std::vector<int> devs(gpus);
+        for (int g = 0; g < gpus; ++g) devs[g] = g;
+        rc = b2_multi_init(devs.data(), gpus);
+    }
     std::vector<float> film((size_t) 3 * width * height, 0.0f);
     B2Stats st; memset(&st, 0, sizeof(st));
     if (rc == B2_OK) {

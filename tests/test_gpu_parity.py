@@ -302,8 +302,17 @@ def test_in_process_multi_gpu_entry_point():
     whole, st = s0.render_bdpt(**kw)
     one, st1 = api.render_bdpt_multi([s0], **kw)
     assert np.allclose(one, whole, rtol=1e-5, atol=1e-6) and st1["eye_samples"] == st["eye_samples"]
+    for entry in (lambda **k: s0.render_bdpt(**k), lambda **k: api.render_bdpt_multi([s0], **k)):
+        with pytest.raises(RuntimeError, match="film_mode"):              # ACCUMULATE adds into a DEVICE film: device entry point only
+            entry(film_mode=2, **kw)
+    import ctypes
+    from path_tracing_b200 import _abi as A
+    big = s0._params(1, 1, 1, 1 << 20, 1, 1 << 8, 1, 0, 1, 0, 0, 0, False)   # lights * 2^28 pool vertices: refused before anything is written
+    with pytest.raises(RuntimeError, match="2\\^27"):
+        A.check(A.lib().b2_light_pool(s0._h, ctypes.byref(big), A.ptr(np.zeros(20, np.float32))))
     n = min(api.device_count(), 4)
     if n >= 2:
+        api.multi_init(list(range(n)))                                    # communicators ahead of the render (b2_multi_init)
         scenes = [s0] + [api.Scene(sd, device=g) for g in range(1, n)]
         film, stn = api.render_bdpt_multi(scenes, **kw)
         assert stn["eye_samples"] == st["eye_samples"] and stn["shadow_rays"] == st["shadow_rays"]
