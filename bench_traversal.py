@@ -60,7 +60,7 @@ def run(tris=10_000_000, rays=100_000_000, steps=3, check=2000, cpu_check=50, pk
         flops = n * (nodes * bench.NODE_FLOP + tris_r * bench.TRI_FLOP)
         out[name] = {"mrays_per_s": n / ms / 1e3, "ms": ms, "nodes_per_ray": nodes, "tris_per_ray": tris_r,
                      "hit_fraction": float((ids != -1).float().mean()) if mode == api.CLOSEST else float((ids == 0).float().mean()),
-                     "roofline": pk.roofline("k_closest_pooled<0>" if mode == api.CLOSEST else "k_intersect<1, 0, 0>", alg, flops, ms,
+                     "roofline": pk.roofline("k_closest_pooled<0>" if mode == api.CLOSEST else "k_any_pooled<0, 0>", alg, flops, ms,
                                              info["node_bytes"] + info["tri_bytes"])}
     # parity on a subset: BVH == exhaustive kernel == CPU intersector (bit-exact ids and t)
     k = check

@@ -192,6 +192,88 @@ __global__ void __launch_bounds__(Q_THREADS) k_closest_pooled(DevScene sc, const
     if (COUNT) { warp_add64(&counters[0], rays); warp_add64(&counters[1], tc.nodes); warp_add64(&counters[2], tc.tris); }
 }
 
+// Any hit with the leaf triangles of a whole warp pooled: k_connect's trace phase (b2_render.cu) as a ray-query kernel.  Every
+// lane walks its own segment through the wide nodes and takes its next segment the moment this one is decided; the candidate
+// triangles of the 32 node tests are numbered with a warp prefix sum and tested 32 at a time by whichever lanes are free.  The
+// answer does not depend on the order in which candidates are tested (any opaque hit inside the segment decides), so it is
+// the answer of the per-lane loop, bit for bit.  ncu on C5 with the per-lane loop (k_intersect<1,...>): 9.7 of 32 lanes active.
+#ifndef B2_QUERY_ANY_POOL
+#define B2_QUERY_ANY_POOL 1
+#endif
+#ifndef B2_QUERY_ANY_POOL_MIN_TRIS
+#define B2_QUERY_ANY_POOL_MIN_TRIS 2048     // below: a segment meets 1-2 triangles, the per-lane loop wins (as in k_connect)
+#endif
+template <bool COUNT, bool FAST>
+__global__ void __launch_bounds__(Q_THREADS) k_any_pooled(DevScene sc, const float *__restrict__ p1, const float *__restrict__ p2, size_t n,
+                                                          int32_t *__restrict__ vis_out, unsigned long long *counters) {
+    extern __shared__ uint2 s_stack[];
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    TravCounters tc{ 0u, 0u };
+    uint32_t rays = 0;
+    const size_t stride = (size_t) gridDim.x * blockDim.x;
+    size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    uint2 *stack = s_stack + threadIdx.x;
+    bool busy = false;
+    AnyTrav at;
+    at.r.o = at.r.d = at.r.idir = make_float3(0.f, 0.f, 0.f); at.r.oct = 0u; at.tmax = 0.0f;
+    for (;;) {
+        if (!busy && i < n) {
+            const ShadowRay sr = make_shadow_ray(ld3(p1, i), ld3(p2, i));
+            any_init(at, sc, sr.o, sr.d, sr.tmax);
+            rays++;
+            busy = true;
+        }
+        if (!__any_sync(FULL, busy)) break;
+        uint32_t tribits = 0u, tri_base = 0u, vmask = 0u;
+        bool exhausted = false;
+        if (busy) exhausted = !any_node_step<COUNT>(sc, at, stack, blockDim.x, &tc, tribits, tri_base, vmask);
+        const int cnt = __popc(tribits);
+        int incl = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(FULL, incl, d); if (lane >= d) incl += v; }
+        const int total = __shfl_sync(FULL, incl, 31);
+        uint32_t blocked = 0u;                                  // bit j: the segment of lane j met an opaque triangle
+        for (int base = 0; base < total; base += 32) {
+            const int k = base + lane;
+            int owner = 0;
+#pragma unroll
+            for (int step = 16; step >= 1; step >>= 1) { const int v = __shfl_sync(FULL, incl, owner + step - 1); if (v <= k) owner += step; }
+            owner = min(owner, 31);
+            const int o_excl = __shfl_sync(FULL, incl - cnt, owner);
+            const uint32_t o_bits = __shfl_sync(FULL, tribits, owner), o_base = __shfl_sync(FULL, tri_base, owner), o_vmask = __shfl_sync(FULL, vmask, owner);
+            float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a, c = a;
+            if (k < total) {
+                const int ti = tri_of_bit(o_base, o_vmask, nth_bit(o_bits, k - o_excl));
+                a = sc.tri[3 * ti]; b = sc.tri[3 * ti + 1]; c = sc.tri[3 * ti + 2];
+            }
+            RayPre r;
+            r.o = make_float3(__shfl_sync(FULL, at.r.o.x, owner), __shfl_sync(FULL, at.r.o.y, owner), __shfl_sync(FULL, at.r.o.z, owner));
+            r.d = make_float3(__shfl_sync(FULL, at.r.d.x, owner), __shfl_sync(FULL, at.r.d.y, owner), __shfl_sync(FULL, at.r.d.z, owner));
+            const float o_tmax = __shfl_sync(FULL, at.tmax, owner);
+            if (FAST) r.idir = make_float3(__shfl_sync(FULL, at.r.idir.x, owner), __shfl_sync(FULL, at.r.idir.y, owner), __shfl_sync(FULL, at.r.idir.z, owner));
+            bool hit = false;
+            if (k < total && !(f2u(b.w) & B2_MAT_TRANSPARENT)) {
+                if (COUNT) tc.tris++;
+                float tt;
+                if (FAST) hit = tri_test_fast(r.o, r.d, mk3(a), mk3(b), mk3(c), 1e-3f, o_tmax) && group_pass_fast(sc, (int) f2u(c.w), r, 1e-3f, o_tmax);
+                else hit = tri_test(r.o, r.d, mk3(a), mk3(b), mk3(c), 1e-3f, o_tmax, tt) && group_pass(sc, (int) f2u(c.w), r.o, r.d, 1e-3f, o_tmax);
+            }
+            blocked |= __reduce_or_sync(FULL, hit ? 1u << owner : 0u);
+        }
+        if (busy) {
+            const bool occ = (blocked >> lane) & 1u;
+            if (occ || exhausted) {
+                bool o2 = occ;
+                if (!o2) o2 = (FAST && !sc.gpu_sem) ? occluded_spheres_fast(sc, at.r, 1e-3f, at.tmax) : occluded_spheres(sc, at.r.o, at.r.d, 1e-3f, at.tmax);
+                vis_out[i] = o2 ? 0 : 1;
+                i += stride; busy = false;
+            }
+        }
+    }
+    if (COUNT) { warp_add64(&counters[0], rays); warp_add64(&counters[1], tc.nodes); warp_add64(&counters[2], tc.tris); }
+}
+
 __device__ __forceinline__ Mat ld_mat(const float *m, size_t i) {
     Mat r; r.base = make_float3(m[6 * i], m[6 * i + 1], m[6 * i + 2]); r.roughness = m[6 * i + 3]; r.metallic = m[6 * i + 4]; r.eta = m[6 * i + 5];
     return r;
@@ -264,6 +346,9 @@ int launch_isect(const DevScene &sc, int bvh_depth, const float *o, const float 
     if (!ANY && !BRUTE && B2_QUERY_POOL) {
         if (sb + 2048 > 48 * 1024) B2_CUDA(cudaFuncSetAttribute(k_closest_pooled<COUNT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb));
         k_closest_pooled<COUNT><<<grid, Q_THREADS, sb, st>>>(sc, o, d, n, id, t, cnt);
+    } else if (ANY && !BRUTE && B2_QUERY_ANY_POOL && sc.n_tris >= B2_QUERY_ANY_POOL_MIN_TRIS) {
+        if (sb > 48 * 1024) B2_CUDA(cudaFuncSetAttribute(k_any_pooled<COUNT, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb));
+        k_any_pooled<COUNT, FAST><<<grid, Q_THREADS, sb, st>>>(sc, o, d, n, id, cnt);
     } else
         k_intersect<ANY, BRUTE, COUNT, FAST><<<grid, Q_THREADS, sb, st>>>(sc, o, d, n, id, t, cnt);
     B2_CUDA(cudaGetLastError());
