@@ -304,6 +304,9 @@ __global__ void __launch_bounds__(CONN_THREADS, CONN_BLOCKS_PER_SM) k_connect(Re
                 uint32_t tribits = 0u, tri_base = 0u, vmask = 0u;
                 bool exhausted = false;
                 if (busy) exhausted = !any_node_step<COUNT>(c.sc, tv, stack, CONN_THREADS, &tc, tribits, tri_base, vmask);
+                // (an L1 prefetch of the node the NEXT step will test - trav_peek + prefetch.global.L1 here, before the pooled triangle
+                //  tests - was measured: C3 1110 -> 1756 ms; 33 KB of queues and stacks per block leave ~50 KB of L1 per SM, the
+                //  prefetched lines evict the triangle rows and each other.  profiles/r02_connect_summary.md)
                 const int cnt = __popc(tribits);
                 int incl = cnt;
 #pragma unroll
