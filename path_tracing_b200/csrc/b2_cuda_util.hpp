@@ -38,6 +38,15 @@ struct DevBuf {
     T *release_ptr() { T *q = p; p = nullptr; n = 0; return q; }
 };
 
+// Traversal stack of one CTA.  The stack holds at most one group of unvisited siblings per level 2 .. L - 1 while a node of
+// level L is current (a descent from level L pushes the rest of level L's group; the root has no siblings), so bvh_depth - 2
+// entries are the most a walk can stack; one spare.
+#ifndef B2_STACK_SPARE
+#define B2_STACK_SPARE 1
+#endif
+inline size_t stack_entries(int bvh_depth) { return (size_t) (bvh_depth - 2 + B2_STACK_SPARE > 2 ? bvh_depth - 2 + B2_STACK_SPARE : 2); }
+inline size_t stack_bytes(int threads, int bvh_depth) { return (size_t) threads * stack_entries(bvh_depth) * sizeof(uint2); }
+
 // RAII CUDA event: destroyed on every return path (error returns used to leak the timing events of a render)
 struct CudaEvent {
     cudaEvent_t e = nullptr;

@@ -335,7 +335,7 @@ __global__ void k_philox(size_t n, const uint32_t *ctr4, const uint32_t *key2, u
 
 template <bool ANY, bool BRUTE, bool COUNT, bool FAST = false>
 int launch_isect(const DevScene &sc, int bvh_depth, const float *o, const float *d, size_t n, int32_t *id, float *t, unsigned long long *cnt, cudaStream_t st) {
-    const size_t sb = (size_t) Q_THREADS * (size_t) (bvh_depth + 2) * sizeof(uint2);
+    const size_t sb = stack_bytes(Q_THREADS, bvh_depth);
     static size_t configured = 0;
     if (sb > 48 * 1024 && sb > configured) {
         B2_CUDA(cudaFuncSetAttribute(k_intersect<ANY, BRUTE, COUNT, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sb));

@@ -31,7 +31,10 @@ constexpr int CONN_WARPS = CONN_THREADS / 32;
 #define B2_CONN_BLOCKS 6
 #endif
 constexpr int CONN_BLOCKS_PER_SM = B2_CONN_BLOCKS; // persistent grid = 148 SMs x this (also the register budget: launch bounds)
-constexpr int CONN_CHUNK = 8;         // pool vertices pre-tested per compaction round; the pre-test table is padded to a
+#ifndef B2_CONN_CHUNK
+#define B2_CONN_CHUNK 4
+#endif
+constexpr int CONN_CHUNK = B2_CONN_CHUNK;         // pool vertices pre-tested per compaction round; the pre-test table is padded to a
                                       // multiple of this with records that never pass, and pool slices are whole chunks
 
 template <bool COUNT>
@@ -136,7 +139,10 @@ constexpr int CONN_MQ = 64;           // visible-pair queue: < 32 left + 32 new 
 // ready-ray queue: < low left + 32 new per prepare round.  POOL (large scenes): a trace step frees ~4 lanes, 16 ready rays are
 // plenty and the shared memory goes to the traversal stacks; small scenes: every lane finishes its ray within the step (below),
 // so a step wants 32 ready rays
-template <bool POOL> struct ConnCfg { static constexpr int RQ = POOL ? 48 : 64, RQ_LOW = POOL ? 16 : 32; };
+#ifndef B2_CONN_RQ_POOL
+#define B2_CONN_RQ_POOL 40
+#endif
+template <bool POOL> struct ConnCfg { static constexpr int RQ = POOL ? B2_CONN_RQ_POOL : 64, RQ_LOW = POOL ? B2_CONN_RQ_POOL - 32 : 32; };
 #ifndef B2_FAST_SHADOW_TRI
 #define B2_FAST_SHADOW_TRI 1          // contracted Moeller-Trumbore for the shadow rays of the connection stage (b2_isect.cuh)
 #endif

@@ -31,7 +31,6 @@ struct RenderWorkspace {
     ~RenderWorkspace() { release(); }
 };
 
-inline size_t stack_bytes(int threads, int bvh_depth) { return (size_t) threads * (size_t) (bvh_depth + 1 > 2 ? bvh_depth + 1 : 2) * sizeof(uint2); }
 void b2_setup_ctx(RenderCtx &c, const DevScene &sc, const B2Camera &cam, const B2RenderParams &p, RenderWorkspace &ws, int max_paths);
 int b2_render_pt_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws, const B2Camera &cam, const B2RenderParams &p,
                       float *d_film_out, cudaStream_t st, B2Stats *stats);
