@@ -390,23 +390,28 @@ def gpu_arm(args):
     # ---- e2e on N GPUs: what a caller pays from HOST buffers, every rank: scene upload + BVH build + shard render + NCCL
     #      reduce, film read-back to pinned host memory on rank 0; max over ranks (device-synchronised wall clock) ----
     host_film = torch.zeros((H, W, 3), dtype=torch.float32, pin_memory=True)
-    e2e_ms = []
+    e2e_ms, e2e_parts = [], []
     for i in range(3 if args.steps >= 3 else 2):
         barrier()
         t0 = time.perf_counter()
-        s2 = api.Scene(sd, device=local)
-        s2.render_bdpt(device_ptr=film.data_ptr(), stream=stream, **kw)
+        s2 = api.Scene(sd, device=local)                      # b2_scene_create (flatten + upload) + b2_scene_build_bvh; synchronous
+        t1 = time.perf_counter()
+        s2.render_bdpt(device_ptr=film.data_ptr(), stream=stream, **kw)   # returns when the stream has drained the render
+        t2 = time.perf_counter()
         if world > 1:
             multi.reduce_film(film, w["spp"], dst=0)
         if rank == 0:
             host_film.copy_(film, non_blocking=True)
         torch.cuda.synchronize()
+        t3 = time.perf_counter()
         s2.close()
-        dt = torch.tensor([(time.perf_counter() - t0) * 1e3], dtype=torch.float64, device=dev)
+        t4 = time.perf_counter()
+        dt = torch.tensor([(t4 - t0) * 1e3, (t1 - t0) * 1e3, (t2 - t1) * 1e3, (t3 - t2) * 1e3, (t4 - t3) * 1e3], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         if i > 0:
-            e2e_ms.append(float(dt.item()))
+            e2e_ms.append(float(dt[0].item())); e2e_parts.append([float(x) for x in dt[1:].tolist()])
+    e2e_parts = dict(zip(("scene_create_plus_bvh_build", "render_wall", "reduce_plus_film_readback", "scene_destroy"), [float(x) for x in np.mean(np.array(e2e_parts), axis=0)]))
     e2e = float(np.mean(e2e_ms))
 
     out = None
@@ -433,7 +438,7 @@ def gpu_arm(args):
                       "obj_reader": "tinyobjloader" if _abi.lib().b2_obj_has_tinyobj() else "own reader (library built without tiny_obj_loader.h)"},
             "stages_ms": stages, "stage_total_ms": sp["ms_total"], "stages_note": "rank 0's shard, one untimed profiled render",
             "roofline": roof,
-            "e2e": {"value": eye_samples / (e2e * 1e-3) / 1e6, "unit": "Msamples/s", "ms_per_step": e2e, "n_gpus": world,
+            "e2e": {"value": eye_samples / (e2e * 1e-3) / 1e6, "unit": "Msamples/s", "ms_per_step": e2e, "parts_ms_max_over_ranks": e2e_parts, "n_gpus": world,
                     "h2d_bytes_per_step": scene_bytes(sd) * world, "d2h_bytes_per_step": int(host_film.numel() * 4),
                     "note": f"per rank: b2_scene_create + b2_scene_build_bvh + shard render; NCCL reduce; film to pinned host memory on rank 0; max over {world} rank(s)"},
             "gpu_launches": int(launches), "clocks": clocks, "version": version,

@@ -1,20 +1,23 @@
-"""Where the end-to-end step (host scene arrays -> host film) spends its wall time.  Run on a GPU box."""
+"""Where the end-to-end step of bench.py goes beyond the device render: wall times of b2_scene_create, b2_scene_build_bvh, the first
+render of a fresh scene (workspace allocation inside), a second render, film read-back and b2_scene_destroy on the C3 scene.
+usage: python tools/e2e_breakdown.py [spp=4]"""
 import json, sys, time
-import numpy as np
 sys.path.insert(0, ".")
-from path_tracing_b200 import api as b2
-from path_tracing_b200.scene import reference_scene
-
-data = reference_scene("mis")
+import numpy as np
 import torch
-host = torch.empty((1024, 1024, 3), dtype=torch.float32).pin_memory().numpy()      # the caller's film, pinned as in bench.py
-out = {}
-for it in range(5):
-    t0 = time.perf_counter(); s = b2.Scene(data, build=False); t1 = time.perf_counter()
-    s.build_bvh(); t2 = time.perf_counter()
-    film, st = s.render_bdpt(width=1024, height=1024, spp=64, spl=8, eye_depth=8, light_depth=8, seed=1, out=host); t3 = time.perf_counter()
-    film, st2 = s.render_bdpt(width=1024, height=1024, spp=64, spl=8, eye_depth=8, light_depth=8, seed=1, out=host); t4 = time.perf_counter()
-    s.close(); t5 = time.perf_counter()
-    out[f"iter{it}"] = dict(create_ms=(t1 - t0) * 1e3, build_ms=(t2 - t1) * 1e3, render1_ms=(t3 - t2) * 1e3, render1_dev_ms=st["ms_total"],
-                            render2_ms=(t4 - t3) * 1e3, render2_dev_ms=st2["ms_total"], destroy_ms=(t5 - t4) * 1e3)
-print(json.dumps(out, indent=1))
+import bench
+from path_tracing_b200 import api
+
+spp = int(sys.argv[1]) if len(sys.argv) > 1 else 4
+sd = bench.c3_scene()
+film = torch.empty((1080, 1920, 3), dtype=torch.float32).pin_memory().numpy()
+kw = dict(width=1920, height=1080, spp=spp, spl=8, eye_depth=16, light_depth=16, seed=1)
+for rep in range(3):
+    torch.cuda.synchronize(); t0 = time.perf_counter()
+    sc = api.Scene(sd); torch.cuda.synchronize(); t1 = time.perf_counter()
+    _, st1 = sc.render_bdpt(**kw); torch.cuda.synchronize(); t2 = time.perf_counter()
+    _, st2 = sc.render_bdpt(**kw); torch.cuda.synchronize(); t3 = time.perf_counter()
+    sc.close(); torch.cuda.synchronize(); t4 = time.perf_counter()
+    print(json.dumps({"rep": rep, "create_plus_build_ms": 1e3 * (t1 - t0), "bvh_build_device_ms": sc_info if (sc_info := None) else None,
+                      "first_render_wall_ms": 1e3 * (t2 - t1), "first_render_device_ms": st1["ms_total"],
+                      "second_render_wall_ms": 1e3 * (t3 - t2), "second_render_device_ms": st2["ms_total"], "destroy_ms": 1e3 * (t4 - t3)}), flush=True)
