@@ -46,6 +46,43 @@ static int need_device(int device) {
     B2_CUDA(cudaSetDevice(device));
     return B2_OK;
 }
+// Page-locked staging memory for the triangle upload records, kept for the life of the process: one block, handed to one
+// scene at a time (HostScene's TriBuf hooks).  b2_scene_create returns it as soon as the records are on the device, so eight
+// scenes created one after the other (pt_cli --gpus 8) share it; a scene that finds it taken gets its own cudaHostAlloc.
+namespace {
+std::mutex g_stage_mtx;
+void *g_stage = nullptr; size_t g_stage_cap = 0; bool g_stage_busy = false;
+void *stage_alloc(size_t bytes) {
+    {
+        std::lock_guard<std::mutex> lk(g_stage_mtx);
+        if (!g_stage_busy) {
+            if (g_stage_cap < bytes) {
+                if (g_stage) cudaFreeHost(g_stage);
+                g_stage = nullptr; g_stage_cap = 0;
+                const size_t cap = bytes + bytes / 8;              // a little room: the next scene of a session is rarely the same size
+                if (cudaHostAlloc(&g_stage, cap, cudaHostAllocPortable) == cudaSuccess) g_stage_cap = cap; else { g_stage = nullptr; cudaGetLastError(); }
+            }
+            if (g_stage) { g_stage_busy = true; return g_stage; }
+        }
+    }
+    void *p = nullptr;
+    if (cudaHostAlloc(&p, bytes, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return nullptr; }   // nullptr: TriBuf falls back to malloc
+    return p;
+}
+void stage_free(void *p) {
+    {
+        std::lock_guard<std::mutex> lk(g_stage_mtx);
+        if (p == g_stage) { g_stage_busy = false; return; }
+    }
+    cudaFreeHost(p);
+}
+int upload_tris(DevBuf<BuildTri> &d, const TriBuf &h, cudaStream_t st) {
+    B2_TRY(d.alloc(h.size()));
+    if (h.size()) B2_CUDA(cudaMemcpyAsync(d.p, h.data(), h.size() * sizeof(BuildTri), cudaMemcpyHostToDevice, st));
+    return B2_OK;
+}
+}  // namespace
+
 template <class T> static int upload(DevBuf<T> &d, const std::vector<T> &h, cudaStream_t st) {
     B2_TRY(d.alloc(h.size()));
     if (!h.empty()) B2_CUDA(cudaMemcpyAsync(d.p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, st));
@@ -76,11 +113,12 @@ int b2_scene_create(const B2Tri *tris, size_t n_tris, const B2Sphere *spheres, s
     s->device = device;
     if (cudaDeviceGetAttribute(&s->n_sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || s->n_sms <= 0) s->n_sms = 148;   // B200
     const char *err = nullptr;
+    TriBuf::alloc_hook() = stage_alloc; TriBuf::free_hook() = stage_free;
     if (!flatten_scene(tris, n_tris, spheres, n_spheres, materials, n_materials, lights, n_lights, s->hs, &err)) { b2_set_error("%s", err ? err : "bad scene"); delete s; return B2_ERR_INVALID; }
     int rc = B2_OK;
     do {
         if (cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking) != cudaSuccess) { b2_set_error("cudaStreamCreate failed"); rc = B2_ERR_CUDA; break; }
-        if ((rc = upload(s->d_in, s->hs.tris, s->stream)) != B2_OK) break;
+        if ((rc = upload_tris(s->d_in, s->hs.tris, s->stream)) != B2_OK) break;
         if ((rc = upload(s->sph, s->hs.sph, s->stream)) != B2_OK) break;
         if ((rc = upload(s->lights, s->hs.lights, s->stream)) != B2_OK) break;
         if ((rc = upload(s->mats, s->hs.mats, s->stream)) != B2_OK) break;
@@ -90,7 +128,8 @@ int b2_scene_create(const B2Tri *tris, size_t n_tris, const B2Sphere *spheres, s
             b2_set_error("scene upload failed: %s", cudaGetErrorString(cudaGetLastError())); rc = B2_ERR_CUDA; break;
         }
     } while (0);
-    if (rc != B2_OK) { b2_scene_destroy(s); return rc; }
+    if (rc != B2_OK) { b2_scene_destroy(s); return rc; }           // (drains the stream before the records are freed)
+    s->hs.tris.release();                                      // the records are on the device (stream drained above): staging block back to the cache
     *out = s;
     return B2_OK;
 }
@@ -116,7 +155,7 @@ int b2_scene_build_bvh(B2Scene *s, const B2BvhParams *params) {
     const int builder = params ? params->builder : B2_BUILDER_PLOC;
     if (builder != B2_BUILDER_PLOC && builder != B2_BUILDER_LBVH) { b2_set_error("unknown BVH builder %d", builder); return B2_ERR_INVALID; }
     const int radius = (params && params->ploc_radius > 0) ? std::min(params->ploc_radius, 64) : 2;   // measured on C3 / C5: radius 2 > 3 > 4 > 8 (profiles/r01_ploc_summary.md)
-    B2_TRY(b2_build_bvh_device(s->d_in.p, (int) hs.tris.size(), pad, max_leaf, builder, radius, s->stream, s->bvh));
+    B2_TRY(b2_build_bvh_device(s->d_in.p, (int) hs.n_tris, pad, max_leaf, builder, radius, s->stream, s->bvh));
     s->built = true; s->max_leaf = max_leaf;
     // persisting-L2 carve-out for the top of the node array: at most half of the L2 and at most what the device allows;
     // B2_L2_PERSIST_MB overrides (0 = no window) for A/B measurements (profiles/r02_l2_window.md)
