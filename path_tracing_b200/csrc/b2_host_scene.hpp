@@ -172,7 +172,8 @@ inline bool flatten_triangles_fast(const B2Tri *tris, size_t n_tris, const B2Mat
 inline bool flatten_scene(const B2Tri *tris, size_t n_tris, const B2Sphere *sph, size_t n_sph, const B2Material *mats, size_t n_mats,
                           const B2Light *lights, size_t n_lights, HostScene &hs, const char **err) {
     *err = nullptr;
-    if (n_sph == 0 && n_tris >= (1u << 15)) {            // large triangle-only scenes (OBJ meshes, generated scenes): several threads, no per-object tables
+    const char *force_general = getenv("B2_FLATTEN_GENERAL");                        // tests: the general path on a scene the fast one would take
+    if (n_sph == 0 && n_tris >= (1u << 15) && !(force_general && atoi(force_general) != 0)) {            // large triangle-only scenes (OBJ meshes, generated scenes): several threads, no per-object tables
         if (flatten_triangles_fast(tris, n_tris, mats, n_mats, hs, err)) {
             hs.sph.clear(); hs.n_sph = 0;
             flatten_tables(mats, n_mats, lights, n_lights, hs);

@@ -67,6 +67,36 @@ def test_bvh_equals_brute_force_and_oracle_on_triangle_soup(n, max_leaf):
     P.destroy(h); hs.close()
 
 
+def test_threaded_flatten_of_large_triangle_scenes_equals_the_general_path(monkeypatch):
+    """csrc/b2_host_scene.hpp: triangle-only scenes of >= 2^15 triangles take flatten_triangles_fast (two threaded passes, no
+    per-object tables); B2_FLATTEN_GENERAL=1 forces the general path.  Same group boxes, visiting ranks and records <=> the same
+    tree, the same hits (ids, t bits, visibility) and the same visit counters; and both equal the CPU intersector."""
+    sd = random_soup(40_000, 77, lights=1)
+    rng = np.random.default_rng(5)
+    m = 4000
+    org = rng.uniform(-1.2, 1.2, (m, 3)).astype(np.float32)
+    dr = rng.normal(size=(m, 3)).astype(np.float32); dr /= np.linalg.norm(dr, axis=1, keepdims=True)
+    p2 = rng.uniform(-1.2, 1.2, (m, 3)).astype(np.float32)
+    out = []
+    for general in ("0", "1"):
+        monkeypatch.setenv("B2_FLATTEN_GENERAL", general)
+        for threads in (("1", "3") if general == "0" else ("1",)):
+            monkeypatch.setenv("B2_FLATTEN_THREADS", threads)
+            hs = HostSim(sd)
+            ids, t, cnt = hs.intersect(org, dr, 0)
+            vis, _, cnt2 = hs.intersect(org, p2, 1)
+            out.append((ids, t.view(np.uint32), vis, tuple(cnt), tuple(cnt2), hs.bvh_info()))
+            hs.close()
+    for o in out[1:]:
+        assert all(np.array_equal(a, b) for a, b in zip(o[:3], out[0][:3])) and o[3:] == out[0][3:]
+    P = O.Port(); h = P.scene(desc(sd))
+    k = 300
+    r = P.closest_hit(h, org[:k], dr[:k])
+    assert np.array_equal(out[0][0][:k], r["id"]) and np.array_equal(out[0][1][:k], r["t"].view(np.uint32))
+    assert np.array_equal(out[0][2][:k], P.visibility(h, org[:k], p2[:k]).astype(np.int32))
+    P.destroy(h)
+
+
 @pytest.mark.parametrize("name,depth", [("cornell", 6), ("mis", 8)])
 def test_wavefront_bodies_reproduce_the_oracle_render(name, depth):
     sd = reference_scene(name)
