@@ -1,6 +1,6 @@
 """Attribute the per-instruction counters of one `ncu --set full --import-source on` capture to source lines.
 
-    python tools/ncu_by_line.py <report.ncu-rep> <object.o> <mangled-kernel-substring> [--match <demangled substring>] [--top N]
+    python tools/ncu_by_line.py <report.ncu-rep> <object.o> <mangled-kernel-substring> [--match <demangled substring>] [--top N] [--mem]
 
 (<mangled-kernel-substring> selects the function in the object, e.g. k_connectILb0ELb1; --match selects the kernel in the
 report, e.g. "k_connect<(bool)0, (bool)1>"; default: the first kernel of the report)
@@ -82,6 +82,26 @@ def main():
     print("-- by line of the kernel body (outermost frame): inst %%, stall-sample %%, active threads / instruction")
     for k, v in sorted(outer_i.items(), key=lambda kv: -kv[1])[:top]:
         print("  %-28s %6.2f %%  %6.2f %%  %5.1f" % (k, 100 * v / tot_i, 100 * outer_s[k] / max(tot_s, 1), thr[k] / max(v, 1)))
+    if "--mem" in sys.argv:
+        # memory instructions by innermost source line: L1 tag requests and the sectors they ask L2 for ("theoretical": before
+        # the L1 hit rate), global and local; x 32 B = bytes.  Names the buffer behind every load of the kernel.
+        il1, il2g, il2l = hdr.index("L1 Tag Requests Global"), hdr.index("L2 Theoretical Sectors Global"), hdr.index("L2 Theoretical Sectors Local")
+        mem = defaultdict(lambda: [0.0, 0.0, 0.0, ""])
+        for r in rows[1:]:
+            if len(r) <= max(il1, il2g, il2l) or not r[ia]:
+                continue
+            a = int(r[ia], 16)
+            chain, ins = amap.get(a - base, ([("?", 0)], ""))
+            v = [float(r[k] or 0) for k in (il1, il2g, il2l)]
+            if sum(v) == 0:
+                continue
+            key = "%s:%d" % (os.path.basename(chain[0][0]), chain[0][1])
+            m = mem[key]; m[0] += v[0]; m[1] += v[1]; m[2] += v[2]; m[3] = ins.split()[0] if ins else m[3]
+        tg = sum(m[1] for m in mem.values()); tl = sum(m[2] for m in mem.values())
+        print("-- memory instructions by innermost line: L1 tag requests, L2 theoretical sectors global (share) / local (share), bytes = sectors x 32")
+        print("   total: global %.3f GB, local %.3f GB" % (tg * 32 / 1e9, tl * 32 / 1e9))
+        for k, m in sorted(mem.items(), key=lambda kv: -(kv[1][1] + kv[1][2]))[:top]:
+            print("  %-26s %-8s tags %12.0f  global %8.3f GB (%5.1f %%)  local %8.3f GB (%5.1f %%)" % (k, m[3], m[0], m[1] * 32 / 1e9, 100 * m[1] / max(tg, 1), m[2] * 32 / 1e9, 100 * m[2] / max(tl, 1)))
     print("-- by innermost line: inst %%, stall-sample %%")
     for k, v in sorted(inner_i.items(), key=lambda kv: -kv[1])[:top]:
         print("  %-28s %6.2f %%  %6.2f %%" % (k, 100 * v / tot_i, 100 * inner_s[k] / max(tot_s, 1)))
