@@ -115,8 +115,13 @@ B2_HD float bsdf_pdf_local(const Mat &m, float3 wo, float3 wi) {        // :464-
 }
 // The world-space entry points are deliberately NOT inlined on the device: the connect stage calls each of them twice
 // per pair, and inlining every copy made the kernel miss in the instruction cache (ncu: 41 % stall_no_inst).
+// B2_MAT_LOCAL_COPY: the callers in the connection stage (b2_bdpt.cuh) hand these a 24-byte local copy of the material, not a
+// reference into the 80-byte vertex record, which would force the whole record into local memory.  With 28 KB of L1 per SM
+// the big records were the faster form (a hand-placed spill of cold data: C3 1198 vs 1221 ms); since 0.2.3 leaves L1 60 KB
+// the 51 GB of local traffic per launch they cause costs more than it saves: C3 1042 -> 1004 ms, C1 250 -> 228 ms
+// (profiles/r02_connect_summary.md).  B2_MAT_BY_VALUE: Mat in registers through the call (measured slower both times).
 #ifndef B2_MAT_LOCAL_COPY
-#define B2_MAT_LOCAL_COPY 0
+#define B2_MAT_LOCAL_COPY 1
 #endif
 #ifndef B2_MAT_BY_VALUE
 #define B2_MAT_BY_VALUE 0
