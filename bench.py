@@ -411,7 +411,9 @@ def gpu_arm(args):
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         if i > 0:
             e2e_ms.append(float(dt[0].item())); e2e_parts.append([float(x) for x in dt[1:].tolist()])
+    e2e_iters = [[round(x, 3) for x in it] for it in e2e_parts]
     e2e_parts = dict(zip(("scene_create_plus_bvh_build", "render_wall", "reduce_plus_film_readback", "scene_destroy"), [float(x) for x in np.mean(np.array(e2e_parts), axis=0)]))
+    e2e_parts["per_iteration"] = e2e_iters
     e2e = float(np.mean(e2e_ms))
 
     out = None

@@ -139,6 +139,9 @@ void b2_scene_destroy(B2Scene *s) {
     cudaSetDevice(s->device);
     if (s->stream) { cudaStreamSynchronize(s->stream); cudaStreamDestroy(s->stream); }
     b2_workspace_release(s);
+    // the stream has drained: the scene's device blocks go to the block cache for the next scene (DevBlockCache, b2_cuda_util.hpp)
+    s->d_in.release_cached(); s->sph.release_cached(); s->lights.release_cached(); s->mats.release_cached(); s->groups.release_cached();
+    s->isect_counters.release_cached(); s->bvh.nodes.release_cached(); s->bvh.tri.release_cached(); s->bvh.tri_obj.release_cached();
     delete s;
 }
 
