@@ -64,13 +64,28 @@ B2_HD float byte_f32(uint32_t lo_word, uint32_t hi_word, int i, uint32_t magic) 
 // triangle slot of bit `bit` of a node's vmask-relative leaf mask (b2_scene.cuh)
 B2_HD int tri_of_bit(uint32_t tri_base, uint32_t vmask, int bit) { return (int) tri_base + popc32(vmask & ((1u << bit) - 1u)); }
 
+// One 16-byte row of a wide node.  B2_NODE_L1_HINT = 1: loaded with the L1 eviction priority "evict_last" (LDG.E.EL), meant to
+// let the node lines outlive the triangle rows, vertex records and local-memory lines that share the 60 KB of L1 with them.
+// Measured: C3 1003.4 -> 1006.0 ms, C5 unchanged - off (profiles/r02_connect_summary.md).
+#ifndef B2_NODE_L1_HINT
+#define B2_NODE_L1_HINT 0
+#endif
+B2_HD uint4 ld_node(const uint4 *p) {
+#if defined(__CUDA_ARCH__) && B2_NODE_L1_HINT
+    uint4 v;
+    asm volatile("ld.global.L1::evict_last.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+#else
+    return *p;
+#endif
+}
 // Tests the 8 children of `node`: one hit bit per slot from eight branch-free slab tests (an empty slot carries an
 // inverted box).  Returns the hit internal children as bits (slot ^ oct) in hits_p and the hit leaf triangles as a
 // sparse 24-bit mask (bit 3*slot + j; triangle slot = tri_of_bit(tri_base, vmask, bit)).
 B2_HD void node_test(const DevScene &sc, uint32_t node, const RayPre &r, float tmin, float tmax,
                      uint32_t &hits_p, uint32_t &tribits, uint32_t &child_base, uint32_t &tri_base, uint32_t &imask, uint32_t &vmask) {
     const uint4 *__restrict__ np = sc.nodes + (size_t) node * B2_NODE_UINT4;
-    const uint4 w0 = np[0], w1 = np[1], w2 = np[2], w3 = np[3], w4 = np[4];
+    const uint4 w0 = ld_node(np), w1 = ld_node(np + 1), w2 = ld_node(np + 2), w3 = ld_node(np + 3), w4 = ld_node(np + 4);
     const float sx = u2f((w0.w & 0xffu) << 23), sy = u2f(((w0.w >> 8) & 0xffu) << 23), sz = u2f(((w0.w >> 16) & 0xffu) << 23);
     imask = w0.w >> 24;
     child_base = w1.x; tri_base = w1.y; vmask = w1.z;

@@ -334,7 +334,7 @@ __global__ void __launch_bounds__(CONN_THREADS, CONN_BLOCKS_PER_SM) k_connect(Re
                     float4 a = mk4(mk3(0, 0, 0), 0.0f), b = a, cc = a;
                     if (k < total) {
                         const int ti = tri_of_bit(o_base, o_vmask, nth_bit(o_bits, k - o_excl));
-                        a = c.sc.tri[3 * ti]; b = c.sc.tri[3 * ti + 1]; cc = c.sc.tri[3 * ti + 2];   // (through L1: L2-only loads, __ldcg, measured 1042 -> 1078 ms)
+                        a = c.sc.tri[3 * ti]; b = c.sc.tri[3 * ti + 1]; cc = c.sc.tri[3 * ti + 2];   // (plain loads: L2-only (__ldcg) 1042 -> 1078 ms, L1::evict_first 1003 -> 1030 ms)
                     }
                     const float3 ro = mk3(__shfl_sync(0xffffffffu, tv.r.o.x, owner), __shfl_sync(0xffffffffu, tv.r.o.y, owner), __shfl_sync(0xffffffffu, tv.r.o.z, owner));
                     const float3 rd = mk3(__shfl_sync(0xffffffffu, tv.r.d.x, owner), __shfl_sync(0xffffffffu, tv.r.d.y, owner), __shfl_sync(0xffffffffu, tv.r.d.z, owner));
