@@ -43,7 +43,10 @@ def run(tris=10_000_000, rays=100_000_000, steps=3, check=2000, cpu_check=50, pk
            "bvh": dict({k: info[k] for k in ("n_tris", "n_nodes", "node_bytes", "tri_bytes", "depth", "build_ms", "build_passes", "sah_cost")},
                        builder="lbvh" if os.environ.get("B2_BVH_BUILDER", "0") == "1" else "ploc"),
            "scene_gen_s": t_gen, "scene_create_plus_build_wall_s": t_build_wall}
-    for name, mode, second in (("closest", api.CLOSEST, d), ("any", api.ANY, p2)):
+    # "closest" / "any": the library's default = rays walked in (origin cell, direction octant) order, results in the caller's
+    # order, keys + sort inside the timed call; "*_caller_order": B2_KEEP_RAY_ORDER, the incoherent stream walked as it comes
+    for name, mode, second in (("closest", api.CLOSEST, d), ("any", api.ANY, p2),
+                               ("closest_caller_order", api.CLOSEST | api.KEEP_RAY_ORDER, d), ("any_caller_order", api.ANY | api.KEEP_RAY_ORDER, p2)):
         sc.intersect_device(org.data_ptr(), second.data_ptr(), n, mode | api.COUNT_VISITS, ids.data_ptr(), t.data_ptr(), stream)
         torch.cuda.synchronize()
         cnt = sc.intersect_counters()
@@ -59,8 +62,8 @@ def run(tris=10_000_000, rays=100_000_000, steps=3, check=2000, cpu_check=50, pk
         alg = n * (24 + 8 + nodes * bench.NODE_B + tris_r * bench.TRI_B)
         flops = n * (nodes * bench.NODE_FLOP + tris_r * bench.TRI_FLOP)
         out[name] = {"mrays_per_s": n / ms / 1e3, "ms": ms, "nodes_per_ray": nodes, "tris_per_ray": tris_r,
-                     "hit_fraction": float((ids != -1).float().mean()) if mode == api.CLOSEST else float((ids == 0).float().mean()),
-                     "roofline": pk.roofline("k_closest_pooled<0>" if mode == api.CLOSEST else "k_any_pooled<0, 0>", alg, flops, ms,
+                     "hit_fraction": float((ids != -1).float().mean()) if not (mode & api.ANY) else float((ids == 0).float().mean()),
+                     "roofline": pk.roofline("k_closest_pooled<0>" if not (mode & api.ANY) else "k_any_pooled<0, 0>", alg, flops, ms,
                                              info["node_bytes"] + info["tri_bytes"])}
     # parity on a subset: BVH == exhaustive kernel == CPU intersector (bit-exact ids and t)
     k = check

@@ -148,6 +148,10 @@ void b2_scene_destroy(B2Scene *scene);
 #define B2_ANY 1
 #define B2_BRUTE_FORCE 16
 #define B2_COUNT_VISITS 32
+#define B2_KEEP_RAY_ORDER 128 /* walk the rays in the caller's order.  Default for closest hits (batches of >= 2^18 rays against scenes of
+                               * >= 100 000 triangles): the library walks them in the order of (cell of the origin, direction octant,
+                               * coarse direction) - neighbouring lanes then fetch the same nodes - and writes every result to its
+                               * ray's own slot; ids and t are the same either way */
 #define B2_FAST_SHADOW 64   /* with B2_ANY: the arithmetic the RENDER's shadow rays use (contracted Moeller-Trumbore, approximate reciprocals,
                             * csrc/b2_isect.cuh tri_test_fast) instead of the bit-exact test -- exposed so that tests can count where the two differ */
 int b2_intersect(B2Scene *scene, const float *org, const float *dir, size_t n, int mode, int32_t *prim_id, float *t);

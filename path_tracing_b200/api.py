@@ -13,7 +13,7 @@ import numpy as np
 from . import _abi as A
 from .scene import SceneData
 
-CLOSEST, ANY, BRUTE_FORCE, COUNT_VISITS, FAST_SHADOW = 0, 1, 16, 32, 64
+CLOSEST, ANY, BRUTE_FORCE, COUNT_VISITS, FAST_SHADOW, KEEP_RAY_ORDER = 0, 1, 16, 32, 64, 128
 FILM_MEAN, FILM_SUM = 0, 1
 STRATEGIES_REFERENCE, STRATEGIES_FULL, STRATEGIES_LIGHT_TRACING, STRATEGIES_NEE, STRATEGIES_MIS = 0, 1, 2, 3, 4
 NOALLOC_MAX_POOL_VERTICES = 32768                            # B2_NOALLOC_MAX_POOL_VERTICES
@@ -84,20 +84,20 @@ class Scene:
             pass
 
     # ---- ray queries ----
-    def closest_hit(self, org, dirs, brute_force=False, count=False):
+    def closest_hit(self, org, dirs, brute_force=False, count=False, keep_order=False):
         org, dirs = _f32(org, (-1, 3)), _f32(dirs, (-1, 3))
         n = len(org)
         ids = np.full(n, -1, np.int32)
         t = np.full(n, 1e20, np.float32)
-        mode = CLOSEST | (BRUTE_FORCE if brute_force else 0) | (COUNT_VISITS if count else 0)
+        mode = CLOSEST | (BRUTE_FORCE if brute_force else 0) | (COUNT_VISITS if count else 0) | (KEEP_RAY_ORDER if keep_order else 0)
         A.check(A.lib().b2_intersect(self._h, A.ptr(org), A.ptr(dirs), n, mode, A.ptr(ids), A.ptr(t)))
         return ids, t
 
-    def visibility(self, p1, p2, brute_force=False, count=False, fast_shadow=False):
+    def visibility(self, p1, p2, brute_force=False, count=False, fast_shadow=False, keep_order=False):
         p1, p2 = _f32(p1, (-1, 3)), _f32(p2, (-1, 3))
         n = len(p1)
         vis = np.zeros(n, np.int32)
-        mode = ANY | (BRUTE_FORCE if brute_force else 0) | (COUNT_VISITS if count else 0) | (FAST_SHADOW if fast_shadow else 0)
+        mode = ANY | (BRUTE_FORCE if brute_force else 0) | (COUNT_VISITS if count else 0) | (FAST_SHADOW if fast_shadow else 0) | (KEEP_RAY_ORDER if keep_order else 0)
         A.check(A.lib().b2_intersect(self._h, A.ptr(p1), A.ptr(p2), n, mode, A.ptr(vis), None))
         return vis
 

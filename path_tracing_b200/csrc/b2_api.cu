@@ -92,7 +92,7 @@ template <class T> static int upload(DevBuf<T> &d, const std::vector<T> &h, cuda
 extern "C" {
 
 const char *b2_last_error(void) { return g_err; }
-const char *b2_version(void) { return "b2pt 0.2.4 (sm_100a)"; }     // bump with every kernel change: profiles/*_traffic.json are tied to it
+const char *b2_version(void) { return "b2pt 0.2.5 (sm_100a)"; }     // bump with every kernel change: profiles/*_traffic.json are tied to it
 int b2_device_count(int *count) {
     if (!count) { b2_set_error("count is NULL"); return B2_ERR_INVALID; }
     int n = 0;
@@ -202,7 +202,7 @@ int b2_intersect_device(B2Scene *s, const float *d_org, const float *d_dir, size
     if (n && (!d_org || !d_dir || !d_prim_id)) { b2_set_error("NULL ray / result buffer"); return B2_ERR_INVALID; }
     B2_CUDA(cudaSetDevice(s->device));
     L2Window l2w(s, (cudaStream_t) stream);
-    return b2_intersect_launch(s->view(), s->bvh.depth, d_org, d_dir, n, mode, d_prim_id, d_t, s->isect_counters.p, (cudaStream_t) stream);
+    return b2_intersect_launch(s->view(), s->bvh.depth, d_org, d_dir, n, mode, d_prim_id, d_t, s->isect_counters.p, (cudaStream_t) stream, &s->ray_sort);
 }
 
 int b2_intersect(B2Scene *s, const float *org, const float *dir, size_t n, int mode, int32_t *prim_id, float *t) {
@@ -218,7 +218,7 @@ int b2_intersect(B2Scene *s, const float *org, const float *dir, size_t n, int m
     B2_CUDA(cudaMemcpyAsync(d_o.p, org, 3 * n * sizeof(float), cudaMemcpyHostToDevice, s->stream));
     B2_CUDA(cudaMemcpyAsync(d_d.p, dir, 3 * n * sizeof(float), cudaMemcpyHostToDevice, s->stream));
     L2Window l2w(s, s->stream);
-    B2_TRY(b2_intersect_launch(s->view(), s->bvh.depth, d_o.p, d_d.p, n, mode, d_id.p, want_t ? d_t.p : nullptr, s->isect_counters.p, s->stream));
+    B2_TRY(b2_intersect_launch(s->view(), s->bvh.depth, d_o.p, d_d.p, n, mode, d_id.p, want_t ? d_t.p : nullptr, s->isect_counters.p, s->stream, &s->ray_sort));
     B2_CUDA(cudaMemcpyAsync(prim_id, d_id.p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, s->stream));
     if (want_t) B2_CUDA(cudaMemcpyAsync(t, d_t.p, n * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
     B2_CUDA(cudaStreamSynchronize(s->stream));

@@ -13,7 +13,10 @@
 #define B2_STACK_CAP 64
 
 struct RayPre { float3 o, d, idir; uint32_t oct; };
-B2_HD float safe_rcp(float d) { return fabsf(d) > 1e-30f ? 1.0f / d : copysignf(1e30f, d); }
+// 1 / d for the slab tests of the wide nodes ONLY (the boxes are padded and the comparison carries a 4-ulp slack; hit distances
+// never come from it): the approximate reciprocal on the device in every translation unit - b2_render.cu and b2_integrators.cu
+// got it from -prec-div=false already, b2_queries.cu paid three IEEE divisions per ray
+B2_HD float safe_rcp(float d) { return fabsf(d) > 1e-30f ? fast_rcp(d) : copysignf(1e30f, d); }
 B2_HD RayPre ray_pre(float3 o, float3 d, float3 idir) {          // idir = safe_rcp of d, computed elsewhere (k_connect's prepare phase)
     RayPre r; r.o = o; r.d = d; r.idir = idir;
     r.oct = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);

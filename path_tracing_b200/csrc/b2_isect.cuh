@@ -40,7 +40,20 @@ B2_HD bool tri_test_fast(float3 ro, float3 rd, float3 v0, float3 e1, float3 e2, 
     return !(tt < tMin || tt > tMax);
 }
 // Sphere::check_intersect, object.cpp:16-56 with scale (1,1,1): refuses origins on/inside the sphere.
+// Conservative pre-reject of the two quadratic tests below: the discriminant with contracted arithmetic and
+// no square root; "certainly negative" = below minus 1e-4 of the magnitude of its terms, two orders of magnitude more than the
+// rounding of either form (a dozen fp32 operations, |rd| = 1 within 1e-6), so a rejected ray is one the exact test rejects too
+// and hit ids / t stay bit-equal.  A camera ray of C2 ran the exact test (IEEE sqrt, divisions, re-normalisation) against every
+// sphere and every light ball; almost all of them miss by far.
+B2_HD bool quad_certainly_misses(float3 ro, float3 rd, float3 c, float r) {
+    const float3 oc = ro - c;
+    const float b = dot3(oc, rd), l2 = dot3(oc, oc), d2 = dot3(rd, rd), r2 = r * r;
+    // exact forms: h = b^2 - (|oc|^2 - r^2) with |rd| = 1 (light balls); disc = 4 (b'^2 - a (|oc|^2 - r^2)), b' = b / |rd|, a = 1 (spheres)
+    const float h = b * b - d2 * (l2 - r2);
+    return h < -1e-4f * (b * b + d2 * (l2 + r2));
+}
 B2_HD bool sphere_test(float3 ro, float3 rd, float3 c, float r, float tMin, float tMax, float &t) {
+    if (quad_certainly_misses(ro, rd, c, r)) return false;
     float3 D = g3_normalize(rd);
     float3 OC = x3_sub(ro, c);
     float a = x_add(x_add(x_mul(D.x, D.x), x_mul(D.y, D.y)), x_mul(D.z, D.z));
@@ -61,6 +74,7 @@ B2_HD bool sphere_test(float3 ro, float3 rd, float3 c, float r, float tMin, floa
 }
 // intersect_sphere (light balls), geometric.cuh:240-259: strict EPSILON < t < max_dist.
 B2_HD bool light_ball_test(float3 ro, float3 rd, float3 c, float r, float max_dist, float &t) {
+    if (quad_certainly_misses(ro, rd, c, r)) return false;
     float3 oc = x3_sub(ro, c);
     float b = x3_dot(oc, rd);
     float cc = x_sub(x3_dot(oc, oc), x_mul(r, r));

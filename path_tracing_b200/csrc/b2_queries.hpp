@@ -6,8 +6,10 @@
 
 // mode: B2_CLOSEST / B2_ANY, optionally | B2_BRUTE_FORCE, | B2_COUNT_VISITS (d_counters: rays, nodes, tris).
 // All pointers are device pointers; asynchronous on `st`.
+// Scratch of the ray reordering (keys, ray indices, sorted copies, CUB's temporary storage); owned by the scene, grown on demand.
+struct RaySortScratch { DevBuf<uint32_t> keys, keys_sorted, idx, idx_sorted; DevBuf<unsigned char> tmp; };
 int b2_intersect_launch(const DevScene &sc, int bvh_depth, const float *d_org, const float *d_dir, size_t n, int mode,
-                        int32_t *d_prim_id, float *d_t, unsigned long long *d_counters, cudaStream_t st);
+                        int32_t *d_prim_id, float *d_t, unsigned long long *d_counters, cudaStream_t st, RaySortScratch *sort_scratch = nullptr);
 
 int b2_tables_bsdf_evaluate(size_t n, const float *mtl6, const float *wo, const float *wi, const float *N, float *out3);
 int b2_tables_bsdf_pdf(size_t n, const float *mtl6, const float *wo, const float *wi, const float *N, float *out);

@@ -6,6 +6,7 @@
 #include "b2_device_scene.hpp"
 #include "b2_host_scene.hpp"
 #include "b2_render.hpp"
+#include "b2_queries.hpp"
 
 struct B2Scene {
     int device = 0;
@@ -18,6 +19,7 @@ struct B2Scene {
     int max_leaf = 3;
     cudaStream_t stream = nullptr;
     DevBuf<unsigned long long> isect_counters;
+    RaySortScratch ray_sort;              // b2_intersect*: reordering of large ray batches (b2_queries.cu)
     RenderWorkspace *ws_ptr = nullptr;    // taken from the per-device cache at first use, returned to it by b2_scene_destroy
     RenderWorkspace &ws_ref();            // (allocating and freeing ~6 GB of wavefront state per scene handle is what made
                                           //  a create -> render -> destroy cycle 5x slower than the render itself)

@@ -322,6 +322,26 @@ def test_in_process_multi_gpu_entry_point():
     s0.close()
 
 
+def test_reordered_ray_batches_return_the_answers_of_the_callers_order():
+    """b2_intersect (closest hits) on large batches against large scenes walks the rays in (origin cell, direction octant) order
+    (csrc/b2_queries.cu: k_ray_keys + radix sort + perm in the pooled kernels) and writes every result to its ray's own slot:
+    ids, t bits and visibility must equal B2_KEEP_RAY_ORDER's, rays outside the scene box and degenerate directions included."""
+    from path_tracing_b200 import gen
+    sd = gen.soup_scene(150_000)
+    sc = api.Scene(sd)
+    m = 400_000                                                       # >= 2^18 rays, >= 100 000 triangles: the reordering path
+    org, dr, p2 = gen.random_rays(m, 0.0, 1.0, seed=3)
+    org[:1000] = org[:1000] * 3.0 - 1.0                               # origins outside the box (clamped cells)
+    dr[1000:1100] = [0.0, 0.0, 1.0]; dr[1100:1200] = [-1.0, 0.0, 0.0]  # axis-aligned
+    a_id, a_t = sc.closest_hit(org, dr)
+    b_id, b_t = sc.closest_hit(org, dr, keep_order=True)
+    assert np.array_equal(a_id, b_id) and np.array_equal(bits(a_t), bits(b_t)) and 0.2 < (a_id >= 0).mean() <= 1.0
+    p2s = (org + dr * np.float32(0.01)).astype(np.float32)
+    for q in (p2, p2s):
+        assert np.array_equal(sc.visibility(org, q), sc.visibility(org, q, keep_order=True))
+    sc.close()
+
+
 @pytest.mark.parametrize("n", [7, 600, 1024, 1025])
 def test_single_cta_build_of_small_scenes_gives_the_tree_of_the_host_mirror(n):
     """n <= 1024 triangles: every PLOC pass and collapse level runs in one CTA (k_build_small, csrc/b2_bvh_build.cu); above, one
@@ -346,5 +366,7 @@ def test_single_cta_build_of_small_scenes_gives_the_tree_of_the_host_mirror(n):
     cnt = sc.intersect_counters()
     h_vis, _, h_cnt = hs.intersect(org, p2, 1)
     assert np.array_equal(vis, h_vis)
-    assert cnt["nodes"] == int(h_cnt[0]) and cnt["tris"] == int(h_cnt[1])
+    # (the device takes 1 / d of the slab tests from rcp.approx, the host divides: a box grazed within the last ulp may be entered
+    #  on one side only - the padded boxes make that harmless for the hits, and it moves a count by a few at most)
+    assert abs(cnt["nodes"] - int(h_cnt[0])) <= 2 + 1e-3 * int(h_cnt[0]) and abs(cnt["tris"] - int(h_cnt[1])) <= 2 + 1e-3 * int(h_cnt[1])
     hs.close(); sc.close()

@@ -13,7 +13,7 @@ d = torch.randn((n, 3), device=dev, generator=g); d = d / d.norm(dim=1, keepdim=
 p2 = torch.rand((n, 3), device=dev, generator=g)
 ids = torch.empty(n, dtype=torch.int32, device=dev); t = torch.empty(n, dtype=torch.float32, device=dev)
 st = torch.cuda.current_stream().cuda_stream
-for mode, second in ((api.CLOSEST, d), (api.ANY, p2)):
+for mode, second in ((api.CLOSEST, d), (api.ANY, p2), (api.CLOSEST | api.KEEP_RAY_ORDER, d), (api.ANY | api.KEEP_RAY_ORDER, p2)):
     for _ in range(2):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(); sc.intersect_device(org.data_ptr(), second.data_ptr(), n, mode, ids.data_ptr(), t.data_ptr(), st); e1.record(); torch.cuda.synchronize()

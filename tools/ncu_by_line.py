@@ -85,14 +85,15 @@ def main():
     if "--mem" in sys.argv:
         # memory instructions by innermost source line: L1 tag requests and the sectors they ask L2 for ("theoretical": before
         # the L1 hit rate), global and local; x 32 B = bytes.  Names the buffer behind every load of the kernel.
-        il1, il2g, il2l = hdr.index("L1 Tag Requests Global"), hdr.index("L2 Theoretical Sectors Global"), hdr.index("L2 Theoretical Sectors Local")
+        col = lambda name: hdr.index(name) if name in hdr else -1          # a kernel without local memory has no local column
+        il1, il2g, il2l = col("L1 Tag Requests Global"), col("L2 Theoretical Sectors Global"), col("L2 Theoretical Sectors Local")
         mem = defaultdict(lambda: [0.0, 0.0, 0.0, ""])
         for r in rows[1:]:
             if len(r) <= max(il1, il2g, il2l) or not r[ia]:
                 continue
             a = int(r[ia], 16)
             chain, ins = amap.get(a - base, ([("?", 0)], ""))
-            v = [float(r[k] or 0) for k in (il1, il2g, il2l)]
+            v = [float(r[k] or 0) if k >= 0 else 0.0 for k in (il1, il2g, il2l)]
             if sum(v) == 0:
                 continue
             key = "%s:%d" % (os.path.basename(chain[0][0]), chain[0][1])
