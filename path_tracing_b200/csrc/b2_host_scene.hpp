@@ -104,8 +104,10 @@ inline bool flatten_triangles_fast(const B2Tri *tris, size_t n_tris, const B2Mat
     };
     auto run = [&](auto &&fn) {
         std::vector<std::thread> th;
-        for (int c = 1; c < T; ++c) th.emplace_back(fn, c);
+        int started = 1;                                   // chunks [1, started) run on their own threads
+        try { for (; started < T; ++started) th.emplace_back(fn, started); } catch (...) {}   // no more threads: the rest runs here
         fn(0);
+        for (int c = started; c < T; ++c) fn(c);
         for (auto &t : th) t.join();
     };
     run(pass1);
