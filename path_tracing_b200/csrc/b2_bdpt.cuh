@@ -23,12 +23,12 @@
 #define B2_LV_F4 5
 #define B2_LV_SRC 1u
 #define B2_LV_PARALLEL 2u
-struct LightVtx { float3 pos, n, thr; Mat mtl; uint32_t flags; float cutoff, pdf_fwd, pdf_rev; };
+struct LightVtx { float3 pos, n, thr; Mat mtl; uint32_t flags; float cutoff, pdf_fwd, pdf_rev, walk; };   // walk: mis_light_sum, written by k_pool_active
 B2_HD LightVtx load_lv(const float4 *pool, int i) {
     const float4 a = pool[B2_LV_F4 * i], b = pool[B2_LV_F4 * i + 1], c = pool[B2_LV_F4 * i + 2], d = pool[B2_LV_F4 * i + 3], e = pool[B2_LV_F4 * i + 4];
     LightVtx v;
     v.pos = mk3(a); v.flags = f2u(a.w); v.n = mk3(b); v.cutoff = b.w; v.thr = mk3(c); v.pdf_fwd = c.w;
-    v.mtl.base = mk3(d); v.pdf_rev = d.w; v.mtl.roughness = e.x; v.mtl.metallic = e.y; v.mtl.eta = e.z;
+    v.mtl.base = mk3(d); v.pdf_rev = d.w; v.mtl.roughness = e.x; v.mtl.metallic = e.y; v.mtl.eta = e.z; v.walk = e.w;
     return v;
 }
 B2_HD void store_lv(float4 *pool, int i, const LightVtx &v) {
@@ -334,8 +334,39 @@ B2_HD void shade_step(const RenderCtx &c, PathState &ps, HitRec h, ShadeOut &o) 
 //   EA: pos(i) eta(i) pdf_fwd(i) pdf_rev(i) of eye vertex i; cur_n / cur_mtl of vertex s_idx
 //   LA: pos(i) eta(i) pdf_fwd(i) pdf_rev(i) is_src(i) of light vertex i of the SAME light subpath; cur_n / cur_mtl of t_idx
 // =====================================================================================================
+// The eye-side walk (:143-148) is LINEAR in pdf_t_to_s, the only term of it that depends on the light vertex: every ratio
+// carries that factor exactly once.  mis_eye_sum is the walk for pdf_t_to_s = 1; the connection stage computes it once per eye
+// vertex and work item (k_connect) instead of once per visible pair -- at depth d a pair read 2 (d - 1) scattered history
+// rows, which made the deep waves of C3 fetch up to 10 GB from HBM per launch (profiles/r02_connect_summary.md, section 5).
+// Same terms as the sequential walk, summed before instead of after the multiplication by pdf_t_to_s (fp32 rounding only).
+template <class EA>
+B2_HD float mis_eye_sum(const EA &E, int s_idx) {
+    float sum = 0.0f, ratio = 1.0f, prev_rev = 1.0f;
+    for (int i = s_idx; i > 0; --i) {
+        if (E.eta(i) > 0.0f) break;
+        ratio *= fast_div(prev_rev, fmaxf(E.pdf_fwd(i), 1e-8f));
+        sum += ratio;
+        prev_rev = E.pdf_rev(i);
+    }
+    return sum;
+}
+// The light-side walk (:153-163) is linear in pdf_s_to_t in the same way; its value for pdf_s_to_t = 1 is a constant of the pool
+// vertex, stored in the spare slot of its record when the pool is compacted (k_pool_active).
+template <class LA>
+B2_HD float mis_light_sum(const LA &L, int t_idx) {
+    float sum = 0.0f, ratio = 1.0f, prev_rev = 1.0f;
+    for (int i = t_idx; i > 0; --i) {
+        if (L.is_src(i)) { ratio *= fast_div(prev_rev, fmaxf(L.pdf_fwd(i), 1e-8f)); sum += ratio; break; }
+        if (L.eta(i) > 0.0f) break;
+        ratio *= fast_div(prev_rev, fmaxf(L.pdf_fwd(i), 1e-8f));
+        sum += ratio;
+        prev_rev = L.pdf_rev(i);
+    }
+    return sum;
+}
+// eye_sum / light_sum < 0: walk that subpath here (the table kernel, the one-thread-per-sample strategies); >= 0: mis_eye_sum(E, s_idx)
 template <class EA, class LA>
-B2_HD float mis_weight_core(const EA &E, int s_idx, const LA &L, int t_idx, float3 d_vec, float dist2, float3 cam_pos) {
+B2_HD float mis_weight_core(const EA &E, int s_idx, const LA &L, int t_idx, float3 d_vec, float dist2, float3 cam_pos, float eye_sum = -1.0f, float light_sum = -1.0f) {
     if (s_idx < 0 || t_idx < 0) return 0.0f;
     const float3 ns = normalize3(E.cur_n()), nt = normalize3(L.cur_n());
     const float3 md = d_vec * -1.0f;
@@ -356,14 +387,16 @@ B2_HD float mis_weight_core(const EA &E, int s_idx, const LA &L, int t_idx, floa
     const float pdf_s_to_t = pdf_omega_s * cos_t * inv_d2;
     const float pdf_t_to_s = pdf_omega_t * cos_s * inv_d2;
     float sum = 1.0f, ratio = 1.0f, prev_rev = pdf_t_to_s;
-    for (int i = s_idx; i > 0; --i) {                                      // :143-148
+    if (eye_sum >= 0.0f) sum += pdf_t_to_s * eye_sum;
+    else for (int i = s_idx; i > 0; --i) {                                 // :143-148
         if (E.eta(i) > 0.0f) break;
         ratio *= fast_div(prev_rev, fmaxf(E.pdf_fwd(i), 1e-8f));
         sum += ratio;
         prev_rev = E.pdf_rev(i);
     }
     ratio = 1.0f; prev_rev = pdf_s_to_t;
-    for (int i = t_idx; i > 0; --i) {                                      // :153-163
+    if (light_sum >= 0.0f) sum += pdf_s_to_t * light_sum;
+    else for (int i = t_idx; i > 0; --i) {                                 // :153-163
         if (L.is_src(i)) { ratio *= fast_div(prev_rev, fmaxf(L.pdf_fwd(i), 1e-8f)); sum += ratio; break; }
         if (L.eta(i) > 0.0f) break;
         ratio *= fast_div(prev_rev, fmaxf(L.pdf_fwd(i), 1e-8f));
@@ -474,14 +507,15 @@ B2_HD bool connect_prepare(const RenderCtx &c, const EyeVtx &ev, int lv_index, S
     pc = ev.thr * fE * G * fL * lv.thr;                                       // :433 without w (transmittance == 1 here)
     return true;
 }
-B2_HD float3 connect_weight(const RenderCtx &c, const EyeVtx &ev, int lv_index, float3 pc) {
+// eye_sum: mis_eye_sum of ev, or < 0; pool_walk: the pool records carry mis_light_sum (the render's pool; not the host simulator's)
+B2_HD float3 connect_weight(const RenderCtx &c, const EyeVtx &ev, int lv_index, float3 pc, float eye_sum = -1.0f, bool pool_walk = false) {
     const LightVtx lv = load_lv(c.pool, lv_index);
     const float3 d_vec = lv.pos - ev.pos;
     const float dist2 = dot3(d_vec, d_vec);
     const int t_idx = lv_index % c.light_depth;
     const RenderEyeAcc EA{ c, ev };
     const RenderLightAcc LA{ c, lv, lv_index - t_idx };
-    const float w = mis_weight_core(EA, ev.depth, LA, t_idx, d_vec, dist2, c.cam_eye);   // :431
+    const float w = mis_weight_core(EA, ev.depth, LA, t_idx, d_vec, dist2, c.cam_eye, eye_sum, pool_walk ? lv.walk : -1.0f);   // :431
     const float3 contrib = pc * w;
     return valid_color(contrib) ? clamp_radiance(contrib, 15.0f) : mk3(0.0f, 0.0f, 0.0f);   // :435-437
 }

@@ -34,6 +34,9 @@ constexpr int CONN_BLOCKS_PER_SM = B2_CONN_BLOCKS; // persistent grid = 148 SMs 
 #ifndef B2_CONN_CHUNK
 #define B2_CONN_CHUNK 4
 #endif
+#ifndef B2_MIS_WALKS_HOISTED
+#define B2_MIS_WALKS_HOISTED 1        // MIS weight: the light-side walk once per pool vertex (k_pool_active), the eye-side walk once per
+#endif                                // eye vertex and work item (k_connect), instead of both once per visible pair (0: round-1 form)
 constexpr int CONN_CHUNK = B2_CONN_CHUNK;         // pool vertices pre-tested per compaction round; the pre-test table is padded to a
                                       // multiple of this with records that never pass, and pool slices are whole chunks
 
@@ -64,7 +67,16 @@ __global__ void __launch_bounds__(1024) k_pool_active(RenderCtx c) {
         __syncthreads();
         int off = 0, tot = 0;
         for (int w = 0; w < nwarps; ++w) { const int v = s_warp[w]; if (w < warp) off += v; tot += v; }
-        if (act) make_pretest_rec(c, i, c.pre + (size_t) B2_PRE_F4 * (s_base + off + __popc(m & lanemask_lt())));
+        if (act) {
+            make_pretest_rec(c, i, c.pre + (size_t) B2_PRE_F4 * (s_base + off + __popc(m & lanemask_lt())));
+#if B2_MIS_WALKS_HOISTED
+            // the light-side walk of the MIS weight, once per pool vertex instead of once per visible pair (b2_bdpt.cuh: mis_light_sum)
+            const LightVtx lv = load_lv(c.pool, i);
+            const int t_idx = i % c.light_depth;
+            const float ls = mis_light_sum(RenderLightAcc{ c, lv, i - t_idx }, t_idx);
+            reinterpret_cast<float *>(c.pool + B2_LV_F4 * i + 4)[3] = isfinite(ls) ? ls : 3.0e38f;
+#endif
+        }
         __syncthreads();
         if (threadIdx.x == 0) s_base += tot;
         __syncthreads();
@@ -163,6 +175,7 @@ struct ConnSmem {
     float rq_px[CONN_RQ], rq_py[CONN_RQ], rq_pz[CONN_RQ]; uint32_t rq_e[CONN_RQ];
     float mq_px[CONN_MQ], mq_py[CONN_MQ], mq_pz[CONN_MQ]; uint32_t mq_e[CONN_MQ];
     float acc[3][32];
+    float eye_sum[32];                                         // mis_eye_sum of the item's 32 eye vertices (B2_MIS_WALKS_HOISTED)
 };
 // position of the (j+1)-th set bit of a non-empty mask with more than j bits (j is small: a lane has 0.5 candidate
 // triangles per step on average; the generic __fns costs ~25 instructions whatever j is)
@@ -209,6 +222,13 @@ __global__ void __launch_bounds__(CONN_THREADS, CONN_BLOCKS_PER_SM) k_connect(Re
         uint32_t my_pixel = 0u;
         if (valid) { const float4 f0 = c.cv[B2_CV_F4 * q]; my_pos = mk3(f0); my_pixel = __float_as_uint(f0.w) >> 8; my_n = mk3(c.cv[B2_CV_F4 * q + 1]); }
         Q.acc[0][lane] = 0.0f; Q.acc[1][lane] = 0.0f; Q.acc[2][lane] = 0.0f;
+#if B2_MIS_WALKS_HOISTED
+        {   // the eye-side walk of the MIS weight, once per eye vertex: the weight phase below multiplies it by the pair's pdf
+            float es = 0.0f;
+            if (valid) { const EyeVtx ev = load_cv(c.cv, q); es = mis_eye_sum(RenderEyeAcc{ c, ev }, ev.depth); }
+            Q.eye_sum[lane] = isfinite(es) ? es : 3.0e38f;     // an overflowing walk: the weight is zero either way (sum = inf)
+        }
+#endif
         __syncwarp();
         int n_buf = 0, n_rq = 0, n_mq = 0, ch = ch_begin;  // warp-uniform
         bool busy = false;                                 // this lane holds a shadow ray: tv, pc, e
@@ -226,7 +246,11 @@ __global__ void __launch_bounds__(CONN_THREADS, CONN_BLOCKS_PER_SM) k_connect(Re
                     const uint32_t ee = Q.mq_e[k];
                     const int owner = (int) (ee >> 27);
                     const EyeVtx ev = load_cv(c.cv, q0 + owner);
+#if B2_MIS_WALKS_HOISTED
+                    const float3 r = connect_weight(c, ev, (int) (ee & 0x7ffffffu), mk3(Q.mq_px[k], Q.mq_py[k], Q.mq_pz[k]), Q.eye_sum[owner], true);
+#else
                     const float3 r = connect_weight(c, ev, (int) (ee & 0x7ffffffu), mk3(Q.mq_px[k], Q.mq_py[k], Q.mq_pz[k]));
+#endif
                     n_path++;
                     if (r.x != 0.0f) atomicAdd(&Q.acc[0][owner], r.x);
                     if (r.y != 0.0f) atomicAdd(&Q.acc[1][owner], r.y);

@@ -96,6 +96,13 @@ void hs_render_bdpt(void *h, const B2Camera *cam, const B2RenderParams *p, float
     hs_render(s->view, *cam, *p, film, out);
     if (counters) { memcpy(counters, out.counters, sizeof(out.counters)); counters[B2_CNT_N] = out.pretest_mismatch; }
 }
+// the same render with the MIS walks hoisted out of the pair loop (k_pool_active + k_connect's form of the weight)
+void hs_render_bdpt_factored(void *h, const B2Camera *cam, const B2RenderParams *p, float *film, unsigned long long *counters) {
+    HsScene *s = (HsScene *) h;
+    HsRenderOut out;
+    hs_render(s->view, *cam, *p, film, out, true);
+    if (counters) { memcpy(counters, out.counters, sizeof(out.counters)); counters[B2_CNT_N] = out.pretest_mismatch; }
+}
 // pool20 layout as b2_light_pool / or_light_pool
 void hs_light_pool(void *h, const B2RenderParams *p, float *pool20) {
     HsScene *s = (HsScene *) h;

@@ -17,7 +17,9 @@ inline void hs_setup_ctx(RenderCtx &c, const DevScene &sc, const B2Camera &cam, 
     c.key = make_uint2((uint32_t) p.seed, (uint32_t) (p.seed >> 32));
 }
 
-inline void hs_build_pool(RenderCtx &c, std::vector<float4> &pool, std::vector<float4> &pre, unsigned long long *counters) {
+// factored: the MIS weight with its two walks hoisted out of the pair loop, as k_pool_active / k_connect run it (mis_light_sum in
+// the pool record, mis_eye_sum once per eye vertex); false: the reference's sequential walks per pair
+inline void hs_build_pool(RenderCtx &c, std::vector<float4> &pool, std::vector<float4> &pre, unsigned long long *counters, bool factored = false) {
     const int n_paths = c.sc.n_lights * c.spl;
     c.n_pool = n_paths * c.light_depth;
     pool.assign((size_t) B2_LV_F4 * std::max(c.n_pool, 1), make_float4(0, 0, 0, 0));
@@ -28,12 +30,20 @@ inline void hs_build_pool(RenderCtx &c, std::vector<float4> &pool, std::vector<f
     counters[B2_CNT_CLOSEST] += ncl; counters[B2_CNT_DELTA_CAP] += ncap; counters[B2_CNT_NODES] += tc.nodes; counters[B2_CNT_TRIS] += tc.tris;
     pre.clear();
     for (int i = 0; i < c.n_pool; ++i)
-        if (pool_vertex_active(c.pool, i)) { float4 r[B2_PRE_F4]; make_pretest_rec(c, i, r); pre.insert(pre.end(), r, r + B2_PRE_F4); }
+        if (pool_vertex_active(c.pool, i)) {
+            float4 r[B2_PRE_F4]; make_pretest_rec(c, i, r); pre.insert(pre.end(), r, r + B2_PRE_F4);
+            if (factored) {
+                const LightVtx lv = load_lv(c.pool, i);
+                const int t_idx = i % c.light_depth;
+                const float ls = mis_light_sum(RenderLightAcc{ c, lv, i - t_idx }, t_idx);
+                c.pool[B2_LV_F4 * i + 4].w = std::isfinite(ls) ? ls : 3.0e38f;
+            }
+        }
     c.pre = pre.data();
 }
 
 // Same wave structure as b2_render.cu: extend (primary or from stored state) -> compact eye-vertex list -> connect.
-inline void hs_render(const DevScene &sc, const B2Camera &cam, const B2RenderParams &p, float *film_out, HsRenderOut &out) {
+inline void hs_render(const DevScene &sc, const B2Camera &cam, const B2RenderParams &p, float *film_out, HsRenderOut &out, bool factored = false) {
     RenderCtx c; hs_setup_ctx(c, sc, cam, p);
     memset(&out, 0, sizeof(out));
     const int npix = p.width * p.height;
@@ -43,7 +53,7 @@ inline void hs_render(const DevScene &sc, const B2Camera &cam, const B2RenderPar
     for (int s = c.sample_offset; s < p.spp; s += c.sample_stride) n_my++;
     if (sc.n_lights > 0 && n_my > 0) {
         std::vector<float4> pool, pre;
-        hs_build_pool(c, pool, pre, out.counters);
+        hs_build_pool(c, pool, pre, out.counters, factored);
         const int n_act = (int) (pre.size() / B2_PRE_F4);
         const int max_paths = p.max_batch_paths > 0 ? p.max_batch_paths : (1 << 16);
         c.max_paths = max_paths;
@@ -87,6 +97,8 @@ inline void hs_render(const DevScene &sc, const B2Camera &cam, const B2RenderPar
                     const EyeVtx ev = load_cv(c.cv, q);
                     float3 sum = mk3(0, 0, 0);
                     uint32_t nsh = 0, npa = 0;
+                    float es = factored ? mis_eye_sum(RenderEyeAcc{ c, ev }, ev.depth) : -1.0f;
+                    if (factored && !std::isfinite(es)) es = 3.0e38f;
                     for (int a = 0; a < n_act; ++a) {
                         out.counters[B2_CNT_PAIRS]++;
                         const float4 r0 = c.pre[B2_PRE_F4 * a], r1 = c.pre[B2_PRE_F4 * a + 1], r2 = c.pre[B2_PRE_F4 * a + 2];
@@ -94,7 +106,13 @@ inline void hs_render(const DevScene &sc, const B2Camera &cam, const B2RenderPar
                         const bool pass = pretest_rec(ev.pos, ev.n, r0, r1, r2);
                         if (pass != connect_pretest(c, ev.pos, ev.n, lvi)) out.pretest_mismatch++;
                         if (!pass) continue;
-                        sum = sum + connect_finish<true>(c, ev, lvi, stack, 1, &tc, nsh, npa);
+                        if (!factored) { sum = sum + connect_finish<true>(c, ev, lvi, stack, 1, &tc, nsh, npa); continue; }
+                        ShadowRay sr; float3 pc;
+                        if (!connect_prepare(c, ev, lvi, sr, pc)) continue;
+                        nsh++;
+                        if (occluded_bvh<true>(c.sc, sr.o, sr.d, sr.tmax, stack, 1, &tc)) continue;
+                        npa++;
+                        sum = sum + connect_weight(c, ev, lvi, pc, es, true);
                     }
                     out.counters[B2_CNT_SHADOW] += nsh; out.counters[B2_CNT_PATH_SAMPLES] += npa;
                     film[3 * (size_t) ev.pixel] += sum.x; film[3 * (size_t) ev.pixel + 1] += sum.y; film[3 * (size_t) ev.pixel + 2] += sum.z;

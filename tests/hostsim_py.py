@@ -33,6 +33,7 @@ class HostSim:
         L.hs_bvh_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.hs_intersect.argtypes = [vp, vp, vp, sz, C.c_int, vp, vp, vp]
         L.hs_render_bdpt.argtypes = [vp, vp, C.POINTER(A.RenderParams), vp, vp]
+        L.hs_render_bdpt_factored.argtypes = [vp, vp, C.POINTER(A.RenderParams), vp, vp]
         L.hs_light_pool.argtypes = [vp, C.POINTER(A.RenderParams), vp]
         L.hs_render_other.argtypes = [vp, vp, C.POINTER(A.RenderParams), vp, vp]
         L.hs_render_strategies_c.argtypes = [vp, vp, C.POINTER(A.RenderParams), vp, vp]
@@ -57,11 +58,12 @@ class HostSim:
         self.L.hs_intersect(self.h, A.ptr(org), A.ptr(dirs), n, mode, A.ptr(ids), A.ptr(t), A.ptr(cnt))
         return ids, t, cnt
 
-    def render(self, W, H, spp, spl, eye_depth, light_depth, seed=1, sample_offset=0, sample_stride=1, film_mode=0, max_batch_paths=0, camera=None):
+    def render(self, W, H, spp, spl, eye_depth, light_depth, seed=1, sample_offset=0, sample_stride=1, film_mode=0, max_batch_paths=0, camera=None, factored=False):
+        """factored: the MIS weight as k_pool_active / k_connect compute it (walks hoisted out of the pair loop)."""
         cam = np.ascontiguousarray(self.data.camera if camera is None else camera, dtype=A.Camera).reshape(())
         p = A.RenderParams(W, H, spp, spl, eye_depth, light_depth, seed, sample_offset, sample_stride, film_mode, 0, 0, max_batch_paths, 1, 0)
         film = np.zeros((H, W, 3), np.float32); cnt = np.zeros(16, np.uint64)
-        self.L.hs_render_bdpt(self.h, cam.ctypes.data_as(C.c_void_p), C.byref(p), A.ptr(film), A.ptr(cnt))
+        (self.L.hs_render_bdpt_factored if factored else self.L.hs_render_bdpt)(self.h, cam.ctypes.data_as(C.c_void_p), C.byref(p), A.ptr(film), A.ptr(cnt))
         names = ["eye_samples", "closest_rays", "shadow_rays", "path_samples", "delta_cap_hits", "nodes", "tris", "pairs", "pretest_mismatch"]
         return film, {k: int(cnt[i]) for i, k in enumerate(names)}
 

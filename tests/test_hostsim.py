@@ -117,4 +117,8 @@ def test_wavefront_bodies_reproduce_the_oracle_render(name, depth):
     a, _ = hs.render(W, H, 3, 8, depth, depth, seed=5, sample_offset=0, sample_stride=2, film_mode=1)
     b, _ = hs.render(W, H, 3, 8, depth, depth, seed=5, sample_offset=1, sample_stride=2, film_mode=1)
     assert np.allclose((a + b) / 3.0, fo, rtol=1e-4, atol=1e-6)
+    # the MIS weight with both walks hoisted out of the pair loop (what k_pool_active + k_connect run): same terms, fp32 rounding only
+    ff, cf = hs.render(W, H, 3, 8, depth, depth, seed=5, max_batch_paths=500, factored=True)
+    assert cf["shadow_rays"] == cnt["shadow_rays"] and cf["path_samples"] == cnt["path_samples"]
+    assert np.allclose(ff, fh, rtol=2e-5, atol=1e-7)
     P.destroy(h); hs.close()
