@@ -426,6 +426,19 @@ int launch_isect(const DevScene &sc, int bvh_depth, const float *o, const float 
 
 }  // namespace
 
+int b2_sort_reserve(RaySortScratch &ss, size_t n) {
+    if (n >= ((size_t) 1 << 31)) { b2_set_error("more than 2^31 sort keys"); return B2_ERR_INVALID; }
+    B2_TRY(ss.keys.ensure(n)); B2_TRY(ss.keys_sorted.ensure(n)); B2_TRY(ss.idx.ensure(n)); B2_TRY(ss.idx_sorted.ensure(n));
+    size_t tmp_bytes = 0;
+    B2_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, ss.keys.p, ss.keys_sorted.p, ss.idx.p, ss.idx_sorted.p, (int) n, 0, 32, 0));
+    return ss.tmp.ensure(tmp_bytes);
+}
+int b2_sort_pairs(RaySortScratch &ss, size_t n, int end_bit, cudaStream_t st) {
+    size_t tmp_bytes = ss.tmp.n;
+    B2_CUDA(cub::DeviceRadixSort::SortPairs(ss.tmp.p, tmp_bytes, ss.keys.p, ss.keys_sorted.p, ss.idx.p, ss.idx_sorted.p, (int) n, 0, end_bit, st));
+    return B2_OK;
+}
+
 int b2_intersect_launch(const DevScene &sc, int bvh_depth, const float *d_org, const float *d_dir, size_t n, int mode,
                         int32_t *d_prim_id, float *d_t, unsigned long long *d_counters, cudaStream_t st, RaySortScratch *ss) {
     if (n == 0) return B2_OK;

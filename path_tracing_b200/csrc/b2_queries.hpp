@@ -8,6 +8,10 @@
 // All pointers are device pointers; asynchronous on `st`.
 // Scratch of the ray reordering (keys, ray indices, sorted copies, CUB's temporary storage); owned by the scene, grown on demand.
 struct RaySortScratch { DevBuf<uint32_t> keys, keys_sorted, idx, idx_sorted; DevBuf<unsigned char> tmp; };
+// (key, index) pairs of `ss.keys` / `ss.idx` sorted by the low `end_bit` key bits into `ss.keys_sorted` / `ss.idx_sorted`;
+// b2_sort_reserve sizes the five buffers for n pairs first (the connection stage's eye-vertex reordering uses the same scratch type)
+int b2_sort_reserve(RaySortScratch &ss, size_t n);
+int b2_sort_pairs(RaySortScratch &ss, size_t n, int end_bit, cudaStream_t st);
 int b2_intersect_launch(const DevScene &sc, int bvh_depth, const float *d_org, const float *d_dir, size_t n, int mode,
                         int32_t *d_prim_id, float *d_t, unsigned long long *d_counters, cudaStream_t st, RaySortScratch *sort_scratch = nullptr);
 

@@ -20,6 +20,7 @@
 #include "b2_strategies.cuh"
 #include "b2_warp.cuh"
 #include <algorithm>
+#include <cstdlib>
 #include <vector>
 
 namespace {
@@ -90,6 +91,35 @@ __global__ void __launch_bounds__(1024) k_pool_active(RenderCtx c) {
     if (threadIdx.x == 0) *c.n_pool_active = n;
 }
 
+// Connection stage on position-sorted eye vertices (B2_CONN_SORT_CV; A/B in profiles/r02_connect_summary.md, section 5): a work
+// item of k_connect is 32 CONSECUTIVE records, whose shadow rays to one pool vertex share BVH nodes only if the 32 vertices are
+// close together -- true for primary hits of neighbouring pixels, not after a bounce.  Key = 30-bit Morton code of the position
+// inside the scene box; records past n_cv (the launch is sized by the host's upper bound n_live) sort last.
+__device__ __forceinline__ uint32_t spread10(uint32_t x) {
+    x &= 0x3ffu;
+    x = (x | (x << 16)) & 0x030000ffu; x = (x | (x << 8)) & 0x0300f00fu; x = (x | (x << 4)) & 0x030c30c3u; x = (x | (x << 2)) & 0x09249249u;
+    return x;
+}
+__global__ void __launch_bounds__(256) k_cv_keys(RenderCtx c, uint32_t n_upper, uint32_t *__restrict__ keys, uint32_t *__restrict__ idx) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_upper) return;
+    uint32_t key = 1u << 30;
+    if ((int) i < *c.n_cv) {
+        const float4 f0 = c.cv[B2_CV_F4 * (size_t) i];
+        const float3 lo = c.sc.scene_min, hi = c.sc.scene_max;
+        const float qx = (f0.x - lo.x) / fmaxf(hi.x - lo.x, 1e-30f), qy = (f0.y - lo.y) / fmaxf(hi.y - lo.y, 1e-30f), qz = (f0.z - lo.z) / fmaxf(hi.z - lo.z, 1e-30f);
+        const uint32_t cx = (uint32_t) fminf(fmaxf(qx * 1024.0f, 0.0f), 1023.0f), cy = (uint32_t) fminf(fmaxf(qy * 1024.0f, 0.0f), 1023.0f), cz = (uint32_t) fminf(fmaxf(qz * 1024.0f, 0.0f), 1023.0f);
+        key = spread10(cx) | (spread10(cy) << 1) | (spread10(cz) << 2);
+    }
+    keys[i] = key; idx[i] = i;
+}
+__global__ void __launch_bounds__(256) k_cv_gather(RenderCtx c, uint32_t n_upper, const uint32_t *__restrict__ order, float4 *__restrict__ out) {
+    const size_t t = (size_t) blockIdx.x * blockDim.x + threadIdx.x;          // one 16-byte row per thread
+    const uint32_t rec = (uint32_t) (t / B2_CV_F4), row = (uint32_t) (t % B2_CV_F4);
+    if (rec >= n_upper || (int) rec >= *c.n_cv) return;
+    out[t] = c.cv[(size_t) B2_CV_F4 * order[rec] + row];
+}
+
 // One bounce of every live path.  PRIMARY: item = sample w0 + i of the batch (no state in HBM yet).
 template <bool PRIMARY, bool COUNT>
 __global__ void __launch_bounds__(EXT_THREADS) k_extend(RenderCtx c, int n_items, uint32_t pix0, int s0) {
@@ -155,6 +185,15 @@ constexpr int CONN_MQ = 64;           // visible-pair queue: < 32 left + 32 new 
 #define B2_CONN_RQ_POOL 40
 #endif
 template <bool POOL> struct ConnCfg { static constexpr int RQ = POOL ? B2_CONN_RQ_POOL : 64, RQ_LOW = POOL ? B2_CONN_RQ_POOL - 32 : 32; };
+#ifndef B2_CONN_SORT_CV
+#define B2_CONN_SORT_CV 2             // 1: eye vertices of the waves after the primary one sorted by position before k_connect; 2: every wave
+#endif
+#ifndef B2_CONN_SORT_MIN_RAYS
+#define B2_CONN_SORT_MIN_RAYS 16      // ... when the first connection launch sent at least this many shadow rays per eye vertex
+#endif
+#ifndef B2_CONN_SORT_MIN
+#define B2_CONN_SORT_MIN (1 << 16)    // ... for waves of at least this many live paths
+#endif
 #ifndef B2_FAST_SHADOW_TRI
 #define B2_FAST_SHADOW_TRI 1          // contracted Moeller-Trumbore for the shadow rays of the connection stage (b2_isect.cuh)
 #endif
@@ -498,6 +537,10 @@ int RenderWorkspace::ensure(int max_paths, int eye_depth, int n_pool, size_t fil
     if (!h_ints) B2_CUDA(cudaMallocHost((void **) &h_ints, 8 * sizeof(int)));
     return B2_OK;
 }
+int RenderWorkspace::ensure_cv_sort(int max_paths) {
+    if ((size_t) B2_CV_F4 * max_paths > cv_sorted.n) B2_TRY(cv_sorted.alloc((size_t) B2_CV_F4 * max_paths));
+    return b2_sort_reserve(cv_sort, (size_t) max_paths);
+}
 int RenderWorkspace::ensure_out(size_t film_floats) {
     if (film_floats > film_out.n) B2_TRY(film_out.alloc(film_floats));
     if (film_floats > h_film_n) {
@@ -514,6 +557,7 @@ void RenderWorkspace::release() {
     ray_o.release(); ray_d.release(); thr.release(); last_pos.release(); last_n.release();
     hist_pe.release(); hist_pdf.release(); live_a.release(); live_b.release(); cv.release();
     pool.release(); pre.release(); film.release(); ints.release(); counters.release();
+    cv_sorted.release(); cv_sort.keys.release(); cv_sort.keys_sorted.release(); cv_sort.idx.release(); cv_sort.idx_sorted.release(); cv_sort.tmp.release();
     hp_in.release(); hp.release(); flux.release(); hp_keys.release(); hp_keys_sorted.release(); hp_order.release(); hp_order_sorted.release();
     cell_table.release(); sort_tmp.release();
     mw_f4.release(); mw_i32.release(); mw_pairs.release();
@@ -634,7 +678,8 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
         // default: up to 2^26 samples in flight (C2 in one batch: the per-batch tails of the extend/connect waves cost ~0.35 ms
         // each, 8.2 -> 10.0 Gsamples/s from 2^24 to 2^26), halved until the wavefront state (104 + 24 B per depth and sample,
         // 24 GB at depth 8) fits in half of the free HBM
-        const size_t per_path = 5 * sizeof(float4) + (size_t) std::max(p.eye_depth, 1) * (sizeof(float4) + sizeof(float2)) + 2 * sizeof(int) + B2_CV_F4 * sizeof(float4);
+        const size_t per_path = 5 * sizeof(float4) + (size_t) std::max(p.eye_depth, 1) * (sizeof(float4) + sizeof(float2)) + 2 * sizeof(int) + B2_CV_F4 * sizeof(float4)
+                                + (B2_CONN_SORT_CV ? B2_CV_F4 * sizeof(float4) + 24 : 0);      // sorted records, keys, order, radix scratch
         mp = std::min<long long>(1ll << B2_DEFAULT_BATCH_LOG2, std::max<long long>(total, 1));
         if (mp > ws.cap_paths || p.eye_depth > ws.cap_depth) {            // only when the workspace has to grow (cudaMemGetInfo costs > 1 ms)
             size_t free_b = 0, total_b = 0;
@@ -653,9 +698,24 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
     RenderCtx c; b2_setup_ctx(c, sc, cam, p, ws, max_paths);
     const bool count = p.count_traversal != 0;
     uint64_t n_launches = 0, n_batches = 0, n_waves = 0;
+    const bool conn_pool = sc.n_tris >= B2_CONN_POOL_MIN_TRIS;
+    // Eye vertices sorted by position ahead of k_connect: -1 = not decided yet, 0 = no, 1 = yes.  It pays when an eye vertex sends
+    // enough shadow rays (C3: 52 per vertex, 936 -> 837 ms; C1: 74, 187 -> 148 ms; C2: ~2, 5.99 -> 9.7 ms), which only the first
+    // connection launch can tell: that one runs unsorted and its shadow-ray counter decides for the rest of the render; the
+    // workspace remembers the answer for the next call with the same sampling parameters.
+    const unsigned long long sort_cfg = ((unsigned long long) p.spl << 48) ^ ((unsigned long long) p.light_depth << 40) ^ ((unsigned long long) p.eye_depth << 32)
+                                        ^ ((unsigned long long) p.width << 16) ^ (unsigned long long) p.height ^ 0x8000000000000000ull;
+    int sort_cv = (B2_CONN_SORT_CV != 0 && p.strategies == B2_STRATEGIES_REFERENCE && max_paths >= B2_CONN_SORT_MIN) ? -1 : 0;
+    if (sort_cv != 0) {                                       // B2PT_CONN_SORT=0 / 1 in the environment: never / always (tests, A/B runs)
+        const char *force = getenv("B2PT_CONN_SORT");
+        if (force && (force[0] == '0' || force[0] == '1') && force[1] == 0) sort_cv = force[0] - '0';
+    }
+    if (sort_cv < 0 && ws.sort_cfg == sort_cfg) sort_cv = ws.sort_yes;
+    if (sort_cv > 0) B2_TRY(ws.ensure_cv_sort(max_paths));
+    bool sort_probe = false; int sort_probe_vertices = 0;     // counter copy of the first launch queued / its eye-vertex count
     StageTimer tm; tm.on = p.profile_stages != 0; tm.st = st;
-    CudaEvent ev0, ev1, ev2, ev_wave;
-    B2_CUDA(ev0.create()); B2_CUDA(ev1.create()); B2_CUDA(ev2.create()); B2_CUDA(ev_wave.create(cudaEventDisableTiming));
+    CudaEvent ev0, ev1, ev2, ev_wave, ev_pool;
+    B2_CUDA(ev0.create()); B2_CUDA(ev1.create()); B2_CUDA(ev2.create()); B2_CUDA(ev_wave.create(cudaEventDisableTiming)); B2_CUDA(ev_pool.create(cudaEventDisableTiming));
     B2_CUDA(cudaEventRecord(ev0, st));
     B2_CUDA(cudaMemsetAsync(ws.film.p, 0, sizeof(float) * film_floats, st));
     B2_CUDA(cudaMemsetAsync(ws.counters.p, 0, sizeof(unsigned long long) * B2_CNT_N, st));
@@ -668,6 +728,7 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
     if (sc.n_lights > 0 && total > 0) {
         if (ref_set) B2_TRY(build_pool(c, bvh_depth, count, st, n_launches));
         B2_CUDA(cudaEventRecord(ev1, st));
+
         const size_t sb_t = stack_bytes(EXT_THREADS, bvh_depth), sb_c = stack_bytes(CONN_THREADS, bvh_depth);
         if (lt_pass) {                                       // t = 1: W*H*n_my light subpaths, splatted straight into the film sums
             const CamFrame cf = cam_frame(c.cdx, c.cdy);
@@ -712,9 +773,29 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
                 const unsigned gc = (unsigned) std::min<long long>((long long) sc.n_sms * CONN_BLOCKS_PER_SM, std::max<long long>(1, ((long long) n_live * 8 + CONN_THREADS - 1) / CONN_THREADS));
                 tm.begin(StageTimer::CONNECT);
                 if (ref_set) {
-                    const bool pool = sc.n_tris >= B2_CONN_POOL_MIN_TRIS;
-                    if (pool) { if (count) k_connect<true, true><<<gc, CONN_THREADS, sb_c, st>>>(c); else k_connect<false, true><<<gc, CONN_THREADS, sb_c, st>>>(c); }
-                    else { if (count) k_connect<true, false><<<gc, CONN_THREADS, sb_c, st>>>(c); else k_connect<false, false><<<gc, CONN_THREADS, sb_c, st>>>(c); }
+                    const bool pool = conn_pool;
+                    RenderCtx cc = c;
+                    if (sort_cv < 0 && sort_probe) {            // second connection launch: the first one's counter is (nearly) there --
+                        B2_CUDA(cudaEventSynchronize(ev_pool));  // the extend launch queued above keeps the GPU busy meanwhile
+                        unsigned long long rays; memcpy(&rays, ws.h_ints + 6, sizeof(rays));
+                        sort_cv = rays >= (unsigned long long) B2_CONN_SORT_MIN_RAYS * (unsigned long long) std::max(sort_probe_vertices, 1) ? 1 : 0;
+                        ws.sort_cfg = sort_cfg; ws.sort_yes = sort_cv;
+                        if (sort_cv > 0) B2_TRY(ws.ensure_cv_sort(max_paths));      // grows once per workspace
+                    }
+                    if (sort_cv > 0 && n_live >= B2_CONN_SORT_MIN && (!primary || B2_CONN_SORT_CV >= 2)) {
+                        const uint32_t nu = (uint32_t) n_live;                 // n_cv <= n_live; the device count is read by the kernels
+                        k_cv_keys<<<blocks_for(nu, 256), 256, 0, st>>>(c, nu, ws.cv_sort.keys.p, ws.cv_sort.idx.p);
+                        B2_TRY(b2_sort_pairs(ws.cv_sort, nu, 31, st));
+                        k_cv_gather<<<blocks_for((size_t) nu * B2_CV_F4, 256), 256, 0, st>>>(c, nu, ws.cv_sort.idx_sorted.p, ws.cv_sorted.p);
+                        cc.cv = ws.cv_sorted.p;
+                        n_launches += 3;
+                    }
+                    if (pool) { if (count) k_connect<true, true><<<gc, CONN_THREADS, sb_c, st>>>(cc); else k_connect<false, true><<<gc, CONN_THREADS, sb_c, st>>>(cc); }
+                    else { if (count) k_connect<true, false><<<gc, CONN_THREADS, sb_c, st>>>(cc); else k_connect<false, false><<<gc, CONN_THREADS, sb_c, st>>>(cc); }
+                    if (sort_cv < 0 && !sort_probe) {
+                        B2_CUDA(cudaMemcpyAsync(ws.h_ints + 6, ws.counters.p + B2_CNT_SHADOW, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+                        B2_CUDA(cudaEventRecord(ev_pool, st));
+                    }
                 } else {
                     const unsigned gn = (unsigned) std::min<long long>((long long) sc.n_sms * 8, blocks_for(n_live, EXT_THREADS));
                     if (count) k_nee<true><<<gn, EXT_THREADS, sb_t, st>>>(c, w_mix);
@@ -728,6 +809,7 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
                 ws.closest_rays_host += (unsigned long long) n_live;
                 n_live = ws.h_ints[0];
                 eye_vertices += (unsigned long long) ws.h_ints[1];
+                if (sort_cv < 0 && !sort_probe) { sort_probe = true; sort_probe_vertices = ws.h_ints[1]; }
                 std::swap(c.live, c.live_next);
                 primary = false;
             }

@@ -2,6 +2,7 @@
 #pragma once
 #include "b2_cuda_util.hpp"
 #include "b2_bdpt.cuh"
+#include "b2_queries.hpp"
 
 // Device buffers of the wavefront state; owned by a B2Scene and kept across calls (grown on demand).
 struct RenderWorkspace {
@@ -27,6 +28,10 @@ struct RenderWorkspace {
     // B2_STRATEGIES_MIS as a wavefront (b2_mis_wave.cu): walk state, stored light vertices, eye history and records; counters + queues; pairs
     DevBuf<float4> mw_f4; DevBuf<int> mw_i32; DevBuf<uint2> mw_pairs;
     int ensure_mis_wave(int slots, int n_lights, size_t film_floats);
+    // connection stage on position-sorted eye vertices (B2_CONN_SORT_CV): the reordered records and the sort's scratch
+    DevBuf<float4> cv_sorted; RaySortScratch cv_sort;
+    int ensure_cv_sort(int max_paths);
+    unsigned long long sort_cfg = 0; int sort_yes = 0;       // the last render's decision and the sampling parameters it was taken for
     void release();
     ~RenderWorkspace() { release(); }
 };

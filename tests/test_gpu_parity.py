@@ -342,6 +342,30 @@ def test_reordered_ray_batches_return_the_answers_of_the_callers_order():
     sc.close()
 
 
+@pytest.mark.parametrize("name", ["cornell", "mis"])
+def test_position_sorted_eye_vertices_give_the_film_of_the_callers_order(name, monkeypatch):
+    """The connection stage runs on eye-vertex records sorted by position when that pays (csrc/b2_render.cu: k_cv_keys + radix sort
+    + k_cv_gather in front of k_connect; decided from the first launch's shadow rays per eye vertex).  Which 32 vertices share a
+    warp changes nothing any of them computes: every counter is equal and the films differ by the order of the fp32 atomic adds.
+    B2PT_CONN_SORT=1 / 0 force both forms; the default must be one of them."""
+    sd = reference_scene(name)
+    films, stats = {}, {}
+    for mode in ("0", "1", None):
+        if mode is None: monkeypatch.delenv("B2PT_CONN_SORT", raising=False)
+        else: monkeypatch.setenv("B2PT_CONN_SORT", mode)
+        sc = api.Scene(sd)
+        for _ in range(2):                       # the second call of the default mode runs with the remembered decision
+            films[mode], stats[mode] = sc.render_bdpt(width=320, height=256, spp=4, spl=8, eye_depth=8, light_depth=8, seed=3)
+        sc.close()
+    for k in ("eye_samples", "closest_rays", "shadow_rays", "path_samples", "pairs_tested", "eye_vertices"):
+        assert stats["0"][k] == stats["1"][k] == stats[None][k], k
+    assert stats["1"]["n_launches"] > stats["0"]["n_launches"]
+    assert stats[None]["n_launches"] in (stats["0"]["n_launches"], stats["1"]["n_launches"])
+    scale = float(np.abs(films["0"]).mean())
+    assert np.allclose(films["1"], films["0"], rtol=1e-4, atol=1e-5 * scale)
+    assert np.allclose(films[None], films["0"], rtol=1e-4, atol=1e-5 * scale)
+
+
 @pytest.mark.parametrize("n", [7, 600, 1024, 1025])
 def test_single_cta_build_of_small_scenes_gives_the_tree_of_the_host_mirror(n):
     """n <= 1024 triangles: every PLOC pass and collapse level runs in one CTA (k_build_small, csrc/b2_bvh_build.cu); above, one

@@ -9,4 +9,4 @@ with tempfile.TemporaryDirectory() as d:
     sd = SceneData.from_file(gen.write_obj_scene(d, n_tris=1 << 20, width=W, height=H), obj_directive=True)
 sc = api.Scene(sd)
 film, st = sc.render_bdpt(width=W, height=H, spp=spp, spl=spl, eye_depth=depth, light_depth=depth, seed=1, profile_stages=True)
-print(json.dumps({k: st[k] for k in ("ms_total", "ms_primary", "ms_extend", "ms_connect", "eye_samples", "shadow_rays", "path_samples", "pairs_tested", "eye_vertices", "n_waves", "n_launches")}))
+print(json.dumps({k: st[k] for k in ("ms_total", "ms_primary", "ms_extend", "ms_connect", "eye_samples", "shadow_rays", "path_samples", "pairs_tested", "eye_vertices", "n_waves", "n_launches")} | {"film_mean": float(film.mean(dtype="float64"))}))
