@@ -92,7 +92,7 @@ template <class T> static int upload(DevBuf<T> &d, const std::vector<T> &h, cuda
 extern "C" {
 
 const char *b2_last_error(void) { return g_err; }
-const char *b2_version(void) { return "b2pt 0.2.5 (sm_100a)"; }     // bump with every kernel change: profiles/*_traffic.json are tied to it
+const char *b2_version(void) { return "b2pt 0.2.6 (sm_100a)"; }     // bump with every kernel change: profiles/*_traffic.json are tied to it
 int b2_device_count(int *count) {
     if (!count) { b2_set_error("count is NULL"); return B2_ERR_INVALID; }
     int n = 0;
