@@ -161,7 +161,13 @@ int b2_intersect_device(B2Scene *scene, const float *d_org, const float *d_dir, 
 /* Visit counters accumulated by B2_COUNT_VISITS launches since the last reset: out[0]=rays, [1]=nodes, [2]=tris. */
 int b2_intersect_counters(B2Scene *scene, uint64_t out[3], int reset);
 
-/* ---- render ---- */
+/* ---- render ----
+ * BDPT reference strategy set: when the first connection launch of a render sends >= 16 shadow rays per eye vertex, the
+ * connection stage of every later wave (and of later calls with the same spl / depths / film size on this handle) runs on
+ * eye-vertex records sorted by position (30-bit Morton keys, one radix sort per wave; csrc/b2_render.cu).  This changes which
+ * 32 vertices share a warp, not what any of them computes: counters are equal, films differ by the order of the fp32 atomic
+ * adds only.  It holds a second record buffer (80 B per eye sample in flight) on the handle.  The environment variable
+ * B2PT_CONN_SORT=0 / 1 forces caller order / sorted order (tests, A/B runs). */
 int b2_render_bdpt(B2Scene *scene, const B2Camera *cam, const B2RenderParams *params, float *film_rgb_host,
                    B2Stats *stats);
 /* Film stays on the device (W*H*3 fp32, caller-owned, e.g. a torch tensor); work is enqueued on `stream`

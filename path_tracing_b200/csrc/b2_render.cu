@@ -711,7 +711,8 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
         if (force && (force[0] == '0' || force[0] == '1') && force[1] == 0) sort_cv = force[0] - '0';
     }
     if (sort_cv < 0 && ws.sort_cfg == sort_cfg) sort_cv = ws.sort_yes;
-    if (sort_cv > 0) B2_TRY(ws.ensure_cv_sort(max_paths));
+    // the reordering is an optimisation: without memory for the second record buffer the render goes on in caller order
+    if (sort_cv > 0 && ws.ensure_cv_sort(max_paths) != B2_OK) { cudaGetLastError(); sort_cv = 0; }
     bool sort_probe = false; int sort_probe_vertices = 0;     // counter copy of the first launch queued / its eye-vertex count
     StageTimer tm; tm.on = p.profile_stages != 0; tm.st = st;
     CudaEvent ev0, ev1, ev2, ev_wave, ev_pool;
@@ -780,7 +781,7 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
                         unsigned long long rays; memcpy(&rays, ws.h_ints + 6, sizeof(rays));
                         sort_cv = rays >= (unsigned long long) B2_CONN_SORT_MIN_RAYS * (unsigned long long) std::max(sort_probe_vertices, 1) ? 1 : 0;
                         ws.sort_cfg = sort_cfg; ws.sort_yes = sort_cv;
-                        if (sort_cv > 0) B2_TRY(ws.ensure_cv_sort(max_paths));      // grows once per workspace
+                        if (sort_cv > 0 && ws.ensure_cv_sort(max_paths) != B2_OK) { cudaGetLastError(); sort_cv = 0; }   // grows once per workspace
                     }
                     if (sort_cv > 0 && n_live >= B2_CONN_SORT_MIN && (!primary || B2_CONN_SORT_CV >= 2)) {
                         const uint32_t nu = (uint32_t) n_live;                 // n_cv <= n_live; the device count is read by the kernels
@@ -788,7 +789,7 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
                         B2_TRY(b2_sort_pairs(ws.cv_sort, nu, 31, st));
                         k_cv_gather<<<blocks_for((size_t) nu * B2_CV_F4, 256), 256, 0, st>>>(c, nu, ws.cv_sort.idx_sorted.p, ws.cv_sorted.p);
                         cc.cv = ws.cv_sorted.p;
-                        n_launches += 3;
+                        n_launches += 8;                                       // keys, gather, CUB: histogram + scan + four 8-bit passes
                     }
                     if (pool) { if (count) k_connect<true, true><<<gc, CONN_THREADS, sb_c, st>>>(cc); else k_connect<false, true><<<gc, CONN_THREADS, sb_c, st>>>(cc); }
                     else { if (count) k_connect<true, false><<<gc, CONN_THREADS, sb_c, st>>>(cc); else k_connect<false, false><<<gc, CONN_THREADS, sb_c, st>>>(cc); }
