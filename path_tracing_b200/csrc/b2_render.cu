@@ -684,7 +684,8 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
         if (mp > ws.cap_paths || p.eye_depth > ws.cap_depth) {            // only when the workspace has to grow (cudaMemGetInfo costs > 1 ms)
             size_t free_b = 0, total_b = 0;
             B2_CUDA(cudaMemGetInfo(&free_b, &total_b));
-            const size_t have = (size_t) std::max(ws.cap_paths, 0) * (5 * sizeof(float4) + (size_t) std::max(ws.cap_depth, 0) * (sizeof(float4) + sizeof(float2)) + 2 * sizeof(int) + B2_CV_F4 * sizeof(float4));
+            const size_t have = (size_t) std::max(ws.cap_paths, 0) * (5 * sizeof(float4) + (size_t) std::max(ws.cap_depth, 0) * (sizeof(float4) + sizeof(float2)) + 2 * sizeof(int) + B2_CV_F4 * sizeof(float4))
+                                + ws.cv_sorted.n * sizeof(float4) + ws.cv_sort.keys.n * 16 + ws.cv_sort.tmp.n;
             while (mp > (1ll << 20) && (size_t) mp * per_path > (free_b + have) / 2) mp >>= 1;
             if (mp < ws.cap_paths && p.eye_depth <= ws.cap_depth) mp = ws.cap_paths;
         }
