@@ -103,6 +103,41 @@ void hs_render_bdpt_factored(void *h, const B2Camera *cam, const B2RenderParams 
     hs_render(s->view, *cam, *p, film, out, true);
     if (counters) { memcpy(counters, out.counters, sizeof(out.counters)); counters[B2_CNT_N] = out.pretest_mismatch; }
 }
+// mis_weight_core over flat vertex arrays (the layout of b2_mis_weight: eye 17 floats, light 20 floats per vertex, V vertices per
+// chain); factored != 0: both walks through mis_eye_sum / mis_light_sum, as the connection stage evaluates the weight
+namespace {
+struct HsFlatEye {
+    const float *v; int s;
+    float3 pos(int i) const { return make_float3(v[17 * i], v[17 * i + 1], v[17 * i + 2]); }
+    float eta(int i) const { return v[17 * i + 14]; }
+    float pdf_fwd(int i) const { return v[17 * i + 15]; }
+    float pdf_rev(int i) const { return v[17 * i + 16]; }
+    float3 cur_n() const { return make_float3(v[17 * s + 3], v[17 * s + 4], v[17 * s + 5]); }
+    Mat cur_mtl() const { const float *m = v + 17 * s + 9; Mat r; r.base = make_float3(m[0], m[1], m[2]); r.roughness = m[3]; r.metallic = m[4]; r.eta = m[5]; return r; }
+};
+struct HsFlatLight {
+    const float *v; int t;
+    float3 pos(int i) const { return make_float3(v[20 * i], v[20 * i + 1], v[20 * i + 2]); }
+    float eta(int i) const { return v[20 * i + 14]; }
+    bool is_src(int i) const { return v[20 * i + 15] != 0.0f; }
+    float pdf_fwd(int i) const { return v[20 * i + 18]; }
+    float pdf_rev(int i) const { return v[20 * i + 19]; }
+    float3 cur_n() const { return make_float3(v[20 * t + 3], v[20 * t + 4], v[20 * t + 5]); }
+    Mat cur_mtl() const { const float *m = v + 20 * t + 9; Mat r; r.base = make_float3(m[0], m[1], m[2]); r.roughness = m[3]; r.metallic = m[4]; r.eta = m[5]; return r; }
+};
+}
+void hs_mis_weight(size_t n, int V, const float *eye17, const int32_t *s_idx, const float *lit20, const int32_t *t_idx, const float *d_vec,
+                   const float *dist2, const float *cam_pos, int factored, float *out) {
+    for (size_t i = 0; i < n; ++i) {
+        const int s = s_idx[i], t = t_idx[i];
+        if (s < 0 || t < 0 || s >= V || t >= V) { out[i] = 0.0f; continue; }
+        const HsFlatEye E{ eye17 + (size_t) 17 * V * i, s };
+        const HsFlatLight L{ lit20 + (size_t) 20 * V * i, t };
+        const float3 d = make_float3(d_vec[3 * i], d_vec[3 * i + 1], d_vec[3 * i + 2]), cp = make_float3(cam_pos[3 * i], cam_pos[3 * i + 1], cam_pos[3 * i + 2]);
+        out[i] = factored ? mis_weight_core(E, s, L, t, d, dist2[i], cp, mis_eye_sum(E, s), mis_light_sum(L, t))
+                          : mis_weight_core(E, s, L, t, d, dist2[i], cp);
+    }
+}
 // pool20 layout as b2_light_pool / or_light_pool
 void hs_light_pool(void *h, const B2RenderParams *p, float *pool20) {
     HsScene *s = (HsScene *) h;

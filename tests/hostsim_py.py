@@ -22,6 +22,22 @@ def build():
                     os.path.join(HERE, "hostsim.cpp"), "-o", SO], check=True)
 
 
+def mis_weight(eye, s_idx, lit, t_idx, d_vec, dist2, cam_pos, factored=False):
+    """mis_weight_core of csrc/b2_bdpt.cuh compiled for the host, over flat chains (eye [n, V, 17], lit [n, V, 20]);
+    factored: the two walks through mis_eye_sum / mis_light_sum (what k_pool_active + k_connect evaluate)."""
+    build()
+    L = C.CDLL(SO)
+    eye = np.ascontiguousarray(eye, np.float32); lit = np.ascontiguousarray(lit, np.float32)
+    n, V = eye.shape[0], eye.shape[1]
+    s_idx = np.ascontiguousarray(s_idx, np.int32); t_idx = np.ascontiguousarray(t_idx, np.int32)
+    d_vec = np.ascontiguousarray(d_vec, np.float32); dist2 = np.ascontiguousarray(dist2, np.float32); cam_pos = np.ascontiguousarray(cam_pos, np.float32)
+    out = np.zeros(n, np.float32)
+    vp = C.c_void_p
+    L.hs_mis_weight.argtypes = [C.c_size_t, C.c_int, vp, vp, vp, vp, vp, vp, vp, C.c_int, vp]
+    L.hs_mis_weight(n, V, A.ptr(eye), A.ptr(s_idx), A.ptr(lit), A.ptr(t_idx), A.ptr(d_vec), A.ptr(dist2), A.ptr(cam_pos), int(factored), A.ptr(out))
+    return out
+
+
 class HostSim:
     def __init__(self, data, max_leaf=0, pad_rel=0.0):
         build()

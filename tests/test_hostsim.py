@@ -97,7 +97,7 @@ def test_threaded_flatten_of_large_triangle_scenes_equals_the_general_path(monke
     P.destroy(h)
 
 
-@pytest.mark.parametrize("name,depth", [("cornell", 6), ("mis", 8)])
+@pytest.mark.parametrize("name,depth", [("cornell", 6), ("mis", 8), ("mis_variant", 8)])
 def test_wavefront_bodies_reproduce_the_oracle_render(name, depth):
     sd = reference_scene(name)
     hs = HostSim(sd)
@@ -122,3 +122,22 @@ def test_wavefront_bodies_reproduce_the_oracle_render(name, depth):
     assert cf["shadow_rays"] == cnt["shadow_rays"] and cf["path_samples"] == cnt["path_samples"]
     assert np.allclose(ff, fh, rtol=2e-5, atol=1e-7)
     P.destroy(h); hs.close()
+
+
+def test_factored_mis_weight_reproduces_the_reference_golden_weights():
+    """The connection stage evaluates cpu_calculate_mis_weight (cpu_bdpt.cpp:112-167) with both subpath walks hoisted out of the
+    pair loop: each walk is linear in the one pdf that depends on the pair (mis_eye_sum / mis_light_sum, csrc/b2_bdpt.cuh).
+    On the 3 000 chains the unmodified reference produced (arbitrary pdf_fwd / pdf_rev at every vertex, delta vertices,
+    pseudo-source vertices): the sequential form on the host, the factored form, and the golden weights agree - the same
+    vertices give a zero weight, and the non-zero ones are within fp32 rounding of each other."""
+    from hostsim_py import mis_weight
+    g = np.load(os.path.join(GOLD, "mis_tables.npz"))
+    args = (g["eye"], g["s_idx"], g["lit"], g["t_idx"], g["d_vec"], g["dist2"], g["cam_pos"])
+    seq, fac = mis_weight(*args), mis_weight(*args, factored=True)
+    want = g["w"]
+    assert ((seq > 0) == (want > 0)).all() and ((fac > 0) == (want > 0)).mean() > 0.999
+    live = (want > 0) & (fac > 0)
+    assert live.mean() > 0.3
+    assert np.allclose(seq[live], want[live], rtol=2e-5, atol=0.0)
+    assert np.allclose(fac[live], seq[live], rtol=2e-5, atol=0.0)
+
