@@ -53,6 +53,24 @@ __global__ void __launch_bounds__(EXT_THREADS) k_light_paths(RenderCtx c, int n_
     if (COUNT) { warp_count_add(&c.counters[B2_CNT_NODES], tc.nodes); warp_count_add(&c.counters[B2_CNT_TRIS], tc.tris); }
 }
 
+// 30-bit Morton code of a position inside the scene box (NaN / outside: clamped, any order is a valid order)
+__device__ __forceinline__ uint32_t spread10(uint32_t x) {
+    x &= 0x3ffu;
+    x = (x | (x << 16)) & 0x030000ffu; x = (x | (x << 8)) & 0x0300f00fu; x = (x | (x << 4)) & 0x030c30c3u; x = (x | (x << 2)) & 0x09249249u;
+    return x;
+}
+__device__ __forceinline__ uint32_t morton30(const DevScene &sc, float x, float y, float z) {
+    const float3 lo = sc.scene_min, hi = sc.scene_max;
+    const float qx = (x - lo.x) / fmaxf(hi.x - lo.x, 1e-30f), qy = (y - lo.y) / fmaxf(hi.y - lo.y, 1e-30f), qz = (z - lo.z) / fmaxf(hi.z - lo.z, 1e-30f);
+    const uint32_t cx = (uint32_t) fminf(fmaxf(qx * 1024.0f, 0.0f), 1023.0f), cy = (uint32_t) fminf(fmaxf(qy * 1024.0f, 0.0f), 1023.0f), cz = (uint32_t) fminf(fmaxf(qz * 1024.0f, 0.0f), 1023.0f);
+    return spread10(cx) | (spread10(cy) << 1) | (spread10(cz) << 2);
+}
+#ifndef B2_POOL_SORT
+#define B2_POOL_SORT 0                // 1: the active pool vertices (<= 2048 of them) in position order instead of pool order
+#endif
+#ifndef B2_CV_KEY_NORMAL
+#define B2_CV_KEY_NORMAL 0            // 1: eye-vertex sort key = 27-bit position code + octant of the normal
+#endif
 // Single block: pre-test records of the pool vertices with |throughput| >= 1e-6, in ascending pool order (deterministic).
 __global__ void __launch_bounds__(1024) k_pool_active(RenderCtx c) {
     __shared__ int s_warp[32];
@@ -89,27 +107,47 @@ __global__ void __launch_bounds__(1024) k_pool_active(RenderCtx c) {
         rec[0] = make_float4(0.0f, 0.0f, 0.0f, B2_NO_GATE); rec[1] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); rec[2] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     }
     if (threadIdx.x == 0) *c.n_pool_active = n;
+#if B2_POOL_SORT
+    // position order: the pool vertices a warp's 32 (neighbouring) eye vertices meet in one pre-test window are neighbours too
+    __shared__ uint32_t s_key[2048];
+    if (n > 1 && n <= 2048) {
+        float4 r[2][B2_PRE_F4]; int rank[2] = { 0, 0 };
+        for (int k = 0; k < 2; ++k) {
+            const int t = threadIdx.x + k * 1024;
+            if (t < n) {
+                for (int j = 0; j < B2_PRE_F4; ++j) r[k][j] = c.pre[(size_t) B2_PRE_F4 * t + j];
+                s_key[t] = morton30(c.sc, r[k][0].x, r[k][0].y, r[k][0].z);
+            }
+        }
+        __syncthreads();
+        for (int k = 0; k < 2; ++k) {
+            const int t = threadIdx.x + k * 1024;
+            if (t < n) { const uint32_t kt = s_key[t]; int cnt = 0; for (int u = 0; u < n; ++u) { const uint32_t ku = s_key[u]; cnt += (ku < kt || (ku == kt && u < t)) ? 1 : 0; } rank[k] = cnt; }
+        }
+        __syncthreads();
+        for (int k = 0; k < 2; ++k) {
+            const int t = threadIdx.x + k * 1024;
+            if (t < n) for (int j = 0; j < B2_PRE_F4; ++j) c.pre[(size_t) B2_PRE_F4 * rank[k] + j] = r[k][j];
+        }
+    }
+#endif
 }
 
 // Connection stage on position-sorted eye vertices (B2_CONN_SORT_CV; A/B in profiles/r02_connect_summary.md, section 5): a work
 // item of k_connect is 32 CONSECUTIVE records, whose shadow rays to one pool vertex share BVH nodes only if the 32 vertices are
 // close together -- true for primary hits of neighbouring pixels, not after a bounce.  Key = 30-bit Morton code of the position
 // inside the scene box; records past n_cv (the launch is sized by the host's upper bound n_live) sort last.
-__device__ __forceinline__ uint32_t spread10(uint32_t x) {
-    x &= 0x3ffu;
-    x = (x | (x << 16)) & 0x030000ffu; x = (x | (x << 8)) & 0x0300f00fu; x = (x | (x << 4)) & 0x030c30c3u; x = (x | (x << 2)) & 0x09249249u;
-    return x;
-}
 __global__ void __launch_bounds__(256) k_cv_keys(RenderCtx c, uint32_t n_upper, uint32_t *__restrict__ keys, uint32_t *__restrict__ idx) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_upper) return;
     uint32_t key = 1u << 30;
     if ((int) i < *c.n_cv) {
         const float4 f0 = c.cv[B2_CV_F4 * (size_t) i];
-        const float3 lo = c.sc.scene_min, hi = c.sc.scene_max;
-        const float qx = (f0.x - lo.x) / fmaxf(hi.x - lo.x, 1e-30f), qy = (f0.y - lo.y) / fmaxf(hi.y - lo.y, 1e-30f), qz = (f0.z - lo.z) / fmaxf(hi.z - lo.z, 1e-30f);
-        const uint32_t cx = (uint32_t) fminf(fmaxf(qx * 1024.0f, 0.0f), 1023.0f), cy = (uint32_t) fminf(fmaxf(qy * 1024.0f, 0.0f), 1023.0f), cz = (uint32_t) fminf(fmaxf(qz * 1024.0f, 0.0f), 1023.0f);
-        key = spread10(cx) | (spread10(cy) << 1) | (spread10(cz) << 2);
+        key = morton30(c.sc, f0.x, f0.y, f0.z);
+#if B2_CV_KEY_NORMAL
+        const float4 f1 = c.cv[B2_CV_F4 * (size_t) i + 1];
+        key = (key & ~7u) | (f1.x < 0.0f ? 1u : 0u) | (f1.y < 0.0f ? 2u : 0u) | (f1.z < 0.0f ? 4u : 0u);   // lowest position bits -> normal octant
+#endif
     }
     keys[i] = key; idx[i] = i;
 }
