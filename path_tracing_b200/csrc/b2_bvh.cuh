@@ -127,6 +127,9 @@ B2_HD void node_test(const DevScene &sc, uint32_t node, const RayPre &r, float t
 
 // The still-unvisited part of the tree: the current group of hit children plus the shared-memory stack of older groups.
 struct TravPos { int sp; uint2 grp; uint32_t node; bool have; };
+#ifdef B2_TRACK_STACK_DEPTH
+static int b2_max_stack_depth = 0;
+#endif
 B2_HD void trav_reset(TravPos &p, bool has_root) { p.sp = 0; p.grp = make_uint2(0u, 0u); p.node = 0u; p.have = has_root; }
 // Makes p.node the next wide node to test (the root at first, then the nearest unvisited hit child); false = exhausted.
 B2_HD bool trav_next(TravPos &p, uint32_t oct, const uint2 *stack, int sstride) {
@@ -144,6 +147,9 @@ B2_HD bool trav_next(TravPos &p, uint32_t oct, const uint2 *stack, int sstride) 
 B2_HD void trav_push(TravPos &p, uint32_t hits_p, uint32_t child_base, uint32_t imask, uint2 *stack, int sstride) {
     if (hits_p) {
         if ((p.grp.y >> 8) != 0u && p.sp < B2_STACK_CAP) stack[(p.sp++) * sstride] = p.grp;
+#ifdef B2_TRACK_STACK_DEPTH         // host compilation of the tests only: the deepest stack any walk reached (tests/hostsim)
+        if (p.sp > b2_max_stack_depth) b2_max_stack_depth = p.sp;
+#endif
         p.grp = make_uint2(child_base, (hits_p << 8) | imask);
     }
 }

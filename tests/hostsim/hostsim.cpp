@@ -2,6 +2,7 @@
 // Purpose: debug the BVH build, the traversal and the wavefront stage logic on the CPU-only dev box, and
 // compare them with the oracle in `-m "not gpu"` tests.  This library is NOT part of the product: libb2pt.so
 // contains no host execution path, and nothing under path_tracing_b200/ loads this file.
+#define B2_TRACK_STACK_DEPTH 1      // csrc/b2_bvh.cuh records the deepest traversal stack (hs_max_stack_depth)
 #include "hostsim_bvh.hpp"
 #include <cstdio>
 
@@ -47,6 +48,9 @@ static int public_id(const DevScene &sc, int prim) {
     return -2 - i;
 }
 // mode: 0 closest BVH, 1 any BVH, 16 closest brute, 17 any brute.  counters: [nodes, tris] totals (may be NULL)
+// deepest traversal stack (entries) any walk of this library reached since the last reset
+int hs_max_stack_depth(int reset) { const int d = b2_max_stack_depth; if (reset) b2_max_stack_depth = 0; return d; }
+
 void hs_intersect(void *h, const float *org, const float *dir, size_t n, int mode, int32_t *prim_id, float *t, uint64_t *counters) {
     HsScene *s = (HsScene *) h;
     const DevScene &sc = s->view;

@@ -58,6 +58,11 @@ class HostSim:
                                    len(data.materials), A.ptr(data.lights), len(data.lights), max_leaf, pad_rel)
         assert self.h
 
+    def max_stack_depth(self, reset=False):
+        """Deepest traversal stack (entries) any walk of the host library reached since the last reset (process-wide)."""
+        self.L.hs_max_stack_depth.argtypes = [C.c_int]; self.L.hs_max_stack_depth.restype = C.c_int
+        return int(self.L.hs_max_stack_depth(1 if reset else 0))
+
     def close(self):
         if self.h:
             self.L.hs_scene_destroy(self.h); self.h = None

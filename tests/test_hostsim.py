@@ -141,3 +141,28 @@ def test_factored_mis_weight_reproduces_the_reference_golden_weights():
     assert np.allclose(seq[live], want[live], rtol=2e-5, atol=0.0)
     assert np.allclose(fac[live], seq[live], rtol=2e-5, atol=0.0)
 
+
+def test_traversal_stacks_stay_inside_the_short_shared_memory_stacks(tmp_path):
+    """The kernels give every thread bvh_depth - 2 (+ 1 spare) stack entries of shared memory (stack_entries, csrc/b2_cuda_util.hpp):
+    a walk stacks at most one group of unvisited siblings per level between the root's children and the current node's parent.
+    The host compilation records the deepest stack of every closest-hit and any-hit walk of a BDPT render on a generated
+    mesh scene (tree of depth >= 8) and of random rays through a triangle soup."""
+    from path_tracing_b200 import gen
+    sd = SceneData.from_file(gen.write_obj_scene(str(tmp_path), n_tris=1 << 15, width=48, height=32, tex_size=64), obj_directive=True)
+    hs = HostSim(sd)
+    depth = hs.bvh_info()["depth"]
+    assert depth >= 8
+    hs.max_stack_depth(reset=True)
+    _, cnt = hs.render(48, 32, 1, 8, 8, 8, seed=2)
+    assert cnt["shadow_rays"] > 100_000
+    assert 1 <= hs.max_stack_depth() <= depth - 2
+    hs.close()
+    soup = HostSim(random_soup(20_000, 7))
+    d2 = soup.bvh_info()["depth"]
+    rng = np.random.default_rng(1)
+    org = rng.uniform(-0.2, 1.2, (20_000, 3)).astype(np.float32); dr = rng.normal(size=(20_000, 3)).astype(np.float32)
+    soup.max_stack_depth(reset=True)
+    soup.intersect(org, dr, 0); soup.intersect(org, org + dr, 1)
+    assert 1 <= soup.max_stack_depth() <= d2 - 2
+    soup.close()
+
