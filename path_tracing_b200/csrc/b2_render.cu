@@ -754,8 +754,8 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
     if (sort_cv > 0 && ws.ensure_cv_sort(max_paths) != B2_OK) { cudaGetLastError(); sort_cv = 0; }
     bool sort_probe = false; int sort_probe_vertices = 0;     // counter copy of the first launch queued / its eye-vertex count
     StageTimer tm; tm.on = p.profile_stages != 0; tm.st = st;
-    CudaEvent ev0, ev1, ev2, ev_wave, ev_pool;
-    B2_CUDA(ev0.create()); B2_CUDA(ev1.create()); B2_CUDA(ev2.create()); B2_CUDA(ev_wave.create(cudaEventDisableTiming)); B2_CUDA(ev_pool.create(cudaEventDisableTiming));
+    CudaEvent ev0, ev1, ev2, ev_wave, ev_probe;
+    B2_CUDA(ev0.create()); B2_CUDA(ev1.create()); B2_CUDA(ev2.create()); B2_CUDA(ev_wave.create(cudaEventDisableTiming)); B2_CUDA(ev_probe.create(cudaEventDisableTiming));
     B2_CUDA(cudaEventRecord(ev0, st));
     B2_CUDA(cudaMemsetAsync(ws.film.p, 0, sizeof(float) * film_floats, st));
     B2_CUDA(cudaMemsetAsync(ws.counters.p, 0, sizeof(unsigned long long) * B2_CNT_N, st));
@@ -816,7 +816,7 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
                     const bool pool = conn_pool;
                     RenderCtx cc = c;
                     if (sort_cv < 0 && sort_probe) {            // second connection launch: the first one's counter is (nearly) there --
-                        B2_CUDA(cudaEventSynchronize(ev_pool));  // the extend launch queued above keeps the GPU busy meanwhile
+                        B2_CUDA(cudaEventSynchronize(ev_probe));  // the extend launch queued above keeps the GPU busy meanwhile
                         unsigned long long rays; memcpy(&rays, ws.h_ints + 6, sizeof(rays));
                         sort_cv = rays >= (unsigned long long) B2_CONN_SORT_MIN_RAYS * (unsigned long long) std::max(sort_probe_vertices, 1) ? 1 : 0;
                         ws.sort_cfg = sort_cfg; ws.sort_yes = sort_cv;
@@ -834,7 +834,7 @@ int b2_render_device_impl(const DevScene &sc, int bvh_depth, RenderWorkspace &ws
                     else { if (count) k_connect<true, false><<<gc, CONN_THREADS, sb_c, st>>>(cc); else k_connect<false, false><<<gc, CONN_THREADS, sb_c, st>>>(cc); }
                     if (sort_cv < 0 && !sort_probe) {
                         B2_CUDA(cudaMemcpyAsync(ws.h_ints + 6, ws.counters.p + B2_CNT_SHADOW, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
-                        B2_CUDA(cudaEventRecord(ev_pool, st));
+                        B2_CUDA(cudaEventRecord(ev_probe, st));
                     }
                 } else {
                     const unsigned gn = (unsigned) std::min<long long>((long long) sc.n_sms * 8, blocks_for(n_live, EXT_THREADS));
